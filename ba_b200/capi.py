@@ -1,0 +1,62 @@
+"""Loader for the CUDA product library ba_b200/libba_b200.so (C ABI: include/ba_b200.h).
+
+There is no CPU fallback: if the library has not been built the import of the solver
+fails loudly, and on a box without a CUDA device every compute entry point returns
+BAGPU_ERR_NO_DEVICE (raised here as RuntimeError).
+"""
+import ctypes as C
+import os
+import subprocess
+from .abi import Binding
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+SO_PATH = os.path.join(_HERE, "libba_b200.so")
+_LIB = None
+
+EXPORTS = [
+    "create", "destroy", "last_error", "set_options", "default_options", "set_cameras", "set_poses",
+    "set_landmarks", "set_proj_residuals", "set_unary_residuals", "set_binary_residuals",
+    "set_imu_residuals", "solve", "build", "get_poses", "get_landmarks", "get_proj_residuals",
+    "get_trace", "get_deltas", "get_pattern", "get_system", "dump", "nccl_unique_id", "comm_init",
+    "get_phase_ms",
+]
+
+
+def build(force=False):
+    """Compile the sm_100a kernels in-tree (nvcc cross-compiles without a GPU)."""
+    src = os.path.join(_HERE, "csrc")
+    if force:
+        subprocess.check_call(["make", "-C", src, "-s", "clean"])
+    subprocess.check_call(["make", "-C", src, "-s", "-j8"])
+    return SO_PATH
+
+
+def lib():
+    global _LIB
+    if _LIB is None:
+        if not os.path.exists(SO_PATH):
+            raise ImportError("ba_b200/libba_b200.so is missing: run `python -c 'import __graft_entry__ as g; g.build()'` "
+                              "(the CUDA extension is the only implementation; there is no fallback)")
+        _LIB = C.CDLL(SO_PATH)
+    return _LIB
+
+
+class BundleAdjusterGPU(Binding):
+    """ba::BundleAdjuster<double, LmSize, PoseSize, 0, false> on the GPU, through the C ABI."""
+
+    def __init__(self, lm_dim, pose_dim, options=None):
+        super().__init__(lib(), "bagpu_", lm_dim, pose_dim, options)
+
+    def comm_init(self, rank, world, unique_id):
+        buf = (C.c_char * 128).from_buffer_copy(unique_id)
+        self._check(self._f("comm_init")(self.h, C.c_int(rank), C.c_int(world), buf))
+
+    @staticmethod
+    def nccl_unique_id():
+        buf = (C.c_char * 128)()
+        rc = lib().bagpu_nccl_unique_id(buf)
+        if rc != 0:
+            f = lib().bagpu_last_error
+            f.restype = C.c_char_p
+            raise RuntimeError("bagpu_nccl_unique_id: %s" % f().decode())
+        return bytes(buf)

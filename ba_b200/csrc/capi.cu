@@ -1,0 +1,1139 @@
+// capi.cu — C ABI of the B200 BundleAdjuster hot path (include/ba_b200.h) and the host
+// orchestration of one Solve() call.
+//
+// Host side of (reference file:line):
+//   Solve            src/BundleAdjuster.cpp:278-705     -> bagpu_solve
+//   BuildProblem     src/BundleAdjuster.cpp:1166-1803   -> Handle::build (mask logic literal, kernels for the rest)
+//   SolveInternal    src/BundleAdjuster.cpp:838-1161    -> Handle::solve_internal (scalars on host, vectors on device)
+// Everything numerical runs in the kernels of proj_kernels.cu / other_kernels.cu / select.cu /
+// chol.cu; there is no CPU fallback: without a CUDA device every entry point that would
+// compute returns BAGPU_ERR_NO_DEVICE.
+#include <algorithm>
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+#include <dlfcn.h>
+#include "ba_gpu.h"
+#include "device_math.cuh"
+#include "launch.h"
+
+using namespace bagpu;
+
+namespace {
+
+thread_local std::string g_err;
+int fail(int code, const std::string& msg) { g_err = msg; return code; }
+
+#define CU(x)                                                                                        \
+  do {                                                                                               \
+    cudaError_t e_ = (x);                                                                            \
+    if (e_ != cudaSuccess) throw std::string(#x) + ": " + cudaGetErrorString(e_);                    \
+  } while (0)
+
+template <typename T>
+struct DevBuf {
+  T* p = nullptr;
+  size_t n = 0;
+  ~DevBuf() { release(); }
+  void release() { if (p) cudaFree(p); p = nullptr; n = 0; }
+  void alloc(size_t count) {
+    if (count <= n && p) return;
+    release();
+    if (count == 0) count = 1;
+    CU(cudaMalloc(&p, count * sizeof(T)));
+    n = count;
+  }
+  void upload(const std::vector<T>& h, cudaStream_t st) {
+    alloc(h.size());
+    if (!h.empty()) CU(cudaMemcpyAsync(p, h.data(), h.size() * sizeof(T), cudaMemcpyHostToDevice, st));
+  }
+  void upload(const T* h, size_t count, cudaStream_t st) {
+    alloc(count);
+    if (count) CU(cudaMemcpyAsync(p, h, count * sizeof(T), cudaMemcpyHostToDevice, st));
+  }
+  void download(T* h, size_t count, cudaStream_t st) const {
+    if (count) CU(cudaMemcpyAsync(h, p, count * sizeof(T), cudaMemcpyDeviceToHost, st));
+  }
+  void zero(cudaStream_t st, size_t count = (size_t)-1) { if (p) CU(cudaMemsetAsync(p, 0, std::min(count, n) * sizeof(T), st)); }
+};
+
+// ---- NCCL through dlopen: the library must load (and export its symbols) on a box without NCCL
+struct UniqueId { char b[128]; };
+struct NcclApi {
+  void* lib = nullptr;
+  int (*getUniqueId)(UniqueId*) = nullptr;
+  int (*commInitRank)(void**, int, UniqueId, int) = nullptr;
+  int (*allReduce)(const void*, void*, size_t, int, int, void*, cudaStream_t) = nullptr;
+  int (*commDestroy)(void*) = nullptr;
+  const char* (*getErrorString)(int) = nullptr;
+  bool load() {
+    if (lib) return true;
+    const char* env = getenv("BAGPU_NCCL_LIB");
+    const char* names[] = {env, "libnccl.so.2", "libnccl.so"};
+    for (const char* nm : names) {
+      if (!nm) continue;
+      lib = dlopen(nm, RTLD_NOW | RTLD_GLOBAL);
+      if (lib) break;
+    }
+    if (!lib) return false;
+    getUniqueId = (int (*)(UniqueId*))dlsym(lib, "ncclGetUniqueId");
+    commInitRank = (int (*)(void**, int, UniqueId, int))dlsym(lib, "ncclCommInitRank");
+    allReduce = (int (*)(const void*, void*, size_t, int, int, void*, cudaStream_t))dlsym(lib, "ncclAllReduce");
+    commDestroy = (int (*)(void*))dlsym(lib, "ncclCommDestroy");
+    getErrorString = (const char* (*)(int))dlsym(lib, "ncclGetErrorString");
+    return getUniqueId && commInitRank && allReduce && commDestroy;
+  }
+};
+NcclApi g_nccl;
+constexpr int kNcclFloat64 = 8, kNcclUint32 = 3, kNcclSum = 0;  // ncclDataType_t / ncclRedOp_t values (nccl.h)
+
+}  // namespace
+
+struct bagpu_handle_s {
+  bagpu_dims dims;
+  bagpu_options opt;
+  int L = 0, D = 6;
+  bool has_device = false;
+  int sms = 148;
+  cudaStream_t st = nullptr;
+
+  // ---- host copies of the problem (the reference's poses_/landmarks_/residual vectors) ----
+  std::vector<double> cam_params, cam_tvs;
+  std::vector<double> pose_t7, pose_v, pose_b;
+  std::vector<uint8_t> pose_active, pose_mask_used, pose_mask;   // mask: D per pose, 1 = free
+  std::vector<double> lm_xw, lm_xs;
+  std::vector<uint32_t> lm_ref_pose, lm_ref_cam;
+  std::vector<uint8_t> lm_active, lm_reliable;
+  std::vector<uint32_t> lm_outliers;
+  std::vector<double> proj_z, proj_w0;
+  std::vector<uint32_t> proj_pose, proj_lm, proj_cam;
+  std::vector<uint32_t> un_pose; std::vector<double> un_t, un_cov_inv; std::vector<uint8_t> un_rot;
+  std::vector<uint32_t> bin_p1, bin_p2; std::vector<double> bin_t, bin_cov_inv, bin_w; std::vector<uint8_t> bin_rot;
+  std::vector<uint32_t> imu_p1, imu_p2, imu_ms; std::vector<double> imu_meas, imu_w;
+  bool dirty = true;
+  bool solved_once = false;
+
+  // ---- derived host data ----
+  int n_cams = 0, n_poses = 0, n_lms = 0, n_obs = 0, n_obs_total = 0, n_ap = 0, n_al = 0;
+  int lm_owner_lo = 0, lm_owner_hi = 0;
+  std::vector<int> pose_opt, lm_opt;
+  std::vector<uint8_t> pose_has_res;     // any residual in the pose's lists
+  std::vector<uint8_t> pose_has_imu;
+  std::vector<uint32_t> lm_obs_start, obs_perm;
+  int G = 8;
+  int nT = 0, T = 48, n_tiles = 0, max_row = 0;
+  std::vector<int> tile_map, row_ptr, row_col;
+  double trust_region = -1;
+  bool is_param_mask_used = false;
+
+  // ---- device buffers ----
+  DevBuf<double> d_cam_params, d_cam_Rvs, d_cam_tvs;
+  DevBuf<double> d_pose_q, d_pose_t, d_pose_v, d_pose_b, d_Tsw, d_Tws, d_Rwp;
+  DevBuf<double> d_bk_q, d_bk_t, d_bk_v, d_bk_b, d_bk_lm_x; DevBuf<uint8_t> d_bk_rel;
+  DevBuf<int> d_pose_opt, d_lm_opt; DevBuf<uint32_t> d_pose_free; DevBuf<uint8_t> d_pose_mask_used;
+  DevBuf<double> d_lm_x, d_lm_xw; DevBuf<uint32_t> d_lm_ref_pose, d_lm_ref_cam, d_lm_outliers, d_lm_obs_start;
+  DevBuf<uint8_t> d_lm_reliable;
+  DevBuf<double2> d_obs_z; DevBuf<uint32_t> d_obs_pose, d_obs_cam, d_obs_perm; DevBuf<double> d_obs_w0, d_obs_maha0, d_obs_w, d_obs_W;
+  DevBuf<double> d_lm_Vinv, d_lm_bl, d_lm_Wref;
+  DevBuf<double> d_S, d_S_copy, d_uinv, d_scratch, d_bp, d_rhs_sc, d_rhs_work;
+  DevBuf<int> d_tile_map, d_row_ptr, d_row_col, d_fail;
+  DevBuf<Scalars> d_sc; DevBuf<SelectState> d_sel;
+  DevBuf<double> d_bl_compact, d_gn_p, d_gn_l, d_dl_p, d_dl_l, d_tmp_p, d_tmp_l;
+  DevBuf<double> d_res_out, d_maha_out;
+  // other residuals
+  DevBuf<uint32_t> d_un_pose, d_bin_p1, d_bin_p2, d_imu_p1, d_imu_p2, d_imu_ms;
+  DevBuf<double> d_un_t, d_un_cov_inv, d_un_maha, d_bin_t, d_bin_cov_inv, d_bin_w, d_imu_meas, d_imu_w;
+  DevBuf<double> d_imu_cov_inv, d_imu_J1, d_imu_J2, d_imu_res;
+  DevBuf<uint8_t> d_un_rot, d_bin_rot;
+
+  DeviceProblem P;
+  OtherResiduals R;
+
+  // ---- results ----
+  bagpu_summary summary;
+  std::vector<bagpu_iter_trace> trace;
+  std::vector<std::vector<double>> rec_dp, rec_dl;
+  double proj_error = 0, binary_error = 0, unary_error = 0, inertial_error = 0;
+  float phase_ms[BAGPU_PH_COUNT] = {0};
+  uint64_t launches = 0;
+  cudaEvent_t ev[16];
+  bool ev_ok = false;
+  bool keep_S_copy = false;
+
+  // ---- multi-GPU ----
+  void* comm = nullptr;
+  int rank = 0, world = 1;
+
+  // =======================================================================================
+  void sync() { CU(cudaStreamSynchronize(st)); }
+
+  void ensure_device() {
+    if (has_device) return;
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess || n == 0) throw std::string("no CUDA device (the product path has no CPU fallback)");
+    cudaDeviceProp prop;
+    int dev = 0;
+    CU(cudaGetDevice(&dev));
+    CU(cudaGetDeviceProperties(&prop, dev));
+    sms = prop.multiProcessorCount;
+    set_sm_count(sms);
+    CU(cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking));
+    for (auto& e : ev) CU(cudaEventCreate(&e));
+    ev_ok = true;
+    has_device = true;
+  }
+
+  // ---- symbolic set-up: ids, landmark-major observation order, tile pattern of S ----------
+  void setup() {
+    n_cams = (int)cam_params.size() / 4;
+    n_poses = (int)pose_t7.size() / 7;
+    n_lms = (int)lm_xw.size() / 4;
+    n_obs = (int)proj_pose.size();
+    if (n_cams == 0) { n_cams = 1; cam_params = {1, 1, 0, 0}; cam_tvs = {0, 0, 0, 1, 0, 0, 0}; }
+    pose_opt.assign(n_poses, -1); n_ap = 0;
+    for (int i = 0; i < n_poses; ++i) if (pose_active[i]) pose_opt[i] = n_ap++;
+    lm_opt.assign(n_lms, -1); n_al = 0;
+    for (int i = 0; i < n_lms; ++i) if (lm_active[i]) lm_opt[i] = n_al++;
+    // residual membership per pose (reference BundleAdjuster.h:490-497, :405, :452-453, :537-538)
+    pose_has_res.assign(n_poses, 0); pose_has_imu.assign(n_poses, 0);
+    for (int i = 0; i < n_obs; ++i) {
+      const uint32_t m = proj_pose[i], r = lm_ref_pose[proj_lm[i]];
+      const bool diff = m != r;
+      if (diff || L != 1) { pose_has_res[m] = 1; if (L == 1) pose_has_res[r] = 1; }
+    }
+    for (uint32_t p : un_pose) pose_has_res[p] = 1;
+    for (size_t i = 0; i < bin_p1.size(); ++i) { pose_has_res[bin_p1[i]] = 1; pose_has_res[bin_p2[i]] = 1; }
+    for (size_t i = 0; i < imu_p1.size(); ++i) { pose_has_res[imu_p1[i]] = 1; pose_has_res[imu_p2[i]] = 1; pose_has_imu[imu_p1[i]] = 1; pose_has_imu[imu_p2[i]] = 1; }
+    // observations sorted by landmark (stable counting sort keeps residual ids ascending)
+    lm_obs_start.assign(n_lms + 1, 0);
+    for (int i = 0; i < n_obs; ++i) lm_obs_start[proj_lm[i] + 1]++;
+    for (int l = 0; l < n_lms; ++l) lm_obs_start[l + 1] += lm_obs_start[l];
+    obs_perm.resize(n_obs);
+    {
+      std::vector<uint32_t> cur(lm_obs_start.begin(), lm_obs_start.end() - 1);
+      for (int i = 0; i < n_obs; ++i) obs_perm[cur[proj_lm[i]]++] = i;
+    }
+    n_obs_total = n_obs;
+    int lms_with_obs = 0;
+    for (int l = 0; l < n_lms; ++l) lms_with_obs += lm_obs_start[l + 1] > lm_obs_start[l];
+    const double mean_track = lms_with_obs ? (double)n_obs / lms_with_obs : 0.0;
+    G = mean_track <= 4 ? 4 : mean_track <= 8 ? 8 : mean_track <= 16 ? 16 : 32;
+
+    // ---- tile pattern of S (upper), symbolic fill ----
+    T = kTilePoses * D;
+    nT = (n_ap + kTilePoses - 1) / kTilePoses;
+    std::vector<std::vector<uint8_t>> present(nT, std::vector<uint8_t>(nT, 0));
+    for (int k = 0; k < nT; ++k) present[k][k] = 1;
+    {
+      std::vector<int> tl;
+      for (int l = 0; l < n_lms; ++l) {
+        if (lm_opt[l] < 0 && L != 1) {}
+        tl.clear();
+        const int rp = (int)lm_ref_pose[l];
+        for (uint32_t e = lm_obs_start[l]; e < lm_obs_start[l + 1]; ++e) {
+          const int m = (int)proj_pose[obs_perm[e]];
+          if (m != rp && pose_opt[m] >= 0) tl.push_back(pose_opt[m] / kTilePoses);
+        }
+        if (L == 1 && pose_opt[rp] >= 0 && !tl.empty()) tl.push_back(pose_opt[rp] / kTilePoses);
+        std::sort(tl.begin(), tl.end());
+        tl.erase(std::unique(tl.begin(), tl.end()), tl.end());
+        for (size_t a = 0; a < tl.size(); ++a) for (size_t b = a; b < tl.size(); ++b) present[tl[a]][tl[b]] = 1;
+      }
+      auto mark = [&](uint32_t p1, uint32_t p2) {
+        const int o1 = pose_opt[p1], o2 = pose_opt[p2];
+        if (o1 < 0 || o2 < 0) return;
+        const int a = std::min(o1, o2) / kTilePoses, b = std::max(o1, o2) / kTilePoses;
+        present[a][b] = 1;
+      };
+      for (size_t i = 0; i < bin_p1.size(); ++i) mark(bin_p1[i], bin_p2[i]);
+      for (size_t i = 0; i < imu_p1.size(); ++i) mark(imu_p1[i], imu_p2[i]);
+    }
+    for (int k = 0; k < nT; ++k) {   // fill: eliminating tile row k couples every pair of its columns
+      std::vector<int> cols;
+      for (int j = k + 1; j < nT; ++j) if (present[k][j]) cols.push_back(j);
+      for (size_t a = 0; a < cols.size(); ++a) for (size_t b = a; b < cols.size(); ++b) present[cols[a]][cols[b]] = 1;
+    }
+    // ---- landmark sharding: contiguous landmark ranges balanced by observation
+    // count; the tile pattern above is global so the value arrays line up across ranks ----
+    lm_owner_lo = 0; lm_owner_hi = n_lms;
+    if (world > 1) {
+      const double per = (double)n_obs_total / world;
+      int lo = 0, hi = n_lms;
+      for (int l = 0; l <= n_lms; ++l) {
+        if ((double)lm_obs_start[l] <= per * rank) lo = l;
+        if ((double)lm_obs_start[l] <= per * (rank + 1)) hi = l;
+      }
+      if (rank == world - 1) hi = n_lms;
+      if (rank == 0) lo = 0;
+      lm_owner_lo = lo; lm_owner_hi = hi;
+      std::vector<uint32_t> ns(n_lms + 1, 0), np;
+      for (int l = lo; l < hi; ++l) for (uint32_t e = lm_obs_start[l]; e < lm_obs_start[l + 1]; ++e) np.push_back(obs_perm[e]);
+      uint32_t acc = 0;
+      for (int l = 0; l < n_lms; ++l) { ns[l] = acc; if (l >= lo && l < hi) acc += lm_obs_start[l + 1] - lm_obs_start[l]; }
+      ns[n_lms] = acc;
+      lm_obs_start.swap(ns); obs_perm.swap(np);
+      n_obs = (int)obs_perm.size();
+    }
+    tile_map.assign((size_t)nT * nT, -1);
+    row_ptr.assign(nT + 1, 0); row_col.clear();
+    n_tiles = 0; max_row = 0;
+    for (int k = 0; k < nT; ++k) {
+      tile_map[(size_t)k * nT + k] = n_tiles++;
+      for (int j = k + 1; j < nT; ++j) if (present[k][j]) { tile_map[(size_t)k * nT + j] = n_tiles++; row_col.push_back(j); }
+      row_ptr[k + 1] = (int)row_col.size();
+      max_row = std::max(max_row, row_ptr[k + 1] - row_ptr[k]);
+    }
+  }
+
+  void upload_all() {
+    // cameras
+    std::vector<double> Rvs(9 * n_cams), tvs(3 * n_cams);
+    for (int c = 0; c < n_cams; ++c) {
+      quat_to_R(&cam_tvs[7 * c], &Rvs[9 * c]);
+      for (int k = 0; k < 3; ++k) tvs[3 * c + k] = cam_tvs[7 * c + 4 + k];
+    }
+    d_cam_params.upload(cam_params, st); d_cam_Rvs.upload(Rvs, st); d_cam_tvs.upload(tvs, st);
+    // poses
+    std::vector<double> q(4 * n_poses), t(3 * n_poses);
+    for (int i = 0; i < n_poses; ++i) { for (int k = 0; k < 4; ++k) q[4 * i + k] = pose_t7[7 * i + k]; for (int k = 0; k < 3; ++k) t[3 * i + k] = pose_t7[7 * i + 4 + k]; }
+    d_pose_q.upload(q, st); d_pose_t.upload(t, st); d_pose_v.upload(pose_v, st); d_pose_b.upload(pose_b, st);
+    d_bk_q.alloc(q.size()); d_bk_t.alloc(t.size()); d_bk_v.alloc(pose_v.size()); d_bk_b.alloc(pose_b.size());
+    d_pose_opt.upload(pose_opt, st); d_pose_free.alloc(n_poses); d_pose_mask_used.alloc(n_poses);
+    d_Tsw.alloc((size_t)n_poses * n_cams * 12); d_Tws.alloc((size_t)n_poses * n_cams * 12); d_Rwp.alloc((size_t)n_poses * 9);
+    // landmarks
+    d_lm_xw.upload(lm_xw, st); d_lm_x.alloc(lm_xw.size()); d_bk_lm_x.alloc(lm_xw.size());
+    d_lm_ref_pose.upload(lm_ref_pose, st); d_lm_ref_cam.upload(lm_ref_cam, st); d_lm_opt.upload(lm_opt, st);
+    d_lm_reliable.upload(lm_reliable, st); d_bk_rel.alloc(lm_reliable.size()); d_lm_outliers.alloc(n_lms);
+    d_lm_outliers.zero(st);
+    d_lm_obs_start.upload(lm_obs_start, st);
+    // observations in landmark order
+    std::vector<double2> z(n_obs); std::vector<uint32_t> op(n_obs), oc(n_obs); std::vector<double> w0(n_obs);
+    bool multi_cam = n_cams > 1;
+    for (int i = 0; i < n_obs; ++i) {
+      const uint32_t r = obs_perm[i];
+      z[i] = make_double2(proj_z[2 * r], proj_z[2 * r + 1]); op[i] = proj_pose[r]; oc[i] = proj_cam[r]; w0[i] = proj_w0[r];
+    }
+    d_obs_z.upload(z, st); d_obs_pose.upload(op, st); d_obs_w0.upload(w0, st); d_obs_perm.upload(obs_perm, st);
+    if (multi_cam) d_obs_cam.upload(oc, st);
+    d_obs_maha0.alloc(n_obs); d_obs_w.alloc(n_obs); d_obs_W.alloc((size_t)n_obs * 6 * std::max(1, L));
+    const int Ls = std::max(1, L);
+    d_lm_Vinv.alloc((size_t)n_lms * Ls * Ls); d_lm_bl.alloc((size_t)n_lms * Ls); d_lm_Wref.alloc((size_t)n_lms * 6 * Ls);
+    d_lm_bl.zero(st);
+    // reduced system
+    const size_t tsz = (size_t)T * T;
+    d_S.alloc((size_t)n_tiles * tsz); d_uinv.alloc((size_t)nT * tsz); d_scratch.alloc((size_t)std::max(1, max_row) * tsz);
+    d_bp.alloc((size_t)nT * T); d_rhs_sc.alloc((size_t)nT * T); d_rhs_work.alloc((size_t)nT * T);
+    d_tile_map.upload(tile_map, st); d_row_ptr.upload(row_ptr, st); d_row_col.upload(row_col, st); d_fail.alloc(1);
+    d_sc.alloc(1); d_sc.zero(st); d_sel.alloc(1);
+    d_bl_compact.alloc((size_t)n_al * Ls); d_gn_p.alloc((size_t)nT * T); d_gn_l.alloc((size_t)n_al * Ls);
+    d_dl_p.alloc((size_t)nT * T); d_dl_l.alloc((size_t)n_al * Ls); d_tmp_p.alloc((size_t)nT * T); d_tmp_l.alloc((size_t)n_al * Ls);
+    d_gn_p.zero(st); d_gn_l.zero(st); d_dl_p.zero(st); d_dl_l.zero(st); d_bl_compact.zero(st);
+    // other residuals
+    d_un_pose.upload(un_pose, st); d_un_t.upload(un_t, st); d_un_cov_inv.upload(un_cov_inv, st); d_un_rot.upload(un_rot, st); d_un_maha.alloc(un_pose.size());
+    d_bin_p1.upload(bin_p1, st); d_bin_p2.upload(bin_p2, st); d_bin_t.upload(bin_t, st); d_bin_cov_inv.upload(bin_cov_inv, st);
+    d_bin_w.upload(bin_w, st); d_bin_rot.upload(bin_rot, st);
+    d_imu_p1.upload(imu_p1, st); d_imu_p2.upload(imu_p2, st); d_imu_ms.upload(imu_ms, st); d_imu_meas.upload(imu_meas, st); d_imu_w.upload(imu_w, st);
+    const size_t ni = imu_p1.size();
+    d_imu_cov_inv.alloc(ni * D * D); d_imu_J1.alloc(ni * D * D); d_imu_J2.alloc(ni * D * D); d_imu_res.alloc(ni * D);
+
+    memset(&P, 0, sizeof(P));
+    P.L = L; P.D = D; P.n_cams = n_cams; P.n_poses = n_poses; P.n_active_poses = n_ap; P.n_lms = n_lms; P.n_active_lms = n_al; P.n_obs = n_obs;
+    P.n_unary = (int)un_pose.size(); P.n_binary = (int)bin_p1.size(); P.n_imu = (int)imu_p1.size();
+    P.cam_params = d_cam_params.p; P.cam_Rvs = d_cam_Rvs.p; P.cam_tvs = d_cam_tvs.p;
+    P.pose_q = d_pose_q.p; P.pose_t = d_pose_t.p; P.pose_v = d_pose_v.p; P.pose_b = d_pose_b.p; P.pose_opt = d_pose_opt.p; P.pose_free = d_pose_free.p;
+    P.Tsw = d_Tsw.p; P.Tws = d_Tws.p; P.Rwp = d_Rwp.p;
+    P.lm_x = d_lm_x.p; P.lm_ref_pose = d_lm_ref_pose.p; P.lm_ref_cam = d_lm_ref_cam.p; P.lm_opt = d_lm_opt.p; P.lm_reliable = d_lm_reliable.p;
+    P.lm_outliers = d_lm_outliers.p; P.lm_obs_start = d_lm_obs_start.p;
+    P.obs_z = d_obs_z.p; P.obs_pose = d_obs_pose.p; P.obs_cam = multi_cam ? d_obs_cam.p : nullptr; P.obs_w0 = d_obs_w0.p; P.obs_perm = d_obs_perm.p;
+    P.obs_maha0 = d_obs_maha0.p; P.obs_w = d_obs_w.p; P.obs_W = d_obs_W.p;
+    P.lm_Vinv = d_lm_Vinv.p; P.lm_bl = d_lm_bl.p; P.lm_Wref = d_lm_Wref.p;
+    P.S_tiles = d_S.p; P.tile_map = d_tile_map.p; P.nT = nT; P.T = T; P.b_p = d_bp.p; P.rhs_sc = d_rhs_sc.p; P.sc = d_sc.p;
+    P.c_huber_factor = 1.2107; P.use_robust = opt.use_robust_norm_for_proj_residuals; P.outlier_threshold = opt.projection_outlier_threshold;
+
+    memset(&R, 0, sizeof(R));
+    R.n_unary = P.n_unary; R.n_binary = P.n_binary; R.n_imu = P.n_imu;
+    R.un_pose = d_un_pose.p; R.un_t = d_un_t.p; R.un_cov_inv = d_un_cov_inv.p; R.un_use_rot = d_un_rot.p; R.un_maha = d_un_maha.p;
+    R.bin_p1 = d_bin_p1.p; R.bin_p2 = d_bin_p2.p; R.bin_t12 = d_bin_t.p; R.bin_cov_inv = d_bin_cov_inv.p; R.bin_weight = d_bin_w.p; R.bin_use_rot = d_bin_rot.p;
+    R.imu_p1 = d_imu_p1.p; R.imu_p2 = d_imu_p2.p; R.imu_meas_start = d_imu_ms.p; R.imu_meas = d_imu_meas.p; R.imu_weight = d_imu_w.p;
+    R.imu_cov_inv = d_imu_cov_inv.p; R.imu_J1 = d_imu_J1.p; R.imu_J2 = d_imu_J2.p; R.imu_res = d_imu_res.p;
+    for (int k = 0; k < 3; ++k) R.gravity[k] = opt.gravity[k];
+    for (int k = 0; k < 3; ++k) {
+      R.imu_r[k] = opt.gyro_sigma * opt.gyro_sigma; R.imu_r[3 + k] = opt.accel_sigma * opt.accel_sigma;
+      R.imu_rb[k] = opt.gyro_bias_sigma * opt.gyro_bias_sigma; R.imu_rb[3 + k] = opt.accel_bias_sigma * opt.accel_bias_sigma;
+    }
+    dirty = false;
+  }
+
+  // ---- parameter masks, literal from src/BundleAdjuster.cpp:1237-1330 ------------------------
+  uint32_t gravity_reg_dim(const double* q) {   // BundleAdjuster.h:634-652
+    double Rm[9];
+    quat_to_R(q, Rm);
+    double max_dot = 0; uint32_t max_dim = 0;
+    for (uint32_t ii = 0; ii < 3; ++ii) {
+      const double d = std::fabs(Rm[ii] * opt.gravity[0] + Rm[3 + ii] * opt.gravity[1] + Rm[6 + ii] * opt.gravity[2]);
+      if (d > max_dot) { max_dot = d; max_dim = ii; }
+    }
+    return max_dim + 3;
+  }
+
+  void compute_masks() {
+    const bool vel = D >= 9, bias = D >= 15;
+    bool are_all_active = true;
+    for (int i = 0; i < n_poses; ++i) {
+      if (!pose_active[i]) { are_all_active = false; break; }      // quirk Q8
+      if (!pose_has_res[i]) { pose_mask_used[i] = 1; for (int k = 0; k < D; ++k) pose_mask[(size_t)i * D + k] = 0; }
+    }
+    if (vel) {
+      for (int i = 0; i < n_poses; ++i) {
+        if (!pose_has_imu[i] && pose_active[i]) {
+          pose_mask_used[i] = 1;
+          for (int k = 0; k < D; ++k) pose_mask[(size_t)i * D + k] = 1;
+          pose_mask[(size_t)i * D + 6] = pose_mask[(size_t)i * D + 7] = pose_mask[(size_t)i * D + 8] = 0;
+          if (bias) for (int k = 9; k < 15; ++k) pose_mask[(size_t)i * D + k] = 0;
+        }
+      }
+    }
+    if (are_all_active && un_pose.empty() && opt.enable_auto_regularization && n_poses > 0) {
+      const int r = (int)opt.root_pose_id;
+      uint8_t* m = &pose_mask[(size_t)r * D];
+      pose_mask_used[r] = 1;
+      for (int k = 0; k < D; ++k) m[k] = 1;
+      m[0] = m[1] = m[2] = 0;
+      if (bias && opt.regularize_biases_in_batch) for (int k = 9; k < 15; ++k) m[k] = 0;
+      if (!vel) {
+        m[3] = m[4] = m[5] = 0;
+      } else {
+        double q[4];
+        CU(cudaMemcpyAsync(q, d_pose_q.p + 4 * (size_t)r, 4 * sizeof(double), cudaMemcpyDeviceToHost, st));
+        sync();
+        m[gravity_reg_dim(q)] = 0;
+      }
+    }
+    std::vector<uint32_t> fr(n_poses, 0);
+    is_param_mask_used = false;
+    for (int i = 0; i < n_poses; ++i) {
+      uint32_t bits = (D >= 32) ? 0xffffffffu : ((1u << D) - 1u);
+      if (pose_mask_used[i]) {
+        bits = 0;
+        for (int k = 0; k < D; ++k) if (pose_mask[(size_t)i * D + k]) bits |= (1u << k);
+        if (pose_active[i] && pose_has_res[i]) is_param_mask_used = true;
+      }
+      fr[i] = bits;
+    }
+    d_pose_free.upload(fr, st);
+    d_pose_mask_used.upload(pose_mask_used, st);
+  }
+
+  // ---- median of maha0 (exact) -------------------------------------------------------------
+  void run_select(const double* x, size_t n_local, unsigned long long n_total, double* out) {
+    if (n_total == 0) return;
+    launch_select_init(d_sel.p, n_total / 2, st); ++launches;
+    for (int pass = 0; pass < select_num_passes(); ++pass) {
+      launch_select_hist(x, n_local, d_sel.p, pass, sms, st); ++launches;
+      if (world > 1) allreduce_u32(d_sel.p->hist, 4096);
+      launch_select_scan(d_sel.p, pass, out, st); ++launches;
+    }
+  }
+
+  void allreduce_f64(double* buf, size_t n) {
+    if (world <= 1 || n == 0) return;
+    int rc = g_nccl.allReduce(buf, buf, n, kNcclFloat64, kNcclSum, comm, st);
+    if (rc != 0) throw std::string("ncclAllReduce(f64) failed: ") + (g_nccl.getErrorString ? g_nccl.getErrorString(rc) : "?");
+  }
+  void allreduce_u32(unsigned int* buf, size_t n) {
+    if (world <= 1 || n == 0) return;
+    int rc = g_nccl.allReduce(buf, buf, n, kNcclUint32, kNcclSum, comm, st);
+    if (rc != 0) throw std::string("ncclAllReduce(u32) failed");
+  }
+
+  // ---- BuildProblem + Schur assembly ----------------------------------------------------------
+  void build() {
+    compute_masks();
+    CU(cudaEventRecord(ev[0], st));
+    d_S.zero(st, (size_t)n_tiles * T * T); d_bp.zero(st); d_sc.zero(st);
+    launch_pose_frames(P, st); ++launches;
+    launch_residual(P, G, st); if (n_obs) ++launches;
+    CU(cudaEventRecord(ev[1], st));
+    const unsigned long long n_total = (unsigned long long)n_obs_total;   // ranks hold disjoint landmark shards
+    run_select(d_obs_maha0.p, (size_t)n_obs, n_total, &d_sc.p->median);
+    CU(cudaEventRecord(ev[2], st));
+    launch_accumulate(P, G, st); if (n_obs) ++launches;
+    CU(cudaEventRecord(ev[3], st));
+    if (rank == 0) {   // replicated residuals are added once
+      if (R.n_unary) {
+        launch_unary_maha(P, R, st); ++launches;
+        run_select(d_un_maha.p, R.n_unary, R.n_unary, &d_sc.p->unary_median);
+      }
+      launch_other_build(P, R, st, &launches);
+    }
+    CU(cudaEventRecord(ev[4], st));
+    CU(cudaMemcpyAsync(d_rhs_sc.p, d_bp.p, sizeof(double) * (size_t)nT * T, cudaMemcpyDeviceToDevice, st));
+    launch_schur(P, st); if (n_obs && n_al && n_ap) ++launches;
+    CU(cudaEventRecord(ev[5], st));
+    if (world > 1) {
+      allreduce_f64(d_S.p, (size_t)n_tiles * T * T);
+      allreduce_f64(d_bp.p, (size_t)nT * T);
+      allreduce_f64(d_rhs_sc.p, (size_t)nT * T);
+      allreduce_f64(&d_sc.p->proj_error, 8);   // proj_error .. inertial_error
+    }
+    launch_mask_diagonal(P, d_pose_mask_used.p, is_param_mask_used ? 1 : 0, st); launches += is_param_mask_used ? 2 : 1;
+    CU(cudaEventRecord(ev[6], st));
+    if (keep_S_copy) {
+      d_S_copy.alloc((size_t)n_tiles * T * T);
+      CU(cudaMemcpyAsync(d_S_copy.p, d_S.p, sizeof(double) * (size_t)n_tiles * T * T, cudaMemcpyDeviceToDevice, st));
+    }
+  }
+
+  void collect_build_times() {
+    float ms;
+    cudaEventElapsedTime(&ms, ev[0], ev[1]); phase_ms[BAGPU_PH_RESIDUAL] += ms;
+    cudaEventElapsedTime(&ms, ev[1], ev[2]); phase_ms[BAGPU_PH_MEDIAN] += ms;
+    cudaEventElapsedTime(&ms, ev[2], ev[3]); phase_ms[BAGPU_PH_ACCUMULATE] += ms;
+    cudaEventElapsedTime(&ms, ev[3], ev[4]); phase_ms[BAGPU_PH_OTHER_RES] += ms;
+    cudaEventElapsedTime(&ms, ev[4], ev[5]); phase_ms[BAGPU_PH_ACCUMULATE] += ms;
+    cudaEventElapsedTime(&ms, ev[5], ev[6]); phase_ms[BAGPU_PH_ALLREDUCE] += ms;
+  }
+
+  Scalars read_scalars() {
+    Scalars s;
+    d_sc.download(&s, 1, st);
+    sync();
+    return s;
+  }
+
+  double dot(const double* a, const double* b, size_t n, int slot) {
+    (void)slot;
+    CU(cudaMemsetAsync(&d_sc.p->dot[0], 0, sizeof(double), st));
+    launch_dot(a, b, n, &d_sc.p->dot[0], st); if (n) ++launches;
+    double v;
+    CU(cudaMemcpyAsync(&v, &d_sc.p->dot[0], sizeof(double), cudaMemcpyDeviceToHost, st));
+    sync();
+    return v;
+  }
+  // sum over ranks of a landmark-sharded quantity
+  double shard_sum(double v) {
+    if (world <= 1) return v;
+    CU(cudaMemcpyAsync(&d_sc.p->dot[6], &v, sizeof(double), cudaMemcpyHostToDevice, st));
+    allreduce_f64(&d_sc.p->dot[6], 1);
+    CU(cudaMemcpyAsync(&v, &d_sc.p->dot[6], sizeof(double), cudaMemcpyDeviceToHost, st));
+    sync();
+    return v;
+  }
+
+  void backup_state() {
+    CU(cudaMemcpyAsync(d_bk_q.p, d_pose_q.p, sizeof(double) * 4 * n_poses, cudaMemcpyDeviceToDevice, st));
+    CU(cudaMemcpyAsync(d_bk_t.p, d_pose_t.p, sizeof(double) * 3 * n_poses, cudaMemcpyDeviceToDevice, st));
+    CU(cudaMemcpyAsync(d_bk_v.p, d_pose_v.p, sizeof(double) * 3 * n_poses, cudaMemcpyDeviceToDevice, st));
+    CU(cudaMemcpyAsync(d_bk_b.p, d_pose_b.p, sizeof(double) * 6 * n_poses, cudaMemcpyDeviceToDevice, st));
+    if (n_lms) {
+      CU(cudaMemcpyAsync(d_bk_lm_x.p, d_lm_x.p, sizeof(double) * 4 * n_lms, cudaMemcpyDeviceToDevice, st));
+      CU(cudaMemcpyAsync(d_bk_rel.p, d_lm_reliable.p, n_lms, cudaMemcpyDeviceToDevice, st));
+    }
+  }
+  void restore_state() {
+    CU(cudaMemcpyAsync(d_pose_q.p, d_bk_q.p, sizeof(double) * 4 * n_poses, cudaMemcpyDeviceToDevice, st));
+    CU(cudaMemcpyAsync(d_pose_t.p, d_bk_t.p, sizeof(double) * 3 * n_poses, cudaMemcpyDeviceToDevice, st));
+    CU(cudaMemcpyAsync(d_pose_v.p, d_bk_v.p, sizeof(double) * 3 * n_poses, cudaMemcpyDeviceToDevice, st));
+    CU(cudaMemcpyAsync(d_pose_b.p, d_bk_b.p, sizeof(double) * 6 * n_poses, cudaMemcpyDeviceToDevice, st));
+    if (n_lms) {
+      CU(cudaMemcpyAsync(d_lm_x.p, d_bk_lm_x.p, sizeof(double) * 4 * n_lms, cudaMemcpyDeviceToDevice, st));
+      CU(cudaMemcpyAsync(d_lm_reliable.p, d_bk_rel.p, n_lms, cudaMemcpyDeviceToDevice, st));
+    }
+    launch_pose_frames(P, st); ++launches;
+  }
+
+  // EvaluateResiduals at the current state (cpp:144-274); returns the four sums
+  void evaluate(double* e_proj, double* e_bin, double* e_un, double* e_in) {
+    CU(cudaMemsetAsync(&d_sc.p->eval_proj, 0, 4 * sizeof(double), st));
+    launch_evaluate(P, G, &d_sc.p->eval_proj, nullptr, nullptr, st); if (n_obs) ++launches;
+    if (rank == 0) launch_other_evaluate(P, R, st, &launches);
+    if (world > 1) allreduce_f64(&d_sc.p->eval_proj, 4);
+    double v[4];
+    CU(cudaMemcpyAsync(v, &d_sc.p->eval_proj, 4 * sizeof(double), cudaMemcpyDeviceToHost, st));
+    sync();
+    *e_proj = v[0]; *e_bin = v[1]; *e_un = v[2]; *e_in = v[3];
+  }
+
+  // CalculateGn + GetLandmarkDelta -> d_gn_p, d_gn_l
+  bool gauss_newton() {
+    CU(cudaEventRecord(ev[8], st));
+    const size_t np = (size_t)nT * T;
+    if (n_ap > 0) {
+      CU(cudaMemcpyAsync(d_rhs_work.p, d_rhs_sc.p, sizeof(double) * np, cudaMemcpyDeviceToDevice, st));
+      d_fail.zero(st);
+      launch_cholesky_solve(T, d_S.p, d_uinv.p, d_scratch.p, d_rhs_work.p, d_tile_map.p, d_row_ptr.p, d_row_col.p, row_ptr.data(), nT,
+                            d_fail.p, st, &launches);
+      CU(cudaMemcpyAsync(d_gn_p.p, d_rhs_work.p, sizeof(double) * np, cudaMemcpyDeviceToDevice, st));
+      int f = 0;
+      d_fail.download(&f, 1, st);
+      sync();
+      if (f != 0) { summary.result = BAGPU_FactorizationError; return false; }
+    }
+    summary.result = BAGPU_Success;
+    if (n_al > 0) { launch_back_substitute(P, G, d_gn_p.p, d_gn_l.p, st); ++launches; }
+    CU(cudaEventRecord(ev[9], st));
+    sync();
+    float ms; cudaEventElapsedTime(&ms, ev[8], ev[9]); phase_ms[BAGPU_PH_SOLVE] += ms;
+    return true;
+  }
+
+  // SolveInternal (cpp:838-1161)
+  bool solve_internal(double gn_damping, bool error_increase_allowed, bagpu_iter_trace& tr, const Scalars& sb) {
+    const size_t np = (size_t)n_ap * D, nl = (size_t)n_al * std::max(1, L);
+    const double pre_proj = sb.proj_error, pre_un = sb.unary_error, pre_in = sb.inertial_error;
+    bool gn_computed = false;
+    double e_proj, e_bin, e_un, e_in;
+    if (opt.use_dogleg) {
+      // steepest descent step (cpp:857-929)
+      if (L > 0 && n_al > 0) { launch_compact_bl(P, d_bl_compact.p, st); ++launches; }
+      const double n2_bp = np ? dot(d_bp.p, d_bp.p, np, 0) : 0.0;
+      const double n2_bl = shard_sum((L > 0 && nl) ? dot(d_bl_compact.p, d_bl_compact.p, nl, 1) : 0.0);
+      const double numerator = n2_bp + n2_bl;
+      CU(cudaMemsetAsync(&d_sc.p->sd_den_proj, 0, 2 * sizeof(double), st));
+      if (n_ap > 0 || n_al > 0) { launch_sd_denominator(P, G, st); if (n_obs) ++launches; }
+      if (n_ap > 0 && rank == 0) launch_other_sd(P, R, st, &launches);
+      if (world > 1) allreduce_f64(&d_sc.p->sd_den_proj, 2);
+      double den[2];
+      CU(cudaMemcpyAsync(den, &d_sc.p->sd_den_proj, 2 * sizeof(double), cudaMemcpyDeviceToHost, st));
+      sync();
+      const double denominator = den[0] + den[1];
+      const double factor = numerator / denominator;
+      const double delta_sd_norm = std::sqrt(factor * factor * n2_bp + factor * factor * n2_bl);
+      tr.sd_numerator = numerator; tr.sd_denominator = denominator; tr.sd_norm = delta_sd_norm;
+      double gn_norm2_p = 0, gn_norm2_l = 0;
+      uint32_t iteration_count = 0;
+      while (true) {
+        iteration_count++;
+        if (iteration_count > opt.dogleg_max_inner_iterations) break;
+        tr.inner_iterations = iteration_count;
+        double n2_dl_p = 0, n2_dl_l = 0;
+        if (delta_sd_norm > trust_region && trust_region != -1.0) {
+          const double f = trust_region / delta_sd_norm * factor;
+          launch_axpby(d_dl_p.p, f, d_bp.p, 0, nullptr, np, st); if (np) ++launches;
+          if (nl) { launch_axpby(d_dl_l.p, f, d_bl_compact.p, 0, nullptr, nl, st); ++launches; }
+          n2_dl_p = f * f * n2_bp; n2_dl_l = f * f * n2_bl;
+        } else {
+          if (!gn_computed) {
+            if (!gauss_newton()) return false;
+            gn_computed = true;
+            gn_norm2_p = np ? dot(d_gn_p.p, d_gn_p.p, np, 2) : 0.0;
+            gn_norm2_l = shard_sum(nl ? dot(d_gn_l.p, d_gn_l.p, nl, 3) : 0.0);
+          }
+          const double delta_gn_norm = std::sqrt(gn_norm2_p + gn_norm2_l);
+          tr.gn_norm = delta_gn_norm;
+          const bool good = !std::isnan(delta_gn_norm) && !std::isinf(delta_gn_norm);
+          if (good && trust_region == -1.0) trust_region = delta_gn_norm;
+          if (good && delta_gn_norm <= trust_region) {
+            CU(cudaMemcpyAsync(d_dl_p.p, d_gn_p.p, sizeof(double) * np, cudaMemcpyDeviceToDevice, st));
+            if (nl) CU(cudaMemcpyAsync(d_dl_l.p, d_gn_l.p, sizeof(double) * nl, cudaMemcpyDeviceToDevice, st));
+            n2_dl_p = gn_norm2_p; n2_dl_l = gn_norm2_l;
+          } else {
+            // diff = gn - sd, formed explicitly like the reference (cpp:991-1017)
+            launch_axpby(d_tmp_p.p, 1.0, d_gn_p.p, -factor, d_bp.p, np, st); if (np) ++launches;
+            if (nl) { launch_axpby(d_tmp_l.p, 1.0, d_gn_l.p, -factor, d_bl_compact.p, nl, st); ++launches; }
+            const double a = (np ? dot(d_tmp_p.p, d_tmp_p.p, np, 4) : 0.0) + shard_sum(nl ? dot(d_tmp_l.p, d_tmp_l.p, nl, 5) : 0.0);
+            const double b = 2 * ((np ? factor * dot(d_tmp_p.p, d_bp.p, np, 4) : 0.0) + shard_sum(nl ? factor * dot(d_tmp_l.p, d_bl_compact.p, nl, 5) : 0.0));
+            const double c = (factor * factor * n2_bp + factor * factor * n2_bl) - trust_region * trust_region;
+            double beta = 0;
+            if (b * b > 4 * a * c && a > 1e-10) beta = (-(b * b) + std::sqrt(b * b - 4 * a * c)) / (2 * a);   // quirk Q4
+            launch_axpby(d_dl_p.p, beta, d_tmp_p.p, factor, d_bp.p, np, st); if (np) ++launches;
+            if (nl) { launch_axpby(d_dl_l.p, beta, d_tmp_l.p, factor, d_bl_compact.p, nl, st); ++launches; }
+            n2_dl_p = np ? dot(d_dl_p.p, d_dl_p.p, np, 4) : 0.0;
+            n2_dl_l = shard_sum(nl ? dot(d_dl_l.p, d_dl_l.p, nl, 5) : 0.0);
+          }
+        }
+        CU(cudaEventRecord(ev[10], st));
+        backup_state();
+        // "pre" evaluation: same state and weights as the build, so the build sums are reused;
+        // only the binary error uses a different formula in EvaluateResiduals (quirk Q7).
+        double pre_bin = 0;
+        if (R.n_binary && rank == 0) {
+          CU(cudaMemsetAsync(&d_sc.p->eval_binary, 0, sizeof(double), st));
+          OtherResiduals Rb = R; Rb.n_unary = 0; Rb.n_imu = 0;
+          launch_other_evaluate(P, Rb, st, &launches);
+          CU(cudaMemcpyAsync(&pre_bin, &d_sc.p->eval_binary, sizeof(double), cudaMemcpyDeviceToHost, st));
+          sync();
+        }
+        summary.pre_solve_norm = pre_proj + pre_in + pre_bin + pre_un;
+        if (opt.apply_results) {
+          summary.delta_norm = std::sqrt(n2_dl_l) + std::sqrt(n2_dl_p);
+          launch_update_poses(P, d_dl_p.p, 1.0, st); ++launches;
+          launch_update_landmarks(P, d_dl_l.p, 1.0, st); if (n_lms && L) ++launches;
+          launch_pose_frames(P, st); ++launches;
+        }
+        evaluate(&e_proj, &e_bin, &e_un, &e_in);
+        summary.post_solve_norm = e_proj + e_in + e_bin + e_un;
+        tr.delta_p_norm = std::sqrt(n2_dl_p); tr.delta_l_norm = std::sqrt(n2_dl_l);
+        CU(cudaEventRecord(ev[11], st));
+        sync();
+        { float ms; cudaEventElapsedTime(&ms, ev[10], ev[11]); phase_ms[BAGPU_PH_STEP] += ms; }
+        if (summary.post_solve_norm > summary.pre_solve_norm) {
+          if (opt.apply_results) restore_state();
+          trust_region /= 2;
+        } else {
+          proj_error = e_proj; unary_error = e_un; binary_error = e_bin; inertial_error = e_in;
+          trust_region *= 2;
+          break;
+        }
+      }
+    } else {
+      // damped Gauss-Newton (cpp:1084-1159)
+      if (L > 0 && n_al > 0) { launch_compact_bl(P, d_bl_compact.p, st); ++launches; }
+      if (!gauss_newton()) return false;
+      backup_state();
+      launch_axpby(d_dl_p.p, gn_damping, d_gn_p.p, 0, nullptr, np, st); if (np) ++launches;
+      if (nl) { launch_axpby(d_dl_l.p, gn_damping, d_gn_l.p, 0, nullptr, nl, st); ++launches; }
+      const double n2p = np ? dot(d_dl_p.p, d_dl_p.p, np, 0) : 0.0, n2l = shard_sum(nl ? dot(d_dl_l.p, d_dl_l.p, nl, 1) : 0.0);
+      tr.gn_norm = std::sqrt(n2p + n2l); tr.delta_p_norm = std::sqrt(n2p); tr.delta_l_norm = std::sqrt(n2l);
+      evaluate(&e_proj, &e_bin, &e_un, &e_in);
+      const double prev_error = e_proj + e_in + e_bin + e_un;
+      if (opt.apply_results) {
+        summary.delta_norm = std::sqrt(n2l) + std::sqrt(n2p);
+        launch_update_poses(P, d_dl_p.p, 1.0, st); ++launches;
+        launch_update_landmarks(P, d_dl_l.p, 1.0, st); if (n_lms && L) ++launches;
+        launch_pose_frames(P, st); ++launches;
+      }
+      evaluate(&e_proj, &e_bin, &e_un, &e_in);
+      const double post_error = e_proj + e_in + e_bin + e_un;
+      tr.inner_iterations = 1; tr.pre_solve_norm = prev_error; tr.post_solve_norm = post_error;
+      if (post_error > prev_error && !error_increase_allowed) {
+        if (opt.apply_results) restore_state();
+        summary.result = BAGPU_ErrorIncreased;
+        return false;
+      }
+      proj_error = e_proj; unary_error = e_un; binary_error = e_bin; inertial_error = e_in;
+    }
+    return true;
+  }
+
+  void prepare_solve() {
+    ensure_device();
+    if (dirty) { setup(); upload_all(); solved_once = false; }
+    // Solve() prologue (cpp:287-296)
+    launch_pose_frames(P, st); ++launches;
+    if (L == 1) { launch_prepare_xs(P, d_lm_xw.p, st); ++launches; }
+    else if (n_lms) CU(cudaMemcpyAsync(d_lm_x.p, d_lm_xw.p, sizeof(double) * 4 * n_lms, cudaMemcpyDeviceToDevice, st));
+  }
+
+  void download_state() {
+    // poses, landmarks back into the host vectors so a second Solve() continues from here
+    std::vector<double> q(4 * n_poses), t(3 * n_poses);
+    d_pose_q.download(q.data(), q.size(), st); d_pose_t.download(t.data(), t.size(), st);
+    d_pose_v.download(pose_v.data(), pose_v.size(), st); d_pose_b.download(pose_b.data(), pose_b.size(), st);
+    if (n_lms) {
+      if (world > 1) {   // every landmark is owned by exactly one rank: zero the others and sum
+        if (lm_owner_lo > 0) CU(cudaMemsetAsync(d_lm_x.p, 0, sizeof(double) * 4 * (size_t)lm_owner_lo, st));
+        if (lm_owner_hi < n_lms) CU(cudaMemsetAsync(d_lm_x.p + 4 * (size_t)lm_owner_hi, 0, sizeof(double) * 4 * (size_t)(n_lms - lm_owner_hi), st));
+        allreduce_f64(d_lm_x.p, 4 * (size_t)n_lms);
+      }
+      if (L == 1) { launch_finish_xw(P, d_lm_xw.p, st); ++launches; }
+      else CU(cudaMemcpyAsync(d_lm_xw.p, d_lm_x.p, sizeof(double) * 4 * n_lms, cudaMemcpyDeviceToDevice, st));
+      d_lm_xw.download(lm_xw.data(), lm_xw.size(), st);
+      lm_xs.resize(lm_xw.size());
+      d_lm_x.download(lm_xs.data(), lm_xs.size(), st);
+      d_lm_reliable.download(lm_reliable.data(), lm_reliable.size(), st);
+      lm_outliers.resize(n_lms);
+      d_lm_outliers.download(lm_outliers.data(), n_lms, st);
+    }
+    sync();
+    for (int i = 0; i < n_poses; ++i) { for (int k = 0; k < 4; ++k) pose_t7[7 * i + k] = q[4 * i + k]; for (int k = 0; k < 3; ++k) pose_t7[7 * i + 4 + k] = t[3 * i + k]; }
+  }
+
+  // Solve (cpp:278-705)
+  void solve(uint32_t max_iter, double gn_damping, bool error_increase_allowed) {
+    trace.clear(); rec_dp.clear(); rec_dl.clear();
+    for (float& m : phase_ms) m = 0;
+    launches = 0;
+    summary.iterations = 0;
+    if (proj_pose.empty() && bin_p1.empty() && un_pose.empty() && imu_p1.empty()) return;
+    prepare_solve();
+    for (uint32_t kk = 0; kk < max_iter; ++kk) {
+      build();
+      const Scalars sb = read_scalars();
+      collect_build_times();
+      bagpu_iter_trace tr; memset(&tr, 0, sizeof(tr));
+      tr.proj_error_build = sb.proj_error; tr.binary_error_build = sb.binary_error;
+      tr.unary_error_build = sb.unary_error; tr.inertial_error_build = sb.inertial_error; tr.median_maha = sb.median;
+      proj_error = sb.proj_error; binary_error = sb.binary_error; unary_error = sb.unary_error; inertial_error = sb.inertial_error;
+      const bool ok = solve_internal(gn_damping, error_increase_allowed, tr, sb);
+      summary.iterations = kk + 1;
+      if (opt.use_dogleg) { tr.pre_solve_norm = summary.pre_solve_norm; tr.post_solve_norm = summary.post_solve_norm; }
+      tr.delta_norm = summary.delta_norm; tr.trust_region_after = trust_region;
+      if (opt.record_deltas) {
+        std::vector<double> dp((size_t)n_ap * D), dl((size_t)n_al * std::max(1, L));
+        d_dl_p.download(dp.data(), dp.size(), st); d_dl_l.download(dl.data(), dl.size(), st); sync();
+        rec_dp.push_back(dp); rec_dl.push_back(dl);
+      }
+      if (!ok) { tr.result = summary.result; trace.push_back(tr); break; }
+      if ((std::fabs(summary.post_solve_norm - summary.pre_solve_norm) / summary.pre_solve_norm) < opt.error_change_threshold) {
+        summary.result = BAGPU_ErrorChangeBelowThreshold; tr.result = summary.result; trace.push_back(tr); break;
+      }
+      if (summary.delta_norm < opt.param_change_threshold) {
+        summary.result = BAGPU_ParamChangeBelowThreshold; tr.result = summary.result; trace.push_back(tr); break;
+      }
+      tr.result = summary.result; trace.push_back(tr);
+    }
+    download_state();
+    solved_once = true;
+    // summary (cpp:680-704)
+    summary.num_proj_residuals = n_obs; summary.num_inertial_residuals = (uint32_t)imu_p1.size();
+    summary.proj_error = proj_error; summary.inertial_error = inertial_error; summary.unary_error = unary_error; summary.binary_error = binary_error;
+    summary.trust_region_size = trust_region;
+    uint32_t ncp = 0;
+    for (int i = 0; i < n_obs; ++i) if (!pose_active[lm_ref_pose[proj_lm[i]]] && pose_active[proj_pose[i]]) ++ncp;
+    summary.num_cond_proj_residuals = ncp;
+    uint32_t nci = 0;
+    for (size_t i = 0; i < imu_p1.size(); ++i) if (!pose_active[imu_p1[i]] && pose_active[imu_p2[i]]) ++nci;
+    summary.num_cond_inertial_residuals = nci;
+    summary.cond_proj_error = 0; summary.cond_inertial_error = 0;
+    if (ncp) {
+      std::vector<double> r(2 * (size_t)n_obs), w(n_obs), m(n_obs);
+      export_residuals(r.data(), w.data(), m.data());
+      for (int i = 0; i < n_obs; ++i)
+        if (!pose_active[lm_ref_pose[proj_lm[i]]] && pose_active[proj_pose[i]]) summary.cond_proj_error += m[i] / w[i];
+    }
+  }
+
+  void export_residuals(double* res2, double* weight, double* maha) {
+    if (n_obs == 0) return;
+    d_res_out.alloc(2 * (size_t)n_obs); d_maha_out.alloc(n_obs);
+    CU(cudaMemsetAsync(&d_sc.p->dot[5], 0, sizeof(double), st));
+    launch_evaluate(P, G, &d_sc.p->dot[5], d_res_out.p, d_maha_out.p, st); ++launches;
+    std::vector<double> wsorted(n_obs);
+    d_obs_w.download(wsorted.data(), n_obs, st);
+    if (res2) d_res_out.download(res2, 2 * (size_t)n_obs, st);
+    if (maha) d_maha_out.download(maha, n_obs, st);
+    sync();
+    if (weight) for (int i = 0; i < n_obs; ++i) weight[obs_perm[i]] = wsorted[i];
+  }
+};
+
+// ============================================================================================
+extern "C" {
+
+const char* bagpu_last_error(void) { return g_err.c_str(); }
+
+void bagpu_default_options(bagpu_options* o) {
+  memset(o, 0, sizeof(*o));
+  o->trust_region_size = -1;            // reference BundleAdjuster.h:75 (kTrustRegionAuto)
+  o->gyro_sigma = 5.3088444e-5; o->accel_sigma = 0.001883649;           // Types.h:33,35
+  o->gyro_bias_sigma = 1.4125375e-4; o->accel_bias_sigma = 1.2589254e-2;  // Types.h:34,36
+  o->projection_outlier_threshold = 1.0; o->error_change_threshold = 0.01; o->param_change_threshold = 1e-3;
+  o->dogleg_max_inner_iterations = 100; o->apply_results = 1; o->use_dogleg = 1; o->use_triangular_matrices = 1;
+  o->use_sparse_solver = 1; o->regularize_biases_in_batch = 1; o->enable_auto_regularization = 1;
+  o->use_robust_norm_for_proj_residuals = 1;
+  o->pcg_tolerance = 1e-12; o->pcg_max_iterations = 1000;
+}
+
+int bagpu_create(const bagpu_dims* d, bagpu_handle* out) {
+  if (!d || !out) return fail(BAGPU_ERR_INVALID, "null argument");
+  if (d->scalar_bytes != 8) return fail(BAGPU_ERR_UNSUPPORTED, "this build computes in double only (REAL_TYPE=double)");
+  if (d->calib_dim != 0 || d->do_tvs != 0) return fail(BAGPU_ERR_UNSUPPORTED, "CalibSize>0 / DoTvs not built (SURVEY.md §8f rank 3)");
+  if (!(d->lm_dim == 0 || d->lm_dim == 1 || d->lm_dim == 3)) return fail(BAGPU_ERR_UNSUPPORTED, "LmSize must be 0, 1 or 3");
+  if (!(d->pose_dim == 6 || d->pose_dim == 9 || d->pose_dim == 15)) return fail(BAGPU_ERR_UNSUPPORTED, "PoseSize must be 6, 9 or 15");
+  bagpu_handle h = new bagpu_handle_s();
+  h->dims = *d; h->L = d->lm_dim; h->D = d->pose_dim;
+  bagpu_default_options(&h->opt);
+  h->trust_region = h->opt.trust_region_size;
+  memset(&h->summary, 0, sizeof(h->summary));
+  *out = h;
+  return BAGPU_OK;
+}
+
+void bagpu_destroy(bagpu_handle h) {
+  if (!h) return;
+  if (h->comm && g_nccl.commDestroy) g_nccl.commDestroy(h->comm);
+  if (h->ev_ok) for (auto& e : h->ev) cudaEventDestroy(e);
+  if (h->st) cudaStreamDestroy(h->st);
+  delete h;
+}
+
+int bagpu_set_options(bagpu_handle h, const bagpu_options* o) {
+  if (!h || !o) return fail(BAGPU_ERR_INVALID, "null argument");
+  h->opt = *o;
+  h->trust_region = o->trust_region_size;   // Init(): trust_region_size_ = options_.trust_region_size (BundleAdjuster.h:193)
+  h->dirty = true;
+  return BAGPU_OK;
+}
+
+int bagpu_set_cameras(bagpu_handle h, uint32_t n, const double* p, const double* t) {
+  h->cam_params.assign(p, p + 4 * (size_t)n); h->cam_tvs.assign(t, t + 7 * (size_t)n); h->dirty = true; return BAGPU_OK;
+}
+int bagpu_set_poses(bagpu_handle h, uint32_t n, const double* t, const double* v, const double* b, const uint8_t* a,
+                    const uint8_t* mu, const uint8_t* m) {
+  const int D = h->D;
+  h->pose_t7.assign(t, t + 7 * (size_t)n);
+  if (v) h->pose_v.assign(v, v + 3 * (size_t)n); else h->pose_v.assign(3 * (size_t)n, 0.0);
+  if (b) h->pose_b.assign(b, b + 6 * (size_t)n); else h->pose_b.assign(6 * (size_t)n, 0.0);
+  if (a) h->pose_active.assign(a, a + n); else h->pose_active.assign(n, 1);
+  if (mu) h->pose_mask_used.assign(mu, mu + n); else h->pose_mask_used.assign(n, 0);
+  if (m) h->pose_mask.assign(m, m + (size_t)n * D); else h->pose_mask.assign((size_t)n * D, 1);
+  h->dirty = true;
+  return BAGPU_OK;
+}
+int bagpu_set_landmarks(bagpu_handle h, uint32_t n, const double* x, const uint32_t* rp, const uint32_t* rc, const uint8_t* a) {
+  const size_t np = h->pose_t7.size() / 7;
+  for (uint32_t i = 0; i < n; ++i) if (rp[i] >= np) return fail(BAGPU_ERR_INVALID, "landmark ref_pose_id out of range");
+  h->lm_xw.assign(x, x + 4 * (size_t)n); h->lm_xs.assign(4 * (size_t)n, 0.0);
+  h->lm_ref_pose.assign(rp, rp + n);
+  if (rc) h->lm_ref_cam.assign(rc, rc + n); else h->lm_ref_cam.assign(n, 0);
+  if (a) h->lm_active.assign(a, a + n); else h->lm_active.assign(n, 1);
+  h->lm_reliable.assign(n, 1); h->lm_outliers.assign(n, 0);
+  h->dirty = true;
+  return BAGPU_OK;
+}
+int bagpu_set_proj_residuals(bagpu_handle h, uint32_t n, const double* z, const uint32_t* mp, const uint32_t* lm, const uint32_t* cam,
+                             const double* w) {
+  const size_t np = h->pose_t7.size() / 7, nl = h->lm_xw.size() / 4;
+  for (uint32_t i = 0; i < n; ++i) {
+    if (mp[i] >= np || lm[i] >= nl) return fail(BAGPU_ERR_INVALID, "projection residual id out of range");
+    const uint32_t c = cam ? cam[i] : 0;
+    if (h->L == 1 && mp[i] == h->lm_ref_pose[lm[i]] && c == h->lm_ref_cam[lm[i]])
+      return fail(BAGPU_ERR_INVALID, "residual of a landmark in its own reference frame (AddProjectionResidual returns -1 for it)");
+  }
+  h->proj_z.assign(z, z + 2 * (size_t)n); h->proj_pose.assign(mp, mp + n); h->proj_lm.assign(lm, lm + n);
+  if (cam) h->proj_cam.assign(cam, cam + n); else h->proj_cam.assign(n, 0);
+  if (w) h->proj_w0.assign(w, w + n); else h->proj_w0.assign(n, 1.0);
+  h->dirty = true;
+  return BAGPU_OK;
+}
+int bagpu_set_unary_residuals(bagpu_handle h, uint32_t n, const uint32_t* pid, const double* t, const double* ci, const uint8_t* ur) {
+  const size_t np = h->pose_t7.size() / 7;
+  for (uint32_t i = 0; i < n; ++i) if (pid[i] >= np) return fail(BAGPU_ERR_INVALID, "unary pose id out of range");
+  h->un_pose.assign(pid, pid + n); h->un_t.assign(t, t + 7 * (size_t)n); h->un_cov_inv.assign(ci, ci + 36 * (size_t)n);
+  if (ur) h->un_rot.assign(ur, ur + n); else h->un_rot.assign(n, 1);
+  h->dirty = true;
+  return BAGPU_OK;
+}
+int bagpu_set_binary_residuals(bagpu_handle h, uint32_t n, const uint32_t* p1, const uint32_t* p2, const double* t, const double* ci,
+                               const double* w, const uint8_t* ur) {
+  const size_t np = h->pose_t7.size() / 7;
+  for (uint32_t i = 0; i < n; ++i) if (p1[i] >= np || p2[i] >= np) return fail(BAGPU_ERR_INVALID, "binary pose id out of range");
+  h->bin_p1.assign(p1, p1 + n); h->bin_p2.assign(p2, p2 + n); h->bin_t.assign(t, t + 7 * (size_t)n); h->bin_cov_inv.assign(ci, ci + 36 * (size_t)n);
+  if (w) h->bin_w.assign(w, w + n); else h->bin_w.assign(n, 1.0);
+  if (ur) h->bin_rot.assign(ur, ur + n); else h->bin_rot.assign(n, 1);
+  h->dirty = true;
+  return BAGPU_OK;
+}
+int bagpu_set_imu_residuals(bagpu_handle h, uint32_t n, const uint32_t* p1, const uint32_t* p2, const uint32_t* ms, const double* m7,
+                            const double* w) {
+  if (n > 0 && h->D < 9) return fail(BAGPU_ERR_INVALID, "inertial residuals need PoseSize >= 9");
+  const size_t np = h->pose_t7.size() / 7;
+  for (uint32_t i = 0; i < n; ++i) if (p1[i] >= np || p2[i] >= np) return fail(BAGPU_ERR_INVALID, "imu pose id out of range");
+  h->imu_p1.assign(p1, p1 + n); h->imu_p2.assign(p2, p2 + n);
+  if (n) { h->imu_ms.assign(ms, ms + n + 1); h->imu_meas.assign(m7, m7 + 7 * (size_t)ms[n]); } else { h->imu_ms.assign(1, 0); h->imu_meas.clear(); }
+  if (w) h->imu_w.assign(w, w + n); else h->imu_w.assign(n, 1.0);
+  h->dirty = true;
+  return BAGPU_OK;
+}
+
+#define GUARD(...)                                                                \
+  try { __VA_ARGS__ } catch (const std::string& e) {                              \
+    const bool nodev = e.find("no CUDA device") != std::string::npos;             \
+    return fail(nodev ? BAGPU_ERR_NO_DEVICE : BAGPU_ERR_CUDA, e);                 \
+  }
+
+int bagpu_solve(bagpu_handle h, uint32_t max_iter, double gn_damping, int allow, bagpu_summary* out) {
+  if (!h) return fail(BAGPU_ERR_INVALID, "null handle");
+  GUARD(h->solve(max_iter, gn_damping, allow != 0);)
+  if (out) *out = h->summary;
+  return BAGPU_OK;
+}
+
+int bagpu_build(bagpu_handle h, float* ms_out) {
+  if (!h) return fail(BAGPU_ERR_INVALID, "null handle");
+  GUARD(
+    if (!h->solved_once || h->dirty) h->prepare_solve();
+    h->solved_once = true;
+    h->build();
+    h->sync();
+    h->collect_build_times();
+    if (ms_out) { float ms; cudaEventElapsedTime(&ms, h->ev[0], h->ev[6]); *ms_out = ms; }
+  )
+  return BAGPU_OK;
+}
+
+int bagpu_get_poses(bagpu_handle h, double* t, double* v, double* b, uint8_t* mu, uint8_t* m) {
+  const size_t n = h->pose_t7.size() / 7;
+  if (t) memcpy(t, h->pose_t7.data(), sizeof(double) * 7 * n);
+  if (v) memcpy(v, h->pose_v.data(), sizeof(double) * 3 * n);
+  if (b) memcpy(b, h->pose_b.data(), sizeof(double) * 6 * n);
+  if (mu) memcpy(mu, h->pose_mask_used.data(), n);
+  if (m) memcpy(m, h->pose_mask.data(), n * h->D);
+  return BAGPU_OK;
+}
+int bagpu_get_landmarks(bagpu_handle h, double* xw, double* xs, uint8_t* rel, uint32_t* nout) {
+  const size_t n = h->lm_xw.size() / 4;
+  if (xw) memcpy(xw, h->lm_xw.data(), sizeof(double) * 4 * n);
+  if (xs) memcpy(xs, h->lm_xs.data(), sizeof(double) * 4 * n);
+  if (rel) memcpy(rel, h->lm_reliable.data(), n);
+  if (nout) memcpy(nout, h->lm_outliers.data(), sizeof(uint32_t) * n);
+  return BAGPU_OK;
+}
+int bagpu_get_proj_residuals(bagpu_handle h, double* r, double* w, double* m) {
+  GUARD(h->ensure_device(); if (h->dirty) return fail(BAGPU_ERR_INVALID, "no solve yet"); h->export_residuals(r, w, m);)
+  return BAGPU_OK;
+}
+int bagpu_get_trace(bagpu_handle h, uint32_t maxr, bagpu_iter_trace* out, uint32_t* n) {
+  const uint32_t c = std::min<uint32_t>(maxr, (uint32_t)h->trace.size());
+  if (out && c) memcpy(out, h->trace.data(), c * sizeof(bagpu_iter_trace));
+  if (n) *n = (uint32_t)h->trace.size();
+  return BAGPU_OK;
+}
+int bagpu_get_deltas(bagpu_handle h, uint32_t iter, double* dp, double* dl) {
+  if (iter >= h->rec_dp.size()) return fail(BAGPU_ERR_INVALID, "delta not recorded (options.record_deltas)");
+  if (dp) memcpy(dp, h->rec_dp[iter].data(), h->rec_dp[iter].size() * 8);
+  if (dl) memcpy(dl, h->rec_dl[iter].data(), h->rec_dl[iter].size() * 8);
+  return BAGPU_OK;
+}
+
+// Block patterns exactly as the reference's sparse products produce them (host, from the ids):
+//   U  = pattern of J^T J (upper, SparseBlockMatrixOps.h:236-238) over all residual types
+//   W  = jt_pr_j_l_ (P x N_l)   S = U  union  pattern of (W V^-1) W^T (upper)
+int bagpu_get_pattern(bagpu_handle h, int which, uint32_t* ncols, uint32_t* nnzb, uint32_t* colptr, uint32_t* rowidx) {
+  if (h->dirty) { h->setup(); }
+  const int P = h->n_ap, NL = h->n_al, L = h->L;
+  std::vector<std::vector<uint32_t>> cols;
+  auto lm_poses = [&](int l, std::vector<uint32_t>& out) {   // pose rows of W column l (sorted unique)
+    out.clear();
+    const int rp = (int)h->lm_ref_pose[l];
+    bool any = false;
+    for (uint32_t e = h->lm_obs_start[l]; e < h->lm_obs_start[l + 1]; ++e) {
+      const int m = (int)h->proj_pose[h->obs_perm[e]];
+      if (m != rp || L != 1) {
+        if (m != rp) any = true;
+        if (h->pose_opt[m] >= 0 && (m != rp || L != 1)) out.push_back(h->pose_opt[m]);
+      }
+    }
+    if (L == 1 && any && h->pose_opt[rp] >= 0) out.push_back(h->pose_opt[rp]);
+    std::sort(out.begin(), out.end()); out.erase(std::unique(out.begin(), out.end()), out.end());
+  };
+  if (which == BAGPU_PATTERN_W) {
+    cols.assign(NL, {});
+    for (int l = 0; l < h->n_lms; ++l) if (h->lm_opt[l] >= 0) lm_poses(l, cols[h->lm_opt[l]]);
+  } else if (which == BAGPU_PATTERN_U || which == BAGPU_PATTERN_S) {
+    cols.assign(P, {});
+    auto add = [&](int a, int b) { if (a < 0 || b < 0) return; cols[std::max(a, b)].push_back(std::min(a, b)); };
+    for (int i = 0; i < h->n_obs; ++i) {
+      const int m = (int)h->proj_pose[i], rp = (int)h->lm_ref_pose[h->proj_lm[i]];
+      if (m != rp || L != 1) {
+        add(h->pose_opt[m], h->pose_opt[m]);
+        if (L == 1) { add(h->pose_opt[rp], h->pose_opt[rp]); add(h->pose_opt[m], h->pose_opt[rp]); }
+      }
+    }
+    for (size_t i = 0; i < h->bin_p1.size(); ++i) {
+      const int a = h->pose_opt[h->bin_p1[i]], b = h->pose_opt[h->bin_p2[i]];
+      add(a, a); add(b, b); add(a, b);
+    }
+    for (uint32_t p : h->un_pose) add(h->pose_opt[p], h->pose_opt[p]);
+    for (size_t i = 0; i < h->imu_p1.size(); ++i) {
+      const int a = h->pose_opt[h->imu_p1[i]], b = h->pose_opt[h->imu_p2[i]];
+      add(a, a); add(b, b); add(a, b);
+    }
+    if (which == BAGPU_PATTERN_S && L > 0 && NL > 0) {
+      std::vector<uint32_t> ps;
+      for (int l = 0; l < h->n_lms; ++l) {
+        if (h->lm_opt[l] < 0) continue;
+        lm_poses(l, ps);
+        for (size_t a = 0; a < ps.size(); ++a) for (size_t b = a; b < ps.size(); ++b) cols[ps[b]].push_back(ps[a]);
+      }
+    }
+    for (auto& c : cols) { std::sort(c.begin(), c.end()); c.erase(std::unique(c.begin(), c.end()), c.end()); }
+  } else {
+    return fail(BAGPU_ERR_INVALID, "unknown pattern id");
+  }
+  size_t nz = 0;
+  for (auto& c : cols) nz += c.size();
+  if (ncols) *ncols = (uint32_t)cols.size();
+  if (nnzb) *nnzb = (uint32_t)nz;
+  if (colptr) { colptr[0] = 0; for (size_t j = 0; j < cols.size(); ++j) colptr[j + 1] = colptr[j] + (uint32_t)cols[j].size(); }
+  if (rowidx) { size_t k = 0; for (auto& c : cols) for (uint32_t r : c) rowidx[k++] = r; }
+  return BAGPU_OK;
+}
+
+int bagpu_get_system(bagpu_handle h, double* s_dense, double* rhs_sc, double* rhs_p, double* rhs_l, double* v_inv) {
+  GUARD(
+    h->ensure_device();
+    if (h->dirty) return fail(BAGPU_ERR_INVALID, "no build yet");
+    const int n = h->n_ap * h->D, T = h->T, nT = h->nT;
+    if (s_dense) {
+      std::vector<double> tiles((size_t)h->n_tiles * T * T);
+      h->d_S.download(tiles.data(), tiles.size(), h->st);
+      h->sync();
+      memset(s_dense, 0, sizeof(double) * (size_t)n * n);
+      for (int tI = 0; tI < nT; ++tI) for (int tJ = tI; tJ < nT; ++tJ) {
+        const int slot = h->tile_map[(size_t)tI * nT + tJ];
+        if (slot < 0) continue;
+        for (int c = 0; c < T; ++c) for (int r = 0; r < T; ++r) {
+          const int gi = tI * T + r, gj = tJ * T + c;
+          if (gi < n && gj < n && gi <= gj) s_dense[(size_t)gj * n + gi] = tiles[(size_t)slot * T * T + (size_t)c * T + r];
+        }
+      }
+    }
+    if (rhs_sc) h->d_rhs_sc.download(rhs_sc, n, h->st);
+    if (rhs_p) h->d_bp.download(rhs_p, n, h->st);
+    const int Ls = std::max(1, h->L);
+    if ((rhs_l || v_inv) && h->L > 0 && h->n_lms) {
+      std::vector<double> bl((size_t)h->n_lms * Ls), vi((size_t)h->n_lms * Ls * Ls);
+      h->d_lm_bl.download(bl.data(), bl.size(), h->st); h->d_lm_Vinv.download(vi.data(), vi.size(), h->st);
+      h->sync();
+      for (int l = 0; l < h->n_lms; ++l) {
+        const int o = h->lm_opt[l];
+        if (o < 0) continue;
+        if (rhs_l) for (int k = 0; k < Ls; ++k) rhs_l[(size_t)o * Ls + k] = bl[(size_t)l * Ls + k];
+        if (v_inv) for (int k = 0; k < Ls * Ls; ++k) v_inv[(size_t)o * Ls * Ls + k] = vi[(size_t)l * Ls * Ls + k];
+      }
+    }
+    h->sync();
+  )
+  return BAGPU_OK;
+}
+
+int bagpu_dump(bagpu_handle h, const char* dir) {
+  // s.txt / rhs.txt with Eigen's FullPrecision ", " separated rows (reference Utils.h:66, cpp:604-605)
+  const int n = h->n_ap * h->D;
+  std::vector<double> s((size_t)n * n), r(n);
+  int rc = bagpu_get_system(h, s.data(), r.data(), nullptr, nullptr, nullptr);
+  if (rc) return rc;
+  const std::string d = dir ? dir : ".";
+  FILE* f = fopen((d + "/s.txt").c_str(), "w");
+  if (!f) return fail(BAGPU_ERR_INVALID, "cannot open s.txt");
+  for (int i = 0; i < n; ++i) { for (int j = 0; j < n; ++j) fprintf(f, j ? ", %.17g" : "%.17g", s[(size_t)j * n + i]); fprintf(f, "\n"); }
+  fclose(f);
+  f = fopen((d + "/rhs.txt").c_str(), "w");
+  if (!f) return fail(BAGPU_ERR_INVALID, "cannot open rhs.txt");
+  for (int i = 0; i < n; ++i) fprintf(f, "%.17g\n", r[i]);
+  fclose(f);
+  return BAGPU_OK;
+}
+
+int bagpu_nccl_unique_id(void* out128) {
+  if (!g_nccl.load()) return fail(BAGPU_ERR_NCCL, "libnccl not found (set BAGPU_NCCL_LIB)");
+  UniqueId id;
+  int rc = g_nccl.getUniqueId(&id);
+  if (rc) return fail(BAGPU_ERR_NCCL, "ncclGetUniqueId failed");
+  memcpy(out128, &id, 128);
+  return BAGPU_OK;
+}
+
+int bagpu_comm_init(bagpu_handle h, int rank, int world, const void* id128) {
+  if (world <= 1) { h->rank = 0; h->world = 1; return BAGPU_OK; }
+  if (!g_nccl.load()) return fail(BAGPU_ERR_NCCL, "libnccl not found (set BAGPU_NCCL_LIB)");
+  GUARD(h->ensure_device();)
+  UniqueId id;
+  memcpy(&id, id128, 128);
+  int rc = g_nccl.commInitRank(&h->comm, world, id, rank);
+  if (rc) return fail(BAGPU_ERR_NCCL, std::string("ncclCommInitRank failed: ") + (g_nccl.getErrorString ? g_nccl.getErrorString(rc) : "?"));
+  h->rank = rank; h->world = world;
+  return BAGPU_OK;
+}
+
+int bagpu_get_phase_ms(bagpu_handle h, float* ms, uint64_t* launches) {
+  if (ms) for (int i = 0; i < BAGPU_PH_COUNT; ++i) ms[i] = h->phase_ms[i];
+  if (launches) *launches = h->launches;
+  return BAGPU_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,206 @@
+/*
+ * ba_b200.h — C ABI of the B200-native optimisation inner loop of ba::BundleAdjuster.
+ *
+ * This is the drop-in boundary: everything the reference does inside
+ *   BundleAdjuster::Solve            (reference src/BundleAdjuster.cpp:278-705)
+ *   BundleAdjuster::BuildProblem     (reference src/BundleAdjuster.cpp:1166-1803)
+ *   BundleAdjuster::SolveInternal    (reference src/BundleAdjuster.cpp:838-1161)
+ *   BundleAdjuster::CalculateGn      (reference src/BundleAdjuster.cpp:748-833)
+ *   BundleAdjuster::GetLandmarkDelta (reference src/BundleAdjuster.cpp:709-744)
+ *   BundleAdjuster::ApplyUpdate      (reference src/BundleAdjuster.cpp:21-140)
+ *   BundleAdjuster::EvaluateResiduals(reference src/BundleAdjuster.cpp:144-274)
+ * happens behind these entry points, on the GPU.  The host template class
+ * (include/ba/BundleAdjuster.h in this repo, mirroring reference
+ * include/ba/BundleAdjuster.h:111-753) only does bookkeeping and calls this ABI.
+ *
+ * Plain C: pointers and sizes only.  All floating point arrays are double (the
+ * reference's REAL_TYPE, reference CMakeLists.txt:16-20); compute precision on the
+ * device is selected by bagpu_dims.scalar_bytes.
+ *
+ * Conventions
+ *   SE3 = 7 doubles: qx qy qz qw tx ty tz   (Hamilton quaternion, Eigen coefficient order)
+ *   ids are uint32_t, identical to the ids the reference's Add* calls return.
+ *   all functions return bagpu_status (0 = ok); bagpu_last_error() gives a message.
+ */
+#ifndef BA_B200_H
+#define BA_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef enum bagpu_status {
+  BAGPU_OK = 0,
+  BAGPU_ERR_INVALID = 1,     /* bad argument / bad ids (reference asserts, BundleAdjuster.h:332,383,433,465,521) */
+  BAGPU_ERR_NO_DEVICE = 2,   /* no CUDA device: the product path never falls back to the CPU */
+  BAGPU_ERR_CUDA = 3,
+  BAGPU_ERR_NCCL = 4,
+  BAGPU_ERR_UNSUPPORTED = 5  /* template instantiation outside this build (e.g. CalibSize>0) */
+} bagpu_status;
+
+/* reference include/ba/BundleAdjuster.h:38-46 (same numeric values) */
+typedef enum bagpu_result {
+  BAGPU_Success = 0,
+  BAGPU_ErrorIncreased = 1,
+  BAGPU_ErrorChangeBelowThreshold = 2,
+  BAGPU_ParamChangeBelowThreshold = 3,
+  BAGPU_FactorizationError = 4,
+  BAGPU_SolverError = 5
+} bagpu_result;
+
+/* Template parameters of ba::BundleAdjuster<Scalar,LmSize,PoseSize,CalibSize,DoTvs>
+ * (reference include/ba/BundleAdjuster.h:111-134). */
+typedef struct bagpu_dims {
+  int32_t scalar_bytes; /* 8 (double) — 4 reserved for the REAL_TYPE=float build */
+  int32_t lm_dim;       /* LmSize   : 0, 1 (inverse depth) or 3 */
+  int32_t pose_dim;     /* PoseSize : 6, 9 or 15 */
+  int32_t calib_dim;    /* CalibSize: 0 in this build */
+  int32_t do_tvs;       /* DoTvs    : 0 in this build */
+} bagpu_dims;
+
+/* POD mirror of ba::Options<Scalar> (reference include/ba/BundleAdjuster.h:72-107)
+ * plus gravity (SetGravity, BundleAdjuster.h:243-252) and the solver choice. */
+typedef struct bagpu_options {
+  double trust_region_size;            /* -1 = kTrustRegionAuto (BundleAdjuster.h:30) */
+  double gyro_sigma, accel_sigma, gyro_bias_sigma, accel_bias_sigma;
+  double projection_outlier_threshold;
+  double error_change_threshold;
+  double param_change_threshold;
+  uint32_t dogleg_max_inner_iterations;
+  int32_t apply_results;
+  int32_t use_dogleg;
+  int32_t use_triangular_matrices;
+  int32_t use_sparse_solver;
+  int32_t write_reduced_camera_matrix;
+  int32_t calculate_calibration_marginals;
+  int32_t use_per_pose_cam_params;
+  int32_t regularize_biases_in_batch;
+  int32_t enable_auto_regularization;
+  int32_t use_robust_norm_for_proj_residuals;
+  int32_t use_robust_norm_for_inertial_residuals;
+  int32_t calculate_inertial_covariance_once;
+  double gravity[3];                   /* imu_.g_vec */
+  uint32_t root_pose_id;               /* SetRootPoseId, BundleAdjuster.h:553 */
+  /* extensions (not in the reference): */
+  int32_t reduced_solver;              /* 0 = tiled Cholesky (default), 1 = block-Jacobi PCG */
+  int32_t record_deltas;               /* keep per-iteration delta_p / delta_l for parity tests */
+  double pcg_tolerance;                /* relative residual for solver 1 */
+  uint32_t pcg_max_iterations;
+} bagpu_options;
+
+/* reference ba::SolutionSummary<Scalar> (BundleAdjuster.h:48-70) + the private error
+ * members GetErrors returns (BundleAdjuster.h:593-602) + trust_region_size_ (:720). */
+typedef struct bagpu_summary {
+  uint32_t num_proj_residuals, num_inertial_residuals;
+  uint32_t num_cond_proj_residuals, num_cond_inertial_residuals;
+  double cond_proj_error, cond_inertial_error;
+  double proj_error, inertial_error, unary_error, binary_error;
+  double delta_norm, pre_solve_norm, post_solve_norm;
+  double trust_region_size;
+  int32_t result;            /* bagpu_result */
+  uint32_t iterations;       /* outer iterations executed */
+} bagpu_summary;
+
+/* One record per outer iteration; this is what the parity tests compare. */
+typedef struct bagpu_iter_trace {
+  double proj_error_build, binary_error_build, unary_error_build, inertial_error_build;
+  double median_maha;        /* nth_element value, src/BundleAdjuster.cpp:1356-1358 */
+  double sd_numerator, sd_denominator, sd_norm;   /* src/BundleAdjuster.cpp:858-929 */
+  double gn_norm;            /* src/BundleAdjuster.cpp:971-973 (0 if GN not computed) */
+  double trust_region_after;
+  double pre_solve_norm, post_solve_norm, delta_norm;
+  double delta_p_norm, delta_l_norm;
+  uint32_t inner_iterations;
+  int32_t result;
+} bagpu_iter_trace;
+
+typedef struct bagpu_handle_s* bagpu_handle;
+
+/* ---- lifetime ------------------------------------------------------------------- */
+int bagpu_create(const bagpu_dims* dims, bagpu_handle* out);
+void bagpu_destroy(bagpu_handle h);
+const char* bagpu_last_error(void);
+int bagpu_set_options(bagpu_handle h, const bagpu_options* opt);
+void bagpu_default_options(bagpu_options* opt);   /* values of BundleAdjuster.h:75-106 */
+
+/* ---- problem upload (host -> HBM).  Replaces the AoS vectors BundleAdjuster.h:738-745 -- */
+/* rig: calibu linear camera params fx fy u0 v0 and T_vs per camera (BundleAdjuster.h:259) */
+int bagpu_set_cameras(bagpu_handle h, uint32_t n, const double* params4, const double* t_vs7);
+/* AddPose (BundleAdjuster.h:267-323). mask: pose_dim bytes per pose, 1 = parameter free
+ * (PoseT::param_mask, Types.h:47); mask_used = PoseT::is_param_mask_used. May be NULL. */
+int bagpu_set_poses(bagpu_handle h, uint32_t n, const double* t_wp7, const double* v_w3,
+                    const double* b6, const uint8_t* is_active,
+                    const uint8_t* mask_used, const uint8_t* mask);
+/* AddLandmark (BundleAdjuster.h:326-367) */
+int bagpu_set_landmarks(bagpu_handle h, uint32_t n, const double* x_w4,
+                        const uint32_t* ref_pose_id, const uint32_t* ref_cam_id,
+                        const uint8_t* is_active);
+/* AddProjectionResidual (BundleAdjuster.h:459-513): only residuals that call kept. */
+int bagpu_set_proj_residuals(bagpu_handle h, uint32_t n, const double* z2,
+                             const uint32_t* meas_pose_id, const uint32_t* landmark_id,
+                             const uint32_t* cam_id, const double* orig_weight);
+/* AddUnaryConstraint (BundleAdjuster.h:377-407): cov_inv = covariance^-1, 36 doubles row-major */
+int bagpu_set_unary_residuals(bagpu_handle h, uint32_t n, const uint32_t* pose_id,
+                              const double* t_wp7, const double* cov_inv36,
+                              const uint8_t* use_rotation);
+/* AddBinaryConstraint (BundleAdjuster.h:410-456) */
+int bagpu_set_binary_residuals(bagpu_handle h, uint32_t n, const uint32_t* pose1_id,
+                               const uint32_t* pose2_id, const double* t_12_7,
+                               const double* cov_inv36, const double* weight,
+                               const uint8_t* use_rotation);
+/* AddImuResidual (BundleAdjuster.h:516-546): CSR over measurements,
+ * meas7 = wx wy wz ax ay az time (Types.h:222-244) */
+int bagpu_set_imu_residuals(bagpu_handle h, uint32_t n, const uint32_t* pose1_id,
+                            const uint32_t* pose2_id, const uint32_t* meas_start /* n+1 */,
+                            const double* meas7, const double* weight);
+
+/* ---- the hot path ------------------------------------------------------------- */
+/* BundleAdjuster::Solve(uMaxIter, gn_damping, error_increase_allowed), BundleAdjuster.h:549 */
+int bagpu_solve(bagpu_handle h, uint32_t max_iter, double gn_damping,
+                int error_increase_allowed, bagpu_summary* out);
+
+/* One BuildProblem + Schur assembly at the current state without stepping: the
+ * "Schur-build" phase of the metric (reference timers _BuildProblem_ + _steup_problem_,
+ * src/BundleAdjuster.cpp:300-302,309,629).  ms_out (may be NULL) = device time. */
+int bagpu_build(bagpu_handle h, float* ms_out);
+
+/* ---- results (HBM -> host). Buffers may be NULL to skip. ------------------------- */
+int bagpu_get_poses(bagpu_handle h, double* t_wp7, double* v_w3, double* b6,
+                    uint8_t* mask_used, uint8_t* mask);
+int bagpu_get_landmarks(bagpu_handle h, double* x_w4, double* x_s4, uint8_t* is_reliable,
+                        uint32_t* num_outlier_residuals);
+int bagpu_get_proj_residuals(bagpu_handle h, double* residual2, double* weight, double* maha);
+int bagpu_get_trace(bagpu_handle h, uint32_t max_records, bagpu_iter_trace* out, uint32_t* n_out);
+/* delta of outer iteration `iter` (needs options.record_deltas) */
+int bagpu_get_deltas(bagpu_handle h, uint32_t iter, double* delta_p, double* delta_l);
+
+/* ---- inspection of the assembled system (parity of block structure and values) --- */
+typedef enum bagpu_pattern { BAGPU_PATTERN_U = 0, BAGPU_PATTERN_W = 1, BAGPU_PATTERN_S = 2 } bagpu_pattern;
+/* block-CSC, column pointers (ncols+1) and ascending row indices, as the reference's
+ * SparseBlockMatrix stores them (SparseBlockMatrix.h:108-112). First call with NULLs to size. */
+int bagpu_get_pattern(bagpu_handle h, int which, uint32_t* ncols, uint32_t* nnzb,
+                      uint32_t* colptr, uint32_t* rowidx);
+/* dense upper-triangular S ((P*d)^2, column-major like Eigen MatrixXt, BundleAdjuster.h:718),
+ * rhs_p_sc, rhs_p_, rhs_l_, vi_ (L*L per active landmark) of the last build */
+int bagpu_get_system(bagpu_handle h, double* s_dense, double* rhs_sc, double* rhs_p,
+                     double* rhs_l, double* v_inv);
+/* s.txt / rhs.txt in the reference's CSV format (src/BundleAdjuster.cpp:600-606) */
+int bagpu_dump(bagpu_handle h, const char* dir);
+
+/* ---- multi-GPU (landmark sharding) --------------------------------- */
+/* nccl_unique_id: 128 bytes from bagpu_nccl_unique_id() on rank 0, broadcast by the caller. */
+int bagpu_nccl_unique_id(void* out128);
+int bagpu_comm_init(bagpu_handle h, int rank, int world, const void* nccl_unique_id128);
+/* per-phase device timings of the last solve/build in ms: see bagpu_phase */
+typedef enum bagpu_phase {
+  BAGPU_PH_RESIDUAL = 0, BAGPU_PH_MEDIAN = 1, BAGPU_PH_ACCUMULATE = 2, BAGPU_PH_OTHER_RES = 3,
+  BAGPU_PH_ALLREDUCE = 4, BAGPU_PH_SOLVE = 5, BAGPU_PH_STEP = 6, BAGPU_PH_COUNT = 7
+} bagpu_phase;
+int bagpu_get_phase_ms(bagpu_handle h, float* ms /* BAGPU_PH_COUNT */, uint64_t* kernel_launches);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* BA_B200_H */
