@@ -291,13 +291,16 @@ struct bagpu_handle_s {
     // cameras
     std::vector<double> Rvs(9 * n_cams), tvs(3 * n_cams);
     for (int c = 0; c < n_cams; ++c) {
+      quat_normalize(&cam_tvs[7 * c]);   // Sophus::SO3Group's constructor normalises
       quat_to_R(&cam_tvs[7 * c], &Rvs[9 * c]);
       for (int k = 0; k < 3; ++k) tvs[3 * c + k] = cam_tvs[7 * c + 4 + k];
     }
     d_cam_params.upload(cam_params, st); d_cam_Rvs.upload(Rvs, st); d_cam_tvs.upload(tvs, st);
     // poses
     std::vector<double> q(4 * n_poses), t(3 * n_poses);
-    for (int i = 0; i < n_poses; ++i) { for (int k = 0; k < 4; ++k) q[4 * i + k] = pose_t7[7 * i + k]; for (int k = 0; k < 3; ++k) t[3 * i + k] = pose_t7[7 * i + 4 + k]; }
+    for (int i = 0; i < n_poses; ++i) { quat_normalize(&pose_t7[7 * i]); for (int k = 0; k < 4; ++k) q[4 * i + k] = pose_t7[7 * i + k]; for (int k = 0; k < 3; ++k) t[3 * i + k] = pose_t7[7 * i + 4 + k]; }
+    for (size_t i = 0; i < un_pose.size(); ++i) quat_normalize(&un_t[7 * i]);
+    for (size_t i = 0; i < bin_p1.size(); ++i) quat_normalize(&bin_t[7 * i]);
     d_pose_q.upload(q, st); d_pose_t.upload(t, st); d_pose_v.upload(pose_v, st); d_pose_b.upload(pose_b, st);
     d_bk_q.alloc(q.size()); d_bk_t.alloc(t.size()); d_bk_v.alloc(pose_v.size()); d_bk_b.alloc(pose_b.size());
     d_pose_opt.upload(pose_opt, st); d_pose_free.alloc(n_poses); d_pose_mask_used.alloc(n_poses);
@@ -350,7 +353,7 @@ struct bagpu_handle_s {
     P.obs_maha0 = d_obs_maha0.p; P.obs_w = d_obs_w.p; P.obs_W = d_obs_W.p;
     P.lm_Vinv = d_lm_Vinv.p; P.lm_bl = d_lm_bl.p; P.lm_Wref = d_lm_Wref.p;
     P.S_tiles = d_S.p; P.tile_map = d_tile_map.p; P.nT = nT; P.T = T; P.b_p = d_bp.p; P.rhs_sc = d_rhs_sc.p; P.sc = d_sc.p;
-    P.c_huber_factor = 1.2107; P.use_robust = opt.use_robust_norm_for_proj_residuals; P.outlier_threshold = opt.projection_outlier_threshold;
+    P.c_huber_factor = 1.2107; P.use_robust = (opt.use_robust_norm_for_proj_residuals ? 1 : 0) | (opt.use_robust_norm_for_inertial_residuals ? 2 : 0); P.outlier_threshold = opt.projection_outlier_threshold;
 
     memset(&R, 0, sizeof(R));
     R.n_unary = P.n_unary; R.n_binary = P.n_binary; R.n_imu = P.n_imu;
@@ -453,6 +456,7 @@ struct bagpu_handle_s {
     compute_masks();
     CU(cudaEventRecord(ev[0], st));
     d_S.zero(st, (size_t)n_tiles * T * T); d_bp.zero(st); d_sc.zero(st);
+    { const double flag = n_obs_total > 0 ? 1.0 : 0.0; CU(cudaMemcpyAsync(&d_sc.p->dot[7], &flag, sizeof(double), cudaMemcpyHostToDevice, st)); }
     launch_pose_frames(P, st); ++launches;
     launch_residual(P, G, st); if (n_obs) ++launches;
     CU(cudaEventRecord(ev[1], st));

@@ -175,7 +175,7 @@ BA_D void obs_jacobians(const DeviceProblem& P, const LmCtx<L>& c, int obs, ObsJ
 
 BA_D double huber_weight(double maha0, double w0, double c_huber, int use_robust) {
   const double e = sqrt(maha0);
-  return (use_robust && e > c_huber) ? w0 * (c_huber / e) : w0;
+  return ((use_robust & 1) && e > c_huber) ? w0 * (c_huber / e) : w0;
 }
 
 // address of element (r, c) of pose block (i, j), i <= j, inside the tiled S

@@ -56,7 +56,7 @@ def compare(name, p, iters=5, **opts):
             i, a["inner_iterations"], b["inner_iterations"], a["post_solve_norm"], b["post_solve_norm"], worst[0], worst[1],
             rel(dpg, dpo), rel(dlg, dlo) if len(dlo) else 0.0))
     pg, po = g.get_poses(), o.get_poses()
-    print("  final poses rel %.2e  cost rel %.2e" % (rel(pg["t_wp"], po["t_wp"]), abs(sg.post_solve_norm - so.post_solve_norm) / so.post_solve_norm))
+    print("  final poses rel %.2e  cost rel %.2e" % (rel(pg["t_wp"], po["t_wp"]), abs(sg.post_solve_norm - so.post_solve_norm) / max(so.post_solve_norm, 1e-300)))
     if p.lm_dim:
         lg, lo = g.get_landmarks(), o.get_landmarks()
         print("  final landmarks x_w rel %.2e outliers equal %s reliable equal %s" % (rel(lg["x_w"], lo["x_w"]), bool(np.array_equal(lg["num_outlier_residuals"], lo["num_outlier_residuals"])), bool(np.array_equal(lg["is_reliable"], lo["is_reliable"]))))
@@ -77,5 +77,12 @@ if __name__ == "__main__":
         compare("c4-mini", synth.make_c4(n_cams=60, n_points=2000))
     if "c5" in which:
         compare("c5-mini", synth.make_c5(n_poses=200))
+    if "c3" in which:
+        compare("c3-mini", synth.make_c3(n_keyframes=40, n_landmarks=300, obs_per_lm=10))
+        compare("c3-mini-d9-nolm", synth.make_c3(n_keyframes=30, n_landmarks=0, pose_dim=9, lm_dim=0))
+    if "c2mid" in which:
+        compare("c2-mid", synth.make("c2", 0.1), iters=3)
+    if "c4mid" in which:
+        compare("c4-mid", synth.make("c4", 0.02), iters=3)
     if "c1full" in which:
         compare("c1-full", synth.make_c1(), iters=10)
