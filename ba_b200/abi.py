@@ -8,7 +8,7 @@ The same class binds any library exporting these entry points under a prefix
 import ctypes as C
 import numpy as np
 
-PH_NAMES = ["residual", "median", "accumulate", "other_residuals", "allreduce", "solve", "step"]
+PH_NAMES = ["residual", "median", "accumulate", "other_residuals", "schur", "allreduce", "solve", "step", "total"]
 RESULT_NAMES = ["Success", "ErrorIncreased", "ErrorChangeBelowThreshold",
                 "ParamChangeBelowThreshold", "FactorizationError", "SolverError"]
 PATTERN_U, PATTERN_W, PATTERN_S = 0, 1, 2
@@ -40,7 +40,8 @@ class Options(C.Structure):
                 ("gravity", C.c_double * 3),
                 ("root_pose_id", C.c_uint32),
                 ("reduced_solver", C.c_int32), ("record_deltas", C.c_int32),
-                ("pcg_tolerance", C.c_double), ("pcg_max_iterations", C.c_uint32)]
+                ("pcg_tolerance", C.c_double), ("pcg_max_iterations", C.c_uint32),
+                ("keep_on_device", C.c_int32)]
 
 
 class Summary(C.Structure):
@@ -237,6 +238,9 @@ class Binding:
         self._check(self._f("get_system")(self.h, _p(s, np.float64), _p(rsc, np.float64), _p(rp, np.float64),
                                           _p(rl, np.float64) if self.lm_dim else None, _p(vi, np.float64) if self.lm_dim else None))
         return dict(S=(s.T.copy() if dense_s else None), rhs_sc=rsc, rhs_p=rp, rhs_l=rl, v_inv=vi)
+
+    def sync_state(self):
+        self._check(self._f("sync_state")(self.h))
 
     def get_phase_ms(self):
         ms = (C.c_float * len(PH_NAMES))()

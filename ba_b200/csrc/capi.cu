@@ -353,7 +353,7 @@ struct bagpu_handle_s {
     P.obs_maha0 = d_obs_maha0.p; P.obs_w = d_obs_w.p; P.obs_W = d_obs_W.p;
     P.lm_Vinv = d_lm_Vinv.p; P.lm_bl = d_lm_bl.p; P.lm_Wref = d_lm_Wref.p;
     P.S_tiles = d_S.p; P.tile_map = d_tile_map.p; P.nT = nT; P.T = T; P.b_p = d_bp.p; P.rhs_sc = d_rhs_sc.p; P.sc = d_sc.p;
-    P.c_huber_factor = 1.2107; P.use_robust = (opt.use_robust_norm_for_proj_residuals ? 1 : 0) | (opt.use_robust_norm_for_inertial_residuals ? 2 : 0); P.outlier_threshold = opt.projection_outlier_threshold;
+    P.c_huber_factor = 1.2107;
 
     memset(&R, 0, sizeof(R));
     R.n_unary = P.n_unary; R.n_binary = P.n_binary; R.n_imu = P.n_imu;
@@ -361,12 +361,19 @@ struct bagpu_handle_s {
     R.bin_p1 = d_bin_p1.p; R.bin_p2 = d_bin_p2.p; R.bin_t12 = d_bin_t.p; R.bin_cov_inv = d_bin_cov_inv.p; R.bin_weight = d_bin_w.p; R.bin_use_rot = d_bin_rot.p;
     R.imu_p1 = d_imu_p1.p; R.imu_p2 = d_imu_p2.p; R.imu_meas_start = d_imu_ms.p; R.imu_meas = d_imu_meas.p; R.imu_weight = d_imu_w.p;
     R.imu_cov_inv = d_imu_cov_inv.p; R.imu_J1 = d_imu_J1.p; R.imu_J2 = d_imu_J2.p; R.imu_res = d_imu_res.p;
+    apply_options();
+    dirty = false;
+  }
+
+  // Options that the kernels read (Init(), BundleAdjuster.h:192-218)
+  void apply_options() {
+    P.use_robust = (opt.use_robust_norm_for_proj_residuals ? 1 : 0) | (opt.use_robust_norm_for_inertial_residuals ? 2 : 0);
+    P.outlier_threshold = opt.projection_outlier_threshold;
     for (int k = 0; k < 3; ++k) R.gravity[k] = opt.gravity[k];
     for (int k = 0; k < 3; ++k) {
       R.imu_r[k] = opt.gyro_sigma * opt.gyro_sigma; R.imu_r[3 + k] = opt.accel_sigma * opt.accel_sigma;
       R.imu_rb[k] = opt.gyro_bias_sigma * opt.gyro_bias_sigma; R.imu_rb[3 + k] = opt.accel_bias_sigma * opt.accel_bias_sigma;
     }
-    dirty = false;
   }
 
   // ---- parameter masks, literal from src/BundleAdjuster.cpp:1237-1330 ------------------------
@@ -496,7 +503,7 @@ struct bagpu_handle_s {
     cudaEventElapsedTime(&ms, ev[1], ev[2]); phase_ms[BAGPU_PH_MEDIAN] += ms;
     cudaEventElapsedTime(&ms, ev[2], ev[3]); phase_ms[BAGPU_PH_ACCUMULATE] += ms;
     cudaEventElapsedTime(&ms, ev[3], ev[4]); phase_ms[BAGPU_PH_OTHER_RES] += ms;
-    cudaEventElapsedTime(&ms, ev[4], ev[5]); phase_ms[BAGPU_PH_ACCUMULATE] += ms;
+    cudaEventElapsedTime(&ms, ev[4], ev[5]); phase_ms[BAGPU_PH_SCHUR] += ms;
     cudaEventElapsedTime(&ms, ev[5], ev[6]); phase_ms[BAGPU_PH_ALLREDUCE] += ms;
   }
 
@@ -715,6 +722,7 @@ struct bagpu_handle_s {
   void prepare_solve() {
     ensure_device();
     if (dirty) { setup(); upload_all(); solved_once = false; }
+    else apply_options();
     // Solve() prologue (cpp:287-296)
     launch_pose_frames(P, st); ++launches;
     if (L == 1) { launch_prepare_xs(P, d_lm_xw.p, st); ++launches; }
@@ -753,6 +761,7 @@ struct bagpu_handle_s {
     summary.iterations = 0;
     if (proj_pose.empty() && bin_p1.empty() && un_pose.empty() && imu_p1.empty()) return;
     prepare_solve();
+    CU(cudaEventRecord(ev[14], st));
     for (uint32_t kk = 0; kk < max_iter; ++kk) {
       build();
       const Scalars sb = read_scalars();
@@ -779,7 +788,10 @@ struct bagpu_handle_s {
       }
       tr.result = summary.result; trace.push_back(tr);
     }
-    download_state();
+    CU(cudaEventRecord(ev[15], st));
+    sync();
+    { float ms; cudaEventElapsedTime(&ms, ev[14], ev[15]); phase_ms[BAGPU_PH_TOTAL] = ms; }
+    if (!opt.keep_on_device) download_state();
     solved_once = true;
     // summary (cpp:680-704)
     summary.num_proj_residuals = n_obs; summary.num_inertial_residuals = (uint32_t)imu_p1.size();
@@ -857,8 +869,9 @@ void bagpu_destroy(bagpu_handle h) {
 int bagpu_set_options(bagpu_handle h, const bagpu_options* o) {
   if (!h || !o) return fail(BAGPU_ERR_INVALID, "null argument");
   h->opt = *o;
-  h->trust_region = o->trust_region_size;   // Init(): trust_region_size_ = options_.trust_region_size (BundleAdjuster.h:193)
-  h->dirty = true;
+  // Init() sets trust_region_size_ = options_.trust_region_size (BundleAdjuster.h:193); later changes through
+  // options() (BundleAdjuster.h:605) leave the running trust region alone
+  if (!h->solved_once) h->trust_region = o->trust_region_size;
   return BAGPU_OK;
 }
 
@@ -1131,6 +1144,12 @@ int bagpu_comm_init(bagpu_handle h, int rank, int world, const void* id128) {
   int rc = g_nccl.commInitRank(&h->comm, world, id, rank);
   if (rc) return fail(BAGPU_ERR_NCCL, std::string("ncclCommInitRank failed: ") + (g_nccl.getErrorString ? g_nccl.getErrorString(rc) : "?"));
   h->rank = rank; h->world = world;
+  return BAGPU_OK;
+}
+
+int bagpu_sync_state(bagpu_handle h) {
+  if (!h) return fail(BAGPU_ERR_INVALID, "null handle");
+  GUARD(h->ensure_device(); if (h->dirty) return fail(BAGPU_ERR_INVALID, "no solve yet"); h->download_state();)
   return BAGPU_OK;
 }
 

