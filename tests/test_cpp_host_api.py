@@ -1,0 +1,116 @@
+"""The C++ drop-in class (include/ba/BundleAdjuster.h) driven like the reference's applications.
+
+tests/cpp/host_api_driver.cpp builds a problem through Init / AddCamera / AddPose / AddLandmark /
+Add*Constraint / Add*Residual, calls Solve and reads the getters.  On a box without a GPU the
+run must fail loudly (exit 3: SolverError, no CPU fallback); on the GPU box the refined state must
+match the CPU oracle fed with the identical arrays.
+"""
+import os
+import struct
+import subprocess
+import numpy as np
+import pytest
+
+from ba_b200 import synth
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+SRC = os.path.join(ROOT, "tests", "cpp", "host_api_driver.cpp")
+EXE = os.path.join(ROOT, "tests", "cpp", "build", "host_api_driver")
+
+
+def build_driver():
+    os.makedirs(os.path.dirname(EXE), exist_ok=True)
+    deps = [SRC, os.path.join(ROOT, "include", "ba", "BundleAdjuster.h"), os.path.join(ROOT, "include", "ba", "MiniTypes.h"),
+            os.path.join(ROOT, "include", "ba_b200.h")]
+    if os.path.exists(EXE) and all(os.path.getmtime(d) <= os.path.getmtime(EXE) for d in deps):
+        return EXE
+    subprocess.check_call(["g++", "-std=c++17", "-O2", "-Wall", "-I" + os.path.join(ROOT, "include"), SRC, "-o", EXE,
+                           "-L" + os.path.join(ROOT, "ba_b200"), "-lba_b200", "-Wl,-rpath," + os.path.join(ROOT, "ba_b200")])
+    return EXE
+
+
+def write_problem(path, p):
+    a = p.arrays()
+    g = getattr(p, "gravity", np.zeros(3))
+    with open(path, "wb") as f:
+        f.write(struct.pack("<ii", p.lm_dim, p.pose_dim))
+
+        def blk(n, *arrs):
+            f.write(struct.pack("<I", n))
+            for x in arrs:
+                f.write(np.ascontiguousarray(x).tobytes())
+        blk(len(a["cam_params"]), a["cam_params"], a["cam_t_vs"])
+        blk(len(a["pose_t_wp"]), a["pose_t_wp"], a["pose_v_w"], a["pose_b"], a["pose_active"])
+        blk(len(a["lm_x_w"]), a["lm_x_w"], a["lm_ref_pose"], a["lm_ref_cam"], a["lm_active"])
+        blk(len(a["proj_z"]), a["proj_z"], a["proj_meas_pose"], a["proj_lm"], a["proj_cam"], a["proj_weight"])
+        # the C++ API takes covariances (it inverts them, reference BundleAdjuster.h:398,444)
+        ucov = np.array([np.linalg.inv(c.reshape(6, 6)).reshape(36) for c in a["un_cov_inv"]]).reshape(-1, 36)
+        blk(len(a["un_pose"]), a["un_pose"], a["un_t_wp"], ucov, a["un_use_rot"])
+        bcov = np.array([np.linalg.inv(c.reshape(6, 6)).reshape(36) for c in a["bin_cov_inv"]]).reshape(-1, 36)
+        blk(len(a["bin_p1"]), a["bin_p1"], a["bin_p2"], a["bin_t_12"], bcov, a["bin_weight"], a["bin_use_rot"])
+        blk(len(a["imu_p1"]), a["imu_p1"], a["imu_p2"], a["imu_meas_start"], a["imu_meas"], a["imu_weight"])
+        f.write(np.asarray(g, np.float64).tobytes())
+
+
+def read_out(path, p):
+    a = p.arrays()
+    d = np.fromfile(path, dtype=np.float64)
+    npose, nl, nr = len(a["pose_t_wp"]), len(a["lm_x_w"]), len(a["proj_z"])
+    head = d[:10]; o = 10
+    poses = d[o:o + 16 * npose].reshape(npose, 16); o += 16 * npose
+    lms = d[o:o + 6 * nl].reshape(nl, 6); o += 6 * nl
+    res = d[o:o + 3 * nr].reshape(nr, 3)
+    return head, poses, lms, res
+
+
+def test_driver_builds_and_fails_loudly_without_a_gpu(tmp_path):
+    import torch
+    exe = build_driver()
+    p = synth.make_c1(n_poses=8, n_landmarks=60, obs_per_lm=4)
+    write_problem(tmp_path / "p.bin", p)
+    r = subprocess.run([exe, str(tmp_path / "p.bin"), str(tmp_path / "o.bin"), "2"], capture_output=True, text=True)
+    if torch.cuda.is_available():
+        assert r.returncode == 0, r.stderr
+    else:
+        assert r.returncode == 3, (r.returncode, r.stderr)          # SolverError: no device, no CPU path
+        assert "no CUDA device" in r.stderr
+        assert not (tmp_path / "o.bin").exists()
+
+
+CASES = {
+    "c1": (lambda: synth.make_c1(n_poses=12, n_landmarks=200, obs_per_lm=8), 5, 1e-9),
+    "c2": (lambda: synth.make_c2(n_cams=80, n_points=1500), 4, 1e-9),
+    "c5": (lambda: synth.make_c5(n_poses=120), 3, 1e-8),
+    "c3": (lambda: synth.make_c3(n_keyframes=30, n_landmarks=200, obs_per_lm=8), 3, 1e-5),
+}
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", sorted(CASES))
+def test_cpp_class_matches_oracle(name, tmp_path):
+    from oracle.oracle_py import Oracle
+    exe = build_driver()
+    make, iters, tol = CASES[name]
+    p = make()
+    write_problem(tmp_path / "p.bin", p)
+    r = subprocess.run([exe, str(tmp_path / "p.bin"), str(tmp_path / "o.bin"), str(iters)], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr + r.stdout
+    head, poses, lms, res = read_out(tmp_path / "o.bin", p)
+    o = Oracle(p.lm_dim, p.pose_dim)
+    opt = o.default_options()
+    opt.error_change_threshold = 0; opt.param_change_threshold = 0
+    if hasattr(p, "gravity"):
+        opt.gravity[0], opt.gravity[1], opt.gravity[2] = [float(x) for x in p.gravity]
+    o.set_options(opt); o.load(p)
+    so = o.solve(iters)
+    assert int(head[0]) == so.result and int(head[1]) == so.iterations
+    assert abs(head[3] - so.post_solve_norm) <= max(tol, 1e-9) * so.post_solve_norm
+    po = o.get_poses()
+    assert np.linalg.norm(poses[:, :7] - po["t_wp"]) <= tol * np.linalg.norm(po["t_wp"])
+    if p.lm_dim:
+        lo = o.get_landmarks()
+        assert np.linalg.norm(lms[:, :4] - lo["x_w"]) <= tol * np.linalg.norm(lo["x_w"])
+        assert np.array_equal(lms[:, 4] != 0, lo["is_reliable"] != 0)
+        ro = o.get_proj_residuals()
+        assert np.linalg.norm(res[:, :2] - ro["residual"]) <= max(tol, 1e-8) * np.linalg.norm(ro["residual"])
+        assert np.linalg.norm(res[:, 2] - ro["weight"]) <= max(tol, 1e-9) * np.linalg.norm(ro["weight"])
