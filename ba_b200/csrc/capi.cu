@@ -326,7 +326,7 @@ struct bagpu_handle_s {
     d_lm_bl.zero(st);
     // reduced system
     const size_t tsz = (size_t)T * T;
-    d_S.alloc((size_t)n_tiles * tsz); d_uinv.alloc((size_t)nT * tsz); d_scratch.alloc((size_t)std::max(1, max_row) * tsz);
+    d_S.alloc((size_t)n_tiles * tsz); d_uinv.alloc((size_t)nT * tsz); d_scratch.alloc(2 * (size_t)nT * T);
     d_bp.alloc((size_t)nT * T); d_rhs_sc.alloc((size_t)nT * T); d_rhs_work.alloc((size_t)nT * T);
     d_tile_map.upload(tile_map, st); d_row_ptr.upload(row_ptr, st); d_row_col.upload(row_col, st); d_fail.alloc(1);
     d_sc.alloc(1); d_sc.zero(st); d_sel.alloc(1);

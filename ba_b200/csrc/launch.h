@@ -54,7 +54,7 @@ void launch_select_init(SelectState* st, unsigned long long k, cudaStream_t s);
 void launch_select_hist(const double* x, size_t n, SelectState* st, int pass, int sms, cudaStream_t s);
 void launch_select_scan(SelectState* st, int pass, double* out, cudaStream_t s);
 
-void launch_cholesky_solve(int T, double* tiles, double* uinv, double* scratch, double* rhs, const int* tile_map,
+void launch_cholesky_solve(int T, double* tiles, double* uinv, double* work /* 2*nT*T */, double* rhs, const int* tile_map,
                            const int* row_ptr_dev, const int* row_col_dev, const int* row_ptr_host, int nT, int* fail,
                            cudaStream_t st, uint64_t* launches);
 

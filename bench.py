@@ -207,8 +207,10 @@ def main():
         s.solve(W)
     barrier()
     with ClockSampler(local_rank) as clk:
-        s.solve(K)
+        sm = s.solve(K)
         barrier()
+    if sm.iterations != K or sm.result in (4, 5):
+        raise SystemExit("bench.py: the timed Solve() stopped after %d of %d iterations (result %d): no number" % (sm.iterations, K, sm.result))
     ph, launches = s.get_phase_ms()
     t_ms = torch.tensor([ph["total"]], dtype=torch.float64, device="cuda")
     if world > 1:
@@ -244,7 +246,9 @@ def main():
     t0 = time.time()
     s3 = fresh(False)
     s3.load(p)
-    s3.solve(K)
+    sm3 = s3.solve(K)
+    if sm3.iterations != K:
+        raise SystemExit("bench.py: the e2e Solve() stopped after %d of %d iterations" % (sm3.iterations, K))
     res = s3.get_poses(); lm = s3.get_landmarks() if L else None
     barrier()
     t_e2e = torch.tensor([time.time() - t0], dtype=torch.float64, device="cuda")

@@ -3,7 +3,7 @@
 // applications/unary_binary_imu_test/main.cpp:243-296: Init -> SetGravity -> AddPose ->
 // Add*Constraint / Add*Residual -> Solve -> GetPose).
 //
-//   host_api_driver <problem.bin> <out.bin> <iterations> [use_dogleg]
+//   host_api_driver <problem.bin> <out.bin> <iterations> [use_dogleg [gyro_sigma accel_sigma gyro_bias_sigma accel_bias_sigma]]
 //
 // problem.bin (little endian, written by tests/test_cpp_host_api.py): int32 L, D, then per
 // category a uint32 count followed by the raw arrays in the order read below.  out.bin: the
@@ -22,13 +22,14 @@ struct Reader {
 };
 
 template <typename Scalar, int L, int D>
-int run(Reader& rd, const char* out_path, int iters, bool dogleg) {
+int run(Reader& rd, const char* out_path, int iters, bool dogleg, const double* sig) {
   typedef ba::BundleAdjuster<Scalar, L, D, 0> BA;
   typedef typename BA::SE3t SE3t;
   auto se3 = [](const double* p) { return ba::detail::se3_from7<SE3t, Scalar>(p); };
   BA ba;
   ba::Options<Scalar> opt;
   opt.error_change_threshold = 0; opt.param_change_threshold = 0; opt.use_dogleg = dogleg;
+  if (sig) { opt.gyro_sigma = (Scalar)sig[0]; opt.accel_sigma = (Scalar)sig[1]; opt.gyro_bias_sigma = (Scalar)sig[2]; opt.accel_bias_sigma = (Scalar)sig[3]; }
   const uint32_t nc = rd.u32();
   auto cp = rd.arr<double>(4 * nc), ct = rd.arr<double>(7 * nc);
   const uint32_t np = rd.u32();
@@ -132,15 +133,17 @@ int main(int argc, char** argv) {
   Reader rd{f};
   const int iters = atoi(argv[3]);
   const bool dogleg = argc > 4 ? atoi(argv[4]) != 0 : true;
+  double sigv[4]; const double* sig = nullptr;
+  if (argc > 8) { for (int k = 0; k < 4; ++k) sigv[k] = atof(argv[5 + k]); sig = sigv; }
   int hdr[2];
   if (fread(hdr, sizeof(int), 2, f) != 2) return 2;
   const int L = hdr[0], D = hdr[1];
-  if (L == 1 && D == 6) return run<double, 1, 6>(rd, argv[2], iters, dogleg);
-  if (L == 3 && D == 6) return run<double, 3, 6>(rd, argv[2], iters, dogleg);
-  if (L == 0 && D == 6) return run<double, 0, 6>(rd, argv[2], iters, dogleg);
-  if (L == 1 && D == 15) return run<double, 1, 15>(rd, argv[2], iters, dogleg);
-  if (L == 0 && D == 9) return run<double, 0, 9>(rd, argv[2], iters, dogleg);
-  if (L == 0 && D == 15) return run<double, 0, 15>(rd, argv[2], iters, dogleg);
+  if (L == 1 && D == 6) return run<double, 1, 6>(rd, argv[2], iters, dogleg, sig);
+  if (L == 3 && D == 6) return run<double, 3, 6>(rd, argv[2], iters, dogleg, sig);
+  if (L == 0 && D == 6) return run<double, 0, 6>(rd, argv[2], iters, dogleg, sig);
+  if (L == 1 && D == 15) return run<double, 1, 15>(rd, argv[2], iters, dogleg, sig);
+  if (L == 0 && D == 9) return run<double, 0, 9>(rd, argv[2], iters, dogleg, sig);
+  if (L == 0 && D == 15) return run<double, 0, 15>(rd, argv[2], iters, dogleg, sig);
   fprintf(stderr, "instantiation <double,%d,%d,0> not compiled into this driver\n", L, D);
   return 2;
 }
