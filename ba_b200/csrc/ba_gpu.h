@@ -7,8 +7,16 @@
 //   landmarks    x[4N] (x_s for LmSize 1, x_w for LmSize 3), ref pose/cam, opt id, reliable flag
 //   observations sorted by landmark id, ties by residual id: z[2] (double2), meas pose (u32),
 //                cam (u32), orig weight; CSR lm_obs_start[N+1]; perm[] back to residual ids
-//   per-obs      maha0 (median input), weight (Huber), W = w J_p^T J_l (6 x L, row-major)
-//   per-landmark V^-1 (L x L), b_l (L), W_ref (6 x L, LmSize 1 only), delta_l
+//   per-obs      maha0 (median input), weight (Huber)
+//   records      one per observation whose measurement pose is optimised, stored POSE-MAJOR
+//                (slot = obs_slot[obs]; pose p owns slots pose_rec_start[p] .. [p+1]):
+//                  LmSize 3 (28 doubles): C = Bt V^-1 (2x3) | At (2x6) | Bt (2x3) | rt (2) | rho (2)
+//                  LmSize 1 (40 doubles): E = W V^-1 (6) | W = At^T Bt (6) | At (2x6) | Q (2x6) | rt (2) | rho (2)
+//                with At = sqrt(w) J_meas, Bt = sqrt(w) J_lm, rt = sqrt(w) r, rho = rt - Bt V^-1 b_l,
+//                Q = At_ref - Bt V^-1 W_ref^T (the reference-pose Jacobian with the landmark projected out)
+//   per-landmark V^-1 (L x L), b_l (L), dhat = V^-1 b_l, W_ref (6, LmSize 1 only), and for LmSize 1 a
+//                reference-pose record (36 doubles, stored by reference pose): H_rr - W_r V^-1 W_r^T
+//                (upper, 21) | g_r (6) | g_r - W_r dhat (6)
 //   reduced S    upper block-tile storage: tiles of T x T doubles (T = 8 poses x PoseSize),
 //                column-major inside a tile, tile_map[tI * nT + tJ] -> tile slot or -1
 #pragma once
@@ -19,6 +27,8 @@
 namespace bagpu {
 
 constexpr int kTilePoses = 8;   // poses per S tile
+constexpr uint32_t kNoSlot = 0xffffffffu;
+constexpr int kRec3 = 28, kRec1 = 40, kLmRec = 36;
 
 struct Scalars {       // device-resident scalar block (one per handle)
   double median;       // nth_element value of maha0
@@ -65,11 +75,16 @@ struct DeviceProblem {
   const uint32_t* obs_perm;  // sorted index -> residual id
   double* obs_maha0;
   double* obs_w;
-  double* obs_W;             // 6*L per obs
+  const uint32_t* obs_slot;  // pose-major record slot of the observation, kNoSlot if its pose takes no part
+  double* rec;               // records, rec_stride doubles each
+  int rec_stride;            // 28 (LmSize 3) or 40 (LmSize 1)
   // per landmark outputs
   double* lm_Vinv;           // L*L
   double* lm_bl;             // L  (rhs_l_, indexed by landmark id; compacted on read-back)
-  double* lm_Wref;           // 6*L (L == 1)
+  double* lm_dhat;           // L  V^-1 b_l
+  double* lm_Wref;           // 6 (L == 1)
+  const uint32_t* lm_rslot;  // L == 1: slot of the landmark's reference-pose record, kNoSlot if none
+  double* lm_rec;            // L == 1: 36 doubles per slot
   // reduced system
   double* S_tiles;
   const int* tile_map;

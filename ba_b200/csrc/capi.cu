@@ -122,6 +122,11 @@ struct bagpu_handle_s {
   std::vector<uint8_t> pose_has_res;     // any residual in the pose's lists
   std::vector<uint8_t> pose_has_imu;
   std::vector<uint32_t> lm_obs_start, obs_perm;
+  std::vector<uint32_t> obs_slot, pose_rec_start, lm_rslot, pose_lmrec_start;   // pose-major record slots (ba_gpu.h)
+  uint32_t n_rec = 0, n_lmrec = 0;
+  int n_items = 0, n_items_sym = 0;
+  size_t n_pairs = 0;
+  uint2* d_pairs = nullptr;            // cudaMalloc'ed by build_pair_lists
   int G = 8;
   int nT = 0, T = 48, n_tiles = 0, max_row = 0;
   std::vector<int> tile_map, row_ptr, row_col;
@@ -135,8 +140,10 @@ struct bagpu_handle_s {
   DevBuf<int> d_pose_opt, d_lm_opt; DevBuf<uint32_t> d_pose_free; DevBuf<uint8_t> d_pose_mask_used;
   DevBuf<double> d_lm_x, d_lm_xw; DevBuf<uint32_t> d_lm_ref_pose, d_lm_ref_cam, d_lm_outliers, d_lm_obs_start;
   DevBuf<uint8_t> d_lm_reliable;
-  DevBuf<double2> d_obs_z; DevBuf<uint32_t> d_obs_pose, d_obs_cam, d_obs_perm; DevBuf<double> d_obs_w0, d_obs_maha0, d_obs_w, d_obs_W;
-  DevBuf<double> d_lm_Vinv, d_lm_bl, d_lm_Wref;
+  DevBuf<double2> d_obs_z; DevBuf<uint32_t> d_obs_pose, d_obs_cam, d_obs_perm; DevBuf<double> d_obs_w0, d_obs_maha0, d_obs_w;
+  DevBuf<uint32_t> d_obs_slot, d_lm_rslot; DevBuf<double> d_rec, d_lm_rec, d_partial; DevBuf<unsigned int> d_counters;
+  DevBuf<ReduceItem> d_items, d_items_sym;
+  DevBuf<double> d_lm_Vinv, d_lm_bl, d_lm_dhat, d_lm_Wref;
   DevBuf<double> d_S, d_S_copy, d_uinv, d_scratch, d_bp, d_rhs_sc, d_rhs_work;
   DevBuf<int> d_tile_map, d_row_ptr, d_row_col, d_fail;
   DevBuf<Scalars> d_sc; DevBuf<SelectState> d_sel;
@@ -276,6 +283,36 @@ struct bagpu_handle_s {
       lm_obs_start.swap(ns); obs_perm.swap(np);
       n_obs = (int)obs_perm.size();
     }
+    // ---- pose-major record slots of the local observations (counting sort by pose opt id, stable in
+    // landmark order) and, for LmSize 1, reference-pose record slots of the landmarks ----
+    obs_slot.assign(n_obs, kNoSlot);
+    pose_rec_start.assign(n_ap + 1, 0);
+    lm_rslot.assign(L == 1 ? n_lms : 0, kNoSlot);
+    pose_lmrec_start.assign(n_ap + 1, 0);
+    {
+      std::vector<uint8_t> lm_any(L == 1 ? n_lms : 0, 0);
+      for (int l = 0; l < n_lms; ++l) {
+        const uint32_t rp = lm_ref_pose[l];
+        for (uint32_t e = lm_obs_start[l]; e < lm_obs_start[l + 1]; ++e) {
+          const uint32_t m = proj_pose[obs_perm[e]];
+          if (m == rp) continue;
+          if (L == 1) lm_any[l] = 1;
+          if (pose_opt[m] >= 0) pose_rec_start[pose_opt[m] + 1]++;
+        }
+        if (L == 1 && lm_any[l] && pose_opt[rp] >= 0) pose_lmrec_start[pose_opt[rp] + 1]++;
+      }
+      for (int p = 0; p < n_ap; ++p) { pose_rec_start[p + 1] += pose_rec_start[p]; pose_lmrec_start[p + 1] += pose_lmrec_start[p]; }
+      n_rec = pose_rec_start[n_ap]; n_lmrec = pose_lmrec_start[n_ap];
+      std::vector<uint32_t> cur(pose_rec_start.begin(), pose_rec_start.end() - 1), curl(pose_lmrec_start.begin(), pose_lmrec_start.end() - 1);
+      for (int l = 0; l < n_lms; ++l) {
+        const uint32_t rp = lm_ref_pose[l];
+        for (uint32_t e = lm_obs_start[l]; e < lm_obs_start[l + 1]; ++e) {
+          const uint32_t m = proj_pose[obs_perm[e]];
+          if (m != rp && pose_opt[m] >= 0) obs_slot[e] = cur[pose_opt[m]]++;
+        }
+        if (L == 1 && lm_any[l] && pose_opt[rp] >= 0) lm_rslot[l] = curl[pose_opt[rp]]++;
+      }
+    }
     tile_map.assign((size_t)nT * nT, -1);
     row_ptr.assign(nT + 1, 0); row_col.clear();
     n_tiles = 0; max_row = 0;
@@ -320,9 +357,12 @@ struct bagpu_handle_s {
     }
     d_obs_z.upload(z, st); d_obs_pose.upload(op, st); d_obs_w0.upload(w0, st); d_obs_perm.upload(obs_perm, st);
     if (multi_cam) d_obs_cam.upload(oc, st);
-    d_obs_maha0.alloc(n_obs); d_obs_w.alloc(n_obs); d_obs_W.alloc((size_t)n_obs * 6 * std::max(1, L));
+    d_obs_maha0.alloc(n_obs); d_obs_w.alloc(n_obs);
     const int Ls = std::max(1, L);
-    d_lm_Vinv.alloc((size_t)n_lms * Ls * Ls); d_lm_bl.alloc((size_t)n_lms * Ls); d_lm_Wref.alloc((size_t)n_lms * 6 * Ls);
+    const int rec_stride = (L == 1) ? kRec1 : kRec3;
+    d_obs_slot.upload(obs_slot, st); d_rec.alloc((size_t)n_rec * rec_stride);
+    if (L == 1) { d_lm_rslot.upload(lm_rslot, st); d_lm_rec.alloc((size_t)n_lmrec * kLmRec); }
+    d_lm_Vinv.alloc((size_t)n_lms * Ls * Ls); d_lm_bl.alloc((size_t)n_lms * Ls); d_lm_dhat.alloc((size_t)n_lms * Ls); d_lm_Wref.alloc((size_t)n_lms * 6);
     d_lm_bl.zero(st);
     // reduced system
     const size_t tsz = (size_t)T * T;
@@ -350,8 +390,10 @@ struct bagpu_handle_s {
     P.lm_x = d_lm_x.p; P.lm_ref_pose = d_lm_ref_pose.p; P.lm_ref_cam = d_lm_ref_cam.p; P.lm_opt = d_lm_opt.p; P.lm_reliable = d_lm_reliable.p;
     P.lm_outliers = d_lm_outliers.p; P.lm_obs_start = d_lm_obs_start.p;
     P.obs_z = d_obs_z.p; P.obs_pose = d_obs_pose.p; P.obs_cam = multi_cam ? d_obs_cam.p : nullptr; P.obs_w0 = d_obs_w0.p; P.obs_perm = d_obs_perm.p;
-    P.obs_maha0 = d_obs_maha0.p; P.obs_w = d_obs_w.p; P.obs_W = d_obs_W.p;
-    P.lm_Vinv = d_lm_Vinv.p; P.lm_bl = d_lm_bl.p; P.lm_Wref = d_lm_Wref.p;
+    P.obs_maha0 = d_obs_maha0.p; P.obs_w = d_obs_w.p;
+    P.obs_slot = d_obs_slot.p; P.rec = d_rec.p; P.rec_stride = rec_stride;
+    P.lm_rslot = (L == 1) ? d_lm_rslot.p : nullptr; P.lm_rec = (L == 1) ? d_lm_rec.p : nullptr;
+    P.lm_Vinv = d_lm_Vinv.p; P.lm_bl = d_lm_bl.p; P.lm_dhat = d_lm_dhat.p; P.lm_Wref = d_lm_Wref.p;
     P.S_tiles = d_S.p; P.tile_map = d_tile_map.p; P.nT = nT; P.T = T; P.b_p = d_bp.p; P.rhs_sc = d_rhs_sc.p; P.sc = d_sc.p;
     P.c_huber_factor = 1.2107;
 
@@ -362,7 +404,58 @@ struct bagpu_handle_s {
     R.imu_p1 = d_imu_p1.p; R.imu_p2 = d_imu_p2.p; R.imu_meas_start = d_imu_ms.p; R.imu_meas = d_imu_meas.p; R.imu_weight = d_imu_w.p;
     R.imu_cov_inv = d_imu_cov_inv.p; R.imu_J1 = d_imu_J1.p; R.imu_J2 = d_imu_J2.p; R.imu_res = d_imu_res.p;
     apply_options();
+    build_reduce_items();
     dirty = false;
+  }
+
+  // ---- work items of the pose-pair-major reduction (schur_kernels.cu): the device builds the pair
+  // lists (symbolic.cu), the host cuts every S block into chunks of at most kChunk entries ----
+  void build_reduce_items() {
+    constexpr uint32_t kChunk = 512;
+    if (d_pairs) { cudaFree(d_pairs); d_pairs = nullptr; }
+    n_pairs = 0; n_items = 0; n_items_sym = 0;
+    if (L == 0 || n_obs == 0 || n_ap == 0) return;
+    std::vector<unsigned long long> bkey; std::vector<uint32_t> bcnt; std::string err;
+    if (build_pair_lists(P, st, &d_pairs, &n_pairs, bkey, bcnt, err) != 0) throw std::string("pair lists: ") + err;
+    std::vector<ReduceItem> items, sym;
+    uint32_t n_partial = 0, n_groups = 0;
+    auto push_block = [&](std::vector<ReduceItem>& out, std::vector<ReduceItem>& chunks) {
+      if (chunks.empty()) return;
+      const uint32_t mc = (uint32_t)chunks.size();
+      for (uint32_t k = 0; k < mc; ++k) {
+        ReduceItem& it = chunks[k];
+        it.mcount = mc; it.mfirst = 0; it.mself = 0; it.mgroup = 0;
+        if (mc > 1) { it.mfirst = n_partial; it.mself = n_partial + k; it.mgroup = n_groups; }
+        out.push_back(it);
+      }
+      if (mc > 1) { n_partial += mc; ++n_groups; }
+      chunks.clear();
+    };
+    auto cut = [&](std::vector<ReduceItem>& chunks, uint32_t lo, uint32_t hi, uint32_t row, uint32_t col, uint32_t kind) {
+      for (uint32_t b = lo; b < hi; b += kChunk) {
+        ReduceItem it; memset(&it, 0, sizeof(it));
+        it.begin = b; it.end = std::min(hi, b + kChunk); it.row = row; it.col = col; it.kind = kind;
+        chunks.push_back(it);
+      }
+    };
+    std::vector<ReduceItem> chunks;
+    size_t bi = 0; uint32_t pair_off = 0;
+    for (int p = 0; p < n_ap; ++p) {
+      cut(chunks, pose_rec_start[p], pose_rec_start[p + 1], p, p, kItemDiagObs);
+      if (L == 1) cut(chunks, pose_lmrec_start[p], pose_lmrec_start[p + 1], p, p, kItemDiagLm);
+      push_block(items, chunks);
+      while (bi < bkey.size() && (int)(bkey[bi] / (unsigned long long)n_ap) == p) {
+        const uint32_t col = (uint32_t)(bkey[bi] % (unsigned long long)n_ap);
+        const bool is_sym = (col == (uint32_t)p);
+        cut(chunks, pair_off, pair_off + bcnt[bi], p, col, is_sym ? kItemSym : kItemOff);
+        push_block(is_sym ? sym : items, chunks);
+        pair_off += bcnt[bi]; ++bi;
+      }
+    }
+    n_items = (int)items.size(); n_items_sym = (int)sym.size();
+    d_items.upload(items, st); d_items_sym.upload(sym, st);
+    d_partial.alloc((size_t)std::max<uint32_t>(1, n_partial) * 36); d_counters.alloc(std::max<uint32_t>(1, n_groups)); d_counters.zero(st);
+    sync();   // the host vectors above go out of scope
   }
 
   // Options that the kernels read (Init(), BundleAdjuster.h:192-218)
@@ -470,7 +563,7 @@ struct bagpu_handle_s {
     const unsigned long long n_total = (unsigned long long)n_obs_total;   // ranks hold disjoint landmark shards
     run_select(d_obs_maha0.p, (size_t)n_obs, n_total, &d_sc.p->median);
     CU(cudaEventRecord(ev[2], st));
-    launch_accumulate(P, G, st); if (n_obs) ++launches;
+    launch_linearize(P, G, st); if (n_obs) ++launches;
     CU(cudaEventRecord(ev[3], st));
     if (rank == 0) {   // replicated residuals are added once
       if (R.n_unary) {
@@ -481,7 +574,8 @@ struct bagpu_handle_s {
     }
     CU(cudaEventRecord(ev[4], st));
     CU(cudaMemcpyAsync(d_rhs_sc.p, d_bp.p, sizeof(double) * (size_t)nT * T, cudaMemcpyDeviceToDevice, st));
-    launch_schur(P, st); if (n_obs && n_al && n_ap) ++launches;
+    if (n_items) { launch_reduce_blocks(P, d_items.p, n_items, d_pairs, d_partial.p, d_counters.p, st); ++launches; }
+    if (n_items_sym) { launch_reduce_blocks(P, d_items_sym.p, n_items_sym, d_pairs, d_partial.p, d_counters.p, st); ++launches; }
     CU(cudaEventRecord(ev[5], st));
     if (world > 1) {
       allreduce_f64(d_S.p, (size_t)n_tiles * T * T);
@@ -862,6 +956,7 @@ void bagpu_destroy(bagpu_handle h) {
   if (!h) return;
   if (h->comm && g_nccl.commDestroy) g_nccl.commDestroy(h->comm);
   if (h->ev_ok) for (auto& e : h->ev) cudaEventDestroy(e);
+  if (h->d_pairs) cudaFree(h->d_pairs);
   if (h->st) cudaStreamDestroy(h->st);
   delete h;
 }

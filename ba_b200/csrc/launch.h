@@ -2,6 +2,8 @@
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <string>
+#include <vector>
 #include "ba_gpu.h"
 
 namespace bagpu {
@@ -32,13 +34,34 @@ struct OtherResiduals {
   double imu_rb[6];         // bias random walk (imu_.r_b)
 };
 
+// ---- pose-pair-major reduction (schur_kernels.cu / symbolic.cu) -------------------------------
+// pair list entry: (a, b) record slots, a belongs to the block's row pose.  LmSize 1 also lists
+// one entry per observation for the (measurement pose, reference pose) block, tagged in b.
+constexpr uint32_t kPairTagMeasRow = 0xffffffffu;   // row pose = measurement pose: += At^T Q
+constexpr uint32_t kPairTagRefRow = 0xfffffffeu;    // row pose = reference pose:   += Q^T At
+enum { kItemDiagObs = 0, kItemDiagLm = 1, kItemOff = 2, kItemSym = 3 };
+struct ReduceItem {        // one warp's share of one S block
+  uint32_t begin, end;     // record-slot range (diagonal kinds) or pair range
+  uint32_t row, col;       // pose opt ids, row <= col
+  uint32_t kind;
+  uint32_t mfirst, mcount; // chunks of the same block: partial-sum slots mfirst .. mfirst + mcount
+  uint32_t mself, mgroup;  // this chunk's slot, the block's arrival counter
+  uint32_t pad;
+};
+
+// Builds the pair list on the device (symbolic.cu): *pairs_out is cudaMalloc'ed (caller frees), sorted by
+// block key = row * n_active_poses + col, stable in landmark order; block_key / block_count = the block table.
+int build_pair_lists(const DeviceProblem& P, cudaStream_t st, uint2** pairs_out, size_t* n_pairs_out,
+                     std::vector<unsigned long long>& block_key, std::vector<uint32_t>& block_count, std::string& err);
+
 void set_sm_count(int n);
 void launch_pose_frames(const DeviceProblem& P, cudaStream_t st);
 void launch_prepare_xs(const DeviceProblem& P, const double* lm_xw, cudaStream_t st);
 void launch_finish_xw(const DeviceProblem& P, double* lm_xw, cudaStream_t st);
 void launch_residual(const DeviceProblem& P, int G, cudaStream_t st);
-void launch_accumulate(const DeviceProblem& P, int G, cudaStream_t st);
-void launch_schur(const DeviceProblem& P, cudaStream_t st);
+void launch_linearize(const DeviceProblem& P, int G, cudaStream_t st);
+void launch_reduce_blocks(const DeviceProblem& P, const ReduceItem* items, int n_items, const uint2* pairs, double* partial,
+                          unsigned int* counters, cudaStream_t st);
 void launch_sd_denominator(const DeviceProblem& P, int G, cudaStream_t st);
 void launch_back_substitute(const DeviceProblem& P, int G, const double* delta_p, double* delta_l, cudaStream_t st);
 void launch_evaluate(const DeviceProblem& P, int G, double* out_sum, double* res_out, double* maha_out, cudaStream_t st);

@@ -83,280 +83,8 @@ __global__ void __launch_bounds__(256) k_residual(DeviceProblem P) {
   }
 }
 
-// ---------------------------------------------------------------------------------------
-// pass 2: Jacobians, Huber weights, V / b_l / V^-1, W, U and b_p
-template <int L, int G>
-__global__ void __launch_bounds__(128) k_accumulate(DeviceProblem P) {
-  constexpr int NV = L * (L + 1) / 2;
-  const int lane = threadIdx.x & 31, gl = lane % G;
-  const unsigned gmask = group_mask<G>(lane);
-  const int group = (blockIdx.x * blockDim.x + threadIdx.x) / G;
-  const int n_groups = (gridDim.x * blockDim.x) / G;
-  const double c_huber = P.c_huber_factor * sqrt(P.sc->median);
-  double err = 0.0;
-  for (int lm = group; lm < P.n_lms; lm += n_groups) {
-    const int s = P.lm_obs_start[lm], e = P.lm_obs_start[lm + 1];
-    LmCtx<L> c;
-    load_lm<L>(P, lm, c);
-    const bool lm_on = c.lm_opt >= 0;
-    double V[NV], bl[L];
-#pragma unroll
-    for (int i = 0; i < NV; ++i) V[i] = 0.0;
-#pragma unroll
-    for (int i = 0; i < L; ++i) bl[i] = 0.0;
-    // reference-pose accumulators (LmSize 1): H_rr upper (21), g_r (6), W_r (6)
-    double Hrr[L == 1 ? 21 : 1], gr[L == 1 ? 6 : 1], Wr[L == 1 ? 6 : 1];
-    if (L == 1) {
-#pragma unroll
-      for (int i = 0; i < 21; ++i) Hrr[i] = 0.0;
-#pragma unroll
-      for (int i = 0; i < 6; ++i) { gr[i] = 0.0; Wr[i] = 0.0; }
-    }
-    bool any_ref = false;
-    for (int i = s + gl; i < e; i += G) {
-      ObsJac<L> o;
-      obs_jacobians<L>(P, c, i, o);
-      const double w0 = P.obs_w0[i];
-      const double maha0 = (o.r[0] * o.r[0] + o.r[1] * o.r[1]) * w0;
-      const double w = huber_weight(maha0, w0, c_huber, P.use_robust);
-      P.obs_w[i] = w;
-      err += (o.r[0] * o.r[0] + o.r[1] * o.r[1]) * w;
-      const double wr0 = w * o.r[0], wr1 = w * o.r[1];
-      if (lm_on) {
-        int k = 0;
-#pragma unroll
-        for (int a = 0; a < L; ++a) {
-#pragma unroll
-          for (int b = a; b < L; ++b) { V[k] += w * (o.Jl[a] * o.Jl[b] + o.Jl[L + a] * o.Jl[L + b]); ++k; }
-          bl[a] += o.Jl[a] * wr0 + o.Jl[L + a] * wr1;
-        }
-      }
-      double* Wout = P.obs_W + (size_t)i * 6 * L;
-      if (o.pm >= 0) {
-        // W_m = w J_m^T J_l  (6 x L, row-major)
-#pragma unroll
-        for (int a = 0; a < 6; ++a)
-#pragma unroll
-          for (int b = 0; b < L; ++b)
-            Wout[a * L + b] = lm_on ? w * (o.Jm[a] * o.Jl[b] + o.Jm[6 + a] * o.Jl[L + b]) : 0.0;
-        // U(m,m) += w J_m^T J_m (upper triangle of the diagonal block), b_p[m] += w J_m^T r
-        double* blk = s_block(P, o.pm, o.pm);
-#pragma unroll
-        for (int b = 0; b < 6; ++b)
-#pragma unroll
-          for (int a = 0; a <= b; ++a) red_add(blk + (size_t)b * P.T + a, w * (o.Jm[a] * o.Jm[b] + o.Jm[6 + a] * o.Jm[6 + b]));
-        double* bp = P.b_p + (size_t)o.pm * P.D;
-#pragma unroll
-        for (int a = 0; a < 6; ++a) red_add(bp + a, o.Jm[a] * wr0 + o.Jm[6 + a] * wr1);
-      } else {
-#pragma unroll
-        for (int a = 0; a < 6 * L; ++a) Wout[a] = 0.0;
-      }
-      if (L == 1 && o.ref_on) {
-        any_ref = true;
-        int k = 0;
-#pragma unroll
-        for (int b = 0; b < 6; ++b) {
-#pragma unroll
-          for (int a = 0; a <= b; ++a) { Hrr[k] += w * (o.Jr[a] * o.Jr[b] + o.Jr[6 + a] * o.Jr[6 + b]); ++k; }
-          gr[b] += o.Jr[b] * wr0 + o.Jr[6 + b] * wr1;
-          if (lm_on) Wr[b] += w * (o.Jr[b] * o.Jl[0] + o.Jr[6 + b] * o.Jl[1]);
-        }
-        if (o.pm >= 0) {
-          // cross block of this residual: U(min,max) += w J_min^T J_max  (SparseBlockMatrixOps.h:236-241)
-          const bool m_first = o.pm < c.ref_opt;
-          double* blk = m_first ? s_block(P, o.pm, c.ref_opt) : s_block(P, c.ref_opt, o.pm);
-          const double* Ja = m_first ? o.Jm : o.Jr;
-          const double* Jb = m_first ? o.Jr : o.Jm;
-#pragma unroll
-          for (int b = 0; b < 6; ++b)
-#pragma unroll
-            for (int a = 0; a < 6; ++a) red_add(blk + (size_t)b * P.T + a, w * (Ja[a] * Jb[b] + Ja[6 + a] * Jb[6 + b]));
-        }
-      }
-    }
-    // ---- group reductions -------------------------------------------------------------
-#pragma unroll
-    for (int i = 0; i < NV; ++i) V[i] = group_sum<G>(V[i], gmask);
-#pragma unroll
-    for (int i = 0; i < L; ++i) bl[i] = group_sum<G>(bl[i], gmask);
-    if (L == 1) {
-      const bool grp_ref = __any_sync(gmask, any_ref);
-      if (grp_ref) {
-#pragma unroll
-        for (int i = 0; i < 21; ++i) Hrr[i] = group_sum<G>(Hrr[i], gmask);
-#pragma unroll
-        for (int i = 0; i < 6; ++i) { gr[i] = group_sum<G>(gr[i], gmask); Wr[i] = group_sum<G>(Wr[i], gmask); }
-        // scatter the reference-pose blocks, elements spread over the lanes of the group
-        double* blk = s_block(P, c.ref_opt, c.ref_opt);
-        int k = 0;
-#pragma unroll
-        for (int b = 0; b < 6; ++b)
-#pragma unroll
-          for (int a = 0; a <= b; ++a) { if ((k % G) == gl) red_add(blk + (size_t)b * P.T + a, Hrr[k]); ++k; }
-#pragma unroll
-        for (int a = 0; a < 6; ++a) if ((a % G) == gl) red_add(P.b_p + (size_t)c.ref_opt * P.D + a, gr[a]);
-      }
-      if (gl == 0) {
-#pragma unroll
-        for (int a = 0; a < 6; ++a) P.lm_Wref[(size_t)lm * 6 + a] = (grp_ref && lm_on) ? Wr[a] : 0.0;
-      }
-    }
-    if (gl == 0) {
-      double* vo = P.lm_Vinv + (size_t)lm * L * L;
-      double* bo = P.lm_bl + (size_t)lm * L;
-      if (lm_on) {
-        if (L == 1) {
-          double v = V[0];
-          if (fabs(v) < 1e-6) v += 1e-6;            // cpp:431-434
-          vo[0] = 1.0 / v;
-          bo[0] = bl[0];
-        } else {
-          double M[9] = {V[0], V[1], V[2], V[1], V[3], V[4], V[2], V[4], V[5]};
-          double n2 = 0.0;
-#pragma unroll
-          for (int i = 0; i < 9; ++i) n2 += M[i] * M[i];
-          if (sqrt(n2) < 1e-6) { M[0] += 1e-6; M[4] += 1e-6; M[8] += 1e-6; }   // cpp:436-439
-          double Mi[9];
-          inv3(M, Mi);
-#pragma unroll
-          for (int i = 0; i < 9; ++i) vo[i] = Mi[i];
-#pragma unroll
-          for (int i = 0; i < L; ++i) bo[i] = bl[i];
-        }
-      } else {
-#pragma unroll
-        for (int i = 0; i < L * L; ++i) vo[i] = 0.0;
-#pragma unroll
-        for (int i = 0; i < L; ++i) bo[i] = 0.0;
-      }
-    }
-  }
-  err = warp_sum(err);
-  if (lane == 0) red_add(&P.sc->proj_error, err);
-}
-
-// ---------------------------------------------------------------------------------------
-// Schur-product kernel: S -= W V^-1 W^T, rhs_sc -= W V^-1 b_l, one warp per landmark.
-// Entries of a landmark = its observations (+ the reference pose for LmSize 1); they are staged
-// NE at a time in shared memory (W and E = W V^-1), and the (pair, element) work items are
-// spread over the 32 lanes so that consecutive lanes hit consecutive addresses of one block.
-template <int L>
-struct SchurStage {
-  double W[16][6 * L];
-  double E[16][6 * L];
-  int P[16];
-};
-
-template <int L>
-BA_D void schur_stage_load(const DeviceProblem& P, SchurStage<L>& st, int lm, int s, int n_obs_lm, int n_ent,
-                           int base, const double* Vinv, int ref_pose, int ref_opt, int lane) {
-  constexpr int NE = 16;
-  const int cnt = min(NE, n_ent - base);
-  for (int t = lane; t < cnt * 6 * L; t += 32) {
-    const int e = base + t / (6 * L), idx = t % (6 * L);
-    st.W[t / (6 * L)][idx] = (e < n_obs_lm) ? P.obs_W[(size_t)(s + e) * 6 * L + idx] : P.lm_Wref[(size_t)lm * 6 * L + idx];
-  }
-  if (lane < cnt) {
-    const int e = base + lane;
-    int po;
-    if (e < n_obs_lm) {
-      const int m = (int)P.obs_pose[s + e];
-      const int mo = P.pose_opt[m];
-      po = (m != ref_pose && mo >= 0) ? mo : -1;
-    } else {
-      po = ref_opt;
-    }
-    st.P[lane] = po;
-  }
-  __syncwarp();
-  for (int t = lane; t < cnt * 6 * L; t += 32) {
-    const int e = t / (6 * L), idx = t % (6 * L), r = idx / L, cc = idx % L;
-    double v = 0.0;
-#pragma unroll
-    for (int k = 0; k < L; ++k) v += st.W[e][r * L + k] * Vinv[k * L + cc];
-    st.E[e][idx] = v;
-  }
-  __syncwarp();
-}
-
-template <int L>
-__global__ void __launch_bounds__(128) k_schur(DeviceProblem P) {
-  constexpr int NE = 16;
-  __shared__ SchurStage<L> stA[4], stB[4];
-  const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
-  const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-  const int n_warps = (gridDim.x * blockDim.x) >> 5;
-  SchurStage<L>& A = stA[wib];
-  for (int lm = warp; lm < P.n_lms; lm += n_warps) {
-    if (P.lm_opt[lm] < 0) continue;
-    const int s = P.lm_obs_start[lm], n_obs_lm = P.lm_obs_start[lm + 1] - s;
-    const int ref_pose = (int)P.lm_ref_pose[lm];
-    const int ref_opt = (L == 1) ? P.pose_opt[ref_pose] : -1;
-    const int n_ent = n_obs_lm + ((L == 1 && ref_opt >= 0) ? 1 : 0);
-    if (n_ent == 0) continue;
-    double Vinv[L * L], bl[L];
-#pragma unroll
-    for (int i = 0; i < L * L; ++i) Vinv[i] = P.lm_Vinv[(size_t)lm * L * L + i];
-#pragma unroll
-    for (int i = 0; i < L; ++i) bl[i] = P.lm_bl[(size_t)lm * L + i];
-    for (int ab = 0; ab < n_ent; ab += NE) {
-      schur_stage_load<L>(P, A, lm, s, n_obs_lm, n_ent, ab, Vinv, ref_pose, ref_opt, lane);
-      const int na = min(NE, n_ent - ab);
-      // rhs_sc[p_a] -= E_a b_l
-      for (int t = lane; t < na * 6; t += 32) {
-        const int e = t / 6, r = t % 6;
-        const int po = A.P[e];
-        if (po >= 0) {
-          double v = 0.0;
-#pragma unroll
-          for (int k = 0; k < L; ++k) v += A.E[e][r * L + k] * bl[k];
-          red_add(P.rhs_sc + (size_t)po * P.D + r, -v);
-        }
-      }
-      for (int bb = ab; bb < n_ent; bb += NE) {
-        SchurStage<L>& B = (bb == ab) ? A : stB[wib];
-        if (bb != ab) schur_stage_load<L>(P, B, lm, s, n_obs_lm, n_ent, bb, Vinv, ref_pose, ref_opt, lane);
-        const int nb = min(NE, n_ent - bb);
-        const int n_pairs = (bb == ab) ? na * (na + 1) / 2 : na * nb;
-        for (int t = lane; t < n_pairs * 36; t += 32) {
-          const int pr = t / 36, el = t % 36;
-          int a, b;
-          if (bb == ab) {  // upper-triangular enumeration by column b: pr = b(b+1)/2 + a
-            b = (int)((sqrtf(8.0f * pr + 1.0f) - 1.0f) * 0.5f);
-            while ((b + 1) * (b + 2) / 2 <= pr) ++b;
-            while (b * (b + 1) / 2 > pr) --b;
-            a = pr - b * (b + 1) / 2;
-          } else {
-            b = pr / na; a = pr % na;
-          }
-          const int pa = A.P[a], pb = B.P[b];
-          if (pa < 0 || pb < 0) continue;
-          const int r = el % 6, cidx = el / 6;
-          double v = 0.0;
-          int bi, bj;
-          if (pa < pb || (pa == pb && bb == ab && a == b)) {
-            bi = pa; bj = pb;
-            if (pa == pb && r > cidx) continue;  // diagonal block: upper triangle only
-#pragma unroll
-            for (int k = 0; k < L; ++k) v += A.E[a][r * L + k] * B.W[b][cidx * L + k];
-          } else if (pa > pb) {
-            bi = pb; bj = pa;
-#pragma unroll
-            for (int k = 0; k < L; ++k) v += B.E[b][r * L + k] * A.W[a][cidx * L + k];
-          } else {  // same pose seen twice (multi-camera rig): both cross terms land in the diagonal block
-            bi = pa; bj = pa;
-            if (r > cidx) continue;
-#pragma unroll
-            for (int k = 0; k < L; ++k) v += A.E[a][r * L + k] * B.W[b][cidx * L + k] + B.E[b][r * L + k] * A.W[a][cidx * L + k];
-          }
-          red_add(s_block(P, bi, bj) + (size_t)cidx * P.T + r, -v);
-        }
-        __syncwarp();
-      }
-    }
-  }
-}
+// pass 2 (Jacobians, weights, landmark blocks, pose-major records) and the pose-pair-major
+// reduction into S live in schur_kernels.cu.
 
 // ---------------------------------------------------------------------------------------
 // steepest-descent denominator |J_p b_p + J_l b_l|^2 over projection residuals (cpp:879-906)
@@ -398,7 +126,8 @@ __global__ void __launch_bounds__(128) k_sd_denominator(DeviceProblem P) {
 }
 
 // ---------------------------------------------------------------------------------------
-// back-substitution: delta_l = V^-1 (b_l - W^T delta_p)   (cpp:709-744)
+// back-substitution: delta_l = V^-1 (b_l - W^T delta_p)   (cpp:709-744), from the pose-major
+// records: V^-1 W_a^T delta = C_a^T (At_a delta) for LmSize 3, E_a . delta for LmSize 1
 template <int L, int G>
 __global__ void __launch_bounds__(256) k_back_substitute(DeviceProblem P, const double* delta_p, double* delta_l) {
   const int lane = threadIdx.x & 31, gl = lane % G;
@@ -409,44 +138,41 @@ __global__ void __launch_bounds__(256) k_back_substitute(DeviceProblem P, const 
     const int lo = P.lm_opt[lm];
     if (lo < 0) continue;
     const int s = P.lm_obs_start[lm], e = P.lm_obs_start[lm + 1];
-    const int ref_pose = (int)P.lm_ref_pose[lm];
     double acc[L];
 #pragma unroll
     for (int k = 0; k < L; ++k) acc[k] = 0.0;
     for (int i = s + gl; i < e; i += G) {
-      const int m = (int)P.obs_pose[i];
-      const int mo = P.pose_opt[m];
-      if (m == ref_pose || mo < 0) continue;
-      const double* W = P.obs_W + (size_t)i * 6 * L;
-      const double* dp = delta_p + (size_t)mo * P.D;
+      const uint32_t slot = P.obs_slot[i];
+      if (slot == kNoSlot) continue;
+      const double* r = P.rec + (size_t)slot * P.rec_stride;
+      const double* dp = delta_p + (size_t)P.pose_opt[P.obs_pose[i]] * P.D;
+      if (L == 3) {
+        double t0 = 0.0, t1 = 0.0;
 #pragma unroll
-      for (int a = 0; a < 6; ++a)
+        for (int a = 0; a < 6; ++a) { t0 += r[6 + a] * dp[a]; t1 += r[12 + a] * dp[a]; }
 #pragma unroll
-        for (int k = 0; k < L; ++k) acc[k] += W[a * L + k] * dp[a];
+        for (int k = 0; k < L; ++k) acc[k] += r[k] * t0 + r[3 + k] * t1;
+      } else {
+#pragma unroll
+        for (int a = 0; a < 6; ++a) acc[0] += r[a] * dp[a];
+      }
     }
 #pragma unroll
     for (int k = 0; k < L; ++k) acc[k] = group_sum<G>(acc[k], gmask);
     if (gl == 0) {
       if (L == 1) {
-        const int ro = P.pose_opt[ref_pose];
+        const int ro = P.pose_opt[P.lm_ref_pose[lm]];
         if (ro >= 0) {
           const double* W = P.lm_Wref + (size_t)lm * 6;
           const double* dp = delta_p + (size_t)ro * P.D;
+          double t = 0.0;
 #pragma unroll
-          for (int a = 0; a < 6; ++a) acc[0] += W[a] * dp[a];
+          for (int a = 0; a < 6; ++a) t += W[a] * dp[a];
+          acc[0] += P.lm_Vinv[lm] * t;
         }
       }
-      double rhs[L];
 #pragma unroll
-      for (int k = 0; k < L; ++k) rhs[k] = P.lm_bl[(size_t)lm * L + k] - acc[k];
-      const double* Vi = P.lm_Vinv + (size_t)lm * L * L;
-#pragma unroll
-      for (int r = 0; r < L; ++r) {
-        double v = 0.0;
-#pragma unroll
-        for (int k = 0; k < L; ++k) v += Vi[r * L + k] * rhs[k];
-        delta_l[(size_t)lo * L + r] = v;
-      }
+      for (int k = 0; k < L; ++k) delta_l[(size_t)lo * L + k] = P.lm_dhat[(size_t)lm * L + k] - acc[k];
     }
   }
 }
@@ -615,19 +341,6 @@ void launch_residual(const DeviceProblem& P, int G, cudaStream_t st) {
 #define CALL(LL, GG) k_residual<LL, GG><<<grid, 256, 0, st>>>(P)
   DISPATCH_LG(P.L, G, CALL);
 #undef CALL
-}
-void launch_accumulate(const DeviceProblem& P, int G, cudaStream_t st) {
-  if (P.n_obs == 0) return;
-  const int grid = grid_for((size_t)P.n_lms * G, 128, 12);
-#define CALL(LL, GG) k_accumulate<LL, GG><<<grid, 128, 0, st>>>(P)
-  DISPATCH_LG(P.L, G, CALL);
-#undef CALL
-}
-void launch_schur(const DeviceProblem& P, cudaStream_t st) {
-  if (P.n_obs == 0 || P.n_active_lms == 0 || P.n_active_poses == 0) return;
-  const int grid = grid_for((size_t)P.n_lms * 32, 128, 8);
-  if (P.L == 1) k_schur<1><<<grid, 128, 0, st>>>(P);
-  else k_schur<3><<<grid, 128, 0, st>>>(P);
 }
 void launch_sd_denominator(const DeviceProblem& P, int G, cudaStream_t st) {
   if (P.n_obs == 0) return;

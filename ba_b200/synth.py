@@ -180,7 +180,7 @@ def make_c1(n_poses=50, n_landmarks=5000, obs_per_lm=20, seed=1001, t_vs=None, n
 
 
 # ---- windowed generator shared by C2 (L=3) and C4 (L=1/3) ----------------------------------
-def _windowed(rng, n_cams, n_points, window, track_len, lm_dim, noise_px=0.5, step=0.15, n_inactive=2):
+def _windowed(rng, n_cams, n_points, window, track_len, lm_dim, noise_px=0.5, step=0.15, n_inactive=2, anchor_every=0):
     # smooth 3-D random walk along world +x with the camera looking sideways (+y): every
     # window of consecutive cameras has a real baseline, so depth is well constrained
     R0 = np.array([[1.0, 0, 0], [0, 0, 1.0], [0, -1.0, 0]])      # columns: cam x=+x, cam y=-z (down), cam z=+y
@@ -202,8 +202,11 @@ def _windowed(rng, n_cams, n_points, window, track_len, lm_dim, noise_px=0.5, st
     # point in front of its centre camera
     local = np.stack([rng.uniform(-3, 3, n_points), rng.uniform(-2, 2, n_points), rng.uniform(8, 25, n_points)], axis=1)
     X = C[center] + np.einsum("nij,nj->ni", Rw[center], local)
-    T_init = _perturb_poses(rng, T_true, 0.02, 0.002, fixed=list(range(n_inactive)))
-    active = np.ones(n_cams, np.uint8); active[:n_inactive] = 0
+    fixed = list(range(n_inactive))
+    if anchor_every:        # surveyed keyframes along the chain: inactive poses at their true value
+        fixed = sorted(set(fixed) | set(range(0, n_cams, anchor_every)))
+    T_init = _perturb_poses(rng, T_true, 0.02, 0.002, fixed=fixed)
+    active = np.ones(n_cams, np.uint8); active[fixed] = 0
     start = np.concatenate([[0], np.cumsum(k)[:-1]])
     ref_pose = cam[start]
     if lm_dim == 1:
@@ -238,11 +241,13 @@ def make_c2(n_cams=1778, n_points=993000, seed=1002, window=64):
     return _windowed(rng, n_cams, n_points, window, track, 3)
 
 
-def make_c4(n_cams=10000, n_points=2000000, seed=1004, lm_dim=1, obs_per_point=5, window=8):
-    """Large BA <double,1,6,0> (or L=3): obs_per_point residuals per point from `window` consecutive cameras."""
+def make_c4(n_cams=10000, n_points=2000000, seed=1004, lm_dim=1, obs_per_point=5, window=8, anchor_every=0):
+    """Large BA <double,1,6,0> (or L=3): obs_per_point residuals per point from `window` consecutive cameras.
+    `anchor_every` > 0 holds every anchor_every-th camera fixed (a 10k-camera monocular chain with an 8-camera
+    window and two fixed cameras drifts along its scale gauge, cond(S) grows with the chain length)."""
     rng = np.random.default_rng(seed)
     k = obs_per_point + (1 if lm_dim == 1 else 0)
-    return _windowed(rng, n_cams, n_points, window, lambda n: np.full(n, k), lm_dim)
+    return _windowed(rng, n_cams, n_points, window, lambda n: np.full(n, k), lm_dim, anchor_every=anchor_every)
 
 
 # ---- C3: visual-inertial <double,1,15,0> -----------------------------------------------------
