@@ -145,7 +145,8 @@ struct bagpu_handle_s {
   DevBuf<ReduceItem> d_items, d_items_sym;
   DevBuf<double> d_lm_Vinv, d_lm_bl, d_lm_dhat, d_lm_Wref;
   DevBuf<double> d_S, d_S_copy, d_uinv, d_scratch, d_bp, d_rhs_sc, d_rhs_work;
-  DevBuf<int> d_tile_map, d_row_ptr, d_row_col, d_fail;
+  DevBuf<int> d_tile_map, d_row_ptr, d_row_col, d_chol_sync;
+  DevBuf<CholTask> d_chol_tasks; DevBuf<CholTerm> d_chol_terms; int n_chol_tasks = 0;
   DevBuf<Scalars> d_sc; DevBuf<SelectState> d_sel;
   DevBuf<double> d_bl_compact, d_gn_p, d_gn_l, d_dl_p, d_dl_l, d_tmp_p, d_tmp_l;
   DevBuf<double> d_res_out, d_maha_out;
@@ -366,9 +367,17 @@ struct bagpu_handle_s {
     d_lm_bl.zero(st);
     // reduced system
     const size_t tsz = (size_t)T * T;
-    d_S.alloc((size_t)n_tiles * tsz); d_uinv.alloc((size_t)nT * tsz); d_scratch.alloc(2 * (size_t)nT * T);
+    d_S.alloc((size_t)n_tiles * tsz); d_uinv.alloc((size_t)nT * tsz); d_scratch.alloc(3 * (size_t)nT * T + 2 * (size_t)n_tiles * T);
     d_bp.alloc((size_t)nT * T); d_rhs_sc.alloc((size_t)nT * T); d_rhs_work.alloc((size_t)nT * T);
-    d_tile_map.upload(tile_map, st); d_row_ptr.upload(row_ptr, st); d_row_col.upload(row_col, st); d_fail.alloc(1);
+    d_tile_map.upload(tile_map, st); d_row_ptr.upload(row_ptr, st); d_row_col.upload(row_col, st);
+    {
+      std::vector<CholTask> tasks; std::vector<CholTerm> terms;
+      chol_build_plan(nT, tile_map, row_ptr, row_col, tasks, terms);
+      n_chol_tasks = (int)tasks.size();
+      if (getenv("BAGPU_CHOL_TRACE")) h_chol_tasks = tasks;
+      d_chol_tasks.upload(tasks, st); d_chol_terms.upload(terms, st); d_chol_sync.alloc(chol_sync_ints(n_tiles, nT));
+      sync();
+    }
     d_sc.alloc(1); d_sc.zero(st); d_sel.alloc(1);
     d_bl_compact.alloc((size_t)n_al * Ls); d_gn_p.alloc((size_t)nT * T); d_gn_l.alloc((size_t)n_al * Ls);
     d_dl_p.alloc((size_t)nT * T); d_dl_l.alloc((size_t)n_al * Ls); d_tmp_p.alloc((size_t)nT * T); d_tmp_l.alloc((size_t)n_al * Ls);
@@ -661,19 +670,42 @@ struct bagpu_handle_s {
     *e_proj = v[0]; *e_bin = v[1]; *e_un = v[2]; *e_in = v[3];
   }
 
+  // development aid: BAGPU_CHOL_TRACE=<file> dumps the task table and 4 globaltimer stamps per task of the last solve
+  DevBuf<unsigned long long> d_chol_trace;
+  std::vector<CholTask> h_chol_tasks;
+  unsigned long long* chol_trace_buf() {
+    if (!getenv("BAGPU_CHOL_TRACE")) return nullptr;
+    d_chol_trace.alloc((size_t)n_chol_tasks * 4); d_chol_trace.zero(st);
+    return d_chol_trace.p;
+  }
+  void chol_trace_dump() {
+    const char* path = getenv("BAGPU_CHOL_TRACE");
+    if (!path || !d_chol_trace.p) return;
+    std::vector<unsigned long long> tr((size_t)n_chol_tasks * 4);
+    d_chol_trace.download(tr.data(), tr.size(), st); sync();
+    FILE* f = fopen(path, "wb");
+    if (!f) return;
+    fwrite(&n_chol_tasks, sizeof(int), 1, f);
+    fwrite(h_chol_tasks.data(), sizeof(CholTask), n_chol_tasks, f);
+    fwrite(tr.data(), sizeof(unsigned long long), tr.size(), f);
+    fclose(f);
+  }
+
   // CalculateGn + GetLandmarkDelta -> d_gn_p, d_gn_l
   bool gauss_newton() {
     CU(cudaEventRecord(ev[8], st));
     const size_t np = (size_t)nT * T;
     if (n_ap > 0) {
       CU(cudaMemcpyAsync(d_rhs_work.p, d_rhs_sc.p, sizeof(double) * np, cudaMemcpyDeviceToDevice, st));
-      d_fail.zero(st);
-      launch_cholesky_solve(T, d_S.p, d_uinv.p, d_scratch.p, d_rhs_work.p, d_tile_map.p, d_row_ptr.p, d_row_col.p, row_ptr.data(), nT,
-                            d_fail.p, st, &launches);
+      const int rc = launch_cholesky_solve(T, d_S.p, d_uinv.p, d_scratch.p, d_rhs_work.p, d_chol_tasks.p, d_chol_terms.p, n_chol_tasks,
+                                           d_chol_sync.p, n_tiles, nT, sms, st, chol_trace_buf());
+      if (rc != 0) throw std::string("cholesky launch: ") + cudaGetErrorString((cudaError_t)rc);
+      ++launches;
       CU(cudaMemcpyAsync(d_gn_p.p, d_rhs_work.p, sizeof(double) * np, cudaMemcpyDeviceToDevice, st));
       int f = 0;
-      d_fail.download(&f, 1, st);
+      CU(cudaMemcpyAsync(&f, d_chol_sync.p + 1, sizeof(int), cudaMemcpyDeviceToHost, st));
       sync();
+      chol_trace_dump();
       if (f != 0) { summary.result = BAGPU_FactorizationError; return false; }
     }
     summary.result = BAGPU_Success;

@@ -77,9 +77,16 @@ void launch_select_init(SelectState* st, unsigned long long k, cudaStream_t s);
 void launch_select_hist(const double* x, size_t n, SelectState* st, int pass, int sms, cudaStream_t s);
 void launch_select_scan(SelectState* st, int pass, double* out, cudaStream_t s);
 
-void launch_cholesky_solve(int T, double* tiles, double* uinv, double* work /* 2*nT*T */, double* rhs, const int* tile_map,
-                           const int* row_ptr_dev, const int* row_col_dev, const int* row_ptr_host, int nT, int* fail,
-                           cudaStream_t st, uint64_t* launches);
+// reduced solve (chol.cu): tile tasks of the persistent dataflow kernel, built on the host from the tile pattern
+struct CholTask { int kind, i, j, slot, lb, le, pad0, pad1; };
+struct CholTerm { int sa, sb, k; };   // slots of U_ki, U_kj and the row k of one left-looking update term
+void chol_build_plan(int nT, const std::vector<int>& tile_map, const std::vector<int>& row_ptr, const std::vector<int>& row_col,
+                     std::vector<CholTask>& tasks, std::vector<CholTerm>& terms);
+size_t chol_sync_ints(int n_tiles, int nT);
+// sync_ints[1] holds the first failing pivot + 1 (0 = ok) after the solve; returns a cudaError_t
+int launch_cholesky_solve(int T, double* tiles, double* uinv, double* work /* 3*nT*T + 2*n_tiles*T */, double* rhs,
+                          const CholTask* tasks, const CholTerm* terms, int n_tasks, int* sync_ints, int n_tiles, int nT, int sms,
+                          cudaStream_t st, unsigned long long* trace = nullptr);
 
 // unary / binary / inertial residuals (other_kernels.cu)
 void launch_unary_maha(const DeviceProblem& P, const OtherResiduals& R, cudaStream_t st);
