@@ -87,7 +87,8 @@ struct DeviceProblem {
   double* lm_rec;            // L == 1: 36 doubles per slot
   // reduced system
   double* S_tiles;
-  const int* tile_map;
+  const int* tile_map;       // [nT * nT] in PERMUTED tile coordinates -> slot or -1
+  const int* tile_perm;      // natural tile (opt id / 8) -> position in the elimination order (nested dissection)
   int nT, T;
   double* b_p;               // rhs_p_   [n_active_poses * D] padded to nT*T
   double* rhs_sc;            // rhs_p_sc [nT*T]

@@ -129,7 +129,7 @@ struct bagpu_handle_s {
   uint2* d_pairs = nullptr;            // cudaMalloc'ed by build_pair_lists
   int G = 8;
   int nT = 0, T = 48, n_tiles = 0, max_row = 0;
-  std::vector<int> tile_map, row_ptr, row_col;
+  std::vector<int> tile_map, row_ptr, row_col, tile_perm;
   double trust_region = -1;
   bool is_param_mask_used = false;
 
@@ -145,7 +145,7 @@ struct bagpu_handle_s {
   DevBuf<ReduceItem> d_items, d_items_sym;
   DevBuf<double> d_lm_Vinv, d_lm_bl, d_lm_dhat, d_lm_Wref;
   DevBuf<double> d_S, d_S_copy, d_uinv, d_scratch, d_bp, d_rhs_sc, d_rhs_work;
-  DevBuf<int> d_tile_map, d_row_ptr, d_row_col, d_chol_sync;
+  DevBuf<int> d_tile_map, d_row_ptr, d_row_col, d_chol_sync, d_tile_perm;
   DevBuf<CholTask> d_chol_tasks; DevBuf<CholTerm> d_chol_terms; int n_chol_tasks = 0;
   DevBuf<Scalars> d_sc; DevBuf<SelectState> d_sel;
   DevBuf<double> d_bl_compact, d_gn_p, d_gn_l, d_dl_p, d_dl_l, d_tmp_p, d_tmp_l;
@@ -258,6 +258,17 @@ struct bagpu_handle_s {
       for (size_t i = 0; i < bin_p1.size(); ++i) mark(bin_p1[i], bin_p2[i]);
       for (size_t i = 0; i < imu_p1.size(); ++i) mark(imu_p1[i], imu_p2[i]);
     }
+    // ---- elimination order of the tiles: nested dissection (a banded S is a chain of nT dependent tile rows;
+    // dissection turns it into a tree of depth ~log nT whose branches the dataflow solver runs concurrently) ----
+    nested_dissection(present);
+    {
+      std::vector<std::vector<uint8_t>> pp(nT, std::vector<uint8_t>(nT, 0));
+      for (int a = 0; a < nT; ++a) for (int b = a; b < nT; ++b) if (present[a][b]) {
+        const int x = tile_perm[a], y = tile_perm[b];
+        pp[std::min(x, y)][std::max(x, y)] = 1;
+      }
+      present.swap(pp);
+    }
     for (int k = 0; k < nT; ++k) {   // fill: eliminating tile row k couples every pair of its columns
       std::vector<int> cols;
       for (int j = k + 1; j < nT; ++j) if (present[k][j]) cols.push_back(j);
@@ -325,6 +336,51 @@ struct bagpu_handle_s {
     }
   }
 
+  // Nested dissection on the tile graph (upper pattern `present`, natural tile ids), generic recursive
+  // bisection of index-sorted node lists: the separator is the smaller set of nodes on one side of the
+  // split that touch the other side.  Falls back to the natural order where the separator is not small
+  // (dense S).  Output: tile_perm[natural tile] = position in the elimination order.
+  void nested_dissection(const std::vector<std::vector<uint8_t>>& present) {
+    tile_perm.assign(nT, 0);
+    for (int i = 0; i < nT; ++i) tile_perm[i] = i;
+    if (nT < 8 || getenv("BAGPU_NO_ND")) return;
+    std::vector<std::vector<int>> adj(nT);
+    for (int a = 0; a < nT; ++a) for (int b = a + 1; b < nT; ++b) if (present[a][b]) { adj[a].push_back(b); adj[b].push_back(a); }
+    std::vector<int> order; order.reserve(nT);
+    std::vector<int> side(nT, 0);   // scratch: 1 = left, 2 = right of the current split
+    struct Frame { std::vector<int> nodes; bool emit; };
+    std::vector<Frame> stack;
+    { Frame f; f.nodes.resize(nT); for (int i = 0; i < nT; ++i) f.nodes[i] = i; f.emit = false; stack.push_back(std::move(f)); }
+    while (!stack.empty()) {
+      Frame f = std::move(stack.back()); stack.pop_back();
+      const int n = (int)f.nodes.size();
+      if (f.emit || n <= 4) { for (int v : f.nodes) order.push_back(v); continue; }
+      const int mid = n / 2;
+      for (int k = 0; k < n; ++k) side[f.nodes[k]] = k < mid ? 1 : 2;
+      std::vector<int> sl, sr;
+      for (int k = 0; k < n; ++k) {
+        const int v = f.nodes[k], other = k < mid ? 2 : 1;
+        bool touch = false;
+        for (int u : adj[v]) if (side[u] == other) { touch = true; break; }
+        if (touch) (k < mid ? sl : sr).push_back(v);
+      }
+      const bool use_left = sl.size() <= sr.size();
+      const std::vector<int>& sep = use_left ? sl : sr;
+      for (int v : f.nodes) side[v] = 0;
+      if (sep.empty() || (int)sep.size() * 3 >= n) { for (int v : f.nodes) order.push_back(v); continue; }
+      std::vector<uint8_t> in_sep_mark;   // small: mark through `side`
+      for (int v : sep) side[v] = 3;
+      Frame left, right, sp;
+      for (int k = 0; k < n; ++k) { const int v = f.nodes[k]; if (side[v] == 3) continue; (k < mid ? left : right).nodes.push_back(v); }
+      for (int v : sep) side[v] = 0;
+      left.emit = right.emit = false;
+      sp.nodes = sep; sp.emit = true;
+      // post-order: left subtree, right subtree, separator (stack pops in reverse)
+      stack.push_back(std::move(sp)); stack.push_back(std::move(right)); stack.push_back(std::move(left));
+    }
+    for (int pos = 0; pos < nT; ++pos) tile_perm[order[pos]] = pos;
+  }
+
   void upload_all() {
     // cameras
     std::vector<double> Rvs(9 * n_cams), tvs(3 * n_cams);
@@ -369,7 +425,7 @@ struct bagpu_handle_s {
     const size_t tsz = (size_t)T * T;
     d_S.alloc((size_t)n_tiles * tsz); d_uinv.alloc((size_t)nT * tsz); d_scratch.alloc(3 * (size_t)nT * T + 2 * (size_t)n_tiles * T);
     d_bp.alloc((size_t)nT * T); d_rhs_sc.alloc((size_t)nT * T); d_rhs_work.alloc((size_t)nT * T);
-    d_tile_map.upload(tile_map, st); d_row_ptr.upload(row_ptr, st); d_row_col.upload(row_col, st);
+    d_tile_map.upload(tile_map, st); d_row_ptr.upload(row_ptr, st); d_row_col.upload(row_col, st); d_tile_perm.upload(tile_perm, st);
     {
       std::vector<CholTask> tasks; std::vector<CholTerm> terms;
       chol_build_plan(nT, tile_map, row_ptr, row_col, tasks, terms);
@@ -403,7 +459,7 @@ struct bagpu_handle_s {
     P.obs_slot = d_obs_slot.p; P.rec = d_rec.p; P.rec_stride = rec_stride;
     P.lm_rslot = (L == 1) ? d_lm_rslot.p : nullptr; P.lm_rec = (L == 1) ? d_lm_rec.p : nullptr;
     P.lm_Vinv = d_lm_Vinv.p; P.lm_bl = d_lm_bl.p; P.lm_dhat = d_lm_dhat.p; P.lm_Wref = d_lm_Wref.p;
-    P.S_tiles = d_S.p; P.tile_map = d_tile_map.p; P.nT = nT; P.T = T; P.b_p = d_bp.p; P.rhs_sc = d_rhs_sc.p; P.sc = d_sc.p;
+    P.S_tiles = d_S.p; P.tile_map = d_tile_map.p; P.tile_perm = d_tile_perm.p; P.nT = nT; P.T = T; P.b_p = d_bp.p; P.rhs_sc = d_rhs_sc.p; P.sc = d_sc.p;
     P.c_huber_factor = 1.2107;
 
     memset(&R, 0, sizeof(R));
@@ -694,14 +750,13 @@ struct bagpu_handle_s {
   // CalculateGn + GetLandmarkDelta -> d_gn_p, d_gn_l
   bool gauss_newton() {
     CU(cudaEventRecord(ev[8], st));
-    const size_t np = (size_t)nT * T;
     if (n_ap > 0) {
-      CU(cudaMemcpyAsync(d_rhs_work.p, d_rhs_sc.p, sizeof(double) * np, cudaMemcpyDeviceToDevice, st));
+      launch_permute_tiles(d_rhs_work.p, d_rhs_sc.p, d_tile_perm.p, T, nT, 1, st); ++launches;
       const int rc = launch_cholesky_solve(T, d_S.p, d_uinv.p, d_scratch.p, d_rhs_work.p, d_chol_tasks.p, d_chol_terms.p, n_chol_tasks,
                                            d_chol_sync.p, n_tiles, nT, sms, st, chol_trace_buf());
       if (rc != 0) throw std::string("cholesky launch: ") + cudaGetErrorString((cudaError_t)rc);
       ++launches;
-      CU(cudaMemcpyAsync(d_gn_p.p, d_rhs_work.p, sizeof(double) * np, cudaMemcpyDeviceToDevice, st));
+      launch_permute_tiles(d_gn_p.p, d_rhs_work.p, d_tile_perm.p, T, nT, 0, st); ++launches;
       int f = 0;
       CU(cudaMemcpyAsync(&f, d_chol_sync.p + 1, sizeof(int), cudaMemcpyDeviceToHost, st));
       sync();
@@ -1207,12 +1262,14 @@ int bagpu_get_system(bagpu_handle h, double* s_dense, double* rhs_sc, double* rh
       h->d_S.download(tiles.data(), tiles.size(), h->st);
       h->sync();
       memset(s_dense, 0, sizeof(double) * (size_t)n * n);
-      for (int tI = 0; tI < nT; ++tI) for (int tJ = tI; tJ < nT; ++tJ) {
-        const int slot = h->tile_map[(size_t)tI * nT + tJ];
+      for (int tI = 0; tI < nT; ++tI) for (int tJ = tI; tJ < nT; ++tJ) {   // natural tile ids
+        const int a = h->tile_perm[tI], b = h->tile_perm[tJ];
+        const int slot = h->tile_map[(size_t)std::min(a, b) * nT + std::max(a, b)];
         if (slot < 0) continue;
         for (int c = 0; c < T; ++c) for (int r = 0; r < T; ++r) {
           const int gi = tI * T + r, gj = tJ * T + c;
-          if (gi < n && gj < n && gi <= gj) s_dense[(size_t)gj * n + gi] = tiles[(size_t)slot * T * T + (size_t)c * T + r];
+          const size_t off = (a <= b) ? (size_t)c * T + r : (size_t)r * T + c;   // stored transposed when the order swaps the tiles
+          if (gi < n && gj < n && gi <= gj) s_dense[(size_t)gj * n + gi] = tiles[(size_t)slot * T * T + off];
         }
       }
     }

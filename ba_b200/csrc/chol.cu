@@ -405,7 +405,13 @@ void chol_build_plan(int nT, const std::vector<int>& tile_map, const std::vector
     CholTask t; t.kind = kind; t.i = i; t.j = j; t.slot = s; t.lb = lb; t.le = le; t.pad0 = 0; t.pad1 = 0;
     tasks.push_back(t);
   };
-  for (int i = 0; i < nT; ++i) {
+  // Rows are issued wavefront by wavefront of the elimination tree (level = longest dependency chain below the
+  // row), so the CTAs' claim window spans every independent branch instead of queueing behind the first one.
+  std::vector<int> level(nT, 0), rows(nT);
+  for (int i = 0; i < nT; ++i) { for (int k : col_rows[i]) level[i] = std::max(level[i], level[k] + 1); rows[i] = i; }
+  std::stable_sort(rows.begin(), rows.end(), [&](int a, int b) { return level[a] < level[b]; });
+  for (int ri = 0; ri < nT; ++ri) {
+    const int i = rows[ri];
     int lb = (int)terms.size();
     for (int k : col_rows[i]) { CholTerm tm; tm.sa = slot(k, i); tm.sb = tm.sa; tm.k = k; terms.push_back(tm); }
     add(kTaskDiag, i, i, slot(i, i), lb, (int)terms.size());
@@ -423,7 +429,14 @@ void chol_build_plan(int nT, const std::vector<int>& tile_map, const std::vector
       add(kTaskOff, i, j, slot(i, j), lb, (int)terms.size());
     }
   }
+  std::vector<int> level2(nT, 0);
   for (int k = nT - 1; k >= 0; --k) {
+    for (int e = row_ptr[k]; e < row_ptr[k + 1]; ++e) level2[k] = std::max(level2[k], level2[row_col[e]] + 1);
+    rows[nT - 1 - k] = k;
+  }
+  std::stable_sort(rows.begin(), rows.end(), [&](int a, int b) { return level2[a] < level2[b]; });
+  for (int ri = 0; ri < nT; ++ri) {
+    const int k = rows[ri];
     const int m = row_ptr[k + 1] - row_ptr[k];
     for (int e = row_ptr[k]; e < row_ptr[k + 1]; ++e) add(kTaskBackTile, k, row_col[e], slot(k, row_col[e]), 0, 0);
     add(kTaskBackRow, k, k, slot(k, k), m, 0);

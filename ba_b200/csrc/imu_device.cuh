@@ -384,16 +384,16 @@ BA_D void imu_build_one(const DeviceProblem& P, const OtherResiduals& R, int i) 
     if (o < 0) continue;
     const double* J = pass ? J2 : J1;
     for (int rr = 0; rr < D; ++rr) for (int c = 0; c < D; ++c) { double s = 0.0; for (int k = 0; k < D; ++k) s += Ci[rr * D + k] * J[k * D + c]; CJ[rr * D + c] = s; }
-    double* blk = s_block(P, o, o);
-    for (int c = 0; c < D; ++c) for (int rr = 0; rr <= c; ++rr) { double s = 0.0; for (int k = 0; k < D; ++k) s += J[k * D + rr] * CJ[k * D + c]; red_add(blk + (size_t)c * P.T + rr, s); }
+    const SBlock blk = s_block(P, o, o);
+    for (int c = 0; c < D; ++c) for (int rr = 0; rr <= c; ++rr) { double s = 0.0; for (int k = 0; k < D; ++k) s += J[k * D + rr] * CJ[k * D + c]; red_add(blk.p + (size_t)rr * blk.rs + (size_t)c * blk.cs, s); }
     for (int c = 0; c < D; ++c) { double s = 0.0; for (int k = 0; k < D; ++k) s += J[k * D + c] * Cr[k]; red_add(P.b_p + (size_t)o * D + c, s); }
     if (pass == 1 && o1 >= 0 && o1 != o2) {
       // cross block (min, max): J_min^T C J_max ; CJ currently holds C J2
       const bool first1 = o1 < o2;
       if (!first1) for (int rr = 0; rr < D; ++rr) for (int c = 0; c < D; ++c) { double s = 0.0; for (int k = 0; k < D; ++k) s += Ci[rr * D + k] * J1[k * D + c]; CJ[rr * D + c] = s; }
       const double* Ja = first1 ? J1 : J2;
-      double* xb = first1 ? s_block(P, o1, o2) : s_block(P, o2, o1);
-      for (int c = 0; c < D; ++c) for (int rr = 0; rr < D; ++rr) { double s = 0.0; for (int k = 0; k < D; ++k) s += Ja[k * D + rr] * CJ[k * D + c]; red_add(xb + (size_t)c * P.T + rr, s); }
+      const SBlock xb = first1 ? s_block(P, o1, o2) : s_block(P, o2, o1);
+      for (int c = 0; c < D; ++c) for (int rr = 0; rr < D; ++rr) { double s = 0.0; for (int k = 0; k < D; ++k) s += Ja[k * D + rr] * CJ[k * D + c]; red_add(xb.p + (size_t)rr * xb.rs + (size_t)c * xb.cs, s); }
     }
   }
 }

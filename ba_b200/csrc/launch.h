@@ -71,6 +71,7 @@ void launch_mask_diagonal(const DeviceProblem& P, const uint8_t* mask_used, int 
 void launch_dot(const double* a, const double* b, size_t n, double* out, cudaStream_t st);
 void launch_axpby(double* out, double alpha, const double* x, double beta, const double* y, size_t n, cudaStream_t st);
 void launch_compact_bl(const DeviceProblem& P, double* out, cudaStream_t st);
+void launch_permute_tiles(double* dst, const double* src, const int* perm, int T, int nT, int forward, cudaStream_t st);
 
 int select_num_passes();
 void launch_select_init(SelectState* st, unsigned long long k, cudaStream_t s);

@@ -40,13 +40,13 @@ BA_D void add_jtcj(const DeviceProblem& P, int i, int j, const double* Ja, const
       for (int k = 0; k < 6; ++k) s += C[6 * r + k] * Jb[6 * k + c];
       CJ[6 * r + c] = s;
     }
-  double* blk = s_block(P, i, j);
+  const SBlock blk = s_block(P, i, j);
   for (int c = 0; c < 6; ++c)
     for (int r = 0; r < 6; ++r) {
       if (i == j && r > c) continue;
       double s = 0.0;
       for (int k = 0; k < 6; ++k) s += Ja[6 * k + r] * CJ[6 * k + c];
-      red_add(blk + (size_t)c * P.T + r, alpha * s);
+      red_add(blk.p + (size_t)r * blk.rs + (size_t)c * blk.cs, alpha * s);
     }
 }
 

@@ -256,9 +256,7 @@ __global__ void k_mask_diagonal(DeviceProblem P, const uint8_t* mask_used, int g
   const int n_pad = P.nT * P.T;
   if (idx >= n_pad) return;
   const int n = P.n_active_poses * P.D;
-  const int tI = idx / P.T;
-  double* diag = P.S_tiles + (size_t)P.tile_map[tI * P.nT + tI] * P.T * P.T + (size_t)(idx % P.T) * P.T + (idx % P.T);
-  if (idx >= n) { *diag = 1.0; return; }
+  if (idx >= n) *s_diag(P, idx) = 1.0;
 }
 
 __global__ void k_mask_diagonal_poses(DeviceProblem P, const uint8_t* mask_used) {
@@ -269,9 +267,7 @@ __global__ void k_mask_diagonal_poses(DeviceProblem P, const uint8_t* mask_used)
   const uint32_t fr = P.pose_free[p];
   for (int k = 0; k < P.D; ++k) {
     if (!((fr >> k) & 1u)) {
-      const int idx = o * P.D + k;
-      const int tI = idx / P.T;
-      P.S_tiles[(size_t)P.tile_map[tI * P.nT + tI] * P.T * P.T + (size_t)(idx % P.T) * P.T + (idx % P.T)] = 1e6;
+      *s_diag(P, o * P.D + k) = 1e6;
     }
   }
 }
@@ -288,6 +284,14 @@ __global__ void k_dot(const double* a, const double* b, size_t n, double* out) {
 __global__ void k_axpby(double* out, double alpha, const double* x, double beta, const double* y, size_t n) {
   for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
     out[i] = alpha * x[i] + (y ? beta * y[i] : 0.0);
+}
+// tile-wise permutation of a padded pose vector: forward (natural -> elimination order) or back
+__global__ void k_permute_tiles(double* dst, const double* src, const int* perm, int T, int nT, int forward) {
+  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= nT * T) return;
+  const int t = idx / T, o = idx - t * T;
+  if (forward) dst[(size_t)perm[t] * T + o] = src[idx];
+  else dst[idx] = src[(size_t)perm[t] * T + o];
 }
 // gather b_l (indexed by landmark id) into opt-id order (rhs_l_)
 template <int L>
@@ -386,6 +390,10 @@ void launch_dot(const double* a, const double* b, size_t n, double* out, cudaStr
 void launch_axpby(double* out, double alpha, const double* x, double beta, const double* y, size_t n, cudaStream_t st) {
   if (n == 0) return;
   k_axpby<<<grid_for(n, 256, 4), 256, 0, st>>>(out, alpha, x, beta, y, n);
+}
+void launch_permute_tiles(double* dst, const double* src, const int* perm, int T, int nT, int forward, cudaStream_t st) {
+  if (nT * T == 0) return;
+  k_permute_tiles<<<(nT * T + 255) / 256, 256, 0, st>>>(dst, src, perm, T, nT, forward);
 }
 void launch_compact_bl(const DeviceProblem& P, double* out, cudaStream_t st) {
   if (P.n_lms == 0 || P.L == 0) return;

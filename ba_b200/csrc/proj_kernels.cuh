@@ -178,11 +178,27 @@ BA_D double huber_weight(double maha0, double w0, double c_huber, int use_robust
   return ((use_robust & 1) && e > c_huber) ? w0 * (c_huber / e) : w0;
 }
 
-// address of element (r, c) of pose block (i, j), i <= j, inside the tiled S
-BA_D double* s_block(const DeviceProblem& P, int i, int j) {
-  const int tI = i / kTilePoses, tJ = j / kTilePoses;
-  const int slot = P.tile_map[tI * P.nT + tJ];
-  return P.S_tiles + (size_t)slot * P.T * P.T + (size_t)((j % kTilePoses) * P.D) * P.T + (i % kTilePoses) * P.D;
+// Pose block (i, j), i <= j (opt ids), inside the tiled S: element (r, c) lives at p[r * rs + c * cs].
+// Tiles are stored for the upper triangle of the PERMUTED tile order; when the permutation swaps the two
+// tiles the block is stored transposed.
+struct SBlock { double* p; int rs, cs; };
+BA_D SBlock s_block(const DeviceProblem& P, int i, int j) {
+  const int a = P.tile_perm[i / kTilePoses], b = P.tile_perm[j / kTilePoses];
+  const int oi = (i % kTilePoses) * P.D, oj = (j % kTilePoses) * P.D;
+  SBlock o;
+  if (a <= b) {
+    o.p = P.S_tiles + (size_t)P.tile_map[a * P.nT + b] * P.T * P.T + (size_t)oj * P.T + oi;
+    o.rs = 1; o.cs = P.T;
+  } else {
+    o.p = P.S_tiles + (size_t)P.tile_map[b * P.nT + a] * P.T * P.T + (size_t)oi * P.T + oj;
+    o.rs = P.T; o.cs = 1;
+  }
+  return o;
+}
+// diagonal element idx (natural order) of S
+BA_D double* s_diag(const DeviceProblem& P, int idx) {
+  const int t = P.tile_perm[idx / P.T], o = idx % P.T;
+  return P.S_tiles + (size_t)P.tile_map[t * P.nT + t] * P.T * P.T + (size_t)o * P.T + o;
 }
 
 }  // namespace bagpu

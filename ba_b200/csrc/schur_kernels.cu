@@ -397,7 +397,7 @@ __global__ void __launch_bounds__(kRedWarps * 32) k_reduce_blocks(DeviceProblem 
     }
     // ---- write-out (exclusive owner: plain read-modify-write) ------------------------------
     const bool diag = (w.kind == kItemDiagObs || w.kind == kItemDiagLm);
-    double* blk = s_block(P, (int)w.row, (int)w.col);
+    const SBlock blk = s_block(P, (int)w.row, (int)w.col);
 #pragma unroll
     for (int half = 0; half < 2; ++half) {
       const int el = half * 32 + lane;
@@ -408,7 +408,7 @@ __global__ void __launch_bounds__(kRedWarps * 32) k_reduce_blocks(DeviceProblem 
           int c = 0;
           while ((c + 1) * (c + 2) / 2 <= el) ++c;
           const int r = el - c * (c + 1) / 2;
-          blk[(size_t)c * P.T + r] += v;
+          blk.p[(size_t)r * blk.rs + (size_t)c * blk.cs] += v;
         } else if (el < 27) {
           P.b_p[(size_t)w.row * P.D + (el - 21)] += v;
         } else if (el < 33) {
@@ -416,7 +416,7 @@ __global__ void __launch_bounds__(kRedWarps * 32) k_reduce_blocks(DeviceProblem 
         }
       } else {
         const int c = el / 6, r = el - c * 6;
-        if (w.kind == kItemOff || r <= c) blk[(size_t)c * P.T + r] += v;
+        if (w.kind == kItemOff || r <= c) blk.p[(size_t)r * blk.rs + (size_t)c * blk.cs] += v;
       }
     }
   }

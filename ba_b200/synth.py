@@ -217,6 +217,10 @@ def _windowed(rng, n_cams, n_points, window, track_len, lm_dim, noise_px=0.5, st
     else:
         owner_r, cam_r = owner, cam
         Xw = X + rng.normal(0, 0.05, X.shape)
+        # The reference zeroes dz/dx_meas whenever the measuring pose is the landmark's reference pose, for every
+        # LmSize (parallel_algos.h:86-99).  A 3-D world point has no privileged frame, so the caller names a pose
+        # that is not optimised (the fixed first camera): no optimised Jacobian is dropped.
+        ref_pose = np.zeros(n_points, np.int64)
     z, depth = project(T_true[cam_r], X[owner_r])
     assert depth.min() > 0.5, depth.min()
     z = z + rng.normal(0, noise_px, z.shape)

@@ -108,7 +108,7 @@ def test_c1_monocular_full_size():
     ("c1", lambda: synth.make_c1(n_poses=12, n_landmarks=200, obs_per_lm=8), 6, 1e-9),
     ("c1_tvs", lambda: synth.make_c1(n_poses=10, n_landmarks=150, obs_per_lm=6, t_vs=[0.01, -0.02, 0.03, 0.9993, 0.1, -0.05, 0.02]), 6, 1e-9),
     ("c1_outliers", lambda: synth.make_c1(n_poses=10, n_landmarks=150, obs_per_lm=6, outlier_frac=0.1), 6, 1e-9),
-    ("c2", lambda: synth.make_c2(n_cams=100, n_points=3000), 5, 1e-9),
+    ("c2", lambda: synth.make_c2(n_cams=100, n_points=3000), 5, 1e-8),    # cond(S) = 7.4e8 (numpy): cond * 2^-53 = 8e-8
     ("c4", lambda: synth.make_c4(n_cams=60, n_points=2000), 5, 1e-8),     # cond(S) ~ 6e8
     ("c4_l3", lambda: synth.make_c4(n_cams=60, n_points=2000, lm_dim=3), 5, 1e-8),
     ("c5", lambda: synth.make_c5(n_poses=200), 3, 1e-8),
@@ -214,9 +214,7 @@ def test_noise_free_round_trip_recovers_ground_truth():
     a = p.arrays()
     z, _ = synth.project(p.truth["T"][a["proj_meas_pose"]], p.truth["X"][a["proj_lm"]])
     p.set_bulk(proj_z=z)
-    # the Huber scale is the median residual (cpp:1353-1388): on exact data it re-weights half of the residuals
-    # every iteration and the reference loop (oracle included) only creeps; plain least squares converges
-    g = gpu(p, use_robust_norm_for_proj_residuals=0)
+    g = gpu(p)
     s = g.solve(15)
     assert s.post_solve_norm < 1e-10
     T = g.get_poses()["t_wp"]
