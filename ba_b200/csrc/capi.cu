@@ -519,7 +519,7 @@ struct bagpu_handle_s {
     }
     n_items = (int)items.size(); n_items_sym = (int)sym.size();
     d_items.upload(items, st); d_items_sym.upload(sym, st);
-    d_partial.alloc((size_t)std::max<uint32_t>(1, n_partial) * 36); d_counters.alloc(std::max<uint32_t>(1, n_groups)); d_counters.zero(st);
+    d_partial.alloc((size_t)std::max<uint32_t>(1, n_partial) * 48); d_counters.alloc((size_t)n_groups + 2); d_counters.zero(st);   // [0] = item counter of the running launch
     sync();   // the host vectors above go out of scope
   }
 
@@ -639,8 +639,8 @@ struct bagpu_handle_s {
     }
     CU(cudaEventRecord(ev[4], st));
     CU(cudaMemcpyAsync(d_rhs_sc.p, d_bp.p, sizeof(double) * (size_t)nT * T, cudaMemcpyDeviceToDevice, st));
-    if (n_items) { launch_reduce_blocks(P, d_items.p, n_items, d_pairs, d_partial.p, d_counters.p, st); ++launches; }
-    if (n_items_sym) { launch_reduce_blocks(P, d_items_sym.p, n_items_sym, d_pairs, d_partial.p, d_counters.p, st); ++launches; }
+    if (n_items) { launch_reduce_blocks(P, d_items.p, n_items, d_pairs, d_partial.p, d_counters.p + 1, d_counters.p, st); ++launches; }
+    if (n_items_sym) { launch_reduce_blocks(P, d_items_sym.p, n_items_sym, d_pairs, d_partial.p, d_counters.p + 1, d_counters.p, st); ++launches; }
     CU(cudaEventRecord(ev[5], st));
     if (world > 1) {
       allreduce_f64(d_S.p, (size_t)n_tiles * T * T);

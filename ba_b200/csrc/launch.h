@@ -61,7 +61,7 @@ void launch_finish_xw(const DeviceProblem& P, double* lm_xw, cudaStream_t st);
 void launch_residual(const DeviceProblem& P, int G, cudaStream_t st);
 void launch_linearize(const DeviceProblem& P, int G, cudaStream_t st);
 void launch_reduce_blocks(const DeviceProblem& P, const ReduceItem* items, int n_items, const uint2* pairs, double* partial,
-                          unsigned int* counters, cudaStream_t st);
+                          unsigned int* counters, unsigned int* next_item, cudaStream_t st);
 void launch_sd_denominator(const DeviceProblem& P, int G, cudaStream_t st);
 void launch_back_substitute(const DeviceProblem& P, int G, const double* delta_p, double* delta_l, cudaStream_t st);
 void launch_evaluate(const DeviceProblem& P, int G, double* out_sum, double* res_out, double* maha_out, cudaStream_t st);

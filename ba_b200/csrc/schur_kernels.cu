@@ -216,170 +216,246 @@ __global__ void __launch_bounds__(128) k_linearize(DeviceProblem P) {
 }
 
 // ---------------------------------------------------------------------------------------
-// pass B: one warp per work item (a chunk of one S block).  Lanes stride over the item's
-// records / pairs with a full set of accumulators in registers, then the 32 partial sets are
-// transposed through shared memory so that lane k owns element k of the block.
-constexpr int kAcc = 36;
+// pass B: one warp per work item (a chunk of one S block), items claimed in order from one counter
+// so that the warps in flight always work on neighbouring blocks (their records stay in L2).
+// The records of 16 pairs (or 16 consecutive records of a diagonal item) are brought into shared
+// memory by cp.async with CHUNK-wise lane mapping — consecutive lanes copy consecutive 16-byte
+// pieces of one record, a few cache lines per instruction instead of 32 — in a 3-stage pipeline.
+// Two lanes share a pair: each multiplies out three of the six block columns (24 accumulators per
+// lane instead of 36+12: registers set the occupancy of this latency-bound gather).  The partial
+// sets are transposed through shared memory so that lane k owns element k of the block.
+constexpr int kAccL = 24;          // per lane: 6 rows x 3 columns, then 6 entries of b_p (even lane) or rhs_sc (odd lane)
+constexpr int kPartial = 48;       // doubles per partial-sum slot: two halves of kAccL
 constexpr int kRedWarps = 4;
+constexpr int kPPB = 16;           // pairs (or records) per batch
+constexpr int kStages = 3;
+template <int L> struct RedCfg {
+  static constexpr int PS = (L == 3) ? 18 : 24;                 // doubles per staged pair part
+  static constexpr int RS = (L == 3) ? kRec3 : kRec1;           // doubles per record
+  static constexpr int DATA = (2 * kPPB * PS > kPPB * RS) ? 2 * kPPB * PS : kPPB * RS;   // >= kPPB * kLmRec
+  static constexpr int BUF = DATA + 8;                          // + 16 uint32 tags
+  static constexpr size_t smem = sizeof(double) * kStages * BUF * kRedWarps;
+};
 
+BA_D void cp_async16(double* smem_dst, const double* gsrc) {
+  const unsigned d = (unsigned)__cvta_generic_to_shared(smem_dst);
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(d), "l"(gsrc) : "memory");
+}
+BA_D void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N> BA_D void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+
+// diagonal record, lane half h: columns 3h..3h+2 of A^T N A (all six rows) and b_p (h = 0) or rhs_sc (h = 1)
 template <int L>
-BA_D void diag_record(const double* __restrict__ r, double* acc) {
-  // acc[0..20] upper triangle (k = c(c+1)/2 + r), acc[21..26] b_p, acc[27..32] rhs_sc
+BA_D void diag_record(const double* r, int h, double* acc) {
   double A[12];
-  double n00, n01, n10, n11, r0, r1, p0, p1;
+#pragma unroll
+  for (int k = 0; k < 6; ++k) ld2(r + (L == 3 ? 6 : 12) + 2 * k, A[2 * k], A[2 * k + 1]);
+  double q0, q1;
+  ld2(r + (L == 3 ? 24 : 36) + 2 * h, q0, q1);     // (r0, r1) or (rho0, rho1)
   if (L == 3) {
     double C[6], B[6];
 #pragma unroll
-    for (int k = 0; k < 3; ++k) ld2(r + 2 * k, C[2 * k], C[2 * k + 1]);
+    for (int k = 0; k < 3; ++k) { ld2(r + 2 * k, C[2 * k], C[2 * k + 1]); ld2(r + 18 + 2 * k, B[2 * k], B[2 * k + 1]); }
+    const double n00 = 1.0 - (C[0] * B[0] + C[1] * B[1] + C[2] * B[2]);
+    const double n01 = -(C[0] * B[3] + C[1] * B[4] + C[2] * B[5]);
+    const double n10 = -(C[3] * B[0] + C[4] * B[1] + C[5] * B[2]);
+    const double n11 = 1.0 - (C[3] * B[3] + C[4] * B[4] + C[5] * B[5]);
 #pragma unroll
-    for (int k = 0; k < 6; ++k) ld2(r + 6 + 2 * k, A[2 * k], A[2 * k + 1]);
+    for (int c = 0; c < 3; ++c) {
+      const double a0 = h ? A[3 + c] : A[c], a1 = h ? A[9 + c] : A[6 + c];
+      const double t0 = n00 * a0 + n01 * a1, t1 = n10 * a0 + n11 * a1;
 #pragma unroll
-    for (int k = 0; k < 3; ++k) ld2(r + 18 + 2 * k, B[2 * k], B[2 * k + 1]);
-    ld2(r + 24, r0, r1);
-    ld2(r + 26, p0, p1);
-    n00 = 1.0 - (C[0] * B[0] + C[1] * B[1] + C[2] * B[2]);
-    n01 = -(C[0] * B[3] + C[1] * B[4] + C[2] * B[5]);
-    n10 = -(C[3] * B[0] + C[4] * B[1] + C[5] * B[2]);
-    n11 = 1.0 - (C[3] * B[3] + C[4] * B[4] + C[5] * B[5]);
-    int k = 0;
-#pragma unroll
-    for (int c = 0; c < 6; ++c) {
-      const double t0 = n00 * A[c] + n01 * A[6 + c], t1 = n10 * A[c] + n11 * A[6 + c];
-#pragma unroll
-      for (int rr = 0; rr <= c; ++rr) { acc[k] += A[rr] * t0 + A[6 + rr] * t1; ++k; }
+      for (int rr = 0; rr < 6; ++rr) acc[c * 6 + rr] += A[rr] * t0 + A[6 + rr] * t1;
     }
   } else {
-    double E[6], W[6];
+    double E[6];
 #pragma unroll
     for (int k = 0; k < 3; ++k) ld2(r + 2 * k, E[2 * k], E[2 * k + 1]);
+    const double* Wh = r + 6 + 3 * h;
 #pragma unroll
-    for (int k = 0; k < 3; ++k) ld2(r + 6 + 2 * k, W[2 * k], W[2 * k + 1]);
+    for (int c = 0; c < 3; ++c) {
+      const double a0 = h ? A[3 + c] : A[c], a1 = h ? A[9 + c] : A[6 + c], wc = Wh[c];
 #pragma unroll
-    for (int k = 0; k < 6; ++k) ld2(r + 12 + 2 * k, A[2 * k], A[2 * k + 1]);
-    ld2(r + 36, r0, r1);
-    ld2(r + 38, p0, p1);
-    int k = 0;
-#pragma unroll
-    for (int c = 0; c < 6; ++c)
-#pragma unroll
-      for (int rr = 0; rr <= c; ++rr) { acc[k] += A[rr] * A[c] + A[6 + rr] * A[6 + c] - E[rr] * W[c]; ++k; }
+      for (int rr = 0; rr < 6; ++rr) acc[c * 6 + rr] += A[rr] * a0 + A[6 + rr] * a1 - E[rr] * wc;
+    }
   }
 #pragma unroll
-  for (int k = 0; k < 6; ++k) {
-    acc[21 + k] += A[k] * r0 + A[6 + k] * r1;
-    acc[27 + k] += A[k] * p0 + A[6 + k] * p1;
-  }
+  for (int k = 0; k < 6; ++k) acc[18 + k] += A[k] * q0 + A[6 + k] * q1;
 }
 
-// Y = contribution of the pair (a in the row pose, b in the column pose) to the block, el = c*6 + r
+// acc += columns 3h..3h+2 of the contribution of one staged pair to its block.  pa: part of the entry in the
+// row pose, pb: part of the entry in the column pose.
+//   LmSize 3: pa = [C (2x3) | At (2x6)], pb = [At (2x6) | Bt (2x3)]          -At_a^T C_a Bt_b^T At_b
+//   LmSize 1: tag < kPairTagRefRow: pa = E (6), pb = W (6)                    -E_a W_b^T
+//             else pa = [At (2x6) | Q (2x6)]:  At^T Q (measurement pose is the row) or Q^T At
 template <int L>
-BA_D void pair_product(const DeviceProblem& P, uint32_t a, uint32_t b, double* Y) {
-  const double* ra = P.rec + (size_t)a * P.rec_stride;
+BA_D void pair_product(const double* pa, const double* pb, uint32_t tag, int h, double* acc) {
   if (L == 3) {
-    const double* rb = P.rec + (size_t)b * kRec3;
-    double C[6], B[6], Ab[12], Aa[12];
+    double C[6], B[6], Aa[12];
 #pragma unroll
-    for (int k = 0; k < 3; ++k) ld2(ra + 2 * k, C[2 * k], C[2 * k + 1]);
-#pragma unroll
-    for (int k = 0; k < 3; ++k) ld2(rb + 18 + 2 * k, B[2 * k], B[2 * k + 1]);
-#pragma unroll
-    for (int k = 0; k < 6; ++k) ld2(rb + 6 + 2 * k, Ab[2 * k], Ab[2 * k + 1]);
-#pragma unroll
-    for (int k = 0; k < 6; ++k) ld2(ra + 6 + 2 * k, Aa[2 * k], Aa[2 * k + 1]);
+    for (int k = 0; k < 3; ++k) { ld2(pa + 2 * k, C[2 * k], C[2 * k + 1]); ld2(pb + 12 + 2 * k, B[2 * k], B[2 * k + 1]); }
     const double m00 = -(C[0] * B[0] + C[1] * B[1] + C[2] * B[2]);
     const double m01 = -(C[0] * B[3] + C[1] * B[4] + C[2] * B[5]);
     const double m10 = -(C[3] * B[0] + C[4] * B[1] + C[5] * B[2]);
     const double m11 = -(C[3] * B[3] + C[4] * B[4] + C[5] * B[5]);
 #pragma unroll
-    for (int c = 0; c < 6; ++c) {
-      const double t0 = m00 * Ab[c] + m01 * Ab[6 + c], t1 = m10 * Ab[c] + m11 * Ab[6 + c];
+    for (int k = 0; k < 6; ++k) ld2(pa + 6 + 2 * k, Aa[2 * k], Aa[2 * k + 1]);
+    const double* b0 = pb + 3 * h;
 #pragma unroll
-      for (int r = 0; r < 6; ++r) Y[c * 6 + r] += Aa[r] * t0 + Aa[6 + r] * t1;
+    for (int c = 0; c < 3; ++c) {
+      const double x0 = b0[c], x1 = b0[6 + c];
+      const double t0 = m00 * x0 + m01 * x1, t1 = m10 * x0 + m11 * x1;
+#pragma unroll
+      for (int r = 0; r < 6; ++r) acc[c * 6 + r] += Aa[r] * t0 + Aa[6 + r] * t1;
     }
   } else {
-    if (b < kPairTagRefRow) {   // measurement x measurement: -E_a W_b^T
-      const double* rb = P.rec + (size_t)b * kRec1;
-      double E[6], W[6];
+    if (tag < kPairTagRefRow) {
+      double E[6];
 #pragma unroll
-      for (int k = 0; k < 3; ++k) ld2(ra + 2 * k, E[2 * k], E[2 * k + 1]);
+      for (int k = 0; k < 3; ++k) ld2(pa + 2 * k, E[2 * k], E[2 * k + 1]);
+      const double* w = pb + 3 * h;
 #pragma unroll
-      for (int k = 0; k < 3; ++k) ld2(rb + 6 + 2 * k, W[2 * k], W[2 * k + 1]);
+      for (int c = 0; c < 3; ++c) {
+        const double wc = w[c];
 #pragma unroll
-      for (int c = 0; c < 6; ++c)
+        for (int r = 0; r < 6; ++r) acc[c * 6 + r] -= E[r] * wc;
+      }
+    } else {
+      double X[12];
+      const bool meas_row = (tag == kPairTagMeasRow);
+      const double* x = pa + (meas_row ? 0 : 12);
+      const double* z = pa + (meas_row ? 12 : 0) + 3 * h;
 #pragma unroll
-        for (int r = 0; r < 6; ++r) Y[c * 6 + r] -= E[r] * W[c];
-    } else {                    // measurement x reference pose of the same observation: A^T Q or Q^T A
-      double X[12], Z[12];
-      const bool meas_row = (b == kPairTagMeasRow);
-      const double* x = ra + (meas_row ? 12 : 24);
-      const double* z = ra + (meas_row ? 24 : 12);
+      for (int k = 0; k < 6; ++k) ld2(x + 2 * k, X[2 * k], X[2 * k + 1]);
 #pragma unroll
-      for (int k = 0; k < 6; ++k) { ld2(x + 2 * k, X[2 * k], X[2 * k + 1]); ld2(z + 2 * k, Z[2 * k], Z[2 * k + 1]); }
+      for (int c = 0; c < 3; ++c) {
+        const double z0 = z[c], z1 = z[6 + c];
 #pragma unroll
-      for (int c = 0; c < 6; ++c)
-#pragma unroll
-        for (int r = 0; r < 6; ++r) Y[c * 6 + r] += X[r] * Z[c] + X[6 + r] * Z[6 + c];
+        for (int r = 0; r < 6; ++r) acc[c * 6 + r] += X[r] * z0 + X[6 + r] * z1;
+      }
     }
   }
 }
 
+// stage the parts of up to kPPB pairs (batch `bt` of the item) into buf, their tags behind the data
 template <int L>
-__global__ void __launch_bounds__(kRedWarps * 32) k_reduce_blocks(DeviceProblem P, const ReduceItem* __restrict__ items, int n_items,
-                                                                  const uint2* __restrict__ pairs, double* __restrict__ partial,
-                                                                  unsigned int* __restrict__ counters) {
-  __shared__ double sbuf[kRedWarps][kAcc][33];
-  const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
-  const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-  const int n_warps = (gridDim.x * blockDim.x) >> 5;
-  double (*buf)[33] = sbuf[wib];
-  for (int it = warp; it < n_items; it += n_warps) {
-    const ReduceItem w = items[it];
-    double acc[kAcc];
+BA_D void stage_pairs(const DeviceProblem& P, const uint2* __restrict__ pairs, uint32_t begin, uint32_t end, int bt, double* buf, int lane) {
+  constexpr int PS = RedCfg<L>::PS, PC = PS / 2;     // 16-byte chunks per part
+  const uint32_t p = begin + (uint32_t)bt * kPPB + (lane & (kPPB - 1));
+  const uint2 ab = (p < end) ? pairs[p] : make_uint2(kNoSlot, kNoSlot);
+  if (lane < kPPB) reinterpret_cast<uint32_t*>(buf + RedCfg<L>::DATA)[lane] = (ab.x == kNoSlot) ? kNoSlot - 2 : ab.y;
 #pragma unroll
-    for (int k = 0; k < kAcc; ++k) acc[k] = 0.0;
-    if (w.kind == kItemDiagObs) {
-      for (uint32_t s = w.begin + lane; s < w.end; s += 32) diag_record<L>(P.rec + (size_t)s * P.rec_stride, acc);
-    } else if (w.kind == kItemDiagLm) {
-      for (uint32_t s = w.begin + lane; s < w.end; s += 32) {
-        const double* r = P.lm_rec + (size_t)s * kLmRec;
-#pragma unroll
-        for (int k = 0; k < 17; ++k) { double a, b; ld2(r + 2 * k, a, b); acc[2 * k] += a; if (2 * k + 1 < 33) acc[2 * k + 1] += b; }
-      }
-    } else if (w.kind == kItemOff) {
-      for (uint32_t p = w.begin + lane; p < w.end; p += 32) {
-        const uint2 ab = pairs[p];
-        pair_product<L>(P, ab.x, ab.y, acc);
-      }
-    } else {   // same pose observed twice (several cameras): both cross terms land in the diagonal block
-      for (uint32_t p = w.begin + lane; p < w.end; p += 32) {
-        const uint2 ab = pairs[p];
-        double Y[kAcc];
-#pragma unroll
-        for (int k = 0; k < kAcc; ++k) Y[k] = 0.0;
-        pair_product<L>(P, ab.x, ab.y, Y);
-#pragma unroll
-        for (int c = 0; c < 6; ++c)
-#pragma unroll
-          for (int r = 0; r < 6; ++r) acc[c * 6 + r] += Y[c * 6 + r] + Y[r * 6 + c];
-      }
+  for (int k = 0; k < (2 * kPPB * PC) / 32; ++k) {
+    const int idx = k * 32 + lane;
+    const int part = idx / PC, chunk = idx - part * PC;
+    const int pl = part >> 1, side = part & 1;
+    const uint32_t sa = __shfl_sync(0xffffffffu, ab.x, pl), sb = __shfl_sync(0xffffffffu, ab.y, pl);
+    if (sa == kNoSlot) continue;
+    const double* src;
+    int n;
+    if (L == 3) {
+      src = P.rec + (size_t)(side ? sb : sa) * kRec3 + (side ? 6 : 0);
+      n = PC;
+    } else if (sb < kPairTagRefRow) {
+      src = P.rec + (size_t)(side ? sb : sa) * kRec1 + (side ? 6 : 0);
+      n = 3;
+    } else {
+      src = P.rec + (size_t)sa * kRec1 + 12;
+      n = side ? 0 : 12;
     }
-    // ---- transpose-reduce: lane k ends with element k (lanes 0..3 also element 32 + k) ----
-    __syncwarp();
+    if (chunk < n) cp_async16(buf + part * PS + chunk * 2, src + chunk * 2);
+  }
+}
+
+// stage up to kPPB consecutive records (stride RS doubles) starting at slot s0 (s0 may be past the end)
+template <int RS>
+BA_D void stage_records(const double* __restrict__ base, uint32_t s0, uint32_t end, double* buf, int lane) {
+  if (s0 >= end) return;
+  const int cnt = (int)min((uint32_t)kPPB, end - s0);
+  const double* src = base + (size_t)s0 * RS;
 #pragma unroll
-    for (int k = 0; k < kAcc; ++k) buf[k][lane] = acc[k];
+  for (int k = 0; k < (kPPB * RS / 2 + 31) / 32; ++k) {
+    const int idx = k * 32 + lane;
+    if (idx < cnt * (RS / 2)) cp_async16(buf + idx * 2, src + idx * 2);
+  }
+}
+
+template <int L>
+__global__ void __launch_bounds__(kRedWarps * 32, 4) k_reduce_blocks(DeviceProblem P, const ReduceItem* __restrict__ items, int n_items,
+                                                                     const uint2* __restrict__ pairs, double* __restrict__ partial,
+                                                                     unsigned int* __restrict__ counters, unsigned int* __restrict__ next_item) {
+  typedef RedCfg<L> Cfg;
+  extern __shared__ double sdyn[];
+  const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+  const int pl = lane >> 1, h = lane & 1;
+  double* stage = sdyn + (size_t)wib * kStages * Cfg::BUF;   // the transpose-reduce reuses the stage buffers
+  for (;;) {
+    int it = 0;
+    if (lane == 0) it = (int)atomicAdd(next_item, 1u);
+    it = __shfl_sync(0xffffffffu, it, 0);
+    if (it >= n_items) break;
+    const ReduceItem w = items[it];
+    double acc[kAccL];
+#pragma unroll
+    for (int k = 0; k < kAccL; ++k) acc[k] = 0.0;
+    const int nb = (int)((w.end - w.begin + kPPB - 1) / kPPB);
+    const bool diag = (w.kind == kItemDiagObs || w.kind == kItemDiagLm);
+    const bool obs = (w.kind == kItemDiagObs);
+    // ---- software pipeline: batch bt + kStages - 1 is in flight while batch bt is multiplied out ----
+    for (int bt = -(kStages - 1); bt < nb; ++bt) {
+      const int ld = bt + kStages - 1;
+      if (ld < nb) {
+        double* dst = stage + (ld % kStages) * Cfg::BUF;
+        if (!diag) stage_pairs<L>(P, pairs, w.begin, w.end, ld, dst, lane);
+        else if (obs) stage_records<Cfg::RS>(P.rec, w.begin + (uint32_t)ld * kPPB, w.end, dst, lane);
+        else stage_records<kLmRec>(P.lm_rec, w.begin + (uint32_t)ld * kPPB, w.end, dst, lane);
+      }
+      cp_async_commit();
+      if (bt < 0) continue;
+      cp_async_wait<kStages - 1>();
+      __syncwarp();
+      const double* cur = stage + (bt % kStages) * Cfg::BUF;
+      if (!diag) {
+        const uint32_t tag = reinterpret_cast<const uint32_t*>(cur + Cfg::DATA)[pl];
+        if (tag != kNoSlot - 2) pair_product<L>(cur + (2 * pl) * Cfg::PS, cur + (2 * pl + 1) * Cfg::PS, tag, h, acc);
+      } else if (w.begin + (uint32_t)bt * kPPB + pl < w.end) {
+        if (obs) {
+          diag_record<L>(cur + pl * Cfg::RS, h, acc);
+        } else {   // reference-pose records (LmSize 1): upper triangle (21) | g_r (6) | g_r~ (6), plain sums
+          const double* r = cur + pl * kLmRec;
+#pragma unroll
+          for (int c = 0; c < 3; ++c)
+#pragma unroll
+            for (int rr = 0; rr < 6; ++rr) { const int cg = 3 * h + c; if (rr <= cg) acc[c * 6 + rr] += r[cg * (cg + 1) / 2 + rr]; }
+#pragma unroll
+          for (int k = 0; k < 6; ++k) acc[18 + k] += r[21 + 6 * h + k];
+        }
+      }
+      __syncwarp();
+    }
+    cp_async_wait<0>();
+    // ---- transpose-reduce over the 16 lanes of each half: element e = h * 24 + k, e < 48 ----
+    double (*buf)[33] = reinterpret_cast<double (*)[33]>(stage);
+#pragma unroll
+    for (int k = 0; k < kAccL; ++k) buf[k][lane] = acc[k];
     __syncwarp();
     double v0 = 0.0, v1 = 0.0;
+    {
+      const int e = lane, eh = e / kAccL, ek = e - eh * kAccL;
 #pragma unroll 8
-    for (int j = 0; j < 32; ++j) v0 += buf[lane][j];
-    if (lane < kAcc - 32) {
-#pragma unroll 8
-      for (int j = 0; j < 32; ++j) v1 += buf[32 + lane][j];
+      for (int j = 0; j < 16; ++j) v0 += buf[ek][2 * j + eh];
     }
+    if (lane < 2 * kAccL - 32) {
+      const int e = 32 + lane, eh = e / kAccL, ek = e - eh * kAccL;
+#pragma unroll 8
+      for (int j = 0; j < 16; ++j) v1 += buf[ek][2 * j + eh];
+    }
+    __syncwarp();
     // ---- chunks of one block are combined in index order by the last one to arrive --------
     if (w.mcount > 1) {
-      double* mine = partial + (size_t)w.mself * kAcc;
+      double* mine = partial + (size_t)w.mself * kPartial;
       mine[lane] = v0;
-      if (lane < kAcc - 32) mine[32 + lane] = v1;
+      if (lane < 2 * kAccL - 32) mine[32 + lane] = v1;
       __threadfence();
       __syncwarp();
       unsigned int prev = 0;
@@ -390,35 +466,35 @@ __global__ void __launch_bounds__(kRedWarps * 32) k_reduce_blocks(DeviceProblem 
       if (lane == 0) counters[w.mgroup] = 0;   // ready for the next build
       v0 = 0.0; v1 = 0.0;
       for (uint32_t ch = 0; ch < w.mcount; ++ch) {
-        const volatile double* q = partial + (size_t)(w.mfirst + ch) * kAcc;
+        const volatile double* q = partial + (size_t)(w.mfirst + ch) * kPartial;
         v0 += q[lane];
-        if (lane < kAcc - 32) v1 += q[32 + lane];
+        if (lane < 2 * kAccL - 32) v1 += q[32 + lane];
       }
     }
     // ---- write-out (exclusive owner: plain read-modify-write) ------------------------------
-    const bool diag = (w.kind == kItemDiagObs || w.kind == kItemDiagLm);
     const SBlock blk = s_block(P, (int)w.row, (int)w.col);
+    if (w.kind == kItemSym) {   // same pose observed twice: X + X^T lands in the (upper) diagonal block
+      double* sy = stage;
+      sy[lane] = v0;
+      if (lane < 2 * kAccL - 32) sy[32 + lane] = v1;
+      __syncwarp();
+    }
 #pragma unroll
     for (int half = 0; half < 2; ++half) {
-      const int el = half * 32 + lane;
-      if (half == 1 && lane >= kAcc - 32) break;
-      const double v = half ? v1 : v0;
-      if (diag) {
-        if (el < 21) {
-          int c = 0;
-          while ((c + 1) * (c + 2) / 2 <= el) ++c;
-          const int r = el - c * (c + 1) / 2;
-          blk.p[(size_t)r * blk.rs + (size_t)c * blk.cs] += v;
-        } else if (el < 27) {
-          P.b_p[(size_t)w.row * P.D + (el - 21)] += v;
-        } else if (el < 33) {
-          P.rhs_sc[(size_t)w.row * P.D + (el - 27)] += v;
-        }
-      } else {
-        const int c = el / 6, r = el - c * 6;
+      const int e = half * 32 + lane;
+      if (half == 1 && lane >= 2 * kAccL - 32) break;
+      double v = half ? v1 : v0;
+      const int eh = e / kAccL, ek = e - eh * kAccL;
+      if (ek < 18) {
+        const int c = 3 * eh + ek / 6, r = ek % 6;
+        if (w.kind == kItemSym) v += stage[(r / 3) * kAccL + (r % 3) * 6 + c];   // element (c, r)
         if (w.kind == kItemOff || r <= c) blk.p[(size_t)r * blk.rs + (size_t)c * blk.cs] += v;
+      } else if (diag) {
+        double* dst = eh ? P.rhs_sc : P.b_p;
+        dst[(size_t)w.row * P.D + (ek - 18)] += v;
       }
     }
+    __syncwarp();
   }
 }
 
@@ -451,13 +527,20 @@ void launch_linearize(const DeviceProblem& P, int G, cudaStream_t st) {
 }
 
 void launch_reduce_blocks(const DeviceProblem& P, const ReduceItem* items, int n_items, const uint2* pairs, double* partial,
-                          unsigned int* counters, cudaStream_t st) {
+                          unsigned int* counters, unsigned int* next_item, cudaStream_t st) {
   if (n_items <= 0) return;
+  static bool attr_done = false;
+  if (!attr_done) {
+    cudaFuncSetAttribute(k_reduce_blocks<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)RedCfg<1>::smem);
+    cudaFuncSetAttribute(k_reduce_blocks<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)RedCfg<3>::smem);
+    attr_done = true;
+  }
   int grid = (n_items + kRedWarps - 1) / kRedWarps;
-  const int cap = sm_count_cached() * 8;
+  const int cap = sm_count_cached() * 4;
   if (grid > cap) grid = cap;
-  if (P.L == 1) k_reduce_blocks<1><<<grid, kRedWarps * 32, 0, st>>>(P, items, n_items, pairs, partial, counters);
-  else k_reduce_blocks<3><<<grid, kRedWarps * 32, 0, st>>>(P, items, n_items, pairs, partial, counters);
+  cudaMemsetAsync(next_item, 0, sizeof(unsigned int), st);
+  if (P.L == 1) k_reduce_blocks<1><<<grid, kRedWarps * 32, RedCfg<1>::smem, st>>>(P, items, n_items, pairs, partial, counters, next_item);
+  else k_reduce_blocks<3><<<grid, kRedWarps * 32, RedCfg<3>::smem, st>>>(P, items, n_items, pairs, partial, counters, next_item);
 }
 
 }  // namespace bagpu

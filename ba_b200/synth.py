@@ -360,6 +360,7 @@ def make(name, scale=1.0, **kw):
     if name == "c3":
         return make_c3(n_keyframes=max(40, int(500 * s)), n_landmarks=max(50, int(50000 * s)), **kw)
     if name == "c4":
+        kw.setdefault("anchor_every", 64)   # every 64th camera surveyed (fixed): see make_c4
         return make_c4(n_cams=max(20, int(10000 * s)), n_points=max(100, int(2000000 * s)), **kw)
     if name == "c5":
         return make_c5(n_poses=max(40, int(20000 * s)), **kw)

@@ -5,10 +5,7 @@ from ba_b200 import synth
 from ba_b200.capi import BundleAdjusterGPU
 name = sys.argv[1]; iters = int(sys.argv[2])
 for sc in [float(x) for x in sys.argv[3:]]:
-    if name == "c4a":   # C4 with every 64th camera held fixed
-        p = synth.make_c4(n_cams=max(20, int(10000 * sc)), n_points=max(100, int(2000000 * sc)), anchor_every=64)
-    else:
-        p = synth.make(name, sc)
+    p = synth.make(name, sc)
     s = BundleAdjusterGPU(p.lm_dim, p.pose_dim)
     o = s.default_options(); o.error_change_threshold = 0; o.param_change_threshold = 0
     if hasattr(p, "gravity"):
