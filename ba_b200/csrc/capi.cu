@@ -509,17 +509,22 @@ struct bagpu_handle_s {
       cut(chunks, pose_rec_start[p], pose_rec_start[p + 1], p, p, kItemDiagObs);
       if (L == 1) cut(chunks, pose_lmrec_start[p], pose_lmrec_start[p + 1], p, p, kItemDiagLm);
       push_block(items, chunks);
-      while (bi < bkey.size() && (int)(bkey[bi] / (unsigned long long)n_ap) == p) {
-        const uint32_t col = (uint32_t)(bkey[bi] % (unsigned long long)n_ap);
+      while (bi < bkey.size() && (int)((bkey[bi] >> 1) / (unsigned long long)n_ap) == p) {
+        // all runs of one block (entries between measurement poses, then measurement/reference entries) form one chunk chain
+        const unsigned long long blk = bkey[bi] >> 1;
+        const uint32_t col = (uint32_t)(blk % (unsigned long long)n_ap);
         const bool is_sym = (col == (uint32_t)p);
-        cut(chunks, pair_off, pair_off + bcnt[bi], p, col, is_sym ? kItemSym : kItemOff);
+        while (bi < bkey.size() && (bkey[bi] >> 1) == blk) {
+          const bool is_ref = (bkey[bi] & 1ull) != 0;
+          cut(chunks, pair_off, pair_off + bcnt[bi], p, col, is_ref ? kItemOffRef : (is_sym ? kItemSym : kItemOff));
+          pair_off += bcnt[bi]; ++bi;
+        }
         push_block(is_sym ? sym : items, chunks);
-        pair_off += bcnt[bi]; ++bi;
       }
     }
     n_items = (int)items.size(); n_items_sym = (int)sym.size();
     d_items.upload(items, st); d_items_sym.upload(sym, st);
-    d_partial.alloc((size_t)std::max<uint32_t>(1, n_partial) * 48); d_counters.alloc((size_t)n_groups + 2); d_counters.zero(st);   // [0] = item counter of the running launch
+    d_partial.alloc((size_t)std::max<uint32_t>(1, n_partial) * 64); d_counters.alloc((size_t)n_groups + 2); d_counters.zero(st);   // [0] = item counter of the running launch
     sync();   // the host vectors above go out of scope
   }
 

@@ -39,7 +39,7 @@ struct OtherResiduals {
 // one entry per observation for the (measurement pose, reference pose) block, tagged in b.
 constexpr uint32_t kPairTagMeasRow = 0xffffffffu;   // row pose = measurement pose: += At^T Q
 constexpr uint32_t kPairTagRefRow = 0xfffffffeu;    // row pose = reference pose:   += Q^T At
-enum { kItemDiagObs = 0, kItemDiagLm = 1, kItemOff = 2, kItemSym = 3 };
+enum { kItemDiagObs = 0, kItemDiagLm = 1, kItemOff = 2, kItemSym = 3, kItemOffRef = 4 };
 struct ReduceItem {        // one warp's share of one S block
   uint32_t begin, end;     // record-slot range (diagonal kinds) or pair range
   uint32_t row, col;       // pose opt ids, row <= col
@@ -50,7 +50,8 @@ struct ReduceItem {        // one warp's share of one S block
 };
 
 // Builds the pair list on the device (symbolic.cu): *pairs_out is cudaMalloc'ed (caller frees), sorted by
-// block key = row * n_active_poses + col, stable in landmark order; block_key / block_count = the block table.
+// key = (row * n_active_poses + col) * 2 + (1 for the LmSize-1 measurement/reference entries), stable in landmark
+// order; block_key / block_count = the run table of that key.
 int build_pair_lists(const DeviceProblem& P, cudaStream_t st, uint2** pairs_out, size_t* n_pairs_out,
                      std::vector<unsigned long long>& block_key, std::vector<uint32_t>& block_count, std::string& err);
 

@@ -225,7 +225,7 @@ __global__ void __launch_bounds__(128) k_linearize(DeviceProblem P) {
 // lane instead of 36+12: registers set the occupancy of this latency-bound gather).  The partial
 // sets are transposed through shared memory so that lane k owns element k of the block.
 constexpr int kAccL = 24;          // per lane: 6 rows x 3 columns, then 6 entries of b_p (even lane) or rhs_sc (odd lane)
-constexpr int kPartial = 48;       // doubles per partial-sum slot: two halves of kAccL
+constexpr int kPartial = 64;       // doubles per partial-sum slot (two halves of kAccL, padded)
 constexpr int kRedWarps = 4;
 constexpr int kPPB = 16;           // pairs (or records) per batch
 constexpr int kStages = 3;
@@ -337,33 +337,32 @@ BA_D void pair_product(const double* pa, const double* pb, uint32_t tag, int h, 
   }
 }
 
-// stage the parts of up to kPPB pairs (batch `bt` of the item) into buf, their tags behind the data
-template <int L>
+// stage the parts of up to kPPB list entries (batch `bt` of the item) into buf, their tags behind the data.
+//   entries between two measurement poses: two parts per entry (row-pose part, column-pose part) of
+//     18 doubles (LmSize 3: [C | At] and [At | Bt]) or 6 doubles (LmSize 1: E and W);
+//   LmSize 1 measurement/reference entries (kItemOffRef): one part of 24 doubles [At | Q].
+template <int L, int KIND> struct PartCfg {
+  static constexpr int PC = (KIND == kItemOffRef) ? 12 : (L == 3 ? 9 : 3);     // 16-byte chunks per part
+  static constexpr int NPART = (KIND == kItemOffRef) ? kPPB : 2 * kPPB;
+  static constexpr int PS = 2 * PC;                                            // doubles per part
+};
+template <int L, int KIND>
 BA_D void stage_pairs(const DeviceProblem& P, const uint2* __restrict__ pairs, uint32_t begin, uint32_t end, int bt, double* buf, int lane) {
-  constexpr int PS = RedCfg<L>::PS, PC = PS / 2;     // 16-byte chunks per part
+  typedef PartCfg<L, KIND> C;
   const uint32_t p = begin + (uint32_t)bt * kPPB + (lane & (kPPB - 1));
   const uint2 ab = (p < end) ? pairs[p] : make_uint2(kNoSlot, kNoSlot);
   if (lane < kPPB) reinterpret_cast<uint32_t*>(buf + RedCfg<L>::DATA)[lane] = (ab.x == kNoSlot) ? kNoSlot - 2 : ab.y;
 #pragma unroll
-  for (int k = 0; k < (2 * kPPB * PC) / 32; ++k) {
+  for (int k = 0; k < (C::NPART * C::PC + 31) / 32; ++k) {
     const int idx = k * 32 + lane;
-    const int part = idx / PC, chunk = idx - part * PC;
-    const int pl = part >> 1, side = part & 1;
+    const int part = idx / C::PC, chunk = idx - part * C::PC;
+    const int pl = ((KIND == kItemOffRef) ? part : (part >> 1)) & (kPPB - 1), side = (KIND == kItemOffRef) ? 0 : (part & 1);
     const uint32_t sa = __shfl_sync(0xffffffffu, ab.x, pl), sb = __shfl_sync(0xffffffffu, ab.y, pl);
-    if (sa == kNoSlot) continue;
+    if (sa == kNoSlot || idx >= C::NPART * C::PC) continue;
     const double* src;
-    int n;
-    if (L == 3) {
-      src = P.rec + (size_t)(side ? sb : sa) * kRec3 + (side ? 6 : 0);
-      n = PC;
-    } else if (sb < kPairTagRefRow) {
-      src = P.rec + (size_t)(side ? sb : sa) * kRec1 + (side ? 6 : 0);
-      n = 3;
-    } else {
-      src = P.rec + (size_t)sa * kRec1 + 12;
-      n = side ? 0 : 12;
-    }
-    if (chunk < n) cp_async16(buf + part * PS + chunk * 2, src + chunk * 2);
+    if (KIND == kItemOffRef) src = P.rec + (size_t)sa * kRec1 + 12;
+    else src = P.rec + (size_t)(side ? sb : sa) * (L == 3 ? kRec3 : kRec1) + (side ? 6 : 0);
+    cp_async16(buf + part * C::PS + chunk * 2, src + chunk * 2);
   }
 }
 
@@ -406,7 +405,8 @@ __global__ void __launch_bounds__(kRedWarps * 32, 4) k_reduce_blocks(DeviceProbl
       const int ld = bt + kStages - 1;
       if (ld < nb) {
         double* dst = stage + (ld % kStages) * Cfg::BUF;
-        if (!diag) stage_pairs<L>(P, pairs, w.begin, w.end, ld, dst, lane);
+        if (w.kind == kItemOffRef) { if (L == 1) stage_pairs<1, kItemOffRef>(P, pairs, w.begin, w.end, ld, dst, lane); }
+        else if (!diag) stage_pairs<L, kItemOff>(P, pairs, w.begin, w.end, ld, dst, lane);
         else if (obs) stage_records<Cfg::RS>(P.rec, w.begin + (uint32_t)ld * kPPB, w.end, dst, lane);
         else stage_records<kLmRec>(P.lm_rec, w.begin + (uint32_t)ld * kPPB, w.end, dst, lane);
       }
@@ -417,7 +417,10 @@ __global__ void __launch_bounds__(kRedWarps * 32, 4) k_reduce_blocks(DeviceProbl
       const double* cur = stage + (bt % kStages) * Cfg::BUF;
       if (!diag) {
         const uint32_t tag = reinterpret_cast<const uint32_t*>(cur + Cfg::DATA)[pl];
-        if (tag != kNoSlot - 2) pair_product<L>(cur + (2 * pl) * Cfg::PS, cur + (2 * pl + 1) * Cfg::PS, tag, h, acc);
+        if (tag != kNoSlot - 2) {
+          if (w.kind == kItemOffRef) pair_product<L>(cur + pl * 24, cur, tag, h, acc);
+          else pair_product<L>(cur + (2 * pl) * PartCfg<L, kItemOff>::PS, cur + (2 * pl + 1) * PartCfg<L, kItemOff>::PS, tag, h, acc);
+        }
       } else if (w.begin + (uint32_t)bt * kPPB + pl < w.end) {
         if (obs) {
           diag_record<L>(cur + pl * Cfg::RS, h, acc);
@@ -488,7 +491,7 @@ __global__ void __launch_bounds__(kRedWarps * 32, 4) k_reduce_blocks(DeviceProbl
       if (ek < 18) {
         const int c = 3 * eh + ek / 6, r = ek % 6;
         if (w.kind == kItemSym) v += stage[(r / 3) * kAccL + (r % 3) * 6 + c];   // element (c, r)
-        if (w.kind == kItemOff || r <= c) blk.p[(size_t)r * blk.rs + (size_t)c * blk.cs] += v;
+        if (w.kind == kItemOff || w.kind == kItemOffRef || r <= c) blk.p[(size_t)r * blk.rs + (size_t)c * blk.cs] += v;
       } else if (diag) {
         double* dst = eh ? P.rhs_sc : P.b_p;
         dst[(size_t)w.row * P.D + (ek - 18)] += v;

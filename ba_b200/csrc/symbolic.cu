@@ -46,7 +46,7 @@ __global__ void k_pair_emit(DeviceProblem P, const unsigned long long* __restric
     if (ref_opt >= 0) {   // (measurement pose, reference pose) block of this observation
       const unsigned long long pr = (unsigned long long)ref_opt;
       const bool meas_row = pa < pr;
-      keys[o] = meas_row ? pa * np + pr : pr * np + pa;
+      keys[o] = ((meas_row ? pa * np + pr : pr * np + pa) << 1) | 1ull;
       vals[o] = ((unsigned long long)(meas_row ? kPairTagMeasRow : kPairTagRefRow) << 32) | sa;
       ++o;
     }
@@ -55,8 +55,8 @@ __global__ void k_pair_emit(DeviceProblem P, const unsigned long long* __restric
       const uint32_t sb = P.obs_slot[j];
       if (sb == kNoSlot) continue;
       const unsigned long long pb = (unsigned long long)P.pose_opt[P.obs_pose[j]];
-      if (pa <= pb) { keys[o] = pa * np + pb; vals[o] = ((unsigned long long)sb << 32) | sa; }
-      else { keys[o] = pb * np + pa; vals[o] = ((unsigned long long)sa << 32) | sb; }
+      if (pa <= pb) { keys[o] = (pa * np + pb) << 1; vals[o] = ((unsigned long long)sb << 32) | sa; }
+      else { keys[o] = (pb * np + pa) << 1; vals[o] = ((unsigned long long)sa << 32) | sb; }
       ++o;
     }
   }
@@ -99,7 +99,7 @@ int build_pair_lists(const DeviceProblem& P, cudaStream_t st, uint2** pairs_out,
   SYM_CU(cudaMalloc(&d_keys2, sizeof(u64) * total));
   SYM_CU(cudaMalloc(&d_vals2, sizeof(u64) * total));
   k_pair_emit<<<(n + 255) / 256, 256, 0, st>>>(P, d_offs, d_keys, d_vals);
-  while ((1ull << bits) < (u64)P.n_active_poses * (u64)P.n_active_poses && bits < 64) ++bits;
+  while ((1ull << bits) < 2ull * (u64)P.n_active_poses * (u64)P.n_active_poses && bits < 64) ++bits;
   SYM_CU(cub::DeviceRadixSort::SortPairs(nullptr, tb, d_keys, d_keys2, d_vals, d_vals2, (u64)total, 0, bits, st));
   if (tb > tmp_bytes) { cudaFree(d_tmp); d_tmp = nullptr; SYM_CU(cudaMalloc(&d_tmp, tb)); tmp_bytes = tb; }
   SYM_CU(cub::DeviceRadixSort::SortPairs(d_tmp, tb, d_keys, d_keys2, d_vals, d_vals2, (u64)total, 0, bits, st));
