@@ -18,7 +18,7 @@ EXPORTS = [
     "set_landmarks", "set_proj_residuals", "set_unary_residuals", "set_binary_residuals",
     "set_imu_residuals", "solve", "build", "get_poses", "get_landmarks", "get_proj_residuals",
     "get_trace", "get_deltas", "get_pattern", "get_system", "dump", "nccl_unique_id", "comm_init",
-    "get_phase_ms", "sync_state",
+    "get_phase_ms", "sync_state", "host_alloc", "host_free",
 ]
 
 
@@ -60,3 +60,41 @@ class BundleAdjusterGPU(Binding):
             f.restype = C.c_char_p
             raise RuntimeError("bagpu_nccl_unique_id: %s" % f().decode())
         return bytes(buf)
+
+
+class _PinnedBlock:
+    """One page-locked host allocation (bagpu_host_alloc); freed when the last numpy view goes away."""
+
+    def __init__(self, nbytes):
+        self.p = C.c_void_p()
+        rc = lib().bagpu_host_alloc(C.c_size_t(max(1, nbytes)), C.byref(self.p))
+        if rc != 0 or not self.p:
+            raise MemoryError("bagpu_host_alloc(%d) failed" % nbytes)
+        self.nbytes = nbytes
+
+    def __del__(self):
+        try:
+            lib().bagpu_host_free(self.p)
+        except Exception:
+            pass
+
+
+def pinned_like(a):
+    """Copy of the numpy array `a` in page-locked host memory (the host buffers of an end-to-end Solve()).
+    The block lives until release_pinned()."""
+    import numpy as np
+    a = np.ascontiguousarray(a)
+    blk = _PinnedBlock(a.nbytes)
+    buf = (C.c_char * max(1, a.nbytes)).from_address(blk.p.value)
+    out = np.frombuffer(buf, dtype=a.dtype, count=a.size).reshape(a.shape)
+    out[...] = a
+    _PINNED_KEEP.append(blk)
+    return out
+
+
+def release_pinned():
+    """Free every block handed out by pinned_like (the arrays must not be used afterwards)."""
+    del _PINNED_KEEP[:]
+
+
+_PINNED_KEEP = []

@@ -9,10 +9,14 @@
 // chol.cu; there is no CPU fallback: without a CUDA device every entry point that would
 // compute returns BAGPU_ERR_NO_DEVICE.
 #include <algorithm>
+#include <chrono>
+#include <cstdlib>
 #include <cmath>
 #include <cstdio>
 #include <cstring>
+#include <mutex>
 #include <string>
+#include <unordered_set>
 #include <vector>
 #include <dlfcn.h>
 #include "ba_gpu.h"
@@ -24,6 +28,19 @@ using namespace bagpu;
 namespace {
 
 thread_local std::string g_err;
+std::mutex g_pinned_mu;
+std::unordered_set<void*> g_pinned;   // buffers handed out by bagpu_host_alloc that are page-locked
+// BAGPU_TIMING=1: wall-clock of the set-up phases on stderr (development aid)
+struct PhaseClock {
+  bool on; std::chrono::steady_clock::time_point t;
+  PhaseClock() : on(getenv("BAGPU_TIMING") != nullptr), t(std::chrono::steady_clock::now()) {}
+  void lap(const char* what) {
+    if (!on) return;
+    const auto n = std::chrono::steady_clock::now();
+    fprintf(stderr, "[bagpu timing] %-28s %8.2f ms\n", what, std::chrono::duration<double, std::milli>(n - t).count());
+    t = n;
+  }
+};
 int fail(int code, const std::string& msg) { g_err = msg; return code; }
 
 #define CU(x)                                                                                        \
@@ -121,8 +138,13 @@ struct bagpu_handle_s {
   std::vector<int> pose_opt, lm_opt;
   std::vector<uint8_t> pose_has_res;     // any residual in the pose's lists
   std::vector<uint8_t> pose_has_imu;
-  std::vector<uint32_t> lm_obs_start, obs_perm;
-  std::vector<uint32_t> obs_slot, pose_rec_start, lm_rslot, pose_lmrec_start;   // pose-major record slots (ba_gpu.h)
+  std::vector<uint32_t> lm_obs_start, obs_perm;   // host landmark-major order (pattern queries only, host_order())
+  bool host_order_valid = false;
+  size_t n_raw = 0;                 // projection residuals handed to set_proj_residuals
+  bool raw_on_device = false, raw_has_cam = false, raw_has_w0 = false, ids_on_host = true;
+  uint32_t s_lo = 0, s_hi = 0;      // this rank's slice of the landmark-major stream
+  unsigned int n_cond_proj = 0;
+  std::vector<uint32_t> pose_rec_start, pose_lmrec_start;   // pose-major record slots (ba_gpu.h)
   uint32_t n_rec = 0, n_lmrec = 0;
   int n_items = 0, n_items_sym = 0;
   size_t n_pairs = 0;
@@ -140,7 +162,9 @@ struct bagpu_handle_s {
   DevBuf<int> d_pose_opt, d_lm_opt; DevBuf<uint32_t> d_pose_free; DevBuf<uint8_t> d_pose_mask_used;
   DevBuf<double> d_lm_x, d_lm_xw; DevBuf<uint32_t> d_lm_ref_pose, d_lm_ref_cam, d_lm_outliers, d_lm_obs_start;
   DevBuf<uint8_t> d_lm_reliable;
-  DevBuf<double2> d_obs_z; DevBuf<uint32_t> d_obs_pose, d_obs_cam, d_obs_perm; DevBuf<double> d_obs_w0, d_obs_maha0, d_obs_w;
+  DevBuf<double2> d_raw_z; DevBuf<uint32_t> d_raw_pose, d_raw_lm, d_raw_cam; DevBuf<double> d_raw_w0;   // residual-id order, as set
+  DevBuf<uint32_t> d_sorted_lm, d_perm_global, d_gstarts;   // landmark-major: landmark id, residual id, CSR starts (all ranks' observations)
+  DevBuf<double2> d_obs_z; DevBuf<uint32_t> d_obs_pose, d_obs_cam; DevBuf<double> d_obs_w0, d_obs_maha0, d_obs_w;
   DevBuf<uint32_t> d_obs_slot, d_lm_rslot; DevBuf<double> d_rec, d_lm_rec, d_partial; DevBuf<unsigned int> d_counters;
   DevBuf<ReduceItem> d_items, d_items_sym;
   DevBuf<double> d_lm_Vinv, d_lm_bl, d_lm_dhat, d_lm_Wref;
@@ -193,71 +217,153 @@ struct bagpu_handle_s {
     has_device = true;
   }
 
-  // ---- symbolic set-up: ids, landmark-major observation order, tile pattern of S ----------
+  // ---- set-up, host part: opt ids and the membership flags of the few unary / binary / inertial residuals ----
   void setup() {
     n_cams = (int)cam_params.size() / 4;
     n_poses = (int)pose_t7.size() / 7;
     n_lms = (int)lm_xw.size() / 4;
-    n_obs = (int)proj_pose.size();
+    n_obs = n_obs_total = (int)n_raw;
     if (n_cams == 0) { n_cams = 1; cam_params = {1, 1, 0, 0}; cam_tvs = {0, 0, 0, 1, 0, 0, 0}; }
     pose_opt.assign(n_poses, -1); n_ap = 0;
     for (int i = 0; i < n_poses; ++i) if (pose_active[i]) pose_opt[i] = n_ap++;
     lm_opt.assign(n_lms, -1); n_al = 0;
     for (int i = 0; i < n_lms; ++i) if (lm_active[i]) lm_opt[i] = n_al++;
-    // residual membership per pose (reference BundleAdjuster.h:490-497, :405, :452-453, :537-538)
+    // residual membership per pose (reference BundleAdjuster.h:490-497, :405, :452-453, :537-538); the projection
+    // residuals add theirs on the device (device_symbolic) or in host_order()
     pose_has_res.assign(n_poses, 0); pose_has_imu.assign(n_poses, 0);
-    for (int i = 0; i < n_obs; ++i) {
-      const uint32_t m = proj_pose[i], r = lm_ref_pose[proj_lm[i]];
-      const bool diff = m != r;
-      if (diff || L != 1) { pose_has_res[m] = 1; if (L == 1) pose_has_res[r] = 1; }
-    }
     for (uint32_t p : un_pose) pose_has_res[p] = 1;
     for (size_t i = 0; i < bin_p1.size(); ++i) { pose_has_res[bin_p1[i]] = 1; pose_has_res[bin_p2[i]] = 1; }
     for (size_t i = 0; i < imu_p1.size(); ++i) { pose_has_res[imu_p1[i]] = 1; pose_has_res[imu_p2[i]] = 1; pose_has_imu[imu_p1[i]] = 1; pose_has_imu[imu_p2[i]] = 1; }
-    // observations sorted by landmark (stable counting sort keeps residual ids ascending)
-    lm_obs_start.assign(n_lms + 1, 0);
-    for (int i = 0; i < n_obs; ++i) lm_obs_start[proj_lm[i] + 1]++;
-    for (int l = 0; l < n_lms; ++l) lm_obs_start[l + 1] += lm_obs_start[l];
-    obs_perm.resize(n_obs);
-    {
-      std::vector<uint32_t> cur(lm_obs_start.begin(), lm_obs_start.end() - 1);
-      for (int i = 0; i < n_obs; ++i) obs_perm[cur[proj_lm[i]]++] = i;
-    }
-    n_obs_total = n_obs;
-    int lms_with_obs = 0;
-    for (int l = 0; l < n_lms; ++l) lms_with_obs += lm_obs_start[l + 1] > lm_obs_start[l];
-    const double mean_track = lms_with_obs ? (double)n_obs / lms_with_obs : 0.0;
-    G = mean_track <= 4 ? 4 : mean_track <= 8 ? 8 : mean_track <= 16 ? 16 : 32;
-
-    // ---- tile pattern of S (upper), symbolic fill ----
     T = kTilePoses * D;
     nT = (n_ap + kTilePoses - 1) / kTilePoses;
-    std::vector<std::vector<uint8_t>> present(nT, std::vector<uint8_t>(nT, 0));
-    for (int k = 0; k < nT; ++k) present[k][k] = 1;
-    {
-      std::vector<int> tl;
-      for (int l = 0; l < n_lms; ++l) {
-        if (lm_opt[l] < 0 && L != 1) {}
-        tl.clear();
-        const int rp = (int)lm_ref_pose[l];
-        for (uint32_t e = lm_obs_start[l]; e < lm_obs_start[l + 1]; ++e) {
-          const int m = (int)proj_pose[obs_perm[e]];
-          if (m != rp && pose_opt[m] >= 0) tl.push_back(pose_opt[m] / kTilePoses);
-        }
-        if (L == 1 && pose_opt[rp] >= 0 && !tl.empty()) tl.push_back(pose_opt[rp] / kTilePoses);
-        std::sort(tl.begin(), tl.end());
-        tl.erase(std::unique(tl.begin(), tl.end()), tl.end());
-        for (size_t a = 0; a < tl.size(); ++a) for (size_t b = a; b < tl.size(); ++b) present[tl[a]][tl[b]] = 1;
-      }
-      auto mark = [&](uint32_t p1, uint32_t p2) {
-        const int o1 = pose_opt[p1], o2 = pose_opt[p2];
-        if (o1 < 0 || o2 < 0) return;
-        const int a = std::min(o1, o2) / kTilePoses, b = std::max(o1, o2) / kTilePoses;
-        present[a][b] = 1;
-      };
-      for (size_t i = 0; i < bin_p1.size(); ++i) mark(bin_p1[i], bin_p2[i]);
-      for (size_t i = 0; i < imu_p1.size(); ++i) mark(imu_p1[i], imu_p2[i]);
+    host_order_valid = false;
+  }
+
+  // landmark-major order of the residual ids on the host: only the pattern queries (bagpu_get_pattern) walk it;
+  // the solver derives the same order on the device
+  void host_ids() {
+    if (ids_on_host) return;
+    proj_pose.resize(n_raw); proj_lm.resize(n_raw);
+    d_raw_pose.download(proj_pose.data(), n_raw, st); d_raw_lm.download(proj_lm.data(), n_raw, st);
+    if (raw_has_cam) { proj_cam.resize(n_raw); d_raw_cam.download(proj_cam.data(), n_raw, st); }
+    sync();
+    ids_on_host = true;
+  }
+  void host_order() {
+    host_ids();
+    if (host_order_valid) return;
+    const int n = (int)proj_pose.size();
+    lm_obs_start.assign(n_lms + 1, 0);
+    for (int i = 0; i < n; ++i) lm_obs_start[proj_lm[i] + 1]++;
+    for (int l = 0; l < n_lms; ++l) lm_obs_start[l + 1] += lm_obs_start[l];
+    obs_perm.resize(n);
+    std::vector<uint32_t> cur(lm_obs_start.begin(), lm_obs_start.end() - 1);
+    for (int i = 0; i < n; ++i) obs_perm[cur[proj_lm[i]]++] = i;
+    host_order_valid = true;
+  }
+
+  // ---- set-up, device part (setup_device.cu): landmark-major observation stream, record slots, tile pattern ----
+  void device_symbolic(std::vector<uint8_t>& present) {
+    PhaseClock pc;
+    std::string err;
+    const uint32_t n = (uint32_t)n_obs_total;
+    present.assign((size_t)nT * nT, 0);
+    for (int k = 0; k < nT; ++k) present[(size_t)k * nT + k] = 1;
+    pose_rec_start.assign(n_ap + 1, 0); pose_lmrec_start.assign(n_ap + 1, 0);
+    n_rec = 0; n_lmrec = 0; n_cond_proj = 0; s_lo = 0; s_hi = n;
+    lm_owner_lo = 0; lm_owner_hi = n_lms;
+    G = 4;
+    d_lm_obs_start.alloc((size_t)n_lms + 1); d_lm_obs_start.zero(st);
+    if (n == 0 || n_lms == 0) { n_obs = 0; d_obs_slot.alloc(1); return; }
+    if (!raw_on_device) {   // the setters ran before a device was usable: take the host copies
+      d_raw_pose.upload(proj_pose, st); d_raw_lm.upload(proj_lm, st);
+      if (raw_has_cam) d_raw_cam.upload(proj_cam, st);
+      d_raw_z.upload(reinterpret_cast<const double2*>(proj_z.data()), n, st);
+      if (raw_has_w0) d_raw_w0.upload(proj_w0, st);
+      raw_on_device = true;
     }
+    // 1. landmark-major order
+    d_sorted_lm.alloc(n); d_perm_global.alloc(n); d_gstarts.alloc((size_t)n_lms + 1);
+    if (sort_positions_by_key(d_raw_lm.p, d_sorted_lm.p, d_perm_global.p, n, (uint32_t)n_lms, st, err)) throw err;
+    launch_key_starts(d_sorted_lm.p, n, (uint32_t)n_lms, d_gstarts.p, st);
+    // 2. membership flags, conditioning count, tile pattern (global)
+    DevBuf<uint8_t> d_has, d_present; DevBuf<unsigned int> d_cnt;
+    d_has.upload(pose_has_res, st); d_cnt.alloc(1); d_cnt.zero(st);
+    launch_obs_flags(d_raw_pose.p, d_raw_lm.p, n, L, d_lm_ref_pose.p, d_pose_opt.p, d_has.p, d_cnt.p, st);
+    d_present.upload(present, st);
+    if (n_ap > 0) launch_tile_pattern(d_gstarts.p, d_perm_global.p, d_raw_pose.p, d_lm_ref_pose.p, d_pose_opt.p, (uint32_t)n_lms, L, nT, d_present.p, st);
+    std::vector<uint32_t> gstarts((size_t)n_lms + 1);
+    d_gstarts.download(gstarts.data(), gstarts.size(), st);
+    d_has.download(pose_has_res.data(), pose_has_res.size(), st);
+    d_present.download(present.data(), present.size(), st);
+    d_cnt.download(&n_cond_proj, 1, st);
+    sync();
+    pc.lap("  symbolic: sort + flags + pattern");
+    int lms_with_obs = 0;
+    for (int l = 0; l < n_lms; ++l) lms_with_obs += gstarts[l + 1] > gstarts[l];
+    const double mean_track = lms_with_obs ? (double)n / lms_with_obs : 0.0;
+    G = mean_track <= 4 ? 4 : mean_track <= 8 ? 8 : mean_track <= 16 ? 16 : 32;
+    // 3. landmark sharding: contiguous landmark ranges balanced by observation count; in the
+    // landmark-major stream a shard is one contiguous slice
+    if (world > 1) {
+      const double per = (double)n / world;
+      int lo = 0, hi = n_lms;
+      for (int l = 0; l <= n_lms; ++l) {
+        if ((double)gstarts[l] <= per * rank) lo = l;
+        if ((double)gstarts[l] <= per * (rank + 1)) hi = l;
+      }
+      if (rank == world - 1) hi = n_lms;
+      if (rank == 0) lo = 0;
+      lm_owner_lo = lo; lm_owner_hi = hi;
+      s_lo = gstarts[lo]; s_hi = gstarts[hi];
+    }
+    n_obs = (int)(s_hi - s_lo);
+    launch_local_starts(d_gstarts.p, (uint32_t)n_lms, s_lo, s_hi, d_lm_obs_start.p, st);
+    // 4. the local stream: gathered values, pose-major record slots
+    const uint32_t nl = (uint32_t)n_obs;
+    d_obs_z.alloc(nl); d_obs_pose.alloc(nl); d_obs_w0.alloc(nl); d_obs_slot.alloc(nl);
+    if (n_cams > 1) d_obs_cam.alloc(nl);
+    launch_gather_obs(d_perm_global.p + s_lo, nl, d_raw_z.p, d_raw_pose.p, raw_has_cam ? d_raw_cam.p : nullptr, raw_has_w0 ? d_raw_w0.p : nullptr,
+                      d_obs_z.p, d_obs_pose.p, n_cams > 1 ? d_obs_cam.p : nullptr, d_obs_w0.p, nullptr, st);
+    if (nl) {
+      DevBuf<uint32_t> d_keys, d_keys_s, d_vals_s, d_starts; DevBuf<uint8_t> d_any;
+      d_keys.alloc(std::max<uint32_t>(nl, (uint32_t)n_lms)); d_keys_s.alloc(std::max<uint32_t>(nl, (uint32_t)n_lms));
+      d_vals_s.alloc(std::max<uint32_t>(nl, (uint32_t)n_lms)); d_starts.alloc((size_t)n_ap + 1);
+      d_any.alloc((size_t)n_lms); d_any.zero(st);
+      launch_slot_keys(d_obs_pose.p, d_sorted_lm.p + s_lo, nl, d_lm_ref_pose.p, d_pose_opt.p, (uint32_t)n_ap, d_keys.p, d_any.p, st);
+      if (sort_positions_by_key(d_keys.p, d_keys_s.p, d_vals_s.p, nl, (uint32_t)n_ap, st, err)) throw err;
+      launch_assign_slots(d_keys_s.p, d_vals_s.p, nl, (uint32_t)n_ap, d_obs_slot.p, st);
+      launch_key_starts(d_keys_s.p, nl, (uint32_t)n_ap, d_starts.p, st);
+      d_starts.download(pose_rec_start.data(), (size_t)n_ap + 1, st);
+      sync();
+      n_rec = pose_rec_start[n_ap];
+      if (L == 1) {   // reference-pose record slots of the landmarks
+        d_lm_rslot.alloc((size_t)n_lms);
+        launch_rslot_keys(d_any.p, d_lm_ref_pose.p, d_pose_opt.p, (uint32_t)n_lms, (uint32_t)n_ap, d_keys.p, st);
+        if (sort_positions_by_key(d_keys.p, d_keys_s.p, d_vals_s.p, (uint32_t)n_lms, (uint32_t)n_ap, st, err)) throw err;
+        launch_assign_slots(d_keys_s.p, d_vals_s.p, (uint32_t)n_lms, (uint32_t)n_ap, d_lm_rslot.p, st);
+        launch_key_starts(d_keys_s.p, (uint32_t)n_lms, (uint32_t)n_ap, d_starts.p, st);
+        d_starts.download(pose_lmrec_start.data(), (size_t)n_ap + 1, st);
+        sync();
+        n_lmrec = pose_lmrec_start[n_ap];
+      }
+    }
+    pc.lap("  symbolic: shard + gather + slots");
+  }
+
+  // ---- tile structure of S: binary / inertial couplings, elimination order, symbolic fill, tile table ----
+  void tile_structure(std::vector<uint8_t>& flat) {
+    std::vector<std::vector<uint8_t>> present(nT, std::vector<uint8_t>(nT, 0));
+    for (int a = 0; a < nT; ++a) for (int b = a; b < nT; ++b) present[a][b] = flat[(size_t)a * nT + b];
+    for (int k = 0; k < nT; ++k) present[k][k] = 1;
+    auto mark = [&](uint32_t p1, uint32_t p2) {
+      const int o1 = pose_opt[p1], o2 = pose_opt[p2];
+      if (o1 < 0 || o2 < 0) return;
+      const int a = std::min(o1, o2) / kTilePoses, b = std::max(o1, o2) / kTilePoses;
+      present[a][b] = 1;
+    };
+    for (size_t i = 0; i < bin_p1.size(); ++i) mark(bin_p1[i], bin_p2[i]);
+    for (size_t i = 0; i < imu_p1.size(); ++i) mark(imu_p1[i], imu_p2[i]);
     // ---- elimination order of the tiles: nested dissection (a banded S is a chain of nT dependent tile rows;
     // dissection turns it into a tree of depth ~log nT whose branches the dataflow solver runs concurrently) ----
     nested_dissection(present);
@@ -273,57 +379,6 @@ struct bagpu_handle_s {
       std::vector<int> cols;
       for (int j = k + 1; j < nT; ++j) if (present[k][j]) cols.push_back(j);
       for (size_t a = 0; a < cols.size(); ++a) for (size_t b = a; b < cols.size(); ++b) present[cols[a]][cols[b]] = 1;
-    }
-    // ---- landmark sharding: contiguous landmark ranges balanced by observation
-    // count; the tile pattern above is global so the value arrays line up across ranks ----
-    lm_owner_lo = 0; lm_owner_hi = n_lms;
-    if (world > 1) {
-      const double per = (double)n_obs_total / world;
-      int lo = 0, hi = n_lms;
-      for (int l = 0; l <= n_lms; ++l) {
-        if ((double)lm_obs_start[l] <= per * rank) lo = l;
-        if ((double)lm_obs_start[l] <= per * (rank + 1)) hi = l;
-      }
-      if (rank == world - 1) hi = n_lms;
-      if (rank == 0) lo = 0;
-      lm_owner_lo = lo; lm_owner_hi = hi;
-      std::vector<uint32_t> ns(n_lms + 1, 0), np;
-      for (int l = lo; l < hi; ++l) for (uint32_t e = lm_obs_start[l]; e < lm_obs_start[l + 1]; ++e) np.push_back(obs_perm[e]);
-      uint32_t acc = 0;
-      for (int l = 0; l < n_lms; ++l) { ns[l] = acc; if (l >= lo && l < hi) acc += lm_obs_start[l + 1] - lm_obs_start[l]; }
-      ns[n_lms] = acc;
-      lm_obs_start.swap(ns); obs_perm.swap(np);
-      n_obs = (int)obs_perm.size();
-    }
-    // ---- pose-major record slots of the local observations (counting sort by pose opt id, stable in
-    // landmark order) and, for LmSize 1, reference-pose record slots of the landmarks ----
-    obs_slot.assign(n_obs, kNoSlot);
-    pose_rec_start.assign(n_ap + 1, 0);
-    lm_rslot.assign(L == 1 ? n_lms : 0, kNoSlot);
-    pose_lmrec_start.assign(n_ap + 1, 0);
-    {
-      std::vector<uint8_t> lm_any(L == 1 ? n_lms : 0, 0);
-      for (int l = 0; l < n_lms; ++l) {
-        const uint32_t rp = lm_ref_pose[l];
-        for (uint32_t e = lm_obs_start[l]; e < lm_obs_start[l + 1]; ++e) {
-          const uint32_t m = proj_pose[obs_perm[e]];
-          if (m == rp) continue;
-          if (L == 1) lm_any[l] = 1;
-          if (pose_opt[m] >= 0) pose_rec_start[pose_opt[m] + 1]++;
-        }
-        if (L == 1 && lm_any[l] && pose_opt[rp] >= 0) pose_lmrec_start[pose_opt[rp] + 1]++;
-      }
-      for (int p = 0; p < n_ap; ++p) { pose_rec_start[p + 1] += pose_rec_start[p]; pose_lmrec_start[p + 1] += pose_lmrec_start[p]; }
-      n_rec = pose_rec_start[n_ap]; n_lmrec = pose_lmrec_start[n_ap];
-      std::vector<uint32_t> cur(pose_rec_start.begin(), pose_rec_start.end() - 1), curl(pose_lmrec_start.begin(), pose_lmrec_start.end() - 1);
-      for (int l = 0; l < n_lms; ++l) {
-        const uint32_t rp = lm_ref_pose[l];
-        for (uint32_t e = lm_obs_start[l]; e < lm_obs_start[l + 1]; ++e) {
-          const uint32_t m = proj_pose[obs_perm[e]];
-          if (m != rp && pose_opt[m] >= 0) obs_slot[e] = cur[pose_opt[m]]++;
-        }
-        if (L == 1 && lm_any[l] && pose_opt[rp] >= 0) lm_rslot[l] = curl[pose_opt[rp]]++;
-      }
     }
     tile_map.assign((size_t)nT * nT, -1);
     row_ptr.assign(nT + 1, 0); row_col.clear();
@@ -382,6 +437,7 @@ struct bagpu_handle_s {
   }
 
   void upload_all() {
+    PhaseClock pc;
     // cameras
     std::vector<double> Rvs(9 * n_cams), tvs(3 * n_cams);
     for (int c = 0; c < n_cams; ++c) {
@@ -404,23 +460,26 @@ struct bagpu_handle_s {
     d_lm_ref_pose.upload(lm_ref_pose, st); d_lm_ref_cam.upload(lm_ref_cam, st); d_lm_opt.upload(lm_opt, st);
     d_lm_reliable.upload(lm_reliable, st); d_bk_rel.alloc(lm_reliable.size()); d_lm_outliers.alloc(n_lms);
     d_lm_outliers.zero(st);
-    d_lm_obs_start.upload(lm_obs_start, st);
-    // observations in landmark order
-    std::vector<double2> z(n_obs); std::vector<uint32_t> op(n_obs), oc(n_obs); std::vector<double> w0(n_obs);
-    bool multi_cam = n_cams > 1;
-    for (int i = 0; i < n_obs; ++i) {
-      const uint32_t r = obs_perm[i];
-      z[i] = make_double2(proj_z[2 * r], proj_z[2 * r + 1]); op[i] = proj_pose[r]; oc[i] = proj_cam[r]; w0[i] = proj_w0[r];
+    pc.lap("  upload: cameras, poses, landmarks");
+    // observations: landmark-major stream, record slots and the tile pattern, derived on the device
+    {
+      std::vector<uint8_t> present;
+      device_symbolic(present);
+      tile_structure(present);
+      pc.lap("  tile structure (host)");
     }
-    d_obs_z.upload(z, st); d_obs_pose.upload(op, st); d_obs_w0.upload(w0, st); d_obs_perm.upload(obs_perm, st);
-    if (multi_cam) d_obs_cam.upload(oc, st);
+    const bool multi_cam = n_cams > 1;
     d_obs_maha0.alloc(n_obs); d_obs_w.alloc(n_obs);
     const int Ls = std::max(1, L);
     const int rec_stride = (L == 1) ? kRec1 : kRec3;
-    d_obs_slot.upload(obs_slot, st); d_rec.alloc((size_t)n_rec * rec_stride);
-    if (L == 1) { d_lm_rslot.upload(lm_rslot, st); d_lm_rec.alloc((size_t)n_lmrec * kLmRec); }
+    d_rec.alloc((size_t)n_rec * rec_stride);
+    if (L == 1) {
+      d_lm_rslot.alloc((size_t)n_lms); d_lm_rec.alloc((size_t)n_lmrec * kLmRec);
+      if (n_obs == 0) CU(cudaMemsetAsync(d_lm_rslot.p, 0xff, sizeof(uint32_t) * (size_t)std::max(1, n_lms), st));
+    }
     d_lm_Vinv.alloc((size_t)n_lms * Ls * Ls); d_lm_bl.alloc((size_t)n_lms * Ls); d_lm_dhat.alloc((size_t)n_lms * Ls); d_lm_Wref.alloc((size_t)n_lms * 6);
     d_lm_bl.zero(st);
+    pc.lap("  upload: allocs");
     // reduced system
     const size_t tsz = (size_t)T * T;
     d_S.alloc((size_t)n_tiles * tsz); d_uinv.alloc((size_t)nT * tsz); d_scratch.alloc(3 * (size_t)nT * T + 2 * (size_t)n_tiles * T);
@@ -434,6 +493,7 @@ struct bagpu_handle_s {
       d_chol_tasks.upload(tasks, st); d_chol_terms.upload(terms, st); d_chol_sync.alloc(chol_sync_ints(n_tiles, nT));
       sync();
     }
+    pc.lap("  upload: S + chol plan");
     d_sc.alloc(1); d_sc.zero(st); d_sel.alloc(1);
     d_bl_compact.alloc((size_t)n_al * Ls); d_gn_p.alloc((size_t)nT * T); d_gn_l.alloc((size_t)n_al * Ls);
     d_dl_p.alloc((size_t)nT * T); d_dl_l.alloc((size_t)n_al * Ls); d_tmp_p.alloc((size_t)nT * T); d_tmp_l.alloc((size_t)n_al * Ls);
@@ -454,7 +514,7 @@ struct bagpu_handle_s {
     P.Tsw = d_Tsw.p; P.Tws = d_Tws.p; P.Rwp = d_Rwp.p;
     P.lm_x = d_lm_x.p; P.lm_ref_pose = d_lm_ref_pose.p; P.lm_ref_cam = d_lm_ref_cam.p; P.lm_opt = d_lm_opt.p; P.lm_reliable = d_lm_reliable.p;
     P.lm_outliers = d_lm_outliers.p; P.lm_obs_start = d_lm_obs_start.p;
-    P.obs_z = d_obs_z.p; P.obs_pose = d_obs_pose.p; P.obs_cam = multi_cam ? d_obs_cam.p : nullptr; P.obs_w0 = d_obs_w0.p; P.obs_perm = d_obs_perm.p;
+    P.obs_z = d_obs_z.p; P.obs_pose = d_obs_pose.p; P.obs_cam = multi_cam ? d_obs_cam.p : nullptr; P.obs_w0 = d_obs_w0.p; P.obs_perm = d_perm_global.p ? d_perm_global.p + s_lo : nullptr;
     P.obs_maha0 = d_obs_maha0.p; P.obs_w = d_obs_w.p;
     P.obs_slot = d_obs_slot.p; P.rec = d_rec.p; P.rec_stride = rec_stride;
     P.lm_rslot = (L == 1) ? d_lm_rslot.p : nullptr; P.lm_rec = (L == 1) ? d_lm_rec.p : nullptr;
@@ -469,7 +529,9 @@ struct bagpu_handle_s {
     R.imu_p1 = d_imu_p1.p; R.imu_p2 = d_imu_p2.p; R.imu_meas_start = d_imu_ms.p; R.imu_meas = d_imu_meas.p; R.imu_weight = d_imu_w.p;
     R.imu_cov_inv = d_imu_cov_inv.p; R.imu_J1 = d_imu_J1.p; R.imu_J2 = d_imu_J2.p; R.imu_res = d_imu_res.p;
     apply_options();
+    sync(); pc.lap("  upload: rest");
     build_reduce_items();
+    pc.lap("  build_reduce_items");
     dirty = false;
   }
 
@@ -906,8 +968,9 @@ struct bagpu_handle_s {
   }
 
   void prepare_solve() {
-    ensure_device();
-    if (dirty) { setup(); upload_all(); solved_once = false; }
+    PhaseClock pc;
+    ensure_device(); pc.lap("ensure_device");
+    if (dirty) { setup(); pc.lap("setup (host symbolic)"); upload_all(); sync(); pc.lap("upload_all"); solved_once = false; }
     else apply_options();
     // Solve() prologue (cpp:287-296)
     launch_pose_frames(P, st); ++launches;
@@ -945,7 +1008,8 @@ struct bagpu_handle_s {
     for (float& m : phase_ms) m = 0;
     launches = 0;
     summary.iterations = 0;
-    if (proj_pose.empty() && bin_p1.empty() && un_pose.empty() && imu_p1.empty()) return;
+    if (n_raw == 0 && bin_p1.empty() && un_pose.empty() && imu_p1.empty()) return;
+    PhaseClock pcs;
     prepare_solve();
     CU(cudaEventRecord(ev[14], st));
     for (uint32_t kk = 0; kk < max_iter; ++kk) {
@@ -977,45 +1041,96 @@ struct bagpu_handle_s {
     CU(cudaEventRecord(ev[15], st));
     sync();
     { float ms; cudaEventElapsedTime(&ms, ev[14], ev[15]); phase_ms[BAGPU_PH_TOTAL] = ms; }
+    pcs.lap("solve: prepare + iterations");
     if (!opt.keep_on_device) download_state();
+    pcs.lap("download_state");
     solved_once = true;
     // summary (cpp:680-704)
-    summary.num_proj_residuals = n_obs; summary.num_inertial_residuals = (uint32_t)imu_p1.size();
+    summary.num_proj_residuals = (uint32_t)n_obs_total; summary.num_inertial_residuals = (uint32_t)imu_p1.size();
     summary.proj_error = proj_error; summary.inertial_error = inertial_error; summary.unary_error = unary_error; summary.binary_error = binary_error;
     summary.trust_region_size = trust_region;
-    uint32_t ncp = 0;
-    for (int i = 0; i < n_obs; ++i) if (!pose_active[lm_ref_pose[proj_lm[i]]] && pose_active[proj_pose[i]]) ++ncp;
-    summary.num_cond_proj_residuals = ncp;
+    // conditioning residuals (cpp:682-703): counted at set-up, their maha / weight summed on the device
+    summary.num_cond_proj_residuals = n_cond_proj;
     uint32_t nci = 0;
     for (size_t i = 0; i < imu_p1.size(); ++i) if (!pose_active[imu_p1[i]] && pose_active[imu_p2[i]]) ++nci;
     summary.num_cond_inertial_residuals = nci;
     summary.cond_proj_error = 0; summary.cond_inertial_error = 0;
-    if (ncp) {
-      std::vector<double> r(2 * (size_t)n_obs), w(n_obs), m(n_obs);
-      export_residuals(r.data(), w.data(), m.data());
-      for (int i = 0; i < n_obs; ++i)
-        if (!pose_active[lm_ref_pose[proj_lm[i]]] && pose_active[proj_pose[i]]) summary.cond_proj_error += m[i] / w[i];
+    if (n_cond_proj) {
+      evaluate_by_id();
+      CU(cudaMemsetAsync(&d_sc.p->dot[4], 0, sizeof(double), st));
+      launch_cond_error(d_obs_pose.p, d_sorted_lm.p + s_lo, P.obs_perm, (uint32_t)n_obs, d_lm_ref_pose.p, d_pose_opt.p, d_maha_out.p, d_obs_w.p,
+                        &d_sc.p->dot[4], st); ++launches;
+      double v = 0;
+      CU(cudaMemcpyAsync(&v, &d_sc.p->dot[4], sizeof(double), cudaMemcpyDeviceToHost, st));
+      sync();
+      summary.cond_proj_error = shard_sum(v);
     }
+    pcs.lap("summary");
+  }
+
+  // residual and maha of every local observation, written at its residual id (d_res_out, d_maha_out)
+  void evaluate_by_id() {
+    const size_t nt = (size_t)n_obs_total;
+    d_res_out.alloc(2 * nt); d_maha_out.alloc(nt);
+    if (world > 1) { d_res_out.zero(st); d_maha_out.zero(st); }
+    CU(cudaMemsetAsync(&d_sc.p->dot[5], 0, sizeof(double), st));
+    launch_evaluate(P, G, &d_sc.p->dot[5], d_res_out.p, d_maha_out.p, st); ++launches;
   }
 
   void export_residuals(double* res2, double* weight, double* maha) {
-    if (n_obs == 0) return;
-    d_res_out.alloc(2 * (size_t)n_obs); d_maha_out.alloc(n_obs);
-    CU(cudaMemsetAsync(&d_sc.p->dot[5], 0, sizeof(double), st));
-    launch_evaluate(P, G, &d_sc.p->dot[5], d_res_out.p, d_maha_out.p, st); ++launches;
-    std::vector<double> wsorted(n_obs);
-    d_obs_w.download(wsorted.data(), n_obs, st);
-    if (res2) d_res_out.download(res2, 2 * (size_t)n_obs, st);
-    if (maha) d_maha_out.download(maha, n_obs, st);
+    if (n_obs_total == 0) return;
+    const size_t nt = (size_t)n_obs_total;
+    evaluate_by_id();
+    DevBuf<double> d_w_id;
+    if (weight) {
+      d_w_id.alloc(nt);
+      if (world > 1) d_w_id.zero(st);
+      launch_scatter_by_perm(P.obs_perm, d_obs_w.p, (uint32_t)n_obs, d_w_id.p, st); ++launches;
+      d_w_id.download(weight, nt, st);
+    }
+    if (res2) d_res_out.download(res2, 2 * nt, st);
+    if (maha) d_maha_out.download(maha, nt, st);
     sync();
-    if (weight) for (int i = 0; i < n_obs; ++i) weight[obs_perm[i]] = wsorted[i];
   }
 };
 
 // ============================================================================================
 extern "C" {
 
+#define GUARD(...)                                                                \
+  try { __VA_ARGS__ } catch (const std::string& e) {                              \
+    const bool nodev = e.find("no CUDA device") != std::string::npos;             \
+    return fail(nodev ? BAGPU_ERR_NO_DEVICE : BAGPU_ERR_CUDA, e);                 \
+  }
+
 const char* bagpu_last_error(void) { return g_err.c_str(); }
+
+// Page-locked host buffers for the arrays that cross the ABI (copies from / to them are direct DMA).  Without a
+// device the buffer is ordinary memory, so host code can use the same allocator everywhere.
+int bagpu_host_alloc(size_t bytes, void** out) {
+  if (!out) return fail(BAGPU_ERR_INVALID, "null out pointer");
+  *out = nullptr;
+  if (bytes == 0) bytes = 1;
+  int n = 0;
+  void* p = nullptr;
+  if (cudaGetDeviceCount(&n) == cudaSuccess && n > 0 && cudaHostAlloc(&p, bytes, cudaHostAllocDefault) == cudaSuccess) {
+    std::lock_guard<std::mutex> g(g_pinned_mu);
+    g_pinned.insert(p);
+  } else {
+    cudaGetLastError();
+    p = std::malloc(bytes);
+    if (!p) return fail(BAGPU_ERR_INVALID, "out of host memory");
+  }
+  *out = p;
+  return BAGPU_OK;
+}
+int bagpu_host_free(void* p) {
+  if (!p) return BAGPU_OK;
+  bool pinned = false;
+  { std::lock_guard<std::mutex> g(g_pinned_mu); pinned = g_pinned.erase(p) > 0; }
+  if (pinned) cudaFreeHost(p); else std::free(p);
+  return BAGPU_OK;
+}
 
 void bagpu_default_options(bagpu_options* o) {
   memset(o, 0, sizeof(*o));
@@ -1080,7 +1195,7 @@ int bagpu_set_poses(bagpu_handle h, uint32_t n, const double* t, const double* v
 int bagpu_set_landmarks(bagpu_handle h, uint32_t n, const double* x, const uint32_t* rp, const uint32_t* rc, const uint8_t* a) {
   const size_t np = h->pose_t7.size() / 7;
   for (uint32_t i = 0; i < n; ++i) if (rp[i] >= np) return fail(BAGPU_ERR_INVALID, "landmark ref_pose_id out of range");
-  h->lm_xw.assign(x, x + 4 * (size_t)n); h->lm_xs.assign(4 * (size_t)n, 0.0);
+  h->lm_xw.assign(x, x + 4 * (size_t)n); h->lm_xs.clear();   // x_s is filled by the first Solve()
   h->lm_ref_pose.assign(rp, rp + n);
   if (rc) h->lm_ref_cam.assign(rc, rc + n); else h->lm_ref_cam.assign(n, 0);
   if (a) h->lm_active.assign(a, a + n); else h->lm_active.assign(n, 1);
@@ -1091,15 +1206,45 @@ int bagpu_set_landmarks(bagpu_handle h, uint32_t n, const double* x, const uint3
 int bagpu_set_proj_residuals(bagpu_handle h, uint32_t n, const double* z, const uint32_t* mp, const uint32_t* lm, const uint32_t* cam,
                              const double* w) {
   const size_t np = h->pose_t7.size() / 7, nl = h->lm_xw.size() / 4;
-  for (uint32_t i = 0; i < n; ++i) {
-    if (mp[i] >= np || lm[i] >= nl) return fail(BAGPU_ERR_INVALID, "projection residual id out of range");
-    const uint32_t c = cam ? cam[i] : 0;
-    if (h->L == 1 && mp[i] == h->lm_ref_pose[lm[i]] && c == h->lm_ref_cam[lm[i]])
-      return fail(BAGPU_ERR_INVALID, "residual of a landmark in its own reference frame (AddProjectionResidual returns -1 for it)");
+  bool dev = true;
+  try { h->ensure_device(); } catch (const std::string&) { dev = false; }
+  h->raw_on_device = false; h->raw_has_cam = cam != nullptr; h->raw_has_w0 = w != nullptr; h->n_raw = n;
+  if (dev && n > 0) {
+    // the observations go straight into HBM (the copies below are staged by the driver: the caller's buffers are
+    // free again on return); ids are checked there
+    GUARD(
+      h->d_raw_z.upload(reinterpret_cast<const double2*>(z), n, h->st); h->d_raw_pose.upload(mp, n, h->st); h->d_raw_lm.upload(lm, n, h->st);
+      if (cam) h->d_raw_cam.upload(cam, n, h->st);
+      if (w) h->d_raw_w0.upload(w, n, h->st);
+      h->d_lm_ref_pose.upload(h->lm_ref_pose, h->st); h->d_lm_ref_cam.upload(h->lm_ref_cam, h->st);
+      DevBuf<int> flag; flag.alloc(2); flag.zero(h->st);
+      launch_validate_obs(h->d_raw_pose.p, h->d_raw_lm.p, cam ? h->d_raw_cam.p : nullptr, n, (uint32_t)np, (uint32_t)nl, h->L, h->d_lm_ref_pose.p,
+                          h->d_lm_ref_cam.p, flag.p, h->st);
+      int f[2] = {0, 0};
+      flag.download(f, 2, h->st); h->sync();
+      if (f[0]) { h->n_raw = 0; return fail(BAGPU_ERR_INVALID, "projection residual id out of range"); }
+      if (f[1]) { h->n_raw = 0; return fail(BAGPU_ERR_INVALID, "residual of a landmark in its own reference frame (AddProjectionResidual returns -1 for it)"); }
+      h->raw_on_device = true;
+    )
+  } else {
+    for (uint32_t i = 0; i < n; ++i) {
+      if (mp[i] >= np || lm[i] >= nl) return fail(BAGPU_ERR_INVALID, "projection residual id out of range");
+      const uint32_t c = cam ? cam[i] : 0;
+      if (h->L == 1 && mp[i] == h->lm_ref_pose[lm[i]] && c == h->lm_ref_cam[lm[i]])
+        return fail(BAGPU_ERR_INVALID, "residual of a landmark in its own reference frame (AddProjectionResidual returns -1 for it)");
+    }
+    h->proj_z.assign(z, z + 2 * (size_t)n);
+    if (w) h->proj_w0.assign(w, w + n); else h->proj_w0.clear();
   }
-  h->proj_z.assign(z, z + 2 * (size_t)n); h->proj_pose.assign(mp, mp + n); h->proj_lm.assign(lm, lm + n);
-  if (cam) h->proj_cam.assign(cam, cam + n); else h->proj_cam.assign(n, 0);
-  if (w) h->proj_w0.assign(w, w + n); else h->proj_w0.assign(n, 1.0);
+  // host copies of the ids: only the pattern queries (bagpu_get_pattern) walk them; with the observations in HBM
+  // they are fetched back on demand (host_ids())
+  h->ids_on_host = !h->raw_on_device;
+  if (h->ids_on_host) {
+    h->proj_pose.assign(mp, mp + n); h->proj_lm.assign(lm, lm + n);
+    if (cam) h->proj_cam.assign(cam, cam + n); else h->proj_cam.clear();
+  } else {
+    h->proj_pose.clear(); h->proj_lm.clear(); h->proj_cam.clear();
+  }
   h->dirty = true;
   return BAGPU_OK;
 }
@@ -1133,12 +1278,6 @@ int bagpu_set_imu_residuals(bagpu_handle h, uint32_t n, const uint32_t* p1, cons
   return BAGPU_OK;
 }
 
-#define GUARD(...)                                                                \
-  try { __VA_ARGS__ } catch (const std::string& e) {                              \
-    const bool nodev = e.find("no CUDA device") != std::string::npos;             \
-    return fail(nodev ? BAGPU_ERR_NO_DEVICE : BAGPU_ERR_CUDA, e);                 \
-  }
-
 int bagpu_solve(bagpu_handle h, uint32_t max_iter, double gn_damping, int allow, bagpu_summary* out) {
   if (!h) return fail(BAGPU_ERR_INVALID, "null handle");
   GUARD(h->solve(max_iter, gn_damping, allow != 0);)
@@ -1171,7 +1310,7 @@ int bagpu_get_poses(bagpu_handle h, double* t, double* v, double* b, uint8_t* mu
 int bagpu_get_landmarks(bagpu_handle h, double* xw, double* xs, uint8_t* rel, uint32_t* nout) {
   const size_t n = h->lm_xw.size() / 4;
   if (xw) memcpy(xw, h->lm_xw.data(), sizeof(double) * 4 * n);
-  if (xs) memcpy(xs, h->lm_xs.data(), sizeof(double) * 4 * n);
+  if (xs) { if (h->lm_xs.size() == 4 * n) memcpy(xs, h->lm_xs.data(), sizeof(double) * 4 * n); else memset(xs, 0, sizeof(double) * 4 * n); }
   if (rel) memcpy(rel, h->lm_reliable.data(), n);
   if (nout) memcpy(nout, h->lm_outliers.data(), sizeof(uint32_t) * n);
   return BAGPU_OK;
@@ -1198,6 +1337,7 @@ int bagpu_get_deltas(bagpu_handle h, uint32_t iter, double* dp, double* dl) {
 //   W  = jt_pr_j_l_ (P x N_l)   S = U  union  pattern of (W V^-1) W^T (upper)
 int bagpu_get_pattern(bagpu_handle h, int which, uint32_t* ncols, uint32_t* nnzb, uint32_t* colptr, uint32_t* rowidx) {
   if (h->dirty) { h->setup(); }
+  GUARD(h->host_order();)
   const int P = h->n_ap, NL = h->n_al, L = h->L;
   std::vector<std::vector<uint32_t>> cols;
   auto lm_poses = [&](int l, std::vector<uint32_t>& out) {   // pose rows of W column l (sorted unique)
@@ -1220,7 +1360,7 @@ int bagpu_get_pattern(bagpu_handle h, int which, uint32_t* ncols, uint32_t* nnzb
   } else if (which == BAGPU_PATTERN_U || which == BAGPU_PATTERN_S) {
     cols.assign(P, {});
     auto add = [&](int a, int b) { if (a < 0 || b < 0) return; cols[std::max(a, b)].push_back(std::min(a, b)); };
-    for (int i = 0; i < h->n_obs; ++i) {
+    for (size_t i = 0; i < h->proj_pose.size(); ++i) {
       const int m = (int)h->proj_pose[i], rp = (int)h->lm_ref_pose[h->proj_lm[i]];
       if (m != rp || L != 1) {
         add(h->pose_opt[m], h->pose_opt[m]);

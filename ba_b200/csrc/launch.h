@@ -55,6 +55,28 @@ struct ReduceItem {        // one warp's share of one S block
 int build_pair_lists(const DeviceProblem& P, cudaStream_t st, uint2** pairs_out, size_t* n_pairs_out,
                      std::vector<unsigned long long>& block_key, std::vector<uint32_t>& block_count, std::string& err);
 
+// ---- device-side symbolic set-up (setup_device.cu) ------------------------------------------------
+int sort_positions_by_key(const uint32_t* keys_in, uint32_t* keys_out, uint32_t* vals_out, uint32_t n, uint32_t max_key, cudaStream_t st,
+                          std::string& err);
+void launch_key_starts(const uint32_t* keys_sorted, uint32_t n, uint32_t n_keys, uint32_t* starts, cudaStream_t st);
+void launch_validate_obs(const uint32_t* pose, const uint32_t* lm, const uint32_t* cam, uint32_t n, uint32_t n_poses, uint32_t n_lms, int L,
+                         const uint32_t* lm_ref_pose, const uint32_t* lm_ref_cam, int* flag2, cudaStream_t st);
+void launch_obs_flags(const uint32_t* pose, const uint32_t* lm, uint32_t n, int L, const uint32_t* lm_ref_pose, const int* pose_opt,
+                      uint8_t* has_res, unsigned int* n_cond, cudaStream_t st);
+void launch_gather_obs(const uint32_t* perm, uint32_t n, const double2* z, const uint32_t* pose, const uint32_t* cam, const double* w0,
+                       double2* oz, uint32_t* opose, uint32_t* ocam, double* ow0, uint32_t* operm, cudaStream_t st);
+void launch_local_starts(const uint32_t* gstarts, uint32_t n_lms, uint32_t s_lo, uint32_t s_hi, uint32_t* out, cudaStream_t st);
+void launch_slot_keys(const uint32_t* obs_pose, const uint32_t* obs_lm, uint32_t n, const uint32_t* lm_ref_pose, const int* pose_opt,
+                      uint32_t n_ap, uint32_t* keys, uint8_t* lm_any, cudaStream_t st);
+void launch_assign_slots(const uint32_t* keys_sorted, const uint32_t* vals_sorted, uint32_t n, uint32_t n_ap, uint32_t* slot, cudaStream_t st);
+void launch_rslot_keys(const uint8_t* lm_any, const uint32_t* lm_ref_pose, const int* pose_opt, uint32_t n_lms, uint32_t n_ap, uint32_t* keys,
+                       cudaStream_t st);
+void launch_tile_pattern(const uint32_t* starts, const uint32_t* perm, const uint32_t* pose, const uint32_t* lm_ref_pose, const int* pose_opt,
+                         uint32_t n_lms, int L, int nT, uint8_t* present, cudaStream_t st);
+void launch_cond_error(const uint32_t* obs_pose, const uint32_t* obs_lm, const uint32_t* obs_perm, uint32_t n, const uint32_t* lm_ref_pose,
+                       const int* pose_opt, const double* maha_by_id, const double* w, double* out, cudaStream_t st);
+void launch_scatter_by_perm(const uint32_t* perm, const double* in, uint32_t n, double* out, cudaStream_t st);
+
 void set_sm_count(int n);
 void launch_pose_frames(const DeviceProblem& P, cudaStream_t st);
 void launch_prepare_xs(const DeviceProblem& P, const double* lm_xw, cudaStream_t st);

@@ -115,8 +115,10 @@ __global__ void __launch_bounds__(128) k_sd_denominator(DeviceProblem P) {
       }
       if (L == 1 && o.ref_on) {
         const double* bp = P.b_p + (size_t)c.ref_opt * P.D;
+        double Jr[12];
+        ref_jacobian<L>(c, o, Jr);
 #pragma unroll
-        for (int k = 0; k < 6; ++k) { v0 += o.Jr[k] * bp[k]; v1 += o.Jr[6 + k] * bp[k]; }
+        for (int k = 0; k < 6; ++k) { v0 += Jr[k] * bp[k]; v1 += Jr[6 + k] * bp[k]; }
       }
       acc += P.obs_w[i] * (v0 * v0 + v1 * v1);
     }

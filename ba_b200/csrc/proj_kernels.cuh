@@ -64,7 +64,7 @@ struct ObsJac {
   double r[2];
   double Jl[2 * L];   // row-major 2 x L
   double Jm[12];      // row-major 2 x 6 (measurement pose)
-  double Jr[12];      // row-major 2 x 6 (reference pose, LmSize 1)
+  double Bp[6];       // row-major 2 x 3: d project / d X_world = Jp R_sw (the reference-pose Jacobian is Bp [-rho I | Ar])
   int pm;             // opt id of the measurement pose if it takes part (active, diff_poses), else -1
   bool ref_on;        // reference pose takes part (LmSize 1, active, diff_poses)
 };
@@ -153,23 +153,28 @@ BA_D void obs_jacobians(const DeviceProblem& P, const LmCtx<L>& c, int obs, ObsJ
         if (!((fr >> k) & 1u)) { o.Jm[k] = 0.0; o.Jm[6 + k] = 0.0; }
     }
   }
-  if (L == 1 && o.ref_on) {
-    // d z / d x_ref = [ -rho B | B R_wp_r [Y]x ]
 #pragma unroll
-    for (int rr = 0; rr < 2; ++rr) {
-      const double* Br = B + 3 * rr;
-      o.Jr[6 * rr + 0] = -c.rho * Br[0];
-      o.Jr[6 * rr + 1] = -c.rho * Br[1];
-      o.Jr[6 * rr + 2] = -c.rho * Br[2];
-      o.Jr[6 * rr + 3] = Br[0] * c.Ar[0] + Br[1] * c.Ar[3] + Br[2] * c.Ar[6];
-      o.Jr[6 * rr + 4] = Br[0] * c.Ar[1] + Br[1] * c.Ar[4] + Br[2] * c.Ar[7];
-      o.Jr[6 * rr + 5] = Br[0] * c.Ar[2] + Br[1] * c.Ar[5] + Br[2] * c.Ar[8];
-    }
-    if ((c.ref_free & 63u) != 63u) {
+  for (int i = 0; i < 6; ++i) o.Bp[i] = B[i];
+}
+
+// reference-pose Jacobian of an observation (LmSize 1, o.ref_on): d z / d x_ref = Bp [ -rho I | R_wp_r [Y]x ], columns of
+// masked parameters zeroed
+template <int L>
+BA_D void ref_jacobian(const LmCtx<L>& c, const ObsJac<L>& o, double* Jr) {
 #pragma unroll
-      for (int k = 0; k < 6; ++k)
-        if (!((c.ref_free >> k) & 1u)) { o.Jr[k] = 0.0; o.Jr[6 + k] = 0.0; }
-    }
+  for (int rr = 0; rr < 2; ++rr) {
+    const double* Br = o.Bp + 3 * rr;
+    Jr[6 * rr + 0] = -c.rho * Br[0];
+    Jr[6 * rr + 1] = -c.rho * Br[1];
+    Jr[6 * rr + 2] = -c.rho * Br[2];
+    Jr[6 * rr + 3] = Br[0] * c.Ar[0] + Br[1] * c.Ar[3] + Br[2] * c.Ar[6];
+    Jr[6 * rr + 4] = Br[0] * c.Ar[1] + Br[1] * c.Ar[4] + Br[2] * c.Ar[7];
+    Jr[6 * rr + 5] = Br[0] * c.Ar[2] + Br[1] * c.Ar[5] + Br[2] * c.Ar[8];
+  }
+  if ((c.ref_free & 63u) != 63u) {
+#pragma unroll
+    for (int k = 0; k < 6; ++k)
+      if (!((c.ref_free >> k) & 1u)) { Jr[k] = 0.0; Jr[6 + k] = 0.0; }
   }
 }
 

@@ -33,7 +33,7 @@ BA_D void ld2(const double* p, double& a, double& b) { const double2 v = *reinte
 // ---------------------------------------------------------------------------------------
 // pass A
 template <int L, int G>
-__global__ void __launch_bounds__(128) k_linearize(DeviceProblem P) {
+__global__ void __launch_bounds__(128, (L == 1) ? 3 : 4) k_linearize(DeviceProblem P) {
   constexpr int NV = L * (L + 1) / 2;
   const int lane = threadIdx.x & 31, gl = lane % G;
   const unsigned gmask = group_mask<G>(lane);
@@ -51,21 +51,27 @@ __global__ void __launch_bounds__(128) k_linearize(DeviceProblem P) {
     for (int i = 0; i < NV; ++i) V[i] = 0.0;
 #pragma unroll
     for (int i = 0; i < L; ++i) bl[i] = 0.0;
-    double Hrr[L == 1 ? 21 : 1], gr[L == 1 ? 6 : 1], Wr[L == 1 ? 6 : 1];
+    // LmSize 1: the reference-pose Jacobian of every observation of the landmark is Bp M with the same 3 x 6
+    // M = [-rho I | Ar], so H_rr = M^T (sum w Bp^T Bp) M, g_r = M^T sum w Bp^T r, W_r = M^T sum w Bp^T J_l:
+    // 12 running sums instead of 33
+    double SBB[L == 1 ? 6 : 1], SBr[L == 1 ? 3 : 1], SBl[L == 1 ? 3 : 1], Wr[L == 1 ? 6 : 1];
     if (L == 1) {
 #pragma unroll
-      for (int i = 0; i < 21; ++i) Hrr[i] = 0.0;
+      for (int i = 0; i < 6; ++i) SBB[i] = 0.0;
 #pragma unroll
-      for (int i = 0; i < 6; ++i) { gr[i] = 0.0; Wr[i] = 0.0; }
+      for (int i = 0; i < 3; ++i) { SBr[i] = 0.0; SBl[i] = 0.0; }
     }
     // ---- sweep 1: weights and the landmark sums ---------------------------------------
+    ObsJac<L> o;              // the Jacobians of the lane's LAST observation stay in registers for sweep 2
+    double w_keep = 0.0;
+    int i_keep = -1;
     for (int i = s + gl; i < e; i += G) {
-      ObsJac<L> o;
       obs_jacobians<L>(P, c, i, o);
       const double w0 = P.obs_w0[i];
       const double n2 = o.r[0] * o.r[0] + o.r[1] * o.r[1];
       const double w = huber_weight(n2 * w0, w0, c_huber, P.use_robust);
       P.obs_w[i] = w;
+      w_keep = w; i_keep = i;
       err += n2 * w;
       if (lm_on) {
         const double wr0 = w * o.r[0], wr1 = w * o.r[1];
@@ -81,11 +87,11 @@ __global__ void __launch_bounds__(128) k_linearize(DeviceProblem P) {
         const double wr0 = w * o.r[0], wr1 = w * o.r[1];
         int k = 0;
 #pragma unroll
-        for (int b = 0; b < 6; ++b) {
+        for (int a = 0; a < 3; ++a) {
 #pragma unroll
-          for (int a = 0; a <= b; ++a) { Hrr[k] += w * (o.Jr[a] * o.Jr[b] + o.Jr[6 + a] * o.Jr[6 + b]); ++k; }
-          gr[b] += o.Jr[b] * wr0 + o.Jr[6 + b] * wr1;
-          if (lm_on) Wr[b] += w * (o.Jr[b] * o.Jl[0] + o.Jr[6 + b] * o.Jl[1]);
+          for (int b = a; b < 3; ++b) { SBB[k] += w * (o.Bp[a] * o.Bp[b] + o.Bp[3 + a] * o.Bp[3 + b]); ++k; }
+          SBr[a] += o.Bp[a] * wr0 + o.Bp[3 + a] * wr1;
+          if (lm_on) SBl[a] += w * (o.Bp[a] * o.Jl[0] + o.Bp[3 + a] * o.Jl[1]);
         }
       }
     }
@@ -128,16 +134,41 @@ __global__ void __launch_bounds__(128) k_linearize(DeviceProblem P) {
       const uint32_t rslot = P.lm_rslot[lm];
       if (rslot != kNoSlot) {
 #pragma unroll
-        for (int i = 0; i < 21; ++i) Hrr[i] = group_sum<G>(Hrr[i], gmask);
+        for (int i = 0; i < 6; ++i) SBB[i] = group_sum<G>(SBB[i], gmask);
 #pragma unroll
-        for (int i = 0; i < 6; ++i) { gr[i] = group_sum<G>(gr[i], gmask); Wr[i] = group_sum<G>(Wr[i], gmask); }
+        for (int i = 0; i < 3; ++i) { SBr[i] = group_sum<G>(SBr[i], gmask); SBl[i] = group_sum<G>(SBl[i], gmask); }
+        double M[18];   // 3 x 6 row-major, masked parameter columns zeroed
+#pragma unroll
+        for (int j = 0; j < 3; ++j)
+#pragma unroll
+          for (int k = 0; k < 3; ++k) { M[6 * j + k] = (j == k) ? -c.rho : 0.0; M[6 * j + 3 + k] = c.Ar[3 * j + k]; }
+        if ((c.ref_free & 63u) != 63u) {
+#pragma unroll
+          for (int k = 0; k < 6; ++k)
+            if (!((c.ref_free >> k) & 1u)) { M[k] = 0.0; M[6 + k] = 0.0; M[12 + k] = 0.0; }
+        }
+        const double S3[9] = {SBB[0], SBB[1], SBB[2], SBB[1], SBB[3], SBB[4], SBB[2], SBB[4], SBB[5]};
+        double TM[18];  // S3 M
+#pragma unroll
+        for (int j = 0; j < 3; ++j)
+#pragma unroll
+          for (int k = 0; k < 6; ++k) TM[6 * j + k] = S3[3 * j] * M[k] + S3[3 * j + 1] * M[6 + k] + S3[3 * j + 2] * M[12 + k];
+        double gr[6];
+#pragma unroll
+        for (int k = 0; k < 6; ++k) {
+          gr[k] = M[k] * SBr[0] + M[6 + k] * SBr[1] + M[12 + k] * SBr[2];
+          Wr[k] = M[k] * SBl[0] + M[6 + k] * SBl[1] + M[12 + k] * SBl[2];
+        }
         // reference-pose record: H_rr - W_r V^-1 W_r^T (upper) | g_r | g_r - W_r dhat, spread over the lanes
         double* o = P.lm_rec + (size_t)rslot * kLmRec;
         int k = 0;
 #pragma unroll
         for (int b = 0; b < 6; ++b)
 #pragma unroll
-          for (int a = 0; a <= b; ++a) { if ((k % G) == gl) o[k] = Hrr[k] - Vi[0] * Wr[a] * Wr[b]; ++k; }
+          for (int a = 0; a <= b; ++a) {
+            if ((k % G) == gl) o[k] = (M[a] * TM[b] + M[6 + a] * TM[6 + b] + M[12 + a] * TM[12 + b]) - Vi[0] * Wr[a] * Wr[b];
+            ++k;
+          }
 #pragma unroll
         for (int a = 0; a < 6; ++a)
           if (((21 + a) % G) == gl) { o[21 + a] = gr[a]; o[27 + a] = gr[a] - Wr[a] * dhat[0]; }
@@ -156,13 +187,13 @@ __global__ void __launch_bounds__(128) k_linearize(DeviceProblem P) {
 #pragma unroll
       for (int i = 0; i < L; ++i) { P.lm_bl[(size_t)lm * L + i] = bl[i]; P.lm_dhat[(size_t)lm * L + i] = dhat[i]; }
     }
-    // ---- sweep 2: one pose-major record per observation --------------------------------
-    for (int i = s + gl; i < e; i += G) {
+    // ---- sweep 2: one pose-major record per observation, last observation first (most tracks are not
+    // longer than G, so most records are written without evaluating the Jacobians a second time) ----
+    for (int i = i_keep; i >= s; i -= G) {
       const uint32_t slot = P.obs_slot[i];
       if (slot == kNoSlot) continue;
-      ObsJac<L> o;
-      obs_jacobians<L>(P, c, i, o);
-      const double sw = sqrt(P.obs_w[i]);
+      if (i != i_keep) { obs_jacobians<L>(P, c, i, o); w_keep = P.obs_w[i]; }
+      const double sw = sqrt(w_keep);
       double A[12], B[2 * L];
 #pragma unroll
       for (int k = 0; k < 12; ++k) A[k] = sw * o.Jm[k];
@@ -192,10 +223,13 @@ __global__ void __launch_bounds__(128) k_linearize(DeviceProblem P) {
 #pragma unroll
         for (int k = 0; k < 6; ++k) W[k] = A[k] * bv0 + A[6 + k] * bv1;
         const double c0 = bv0 * Vi[0], c1 = bv1 * Vi[0];
+        if (o.ref_on) {
+          ref_jacobian<L>(c, o, Q);
 #pragma unroll
-        for (int k = 0; k < 6; ++k) {
-          Q[k] = o.ref_on ? sw * o.Jr[k] - c0 * Wr[k] : 0.0;
-          Q[6 + k] = o.ref_on ? sw * o.Jr[6 + k] - c1 * Wr[k] : 0.0;
+          for (int k = 0; k < 6; ++k) { Q[k] = sw * Q[k] - c0 * Wr[k]; Q[6 + k] = sw * Q[6 + k] - c1 * Wr[k]; }
+        } else {
+#pragma unroll
+          for (int k = 0; k < 12; ++k) Q[k] = 0.0;
         }
         const double p0 = r0 - bv0 * dhat[0], p1 = r1 - bv1 * dhat[0];
 #pragma unroll

@@ -28,10 +28,34 @@
 #include <cstdio>
 #include <iostream>
 #include <memory>
+#include <new>
 #include <vector>
 
 #include "../ba_b200.h"
 #include "MiniTypes.h"
+
+namespace ba {
+namespace detail {
+/* Allocator of the observation buffers: page-locked through the C ABI (bagpu_host_alloc), so Solve() hands the
+ * GPU arrays it can DMA from directly.  Init(num_poses, num_measurements, num_landmarks) reserves them once, like
+ * the reference's reserve calls (reference BundleAdjuster.h:226-233). */
+template <typename T>
+struct HostAllocator {
+  typedef T value_type;
+  HostAllocator() {}
+  template <typename U> HostAllocator(const HostAllocator<U>&) {}
+  T* allocate(size_t n) {
+    void* p = nullptr;
+    if (bagpu_host_alloc(n * sizeof(T), &p) != 0 || !p) throw std::bad_alloc();
+    return static_cast<T*>(p);
+  }
+  void deallocate(T* p, size_t) { bagpu_host_free(p); }
+  template <typename U> bool operator==(const HostAllocator<U>&) const { return true; }
+  template <typename U> bool operator!=(const HostAllocator<U>&) const { return false; }
+};
+template <typename T> using HostVector = std::vector<T, HostAllocator<T>>;
+}  // namespace detail
+}  // namespace ba
 
 /* reference include/ba/Types.h:33-36 */
 #ifndef IMU_GYRO_SIGMA
@@ -214,6 +238,7 @@ class BundleAdjuster {
     lm_x_w_.reserve(4 * (size_t)num_landmarks); lm_ref_pose_.reserve(num_landmarks);
     pr_z_.clear(); pr_pose_.clear(); pr_lm_.clear(); pr_cam_.clear(); pr_w0_.clear(); pr_res_.clear(); pr_w_.clear(); pr_maha_.clear();
     pr_z_.reserve(2 * (size_t)num_measurements); pr_pose_.reserve(num_measurements); pr_lm_.reserve(num_measurements);
+    pr_cam_.reserve(num_measurements); pr_w0_.reserve(num_measurements);
     un_pose_.clear(); un_t_.clear(); un_cov_inv_.clear(); un_rot_.clear();
     bin_p1_.clear(); bin_p2_.clear(); bin_t_.clear(); bin_cov_inv_.clear(); bin_w_.clear(); bin_rot_.clear();
     imu_p1_.clear(); imu_p2_.clear(); imu_ms_.assign(1, 0u); imu_meas_.clear(); imu_w_.clear();
@@ -521,8 +546,8 @@ class BundleAdjuster {
   std::vector<uint8_t> lm_active_, lm_reliable_;
   std::vector<int> lm_external_;
   /* projection residuals, SoA (proj_residuals_) */
-  std::vector<double> pr_z_, pr_w0_, pr_res_, pr_w_, pr_maha_;
-  std::vector<uint32_t> pr_pose_, pr_lm_, pr_cam_;
+  detail::HostVector<double> pr_z_, pr_w0_; std::vector<double> pr_res_, pr_w_, pr_maha_;
+  detail::HostVector<uint32_t> pr_pose_, pr_lm_, pr_cam_;
   std::vector<uint32_t> conditioning_proj_residuals_, conditioning_inertial_residuals_;
   /* unary / binary / inertial residuals, SoA */
   std::vector<uint32_t> un_pose_; std::vector<double> un_t_, un_cov_inv_; std::vector<uint8_t> un_rot_;

@@ -25,6 +25,7 @@
 #ifndef BA_B200_H
 #define BA_B200_H
 
+#include <stddef.h>
 #include <stdint.h>
 
 #ifdef __cplusplus
@@ -126,6 +127,13 @@ void bagpu_destroy(bagpu_handle h);
 const char* bagpu_last_error(void);
 int bagpu_set_options(bagpu_handle h, const bagpu_options* opt);
 void bagpu_default_options(bagpu_options* opt);   /* values of BundleAdjuster.h:75-106 */
+
+/* Page-locked host buffers for the arrays handed to bagpu_set_* / bagpu_get_*: copies from and to them run as direct
+ * DMA instead of being staged by the driver.  Optional (any host pointer is accepted by the setters); without a CUDA
+ * device the buffer is ordinary memory.  ba/BundleAdjuster.h keeps its structure-of-arrays observation buffers in
+ * them (the reference's std::vector storage, BundleAdjuster.h:738-745). */
+int bagpu_host_alloc(size_t bytes, void** out);
+int bagpu_host_free(void* p);
 
 /* ---- problem upload (host -> HBM).  Replaces the AoS vectors BundleAdjuster.h:738-745 -- */
 /* rig: calibu linear camera params fx fy u0 v0 and T_vs per camera (BundleAdjuster.h:259) */
