@@ -92,7 +92,7 @@ __global__ void __launch_bounds__(CholCfg<T>::NT, 1) k_chol_dataflow(CholDev c) 
   typedef CholCfg<T> Cfg;
   constexpr int LD = Cfg::LD, NS = Cfg::NS, MH = Cfg::MH, NT = Cfg::NT, KQ = T / 4, NG2 = Cfg::NG2, XC = Cfg::XC;
   extern __shared__ double sm[];
-  __shared__ int s_task;
+  __shared__ int s_task, s_ready;
   double* M = sm;                  // [T][LD]
   double* av = M + T * LD;         // |d|^-1/2
   double* sv = av + T;             // sign(d)
@@ -124,21 +124,27 @@ __global__ void __launch_bounds__(CholCfg<T>::NT, 1) k_chol_dataflow(CholDev c) 
       double acc0[MH], acc1[MH];
 #pragma unroll
       for (int mi = 0; mi < MH; ++mi) { acc0[mi] = 0.0; acc1[mi] = 0.0; }
-      const int n_terms = tk.le - tk.lb;
-      for (int stage = 0; stage < 2; ++stage) {
-        // stage 0: every term but the newest (almost always ready); stage 1: the newest
-        const int e0 = stage == 0 ? tk.lb : tk.le - 1, e1 = stage == 0 ? tk.le - 1 : tk.le;
-        if (n_terms == 0 || e1 <= e0) continue;
+      // Terms are listed by ascending row k, the order in which they become ready.  Warp 0 polls the flags of the
+      // next (up to 32) terms without blocking and the CTA multiplies out the ready prefix, so that when the newest
+      // U_ki arrives everything older is already in the accumulators (waiting for all terms but the newest first
+      // left ~60 serial tile products on the critical path of every separator row).
+      for (int e = tk.lb; e < tk.le;) {
         if (warp == 0) {
-          for (int e = e0 + lane; e < e1; e += 32) {
-            const CholTerm tm = c.terms[e];
-            while (ld_acquire(tile_flag + tm.sa) == 0) __nanosleep(40);
-            while (ld_acquire(tile_flag + tm.sb) == 0) __nanosleep(40);
+          const int idx = e + lane;
+          bool ready = false;
+          if (idx < tk.le) {
+            const CholTerm tm = c.terms[idx];
+            ready = ld_acquire(tile_flag + tm.sa) != 0 && ld_acquire(tile_flag + tm.sb) != 0;
           }
+          const unsigned m = __ballot_sync(0xffffffffu, ready);
+          if (lane == 0) s_ready = (m == 0xffffffffu) ? 32 : (__ffs(~m) - 1);
         }
         __syncthreads();
-        for (int e = e0; e < e1; ++e) {
-          const CholTerm tm = c.terms[e];
+        const int nr = s_ready;
+        __syncthreads();
+        if (nr == 0) { __nanosleep(40); continue; }
+        for (int q = 0; q < nr; ++q) {
+          const CholTerm tm = c.terms[e + q];
           const double* Ua = c.tiles + (size_t)tm.sa * T * T;
           const double* Ub = c.tiles + (size_t)tm.sb * T * T;
           const double* sg = c.sgn + (size_t)tm.k * T;
@@ -157,6 +163,7 @@ __global__ void __launch_bounds__(CholCfg<T>::NT, 1) k_chol_dataflow(CholDev c) 
             }
           }
         }
+        e += nr;
       }
       CHOL_STAMP(1);
       double* Aij = c.tiles + (size_t)tk.slot * T * T;
@@ -413,7 +420,11 @@ void chol_build_plan(int nT, const std::vector<int>& tile_map, const std::vector
   for (int ri = 0; ri < nT; ++ri) {
     const int i = rows[ri];
     int lb = (int)terms.size();
+    // terms in the order their tiles become ready (wavefront level of the producing row, then row): the kernel
+    // accumulates the ready prefix while it waits for the rest
+    auto by_level = [&](const CholTerm& a, const CholTerm& b) { return level[a.k] != level[b.k] ? level[a.k] < level[b.k] : a.k < b.k; };
     for (int k : col_rows[i]) { CholTerm tm; tm.sa = slot(k, i); tm.sb = tm.sa; tm.k = k; terms.push_back(tm); }
+    std::sort(terms.begin() + lb, terms.end(), by_level);
     add(kTaskDiag, i, i, slot(i, i), lb, (int)terms.size());
     for (int e = row_ptr[i]; e < row_ptr[i + 1]; ++e) {
       const int j = row_col[e];
@@ -426,6 +437,7 @@ void chol_build_plan(int nT, const std::vector<int>& tile_map, const std::vector
           ++a; ++b;
         } else if (ci[a] < cj[b]) ++a; else ++b;
       }
+      std::sort(terms.begin() + lb, terms.end(), by_level);
       add(kTaskOff, i, j, slot(i, j), lb, (int)terms.size());
     }
   }

@@ -116,7 +116,7 @@ __global__ void __launch_bounds__(128) k_sd_denominator(DeviceProblem P) {
       if (L == 1 && o.ref_on) {
         const double* bp = P.b_p + (size_t)c.ref_opt * P.D;
         double Jr[12];
-        ref_jacobian<L>(c, o, Jr);
+        ref_jacobian<L>(c, o.Bp, Jr);
 #pragma unroll
         for (int k = 0; k < 6; ++k) { v0 += Jr[k] * bp[k]; v1 += Jr[6 + k] * bp[k]; }
       }

@@ -158,12 +158,12 @@ BA_D void obs_jacobians(const DeviceProblem& P, const LmCtx<L>& c, int obs, ObsJ
 }
 
 // reference-pose Jacobian of an observation (LmSize 1, o.ref_on): d z / d x_ref = Bp [ -rho I | R_wp_r [Y]x ], columns of
-// masked parameters zeroed
+// masked parameters zeroed (linear in Bp: a scaled Bp gives the scaled Jacobian)
 template <int L>
-BA_D void ref_jacobian(const LmCtx<L>& c, const ObsJac<L>& o, double* Jr) {
+BA_D void ref_jacobian(const LmCtx<L>& c, const double* Bp, double* Jr) {
 #pragma unroll
   for (int rr = 0; rr < 2; ++rr) {
-    const double* Br = o.Bp + 3 * rr;
+    const double* Br = Bp + 3 * rr;
     Jr[6 * rr + 0] = -c.rho * Br[0];
     Jr[6 * rr + 1] = -c.rho * Br[1];
     Jr[6 * rr + 2] = -c.rho * Br[2];

@@ -224,7 +224,7 @@ __global__ void __launch_bounds__(128, (L == 1) ? 3 : 4) k_linearize(DeviceProbl
         for (int k = 0; k < 6; ++k) W[k] = A[k] * bv0 + A[6 + k] * bv1;
         const double c0 = bv0 * Vi[0], c1 = bv1 * Vi[0];
         if (o.ref_on) {
-          ref_jacobian<L>(c, o, Q);
+          ref_jacobian<L>(c, o.Bp, Q);
 #pragma unroll
           for (int k = 0; k < 6; ++k) { Q[k] = sw * Q[k] - c0 * Wr[k]; Q[6 + k] = sw * Q[6 + k] - c1 * Wr[k]; }
         } else {

@@ -233,7 +233,14 @@ def main():
         dom = max(("k_linearize", "k_reduce_blocks", "k_residual"), key=lambda k: kt[k])
         ach = per_kernel[dom] / world / (kt[dom] * 1e-3) / 1e9
         t_build = sum(kt.values())
-        roofline = {"bound": "hbm", "kernel": dom, "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak, "traffic": None,
+        traffic = None
+        try:
+            tj = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json")))
+            if world == 1 and args.scale == 1.0:
+                traffic = tj.get(name, {}).get(dom)
+        except Exception:
+            pass
+        roofline = {"bound": "hbm", "kernel": dom, "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak, "traffic": traffic,
                     "algorithmic_bytes_per_launch": per_kernel[dom] / world, "launch_ms": kt[dom], "peak_source": peak_src,
                     "note": "achieved = SURVEY 8d algorithmic bytes of this kernel / its CUDA-event time; the kernel gathers each record once per pose pair from L2 (DESIGN.md 4)",
                     "build": {"algorithmic_bytes": tot_b / world, "ms": t_build, "achieved": tot_b / world / (t_build * 1e-3) / 1e9,
