@@ -140,6 +140,7 @@ struct bagpu_handle_s {
   std::vector<uint8_t> pose_has_imu;
   std::vector<uint32_t> lm_obs_start, obs_perm;   // host landmark-major order (pattern queries only, host_order())
   bool host_order_valid = false;
+  bool maha0_valid = false;         // obs_maha0 holds |r|^2 w0 of the current state (written by the last accepted evaluation)
   size_t n_raw = 0;                 // projection residuals handed to set_proj_residuals
   bool raw_on_device = false, raw_has_cam = false, raw_has_w0 = false, ids_on_host = true;
   uint32_t s_lo = 0, s_hi = 0;      // this rank's slice of the landmark-major stream
@@ -690,7 +691,10 @@ struct bagpu_handle_s {
     d_S.zero(st, (size_t)n_tiles * T * T); d_bp.zero(st); d_sc.zero(st);
     { const double flag = n_obs_total > 0 ? 1.0 : 0.0; CU(cudaMemcpyAsync(&d_sc.p->dot[7], &flag, sizeof(double), cudaMemcpyHostToDevice, st)); }
     launch_pose_frames(P, st); ++launches;
-    launch_residual(P, G, st); if (n_obs) ++launches;
+    // pass 1 (residuals -> median input) is skipped when the accepted EvaluateResiduals of the previous iteration
+    // already left |r|^2 w0 of this very state in obs_maha0
+    if (!maha0_valid) { launch_residual(P, G, st); if (n_obs) ++launches; }
+    maha0_valid = false;
     CU(cudaEventRecord(ev[1], st));
     const unsigned long long n_total = (unsigned long long)n_obs_total;   // ranks hold disjoint landmark shards
     run_select(d_obs_maha0.p, (size_t)n_obs, n_total, &d_sc.p->median);
@@ -749,6 +753,19 @@ struct bagpu_handle_s {
     sync();
     return v;
   }
+  // (a1 . b1, a2 . b2) with one read-back; the second product is over landmark-sharded vectors (summed over ranks)
+  void dot_pair(const double* a1, const double* b1, size_t n1, const double* a2, const double* b2, size_t n2, double* r1, double* r2,
+                bool wait = true) {
+    CU(cudaMemsetAsync(&d_sc.p->dot[0], 0, 2 * sizeof(double), st));
+    if (n1) { launch_dot(a1, b1, n1, &d_sc.p->dot[0], st); ++launches; }
+    if (n2) { launch_dot(a2, b2, n2, &d_sc.p->dot[1], st); ++launches; }
+    if (world > 1) allreduce_f64(&d_sc.p->dot[1], 1);
+    if (!wait) return;
+    double v[2];
+    CU(cudaMemcpyAsync(v, &d_sc.p->dot[0], 2 * sizeof(double), cudaMemcpyDeviceToHost, st));
+    sync();
+    *r1 = v[0]; *r2 = v[1];
+  }
   // sum over ranks of a landmark-sharded quantity
   double shard_sum(double v) {
     if (world <= 1) return v;
@@ -784,7 +801,8 @@ struct bagpu_handle_s {
   // EvaluateResiduals at the current state (cpp:144-274); returns the four sums
   void evaluate(double* e_proj, double* e_bin, double* e_un, double* e_in) {
     CU(cudaMemsetAsync(&d_sc.p->eval_proj, 0, 4 * sizeof(double), st));
-    launch_evaluate(P, G, &d_sc.p->eval_proj, nullptr, nullptr, st); if (n_obs) ++launches;
+    launch_evaluate(P, G, &d_sc.p->eval_proj, nullptr, nullptr, 1, st); if (n_obs) ++launches;
+    maha0_valid = false;   // overwritten with this state's values; valid for the next build only if the step is kept
     if (rank == 0) launch_other_evaluate(P, R, st, &launches);
     if (world > 1) allreduce_f64(&d_sc.p->eval_proj, 4);
     double v[4];
@@ -847,16 +865,18 @@ struct bagpu_handle_s {
     if (opt.use_dogleg) {
       // steepest descent step (cpp:857-929)
       if (L > 0 && n_al > 0) { launch_compact_bl(P, d_bl_compact.p, st); ++launches; }
-      const double n2_bp = np ? dot(d_bp.p, d_bp.p, np, 0) : 0.0;
-      const double n2_bl = shard_sum((L > 0 && nl) ? dot(d_bl_compact.p, d_bl_compact.p, nl, 1) : 0.0);
-      const double numerator = n2_bp + n2_bl;
+      double n2_bp = 0.0, n2_bl = 0.0;
+      dot_pair(d_bp.p, d_bp.p, np, d_bl_compact.p, d_bl_compact.p, (L > 0) ? nl : 0, &n2_bp, &n2_bl, false);
       CU(cudaMemsetAsync(&d_sc.p->sd_den_proj, 0, 2 * sizeof(double), st));
       if (n_ap > 0 || n_al > 0) { launch_sd_denominator(P, G, st); if (n_obs) ++launches; }
       if (n_ap > 0 && rank == 0) launch_other_sd(P, R, st, &launches);
       if (world > 1) allreduce_f64(&d_sc.p->sd_den_proj, 2);
-      double den[2];
+      double den[2], nn[2];
       CU(cudaMemcpyAsync(den, &d_sc.p->sd_den_proj, 2 * sizeof(double), cudaMemcpyDeviceToHost, st));
+      CU(cudaMemcpyAsync(nn, &d_sc.p->dot[0], 2 * sizeof(double), cudaMemcpyDeviceToHost, st));
       sync();
+      n2_bp = nn[0]; n2_bl = nn[1];
+      const double numerator = n2_bp + n2_bl;
       const double denominator = den[0] + den[1];
       const double factor = numerator / denominator;
       const double delta_sd_norm = std::sqrt(factor * factor * n2_bp + factor * factor * n2_bl);
@@ -877,8 +897,7 @@ struct bagpu_handle_s {
           if (!gn_computed) {
             if (!gauss_newton()) return false;
             gn_computed = true;
-            gn_norm2_p = np ? dot(d_gn_p.p, d_gn_p.p, np, 2) : 0.0;
-            gn_norm2_l = shard_sum(nl ? dot(d_gn_l.p, d_gn_l.p, nl, 3) : 0.0);
+            dot_pair(d_gn_p.p, d_gn_p.p, np, d_gn_l.p, d_gn_l.p, nl, &gn_norm2_p, &gn_norm2_l);
           }
           const double delta_gn_norm = std::sqrt(gn_norm2_p + gn_norm2_l);
           tr.gn_norm = delta_gn_norm;
@@ -892,15 +911,17 @@ struct bagpu_handle_s {
             // diff = gn - sd, formed explicitly like the reference (cpp:991-1017)
             launch_axpby(d_tmp_p.p, 1.0, d_gn_p.p, -factor, d_bp.p, np, st); if (np) ++launches;
             if (nl) { launch_axpby(d_tmp_l.p, 1.0, d_gn_l.p, -factor, d_bl_compact.p, nl, st); ++launches; }
-            const double a = (np ? dot(d_tmp_p.p, d_tmp_p.p, np, 4) : 0.0) + shard_sum(nl ? dot(d_tmp_l.p, d_tmp_l.p, nl, 5) : 0.0);
-            const double b = 2 * ((np ? factor * dot(d_tmp_p.p, d_bp.p, np, 4) : 0.0) + shard_sum(nl ? factor * dot(d_tmp_l.p, d_bl_compact.p, nl, 5) : 0.0));
+            double ap = 0, al = 0, bpp = 0, bll = 0;
+            dot_pair(d_tmp_p.p, d_tmp_p.p, np, d_tmp_l.p, d_tmp_l.p, nl, &ap, &al);
+            dot_pair(d_tmp_p.p, d_bp.p, np, d_tmp_l.p, d_bl_compact.p, nl, &bpp, &bll);
+            const double a = ap + al;
+            const double b = 2 * (factor * bpp + factor * bll);
             const double c = (factor * factor * n2_bp + factor * factor * n2_bl) - trust_region * trust_region;
             double beta = 0;
             if (b * b > 4 * a * c && a > 1e-10) beta = (-(b * b) + std::sqrt(b * b - 4 * a * c)) / (2 * a);   // quirk Q4
             launch_axpby(d_dl_p.p, beta, d_tmp_p.p, factor, d_bp.p, np, st); if (np) ++launches;
             if (nl) { launch_axpby(d_dl_l.p, beta, d_tmp_l.p, factor, d_bl_compact.p, nl, st); ++launches; }
-            n2_dl_p = np ? dot(d_dl_p.p, d_dl_p.p, np, 4) : 0.0;
-            n2_dl_l = shard_sum(nl ? dot(d_dl_l.p, d_dl_l.p, nl, 5) : 0.0);
+            dot_pair(d_dl_p.p, d_dl_p.p, np, d_dl_l.p, d_dl_l.p, nl, &n2_dl_p, &n2_dl_l);
           }
         }
         CU(cudaEventRecord(ev[10], st));
@@ -934,6 +955,7 @@ struct bagpu_handle_s {
         } else {
           proj_error = e_proj; unary_error = e_un; binary_error = e_bin; inertial_error = e_in;
           trust_region *= 2;
+          maha0_valid = opt.apply_results != 0;
           break;
         }
       }
@@ -944,7 +966,8 @@ struct bagpu_handle_s {
       backup_state();
       launch_axpby(d_dl_p.p, gn_damping, d_gn_p.p, 0, nullptr, np, st); if (np) ++launches;
       if (nl) { launch_axpby(d_dl_l.p, gn_damping, d_gn_l.p, 0, nullptr, nl, st); ++launches; }
-      const double n2p = np ? dot(d_dl_p.p, d_dl_p.p, np, 0) : 0.0, n2l = shard_sum(nl ? dot(d_dl_l.p, d_dl_l.p, nl, 1) : 0.0);
+      double n2p = 0, n2l = 0;
+      dot_pair(d_dl_p.p, d_dl_p.p, np, d_dl_l.p, d_dl_l.p, nl, &n2p, &n2l);
       tr.gn_norm = std::sqrt(n2p + n2l); tr.delta_p_norm = std::sqrt(n2p); tr.delta_l_norm = std::sqrt(n2l);
       evaluate(&e_proj, &e_bin, &e_un, &e_in);
       const double prev_error = e_proj + e_in + e_bin + e_un;
@@ -963,6 +986,7 @@ struct bagpu_handle_s {
         return false;
       }
       proj_error = e_proj; unary_error = e_un; binary_error = e_bin; inertial_error = e_in;
+      maha0_valid = opt.apply_results != 0;
     }
     return true;
   }
@@ -970,6 +994,7 @@ struct bagpu_handle_s {
   void prepare_solve() {
     PhaseClock pc;
     ensure_device(); pc.lap("ensure_device");
+    maha0_valid = false;
     if (dirty) { setup(); pc.lap("setup (host symbolic)"); upload_all(); sync(); pc.lap("upload_all"); solved_once = false; }
     else apply_options();
     // Solve() prologue (cpp:287-296)
@@ -1074,7 +1099,7 @@ struct bagpu_handle_s {
     d_res_out.alloc(2 * nt); d_maha_out.alloc(nt);
     if (world > 1) { d_res_out.zero(st); d_maha_out.zero(st); }
     CU(cudaMemsetAsync(&d_sc.p->dot[5], 0, sizeof(double), st));
-    launch_evaluate(P, G, &d_sc.p->dot[5], d_res_out.p, d_maha_out.p, st); ++launches;
+    launch_evaluate(P, G, &d_sc.p->dot[5], d_res_out.p, d_maha_out.p, 0, st); ++launches;
   }
 
   void export_residuals(double* res2, double* weight, double* maha) {

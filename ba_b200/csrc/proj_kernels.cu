@@ -182,7 +182,7 @@ __global__ void __launch_bounds__(256) k_back_substitute(DeviceProblem P, const 
 // ---------------------------------------------------------------------------------------
 // residual-only evaluation with the current Huber weights (cpp:148-188)
 template <int L, int G>
-__global__ void __launch_bounds__(256) k_evaluate(DeviceProblem P, double* out_sum, double* res_out, double* maha_out) {
+__global__ void __launch_bounds__(256) k_evaluate(DeviceProblem P, double* out_sum, double* res_out, double* maha_out, int write_maha0) {
   const int lane = threadIdx.x & 31, gl = lane % G;
   const int group = (blockIdx.x * blockDim.x + threadIdx.x) / G;
   const int n_groups = (gridDim.x * blockDim.x) / G;
@@ -200,6 +200,8 @@ __global__ void __launch_bounds__(256) k_evaluate(DeviceProblem P, double* out_s
       const double n2 = r[0] * r[0] + r[1] * r[1];
       const double m = n2 * P.obs_w[i];
       acc += m;
+      // the next BuildProblem starts from this state if the step is accepted: its median input, for free
+      if (write_maha0) P.obs_maha0[i] = n2 * P.obs_w0[i];
       if (sqrt(n2) > P.outlier_threshold) ++n_out;
       if (res_out) {
         const uint32_t id = P.obs_perm[i];
@@ -362,11 +364,11 @@ void launch_back_substitute(const DeviceProblem& P, int G, const double* delta_p
   DISPATCH_LG(P.L, G, CALL);
 #undef CALL
 }
-void launch_evaluate(const DeviceProblem& P, int G, double* out_sum, double* res_out, double* maha_out, cudaStream_t st) {
+void launch_evaluate(const DeviceProblem& P, int G, double* out_sum, double* res_out, double* maha_out, int write_maha0, cudaStream_t st) {
   if (P.n_obs == 0) return;
   cudaMemsetAsync(P.lm_outliers, 0, sizeof(uint32_t) * P.n_lms, st);
   const int grid = grid_for((size_t)P.n_lms * G, 256, 8);
-#define CALL(LL, GG) k_evaluate<LL, GG><<<grid, 256, 0, st>>>(P, out_sum, res_out, maha_out)
+#define CALL(LL, GG) k_evaluate<LL, GG><<<grid, 256, 0, st>>>(P, out_sum, res_out, maha_out, write_maha0)
   DISPATCH_LG(P.L, G, CALL);
 #undef CALL
 }
