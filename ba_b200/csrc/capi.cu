@@ -21,6 +21,7 @@
 #include <dlfcn.h>
 #include "ba_gpu.h"
 #include "device_math.cuh"
+#include "dev_alloc.h"
 #include "launch.h"
 
 using namespace bagpu;
@@ -54,12 +55,12 @@ struct DevBuf {
   T* p = nullptr;
   size_t n = 0;
   ~DevBuf() { release(); }
-  void release() { if (p) cudaFree(p); p = nullptr; n = 0; }
+  void release() { if (p) dev_free(p); p = nullptr; n = 0; }
   void alloc(size_t count) {
     if (count <= n && p) return;
     release();
     if (count == 0) count = 1;
-    CU(cudaMalloc(&p, count * sizeof(T)));
+    CU(dev_alloc((void**)&p, count * sizeof(T)));
     n = count;
   }
   void upload(const std::vector<T>& h, cudaStream_t st) {
@@ -540,7 +541,7 @@ struct bagpu_handle_s {
   // lists (symbolic.cu), the host cuts every S block into chunks of at most kChunk entries ----
   void build_reduce_items() {
     constexpr uint32_t kChunk = 512;
-    if (d_pairs) { cudaFree(d_pairs); d_pairs = nullptr; }
+    if (d_pairs) { dev_free(d_pairs); d_pairs = nullptr; }
     n_pairs = 0; n_items = 0; n_items_sym = 0;
     if (L == 0 || n_obs == 0 || n_ap == 0) return;
     std::vector<unsigned long long> bkey; std::vector<uint32_t> bcnt; std::string err;
@@ -1186,9 +1187,10 @@ int bagpu_create(const bagpu_dims* d, bagpu_handle* out) {
 
 void bagpu_destroy(bagpu_handle h) {
   if (!h) return;
+  if (h->st) cudaStreamSynchronize(h->st);
   if (h->comm && g_nccl.commDestroy) g_nccl.commDestroy(h->comm);
   if (h->ev_ok) for (auto& e : h->ev) cudaEventDestroy(e);
-  if (h->d_pairs) cudaFree(h->d_pairs);
+  if (h->d_pairs) dev_free(h->d_pairs);
   if (h->st) cudaStreamDestroy(h->st);
   delete h;
 }

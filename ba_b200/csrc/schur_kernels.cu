@@ -41,8 +41,13 @@ __global__ void __launch_bounds__(128, (L == 1) ? 3 : 4) k_linearize(DeviceProbl
   const int n_groups = (gridDim.x * blockDim.x) / G;
   const double c_huber = P.c_huber_factor * sqrt(P.sc->median);
   double err = 0.0;
+  // the CSR bounds of the NEXT landmark of the group are requested one landmark ahead (the walk is a chain of
+  // dependent round trips: bounds -> pose id -> pose frame -> slot; each one taken off the chain is ~1 us per landmark)
+  int s_n = 0, e_n = 0;
+  if (group < P.n_lms) { s_n = P.lm_obs_start[group]; e_n = P.lm_obs_start[group + 1]; }
   for (int lm = group; lm < P.n_lms; lm += n_groups) {
-    const int s = P.lm_obs_start[lm], e = P.lm_obs_start[lm + 1];
+    const int s = s_n, e = e_n;
+    if (lm + n_groups < P.n_lms) { s_n = P.lm_obs_start[lm + n_groups]; e_n = P.lm_obs_start[lm + n_groups + 1]; }
     LmCtx<L> c;
     load_lm<L>(P, lm, c);
     const bool lm_on = c.lm_opt >= 0;
@@ -65,7 +70,9 @@ __global__ void __launch_bounds__(128, (L == 1) ? 3 : 4) k_linearize(DeviceProbl
     ObsJac<L> o;              // the Jacobians of the lane's LAST observation stay in registers for sweep 2
     double w_keep = 0.0;
     int i_keep = -1;
+    uint32_t slot_keep = kNoSlot;
     for (int i = s + gl; i < e; i += G) {
+      slot_keep = P.obs_slot[i];   // needed only in sweep 2: requested here, off the dependent chain
       obs_jacobians<L>(P, c, i, o);
       const double w0 = P.obs_w0[i];
       const double n2 = o.r[0] * o.r[0] + o.r[1] * o.r[1];
@@ -190,7 +197,7 @@ __global__ void __launch_bounds__(128, (L == 1) ? 3 : 4) k_linearize(DeviceProbl
     // ---- sweep 2: one pose-major record per observation, last observation first (most tracks are not
     // longer than G, so most records are written without evaluating the Jacobians a second time) ----
     for (int i = i_keep; i >= s; i -= G) {
-      const uint32_t slot = P.obs_slot[i];
+      const uint32_t slot = (i == i_keep) ? slot_keep : P.obs_slot[i];
       if (slot == kNoSlot) continue;
       if (i != i_keep) { obs_jacobians<L>(P, c, i, o); w_keep = P.obs_w[i]; }
       const double sw = sqrt(w_keep);

@@ -14,6 +14,7 @@
 #include <cub/device/device_radix_sort.cuh>
 #include <string>
 #include "ba_gpu.h"
+#include "dev_alloc.h"
 #include "launch.h"
 
 namespace bagpu {
@@ -176,16 +177,16 @@ int sort_positions_by_key(const uint32_t* keys_in, uint32_t* keys_out, uint32_t*
   int bits = 1, rc = 1;
   cudaError_t e;
   while (bits < 32 && (1ull << bits) <= (unsigned long long)max_key) ++bits;
-  if ((e = cudaMalloc(&iota, sizeof(uint32_t) * (size_t)n)) != cudaSuccess) goto fail;
+  if ((e = dev_alloc((void**)&iota, sizeof(uint32_t) * (size_t)n)) != cudaSuccess) goto fail;
   k_iota<<<blocks_for(n), 256, 0, st>>>(iota, n);
   if ((e = cub::DeviceRadixSort::SortPairs(nullptr, tb, keys_in, keys_out, iota, vals_out, (unsigned long long)n, 0, bits, st)) != cudaSuccess) goto fail;
-  if ((e = cudaMalloc(&tmp, tb ? tb : 1)) != cudaSuccess) goto fail;
+  if ((e = dev_alloc((void**)&tmp, tb ? tb : 1)) != cudaSuccess) goto fail;
   if ((e = cub::DeviceRadixSort::SortPairs(tmp, tb, keys_in, keys_out, iota, vals_out, (unsigned long long)n, 0, bits, st)) != cudaSuccess) goto fail;
   if ((e = cudaStreamSynchronize(st)) != cudaSuccess) goto fail;
   rc = 0;
 fail:
   if (rc) err = std::string("sort_positions_by_key: ") + cudaGetErrorString(e);
-  cudaFree(iota); cudaFree(tmp);
+  dev_free(iota); dev_free(tmp);
   return rc;
 }
 

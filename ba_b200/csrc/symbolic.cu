@@ -12,6 +12,7 @@
 #include <string>
 #include <vector>
 #include "ba_gpu.h"
+#include "dev_alloc.h"
 #include "launch.h"
 
 namespace bagpu {
@@ -82,11 +83,11 @@ int build_pair_lists(const DeviceProblem& P, cudaStream_t st, uint2** pairs_out,
   u64 last_off = 0, last_cnt = 0, total = 0;
   int n_runs = 0, bits = 1, rc = 1;
   const int n = P.n_lms;
-  SYM_CU(cudaMalloc(&d_count, sizeof(u64) * n));
-  SYM_CU(cudaMalloc(&d_offs, sizeof(u64) * n));
+  SYM_CU(dev_alloc((void**)&d_count, sizeof(u64) * n));
+  SYM_CU(dev_alloc((void**)&d_offs, sizeof(u64) * n));
   k_pair_count<<<(n + 255) / 256, 256, 0, st>>>(P, d_count);
   SYM_CU(cub::DeviceScan::ExclusiveSum(nullptr, tmp_bytes, d_count, d_offs, n, st));
-  SYM_CU(cudaMalloc(&d_tmp, tmp_bytes ? tmp_bytes : 1));
+  SYM_CU(dev_alloc((void**)&d_tmp, tmp_bytes ? tmp_bytes : 1));
   SYM_CU(cub::DeviceScan::ExclusiveSum(d_tmp, tmp_bytes, d_count, d_offs, n, st));
   SYM_CU(cudaMemcpyAsync(&last_off, d_offs + (n - 1), sizeof(u64), cudaMemcpyDeviceToHost, st));
   SYM_CU(cudaMemcpyAsync(&last_cnt, d_count + (n - 1), sizeof(u64), cudaMemcpyDeviceToHost, st));
@@ -94,20 +95,20 @@ int build_pair_lists(const DeviceProblem& P, cudaStream_t st, uint2** pairs_out,
   total = last_off + last_cnt;
   if (total == 0) { rc = 0; goto done; }
   if (total >= 0xfffffff0ull) { err = "pair list exceeds 2^32 entries"; goto done; }
-  SYM_CU(cudaMalloc(&d_keys, sizeof(u64) * total));
-  SYM_CU(cudaMalloc(&d_vals, sizeof(u64) * total));
-  SYM_CU(cudaMalloc(&d_keys2, sizeof(u64) * total));
-  SYM_CU(cudaMalloc(&d_vals2, sizeof(u64) * total));
+  SYM_CU(dev_alloc((void**)&d_keys, sizeof(u64) * total));
+  SYM_CU(dev_alloc((void**)&d_vals, sizeof(u64) * total));
+  SYM_CU(dev_alloc((void**)&d_keys2, sizeof(u64) * total));
+  SYM_CU(dev_alloc((void**)&d_vals2, sizeof(u64) * total));
   k_pair_emit<<<(n + 255) / 256, 256, 0, st>>>(P, d_offs, d_keys, d_vals);
   while ((1ull << bits) < 2ull * (u64)P.n_active_poses * (u64)P.n_active_poses && bits < 64) ++bits;
   SYM_CU(cub::DeviceRadixSort::SortPairs(nullptr, tb, d_keys, d_keys2, d_vals, d_vals2, (u64)total, 0, bits, st));
-  if (tb > tmp_bytes) { cudaFree(d_tmp); d_tmp = nullptr; SYM_CU(cudaMalloc(&d_tmp, tb)); tmp_bytes = tb; }
+  if (tb > tmp_bytes) { dev_free(d_tmp); d_tmp = nullptr; SYM_CU(dev_alloc((void**)&d_tmp, tb)); tmp_bytes = tb; }
   SYM_CU(cub::DeviceRadixSort::SortPairs(d_tmp, tb, d_keys, d_keys2, d_vals, d_vals2, (u64)total, 0, bits, st));
   // block table: unique keys and their run lengths (reuse d_keys / d_vals as outputs)
   d_unique = d_keys; d_runs = reinterpret_cast<uint32_t*>(d_vals);
-  SYM_CU(cudaMalloc(&d_nruns, sizeof(int)));
+  SYM_CU(dev_alloc((void**)&d_nruns, sizeof(int)));
   SYM_CU(cub::DeviceRunLengthEncode::Encode(nullptr, tb, d_keys2, d_unique, d_runs, d_nruns, (u64)total, st));
-  if (tb > tmp_bytes) { cudaFree(d_tmp); d_tmp = nullptr; SYM_CU(cudaMalloc(&d_tmp, tb)); tmp_bytes = tb; }
+  if (tb > tmp_bytes) { dev_free(d_tmp); d_tmp = nullptr; SYM_CU(dev_alloc((void**)&d_tmp, tb)); tmp_bytes = tb; }
   SYM_CU(cub::DeviceRunLengthEncode::Encode(d_tmp, tb, d_keys2, d_unique, d_runs, d_nruns, (u64)total, st));
   SYM_CU(cudaMemcpyAsync(&n_runs, d_nruns, sizeof(int), cudaMemcpyDeviceToHost, st));
   SYM_CU(cudaStreamSynchronize(st));
@@ -119,8 +120,8 @@ int build_pair_lists(const DeviceProblem& P, cudaStream_t st, uint2** pairs_out,
   *n_pairs_out = (size_t)total;
   rc = 0;
 done:
-  cudaFree(d_count); cudaFree(d_offs); cudaFree(d_keys); cudaFree(d_vals); cudaFree(d_keys2); cudaFree(d_vals2);
-  cudaFree(d_nruns); cudaFree(d_tmp);
+  dev_free(d_count); dev_free(d_offs); dev_free(d_keys); dev_free(d_vals); dev_free(d_keys2); dev_free(d_vals2);
+  dev_free(d_nruns); dev_free(d_tmp);
   return rc;
 }
 

@@ -268,9 +268,10 @@ def test_page_locked_host_buffers_give_identical_results():
     pp.set_bulk(**{k: pinned_like(v) for k, v in a.items()})
     g1, g2 = gpu(p), gpu(pp)
     s1, s2 = g1.solve(3), g2.solve(3)
-    assert s1.post_solve_norm == s2.post_solve_norm          # bit-identical: deterministic kernels, same bytes
-    assert np.array_equal(g1.get_poses()["t_wp"], g2.get_poses()["t_wp"])
-    assert np.array_equal(g1.get_landmarks()["x_w"], g2.get_landmarks()["x_w"])
+    # same bytes in, same kernels: only the order of the atomic error sums differs from run to run
+    assert abs(s1.post_solve_norm - s2.post_solve_norm) <= 1e-12 * s1.post_solve_norm
+    assert rel(g1.get_poses()["t_wp"], g2.get_poses()["t_wp"]) < 1e-12
+    assert rel(g1.get_landmarks()["x_w"], g2.get_landmarks()["x_w"]) < 1e-12
     g2.close()
     release_pinned()
 
