@@ -73,6 +73,7 @@ struct DeviceProblem {
   const uint32_t* obs_cam;   // may be null when n_cams == 1
   const double* obs_w0;
   const uint32_t* obs_perm;  // sorted index -> residual id
+  const uint32_t* obs_lm;    // sorted index -> landmark id (non-decreasing)
   double* obs_maha0;
   double* obs_w;
   const uint32_t* obs_slot;  // pose-major record slot of the observation, kNoSlot if its pose takes no part

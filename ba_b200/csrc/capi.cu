@@ -146,6 +146,8 @@ struct bagpu_handle_s {
   bool raw_on_device = false, raw_has_cam = false, raw_has_w0 = false, ids_on_host = true;
   uint32_t s_lo = 0, s_hi = 0;      // this rank's slice of the landmark-major stream
   unsigned int n_cond_proj = 0;
+  DevBuf<uint2> d_tasks; DevBuf<uint32_t> d_long_lms;   // packed warp tasks of the landmark-major stream (schur_kernels.cu)
+  int n_tasks = 0, n_long = 0;
   std::vector<uint32_t> pose_rec_start, pose_lmrec_start;   // pose-major record slots (ba_gpu.h)
   uint32_t n_rec = 0, n_lmrec = 0;
   int n_items = 0, n_items_sym = 0;
@@ -274,7 +276,7 @@ struct bagpu_handle_s {
     pose_rec_start.assign(n_ap + 1, 0); pose_lmrec_start.assign(n_ap + 1, 0);
     n_rec = 0; n_lmrec = 0; n_cond_proj = 0; s_lo = 0; s_hi = n;
     lm_owner_lo = 0; lm_owner_hi = n_lms;
-    G = 4;
+    G = 4; n_tasks = 0; n_long = 0;
     d_lm_obs_start.alloc((size_t)n_lms + 1); d_lm_obs_start.zero(st);
     if (n == 0 || n_lms == 0) { n_obs = 0; d_obs_slot.alloc(1); return; }
     if (!raw_on_device) {   // the setters ran before a device was usable: take the host copies
@@ -321,6 +323,31 @@ struct bagpu_handle_s {
     }
     n_obs = (int)(s_hi - s_lo);
     launch_local_starts(d_gstarts.p, (uint32_t)n_lms, s_lo, s_hi, d_lm_obs_start.p, st);
+    // warp tasks of the landmark-major kernels: runs of whole landmarks with at most 32 observations in total
+    // (first observation, count); landmarks with longer tracks are listed apart (one warp each)
+    {
+      std::vector<uint2> tasks; std::vector<uint32_t> longs;
+      tasks.reserve((size_t)n_obs / 24 + 16);
+      auto lstart = [&](int l) { const uint32_t v = gstarts[l]; return (v < s_lo ? s_lo : (v > s_hi ? s_hi : v)) - s_lo; };
+      int l = lm_owner_lo;
+      uint32_t b = lstart(l);
+      while (l < lm_owner_hi) {
+        uint32_t e1 = lstart(l + 1);
+        if (e1 - b > 32) { longs.push_back((uint32_t)l); ++l; b = e1; continue; }
+        const uint32_t first = b;
+        uint32_t end = b;
+        while (l < lm_owner_hi) {
+          e1 = lstart(l + 1);
+          if (e1 - end > 32 || e1 - first > 32) break;
+          end = e1; ++l;
+        }
+        if (end > first) tasks.push_back(make_uint2(first, end - first));
+        b = end;
+      }
+      n_tasks = (int)tasks.size(); n_long = (int)longs.size();
+      d_tasks.upload(tasks, st); d_long_lms.upload(longs, st);
+      sync();
+    }
     // 4. the local stream: gathered values, pose-major record slots
     const uint32_t nl = (uint32_t)n_obs;
     d_obs_z.alloc(nl); d_obs_pose.alloc(nl); d_obs_w0.alloc(nl); d_obs_slot.alloc(nl);
@@ -517,6 +544,7 @@ struct bagpu_handle_s {
     P.lm_x = d_lm_x.p; P.lm_ref_pose = d_lm_ref_pose.p; P.lm_ref_cam = d_lm_ref_cam.p; P.lm_opt = d_lm_opt.p; P.lm_reliable = d_lm_reliable.p;
     P.lm_outliers = d_lm_outliers.p; P.lm_obs_start = d_lm_obs_start.p;
     P.obs_z = d_obs_z.p; P.obs_pose = d_obs_pose.p; P.obs_cam = multi_cam ? d_obs_cam.p : nullptr; P.obs_w0 = d_obs_w0.p; P.obs_perm = d_perm_global.p ? d_perm_global.p + s_lo : nullptr;
+    P.obs_lm = d_sorted_lm.p ? d_sorted_lm.p + s_lo : nullptr;
     P.obs_maha0 = d_obs_maha0.p; P.obs_w = d_obs_w.p;
     P.obs_slot = d_obs_slot.p; P.rec = d_rec.p; P.rec_stride = rec_stride;
     P.lm_rslot = (L == 1) ? d_lm_rslot.p : nullptr; P.lm_rec = (L == 1) ? d_lm_rec.p : nullptr;
@@ -700,7 +728,7 @@ struct bagpu_handle_s {
     const unsigned long long n_total = (unsigned long long)n_obs_total;   // ranks hold disjoint landmark shards
     run_select(d_obs_maha0.p, (size_t)n_obs, n_total, &d_sc.p->median);
     CU(cudaEventRecord(ev[2], st));
-    launch_linearize(P, G, st); if (n_obs) ++launches;
+    launch_linearize(P, d_tasks.p, n_tasks, d_long_lms.p, n_long, st); if (n_lms && L) launches += 1 + (n_tasks > 0) + (n_long > 0);
     CU(cudaEventRecord(ev[3], st));
     if (rank == 0) {   // replicated residuals are added once
       if (R.n_unary) {
@@ -850,7 +878,7 @@ struct bagpu_handle_s {
       if (f != 0) { summary.result = BAGPU_FactorizationError; return false; }
     }
     summary.result = BAGPU_Success;
-    if (n_al > 0) { launch_back_substitute(P, G, d_gn_p.p, d_gn_l.p, st); ++launches; }
+    if (n_al > 0) { launch_back_substitute(P, d_tasks.p, n_tasks, d_long_lms.p, n_long, d_gn_p.p, d_gn_l.p, st); launches += (n_tasks > 0) + (n_long > 0); }
     CU(cudaEventRecord(ev[9], st));
     sync();
     float ms; cudaEventElapsedTime(&ms, ev[8], ev[9]); phase_ms[BAGPU_PH_SOLVE] += ms;

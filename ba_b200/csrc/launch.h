@@ -82,11 +82,13 @@ void launch_pose_frames(const DeviceProblem& P, cudaStream_t st);
 void launch_prepare_xs(const DeviceProblem& P, const double* lm_xw, cudaStream_t st);
 void launch_finish_xw(const DeviceProblem& P, double* lm_xw, cudaStream_t st);
 void launch_residual(const DeviceProblem& P, int G, cudaStream_t st);
-void launch_linearize(const DeviceProblem& P, int G, cudaStream_t st);
+// packed tasks: (first observation, number of observations <= 32) of runs of whole landmarks; long_lms: landmarks with > 32 observations
+void launch_linearize(const DeviceProblem& P, const uint2* tasks, int n_tasks, const uint32_t* long_lms, int n_long, cudaStream_t st);
 void launch_reduce_blocks(const DeviceProblem& P, const ReduceItem* items, int n_items, const uint2* pairs, double* partial,
                           unsigned int* counters, unsigned int* next_item, cudaStream_t st);
 void launch_sd_denominator(const DeviceProblem& P, int G, cudaStream_t st);
-void launch_back_substitute(const DeviceProblem& P, int G, const double* delta_p, double* delta_l, cudaStream_t st);
+void launch_back_substitute(const DeviceProblem& P, const uint2* tasks, int n_tasks, const uint32_t* long_lms, int n_long, const double* delta_p,
+                            double* delta_l, cudaStream_t st);
 void launch_evaluate(const DeviceProblem& P, int G, double* out_sum, double* res_out, double* maha_out, int write_maha0, cudaStream_t st);
 void launch_update_poses(const DeviceProblem& P, const double* delta_p, double coef, cudaStream_t st);
 void launch_update_landmarks(const DeviceProblem& P, const double* delta_l, double coef, cudaStream_t st);

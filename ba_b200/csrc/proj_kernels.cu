@@ -65,21 +65,16 @@ __global__ void k_finish_xw(DeviceProblem P, double* lm_xw) {
 
 // ---------------------------------------------------------------------------------------
 // pass 1: residual -> maha0 = |r|^2 * orig_weight   (parallel_algos.h:143-150)
-template <int L, int G>
+// One thread per observation of the landmark-major stream (fully coalesced, every lane busy: with one lane group per
+// landmark only 13 of 32 lanes were active on a BAL-like track-length distribution).
+template <int L>
 __global__ void __launch_bounds__(256) k_residual(DeviceProblem P) {
-  const int lane = threadIdx.x & 31, gl = lane % G;
-  const int group = (blockIdx.x * blockDim.x + threadIdx.x) / G;
-  const int n_groups = (gridDim.x * blockDim.x) / G;
-  for (int lm = group; lm < P.n_lms; lm += n_groups) {
-    const int s = P.lm_obs_start[lm], e = P.lm_obs_start[lm + 1];
-    if (s == e) continue;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < P.n_obs; i += gridDim.x * blockDim.x) {
     LmCtx<L> c;
-    load_lm<L>(P, lm, c);
-    for (int i = s + gl; i < e; i += G) {
-      double r[2];
-      obs_residual<L>(P, c, i, r);
-      P.obs_maha0[i] = (r[0] * r[0] + r[1] * r[1]) * P.obs_w0[i];
-    }
+    load_lm<L>(P, (int)P.obs_lm[i], c);
+    double r[2];
+    obs_residual<L>(P, c, i, r);
+    P.obs_maha0[i] = (r[0] * r[0] + r[1] * r[1]) * P.obs_w0[i];
   }
 }
 
@@ -88,132 +83,158 @@ __global__ void __launch_bounds__(256) k_residual(DeviceProblem P) {
 
 // ---------------------------------------------------------------------------------------
 // steepest-descent denominator |J_p b_p + J_l b_l|^2 over projection residuals (cpp:879-906)
-template <int L, int G>
+template <int L>
 __global__ void __launch_bounds__(128) k_sd_denominator(DeviceProblem P) {
-  const int lane = threadIdx.x & 31, gl = lane % G;
-  const int group = (blockIdx.x * blockDim.x + threadIdx.x) / G;
-  const int n_groups = (gridDim.x * blockDim.x) / G;
   double acc = 0.0;
-  for (int lm = group; lm < P.n_lms; lm += n_groups) {
-    const int s = P.lm_obs_start[lm], e = P.lm_obs_start[lm + 1];
-    if (s == e) continue;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < P.n_obs; i += gridDim.x * blockDim.x) {
+    const int lm = (int)P.obs_lm[i];
     LmCtx<L> c;
     load_lm<L>(P, lm, c);
-    double bl[L];
+    ObsJac<L> o;
+    obs_jacobians<L>(P, c, i, o);
+    double v0 = 0.0, v1 = 0.0;
+    if (c.lm_opt >= 0) {
 #pragma unroll
-    for (int i = 0; i < L; ++i) bl[i] = (c.lm_opt >= 0) ? P.lm_bl[(size_t)lm * L + i] : 0.0;
-    for (int i = s + gl; i < e; i += G) {
-      ObsJac<L> o;
-      obs_jacobians<L>(P, c, i, o);
-      double v0 = 0.0, v1 = 0.0;
-#pragma unroll
-      for (int k = 0; k < L; ++k) { v0 += o.Jl[k] * bl[k]; v1 += o.Jl[L + k] * bl[k]; }
-      if (o.pm >= 0) {
-        const double* bp = P.b_p + (size_t)o.pm * P.D;
-#pragma unroll
-        for (int k = 0; k < 6; ++k) { v0 += o.Jm[k] * bp[k]; v1 += o.Jm[6 + k] * bp[k]; }
-      }
-      if (L == 1 && o.ref_on) {
-        const double* bp = P.b_p + (size_t)c.ref_opt * P.D;
-        double Jr[12];
-        ref_jacobian<L>(c, o.Bp, Jr);
-#pragma unroll
-        for (int k = 0; k < 6; ++k) { v0 += Jr[k] * bp[k]; v1 += Jr[6 + k] * bp[k]; }
-      }
-      acc += P.obs_w[i] * (v0 * v0 + v1 * v1);
+      for (int k = 0; k < L; ++k) { const double b = P.lm_bl[(size_t)lm * L + k]; v0 += o.Jl[k] * b; v1 += o.Jl[L + k] * b; }
     }
+    if (o.pm >= 0) {
+      const double* bp = P.b_p + (size_t)o.pm * P.D;
+#pragma unroll
+      for (int k = 0; k < 6; ++k) { v0 += o.Jm[k] * bp[k]; v1 += o.Jm[6 + k] * bp[k]; }
+    }
+    if (L == 1 && o.ref_on) {
+      const double* bp = P.b_p + (size_t)c.ref_opt * P.D;
+      double Jr[12];
+      ref_jacobian<L>(c, o.Bp, Jr);
+#pragma unroll
+      for (int k = 0; k < 6; ++k) { v0 += Jr[k] * bp[k]; v1 += Jr[6 + k] * bp[k]; }
+    }
+    acc += P.obs_w[i] * (v0 * v0 + v1 * v1);
   }
   acc = warp_sum(acc);
-  if (lane == 0) red_add(&P.sc->sd_den_proj, acc);
+  if ((threadIdx.x & 31) == 0) red_add(&P.sc->sd_den_proj, acc);
 }
 
 // ---------------------------------------------------------------------------------------
 // back-substitution: delta_l = V^-1 (b_l - W^T delta_p)   (cpp:709-744), from the pose-major
 // records: V^-1 W_a^T delta = C_a^T (At_a delta) for LmSize 3, E_a . delta for LmSize 1
-template <int L, int G>
-__global__ void __launch_bounds__(256) k_back_substitute(DeviceProblem P, const double* delta_p, double* delta_l) {
-  const int lane = threadIdx.x & 31, gl = lane % G;
-  const unsigned gmask = group_mask<G>(lane);
-  const int group = (blockIdx.x * blockDim.x + threadIdx.x) / G;
-  const int n_groups = (gridDim.x * blockDim.x) / G;
-  for (int lm = group; lm < P.n_lms; lm += n_groups) {
+// share of one observation: V^-1 W_a^T delta_p(a)
+template <int L>
+BA_D void back_term(const DeviceProblem& P, int i, const double* delta_p, double* acc) {
+  const uint32_t slot = P.obs_slot[i];
+  if (slot == kNoSlot) return;
+  const double* r = P.rec + (size_t)slot * P.rec_stride;
+  const double* dp = delta_p + (size_t)P.pose_opt[P.obs_pose[i]] * P.D;
+  if (L == 3) {
+    double t0 = 0.0, t1 = 0.0;
+#pragma unroll
+    for (int a = 0; a < 6; ++a) { t0 += r[6 + a] * dp[a]; t1 += r[12 + a] * dp[a]; }
+#pragma unroll
+    for (int k = 0; k < L; ++k) acc[k] += r[k] * t0 + r[3 + k] * t1;
+  } else {
+#pragma unroll
+    for (int a = 0; a < 6; ++a) acc[0] += r[a] * dp[a];
+  }
+}
+// landmark part and write-out, by one lane holding the landmark's sum
+template <int L>
+BA_D void back_finish(const DeviceProblem& P, int lm, int lo, const double* delta_p, double* acc, double* delta_l) {
+  if (L == 1) {
+    const int ro = P.pose_opt[P.lm_ref_pose[lm]];
+    if (ro >= 0) {
+      const double* W = P.lm_Wref + (size_t)lm * 6;
+      const double* dp = delta_p + (size_t)ro * P.D;
+      double t = 0.0;
+#pragma unroll
+      for (int a = 0; a < 6; ++a) t += W[a] * dp[a];
+      acc[0] += P.lm_Vinv[lm] * t;
+    }
+  }
+#pragma unroll
+  for (int k = 0; k < L; ++k) delta_l[(size_t)lo * L + k] = P.lm_dhat[(size_t)lm * L + k] - acc[k];
+}
+
+// packed tasks (see k_linearize_packed): one observation per lane, segmented sum over the lanes of a landmark
+template <int L>
+__global__ void __launch_bounds__(256) k_back_substitute_packed(DeviceProblem P, const uint2* __restrict__ tasks, int n_tasks,
+                                                                const double* delta_p, double* delta_l) {
+  const int lane = threadIdx.x & 31;
+  const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, n_warps = (gridDim.x * blockDim.x) >> 5;
+  for (int t = warp; t < n_tasks; t += n_warps) {
+    const uint2 tk = tasks[t];
+    const int s = (int)tk.x, n = (int)tk.y;
+    const bool on = lane < n;
+    const int i = s + (on ? lane : 0);
+    const int lm = (int)P.obs_lm[i];
+    const int lm_prev = __shfl_up_sync(0xffffffffu, lm, 1);
+    const bool head = on && (lane == 0 || lm != lm_prev);
+    const unsigned heads = __ballot_sync(0xffffffffu, head);
+    const unsigned above = (lane == 31) ? 0u : (heads & (0xffffffffu << (lane + 1)));
+    const int seg_end = above ? (__ffs(above) - 1) : n;
+    const int lo = P.lm_opt[lm];
+    double acc[L];
+#pragma unroll
+    for (int k = 0; k < L; ++k) acc[k] = 0.0;
+    if (on && lo >= 0) back_term<L>(P, i, delta_p, acc);
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+      const bool take = on && (lane + d < seg_end);
+#pragma unroll
+      for (int k = 0; k < L; ++k) {
+        const double other = __shfl_down_sync(0xffffffffu, acc[k], d);
+        if (take) acc[k] += other;
+      }
+    }
+    if (head && lo >= 0) back_finish<L>(P, lm, lo, delta_p, acc, delta_l);
+  }
+}
+
+// landmarks with more than 32 observations: one warp per landmark
+template <int L>
+__global__ void __launch_bounds__(256) k_back_substitute_long(DeviceProblem P, const uint32_t* __restrict__ lm_list, int n_list,
+                                                              const double* delta_p, double* delta_l) {
+  const int lane = threadIdx.x & 31;
+  const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, n_warps = (gridDim.x * blockDim.x) >> 5;
+  for (int q = warp; q < n_list; q += n_warps) {
+    const int lm = (int)lm_list[q];
     const int lo = P.lm_opt[lm];
     if (lo < 0) continue;
     const int s = P.lm_obs_start[lm], e = P.lm_obs_start[lm + 1];
     double acc[L];
 #pragma unroll
     for (int k = 0; k < L; ++k) acc[k] = 0.0;
-    for (int i = s + gl; i < e; i += G) {
-      const uint32_t slot = P.obs_slot[i];
-      if (slot == kNoSlot) continue;
-      const double* r = P.rec + (size_t)slot * P.rec_stride;
-      const double* dp = delta_p + (size_t)P.pose_opt[P.obs_pose[i]] * P.D;
-      if (L == 3) {
-        double t0 = 0.0, t1 = 0.0;
+    for (int i = s + lane; i < e; i += 32) back_term<L>(P, i, delta_p, acc);
 #pragma unroll
-        for (int a = 0; a < 6; ++a) { t0 += r[6 + a] * dp[a]; t1 += r[12 + a] * dp[a]; }
-#pragma unroll
-        for (int k = 0; k < L; ++k) acc[k] += r[k] * t0 + r[3 + k] * t1;
-      } else {
-#pragma unroll
-        for (int a = 0; a < 6; ++a) acc[0] += r[a] * dp[a];
-      }
-    }
-#pragma unroll
-    for (int k = 0; k < L; ++k) acc[k] = group_sum<G>(acc[k], gmask);
-    if (gl == 0) {
-      if (L == 1) {
-        const int ro = P.pose_opt[P.lm_ref_pose[lm]];
-        if (ro >= 0) {
-          const double* W = P.lm_Wref + (size_t)lm * 6;
-          const double* dp = delta_p + (size_t)ro * P.D;
-          double t = 0.0;
-#pragma unroll
-          for (int a = 0; a < 6; ++a) t += W[a] * dp[a];
-          acc[0] += P.lm_Vinv[lm] * t;
-        }
-      }
-#pragma unroll
-      for (int k = 0; k < L; ++k) delta_l[(size_t)lo * L + k] = P.lm_dhat[(size_t)lm * L + k] - acc[k];
-    }
+    for (int k = 0; k < L; ++k) acc[k] = warp_sum(acc[k]);
+    if (lane == 0) back_finish<L>(P, lm, lo, delta_p, acc, delta_l);
   }
 }
 
 // ---------------------------------------------------------------------------------------
 // residual-only evaluation with the current Huber weights (cpp:148-188)
-template <int L, int G>
+template <int L>
 __global__ void __launch_bounds__(256) k_evaluate(DeviceProblem P, double* out_sum, double* res_out, double* maha_out, int write_maha0) {
-  const int lane = threadIdx.x & 31, gl = lane % G;
-  const int group = (blockIdx.x * blockDim.x + threadIdx.x) / G;
-  const int n_groups = (gridDim.x * blockDim.x) / G;
   double acc = 0.0;
-  const double thr2 = P.outlier_threshold * P.outlier_threshold;
-  for (int lm = group; lm < P.n_lms; lm += n_groups) {
-    const int s = P.lm_obs_start[lm], e = P.lm_obs_start[lm + 1];
-    if (s == e) continue;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < P.n_obs; i += gridDim.x * blockDim.x) {
+    const int lm = (int)P.obs_lm[i];
     LmCtx<L> c;
     load_lm<L>(P, lm, c);
-    unsigned n_out = 0;
-    for (int i = s + gl; i < e; i += G) {
-      double r[2];
-      obs_residual<L>(P, c, i, r);
-      const double n2 = r[0] * r[0] + r[1] * r[1];
-      const double m = n2 * P.obs_w[i];
-      acc += m;
-      // the next BuildProblem starts from this state if the step is accepted: its median input, for free
-      if (write_maha0) P.obs_maha0[i] = n2 * P.obs_w0[i];
-      if (sqrt(n2) > P.outlier_threshold) ++n_out;
-      if (res_out) {
-        const uint32_t id = P.obs_perm[i];
-        res_out[2 * (size_t)id] = r[0]; res_out[2 * (size_t)id + 1] = r[1];
-        maha_out[id] = m;
-      }
+    double r[2];
+    obs_residual<L>(P, c, i, r);
+    const double n2 = r[0] * r[0] + r[1] * r[1];
+    const double m = n2 * P.obs_w[i];
+    acc += m;
+    // the next BuildProblem starts from this state if the step is accepted: its median input, for free
+    if (write_maha0) P.obs_maha0[i] = n2 * P.obs_w0[i];
+    if (sqrt(n2) > P.outlier_threshold) atomicAdd(&P.lm_outliers[lm], 1u);   // cpp:184-186
+    if (res_out) {
+      const uint32_t id = P.obs_perm[i];
+      res_out[2 * (size_t)id] = r[0]; res_out[2 * (size_t)id + 1] = r[1];
+      maha_out[id] = m;
     }
-    if (n_out) atomicAdd(&P.lm_outliers[lm], n_out);
   }
-  (void)thr2;
   acc = warp_sum(acc);
-  if (lane == 0) red_add(out_sum, acc);
+  if ((threadIdx.x & 31) == 0) red_add(out_sum, acc);
 }
 
 // ---------------------------------------------------------------------------------------
@@ -345,32 +366,37 @@ void launch_finish_xw(const DeviceProblem& P, double* lm_xw, cudaStream_t st) {
 }
 void launch_residual(const DeviceProblem& P, int G, cudaStream_t st) {
   if (P.n_obs == 0) return;
-  const int grid = grid_for((size_t)P.n_lms * G, 256, 8);
-#define CALL(LL, GG) k_residual<LL, GG><<<grid, 256, 0, st>>>(P)
-  DISPATCH_LG(P.L, G, CALL);
-#undef CALL
+  (void)G;
+  const int grid = grid_for((size_t)P.n_obs, 256, 8);
+  if (P.L == 1) k_residual<1><<<grid, 256, 0, st>>>(P); else k_residual<3><<<grid, 256, 0, st>>>(P);
 }
 void launch_sd_denominator(const DeviceProblem& P, int G, cudaStream_t st) {
   if (P.n_obs == 0) return;
-  const int grid = grid_for((size_t)P.n_lms * G, 128, 12);
-#define CALL(LL, GG) k_sd_denominator<LL, GG><<<grid, 128, 0, st>>>(P)
-  DISPATCH_LG(P.L, G, CALL);
-#undef CALL
+  (void)G;
+  const int grid = grid_for((size_t)P.n_obs, 128, 12);
+  if (P.L == 1) k_sd_denominator<1><<<grid, 128, 0, st>>>(P); else k_sd_denominator<3><<<grid, 128, 0, st>>>(P);
 }
-void launch_back_substitute(const DeviceProblem& P, int G, const double* delta_p, double* delta_l, cudaStream_t st) {
+void launch_back_substitute(const DeviceProblem& P, const uint2* tasks, int n_tasks, const uint32_t* long_lms, int n_long, const double* delta_p,
+                            double* delta_l, cudaStream_t st) {
   if (P.n_active_lms == 0) return;
-  const int grid = grid_for((size_t)P.n_lms * G, 256, 8);
-#define CALL(LL, GG) k_back_substitute<LL, GG><<<grid, 256, 0, st>>>(P, delta_p, delta_l)
-  DISPATCH_LG(P.L, G, CALL);
-#undef CALL
+  if (n_tasks > 0) {
+    const int grid = grid_for((size_t)n_tasks * 32, 256, 8);
+    if (P.L == 1) k_back_substitute_packed<1><<<grid, 256, 0, st>>>(P, tasks, n_tasks, delta_p, delta_l);
+    else k_back_substitute_packed<3><<<grid, 256, 0, st>>>(P, tasks, n_tasks, delta_p, delta_l);
+  }
+  if (n_long > 0) {
+    const int grid = grid_for((size_t)n_long * 32, 256, 8);
+    if (P.L == 1) k_back_substitute_long<1><<<grid, 256, 0, st>>>(P, long_lms, n_long, delta_p, delta_l);
+    else k_back_substitute_long<3><<<grid, 256, 0, st>>>(P, long_lms, n_long, delta_p, delta_l);
+  }
 }
 void launch_evaluate(const DeviceProblem& P, int G, double* out_sum, double* res_out, double* maha_out, int write_maha0, cudaStream_t st) {
   if (P.n_obs == 0) return;
   cudaMemsetAsync(P.lm_outliers, 0, sizeof(uint32_t) * P.n_lms, st);
-  const int grid = grid_for((size_t)P.n_lms * G, 256, 8);
-#define CALL(LL, GG) k_evaluate<LL, GG><<<grid, 256, 0, st>>>(P, out_sum, res_out, maha_out, write_maha0)
-  DISPATCH_LG(P.L, G, CALL);
-#undef CALL
+  (void)G;
+  const int grid = grid_for((size_t)P.n_obs, 256, 8);
+  if (P.L == 1) k_evaluate<1><<<grid, 256, 0, st>>>(P, out_sum, res_out, maha_out, write_maha0);
+  else k_evaluate<3><<<grid, 256, 0, st>>>(P, out_sum, res_out, maha_out, write_maha0);
 }
 void launch_update_poses(const DeviceProblem& P, const double* delta_p, double coef, cudaStream_t st) {
   if (P.n_poses == 0) return;

@@ -22,6 +22,7 @@
 //       bit-reproducible run to run.
 // The pair lists depend only on the ids; they are built once per Solve() on the device
 // (symbolic.cu).
+#include <algorithm>
 #include "proj_kernels.cuh"
 #include "launch.h"
 
@@ -32,47 +33,211 @@ BA_D void ld2(const double* p, double& a, double& b) { const double2 v = *reinte
 
 // ---------------------------------------------------------------------------------------
 // pass A
-template <int L, int G>
-__global__ void __launch_bounds__(128, (L == 1) ? 3 : 4) k_linearize(DeviceProblem P) {
-  constexpr int NV = L * (L + 1) / 2;
-  const int lane = threadIdx.x & 31, gl = lane % G;
-  const unsigned gmask = group_mask<G>(lane);
-  const int group = (blockIdx.x * blockDim.x + threadIdx.x) / G;
-  const int n_groups = (gridDim.x * blockDim.x) / G;
+// Running sums of one landmark over its observations.  LmSize 1: the reference-pose Jacobian of every observation of
+// the landmark is Bp M with the same 3 x 6 M = [-rho I | Ar], so H_rr = M^T (sum w Bp^T Bp) M, g_r = M^T sum w Bp^T r,
+// W_r = M^T sum w Bp^T J_l: 12 running sums instead of 33.
+template <int L> struct LmSums {
+  static constexpr int NV = L * (L + 1) / 2;
+  static constexpr int N = NV + L + (L == 1 ? 12 : 0);
+  double v[N];   // V (upper, NV) | b_l (L) | LmSize 1: SBB (6) | SBr (3) | SBl (3)
+};
+
+template <int L>
+BA_D void sums_add(LmSums<L>& S, const ObsJac<L>& o, double w, bool lm_on) {
+  constexpr int NV = LmSums<L>::NV;
+  const double wr0 = w * o.r[0], wr1 = w * o.r[1];
+  if (lm_on) {
+    int k = 0;
+#pragma unroll
+    for (int a = 0; a < L; ++a) {
+#pragma unroll
+      for (int b = a; b < L; ++b) { S.v[k] += w * (o.Jl[a] * o.Jl[b] + o.Jl[L + a] * o.Jl[L + b]); ++k; }
+      S.v[NV + a] += o.Jl[a] * wr0 + o.Jl[L + a] * wr1;
+    }
+  }
+  if (L == 1 && o.ref_on) {
+    double* SBB = S.v + NV + L; double* SBr = SBB + 6; double* SBl = SBr + 3;
+    int k = 0;
+#pragma unroll
+    for (int a = 0; a < 3; ++a) {
+#pragma unroll
+      for (int b = a; b < 3; ++b) { SBB[k] += w * (o.Bp[a] * o.Bp[b] + o.Bp[3 + a] * o.Bp[3 + b]); ++k; }
+      SBr[a] += o.Bp[a] * wr0 + o.Bp[3 + a] * wr1;
+      if (lm_on) SBl[a] += w * (o.Bp[a] * o.Jl[0] + o.Bp[3 + a] * o.Jl[1]);
+    }
+  }
+}
+
+// From the complete sums of a landmark: V^-1 (cpp:431-442), dhat = V^-1 b_l, LmSize 1 W_r and the reference-pose
+// record.  Every lane that holds the sums computes Vi / dhat / Wr (it needs them for its own record); the landmark's
+// outputs are written by the lanes with `writer` set, element k of the reference-pose record by the lane with
+// k % MOD == rem.
+template <int L, int MOD>
+BA_D void lm_finalize(const DeviceProblem& P, int lm, const LmCtx<L>& c, bool lm_on, const LmSums<L>& S, double* Vi, double* dhat, double* Wr,
+                      bool writer, int rem) {
+  constexpr int NV = LmSums<L>::NV;
+  const double* V = S.v;
+  double bl[L];
+#pragma unroll
+  for (int i = 0; i < L; ++i) bl[i] = lm_on ? S.v[NV + i] : 0.0;
+  if (lm_on) {
+    if (L == 1) {
+      double v = V[0];
+      if (fabs(v) < 1e-6) v += 1e-6;
+      Vi[0] = 1.0 / v;
+    } else {
+      double M[9] = {V[0], V[1], V[2], V[1], V[3], V[4], V[2], V[4], V[5]};
+      double n2 = 0.0;
+#pragma unroll
+      for (int i = 0; i < 9; ++i) n2 += M[i] * M[i];
+      if (sqrt(n2) < 1e-6) { M[0] += 1e-6; M[4] += 1e-6; M[8] += 1e-6; }
+      double Mi[9];
+      inv3(M, Mi);
+#pragma unroll
+      for (int i = 0; i < L * L; ++i) Vi[i] = Mi[i];
+    }
+  } else {
+#pragma unroll
+    for (int i = 0; i < L * L; ++i) Vi[i] = 0.0;
+  }
+#pragma unroll
+  for (int r = 0; r < L; ++r) {
+    double v = 0.0;
+#pragma unroll
+    for (int k = 0; k < L; ++k) v += Vi[r * L + k] * bl[k];
+    dhat[r] = v;
+  }
+  if (L == 1) {
+    const uint32_t rslot = P.lm_rslot[lm];
+#pragma unroll
+    for (int i = 0; i < 6; ++i) Wr[i] = 0.0;
+    if (rslot != kNoSlot) {
+      const double* SBB = S.v + NV + L; const double* SBr = SBB + 6; const double* SBl = SBr + 3;
+      double M[18];   // 3 x 6 row-major, masked parameter columns zeroed
+#pragma unroll
+      for (int j = 0; j < 3; ++j)
+#pragma unroll
+        for (int k = 0; k < 3; ++k) { M[6 * j + k] = (j == k) ? -c.rho : 0.0; M[6 * j + 3 + k] = c.Ar[3 * j + k]; }
+      if ((c.ref_free & 63u) != 63u) {
+#pragma unroll
+        for (int k = 0; k < 6; ++k)
+          if (!((c.ref_free >> k) & 1u)) { M[k] = 0.0; M[6 + k] = 0.0; M[12 + k] = 0.0; }
+      }
+      const double S3[9] = {SBB[0], SBB[1], SBB[2], SBB[1], SBB[3], SBB[4], SBB[2], SBB[4], SBB[5]};
+      double TM[18];  // S3 M
+#pragma unroll
+      for (int j = 0; j < 3; ++j)
+#pragma unroll
+        for (int k = 0; k < 6; ++k) TM[6 * j + k] = S3[3 * j] * M[k] + S3[3 * j + 1] * M[6 + k] + S3[3 * j + 2] * M[12 + k];
+      double gr[6];
+#pragma unroll
+      for (int k = 0; k < 6; ++k) {
+        gr[k] = M[k] * SBr[0] + M[6 + k] * SBr[1] + M[12 + k] * SBr[2];
+        Wr[k] = M[k] * SBl[0] + M[6 + k] * SBl[1] + M[12 + k] * SBl[2];
+      }
+      // reference-pose record: H_rr - W_r V^-1 W_r^T (upper) | g_r | g_r - W_r dhat
+      double* o = P.lm_rec + (size_t)rslot * kLmRec;
+      int k = 0;
+#pragma unroll
+      for (int b = 0; b < 6; ++b)
+#pragma unroll
+        for (int a = 0; a <= b; ++a) {
+          if (writer && (k % MOD) == rem) o[k] = (M[a] * TM[b] + M[6 + a] * TM[6 + b] + M[12 + a] * TM[12 + b]) - Vi[0] * Wr[a] * Wr[b];
+          ++k;
+        }
+#pragma unroll
+      for (int a = 0; a < 6; ++a)
+        if (writer && ((21 + a) % MOD) == rem) { o[21 + a] = gr[a]; o[27 + a] = gr[a] - Wr[a] * dhat[0]; }
+    }
+    if (writer && rem == 0) {
+#pragma unroll
+      for (int a = 0; a < 6; ++a) P.lm_Wref[(size_t)lm * 6 + a] = Wr[a];
+    }
+  }
+  if (writer && rem == 0) {
+#pragma unroll
+    for (int i = 0; i < L * L; ++i) P.lm_Vinv[(size_t)lm * L * L + i] = Vi[i];
+#pragma unroll
+    for (int i = 0; i < L; ++i) { P.lm_bl[(size_t)lm * L + i] = bl[i]; P.lm_dhat[(size_t)lm * L + i] = dhat[i]; }
+  }
+}
+
+// the pose-major record of one observation (ba_gpu.h), written once its landmark's V^-1, dhat (and W_r) are known
+template <int L>
+BA_D void emit_record(double* out, const LmCtx<L>& c, const ObsJac<L>& o, double w, bool lm_on, const double* Vi, const double* dhat,
+                      const double* Wr) {
+  const double sw = sqrt(w);
+  double A[12], B[2 * L];
+#pragma unroll
+  for (int k = 0; k < 12; ++k) A[k] = sw * o.Jm[k];
+#pragma unroll
+  for (int k = 0; k < 2 * L; ++k) B[k] = sw * o.Jl[k];
+  const double r0 = sw * o.r[0], r1 = sw * o.r[1];
+  if (L == 3) {
+    double C[6];
+#pragma unroll
+    for (int rr = 0; rr < 2; ++rr)
+#pragma unroll
+      for (int cc = 0; cc < 3; ++cc) C[rr * 3 + cc] = B[rr * 3] * Vi[cc] + B[rr * 3 + 1] * Vi[3 + cc] + B[rr * 3 + 2] * Vi[6 + cc];
+    const double p0 = r0 - (B[0] * dhat[0] + B[1] * dhat[1] + B[2] * dhat[2]);
+    const double p1 = r1 - (B[3] * dhat[0] + B[4] * dhat[1] + B[5] * dhat[2]);
+#pragma unroll
+    for (int k = 0; k < 3; ++k) st2(out + 2 * k, C[2 * k], C[2 * k + 1]);
+#pragma unroll
+    for (int k = 0; k < 6; ++k) st2(out + 6 + 2 * k, A[2 * k], A[2 * k + 1]);
+#pragma unroll
+    for (int k = 0; k < 3; ++k) st2(out + 18 + 2 * k, lm_on ? B[2 * k] : 0.0, lm_on ? B[2 * k + 1] : 0.0);
+    st2(out + 24, r0, r1);
+    st2(out + 26, p0, p1);
+  } else {
+    const double bv0 = lm_on ? B[0] : 0.0, bv1 = lm_on ? B[1] : 0.0;
+    double W[6], Q[12];
+#pragma unroll
+    for (int k = 0; k < 6; ++k) W[k] = A[k] * bv0 + A[6 + k] * bv1;
+    const double c0 = bv0 * Vi[0], c1 = bv1 * Vi[0];
+    if (o.ref_on) {
+      ref_jacobian<L>(c, o.Bp, Q);
+#pragma unroll
+      for (int k = 0; k < 6; ++k) { Q[k] = sw * Q[k] - c0 * Wr[k]; Q[6 + k] = sw * Q[6 + k] - c1 * Wr[k]; }
+    } else {
+#pragma unroll
+      for (int k = 0; k < 12; ++k) Q[k] = 0.0;
+    }
+    const double p0 = r0 - bv0 * dhat[0], p1 = r1 - bv1 * dhat[0];
+#pragma unroll
+    for (int k = 0; k < 3; ++k) st2(out + 2 * k, W[2 * k] * Vi[0], W[2 * k + 1] * Vi[0]);
+#pragma unroll
+    for (int k = 0; k < 3; ++k) st2(out + 6 + 2 * k, W[2 * k], W[2 * k + 1]);
+#pragma unroll
+    for (int k = 0; k < 6; ++k) st2(out + 12 + 2 * k, A[2 * k], A[2 * k + 1]);
+#pragma unroll
+    for (int k = 0; k < 6; ++k) st2(out + 24 + 2 * k, Q[2 * k], Q[2 * k + 1]);
+    st2(out + 36, r0, r1);
+    st2(out + 38, p0, p1);
+  }
+}
+
+// Landmarks with more than 32 observations (lm_list): one warp per landmark, lanes stride over the track.  Two sweeps:
+// weights and sums, then the records (the lane's last observation keeps its Jacobians in registers).
+template <int L>
+__global__ void __launch_bounds__(128, (L == 1) ? 3 : 4) k_linearize_long(DeviceProblem P, const uint32_t* __restrict__ lm_list, int n_list) {
+  const int lane = threadIdx.x & 31;
+  const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, n_warps = (gridDim.x * blockDim.x) >> 5;
   const double c_huber = P.c_huber_factor * sqrt(P.sc->median);
   double err = 0.0;
-  // the CSR bounds of the NEXT landmark of the group are requested one landmark ahead (the walk is a chain of
-  // dependent round trips: bounds -> pose id -> pose frame -> slot; each one taken off the chain is ~1 us per landmark)
-  int s_n = 0, e_n = 0;
-  if (group < P.n_lms) { s_n = P.lm_obs_start[group]; e_n = P.lm_obs_start[group + 1]; }
-  for (int lm = group; lm < P.n_lms; lm += n_groups) {
-    const int s = s_n, e = e_n;
-    if (lm + n_groups < P.n_lms) { s_n = P.lm_obs_start[lm + n_groups]; e_n = P.lm_obs_start[lm + n_groups + 1]; }
+  for (int q = warp; q < n_list; q += n_warps) {
+    const int lm = (int)lm_list[q];
+    const int s = P.lm_obs_start[lm], e = P.lm_obs_start[lm + 1];
     LmCtx<L> c;
     load_lm<L>(P, lm, c);
     const bool lm_on = c.lm_opt >= 0;
-    double V[NV], bl[L];
+    LmSums<L> S;
 #pragma unroll
-    for (int i = 0; i < NV; ++i) V[i] = 0.0;
-#pragma unroll
-    for (int i = 0; i < L; ++i) bl[i] = 0.0;
-    // LmSize 1: the reference-pose Jacobian of every observation of the landmark is Bp M with the same 3 x 6
-    // M = [-rho I | Ar], so H_rr = M^T (sum w Bp^T Bp) M, g_r = M^T sum w Bp^T r, W_r = M^T sum w Bp^T J_l:
-    // 12 running sums instead of 33
-    double SBB[L == 1 ? 6 : 1], SBr[L == 1 ? 3 : 1], SBl[L == 1 ? 3 : 1], Wr[L == 1 ? 6 : 1];
-    if (L == 1) {
-#pragma unroll
-      for (int i = 0; i < 6; ++i) SBB[i] = 0.0;
-#pragma unroll
-      for (int i = 0; i < 3; ++i) { SBr[i] = 0.0; SBl[i] = 0.0; }
-    }
-    // ---- sweep 1: weights and the landmark sums ---------------------------------------
-    ObsJac<L> o;              // the Jacobians of the lane's LAST observation stay in registers for sweep 2
+    for (int i = 0; i < LmSums<L>::N; ++i) S.v[i] = 0.0;
+    ObsJac<L> o;
     double w_keep = 0.0;
     int i_keep = -1;
-    uint32_t slot_keep = kNoSlot;
-    for (int i = s + gl; i < e; i += G) {
-      slot_keep = P.obs_slot[i];   // needed only in sweep 2: requested here, off the dependent chain
+    for (int i = s + lane; i < e; i += 32) {
       obs_jacobians<L>(P, c, i, o);
       const double w0 = P.obs_w0[i];
       const double n2 = o.r[0] * o.r[0] + o.r[1] * o.r[1];
@@ -80,180 +245,117 @@ __global__ void __launch_bounds__(128, (L == 1) ? 3 : 4) k_linearize(DeviceProbl
       P.obs_w[i] = w;
       w_keep = w; i_keep = i;
       err += n2 * w;
-      if (lm_on) {
-        const double wr0 = w * o.r[0], wr1 = w * o.r[1];
-        int k = 0;
-#pragma unroll
-        for (int a = 0; a < L; ++a) {
-#pragma unroll
-          for (int b = a; b < L; ++b) { V[k] += w * (o.Jl[a] * o.Jl[b] + o.Jl[L + a] * o.Jl[L + b]); ++k; }
-          bl[a] += o.Jl[a] * wr0 + o.Jl[L + a] * wr1;
-        }
-      }
-      if (L == 1 && o.ref_on) {
-        const double wr0 = w * o.r[0], wr1 = w * o.r[1];
-        int k = 0;
-#pragma unroll
-        for (int a = 0; a < 3; ++a) {
-#pragma unroll
-          for (int b = a; b < 3; ++b) { SBB[k] += w * (o.Bp[a] * o.Bp[b] + o.Bp[3 + a] * o.Bp[3 + b]); ++k; }
-          SBr[a] += o.Bp[a] * wr0 + o.Bp[3 + a] * wr1;
-          if (lm_on) SBl[a] += w * (o.Bp[a] * o.Jl[0] + o.Bp[3 + a] * o.Jl[1]);
-        }
-      }
+      sums_add<L>(S, o, w, lm_on);
     }
 #pragma unroll
-    for (int i = 0; i < NV; ++i) V[i] = group_sum<G>(V[i], gmask);
-#pragma unroll
-    for (int i = 0; i < L; ++i) bl[i] = group_sum<G>(bl[i], gmask);
-    // V^-1 (cpp:431-442) and dhat = V^-1 b_l, redundantly in every lane of the group
-    double Vi[L * L], dhat[L];
-    if (lm_on) {
-      if (L == 1) {
-        double v = V[0];
-        if (fabs(v) < 1e-6) v += 1e-6;
-        Vi[0] = 1.0 / v;
-      } else {
-        double M[9] = {V[0], V[1], V[2], V[1], V[3], V[4], V[2], V[4], V[5]};
-        double n2 = 0.0;
-#pragma unroll
-        for (int i = 0; i < 9; ++i) n2 += M[i] * M[i];
-        if (sqrt(n2) < 1e-6) { M[0] += 1e-6; M[4] += 1e-6; M[8] += 1e-6; }
-        double Mi[9];
-        inv3(M, Mi);
-#pragma unroll
-        for (int i = 0; i < L * L; ++i) Vi[i] = Mi[i];
-      }
-    } else {
-#pragma unroll
-      for (int i = 0; i < L * L; ++i) Vi[i] = 0.0;
-#pragma unroll
-      for (int i = 0; i < L; ++i) bl[i] = 0.0;
-    }
-#pragma unroll
-    for (int r = 0; r < L; ++r) {
-      double v = 0.0;
-#pragma unroll
-      for (int k = 0; k < L; ++k) v += Vi[r * L + k] * bl[k];
-      dhat[r] = v;
-    }
-    if (L == 1) {
-      const uint32_t rslot = P.lm_rslot[lm];
-      if (rslot != kNoSlot) {
-#pragma unroll
-        for (int i = 0; i < 6; ++i) SBB[i] = group_sum<G>(SBB[i], gmask);
-#pragma unroll
-        for (int i = 0; i < 3; ++i) { SBr[i] = group_sum<G>(SBr[i], gmask); SBl[i] = group_sum<G>(SBl[i], gmask); }
-        double M[18];   // 3 x 6 row-major, masked parameter columns zeroed
-#pragma unroll
-        for (int j = 0; j < 3; ++j)
-#pragma unroll
-          for (int k = 0; k < 3; ++k) { M[6 * j + k] = (j == k) ? -c.rho : 0.0; M[6 * j + 3 + k] = c.Ar[3 * j + k]; }
-        if ((c.ref_free & 63u) != 63u) {
-#pragma unroll
-          for (int k = 0; k < 6; ++k)
-            if (!((c.ref_free >> k) & 1u)) { M[k] = 0.0; M[6 + k] = 0.0; M[12 + k] = 0.0; }
-        }
-        const double S3[9] = {SBB[0], SBB[1], SBB[2], SBB[1], SBB[3], SBB[4], SBB[2], SBB[4], SBB[5]};
-        double TM[18];  // S3 M
-#pragma unroll
-        for (int j = 0; j < 3; ++j)
-#pragma unroll
-          for (int k = 0; k < 6; ++k) TM[6 * j + k] = S3[3 * j] * M[k] + S3[3 * j + 1] * M[6 + k] + S3[3 * j + 2] * M[12 + k];
-        double gr[6];
-#pragma unroll
-        for (int k = 0; k < 6; ++k) {
-          gr[k] = M[k] * SBr[0] + M[6 + k] * SBr[1] + M[12 + k] * SBr[2];
-          Wr[k] = M[k] * SBl[0] + M[6 + k] * SBl[1] + M[12 + k] * SBl[2];
-        }
-        // reference-pose record: H_rr - W_r V^-1 W_r^T (upper) | g_r | g_r - W_r dhat, spread over the lanes
-        double* o = P.lm_rec + (size_t)rslot * kLmRec;
-        int k = 0;
-#pragma unroll
-        for (int b = 0; b < 6; ++b)
-#pragma unroll
-          for (int a = 0; a <= b; ++a) {
-            if ((k % G) == gl) o[k] = (M[a] * TM[b] + M[6 + a] * TM[6 + b] + M[12 + a] * TM[12 + b]) - Vi[0] * Wr[a] * Wr[b];
-            ++k;
-          }
-#pragma unroll
-        for (int a = 0; a < 6; ++a)
-          if (((21 + a) % G) == gl) { o[21 + a] = gr[a]; o[27 + a] = gr[a] - Wr[a] * dhat[0]; }
-      } else {
-#pragma unroll
-        for (int i = 0; i < 6; ++i) Wr[i] = 0.0;
-      }
-      if (gl == 0) {
-#pragma unroll
-        for (int a = 0; a < 6; ++a) P.lm_Wref[(size_t)lm * 6 + a] = Wr[a];
-      }
-    }
-    if (gl == 0) {
-#pragma unroll
-      for (int i = 0; i < L * L; ++i) P.lm_Vinv[(size_t)lm * L * L + i] = Vi[i];
-#pragma unroll
-      for (int i = 0; i < L; ++i) { P.lm_bl[(size_t)lm * L + i] = bl[i]; P.lm_dhat[(size_t)lm * L + i] = dhat[i]; }
-    }
-    // ---- sweep 2: one pose-major record per observation, last observation first (most tracks are not
-    // longer than G, so most records are written without evaluating the Jacobians a second time) ----
-    for (int i = i_keep; i >= s; i -= G) {
-      const uint32_t slot = (i == i_keep) ? slot_keep : P.obs_slot[i];
+    for (int i = 0; i < LmSums<L>::N; ++i) S.v[i] = warp_sum(S.v[i]);
+    double Vi[L * L], dhat[L], Wr[6];
+    lm_finalize<L, 32>(P, lm, c, lm_on, S, Vi, dhat, Wr, true, lane);
+    for (int i = i_keep; i >= s; i -= 32) {
+      const uint32_t slot = P.obs_slot[i];
       if (slot == kNoSlot) continue;
       if (i != i_keep) { obs_jacobians<L>(P, c, i, o); w_keep = P.obs_w[i]; }
-      const double sw = sqrt(w_keep);
-      double A[12], B[2 * L];
-#pragma unroll
-      for (int k = 0; k < 12; ++k) A[k] = sw * o.Jm[k];
-#pragma unroll
-      for (int k = 0; k < 2 * L; ++k) B[k] = sw * o.Jl[k];
-      const double r0 = sw * o.r[0], r1 = sw * o.r[1];
-      double* out = P.rec + (size_t)slot * P.rec_stride;
-      if (L == 3) {
-        double C[6];
-#pragma unroll
-        for (int rr = 0; rr < 2; ++rr)
-#pragma unroll
-          for (int cc = 0; cc < 3; ++cc) C[rr * 3 + cc] = B[rr * 3] * Vi[cc] + B[rr * 3 + 1] * Vi[3 + cc] + B[rr * 3 + 2] * Vi[6 + cc];
-        const double p0 = r0 - (B[0] * dhat[0] + B[1] * dhat[1] + B[2] * dhat[2]);
-        const double p1 = r1 - (B[3] * dhat[0] + B[4] * dhat[1] + B[5] * dhat[2]);
-#pragma unroll
-        for (int k = 0; k < 3; ++k) st2(out + 2 * k, C[2 * k], C[2 * k + 1]);
-#pragma unroll
-        for (int k = 0; k < 6; ++k) st2(out + 6 + 2 * k, A[2 * k], A[2 * k + 1]);
-#pragma unroll
-        for (int k = 0; k < 3; ++k) st2(out + 18 + 2 * k, lm_on ? B[2 * k] : 0.0, lm_on ? B[2 * k + 1] : 0.0);
-        st2(out + 24, r0, r1);
-        st2(out + 26, p0, p1);
-      } else {
-        const double bv0 = lm_on ? B[0] : 0.0, bv1 = lm_on ? B[1] : 0.0;
-        double W[6], Q[12];
-#pragma unroll
-        for (int k = 0; k < 6; ++k) W[k] = A[k] * bv0 + A[6 + k] * bv1;
-        const double c0 = bv0 * Vi[0], c1 = bv1 * Vi[0];
-        if (o.ref_on) {
-          ref_jacobian<L>(c, o.Bp, Q);
-#pragma unroll
-          for (int k = 0; k < 6; ++k) { Q[k] = sw * Q[k] - c0 * Wr[k]; Q[6 + k] = sw * Q[6 + k] - c1 * Wr[k]; }
-        } else {
-#pragma unroll
-          for (int k = 0; k < 12; ++k) Q[k] = 0.0;
-        }
-        const double p0 = r0 - bv0 * dhat[0], p1 = r1 - bv1 * dhat[0];
-#pragma unroll
-        for (int k = 0; k < 3; ++k) st2(out + 2 * k, W[2 * k] * Vi[0], W[2 * k + 1] * Vi[0]);
-#pragma unroll
-        for (int k = 0; k < 3; ++k) st2(out + 6 + 2 * k, W[2 * k], W[2 * k + 1]);
-#pragma unroll
-        for (int k = 0; k < 6; ++k) st2(out + 12 + 2 * k, A[2 * k], A[2 * k + 1]);
-#pragma unroll
-        for (int k = 0; k < 6; ++k) st2(out + 24 + 2 * k, Q[2 * k], Q[2 * k + 1]);
-        st2(out + 36, r0, r1);
-        st2(out + 38, p0, p1);
-      }
+      emit_record<L>(P.rec + (size_t)slot * P.rec_stride, c, o, w_keep, lm_on, Vi, dhat, Wr);
     }
   }
   err = warp_sum(err);
   if (lane == 0) red_add(&P.sc->proj_error, err);
+}
+
+// Packed tasks: a task is a run of consecutive landmarks with at most 32 observations in total (packed on the host from
+// the CSR bounds, symbolic set-up).  One warp per task, ONE OBSERVATION PER LANE: the Jacobians are evaluated once and
+// stay in registers, the per-landmark sums are segmented warp reductions over the lanes of the landmark.  (One lane group
+// per landmark left 13 of 32 lanes busy on a BAL-like track-length distribution and evaluated long tracks twice.)
+template <int L>
+__global__ void __launch_bounds__(128, (L == 1) ? 3 : 4) k_linearize_packed(DeviceProblem P, const uint2* __restrict__ tasks, int n_tasks) {
+  const int lane = threadIdx.x & 31;
+  const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, n_warps = (gridDim.x * blockDim.x) >> 5;
+  const double c_huber = P.c_huber_factor * sqrt(P.sc->median);
+  double err = 0.0;
+  uint2 tk_n = warp < n_tasks ? tasks[warp] : make_uint2(0, 0);
+  for (int t = warp; t < n_tasks; t += n_warps) {
+    const uint2 tk = tk_n;
+    if (t + n_warps < n_tasks) tk_n = tasks[t + n_warps];
+    const int s = (int)tk.x, n = (int)tk.y;            // first observation, number of observations (<= 32)
+    const bool on = lane < n;
+    const int i = s + (on ? lane : 0);
+    const int lm = (int)P.obs_lm[i];
+    // segments = landmarks: head lane of mine, end of mine
+    const int lm_prev = __shfl_up_sync(0xffffffffu, lm, 1);
+    const bool head = on && (lane == 0 || lm != lm_prev);
+    const unsigned heads = __ballot_sync(0xffffffffu, head);
+    const int hl = 31 - __clz(heads & (0xffffffffu >> (31 - lane)));          // lane 0 is always a head (n >= 1)
+    const unsigned above = (lane == 31) ? 0u : (heads & (0xffffffffu << (lane + 1)));
+    const int seg_end = above ? (__ffs(above) - 1) : n;
+    LmCtx<L> c;
+    load_lm<L>(P, lm, c);
+    const bool lm_on = c.lm_opt >= 0;
+    LmSums<L> S;
+#pragma unroll
+    for (int k = 0; k < LmSums<L>::N; ++k) S.v[k] = 0.0;
+    ObsJac<L> o;
+    uint32_t slot = kNoSlot;
+    double w = 0.0;
+    if (on) {
+      slot = P.obs_slot[i];
+      obs_jacobians<L>(P, c, i, o);
+      const double w0 = P.obs_w0[i];
+      const double n2 = o.r[0] * o.r[0] + o.r[1] * o.r[1];
+      w = huber_weight(n2 * w0, w0, c_huber, P.use_robust);
+      P.obs_w[i] = w;
+      err += n2 * w;
+      sums_add<L>(S, o, w, lm_on);
+    }
+    // segmented reduction to the head lane (a lane adds its neighbour at distance d only inside its own landmark),
+    // then every lane of the landmark reads the totals from its head
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+      const bool take = on && (lane + d < seg_end);
+#pragma unroll
+      for (int k = 0; k < LmSums<L>::N; ++k) {
+        const double other = __shfl_down_sync(0xffffffffu, S.v[k], d);
+        if (take) S.v[k] += other;
+      }
+    }
+#pragma unroll
+    for (int k = 0; k < LmSums<L>::N; ++k) S.v[k] = __shfl_sync(0xffffffffu, S.v[k], on ? hl : lane);
+    if (on) {
+      double Vi[L * L], dhat[L], Wr[6];
+      lm_finalize<L, 1>(P, lm, c, lm_on, S, Vi, dhat, Wr, head, 0);
+      if (slot != kNoSlot) emit_record<L>(P.rec + (size_t)slot * P.rec_stride, c, o, w, lm_on, Vi, dhat, Wr);
+    }
+  }
+  err = warp_sum(err);
+  if (lane == 0) red_add(&P.sc->proj_error, err);
+}
+
+// landmarks without a (local) observation: the outputs the kernels above would have written for an empty track
+template <int L>
+__global__ void k_lm_defaults(DeviceProblem P) {
+  const int lm = blockIdx.x * blockDim.x + threadIdx.x;
+  if (lm >= P.n_lms) return;
+  if (P.lm_obs_start[lm] != P.lm_obs_start[lm + 1]) return;
+  double Vi[L * L];
+#pragma unroll
+  for (int i = 0; i < L * L; ++i) Vi[i] = 0.0;
+  if (P.lm_opt[lm] >= 0) {
+    if (L == 1) {
+      Vi[0] = 1.0 / 1e-6;
+    } else {
+      double M[9] = {1e-6, 0, 0, 0, 1e-6, 0, 0, 0, 1e-6}, Mi[9];
+      inv3(M, Mi);
+#pragma unroll
+      for (int i = 0; i < L * L; ++i) Vi[i] = Mi[i];
+    }
+  }
+#pragma unroll
+  for (int i = 0; i < L * L; ++i) P.lm_Vinv[(size_t)lm * L * L + i] = Vi[i];
+#pragma unroll
+  for (int i = 0; i < L; ++i) { P.lm_bl[(size_t)lm * L + i] = 0.0; P.lm_dhat[(size_t)lm * L + i] = 0.0; }
+  if (L == 1) {
+#pragma unroll
+    for (int a = 0; a < 6; ++a) P.lm_Wref[(size_t)lm * 6 + a] = 0.0;
+  }
 }
 
 // ---------------------------------------------------------------------------------------
@@ -554,20 +656,18 @@ static int sm_count_cached() {
   return n;
 }
 
-void launch_linearize(const DeviceProblem& P, int G, cudaStream_t st) {
-  if (P.n_obs == 0) return;
-  size_t blocks = ((size_t)P.n_lms * G + 127) / 128;
-  const size_t cap = (size_t)sm_count_cached() * 12;
-  if (blocks > cap) blocks = cap;
-  if (blocks < 1) blocks = 1;
-  const int grid = (int)blocks;
-#define CALL(LL, GG) k_linearize<LL, GG><<<grid, 128, 0, st>>>(P)
-  if (P.L == 1) {
-    if (G == 4) { CALL(1, 4); } else if (G == 8) { CALL(1, 8); } else if (G == 16) { CALL(1, 16); } else { CALL(1, 32); }
-  } else {
-    if (G == 4) { CALL(3, 4); } else if (G == 8) { CALL(3, 8); } else if (G == 16) { CALL(3, 16); } else { CALL(3, 32); }
+void launch_linearize(const DeviceProblem& P, const uint2* tasks, int n_tasks, const uint32_t* long_lms, int n_long, cudaStream_t st) {
+  if (P.n_lms == 0 || P.L == 0) return;
+  const int cap = sm_count_cached() * 12;
+  if (P.L == 1) k_lm_defaults<1><<<(P.n_lms + 255) / 256, 256, 0, st>>>(P); else k_lm_defaults<3><<<(P.n_lms + 255) / 256, 256, 0, st>>>(P);
+  if (n_tasks > 0) {
+    const int grid = std::max(1, std::min(cap, (n_tasks + 3) / 4));
+    if (P.L == 1) k_linearize_packed<1><<<grid, 128, 0, st>>>(P, tasks, n_tasks); else k_linearize_packed<3><<<grid, 128, 0, st>>>(P, tasks, n_tasks);
   }
-#undef CALL
+  if (n_long > 0) {
+    const int grid = std::max(1, std::min(cap, (n_long + 3) / 4));
+    if (P.L == 1) k_linearize_long<1><<<grid, 128, 0, st>>>(P, long_lms, n_long); else k_linearize_long<3><<<grid, 128, 0, st>>>(P, long_lms, n_long);
+  }
 }
 
 void launch_reduce_blocks(const DeviceProblem& P, const ReduceItem* items, int n_items, const uint2* pairs, double* partial,
