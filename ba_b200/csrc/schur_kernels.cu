@@ -490,10 +490,8 @@ template <int L, int KIND> struct PartCfg {
   static constexpr int PS = 2 * PC;                                            // doubles per part
 };
 template <int L, int KIND>
-BA_D void stage_pairs(const DeviceProblem& P, const uint2* __restrict__ pairs, uint32_t begin, uint32_t end, int bt, double* buf, int lane) {
+BA_D void stage_pairs(const DeviceProblem& P, const uint2 ab, double* buf, int lane) {
   typedef PartCfg<L, KIND> C;
-  const uint32_t p = begin + (uint32_t)bt * kPPB + (lane & (kPPB - 1));
-  const uint2 ab = (p < end) ? pairs[p] : make_uint2(kNoSlot, kNoSlot);
   if (lane < kPPB) reinterpret_cast<uint32_t*>(buf + RedCfg<L>::DATA)[lane] = (ab.x == kNoSlot) ? kNoSlot - 2 : ab.y;
 #pragma unroll
   for (int k = 0; k < (C::NPART * C::PC + 31) / 32; ++k) {
@@ -544,12 +542,20 @@ __global__ void __launch_bounds__(kRedWarps * 32, 4) k_reduce_blocks(DeviceProbl
     const bool diag = (w.kind == kItemDiagObs || w.kind == kItemDiagLm);
     const bool obs = (w.kind == kItemDiagObs);
     // ---- software pipeline: batch bt + kStages - 1 is in flight while batch bt is multiplied out ----
+    // the list entries of a batch are requested one batch ahead of the record gather that needs them
+    auto entry = [&](int b) {
+      const uint32_t p = w.begin + (uint32_t)b * kPPB + (lane & (kPPB - 1));
+      return (!diag && b < nb && p < w.end) ? pairs[p] : make_uint2(kNoSlot, kNoSlot);
+    };
+    uint2 ab_next = entry(0);
     for (int bt = -(kStages - 1); bt < nb; ++bt) {
       const int ld = bt + kStages - 1;
       if (ld < nb) {
         double* dst = stage + (ld % kStages) * Cfg::BUF;
-        if (w.kind == kItemOffRef) { if (L == 1) stage_pairs<1, kItemOffRef>(P, pairs, w.begin, w.end, ld, dst, lane); }
-        else if (!diag) stage_pairs<L, kItemOff>(P, pairs, w.begin, w.end, ld, dst, lane);
+        const uint2 ab = ab_next;
+        ab_next = entry(ld + 1);
+        if (w.kind == kItemOffRef) { if (L == 1) stage_pairs<1, kItemOffRef>(P, ab, dst, lane); }
+        else if (!diag) stage_pairs<L, kItemOff>(P, ab, dst, lane);
         else if (obs) stage_records<Cfg::RS>(P.rec, w.begin + (uint32_t)ld * kPPB, w.end, dst, lane);
         else stage_records<kLmRec>(P.lm_rec, w.begin + (uint32_t)ld * kPPB, w.end, dst, lane);
       }
