@@ -128,6 +128,9 @@ __global__ void __launch_bounds__(CholCfg<T>::NT, 1) k_chol_dataflow(CholDev c) 
       // next (up to 32) terms without blocking and the CTA multiplies out the ready prefix, so that when the newest
       // U_ki arrives everything older is already in the accumulators (waiting for all terms but the newest first
       // left ~60 serial tile products on the critical path of every separator row).
+      // diagonal task: the forward-substitution shares c_ik of the same terms are folded in as the terms arrive
+      const bool bsum_on = (tk.kind == kTaskDiag) && tid < T;
+      double bsum = bsum_on ? c.rhs[(size_t)tk.i * T + tid] : 0.0;
       for (int e = tk.lb; e < tk.le;) {
         if (warp == 0) {
           const int idx = e + lane;
@@ -148,6 +151,7 @@ __global__ void __launch_bounds__(CholCfg<T>::NT, 1) k_chol_dataflow(CholDev c) 
           const double* Ua = c.tiles + (size_t)tm.sa * T * T;
           const double* Ub = c.tiles + (size_t)tm.sb * T * T;
           const double* sg = c.sgn + (size_t)tm.k * T;
+          if (bsum_on) bsum -= ldcg(c.cvec + (size_t)tm.sa * T + tid);
           double bfr[KQ];
 #pragma unroll
           for (int kq = 0; kq < KQ; ++kq) bfr[kq] = ldcg(Ub + (size_t)(n0 + gid) * T + kq * 4 + tig) * ldcg(sg + kq * 4 + tig);
@@ -179,11 +183,7 @@ __global__ void __launch_bounds__(CholCfg<T>::NT, 1) k_chol_dataflow(CholDev c) 
             M[r * LD + cc + 1] = (r <= cc + 1) ? Aij[(size_t)(cc + 1) * T + r] - acc1[mi] : 0.0;
           }
         }
-        for (int r = tid; r < T; r += NT) {
-          double b = c.rhs[(size_t)k * T + r];
-          for (int e = tk.lb; e < tk.le; ++e) b -= ldcg(c.cvec + (size_t)c.terms[e].sa * T + r);
-          M[r * LD + T] = b;
-        }
+        if (bsum_on) M[tid * LD + T] = bsum;
         __syncthreads();
         // Blocked root-free elimination of [R | I | b], pivot blocks of 8, two barriers per block (the
         // column-at-a-time version cost one barrier + one FP64 division per column: 31 us for T = 48).

@@ -87,8 +87,8 @@ BA_D void obs_residual(const DeviceProblem& P, const LmCtx<L>& c, int obs, doubl
 
 // residual + closed-form Jacobians
 template <int L>
-BA_D void obs_jacobians(const DeviceProblem& P, const LmCtx<L>& c, int obs, ObsJac<L>& o) {
-  const int m = (int)P.obs_pose[obs];
+BA_D void obs_jacobians(const DeviceProblem& P, const LmCtx<L>& c, int obs, ObsJac<L>& o, int m_known = -1) {
+  const int m = m_known >= 0 ? m_known : (int)P.obs_pose[obs];
   const int cam = P.obs_cam ? (int)P.obs_cam[obs] : 0;
   const double* Tsw = P.Tsw + ((size_t)m * P.n_cams + cam) * 12;
   double R[9], t[3];

@@ -23,6 +23,7 @@
 // The pair lists depend only on the ids; they are built once per Solve() on the device
 // (symbolic.cu).
 #include <algorithm>
+#include <cstdlib>
 #include "proj_kernels.cuh"
 #include "launch.h"
 
@@ -266,20 +267,32 @@ __global__ void __launch_bounds__(128, (L == 1) ? 3 : 4) k_linearize_long(Device
 // the CSR bounds, symbolic set-up).  One warp per task, ONE OBSERVATION PER LANE: the Jacobians are evaluated once and
 // stay in registers, the per-landmark sums are segmented warp reductions over the lanes of the landmark.  (One lane group
 // per landmark left 13 of 32 lanes busy on a BAL-like track-length distribution and evaluated long tracks twice.)
-template <int L>
+// STAGE: the 32 records of a task are assembled in shared memory and written out with consecutive lanes on consecutive
+// 16-byte pieces of one record (full 32-byte sectors, a few records per store instruction) instead of every lane
+// storing 14-20 separate half sectors of its own record.
+template <int L, bool STAGE>
 __global__ void __launch_bounds__(128, (L == 1) ? 3 : 4) k_linearize_packed(DeviceProblem P, const uint2* __restrict__ tasks, int n_tasks) {
+  constexpr int RS = (L == 3) ? kRec3 : kRec1;
+  __shared__ double2 srec[STAGE ? 4 * 32 * RS / 2 : 1];
   const int lane = threadIdx.x & 31;
   const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, n_warps = (gridDim.x * blockDim.x) >> 5;
   const double c_huber = P.c_huber_factor * sqrt(P.sc->median);
   double err = 0.0;
+  // two levels of the dependent chain (task -> landmark / pose ids -> landmark point / pose frame) are requested one
+  // task ahead: the next task's bounds, and its lanes' landmark and pose ids
   uint2 tk_n = warp < n_tasks ? tasks[warp] : make_uint2(0, 0);
+  uint2 tk_nn = warp + n_warps < n_tasks ? tasks[warp + n_warps] : make_uint2(0, 0);
+  int lm_n = 0, m_n = 0;
+  if (warp < n_tasks) { const int i0 = (int)tk_n.x + (lane < (int)tk_n.y ? lane : 0); lm_n = (int)P.obs_lm[i0]; m_n = (int)P.obs_pose[i0]; }
   for (int t = warp; t < n_tasks; t += n_warps) {
     const uint2 tk = tk_n;
-    if (t + n_warps < n_tasks) tk_n = tasks[t + n_warps];
+    const int lm = lm_n, m_pre = m_n;
+    tk_n = tk_nn;
+    if (t + 2 * n_warps < n_tasks) tk_nn = tasks[t + 2 * n_warps];
+    if (t + n_warps < n_tasks) { const int i0 = (int)tk_n.x + (lane < (int)tk_n.y ? lane : 0); lm_n = (int)P.obs_lm[i0]; m_n = (int)P.obs_pose[i0]; }
     const int s = (int)tk.x, n = (int)tk.y;            // first observation, number of observations (<= 32)
     const bool on = lane < n;
     const int i = s + (on ? lane : 0);
-    const int lm = (int)P.obs_lm[i];
     // segments = landmarks: head lane of mine, end of mine
     const int lm_prev = __shfl_up_sync(0xffffffffu, lm, 1);
     const bool head = on && (lane == 0 || lm != lm_prev);
@@ -298,7 +311,7 @@ __global__ void __launch_bounds__(128, (L == 1) ? 3 : 4) k_linearize_packed(Devi
     double w = 0.0;
     if (on) {
       slot = P.obs_slot[i];
-      obs_jacobians<L>(P, c, i, o);
+      obs_jacobians<L>(P, c, i, o, m_pre);
       const double w0 = P.obs_w0[i];
       const double n2 = o.r[0] * o.r[0] + o.r[1] * o.r[1];
       w = huber_weight(n2 * w0, w0, c_huber, P.use_robust);
@@ -322,7 +335,23 @@ __global__ void __launch_bounds__(128, (L == 1) ? 3 : 4) k_linearize_packed(Devi
     if (on) {
       double Vi[L * L], dhat[L], Wr[6];
       lm_finalize<L, 1>(P, lm, c, lm_on, S, Vi, dhat, Wr, head, 0);
-      if (slot != kNoSlot) emit_record<L>(P.rec + (size_t)slot * P.rec_stride, c, o, w, lm_on, Vi, dhat, Wr);
+      if (slot != kNoSlot) {
+        double* out = STAGE ? reinterpret_cast<double*>(srec) + ((threadIdx.x >> 5) * 32 + lane) * RS : P.rec + (size_t)slot * P.rec_stride;
+        emit_record<L>(out, c, o, w, lm_on, Vi, dhat, Wr);
+      }
+    }
+    if (STAGE) {
+      __syncwarp();
+      const double2* sw2 = srec + (threadIdx.x >> 5) * 32 * (RS / 2);
+#pragma unroll 2
+      for (int base = 0; base < n * (RS / 2); base += 32) {     // uniform trip count: the shuffle needs every lane
+        const int idx = base + lane;
+        const bool valid = idx < n * (RS / 2);
+        const int rec = valid ? idx / (RS / 2) : 0, ch = idx - rec * (RS / 2);
+        const uint32_t sl = __shfl_sync(0xffffffffu, slot, rec);
+        if (valid && sl != kNoSlot) reinterpret_cast<double2*>(P.rec + (size_t)sl * RS)[ch] = sw2[rec * (RS / 2) + ch];
+      }
+      __syncwarp();
     }
   }
   err = warp_sum(err);
@@ -668,7 +697,9 @@ void launch_linearize(const DeviceProblem& P, const uint2* tasks, int n_tasks, c
   if (P.L == 1) k_lm_defaults<1><<<(P.n_lms + 255) / 256, 256, 0, st>>>(P); else k_lm_defaults<3><<<(P.n_lms + 255) / 256, 256, 0, st>>>(P);
   if (n_tasks > 0) {
     const int grid = std::max(1, std::min(cap, (n_tasks + 3) / 4));
-    if (P.L == 1) k_linearize_packed<1><<<grid, 128, 0, st>>>(P, tasks, n_tasks); else k_linearize_packed<3><<<grid, 128, 0, st>>>(P, tasks, n_tasks);
+    static const bool stage = getenv("BAGPU_LIN_STAGE") ? atoi(getenv("BAGPU_LIN_STAGE")) != 0 : false;
+    if (P.L == 1) { if (stage) k_linearize_packed<1, true><<<grid, 128, 0, st>>>(P, tasks, n_tasks); else k_linearize_packed<1, false><<<grid, 128, 0, st>>>(P, tasks, n_tasks); }
+    else { if (stage) k_linearize_packed<3, true><<<grid, 128, 0, st>>>(P, tasks, n_tasks); else k_linearize_packed<3, false><<<grid, 128, 0, st>>>(P, tasks, n_tasks); }
   }
   if (n_long > 0) {
     const int grid = std::max(1, std::min(cap, (n_long + 3) / 4));
