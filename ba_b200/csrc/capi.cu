@@ -428,6 +428,8 @@ struct bagpu_handle_s {
     tile_perm.assign(nT, 0);
     for (int i = 0; i < nT; ++i) tile_perm[i] = i;
     if (nT < 8 || getenv("BAGPU_NO_ND")) return;
+    // a node list is split while its separator is smaller than 2 / nd_ratio of it (development knob BAGPU_ND_RATIO)
+    const int nd_ratio = getenv("BAGPU_ND_RATIO") ? std::max(2, atoi(getenv("BAGPU_ND_RATIO"))) : 6;
     std::vector<std::vector<int>> adj(nT);
     for (int a = 0; a < nT; ++a) for (int b = a + 1; b < nT; ++b) if (present[a][b]) { adj[a].push_back(b); adj[b].push_back(a); }
     std::vector<int> order; order.reserve(nT);
@@ -451,7 +453,7 @@ struct bagpu_handle_s {
       const bool use_left = sl.size() <= sr.size();
       const std::vector<int>& sep = use_left ? sl : sr;
       for (int v : f.nodes) side[v] = 0;
-      if (sep.empty() || (int)sep.size() * 3 >= n) { for (int v : f.nodes) order.push_back(v); continue; }
+      if (sep.empty() || (int)sep.size() * nd_ratio >= n * 2) { for (int v : f.nodes) order.push_back(v); continue; }
       std::vector<uint8_t> in_sep_mark;   // small: mark through `side`
       for (int v : sep) side[v] = 3;
       Frame left, right, sp;

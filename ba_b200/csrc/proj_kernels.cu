@@ -125,15 +125,22 @@ BA_D void back_term(const DeviceProblem& P, int i, const double* delta_p, double
   if (slot == kNoSlot) return;
   const double* r = P.rec + (size_t)slot * P.rec_stride;
   const double* dp = delta_p + (size_t)P.pose_opt[P.obs_pose[i]] * P.D;
+  // the record is read in 16-byte pieces (half as many memory requests as scalar loads)
   if (L == 3) {
+    double v[18];
+#pragma unroll
+    for (int a = 0; a < 9; ++a) { const double2 x = reinterpret_cast<const double2*>(r)[a]; v[2 * a] = x.x; v[2 * a + 1] = x.y; }
     double t0 = 0.0, t1 = 0.0;
 #pragma unroll
-    for (int a = 0; a < 6; ++a) { t0 += r[6 + a] * dp[a]; t1 += r[12 + a] * dp[a]; }
+    for (int a = 0; a < 6; ++a) { t0 += v[6 + a] * dp[a]; t1 += v[12 + a] * dp[a]; }
 #pragma unroll
-    for (int k = 0; k < L; ++k) acc[k] += r[k] * t0 + r[3 + k] * t1;
+    for (int k = 0; k < L; ++k) acc[k] += v[k] * t0 + v[3 + k] * t1;
   } else {
+    double v[6];
 #pragma unroll
-    for (int a = 0; a < 6; ++a) acc[0] += r[a] * dp[a];
+    for (int a = 0; a < 3; ++a) { const double2 x = reinterpret_cast<const double2*>(r)[a]; v[2 * a] = x.x; v[2 * a + 1] = x.y; }
+#pragma unroll
+    for (int a = 0; a < 6; ++a) acc[0] += v[a] * dp[a];
   }
 }
 // landmark part and write-out, by one lane holding the landmark's sum

@@ -59,6 +59,12 @@ BA_D void load_lm(const DeviceProblem& P, int lm, LmCtx<L>& c) {
   }
 }
 
+// a pose frame [R (9, row-major) | t (3)] in six 16-byte loads (frames are 96 bytes apart)
+BA_D void load_frame(const double* __restrict__ T, double* f) {
+#pragma unroll
+  for (int k = 0; k < 6; ++k) { const double2 v = reinterpret_cast<const double2*>(T)[k]; f[2 * k] = v.x; f[2 * k + 1] = v.y; }
+}
+
 template <int L>
 struct ObsJac {
   double r[2];
@@ -74,7 +80,8 @@ template <int L>
 BA_D void obs_residual(const DeviceProblem& P, const LmCtx<L>& c, int obs, double* r) {
   const int m = (int)P.obs_pose[obs];
   const int cam = P.obs_cam ? (int)P.obs_cam[obs] : 0;
-  const double* Tsw = P.Tsw + ((size_t)m * P.n_cams + cam) * 12;
+  double Tsw[12];
+  load_frame(P.Tsw + ((size_t)m * P.n_cams + cam) * 12, Tsw);
   double Xs[3];
   mat3_vec(Tsw, c.X, Xs);
   Xs[0] += c.rho * Tsw[9]; Xs[1] += c.rho * Tsw[10]; Xs[2] += c.rho * Tsw[11];
@@ -90,7 +97,8 @@ template <int L>
 BA_D void obs_jacobians(const DeviceProblem& P, const LmCtx<L>& c, int obs, ObsJac<L>& o, int m_known = -1) {
   const int m = m_known >= 0 ? m_known : (int)P.obs_pose[obs];
   const int cam = P.obs_cam ? (int)P.obs_cam[obs] : 0;
-  const double* Tsw = P.Tsw + ((size_t)m * P.n_cams + cam) * 12;
+  double Tsw[12];
+  load_frame(P.Tsw + ((size_t)m * P.n_cams + cam) * 12, Tsw);
   double R[9], t[3];
 #pragma unroll
   for (int i = 0; i < 9; ++i) R[i] = Tsw[i];

@@ -697,7 +697,7 @@ void launch_linearize(const DeviceProblem& P, const uint2* tasks, int n_tasks, c
   if (P.L == 1) k_lm_defaults<1><<<(P.n_lms + 255) / 256, 256, 0, st>>>(P); else k_lm_defaults<3><<<(P.n_lms + 255) / 256, 256, 0, st>>>(P);
   if (n_tasks > 0) {
     const int grid = std::max(1, std::min(cap, (n_tasks + 3) / 4));
-    static const bool stage = getenv("BAGPU_LIN_STAGE") ? atoi(getenv("BAGPU_LIN_STAGE")) != 0 : false;
+    static const bool stage = getenv("BAGPU_LIN_STAGE") ? atoi(getenv("BAGPU_LIN_STAGE")) != 0 : true;
     if (P.L == 1) { if (stage) k_linearize_packed<1, true><<<grid, 128, 0, st>>>(P, tasks, n_tasks); else k_linearize_packed<1, false><<<grid, 128, 0, st>>>(P, tasks, n_tasks); }
     else { if (stage) k_linearize_packed<3, true><<<grid, 128, 0, st>>>(P, tasks, n_tasks); else k_linearize_packed<3, false><<<grid, 128, 0, st>>>(P, tasks, n_tasks); }
   }
