@@ -1530,6 +1530,17 @@ int bagpu_comm_init(bagpu_handle h, int rank, int world, const void* id128) {
   int rc = g_nccl.commInitRank(&h->comm, world, id, rank);
   if (rc) return fail(BAGPU_ERR_NCCL, std::string("ncclCommInitRank failed: ") + (g_nccl.getErrorString ? g_nccl.getErrorString(rc) : "?"));
   h->rank = rank; h->world = world;
+  // NCCL connects its channels lazily, at the first collective of each size class (hundreds of ms): do that here, as
+  // part of communicator set-up, with one small and one bulk all-reduce, so that the first Solve() does not pay for it.
+  GUARD({
+    const size_t n_big = (size_t)4 << 20;  // 32 MB of doubles: the order of an S all-reduce
+    DevBuf<double> warm; warm.alloc(n_big);
+    warm.zero(h->st);
+    h->allreduce_u32(reinterpret_cast<unsigned int*>(warm.p), 4096);
+    h->allreduce_f64(warm.p, 64);
+    h->allreduce_f64(warm.p, n_big);
+    CU(cudaStreamSynchronize(h->st));
+  })
   return BAGPU_OK;
 }
 
