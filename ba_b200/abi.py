@@ -197,9 +197,17 @@ class Binding:
         self._check(self._f("get_poses")(self.h, _p(t, np.float64), _p(v, np.float64), _p(b, np.float64), _p(mu, np.uint8), _p(m, np.uint8)))
         return dict(t_wp=t, v_w=v, b=b, mask_used=mu, mask=m)
 
-    def get_landmarks(self):
+    def get_landmarks(self, out=None):
+        """Refined landmarks.  `out` (optional): dict with preallocated C-contiguous arrays x_w, x_s (n x 4 float64),
+        is_reliable (uint8), num_outlier_residuals (uint32) — e.g. page-locked ones — that are filled in place."""
         n = self.n_landmarks
-        xw = np.zeros((n, 4)); xs = np.zeros((n, 4)); rel = np.zeros(n, np.uint8); nout = np.zeros(n, np.uint32)
+        if out is not None:
+            xw, xs, rel, nout = out["x_w"], out["x_s"], out["is_reliable"], out["num_outlier_residuals"]
+            assert xw.shape == (n, 4) and xs.shape == (n, 4) and rel.shape == (n,) and nout.shape == (n,)
+            assert all(a.flags.c_contiguous for a in (xw, xs, rel, nout))
+            assert xw.dtype == np.float64 and xs.dtype == np.float64 and rel.dtype == np.uint8 and nout.dtype == np.uint32
+        else:
+            xw = np.empty((n, 4)); xs = np.empty((n, 4)); rel = np.empty(n, np.uint8); nout = np.empty(n, np.uint32)
         self._check(self._f("get_landmarks")(self.h, _p(xw, np.float64), _p(xs, np.float64), _p(rel, np.uint8), _p(nout, np.uint32)))
         return dict(x_w=xw, x_s=xs, is_reliable=rel, num_outlier_residuals=nout)
 

@@ -22,6 +22,7 @@
 #include "ba_gpu.h"
 #include "device_math.cuh"
 #include "dev_alloc.h"
+#include "peer_reduce.h"
 #include "launch.h"
 
 using namespace bagpu;
@@ -85,6 +86,8 @@ struct NcclApi {
   int (*commInitRank)(void**, int, UniqueId, int) = nullptr;
   int (*allReduce)(const void*, void*, size_t, int, int, void*, cudaStream_t) = nullptr;
   int (*commDestroy)(void*) = nullptr;
+  int (*groupStart)() = nullptr;
+  int (*groupEnd)() = nullptr;
   const char* (*getErrorString)(int) = nullptr;
   bool load() {
     if (lib) return true;
@@ -101,6 +104,8 @@ struct NcclApi {
     allReduce = (int (*)(const void*, void*, size_t, int, int, void*, cudaStream_t))dlsym(lib, "ncclAllReduce");
     commDestroy = (int (*)(void*))dlsym(lib, "ncclCommDestroy");
     getErrorString = (const char* (*)(int))dlsym(lib, "ncclGetErrorString");
+    groupStart = (int (*)())dlsym(lib, "ncclGroupStart");
+    groupEnd = (int (*)())dlsym(lib, "ncclGroupEnd");
     return getUniqueId && commInitRank && allReduce && commDestroy;
   }
 };
@@ -122,6 +127,7 @@ struct bagpu_handle_s {
   std::vector<double> pose_t7, pose_v, pose_b;
   std::vector<uint8_t> pose_active, pose_mask_used, pose_mask;   // mask: D per pose, 1 = free
   std::vector<double> lm_xw, lm_xs;
+  bool lm_host_fresh = true;   // false: the refined landmarks live on the device only (fetched on demand)
   std::vector<uint32_t> lm_ref_pose, lm_ref_cam;
   std::vector<uint8_t> lm_active, lm_reliable;
   std::vector<uint32_t> lm_outliers;
@@ -200,6 +206,7 @@ struct bagpu_handle_s {
 
   // ---- multi-GPU ----
   void* comm = nullptr;
+  PeerReduce peer;   // small reductions over NVLink peer memory (peer_reduce.h); bulk ones go through NCCL
   int rank = 0, world = 1;
 
   // =======================================================================================
@@ -706,11 +713,13 @@ struct bagpu_handle_s {
 
   void allreduce_f64(double* buf, size_t n) {
     if (world <= 1 || n == 0) return;
+    if (peer.fits(n * sizeof(double))) { peer.allreduce_f64(buf, (int)n, st); ++launches; return; }
     int rc = g_nccl.allReduce(buf, buf, n, kNcclFloat64, kNcclSum, comm, st);
     if (rc != 0) throw std::string("ncclAllReduce(f64) failed: ") + (g_nccl.getErrorString ? g_nccl.getErrorString(rc) : "?");
   }
   void allreduce_u32(unsigned int* buf, size_t n) {
     if (world <= 1 || n == 0) return;
+    if (peer.fits(n * sizeof(unsigned int))) { peer.allreduce_u32(buf, (int)n, st); ++launches; return; }
     int rc = g_nccl.allReduce(buf, buf, n, kNcclUint32, kNcclSum, comm, st);
     if (rc != 0) throw std::string("ncclAllReduce(u32) failed");
   }
@@ -745,10 +754,14 @@ struct bagpu_handle_s {
     if (n_items_sym) { launch_reduce_blocks(P, d_items_sym.p, n_items_sym, d_pairs, d_partial.p, d_counters.p + 1, d_counters.p, st); ++launches; }
     CU(cudaEventRecord(ev[5], st));
     if (world > 1) {
+      // one NCCL group: the four reductions share a single launch
+      const bool grp = g_nccl.groupStart && g_nccl.groupEnd;
+      if (grp) g_nccl.groupStart();
       allreduce_f64(d_S.p, (size_t)n_tiles * T * T);
       allreduce_f64(d_bp.p, (size_t)nT * T);
       allreduce_f64(d_rhs_sc.p, (size_t)nT * T);
       allreduce_f64(&d_sc.p->proj_error, 8);   // proj_error .. inertial_error
+      if (grp && g_nccl.groupEnd() != 0) throw std::string("ncclGroupEnd failed");
     }
     launch_mask_diagonal(P, d_pose_mask_used.p, is_param_mask_used ? 1 : 0, st); launches += is_param_mask_used ? 2 : 1;
     CU(cudaEventRecord(ev[6], st));
@@ -1026,7 +1039,7 @@ struct bagpu_handle_s {
     PhaseClock pc;
     ensure_device(); pc.lap("ensure_device");
     maha0_valid = false;
-    if (dirty) { setup(); pc.lap("setup (host symbolic)"); upload_all(); sync(); pc.lap("upload_all"); solved_once = false; }
+    if (dirty) { fetch_landmarks_host(); setup(); pc.lap("setup (host symbolic)"); upload_all(); sync(); pc.lap("upload_all"); solved_once = false; }
     else apply_options();
     // Solve() prologue (cpp:287-296)
     launch_pose_frames(P, st); ++launches;
@@ -1047,15 +1060,30 @@ struct bagpu_handle_s {
       }
       if (L == 1) { launch_finish_xw(P, d_lm_xw.p, st); ++launches; }
       else CU(cudaMemcpyAsync(d_lm_xw.p, d_lm_x.p, sizeof(double) * 4 * n_lms, cudaMemcpyDeviceToDevice, st));
-      d_lm_xw.download(lm_xw.data(), lm_xw.size(), st);
-      lm_xs.resize(lm_xw.size());
-      d_lm_x.download(lm_xs.data(), lm_xs.size(), st);
-      d_lm_reliable.download(lm_reliable.data(), lm_reliable.size(), st);
-      lm_outliers.resize(n_lms);
-      d_lm_outliers.download(lm_outliers.data(), n_lms, st);
+      lm_host_fresh = false;   // bagpu_get_landmarks reads them straight into the caller's buffers
     }
     sync();
     for (int i = 0; i < n_poses; ++i) { for (int k = 0; k < 4; ++k) pose_t7[7 * i + k] = q[4 * i + k]; for (int k = 0; k < 3; ++k) pose_t7[7 * i + 4 + k] = t[3 * i + k]; }
+  }
+
+  // the host copies of the landmark state, needed only when the problem is set up again from the host vectors
+  void fetch_landmarks_host() {
+    if (lm_host_fresh || !n_lms || !d_lm_xw.p) { lm_host_fresh = true; return; }
+    d_lm_xw.download(lm_xw.data(), lm_xw.size(), st);
+    lm_xs.resize(lm_xw.size());
+    d_lm_x.download(lm_xs.data(), lm_xs.size(), st);
+    d_lm_reliable.download(lm_reliable.data(), lm_reliable.size(), st);
+    lm_outliers.resize(n_lms);
+    d_lm_outliers.download(lm_outliers.data(), n_lms, st);
+    sync();
+    lm_host_fresh = true;
+  }
+  void copy_landmarks_out(double* xw, double* xs, uint8_t* rel, uint32_t* nout) {
+    if (xw) d_lm_xw.download(xw, 4 * (size_t)n_lms, st);
+    if (xs) d_lm_x.download(xs, 4 * (size_t)n_lms, st);
+    if (rel) d_lm_reliable.download(rel, n_lms, st);
+    if (nout) d_lm_outliers.download(nout, n_lms, st);
+    sync();
   }
 
   // Solve (cpp:278-705)
@@ -1218,6 +1246,7 @@ int bagpu_create(const bagpu_dims* d, bagpu_handle* out) {
 void bagpu_destroy(bagpu_handle h) {
   if (!h) return;
   if (h->st) cudaStreamSynchronize(h->st);
+  h->peer.destroy();
   if (h->comm && g_nccl.commDestroy) g_nccl.commDestroy(h->comm);
   if (h->ev_ok) for (auto& e : h->ev) cudaEventDestroy(e);
   if (h->d_pairs) dev_free(h->d_pairs);
@@ -1253,6 +1282,7 @@ int bagpu_set_landmarks(bagpu_handle h, uint32_t n, const double* x, const uint3
   const size_t np = h->pose_t7.size() / 7;
   for (uint32_t i = 0; i < n; ++i) if (rp[i] >= np) return fail(BAGPU_ERR_INVALID, "landmark ref_pose_id out of range");
   h->lm_xw.assign(x, x + 4 * (size_t)n); h->lm_xs.clear();   // x_s is filled by the first Solve()
+  h->lm_host_fresh = true;
   h->lm_ref_pose.assign(rp, rp + n);
   if (rc) h->lm_ref_cam.assign(rc, rc + n); else h->lm_ref_cam.assign(n, 0);
   if (a) h->lm_active.assign(a, a + n); else h->lm_active.assign(n, 1);
@@ -1338,6 +1368,8 @@ int bagpu_set_imu_residuals(bagpu_handle h, uint32_t n, const uint32_t* p1, cons
 int bagpu_solve(bagpu_handle h, uint32_t max_iter, double gn_damping, int allow, bagpu_summary* out) {
   if (!h) return fail(BAGPU_ERR_INVALID, "null handle");
   GUARD(h->solve(max_iter, gn_damping, allow != 0);)
+  if (h->peer.ok && h->peer.error(h->st))
+    return fail(BAGPU_ERR_NCCL, "a peer-memory reduction timed out: some rank did not reach the collective");
   if (out) *out = h->summary;
   return BAGPU_OK;
 }
@@ -1366,6 +1398,7 @@ int bagpu_get_poses(bagpu_handle h, double* t, double* v, double* b, uint8_t* mu
 }
 int bagpu_get_landmarks(bagpu_handle h, double* xw, double* xs, uint8_t* rel, uint32_t* nout) {
   const size_t n = h->lm_xw.size() / 4;
+  if (!h->lm_host_fresh && !h->dirty) { GUARD(h->copy_landmarks_out(xw, xs, rel, nout);) return BAGPU_OK; }
   if (xw) memcpy(xw, h->lm_xw.data(), sizeof(double) * 4 * n);
   if (xs) { if (h->lm_xs.size() == 4 * n) memcpy(xs, h->lm_xs.data(), sizeof(double) * 4 * n); else memset(xs, 0, sizeof(double) * 4 * n); }
   if (rel) memcpy(rel, h->lm_reliable.data(), n);
@@ -1540,13 +1573,34 @@ int bagpu_comm_init(bagpu_handle h, int rank, int world, const void* id128) {
     h->allreduce_f64(warm.p, 64);
     h->allreduce_f64(warm.p, n_big);
     CU(cudaStreamSynchronize(h->st));
+    // windows for the small reductions: IPC handles gathered with one all-reduce of a zero-padded table, then a vote
+    // (every rank must have mapped every peer, otherwise all of them stay on NCCL)
+    const char* pe = getenv("BAGPU_P2P");
+    if (world <= kPeerMaxWorld && !(pe && pe[0] == '0')) {
+      std::vector<unsigned int> tab((size_t)world * 16 + 1, 0u);
+      bool mine = h->peer.create_local(rank, world, &tab[(size_t)rank * 16]) == cudaSuccess;
+      if (!mine) { cudaGetLastError(); memset(&tab[(size_t)rank * 16], 0, 64); }
+      unsigned int* d_tab = reinterpret_cast<unsigned int*>(warm.p);
+      CU(cudaMemcpyAsync(d_tab, tab.data(), tab.size() * 4, cudaMemcpyHostToDevice, h->st));
+      h->allreduce_u32(d_tab, tab.size());
+      CU(cudaMemcpyAsync(tab.data(), d_tab, tab.size() * 4, cudaMemcpyDeviceToHost, h->st));
+      CU(cudaStreamSynchronize(h->st));
+      const bool opened = mine && h->peer.open_peers(tab.data());
+      tab.assign(1, opened ? 1u : 0u);
+      CU(cudaMemcpyAsync(d_tab, tab.data(), 4, cudaMemcpyHostToDevice, h->st));
+      h->allreduce_u32(d_tab, 1);
+      CU(cudaMemcpyAsync(tab.data(), d_tab, 4, cudaMemcpyDeviceToHost, h->st));
+      CU(cudaStreamSynchronize(h->st));
+      if (tab[0] == (unsigned int)world) h->peer.ok = true; else h->peer.destroy();
+      if (getenv("BAGPU_TIMING")) fprintf(stderr, "[bagpu] rank %d: peer-memory reductions %s\n", rank, h->peer.ok ? "on" : "off (NCCL only)");
+    }
   })
   return BAGPU_OK;
 }
 
 int bagpu_sync_state(bagpu_handle h) {
   if (!h) return fail(BAGPU_ERR_INVALID, "null handle");
-  GUARD(h->ensure_device(); if (h->dirty) return fail(BAGPU_ERR_INVALID, "no solve yet"); h->download_state();)
+  GUARD(h->ensure_device(); if (h->dirty) return fail(BAGPU_ERR_INVALID, "no solve yet"); h->download_state(); h->fetch_landmarks_host();)
   return BAGPU_OK;
 }
 

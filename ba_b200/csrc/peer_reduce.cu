@@ -1,0 +1,100 @@
+// peer_reduce.cu — see peer_reduce.h.
+#include "peer_reduce.h"
+#include <cstring>
+
+namespace {
+
+__device__ __forceinline__ unsigned char* slot_ptr(unsigned char* win, int parity, int r) {
+  return win + kPeerFlagBytes + ((size_t)parity * kPeerMaxWorld + r) * kPeerSlotBytes;
+}
+__device__ __forceinline__ unsigned long long* flag_ptr(unsigned char* win, int parity, int r) {
+  return reinterpret_cast<unsigned long long*>(win) + parity * kPeerMaxWorld + r;
+}
+
+// Two slot sets, used alternately: a rank can enter reduction s+2 only after finishing s+1, which needs every peer's
+// flag for s+1, which a peer stores only after its kernel for s has finished reading the slots of s (stream order).
+template <typename T>
+__global__ void __launch_bounds__(1024) k_peer_allreduce(PeerWindow w, T* buf, int n, unsigned long long seq, int* err) {
+  const int tid = threadIdx.x, parity = (int)(seq & 1ull);
+  if (*reinterpret_cast<volatile int*>(err)) return;
+  for (int p = 0; p < w.world; ++p) {
+    T* dst = reinterpret_cast<T*>(slot_ptr(w.win[p], parity, w.rank));
+    for (int i = tid; i < n; i += blockDim.x) dst[i] = buf[i];
+  }
+  __syncthreads();
+  if (tid < w.world) {
+    __threadfence_system();
+    unsigned long long* f = flag_ptr(w.win[tid], parity, w.rank);
+    asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(f), "l"(seq) : "memory");
+    const unsigned long long* mine = flag_ptr(w.win[w.rank], parity, tid);
+    const long long t0 = clock64();
+    unsigned long long v;
+    do {
+      asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(mine) : "memory");
+      if (v < seq && clock64() - t0 > 120000000000ll) { *err = 1; break; }  // ~60 s: a peer is gone
+    } while (v < seq);
+  }
+  __syncthreads();
+  unsigned char* local = w.win[w.rank];
+  for (int i = tid; i < n; i += blockDim.x) {
+    T s = 0;
+    for (int q = 0; q < w.world; ++q) s += reinterpret_cast<const volatile T*>(slot_ptr(local, parity, q))[i];
+    buf[i] = s;
+  }
+}
+
+}  // namespace
+
+cudaError_t PeerReduce::create_local(int rank, int world, void* handle64) {
+  w.rank = rank; w.world = world;
+  for (auto& p : w.win) p = nullptr;
+  void* p = nullptr;
+  cudaError_t e = cudaMalloc(&p, kPeerWindowBytes + 256);
+  if (e != cudaSuccess) return e;
+  e = cudaMemset(p, 0, kPeerWindowBytes + 256);
+  if (e != cudaSuccess) return e;
+  w.win[rank] = static_cast<unsigned char*>(p);
+  d_err = reinterpret_cast<int*>(w.win[rank] + kPeerWindowBytes);
+  cudaIpcMemHandle_t h;
+  e = cudaIpcGetMemHandle(&h, p);
+  if (e != cudaSuccess) return e;
+  static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
+  memcpy(handle64, &h, 64);
+  return cudaDeviceSynchronize();
+}
+
+bool PeerReduce::open_peers(const void* handles) {
+  bool all = true;
+  for (int p = 0; p < w.world; ++p) {
+    if (p == w.rank) continue;
+    cudaIpcMemHandle_t h;
+    memcpy(&h, static_cast<const char*>(handles) + (size_t)p * 64, 64);
+    void* q = nullptr;
+    if (cudaIpcOpenMemHandle(&q, h, cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) { cudaGetLastError(); all = false; q = nullptr; }
+    w.win[p] = static_cast<unsigned char*>(q);
+  }
+  return all;
+}
+
+void PeerReduce::destroy() {
+  for (int p = 0; p < w.world; ++p) {
+    if (!w.win[p]) continue;
+    if (p == w.rank) cudaFree(w.win[p]); else cudaIpcCloseMemHandle(w.win[p]);
+    w.win[p] = nullptr;
+  }
+  ok = false; d_err = nullptr;
+}
+
+void PeerReduce::allreduce_f64(double* buf, int n, cudaStream_t st) {
+  k_peer_allreduce<double><<<1, n >= 1024 ? 1024 : (n > 32 ? ((n + 31) / 32) * 32 : 32), 0, st>>>(w, buf, n, ++seq, d_err);
+}
+void PeerReduce::allreduce_u32(unsigned int* buf, int n, cudaStream_t st) {
+  k_peer_allreduce<unsigned int><<<1, n >= 1024 ? 1024 : (n > 32 ? ((n + 31) / 32) * 32 : 32), 0, st>>>(w, buf, n, ++seq, d_err);
+}
+int PeerReduce::error(cudaStream_t st) const {
+  if (!d_err) return 0;
+  int e = 0;
+  cudaMemcpyAsync(&e, d_err, sizeof(int), cudaMemcpyDeviceToHost, st);
+  cudaStreamSynchronize(st);
+  return e;
+}

@@ -298,3 +298,40 @@ def test_invalid_ids_are_rejected_at_upload():
     s = BundleAdjusterGPU(p.lm_dim, p.pose_dim)
     with pytest.raises(RuntimeError, match="out of range"):
         s.load(p)
+
+
+def test_landmarks_stay_on_device_until_asked_for():
+    """Solve() leaves the refined landmarks on the device; get_landmarks reads them straight into the caller's
+    (optionally preallocated) buffers, sync_state refreshes the host copies, and a problem that is set up again
+    without new landmarks (only the residuals are re-sent) continues from the refined ones."""
+    import ctypes as C
+    from ba_b200.abi import _p
+    p = synth.make("c1", 0.3)
+    a = p.arrays()
+    g = gpu(p)
+    g.solve(3)
+    lm1 = g.get_landmarks()
+    n = len(a["lm_x_w"])
+    out = dict(x_w=np.full((n, 4), np.nan), x_s=np.full((n, 4), np.nan), is_reliable=np.full(n, 7, np.uint8),
+               num_outlier_residuals=np.full(n, 9, np.uint32))
+    lm2 = g.get_landmarks(out=out)
+    assert lm2["x_w"] is out["x_w"]
+    for k in lm1:
+        assert np.array_equal(lm1[k], lm2[k]), k
+    assert not np.array_equal(lm1["x_w"], a["lm_x_w"])          # the solve moved them
+    g.sync_state()
+    lm3 = g.get_landmarks()
+    for k in lm1:
+        assert np.array_equal(lm1[k], lm3[k]), k
+    # reference run: 3 + 2 iterations in two calls on one handle without touching the problem in between
+    r = gpu(p); r.solve(3); r.solve(2)
+    want = r.get_landmarks()
+    # same, but the projection residuals are sent again between the calls: full set-up from the host vectors, whose
+    # landmark part has to be fetched from the device first
+    h = gpu(p); h.solve(3)
+    h._check(h._f("set_proj_residuals")(h.h, C.c_uint32(len(a["proj_z"])), _p(a["proj_z"], np.float64), _p(a["proj_meas_pose"], np.uint32),
+                                        _p(a["proj_lm"], np.uint32), _p(a["proj_cam"], np.uint32), _p(a["proj_weight"], np.float64)))
+    h.solve(2)
+    got = h.get_landmarks()
+    np.testing.assert_allclose(got["x_w"], want["x_w"], rtol=0, atol=1e-9)
+    np.testing.assert_allclose(h.get_poses()["t_wp"], r.get_poses()["t_wp"], rtol=0, atol=1e-9)
