@@ -17,6 +17,7 @@
 #include <mutex>
 #include <string>
 #include <unordered_set>
+#include <thread>
 #include <vector>
 #include <dlfcn.h>
 #include "ba_gpu.h"
@@ -43,6 +44,7 @@ struct PhaseClock {
     t = n;
   }
 };
+struct ApiClock { const char* what; PhaseClock pc; explicit ApiClock(const char* w) : what(w) {} ~ApiClock() { pc.lap(what); } };
 int fail(int code, const std::string& msg) { g_err = msg; return code; }
 
 #define CU(x)                                                                                        \
@@ -127,7 +129,10 @@ struct bagpu_handle_s {
   std::vector<double> pose_t7, pose_v, pose_b;
   std::vector<uint8_t> pose_active, pose_mask_used, pose_mask;   // mask: D per pose, 1 = free
   std::vector<double> lm_xw, lm_xs;
-  bool lm_host_fresh = true;   // false: the refined landmarks live on the device only (fetched on demand)
+  bool lm_host_fresh = true;   // false: the current landmarks live on the device only (sent there by the setter, or
+                               // refined by a Solve()); the host vectors are filled on demand
+  bool lm_rel_on_device = false;
+  size_t n_lm_set = 0;         // landmarks handed to bagpu_set_landmarks
   std::vector<uint32_t> lm_ref_pose, lm_ref_cam;
   std::vector<uint8_t> lm_active, lm_reliable;
   std::vector<uint32_t> lm_outliers;
@@ -216,11 +221,9 @@ struct bagpu_handle_s {
     if (has_device) return;
     int n = 0;
     if (cudaGetDeviceCount(&n) != cudaSuccess || n == 0) throw std::string("no CUDA device (the product path has no CPU fallback)");
-    cudaDeviceProp prop;
     int dev = 0;
     CU(cudaGetDevice(&dev));
-    CU(cudaGetDeviceProperties(&prop, dev));
-    sms = prop.multiProcessorCount;
+    CU(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));   // (cudaGetDeviceProperties takes milliseconds)
     set_sm_count(sms);
     CU(cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking));
     for (auto& e : ev) CU(cudaEventCreate(&e));
@@ -232,7 +235,7 @@ struct bagpu_handle_s {
   void setup() {
     n_cams = (int)cam_params.size() / 4;
     n_poses = (int)pose_t7.size() / 7;
-    n_lms = (int)lm_xw.size() / 4;
+    n_lms = (int)n_lm_set;
     n_obs = n_obs_total = (int)n_raw;
     if (n_cams == 0) { n_cams = 1; cam_params = {1, 1, 0, 0}; cam_tvs = {0, 0, 0, 1, 0, 0, 0}; }
     pose_opt.assign(n_poses, -1); n_ap = 0;
@@ -310,10 +313,6 @@ struct bagpu_handle_s {
     d_cnt.download(&n_cond_proj, 1, st);
     sync();
     pc.lap("  symbolic: sort + flags + pattern");
-    int lms_with_obs = 0;
-    for (int l = 0; l < n_lms; ++l) lms_with_obs += gstarts[l + 1] > gstarts[l];
-    const double mean_track = lms_with_obs ? (double)n / lms_with_obs : 0.0;
-    G = mean_track <= 4 ? 4 : mean_track <= 8 ? 8 : mean_track <= 16 ? 16 : 32;
     // 3. landmark sharding: contiguous landmark ranges balanced by observation count; in the
     // landmark-major stream a shard is one contiguous slice
     if (world > 1) {
@@ -331,36 +330,49 @@ struct bagpu_handle_s {
     n_obs = (int)(s_hi - s_lo);
     launch_local_starts(d_gstarts.p, (uint32_t)n_lms, s_lo, s_hi, d_lm_obs_start.p, st);
     // warp tasks of the landmark-major kernels: runs of whole landmarks with at most 32 observations in total
-    // (first observation, count); landmarks with longer tracks are listed apart (one warp each)
-    {
-      std::vector<uint2> tasks; std::vector<uint32_t> longs;
-      tasks.reserve((size_t)n_obs / 24 + 16);
+    // (first observation, count); landmarks with longer tracks are listed apart (one warp each).  Greedy packing on
+    // the host, the landmark range cut into independent pieces (one thread each; a piece boundary ends a task), while
+    // the device gathers and sorts the local stream (below).
+    auto pack_tasks = [&]() {
+      const int n_own = lm_owner_hi - lm_owner_lo;
+      const int n_thr = n_own >= (1 << 16) ? 8 : 1;
+      std::vector<std::vector<uint2>> tparts(n_thr); std::vector<std::vector<uint32_t>> lparts(n_thr);
       auto lstart = [&](int l) { const uint32_t v = gstarts[l]; return (v < s_lo ? s_lo : (v > s_hi ? s_hi : v)) - s_lo; };
-      int l = lm_owner_lo;
-      uint32_t b = lstart(l);
-      while (l < lm_owner_hi) {
-        uint32_t e1 = lstart(l + 1);
-        if (e1 - b > 32) { longs.push_back((uint32_t)l); ++l; b = e1; continue; }
-        const uint32_t first = b;
-        uint32_t end = b;
-        while (l < lm_owner_hi) {
-          e1 = lstart(l + 1);
-          if (e1 - end > 32 || e1 - first > 32) break;
-          end = e1; ++l;
+      auto work = [&](int t) {
+        const int l_end = lm_owner_lo + (int)((long long)n_own * (t + 1) / n_thr);
+        int l = lm_owner_lo + (int)((long long)n_own * t / n_thr);
+        std::vector<uint2>& tasks = tparts[t]; std::vector<uint32_t>& longs = lparts[t];
+        tasks.reserve((size_t)(l_end - l) / 4 + 16);
+        uint32_t b = lstart(l);
+        while (l < l_end) {
+          uint32_t e1 = lstart(l + 1);
+          if (e1 - b > 32) { longs.push_back((uint32_t)l); ++l; b = e1; continue; }
+          const uint32_t first = b;
+          uint32_t end = b;
+          while (l < l_end) {
+            e1 = lstart(l + 1);
+            if (e1 - end > 32 || e1 - first > 32) break;
+            end = e1; ++l;
+          }
+          if (end > first) tasks.push_back(make_uint2(first, end - first));
+          b = end;
         }
-        if (end > first) tasks.push_back(make_uint2(first, end - first));
-        b = end;
-      }
+      };
+      if (n_thr == 1) work(0);
+      else { std::vector<std::thread> th; for (int t = 0; t < n_thr; ++t) th.emplace_back(work, t); for (auto& x : th) x.join(); }
+      std::vector<uint2> tasks; std::vector<uint32_t> longs;
+      for (int t = 0; t < n_thr; ++t) { tasks.insert(tasks.end(), tparts[t].begin(), tparts[t].end()); longs.insert(longs.end(), lparts[t].begin(), lparts[t].end()); }
       n_tasks = (int)tasks.size(); n_long = (int)longs.size();
       d_tasks.upload(tasks, st); d_long_lms.upload(longs, st);
       sync();
-    }
+    };
     // 4. the local stream: gathered values, pose-major record slots
     const uint32_t nl = (uint32_t)n_obs;
     d_obs_z.alloc(nl); d_obs_pose.alloc(nl); d_obs_w0.alloc(nl); d_obs_slot.alloc(nl);
     if (n_cams > 1) d_obs_cam.alloc(nl);
     launch_gather_obs(d_perm_global.p + s_lo, nl, d_raw_z.p, d_raw_pose.p, raw_has_cam ? d_raw_cam.p : nullptr, raw_has_w0 ? d_raw_w0.p : nullptr,
                       d_obs_z.p, d_obs_pose.p, n_cams > 1 ? d_obs_cam.p : nullptr, d_obs_w0.p, nullptr, st);
+    if (!nl) pack_tasks();
     if (nl) {
       DevBuf<uint32_t> d_keys, d_keys_s, d_vals_s, d_starts; DevBuf<uint8_t> d_any;
       d_keys.alloc(std::max<uint32_t>(nl, (uint32_t)n_lms)); d_keys_s.alloc(std::max<uint32_t>(nl, (uint32_t)n_lms));
@@ -371,7 +383,7 @@ struct bagpu_handle_s {
       launch_assign_slots(d_keys_s.p, d_vals_s.p, nl, (uint32_t)n_ap, d_obs_slot.p, st);
       launch_key_starts(d_keys_s.p, nl, (uint32_t)n_ap, d_starts.p, st);
       d_starts.download(pose_rec_start.data(), (size_t)n_ap + 1, st);
-      sync();
+      pack_tasks();   // host work while the sorts run; ends with a sync
       n_rec = pose_rec_start[n_ap];
       if (L == 1) {   // reference-pose record slots of the landmarks
         d_lm_rslot.alloc((size_t)n_lms);
@@ -494,9 +506,11 @@ struct bagpu_handle_s {
     d_pose_opt.upload(pose_opt, st); d_pose_free.alloc(n_poses); d_pose_mask_used.alloc(n_poses);
     d_Tsw.alloc((size_t)n_poses * n_cams * 12); d_Tws.alloc((size_t)n_poses * n_cams * 12); d_Rwp.alloc((size_t)n_poses * 9);
     // landmarks
-    d_lm_xw.upload(lm_xw, st); d_lm_x.alloc(lm_xw.size()); d_bk_lm_x.alloc(lm_xw.size());
+    if (lm_host_fresh) d_lm_xw.upload(lm_xw, st);
+    d_lm_x.alloc(4 * n_lm_set); d_bk_lm_x.alloc(4 * n_lm_set);
     d_lm_ref_pose.upload(lm_ref_pose, st); d_lm_ref_cam.upload(lm_ref_cam, st); d_lm_opt.upload(lm_opt, st);
-    d_lm_reliable.upload(lm_reliable, st); d_bk_rel.alloc(lm_reliable.size()); d_lm_outliers.alloc(n_lms);
+    if (!lm_rel_on_device) { d_lm_reliable.upload(lm_reliable, st); lm_rel_on_device = true; }
+    d_bk_rel.alloc(lm_reliable.size()); d_lm_outliers.alloc(n_lms);
     d_lm_outliers.zero(st);
     pc.lap("  upload: cameras, poses, landmarks");
     // observations: landmark-major stream, record slots and the tile pattern, derived on the device
@@ -1039,7 +1053,7 @@ struct bagpu_handle_s {
     PhaseClock pc;
     ensure_device(); pc.lap("ensure_device");
     maha0_valid = false;
-    if (dirty) { fetch_landmarks_host(); setup(); pc.lap("setup (host symbolic)"); upload_all(); sync(); pc.lap("upload_all"); solved_once = false; }
+    if (dirty) { setup(); pc.lap("setup (host symbolic)"); upload_all(); sync(); pc.lap("upload_all"); solved_once = false; }
     else apply_options();
     // Solve() prologue (cpp:287-296)
     launch_pose_frames(P, st); ++launches;
@@ -1069,6 +1083,7 @@ struct bagpu_handle_s {
   // the host copies of the landmark state, needed only when the problem is set up again from the host vectors
   void fetch_landmarks_host() {
     if (lm_host_fresh || !n_lms || !d_lm_xw.p) { lm_host_fresh = true; return; }
+    lm_xw.resize(4 * n_lm_set);
     d_lm_xw.download(lm_xw.data(), lm_xw.size(), st);
     lm_xs.resize(lm_xw.size());
     d_lm_x.download(lm_xs.data(), lm_xs.size(), st);
@@ -1268,6 +1283,7 @@ int bagpu_set_cameras(bagpu_handle h, uint32_t n, const double* p, const double*
 }
 int bagpu_set_poses(bagpu_handle h, uint32_t n, const double* t, const double* v, const double* b, const uint8_t* a,
                     const uint8_t* mu, const uint8_t* m) {
+  ApiClock api_clock("bagpu_set_poses");
   const int D = h->D;
   h->pose_t7.assign(t, t + 7 * (size_t)n);
   if (v) h->pose_v.assign(v, v + 3 * (size_t)n); else h->pose_v.assign(3 * (size_t)n, 0.0);
@@ -1279,10 +1295,20 @@ int bagpu_set_poses(bagpu_handle h, uint32_t n, const double* t, const double* v
   return BAGPU_OK;
 }
 int bagpu_set_landmarks(bagpu_handle h, uint32_t n, const double* x, const uint32_t* rp, const uint32_t* rc, const uint8_t* a) {
+  ApiClock api_clock("bagpu_set_landmarks");
   const size_t np = h->pose_t7.size() / 7;
   for (uint32_t i = 0; i < n; ++i) if (rp[i] >= np) return fail(BAGPU_ERR_INVALID, "landmark ref_pose_id out of range");
-  h->lm_xw.assign(x, x + 4 * (size_t)n); h->lm_xs.clear();   // x_s is filled by the first Solve()
-  h->lm_host_fresh = true;
+  // with a usable device the positions go straight into HBM (the host copy is made only if somebody asks for it)
+  bool dev = true;
+  try { h->ensure_device(); } catch (const std::string&) { dev = false; }
+  h->n_lm_set = n; h->lm_xs.clear();   // x_s is filled by the first Solve()
+  h->lm_rel_on_device = false;
+  if (dev && n > 0) {
+    GUARD(h->d_lm_xw.upload(x, 4 * (size_t)n, h->st); h->sync();)   // the caller's buffer is free again on return
+    h->lm_xw.clear(); h->lm_host_fresh = false;
+  } else {
+    h->lm_xw.assign(x, x + 4 * (size_t)n); h->lm_host_fresh = true;
+  }
   h->lm_ref_pose.assign(rp, rp + n);
   if (rc) h->lm_ref_cam.assign(rc, rc + n); else h->lm_ref_cam.assign(n, 0);
   if (a) h->lm_active.assign(a, a + n); else h->lm_active.assign(n, 1);
@@ -1292,7 +1318,8 @@ int bagpu_set_landmarks(bagpu_handle h, uint32_t n, const double* x, const uint3
 }
 int bagpu_set_proj_residuals(bagpu_handle h, uint32_t n, const double* z, const uint32_t* mp, const uint32_t* lm, const uint32_t* cam,
                              const double* w) {
-  const size_t np = h->pose_t7.size() / 7, nl = h->lm_xw.size() / 4;
+  ApiClock api_clock("bagpu_set_proj_residuals");
+  const size_t np = h->pose_t7.size() / 7, nl = h->n_lm_set;
   bool dev = true;
   try { h->ensure_device(); } catch (const std::string&) { dev = false; }
   h->raw_on_device = false; h->raw_has_cam = cam != nullptr; h->raw_has_w0 = w != nullptr; h->n_raw = n;
@@ -1303,6 +1330,7 @@ int bagpu_set_proj_residuals(bagpu_handle h, uint32_t n, const double* z, const 
       h->d_raw_z.upload(reinterpret_cast<const double2*>(z), n, h->st); h->d_raw_pose.upload(mp, n, h->st); h->d_raw_lm.upload(lm, n, h->st);
       if (cam) h->d_raw_cam.upload(cam, n, h->st);
       if (w) h->d_raw_w0.upload(w, n, h->st);
+      if (api_clock.pc.on) { h->sync(); api_clock.pc.lap("  raw observation upload"); }
       h->d_lm_ref_pose.upload(h->lm_ref_pose, h->st); h->d_lm_ref_cam.upload(h->lm_ref_cam, h->st);
       DevBuf<int> flag; flag.alloc(2); flag.zero(h->st);
       launch_validate_obs(h->d_raw_pose.p, h->d_raw_lm.p, cam ? h->d_raw_cam.p : nullptr, n, (uint32_t)np, (uint32_t)nl, h->L, h->d_lm_ref_pose.p,
@@ -1388,6 +1416,7 @@ int bagpu_build(bagpu_handle h, float* ms_out) {
 }
 
 int bagpu_get_poses(bagpu_handle h, double* t, double* v, double* b, uint8_t* mu, uint8_t* m) {
+  ApiClock api_clock("bagpu_get_poses");
   const size_t n = h->pose_t7.size() / 7;
   if (t) memcpy(t, h->pose_t7.data(), sizeof(double) * 7 * n);
   if (v) memcpy(v, h->pose_v.data(), sizeof(double) * 3 * n);
@@ -1397,8 +1426,16 @@ int bagpu_get_poses(bagpu_handle h, double* t, double* v, double* b, uint8_t* mu
   return BAGPU_OK;
 }
 int bagpu_get_landmarks(bagpu_handle h, double* xw, double* xs, uint8_t* rel, uint32_t* nout) {
-  const size_t n = h->lm_xw.size() / 4;
-  if (!h->lm_host_fresh && !h->dirty) { GUARD(h->copy_landmarks_out(xw, xs, rel, nout);) return BAGPU_OK; }
+  ApiClock api_clock("bagpu_get_landmarks");
+  const size_t n = h->n_lm_set;
+  if (!h->lm_host_fresh && h->lm_rel_on_device) { GUARD(h->copy_landmarks_out(xw, xs, rel, nout);) return BAGPU_OK; }
+  if (!h->lm_host_fresh) {   // set but not solved yet: positions as sent, x_s not known
+    GUARD(if (xw) { h->d_lm_xw.download(xw, 4 * n, h->st); h->sync(); })
+    if (xs) memset(xs, 0, sizeof(double) * 4 * n);
+    if (rel) memcpy(rel, h->lm_reliable.data(), n);
+    if (nout) memcpy(nout, h->lm_outliers.data(), sizeof(uint32_t) * n);
+    return BAGPU_OK;
+  }
   if (xw) memcpy(xw, h->lm_xw.data(), sizeof(double) * 4 * n);
   if (xs) { if (h->lm_xs.size() == 4 * n) memcpy(xs, h->lm_xs.data(), sizeof(double) * 4 * n); else memset(xs, 0, sizeof(double) * 4 * n); }
   if (rel) memcpy(rel, h->lm_reliable.data(), n);
