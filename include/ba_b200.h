@@ -176,7 +176,11 @@ int bagpu_solve(bagpu_handle h, uint32_t max_iter, double gn_damping,
  * src/BundleAdjuster.cpp:300-302,309,629).  ms_out (may be NULL) = device time. */
 int bagpu_build(bagpu_handle h, float* ms_out);
 
-/* ---- results (HBM -> host). Buffers may be NULL to skip. ------------------------- */
+/* ---- results (HBM -> host). Buffers may be NULL to skip. -------------------------
+ * After a solve only the poses are copied back eagerly; the refined landmarks stay in HBM and
+ * bagpu_get_landmarks copies them straight into the caller's arrays (page-locked ones, see
+ * bagpu_host_alloc, take the copy at full PCIe rate).  The library's own host copies of the
+ * landmark state are refreshed by bagpu_sync_state. */
 int bagpu_get_poses(bagpu_handle h, double* t_wp7, double* v_w3, double* b6,
                     uint8_t* mask_used, uint8_t* mask);
 int bagpu_get_landmarks(bagpu_handle h, double* x_w4, double* x_s4, uint8_t* is_reliable,
@@ -200,7 +204,11 @@ int bagpu_get_system(bagpu_handle h, double* s_dense, double* rhs_sc, double* rh
 int bagpu_dump(bagpu_handle h, const char* dir);
 
 /* ---- multi-GPU (landmark sharding) --------------------------------- */
-/* nccl_unique_id: 128 bytes from bagpu_nccl_unique_id() on rank 0, broadcast by the caller. */
+/* nccl_unique_id: 128 bytes from bagpu_nccl_unique_id() on rank 0, broadcast by the caller.
+ * bagpu_comm_init is collective: it creates the NCCL communicator, connects its channels (one small
+ * and one bulk warm-up all-reduce) and maps the peers' windows for the small reductions over NVLink
+ * peer memory (CUDA IPC; all ranks fall back to NCCL together if a window cannot be mapped;
+ * BAGPU_P2P=0 in the environment forces NCCL). */
 int bagpu_nccl_unique_id(void* out128);
 int bagpu_comm_init(bagpu_handle h, int rank, int world, const void* nccl_unique_id128);
 /* per-phase device timings of the last solve/build in ms: see bagpu_phase */

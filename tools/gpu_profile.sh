@@ -7,7 +7,7 @@ timeout 600 python bench.py --steps 2 --warmup 1 --no-cpu-baseline > gpurun_out/
 timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 3000 --csv --log-file gpurun_out/${TAG}_launches_c2.csv \
   python bench.py --steps 2 --warmup 1 --no-cpu-baseline > gpurun_out/ncu_list_${TAG}.log 2>&1
 echo "launch list rc=$?"
-timeout 900 ncu --set full --clock-control none --import-source on -k regex:"k_reduce_blocks|k_linearize|k_chol_dataflow" -c 3 -o gpurun_out/${TAG}_full_build_c2 -f \
+timeout 900 ncu --set full --clock-control none --import-source on -k regex:"k_reduce_blocks|k_linearize|k_chol_dataflow" -c 5 -o gpurun_out/${TAG}_full_build_c2 -f \
   python bench.py --steps 2 --warmup 1 --no-cpu-baseline > gpurun_out/ncu_full_${TAG}.log 2>&1
 echo "full capture rc=$?"
 ncu -i gpurun_out/${TAG}_full_build_c2.ncu-rep --page raw --csv > gpurun_out/${TAG}_full_build_c2_raw.csv 2>/dev/null
