@@ -1261,6 +1261,24 @@ int bagpu_create(const bagpu_dims* d, bagpu_handle* out) {
 void bagpu_destroy(bagpu_handle h) {
   if (!h) return;
   if (h->st) cudaStreamSynchronize(h->st);
+  bool comm_stuck = false;
+  if (h->comm && h->peer.w.world > 1 && h->peer.w.win[h->peer.w.rank]) {
+    // CUDA IPC: a window may be freed only after every importer has unmapped it.  Unmap the peers' windows, then meet
+    // the other ranks in one tiny NCCL all-reduce before freeing.  The wait is bounded: if the others never come (a
+    // rank died) the window and the communicator are abandoned instead of hanging the caller.
+    h->peer.close_peers();
+    try {
+      DevBuf<unsigned int> one; one.alloc(1); one.zero(h->st);
+      h->allreduce_u32(one.p, 1);
+      const auto t0 = std::chrono::steady_clock::now();
+      while (cudaStreamQuery(h->st) == cudaErrorNotReady) {
+        if (std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count() > 10.0) { comm_stuck = true; break; }
+        std::this_thread::sleep_for(std::chrono::microseconds(50));
+      }
+      if (comm_stuck) one.p = nullptr;   // still in use by the pending collective
+    } catch (const std::string&) {}
+  }
+  if (comm_stuck) return;   // abandon the handle (freeing its buffers would wait for the pending collective): the job is failing anyway
   h->peer.destroy();
   if (h->comm && g_nccl.commDestroy) g_nccl.commDestroy(h->comm);
   if (h->ev_ok) for (auto& e : h->ev) cudaEventDestroy(e);
@@ -1628,7 +1646,13 @@ int bagpu_comm_init(bagpu_handle h, int rank, int world, const void* id128) {
       h->allreduce_u32(d_tab, 1);
       CU(cudaMemcpyAsync(tab.data(), d_tab, 4, cudaMemcpyDeviceToHost, h->st));
       CU(cudaStreamSynchronize(h->st));
-      if (tab[0] == (unsigned int)world) h->peer.ok = true; else h->peer.destroy();
+      if (tab[0] == (unsigned int)world) h->peer.ok = true;
+      else {   // stay on NCCL: unmap, meet the others, then free (same order as in bagpu_destroy)
+        h->peer.close_peers();
+        h->allreduce_u32(d_tab, 1);
+        CU(cudaStreamSynchronize(h->st));
+        h->peer.destroy();
+      }
       if (getenv("BAGPU_TIMING")) fprintf(stderr, "[bagpu] rank %d: peer-memory reductions %s\n", rank, h->peer.ok ? "on" : "off (NCCL only)");
     }
   })

@@ -76,13 +76,19 @@ bool PeerReduce::open_peers(const void* handles) {
   return all;
 }
 
-void PeerReduce::destroy() {
+void PeerReduce::close_peers() {
   for (int p = 0; p < w.world; ++p) {
-    if (!w.win[p]) continue;
-    if (p == w.rank) cudaFree(w.win[p]); else cudaIpcCloseMemHandle(w.win[p]);
+    if (!w.win[p] || p == w.rank) continue;
+    cudaIpcCloseMemHandle(w.win[p]);
     w.win[p] = nullptr;
   }
-  ok = false; d_err = nullptr;
+  ok = false;
+}
+
+void PeerReduce::destroy() {
+  close_peers();
+  if (w.world > 0 && w.win[w.rank]) { cudaFree(w.win[w.rank]); w.win[w.rank] = nullptr; }
+  d_err = nullptr;
 }
 
 void PeerReduce::allreduce_f64(double* buf, int n, cudaStream_t st) {

@@ -31,7 +31,8 @@ struct PeerReduce {
   cudaError_t create_local(int rank, int world, void* handle64);
   // open the peers' windows; returns false when peer mapping is not possible (the caller falls back to NCCL)
   bool open_peers(const void* handles /* world x 64 bytes */);
-  void destroy();
+  void close_peers();   // unmap the peers' windows (every rank must have done this before any rank frees its own)
+  void destroy();       // close_peers + free the local window
   bool fits(size_t bytes) const { return ok && bytes <= kPeerSlotBytes; }
   void allreduce_f64(double* buf, int n, cudaStream_t st);
   void allreduce_u32(unsigned int* buf, int n, cudaStream_t st);
