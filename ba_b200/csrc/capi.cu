@@ -159,6 +159,18 @@ struct bagpu_handle_s {
   unsigned int n_cond_proj = 0;
   DevBuf<uint2> d_tasks; DevBuf<uint32_t> d_long_lms;   // packed warp tasks of the landmark-major stream (schur_kernels.cu)
   int n_tasks = 0, n_long = 0;
+  std::thread packer;                       // greedy task packing, runs beside the device set-up
+  std::vector<uint32_t> pk_gstarts, pk_longs; std::vector<uint2> pk_tasks;
+  void join_packer() { if (packer.joinable()) packer.join(); }
+  ~bagpu_handle_s() { join_packer(); }
+  void finish_task_packing() {
+    if (!packer.joinable()) return;
+    packer.join();
+    n_tasks = (int)pk_tasks.size(); n_long = (int)pk_longs.size();
+    d_tasks.upload(pk_tasks, st); d_long_lms.upload(pk_longs, st);
+    sync();
+    std::vector<uint32_t>().swap(pk_gstarts);
+  }
   std::vector<uint32_t> pose_rec_start, pose_lmrec_start;   // pose-major record slots (ba_gpu.h)
   uint32_t n_rec = 0, n_lmrec = 0;
   int n_items = 0, n_items_sym = 0;
@@ -328,51 +340,44 @@ struct bagpu_handle_s {
       s_lo = gstarts[lo]; s_hi = gstarts[hi];
     }
     n_obs = (int)(s_hi - s_lo);
+    if (pc.on) { sync(); pc.lap("    sharding"); }
     launch_local_starts(d_gstarts.p, (uint32_t)n_lms, s_lo, s_hi, d_lm_obs_start.p, st);
     // warp tasks of the landmark-major kernels: runs of whole landmarks with at most 32 observations in total
-    // (first observation, count); landmarks with longer tracks are listed apart (one warp each).  Greedy packing on
-    // the host, the landmark range cut into independent pieces (one thread each; a piece boundary ends a task), while
-    // the device gathers and sorts the local stream (below).
-    auto pack_tasks = [&]() {
-      const int n_own = lm_owner_hi - lm_owner_lo;
-      const int n_thr = n_own >= (1 << 16) ? 8 : 1;
-      std::vector<std::vector<uint2>> tparts(n_thr); std::vector<std::vector<uint32_t>> lparts(n_thr);
-      auto lstart = [&](int l) { const uint32_t v = gstarts[l]; return (v < s_lo ? s_lo : (v > s_hi ? s_hi : v)) - s_lo; };
-      auto work = [&](int t) {
-        const int l_end = lm_owner_lo + (int)((long long)n_own * (t + 1) / n_thr);
-        int l = lm_owner_lo + (int)((long long)n_own * t / n_thr);
-        std::vector<uint2>& tasks = tparts[t]; std::vector<uint32_t>& longs = lparts[t];
-        tasks.reserve((size_t)(l_end - l) / 4 + 16);
+    // (first observation, count); landmarks with longer tracks are listed apart (one warp each).  Greedy packing from
+    // the CSR bounds on a host thread that runs beside the rest of the set-up; finish_task_packing() joins it.
+    join_packer();
+    pk_gstarts.swap(gstarts);
+    pk_tasks.clear(); pk_longs.clear();
+    {
+      const int lo = lm_owner_lo, hi = lm_owner_hi;
+      const uint32_t slo = s_lo, shi = s_hi;
+      packer = std::thread([this, lo, hi, slo, shi]() {
+        const std::vector<uint32_t>& gs = pk_gstarts;
+        auto lstart = [&](int l) { const uint32_t v = gs[l]; return (v < slo ? slo : (v > shi ? shi : v)) - slo; };
+        pk_tasks.reserve((size_t)(shi - slo) / 24 + 16);
+        int l = lo;
         uint32_t b = lstart(l);
-        while (l < l_end) {
+        while (l < hi) {
           uint32_t e1 = lstart(l + 1);
-          if (e1 - b > 32) { longs.push_back((uint32_t)l); ++l; b = e1; continue; }
+          if (e1 - b > 32) { pk_longs.push_back((uint32_t)l); ++l; b = e1; continue; }
           const uint32_t first = b;
           uint32_t end = b;
-          while (l < l_end) {
+          while (l < hi) {
             e1 = lstart(l + 1);
             if (e1 - end > 32 || e1 - first > 32) break;
             end = e1; ++l;
           }
-          if (end > first) tasks.push_back(make_uint2(first, end - first));
+          if (end > first) pk_tasks.push_back(make_uint2(first, end - first));
           b = end;
         }
-      };
-      if (n_thr == 1) work(0);
-      else { std::vector<std::thread> th; for (int t = 0; t < n_thr; ++t) th.emplace_back(work, t); for (auto& x : th) x.join(); }
-      std::vector<uint2> tasks; std::vector<uint32_t> longs;
-      for (int t = 0; t < n_thr; ++t) { tasks.insert(tasks.end(), tparts[t].begin(), tparts[t].end()); longs.insert(longs.end(), lparts[t].begin(), lparts[t].end()); }
-      n_tasks = (int)tasks.size(); n_long = (int)longs.size();
-      d_tasks.upload(tasks, st); d_long_lms.upload(longs, st);
-      sync();
-    };
+      });
+    }
     // 4. the local stream: gathered values, pose-major record slots
     const uint32_t nl = (uint32_t)n_obs;
     d_obs_z.alloc(nl); d_obs_pose.alloc(nl); d_obs_w0.alloc(nl); d_obs_slot.alloc(nl);
     if (n_cams > 1) d_obs_cam.alloc(nl);
     launch_gather_obs(d_perm_global.p + s_lo, nl, d_raw_z.p, d_raw_pose.p, raw_has_cam ? d_raw_cam.p : nullptr, raw_has_w0 ? d_raw_w0.p : nullptr,
                       d_obs_z.p, d_obs_pose.p, n_cams > 1 ? d_obs_cam.p : nullptr, d_obs_w0.p, nullptr, st);
-    if (!nl) pack_tasks();
     if (nl) {
       DevBuf<uint32_t> d_keys, d_keys_s, d_vals_s, d_starts; DevBuf<uint8_t> d_any;
       d_keys.alloc(std::max<uint32_t>(nl, (uint32_t)n_lms)); d_keys_s.alloc(std::max<uint32_t>(nl, (uint32_t)n_lms));
@@ -383,7 +388,7 @@ struct bagpu_handle_s {
       launch_assign_slots(d_keys_s.p, d_vals_s.p, nl, (uint32_t)n_ap, d_obs_slot.p, st);
       launch_key_starts(d_keys_s.p, nl, (uint32_t)n_ap, d_starts.p, st);
       d_starts.download(pose_rec_start.data(), (size_t)n_ap + 1, st);
-      pack_tasks();   // host work while the sorts run; ends with a sync
+      sync();
       n_rec = pose_rec_start[n_ap];
       if (L == 1) {   // reference-pose record slots of the landmarks
         d_lm_rslot.alloc((size_t)n_lms);
@@ -509,8 +514,12 @@ struct bagpu_handle_s {
     if (lm_host_fresh) d_lm_xw.upload(lm_xw, st);
     d_lm_x.alloc(4 * n_lm_set); d_bk_lm_x.alloc(4 * n_lm_set);
     d_lm_ref_pose.upload(lm_ref_pose, st); d_lm_ref_cam.upload(lm_ref_cam, st); d_lm_opt.upload(lm_opt, st);
-    if (!lm_rel_on_device) { d_lm_reliable.upload(lm_reliable, st); lm_rel_on_device = true; }
-    d_bk_rel.alloc(lm_reliable.size()); d_lm_outliers.alloc(n_lms);
+    if (!lm_rel_on_device) {   // every landmark starts reliable (host copies of these flags exist only after a fetch)
+      d_lm_reliable.alloc(n_lm_set);
+      if (n_lm_set) CU(cudaMemsetAsync(d_lm_reliable.p, 1, n_lm_set, st));
+      lm_rel_on_device = true;
+    }
+    d_bk_rel.alloc(n_lm_set); d_lm_outliers.alloc(n_lms);
     d_lm_outliers.zero(st);
     pc.lap("  upload: cameras, poses, landmarks");
     // observations: landmark-major stream, record slots and the tile pattern, derived on the device
@@ -585,6 +594,8 @@ struct bagpu_handle_s {
     sync(); pc.lap("  upload: rest");
     build_reduce_items();
     pc.lap("  build_reduce_items");
+    finish_task_packing();
+    pc.lap("  task packing (join)");
     dirty = false;
   }
 
@@ -596,7 +607,9 @@ struct bagpu_handle_s {
     n_pairs = 0; n_items = 0; n_items_sym = 0;
     if (L == 0 || n_obs == 0 || n_ap == 0) return;
     std::vector<unsigned long long> bkey; std::vector<uint32_t> bcnt; std::string err;
+    PhaseClock pcr;
     if (build_pair_lists(P, st, &d_pairs, &n_pairs, bkey, bcnt, err) != 0) throw std::string("pair lists: ") + err;
+    pcr.lap("    pair lists (device)");
     std::vector<ReduceItem> items, sym;
     uint32_t n_partial = 0, n_groups = 0;
     auto push_block = [&](std::vector<ReduceItem>& out, std::vector<ReduceItem>& chunks) {
@@ -619,16 +632,25 @@ struct bagpu_handle_s {
       }
     };
     std::vector<ReduceItem> chunks;
+    items.reserve(bkey.size() + (size_t)n_pairs / kChunk + 4 * (size_t)n_ap + (size_t)(n_rec + n_lmrec) / kChunk + 16);
     size_t bi = 0; uint32_t pair_off = 0;
     for (int p = 0; p < n_ap; ++p) {
       cut(chunks, pose_rec_start[p], pose_rec_start[p + 1], p, p, kItemDiagObs);
       if (L == 1) cut(chunks, pose_lmrec_start[p], pose_lmrec_start[p + 1], p, p, kItemDiagLm);
       push_block(items, chunks);
-      while (bi < bkey.size() && (int)((bkey[bi] >> 1) / (unsigned long long)n_ap) == p) {
+      const unsigned long long row_lo = (unsigned long long)p * (unsigned long long)n_ap, row_hi = row_lo + (unsigned long long)n_ap;
+      while (bi < bkey.size() && (bkey[bi] >> 1) < row_hi) {   // keys are sorted by (row, column, kind): no division per block
         // all runs of one block (entries between measurement poses, then measurement/reference entries) form one chunk chain
         const unsigned long long blk = bkey[bi] >> 1;
-        const uint32_t col = (uint32_t)(blk % (unsigned long long)n_ap);
+        const uint32_t col = (uint32_t)(blk - row_lo);
         const bool is_sym = (col == (uint32_t)p);
+        if (!is_sym && bcnt[bi] <= kChunk && (bi + 1 == bkey.size() || (bkey[bi + 1] >> 1) != blk)) {
+          // the common case, one run that fits one chunk: written in place
+          const ReduceItem it = {pair_off, pair_off + bcnt[bi], (uint32_t)p, col, (bkey[bi] & 1ull) ? (uint32_t)kItemOffRef : (uint32_t)kItemOff, 0u, 1u, 0u, 0u, 0u};
+          items.push_back(it);
+          pair_off += bcnt[bi]; ++bi;
+          continue;
+        }
         while (bi < bkey.size() && (bkey[bi] >> 1) == blk) {
           const bool is_ref = (bkey[bi] & 1ull) != 0;
           cut(chunks, pair_off, pair_off + bcnt[bi], p, col, is_ref ? kItemOffRef : (is_sym ? kItemSym : kItemOff));
@@ -638,6 +660,7 @@ struct bagpu_handle_s {
       }
     }
     n_items = (int)items.size(); n_items_sym = (int)sym.size();
+    pcr.lap("    work items (host)");
     d_items.upload(items, st); d_items_sym.upload(sym, st);
     d_partial.alloc((size_t)std::max<uint32_t>(1, n_partial) * 64); d_counters.alloc((size_t)n_groups + 2); d_counters.zero(st);   // [0] = item counter of the running launch
     sync();   // the host vectors above go out of scope
@@ -1087,6 +1110,7 @@ struct bagpu_handle_s {
     d_lm_xw.download(lm_xw.data(), lm_xw.size(), st);
     lm_xs.resize(lm_xw.size());
     d_lm_x.download(lm_xs.data(), lm_xs.size(), st);
+    lm_reliable.resize(n_lms);
     d_lm_reliable.download(lm_reliable.data(), lm_reliable.size(), st);
     lm_outliers.resize(n_lms);
     d_lm_outliers.download(lm_outliers.data(), n_lms, st);
@@ -1278,6 +1302,7 @@ void bagpu_destroy(bagpu_handle h) {
       if (comm_stuck) one.p = nullptr;   // still in use by the pending collective
     } catch (const std::string&) {}
   }
+  h->join_packer();
   if (comm_stuck) return;   // abandon the handle (freeing its buffers would wait for the pending collective): the job is failing anyway
   h->peer.destroy();
   if (h->comm && g_nccl.commDestroy) g_nccl.commDestroy(h->comm);
@@ -1330,7 +1355,7 @@ int bagpu_set_landmarks(bagpu_handle h, uint32_t n, const double* x, const uint3
   h->lm_ref_pose.assign(rp, rp + n);
   if (rc) h->lm_ref_cam.assign(rc, rc + n); else h->lm_ref_cam.assign(n, 0);
   if (a) h->lm_active.assign(a, a + n); else h->lm_active.assign(n, 1);
-  h->lm_reliable.assign(n, 1); h->lm_outliers.assign(n, 0);
+  h->lm_reliable.clear(); h->lm_outliers.clear();   // all reliable, no outliers until a Solve() says otherwise
   h->dirty = true;
   return BAGPU_OK;
 }
@@ -1450,14 +1475,14 @@ int bagpu_get_landmarks(bagpu_handle h, double* xw, double* xs, uint8_t* rel, ui
   if (!h->lm_host_fresh) {   // set but not solved yet: positions as sent, x_s not known
     GUARD(if (xw) { h->d_lm_xw.download(xw, 4 * n, h->st); h->sync(); })
     if (xs) memset(xs, 0, sizeof(double) * 4 * n);
-    if (rel) memcpy(rel, h->lm_reliable.data(), n);
-    if (nout) memcpy(nout, h->lm_outliers.data(), sizeof(uint32_t) * n);
+    if (rel) memset(rel, 1, n);
+    if (nout) memset(nout, 0, sizeof(uint32_t) * n);
     return BAGPU_OK;
   }
   if (xw) memcpy(xw, h->lm_xw.data(), sizeof(double) * 4 * n);
   if (xs) { if (h->lm_xs.size() == 4 * n) memcpy(xs, h->lm_xs.data(), sizeof(double) * 4 * n); else memset(xs, 0, sizeof(double) * 4 * n); }
-  if (rel) memcpy(rel, h->lm_reliable.data(), n);
-  if (nout) memcpy(nout, h->lm_outliers.data(), sizeof(uint32_t) * n);
+  if (rel) { if (h->lm_reliable.size() == n) memcpy(rel, h->lm_reliable.data(), n); else memset(rel, 1, n); }
+  if (nout) { if (h->lm_outliers.size() == n) memcpy(nout, h->lm_outliers.data(), sizeof(uint32_t) * n); else memset(nout, 0, sizeof(uint32_t) * n); }
   return BAGPU_OK;
 }
 int bagpu_get_proj_residuals(bagpu_handle h, double* r, double* w, double* m) {
