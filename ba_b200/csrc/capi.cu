@@ -17,6 +17,7 @@
 #include <mutex>
 #include <string>
 #include <unordered_set>
+#include <iterator>
 #include <thread>
 #include <vector>
 #include <dlfcn.h>
@@ -178,7 +179,7 @@ struct bagpu_handle_s {
   uint2* d_pairs = nullptr;            // cudaMalloc'ed by build_pair_lists
   int G = 8;
   int nT = 0, T = 48, n_tiles = 0, max_row = 0;
-  std::vector<int> tile_map, row_ptr, row_col, tile_perm;
+  std::vector<int> row_ptr, row_col, tile_perm;
   double trust_region = -1;
   bool is_param_mask_used = false;
 
@@ -405,40 +406,72 @@ struct bagpu_handle_s {
   }
 
   // ---- tile structure of S: binary / inertial couplings, elimination order, symbolic fill, tile table ----
+  // `flat` is the nT x nT upper pattern from the observations (device_symbolic).  Everything after the one scan of it
+  // works on sorted column lists per row, so the cost follows the number of tiles, not nT^2 (a 20k-pose graph has
+  // nT = 2500).
+  int tile_slot(int a, int b) const {   // storage slot of tile (a <= b) in permuted tile ids, -1 if structurally empty
+    const int base = a + row_ptr[a];
+    if (a == b) return base;
+    const int* lo = row_col.data() + row_ptr[a];
+    const int* hi = row_col.data() + row_ptr[a + 1];
+    const int* it = std::lower_bound(lo, hi, b);
+    return (it != hi && *it == b) ? base + 1 + (int)(it - lo) : -1;
+  }
   void tile_structure(std::vector<uint8_t>& flat) {
-    std::vector<std::vector<uint8_t>> present(nT, std::vector<uint8_t>(nT, 0));
-    for (int a = 0; a < nT; ++a) for (int b = a; b < nT; ++b) present[a][b] = flat[(size_t)a * nT + b];
-    for (int k = 0; k < nT; ++k) present[k][k] = 1;
+    std::vector<std::vector<int>> rows(nT);   // columns > row of the upper pattern, natural tile ids
+    for (int a = 0; a < nT; ++a) {
+      const uint8_t* r = flat.data() + (size_t)a * nT;
+      int b = a + 1;
+      while (b < nT) {
+        const void* hit = memchr(r + b, 1, (size_t)(nT - b));
+        if (!hit) break;
+        b = (int)(static_cast<const uint8_t*>(hit) - r);
+        rows[a].push_back(b);
+        ++b;
+      }
+    }
+    bool marked = false;
     auto mark = [&](uint32_t p1, uint32_t p2) {
       const int o1 = pose_opt[p1], o2 = pose_opt[p2];
       if (o1 < 0 || o2 < 0) return;
       const int a = std::min(o1, o2) / kTilePoses, b = std::max(o1, o2) / kTilePoses;
-      present[a][b] = 1;
+      if (a != b) { rows[a].push_back(b); marked = true; }
     };
     for (size_t i = 0; i < bin_p1.size(); ++i) mark(bin_p1[i], bin_p2[i]);
     for (size_t i = 0; i < imu_p1.size(); ++i) mark(imu_p1[i], imu_p2[i]);
+    if (marked) for (auto& r : rows) { std::sort(r.begin(), r.end()); r.erase(std::unique(r.begin(), r.end()), r.end()); }
     // ---- elimination order of the tiles: nested dissection (a banded S is a chain of nT dependent tile rows;
     // dissection turns it into a tree of depth ~log nT whose branches the dataflow solver runs concurrently) ----
-    nested_dissection(present);
+    nested_dissection(rows);
     {
-      std::vector<std::vector<uint8_t>> pp(nT, std::vector<uint8_t>(nT, 0));
-      for (int a = 0; a < nT; ++a) for (int b = a; b < nT; ++b) if (present[a][b]) {
+      std::vector<std::vector<int>> pp(nT);
+      for (int a = 0; a < nT; ++a) for (int b : rows[a]) {
         const int x = tile_perm[a], y = tile_perm[b];
-        pp[std::min(x, y)][std::max(x, y)] = 1;
+        pp[std::min(x, y)].push_back(std::max(x, y));
       }
-      present.swap(pp);
+      for (auto& r : pp) std::sort(r.begin(), r.end());
+      rows.swap(pp);
     }
-    for (int k = 0; k < nT; ++k) {   // fill: eliminating tile row k couples every pair of its columns
-      std::vector<int> cols;
-      for (int j = k + 1; j < nT; ++j) if (present[k][j]) cols.push_back(j);
-      for (size_t a = 0; a < cols.size(); ++a) for (size_t b = a; b < cols.size(); ++b) present[cols[a]][cols[b]] = 1;
+    // fill: eliminating tile row k couples every pair of its columns.  It is enough to merge the columns behind the
+    // first one into the row of the first one (its parent in the elimination tree): the parent passes them on.
+    {
+      std::vector<int> merged;
+      for (int k = 0; k < nT; ++k) {
+        const std::vector<int>& cols = rows[k];
+        if (cols.size() < 2) continue;
+        std::vector<int>& par = rows[cols[0]];
+        merged.clear(); merged.reserve(par.size() + cols.size());
+        std::set_union(par.begin(), par.end(), cols.begin() + 1, cols.end(), std::back_inserter(merged));
+        par.assign(merged.begin(), merged.end());
+      }
     }
-    tile_map.assign((size_t)nT * nT, -1);
+    // tiles are numbered row by row, the diagonal tile first (tile_slot()); the dense nT x nT table the kernels look
+    // tiles up in is filled on the device (launch_fill_tile_map)
     row_ptr.assign(nT + 1, 0); row_col.clear();
     n_tiles = 0; max_row = 0;
     for (int k = 0; k < nT; ++k) {
-      tile_map[(size_t)k * nT + k] = n_tiles++;
-      for (int j = k + 1; j < nT; ++j) if (present[k][j]) { tile_map[(size_t)k * nT + j] = n_tiles++; row_col.push_back(j); }
+      n_tiles += 1 + (int)rows[k].size();
+      row_col.insert(row_col.end(), rows[k].begin(), rows[k].end());
       row_ptr[k + 1] = (int)row_col.size();
       max_row = std::max(max_row, row_ptr[k + 1] - row_ptr[k]);
     }
@@ -448,14 +481,15 @@ struct bagpu_handle_s {
   // bisection of index-sorted node lists: the separator is the smaller set of nodes on one side of the
   // split that touch the other side.  Falls back to the natural order where the separator is not small
   // (dense S).  Output: tile_perm[natural tile] = position in the elimination order.
-  void nested_dissection(const std::vector<std::vector<uint8_t>>& present) {
+  void nested_dissection(const std::vector<std::vector<int>>& upper) {
     tile_perm.assign(nT, 0);
     for (int i = 0; i < nT; ++i) tile_perm[i] = i;
     if (nT < 8 || getenv("BAGPU_NO_ND")) return;
     // a node list is split while its separator is smaller than 2 / nd_ratio of it (development knob BAGPU_ND_RATIO)
     const int nd_ratio = getenv("BAGPU_ND_RATIO") ? std::max(2, atoi(getenv("BAGPU_ND_RATIO"))) : 6;
     std::vector<std::vector<int>> adj(nT);
-    for (int a = 0; a < nT; ++a) for (int b = a + 1; b < nT; ++b) if (present[a][b]) { adj[a].push_back(b); adj[b].push_back(a); }
+    for (int a = 0; a < nT; ++a) for (int b : upper[a]) { adj[a].push_back(b); adj[b].push_back(a); }
+    for (auto& r : adj) std::sort(r.begin(), r.end());   // neighbours in ascending order, as a dense scan would list them
     std::vector<int> order; order.reserve(nT);
     std::vector<int> side(nT, 0);   // scratch: 1 = left, 2 = right of the current split
     struct Frame { std::vector<int> nodes; bool emit; };
@@ -545,10 +579,11 @@ struct bagpu_handle_s {
     const size_t tsz = (size_t)T * T;
     d_S.alloc((size_t)n_tiles * tsz); d_uinv.alloc((size_t)nT * tsz); d_scratch.alloc(3 * (size_t)nT * T + 2 * (size_t)n_tiles * T);
     d_bp.alloc((size_t)nT * T); d_rhs_sc.alloc((size_t)nT * T); d_rhs_work.alloc((size_t)nT * T);
-    d_tile_map.upload(tile_map, st); d_row_ptr.upload(row_ptr, st); d_row_col.upload(row_col, st); d_tile_perm.upload(tile_perm, st);
+    d_row_ptr.upload(row_ptr, st); d_row_col.upload(row_col, st); d_tile_perm.upload(tile_perm, st);
+    d_tile_map.alloc((size_t)nT * nT); launch_fill_tile_map(d_row_ptr.p, d_row_col.p, nT, d_tile_map.p, st);
     {
       std::vector<CholTask> tasks; std::vector<CholTerm> terms;
-      chol_build_plan(nT, tile_map, row_ptr, row_col, tasks, terms);
+      chol_build_plan(nT, row_ptr, row_col, tasks, terms);
       n_chol_tasks = (int)tasks.size();
       if (getenv("BAGPU_CHOL_TRACE")) h_chol_tasks = tasks;
       d_chol_tasks.upload(tasks, st); d_chol_terms.upload(terms, st); d_chol_sync.alloc(chol_sync_ints(n_tiles, nT));
@@ -1579,7 +1614,7 @@ int bagpu_get_system(bagpu_handle h, double* s_dense, double* rhs_sc, double* rh
       memset(s_dense, 0, sizeof(double) * (size_t)n * n);
       for (int tI = 0; tI < nT; ++tI) for (int tJ = tI; tJ < nT; ++tJ) {   // natural tile ids
         const int a = h->tile_perm[tI], b = h->tile_perm[tJ];
-        const int slot = h->tile_map[(size_t)std::min(a, b) * nT + std::max(a, b)];
+        const int slot = h->tile_slot(std::min(a, b), std::max(a, b));
         if (slot < 0) continue;
         for (int c = 0; c < T; ++c) for (int r = 0; r < T; ++r) {
           const int gi = tI * T + r, gj = tJ * T + c;

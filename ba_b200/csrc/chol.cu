@@ -401,13 +401,20 @@ __global__ void __launch_bounds__(CholCfg<T>::NT, 1) k_chol_dataflow(CholDev c) 
 }
 
 // ---- host: task list in a topological order (claimed in this order by the CTAs) ---------------
-void chol_build_plan(int nT, const std::vector<int>& tile_map, const std::vector<int>& row_ptr, const std::vector<int>& row_col,
+void chol_build_plan(int nT, const std::vector<int>& row_ptr, const std::vector<int>& row_col,
                      std::vector<CholTask>& tasks, std::vector<CholTerm>& terms) {
   tasks.clear(); terms.clear();
   std::vector<std::vector<int>> col_rows(nT);      // rows k < c that hold tile (k, c), ascending
   for (int k = 0; k < nT; ++k)
     for (int e = row_ptr[k]; e < row_ptr[k + 1]; ++e) col_rows[row_col[e]].push_back(k);
-  auto slot = [&](int a, int b) { return tile_map[(size_t)a * nT + b]; };
+  // tiles are numbered row by row, the diagonal tile first, then the row's columns in ascending order
+  auto slot = [&](int a, int b) {
+    const int base = a + row_ptr[a];
+    if (a == b) return base;
+    const int* lo = row_col.data() + row_ptr[a];
+    const int* hi = row_col.data() + row_ptr[a + 1];
+    return base + 1 + (int)(std::lower_bound(lo, hi, b) - lo);
+  };
   auto add = [&](int kind, int i, int j, int s, int lb, int le) {
     CholTask t; t.kind = kind; t.i = i; t.j = j; t.slot = s; t.lb = lb; t.le = le; t.pad0 = 0; t.pad1 = 0;
     tasks.push_back(t);

@@ -71,6 +71,8 @@ void launch_slot_keys(const uint32_t* obs_pose, const uint32_t* obs_lm, uint32_t
 void launch_assign_slots(const uint32_t* keys_sorted, const uint32_t* vals_sorted, uint32_t n, uint32_t n_ap, uint32_t* slot, cudaStream_t st);
 void launch_rslot_keys(const uint8_t* lm_any, const uint32_t* lm_ref_pose, const int* pose_opt, uint32_t n_lms, uint32_t n_ap, uint32_t* keys,
                        cudaStream_t st);
+// dense nT x nT tile table (-1 = structurally empty) from the CSR rows: tiles numbered row by row, diagonal tile first
+void launch_fill_tile_map(const int* row_ptr, const int* row_col, int nT, int* tile_map, cudaStream_t st);
 void launch_tile_pattern(const uint32_t* starts, const uint32_t* perm, const uint32_t* pose, const uint32_t* lm_ref_pose, const int* pose_opt,
                          uint32_t n_lms, int L, int nT, uint8_t* present, cudaStream_t st);
 void launch_cond_error(const uint32_t* obs_pose, const uint32_t* obs_lm, const uint32_t* obs_perm, uint32_t n, const uint32_t* lm_ref_pose,
@@ -106,7 +108,7 @@ void launch_select_scan(SelectState* st, int pass, double* out, cudaStream_t s);
 // reduced solve (chol.cu): tile tasks of the persistent dataflow kernel, built on the host from the tile pattern
 struct CholTask { int kind, i, j, slot, lb, le, pad0, pad1; };
 struct CholTerm { int sa, sb, k; };   // slots of U_ki, U_kj and the row k of one left-looking update term
-void chol_build_plan(int nT, const std::vector<int>& tile_map, const std::vector<int>& row_ptr, const std::vector<int>& row_col,
+void chol_build_plan(int nT, const std::vector<int>& row_ptr, const std::vector<int>& row_col,
                      std::vector<CholTask>& tasks, std::vector<CholTerm>& terms);
 size_t chol_sync_ints(int n_tiles, int nT);
 // sync_ints[1] holds the first failing pivot + 1 (0 = ok) after the solve; returns a cudaError_t

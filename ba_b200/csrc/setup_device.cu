@@ -219,6 +219,20 @@ void launch_rslot_keys(const uint8_t* lm_any, const uint32_t* lm_ref_pose, const
                        cudaStream_t st) {
   if (n_lms) k_rslot_keys<<<blocks_for(n_lms), 256, 0, st>>>(lm_any, lm_ref_pose, pose_opt, n_lms, n_ap, keys);
 }
+namespace {
+__global__ void k_fill_tile_map(const int* __restrict__ row_ptr, const int* __restrict__ row_col, int nT, int* __restrict__ tile_map) {
+  const int k = blockIdx.x;
+  if (k >= nT) return;
+  const int b = row_ptr[k], e = row_ptr[k + 1], base = k + b;
+  if (threadIdx.x == 0) tile_map[(size_t)k * nT + k] = base;
+  for (int q = b + threadIdx.x; q < e; q += blockDim.x) tile_map[(size_t)k * nT + row_col[q]] = base + 1 + (q - b);
+}
+}  // namespace
+void launch_fill_tile_map(const int* row_ptr, const int* row_col, int nT, int* tile_map, cudaStream_t st) {
+  if (nT <= 0) return;
+  cudaMemsetAsync(tile_map, 0xFF, sizeof(int) * (size_t)nT * nT, st);
+  k_fill_tile_map<<<nT, 64, 0, st>>>(row_ptr, row_col, nT, tile_map);
+}
 void launch_tile_pattern(const uint32_t* starts, const uint32_t* perm, const uint32_t* pose, const uint32_t* lm_ref_pose, const int* pose_opt,
                          uint32_t n_lms, int L, int nT, uint8_t* present, cudaStream_t st) {
   if (n_lms) k_tile_pattern<<<blocks_for(n_lms, 128), 128, 0, st>>>(starts, perm, pose, lm_ref_pose, pose_opt, n_lms, L, nT, present);
