@@ -235,7 +235,8 @@ class BundleAdjuster {
     poses_.clear(); poses_.reserve(num_poses);
     lm_x_w_.clear(); lm_x_s_.clear(); lm_ref_pose_.clear(); lm_ref_cam_.clear(); lm_active_.clear(); lm_reliable_.clear();
     lm_outliers_.clear(); lm_num_res_.clear(); lm_external_.clear(); lm_opt_.clear(); lm_z_ref_.clear();
-    lm_x_w_.reserve(4 * (size_t)num_landmarks); lm_ref_pose_.reserve(num_landmarks);
+    lm_x_w_.reserve(4 * (size_t)num_landmarks); lm_x_s_.reserve(4 * (size_t)num_landmarks); lm_ref_pose_.reserve(num_landmarks);
+    lm_outliers_.reserve(num_landmarks); lm_reliable_.reserve(num_landmarks);
     pr_z_.clear(); pr_pose_.clear(); pr_lm_.clear(); pr_cam_.clear(); pr_w0_.clear(); pr_res_.clear(); pr_w_.clear(); pr_maha_.clear();
     pr_z_.reserve(2 * (size_t)num_measurements); pr_pose_.reserve(num_measurements); pr_lm_.reserve(num_measurements);
     pr_cam_.reserve(num_measurements); pr_w0_.reserve(num_measurements);
@@ -541,9 +542,10 @@ class BundleAdjuster {
   std::shared_ptr<calibu::Rig<Scalar>> rig_;
   std::vector<Pose> poses_;
   /* landmarks, SoA (what the reference keeps in std::vector<Landmark> landmarks_) */
-  std::vector<double> lm_x_w_, lm_x_s_, lm_z_ref_;
-  std::vector<uint32_t> lm_ref_pose_, lm_ref_cam_, lm_outliers_, lm_num_res_, lm_opt_;
-  std::vector<uint8_t> lm_active_, lm_reliable_;
+  /* landmark state the GPU reads from and writes back into directly: page-locked like the observation buffers */
+  detail::HostVector<double> lm_x_w_, lm_x_s_; std::vector<double> lm_z_ref_;
+  std::vector<uint32_t> lm_ref_pose_, lm_ref_cam_, lm_num_res_, lm_opt_; detail::HostVector<uint32_t> lm_outliers_;
+  std::vector<uint8_t> lm_active_; detail::HostVector<uint8_t> lm_reliable_;
   std::vector<int> lm_external_;
   /* projection residuals, SoA (proj_residuals_) */
   detail::HostVector<double> pr_z_, pr_w0_; std::vector<double> pr_res_, pr_w_, pr_maha_;
