@@ -1719,6 +1719,24 @@ int bagpu_comm_init(bagpu_handle h, int rank, int world, const void* id128) {
   return BAGPU_OK;
 }
 
+int bagpu_symbolic_tile_fill(uint32_t nT, uint32_t n_edges, const uint32_t* ea, const uint32_t* eb, uint32_t* perm, uint32_t* row_ptr,
+                             uint32_t* row_col, uint32_t cap) {
+  if (!perm || !row_ptr || (n_edges && (!ea || !eb))) return fail(BAGPU_ERR_INVALID, "null argument");
+  bagpu_handle_s h;
+  h.nT = (int)nT;
+  std::vector<uint8_t> flat((size_t)nT * nT, 0);
+  for (uint32_t e = 0; e < n_edges; ++e) {
+    if (ea[e] >= nT || eb[e] >= nT) return fail(BAGPU_ERR_INVALID, "tile id out of range");
+    flat[(size_t)std::min(ea[e], eb[e]) * nT + std::max(ea[e], eb[e])] = 1;
+  }
+  h.tile_structure(flat);
+  if (h.row_col.size() > cap) return fail(BAGPU_ERR_INVALID, "row_col does not fit");
+  for (uint32_t i = 0; i < nT; ++i) perm[i] = (uint32_t)h.tile_perm[i];
+  for (uint32_t i = 0; i <= nT; ++i) row_ptr[i] = (uint32_t)h.row_ptr[i];
+  for (size_t i = 0; i < h.row_col.size(); ++i) row_col[i] = (uint32_t)h.row_col[i];
+  return BAGPU_OK;
+}
+
 int bagpu_sync_state(bagpu_handle h) {
   if (!h) return fail(BAGPU_ERR_INVALID, "null handle");
   GUARD(h->ensure_device(); if (h->dirty) return fail(BAGPU_ERR_INVALID, "no solve yet"); h->download_state(); h->fetch_landmarks_host();)

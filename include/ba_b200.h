@@ -220,6 +220,14 @@ int bagpu_get_phase_ms(bagpu_handle h, float* ms /* BAGPU_PH_COUNT */, uint64_t*
 /* bring the device state back into the host copies after a solve with options.keep_on_device */
 int bagpu_sync_state(bagpu_handle h);
 
+/* Host-only symbolic step of the reduced solve, exposed for tests (no device needed): from the upper pattern of an
+ * nT x nT tile matrix given as n_edges pairs (a, b), the elimination order (nested dissection; replaces the AMD
+ * ordering inside Eigen::SimplicialLDLT, reference src/BundleAdjuster.cpp:753-761) and the filled pattern in that
+ * order as CSR rows of the strict upper triangle.  perm[natural tile] = position; row_ptr has nT + 1 entries;
+ * row_col takes up to cap entries (BAGPU_ERR_INVALID if it does not fit). */
+int bagpu_symbolic_tile_fill(uint32_t nT, uint32_t n_edges, const uint32_t* edge_a, const uint32_t* edge_b,
+                             uint32_t* perm, uint32_t* row_ptr, uint32_t* row_col, uint32_t cap);
+
 #ifdef __cplusplus
 }
 #endif
