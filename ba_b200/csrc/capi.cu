@@ -117,6 +117,31 @@ constexpr int kNcclFloat64 = 8, kNcclUint32 = 3, kNcclSum = 0;  // ncclDataType_
 
 }  // namespace
 
+// Warp tasks of the landmark-major kernels: greedy runs of whole landmarks [lo, hi) with at most 32 observations in
+// total, as (first observation, count) relative to s_lo; landmarks with more than 32 observations are listed apart.
+// gstarts = CSR bounds of the landmark-major observation stream, clamped to the shard [s_lo, s_hi).
+static void pack_warp_tasks(const uint32_t* gstarts, int lo, int hi, uint32_t s_lo, uint32_t s_hi, std::vector<uint2>& tasks,
+                            std::vector<uint32_t>& longs) {
+  auto lstart = [&](int l) { const uint32_t v = gstarts[l]; return (v < s_lo ? s_lo : (v > s_hi ? s_hi : v)) - s_lo; };
+  tasks.clear(); longs.clear();
+  tasks.reserve((size_t)(s_hi - s_lo) / 24 + 16);
+  int l = lo;
+  uint32_t b = lstart(l);
+  while (l < hi) {
+    uint32_t e1 = lstart(l + 1);
+    if (e1 - b > 32) { longs.push_back((uint32_t)l); ++l; b = e1; continue; }
+    const uint32_t first = b;
+    uint32_t end = b;
+    while (l < hi) {
+      e1 = lstart(l + 1);
+      if (e1 - end > 32 || e1 - first > 32) break;
+      end = e1; ++l;
+    }
+    if (end > first) tasks.push_back(make_uint2(first, end - first));
+    b = end;
+  }
+}
+
 struct bagpu_handle_s {
   bagpu_dims dims;
   bagpu_options opt;
@@ -352,26 +377,7 @@ struct bagpu_handle_s {
     {
       const int lo = lm_owner_lo, hi = lm_owner_hi;
       const uint32_t slo = s_lo, shi = s_hi;
-      packer = std::thread([this, lo, hi, slo, shi]() {
-        const std::vector<uint32_t>& gs = pk_gstarts;
-        auto lstart = [&](int l) { const uint32_t v = gs[l]; return (v < slo ? slo : (v > shi ? shi : v)) - slo; };
-        pk_tasks.reserve((size_t)(shi - slo) / 24 + 16);
-        int l = lo;
-        uint32_t b = lstart(l);
-        while (l < hi) {
-          uint32_t e1 = lstart(l + 1);
-          if (e1 - b > 32) { pk_longs.push_back((uint32_t)l); ++l; b = e1; continue; }
-          const uint32_t first = b;
-          uint32_t end = b;
-          while (l < hi) {
-            e1 = lstart(l + 1);
-            if (e1 - end > 32 || e1 - first > 32) break;
-            end = e1; ++l;
-          }
-          if (end > first) pk_tasks.push_back(make_uint2(first, end - first));
-          b = end;
-        }
-      });
+      packer = std::thread([this, lo, hi, slo, shi]() { pack_warp_tasks(pk_gstarts.data(), lo, hi, slo, shi, pk_tasks, pk_longs); });
     }
     // 4. the local stream: gathered values, pose-major record slots
     const uint32_t nl = (uint32_t)n_obs;
@@ -1716,6 +1722,18 @@ int bagpu_comm_init(bagpu_handle h, int rank, int world, const void* id128) {
       if (getenv("BAGPU_TIMING")) fprintf(stderr, "[bagpu] rank %d: peer-memory reductions %s\n", rank, h->peer.ok ? "on" : "off (NCCL only)");
     }
   })
+  return BAGPU_OK;
+}
+
+int bagpu_pack_warp_tasks(uint32_t n_lms, const uint32_t* starts, uint32_t lm_lo, uint32_t lm_hi, uint32_t* task_first,
+                          uint32_t* task_count, uint32_t* n_tasks, uint32_t* long_lms, uint32_t* n_long) {
+  if (!starts || !n_tasks || !n_long || lm_lo > lm_hi || lm_hi > n_lms) return fail(BAGPU_ERR_INVALID, "bad argument");
+  std::vector<uint2> tasks; std::vector<uint32_t> longs;
+  pack_warp_tasks(starts, (int)lm_lo, (int)lm_hi, starts[lm_lo], starts[lm_hi], tasks, longs);
+  if (tasks.size() > *n_tasks || longs.size() > *n_long) return fail(BAGPU_ERR_INVALID, "output does not fit");
+  for (size_t i = 0; i < tasks.size(); ++i) { if (task_first) task_first[i] = tasks[i].x; if (task_count) task_count[i] = tasks[i].y; }
+  for (size_t i = 0; i < longs.size(); ++i) if (long_lms) long_lms[i] = longs[i];
+  *n_tasks = (uint32_t)tasks.size(); *n_long = (uint32_t)longs.size();
   return BAGPU_OK;
 }
 

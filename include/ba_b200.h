@@ -225,6 +225,13 @@ int bagpu_sync_state(bagpu_handle h);
  * ordering inside Eigen::SimplicialLDLT, reference src/BundleAdjuster.cpp:753-761) and the filled pattern in that
  * order as CSR rows of the strict upper triangle.  perm[natural tile] = position; row_ptr has nT + 1 entries;
  * row_col takes up to cap entries (BAGPU_ERR_INVALID if it does not fit). */
+/* Host-only, for tests: the warp tasks of the landmark-major kernels for the landmark range [lm_lo, lm_hi) of a
+ * landmark-major observation stream with CSR bounds starts[0..n_lms] (the per-landmark residual lists of the
+ * reference, include/ba/Types.h:186-217, flattened).  A task is a run of whole landmarks with at most 32 observations
+ * in total: (first observation relative to starts[lm_lo], count); landmarks with more than 32 observations go to
+ * long_lms.  *n_tasks / *n_long: capacity in, count out. */
+int bagpu_pack_warp_tasks(uint32_t n_lms, const uint32_t* starts, uint32_t lm_lo, uint32_t lm_hi, uint32_t* task_first,
+                          uint32_t* task_count, uint32_t* n_tasks, uint32_t* long_lms, uint32_t* n_long);
 int bagpu_symbolic_tile_fill(uint32_t nT, uint32_t n_edges, const uint32_t* edge_a, const uint32_t* edge_b,
                              uint32_t* perm, uint32_t* row_ptr, uint32_t* row_col, uint32_t cap);
 

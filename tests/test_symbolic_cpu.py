@@ -84,3 +84,45 @@ def test_dissection_shortens_the_dependency_chain_of_a_banded_matrix():
             par = row_col[row_ptr[k]]
             level[par] = max(level[par], level[k] + 1)
     assert level.max() < nT // 4
+
+
+def _pack(starts, lo, hi):
+    lib = capi.lib()
+    starts = np.ascontiguousarray(starts, np.uint32)
+    n = len(starts) - 1
+    first = np.zeros(n + 1, np.uint32); count = np.zeros(n + 1, np.uint32); longs = np.zeros(n + 1, np.uint32)
+    nt = C.c_uint32(n + 1); nl = C.c_uint32(n + 1)
+    p = lambda a: a.ctypes.data_as(C.c_void_p)
+    rc = lib.bagpu_pack_warp_tasks(C.c_uint32(n), p(starts), C.c_uint32(lo), C.c_uint32(hi), p(first), p(count), C.byref(nt), p(longs), C.byref(nl))
+    assert rc == 0
+    return first[:nt.value].astype(int), count[:nt.value].astype(int), longs[:nl.value].astype(int)
+
+
+@pytest.mark.parametrize("seed", [0, 1, 2])
+def test_warp_tasks_partition_the_short_tracks(seed):
+    # every observation of a landmark with <= 32 observations lies in exactly one task, tasks hold whole landmarks
+    # and at most 32 observations, landmarks with longer tracks are listed apart, empty landmarks cost nothing
+    rng = np.random.default_rng(seed)
+    n = 5000
+    track = rng.geometric(0.2, n)                       # BAL-like: mean 5, long tail
+    track[rng.integers(0, n, 40)] = rng.integers(33, 200, 40)
+    track[rng.integers(0, n, 200)] = 0
+    track[rng.integers(0, n, 20)] = 32
+    starts = np.concatenate([[0], np.cumsum(track)])
+    for lo, hi in [(0, n), (1234, 4321), (0, 0), (n - 1, n)]:   # the whole stream and a shard of it
+        first, count, longs = _pack(starts, lo, hi)
+        base = starts[lo]
+        assert np.array_equal(longs, [l for l in range(lo, hi) if track[l] > 32])
+        covered = np.zeros(starts[hi] - base, int)
+        for f, c in zip(first, count):
+            assert 0 < c <= 32
+            assert (f + base) in starts and (f + c + base) in starts         # whole landmarks
+            covered[f:f + c] += 1
+        want = np.zeros_like(covered)
+        for l in range(lo, hi):
+            if track[l] <= 32:
+                want[starts[l] - base:starts[l + 1] - base] = 1
+        assert np.array_equal(covered, want)
+        assert np.all(np.diff(first) > 0)                                      # in stream order
+        if len(count) > 50:
+            assert count.mean() > 24                                           # greedy packing keeps the lanes busy
