@@ -117,6 +117,67 @@ constexpr int kNcclFloat64 = 8, kNcclUint32 = 3, kNcclSum = 0;  // ncclDataType_
 
 }  // namespace
 
+// Work items of the pose-pair-major reduction (k_reduce_blocks): every S block — the diagonal block of a pose over its
+// record slots, an off-diagonal block over its run(s) of the pair list — is cut into chunks of at most kWorkChunk
+// entries, one warp each; the chunks of one block share a group of partial-sum slots (mfirst, mcount, mself, mgroup).
+// block_key (sorted) = (row * n_ap + col) * 2 + (1 for LmSize-1 measurement/reference entries), block_count = run
+// lengths in the pair list.  Blocks with row == col from the pair list (one pose observing a landmark twice) go to `sym`
+// (a second launch: they add into diagonal blocks that the first launch owns).
+constexpr uint32_t kWorkChunk = 512;
+static void build_work_items(int n_ap, int L, const uint32_t* pose_rec_start, const uint32_t* pose_lmrec_start,
+                             const std::vector<unsigned long long>& bkey, const std::vector<uint32_t>& bcnt, size_t n_pairs,
+                             std::vector<ReduceItem>& items, std::vector<ReduceItem>& sym, uint32_t& n_partial, uint32_t& n_groups) {
+  constexpr uint32_t kChunk = kWorkChunk;
+  items.clear(); sym.clear(); n_partial = 0; n_groups = 0;
+  auto push_block = [&](std::vector<ReduceItem>& out, std::vector<ReduceItem>& chunks) {
+    if (chunks.empty()) return;
+    const uint32_t mc = (uint32_t)chunks.size();
+    for (uint32_t k = 0; k < mc; ++k) {
+      ReduceItem& it = chunks[k];
+      it.mcount = mc; it.mfirst = 0; it.mself = 0; it.mgroup = 0;
+      if (mc > 1) { it.mfirst = n_partial; it.mself = n_partial + k; it.mgroup = n_groups; }
+      out.push_back(it);
+    }
+    if (mc > 1) { n_partial += mc; ++n_groups; }
+    chunks.clear();
+  };
+  auto cut = [&](std::vector<ReduceItem>& chunks, uint32_t lo, uint32_t hi, uint32_t row, uint32_t col, uint32_t kind) {
+    for (uint32_t b = lo; b < hi; b += kChunk) {
+      ReduceItem it; memset(&it, 0, sizeof(it));
+      it.begin = b; it.end = std::min(hi, b + kChunk); it.row = row; it.col = col; it.kind = kind;
+      chunks.push_back(it);
+    }
+  };
+  std::vector<ReduceItem> chunks;
+  items.reserve(bkey.size() + n_pairs / kChunk + 4 * (size_t)n_ap + (size_t)(pose_rec_start[n_ap] + (L == 1 ? pose_lmrec_start[n_ap] : 0)) / kChunk + 16);
+  size_t bi = 0; uint32_t pair_off = 0;
+  for (int p = 0; p < n_ap; ++p) {
+    cut(chunks, pose_rec_start[p], pose_rec_start[p + 1], p, p, kItemDiagObs);
+    if (L == 1) cut(chunks, pose_lmrec_start[p], pose_lmrec_start[p + 1], p, p, kItemDiagLm);
+    push_block(items, chunks);
+    const unsigned long long row_lo = (unsigned long long)p * (unsigned long long)n_ap, row_hi = row_lo + (unsigned long long)n_ap;
+    while (bi < bkey.size() && (bkey[bi] >> 1) < row_hi) {   // keys are sorted by (row, column, kind): no division per block
+      // all runs of one block (entries between measurement poses, then measurement/reference entries) form one chunk chain
+      const unsigned long long blk = bkey[bi] >> 1;
+      const uint32_t col = (uint32_t)(blk - row_lo);
+      const bool is_sym = (col == (uint32_t)p);
+      if (!is_sym && bcnt[bi] <= kChunk && (bi + 1 == bkey.size() || (bkey[bi + 1] >> 1) != blk)) {
+        // the common case, one run that fits one chunk: written in place
+        const ReduceItem it = {pair_off, pair_off + bcnt[bi], (uint32_t)p, col, (bkey[bi] & 1ull) ? (uint32_t)kItemOffRef : (uint32_t)kItemOff, 0u, 1u, 0u, 0u, 0u};
+        items.push_back(it);
+        pair_off += bcnt[bi]; ++bi;
+        continue;
+      }
+      while (bi < bkey.size() && (bkey[bi] >> 1) == blk) {
+        const bool is_ref = (bkey[bi] & 1ull) != 0;
+        cut(chunks, pair_off, pair_off + bcnt[bi], p, col, is_ref ? kItemOffRef : (is_sym ? kItemSym : kItemOff));
+        pair_off += bcnt[bi]; ++bi;
+      }
+      push_block(is_sym ? sym : items, chunks);
+    }
+  }
+}
+
 // Warp tasks of the landmark-major kernels: greedy runs of whole landmarks [lo, hi) with at most 32 observations in
 // total, as (first observation, count) relative to s_lo; landmarks with more than 32 observations are listed apart.
 // gstarts = CSR bounds of the landmark-major observation stream, clamped to the shard [s_lo, s_hi).
@@ -643,7 +704,6 @@ struct bagpu_handle_s {
   // ---- work items of the pose-pair-major reduction (schur_kernels.cu): the device builds the pair
   // lists (symbolic.cu), the host cuts every S block into chunks of at most kChunk entries ----
   void build_reduce_items() {
-    constexpr uint32_t kChunk = 512;
     if (d_pairs) { dev_free(d_pairs); d_pairs = nullptr; }
     n_pairs = 0; n_items = 0; n_items_sym = 0;
     if (L == 0 || n_obs == 0 || n_ap == 0) return;
@@ -653,53 +713,7 @@ struct bagpu_handle_s {
     pcr.lap("    pair lists (device)");
     std::vector<ReduceItem> items, sym;
     uint32_t n_partial = 0, n_groups = 0;
-    auto push_block = [&](std::vector<ReduceItem>& out, std::vector<ReduceItem>& chunks) {
-      if (chunks.empty()) return;
-      const uint32_t mc = (uint32_t)chunks.size();
-      for (uint32_t k = 0; k < mc; ++k) {
-        ReduceItem& it = chunks[k];
-        it.mcount = mc; it.mfirst = 0; it.mself = 0; it.mgroup = 0;
-        if (mc > 1) { it.mfirst = n_partial; it.mself = n_partial + k; it.mgroup = n_groups; }
-        out.push_back(it);
-      }
-      if (mc > 1) { n_partial += mc; ++n_groups; }
-      chunks.clear();
-    };
-    auto cut = [&](std::vector<ReduceItem>& chunks, uint32_t lo, uint32_t hi, uint32_t row, uint32_t col, uint32_t kind) {
-      for (uint32_t b = lo; b < hi; b += kChunk) {
-        ReduceItem it; memset(&it, 0, sizeof(it));
-        it.begin = b; it.end = std::min(hi, b + kChunk); it.row = row; it.col = col; it.kind = kind;
-        chunks.push_back(it);
-      }
-    };
-    std::vector<ReduceItem> chunks;
-    items.reserve(bkey.size() + (size_t)n_pairs / kChunk + 4 * (size_t)n_ap + (size_t)(n_rec + n_lmrec) / kChunk + 16);
-    size_t bi = 0; uint32_t pair_off = 0;
-    for (int p = 0; p < n_ap; ++p) {
-      cut(chunks, pose_rec_start[p], pose_rec_start[p + 1], p, p, kItemDiagObs);
-      if (L == 1) cut(chunks, pose_lmrec_start[p], pose_lmrec_start[p + 1], p, p, kItemDiagLm);
-      push_block(items, chunks);
-      const unsigned long long row_lo = (unsigned long long)p * (unsigned long long)n_ap, row_hi = row_lo + (unsigned long long)n_ap;
-      while (bi < bkey.size() && (bkey[bi] >> 1) < row_hi) {   // keys are sorted by (row, column, kind): no division per block
-        // all runs of one block (entries between measurement poses, then measurement/reference entries) form one chunk chain
-        const unsigned long long blk = bkey[bi] >> 1;
-        const uint32_t col = (uint32_t)(blk - row_lo);
-        const bool is_sym = (col == (uint32_t)p);
-        if (!is_sym && bcnt[bi] <= kChunk && (bi + 1 == bkey.size() || (bkey[bi + 1] >> 1) != blk)) {
-          // the common case, one run that fits one chunk: written in place
-          const ReduceItem it = {pair_off, pair_off + bcnt[bi], (uint32_t)p, col, (bkey[bi] & 1ull) ? (uint32_t)kItemOffRef : (uint32_t)kItemOff, 0u, 1u, 0u, 0u, 0u};
-          items.push_back(it);
-          pair_off += bcnt[bi]; ++bi;
-          continue;
-        }
-        while (bi < bkey.size() && (bkey[bi] >> 1) == blk) {
-          const bool is_ref = (bkey[bi] & 1ull) != 0;
-          cut(chunks, pair_off, pair_off + bcnt[bi], p, col, is_ref ? kItemOffRef : (is_sym ? kItemSym : kItemOff));
-          pair_off += bcnt[bi]; ++bi;
-        }
-        push_block(is_sym ? sym : items, chunks);
-      }
-    }
+    build_work_items(n_ap, L, pose_rec_start.data(), pose_lmrec_start.data(), bkey, bcnt, n_pairs, items, sym, n_partial, n_groups);
     n_items = (int)items.size(); n_items_sym = (int)sym.size();
     pcr.lap("    work items (host)");
     d_items.upload(items, st); d_items_sym.upload(sym, st);
@@ -1722,6 +1736,28 @@ int bagpu_comm_init(bagpu_handle h, int rank, int world, const void* id128) {
       if (getenv("BAGPU_TIMING")) fprintf(stderr, "[bagpu] rank %d: peer-memory reductions %s\n", rank, h->peer.ok ? "on" : "off (NCCL only)");
     }
   })
+  return BAGPU_OK;
+}
+
+int bagpu_build_work_items(uint32_t n_active_poses, int lm_dim, const uint32_t* pose_rec_start, const uint32_t* pose_lmrec_start,
+                           uint32_t n_blocks, const uint64_t* block_key, const uint32_t* block_count, uint32_t* items10,
+                           uint32_t* n_items, uint32_t* sym10, uint32_t* n_sym, uint32_t* n_partial, uint32_t* n_groups) {
+  if (!pose_rec_start || !n_items || !n_sym || (lm_dim == 1 && !pose_lmrec_start) || (n_blocks && (!block_key || !block_count)))
+    return fail(BAGPU_ERR_INVALID, "null argument");
+  static_assert(sizeof(ReduceItem) == 10 * sizeof(uint32_t), "ReduceItem is ten uint32");
+  std::vector<unsigned long long> bkey(block_key, block_key + n_blocks);
+  std::vector<uint32_t> bcnt(block_count, block_count + n_blocks);
+  size_t n_pairs = 0;
+  for (uint32_t c : bcnt) n_pairs += c;
+  std::vector<ReduceItem> items, sym;
+  uint32_t np = 0, ng = 0;
+  build_work_items((int)n_active_poses, lm_dim, pose_rec_start, pose_lmrec_start, bkey, bcnt, n_pairs, items, sym, np, ng);
+  if (items.size() > *n_items || sym.size() > *n_sym) return fail(BAGPU_ERR_INVALID, "output does not fit");
+  if (items10 && !items.empty()) memcpy(items10, items.data(), items.size() * sizeof(ReduceItem));
+  if (sym10 && !sym.empty()) memcpy(sym10, sym.data(), sym.size() * sizeof(ReduceItem));
+  *n_items = (uint32_t)items.size(); *n_sym = (uint32_t)sym.size();
+  if (n_partial) *n_partial = np;
+  if (n_groups) *n_groups = ng;
   return BAGPU_OK;
 }
 

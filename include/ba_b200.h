@@ -225,6 +225,15 @@ int bagpu_sync_state(bagpu_handle h);
  * ordering inside Eigen::SimplicialLDLT, reference src/BundleAdjuster.cpp:753-761) and the filled pattern in that
  * order as CSR rows of the strict upper triangle.  perm[natural tile] = position; row_ptr has nT + 1 entries;
  * row_col takes up to cap entries (BAGPU_ERR_INVALID if it does not fit). */
+/* Host-only, for tests: the work-item table of the Schur reduction.  Replaces the column walks of the reference's sparse
+ * block products (include/ba/SparseBlockMatrixOps.h:182-254) as the unit of work.  pose_rec_start[0..n_active_poses]:
+ * pose-major record slots; block_key (sorted) = (row * n_active_poses + col) * 2 + kind bit, block_count = entries of
+ * each run in the pair list.  Items are ten uint32 each: begin, end, row, col, kind (0 diagonal over records, 1
+ * diagonal over reference-pose records, 2 off-diagonal, 3 same-pose pairs, 4 measurement/reference entries), mfirst,
+ * mcount, mself, mgroup, pad.  *n_items / *n_sym: capacity in, count out. */
+int bagpu_build_work_items(uint32_t n_active_poses, int lm_dim, const uint32_t* pose_rec_start, const uint32_t* pose_lmrec_start,
+                           uint32_t n_blocks, const uint64_t* block_key, const uint32_t* block_count, uint32_t* items10,
+                           uint32_t* n_items, uint32_t* sym10, uint32_t* n_sym, uint32_t* n_partial, uint32_t* n_groups);
 /* Host-only, for tests: the warp tasks of the landmark-major kernels for the landmark range [lm_lo, lm_hi) of a
  * landmark-major observation stream with CSR bounds starts[0..n_lms] (the per-landmark residual lists of the
  * reference, include/ba/Types.h:186-217, flattened).  A task is a run of whole landmarks with at most 32 observations

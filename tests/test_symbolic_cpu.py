@@ -126,3 +126,77 @@ def test_warp_tasks_partition_the_short_tracks(seed):
         assert np.all(np.diff(first) > 0)                                      # in stream order
         if len(count) > 50:
             assert count.mean() > 24                                           # greedy packing keeps the lanes busy
+
+
+def _work_items(n_ap, L, rec_start, lmrec_start, keys, counts):
+    lib = capi.lib()
+    rec_start = np.ascontiguousarray(rec_start, np.uint32); lmrec_start = np.ascontiguousarray(lmrec_start, np.uint32)
+    keys = np.ascontiguousarray(keys, np.uint64); counts = np.ascontiguousarray(counts, np.uint32)
+    cap = int(len(keys) + counts.sum() // 512 + rec_start[-1] // 512 + lmrec_start[-1] // 512 + 4 * n_ap + 64)
+    items = np.zeros((cap, 10), np.uint32); sym = np.zeros((cap, 10), np.uint32)
+    ni = C.c_uint32(cap); ns = C.c_uint32(cap); npart = C.c_uint32(0); ngrp = C.c_uint32(0)
+    p = lambda a: a.ctypes.data_as(C.c_void_p)
+    rc = lib.bagpu_build_work_items(C.c_uint32(n_ap), C.c_int(L), p(rec_start), p(lmrec_start), C.c_uint32(len(keys)), p(keys), p(counts),
+                                    p(items), C.byref(ni), p(sym), C.byref(ns), C.byref(npart), C.byref(ngrp))
+    assert rc == 0
+    return items[:ni.value].astype(np.int64), sym[:ns.value].astype(np.int64), npart.value, ngrp.value
+
+
+@pytest.mark.parametrize("L", [1, 3])
+def test_work_items_cover_every_block_exactly_once(L):
+    # columns of an item: begin, end, row, col, kind, mfirst, mcount, mself, mgroup, pad
+    rng = np.random.default_rng(11 + L)
+    n_ap = 37
+    rec = np.concatenate([[0], np.cumsum(rng.integers(0, 1500, n_ap))])           # some poses need several chunks
+    lmrec = np.concatenate([[0], np.cumsum(rng.integers(0, 700, n_ap))]) if L == 1 else np.zeros(n_ap + 1, int)
+    keys, counts = [], []
+    for r in range(n_ap):
+        for c in range(r, min(n_ap, r + 6)):
+            if c == r and rng.random() < 0.7:
+                continue                                                            # same-pose pairs are rare
+            if rng.random() < 0.2:
+                continue
+            keys.append((r * n_ap + c) * 2); counts.append(int(rng.choice([1, 7, 130, 512, 513, 1600])))
+            if L == 1 and c != r and rng.random() < 0.5:                           # measurement/reference run of the same block
+                keys.append((r * n_ap + c) * 2 + 1); counts.append(int(rng.choice([3, 40, 900])))
+    items, sym, n_partial, n_groups = _work_items(n_ap, L, rec, lmrec, keys, counts)
+    allit = np.concatenate([items, sym])
+    assert np.all(allit[:, 1] > allit[:, 0]) and np.all(allit[:, 1] - allit[:, 0] <= 512)
+    # diagonal items tile the record ranges of every pose
+    for kind, starts in ((0, rec), (1, lmrec)):
+        d = items[items[:, 4] == kind]
+        for r in range(n_ap):
+            mine = d[d[:, 2] == r]
+            assert np.all(mine[:, 3] == r)
+            got = sorted((int(b), int(e)) for b, e in mine[:, :2])
+            want = [(b, min(b + 512, int(starts[r + 1]))) for b in range(int(starts[r]), int(starts[r + 1]), 512)]
+            assert got == want
+    # pair-list items tile the runs in list order, with the run's block and kind
+    off = np.concatenate([[0], np.cumsum(counts)])
+    pl = allit[allit[:, 4] >= 2]
+    pl = pl[np.argsort(pl[:, 0])]
+    k = 0
+    for bi, key in enumerate(keys):
+        r, c = divmod(key >> 1, n_ap)
+        kind = 4 if key & 1 else (3 if r == c else 2)
+        pos = off[bi]
+        while pos < off[bi + 1]:
+            it = pl[k]; k += 1
+            assert (it[0], it[1]) == (pos, min(pos + 512, off[bi + 1])) and (it[2], it[3], it[4]) == (r, c, kind)
+            pos = it[1]
+    assert k == len(pl)
+    assert np.all(sym[:, 4] == 3) and not np.any(items[:, 4] == 3)
+    # chunk groups: the items of one block (all its runs) share mcount consecutive partial slots and one counter
+    blocks = {}
+    for it in allit:
+        blocks.setdefault((it[2], it[3], it[4] < 2, it[4] == 3), []).append(it)
+    used = []
+    groups = set()
+    for its in blocks.values():
+        mc = len(its)
+        assert all(it[6] == mc for it in its)
+        if mc > 1:
+            assert len({it[5] for it in its}) == 1 and len({it[8] for it in its}) == 1
+            assert sorted(it[7] for it in its) == list(range(its[0][5], its[0][5] + mc))
+            used += [it[7] for it in its]; groups.add(its[0][8])
+    assert sorted(used) == list(range(n_partial)) and sorted(groups) == list(range(n_groups))
