@@ -273,7 +273,10 @@ __global__ void __launch_bounds__(128, (L == 1) ? 3 : 4) k_linearize_long(Device
 template <int L, bool STAGE>
 __global__ void __launch_bounds__(128, (L == 1) ? 3 : 4) k_linearize_packed(DeviceProblem P, const uint2* __restrict__ tasks, int n_tasks) {
   constexpr int RS = (L == 3) ? kRec3 : kRec1;
-  __shared__ double2 srec[STAGE ? 4 * 32 * RS / 2 : 1];
+  // stage stride RS + 2 doubles: a lane's 16-byte stores land 240 / 336 bytes apart, which spreads the eight lanes of a
+  // store phase over all 32 banks (224 / 320 bytes put them on the same 8 / 16 banks: 2- / 4-way conflicts)
+  constexpr int SS = RS + 2;
+  __shared__ double2 srec[STAGE ? 4 * 32 * SS / 2 : 1];
   const int lane = threadIdx.x & 31;
   const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, n_warps = (gridDim.x * blockDim.x) >> 5;
   const double c_huber = P.c_huber_factor * sqrt(P.sc->median);
@@ -336,20 +339,20 @@ __global__ void __launch_bounds__(128, (L == 1) ? 3 : 4) k_linearize_packed(Devi
       double Vi[L * L], dhat[L], Wr[6];
       lm_finalize<L, 1>(P, lm, c, lm_on, S, Vi, dhat, Wr, head, 0);
       if (slot != kNoSlot) {
-        double* out = STAGE ? reinterpret_cast<double*>(srec) + ((threadIdx.x >> 5) * 32 + lane) * RS : P.rec + (size_t)slot * P.rec_stride;
+        double* out = STAGE ? reinterpret_cast<double*>(srec) + ((threadIdx.x >> 5) * 32 + lane) * SS : P.rec + (size_t)slot * P.rec_stride;
         emit_record<L>(out, c, o, w, lm_on, Vi, dhat, Wr);
       }
     }
     if (STAGE) {
       __syncwarp();
-      const double2* sw2 = srec + (threadIdx.x >> 5) * 32 * (RS / 2);
+      const double2* sw2 = srec + (threadIdx.x >> 5) * 32 * (SS / 2);
 #pragma unroll 2
       for (int base = 0; base < n * (RS / 2); base += 32) {     // uniform trip count: the shuffle needs every lane
         const int idx = base + lane;
         const bool valid = idx < n * (RS / 2);
         const int rec = valid ? idx / (RS / 2) : 0, ch = idx - rec * (RS / 2);
         const uint32_t sl = __shfl_sync(0xffffffffu, slot, rec);
-        if (valid && sl != kNoSlot) reinterpret_cast<double2*>(P.rec + (size_t)sl * RS)[ch] = sw2[rec * (RS / 2) + ch];
+        if (valid && sl != kNoSlot) reinterpret_cast<double2*>(P.rec + (size_t)sl * RS)[ch] = sw2[rec * (SS / 2) + ch];
       }
       __syncwarp();
     }
