@@ -66,6 +66,9 @@ def options_for(solver, p, keep_on_device):
     o = solver.default_options()
     o.error_change_threshold = 0          # run exactly K iterations (quirk Q9: the defaults stop early)
     o.param_change_threshold = 0
+    # `value` times the iterations alone: no end-of-Solve() hand-over of the state.  (The timed Solve(K) then starts
+    # from the warm-up's refined poses and the original landmark positions — a perturbed state like the initial one;
+    # every iteration does the full work.  The e2e leg runs without this flag.)
     o.keep_on_device = 1 if keep_on_device else 0
     if hasattr(p, "gravity"):
         o.gravity[0], o.gravity[1], o.gravity[2] = [float(x) for x in p.gravity]

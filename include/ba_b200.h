@@ -89,8 +89,11 @@ typedef struct bagpu_options {
   int32_t record_deltas;               /* keep per-iteration delta_p / delta_l for parity tests */
   double pcg_tolerance;                /* relative residual for solver 1 */
   uint32_t pcg_max_iterations;
-  int32_t keep_on_device;              /* skip the final device->host copy of the state (benchmarks; the
-                                          next solve without this flag, or bagpu_sync_state, downloads) */
+  int32_t keep_on_device;              /* skip the end-of-Solve() state hand-over (pose read-back, world-frame landmark
+                                          positions): for timing the iterations alone.  A following Solve() continues
+                                          from the refined poses but re-derives the landmarks from the positions of the
+                                          last hand-over; the next solve without this flag, or bagpu_sync_state, hands
+                                          the refined state over */
 } bagpu_options;
 
 /* reference ba::SolutionSummary<Scalar> (BundleAdjuster.h:48-70) + the private error
