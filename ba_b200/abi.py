@@ -6,6 +6,7 @@ The same class binds any library exporting these entry points under a prefix
 (``bagpu_`` for the CUDA product library).
 """
 import ctypes as C
+import os
 import numpy as np
 
 PH_NAMES = ["residual", "median", "accumulate", "other_residuals", "schur", "allreduce", "solve", "step", "total"]
@@ -246,6 +247,11 @@ class Binding:
         self._check(self._f("get_system")(self.h, _p(s, np.float64), _p(rsc, np.float64), _p(rp, np.float64),
                                           _p(rl, np.float64) if self.lm_dim else None, _p(vi, np.float64) if self.lm_dim else None))
         return dict(S=(s.T.copy() if dense_s else None), rhs_sc=rsc, rhs_p=rp, rhs_l=rl, v_inv=vi)
+
+    def dump(self, directory):
+        """s.txt / rhs.txt (the oracle adds j_pr.txt, r_pr.txt, j_l.txt) of the last build, in the reference's CSV
+        format (reference src/BundleAdjuster.cpp:600-620); read them back with ba_b200.dumpio.read_dump."""
+        self._check(self._f("dump")(self.h, C.c_char_p(os.fsencode(directory))))
 
     def sync_state(self):
         self._check(self._f("sync_state")(self.h))

@@ -1194,6 +1194,9 @@ struct bagpu_handle_s {
       build();
       const Scalars sb = read_scalars();
       collect_build_times();
+      // options.write_reduced_camera_matrix (cpp:600-606): s.txt / rhs.txt of this iteration's system into the working
+      // directory, overwritten every iteration like the reference's std::ios_base::trunc streams
+      if (opt.write_reduced_camera_matrix && bagpu_dump(this, ".") != BAGPU_OK) throw std::string("write_reduced_camera_matrix: cannot write s.txt / rhs.txt");
       bagpu_iter_trace tr; memset(&tr, 0, sizeof(tr));
       tr.proj_error_build = sb.proj_error; tr.binary_error_build = sb.binary_error;
       tr.unary_error_build = sb.unary_error; tr.inertial_error_build = sb.inertial_error; tr.median_maha = sb.median;
@@ -1671,11 +1674,12 @@ int bagpu_dump(bagpu_handle h, const char* dir) {
   const std::string d = dir ? dir : ".";
   FILE* f = fopen((d + "/s.txt").c_str(), "w");
   if (!f) return fail(BAGPU_ERR_INVALID, "cannot open s.txt");
-  for (int i = 0; i < n; ++i) { for (int j = 0; j < n; ++j) fprintf(f, j ? ", %.17g" : "%.17g", s[(size_t)j * n + i]); fprintf(f, "\n"); }
+  // Eigen's kLongCsvFmt puts "\n" between rows, none after the last
+  for (int i = 0; i < n; ++i) { if (i) fputc('\n', f); for (int j = 0; j < n; ++j) fprintf(f, j ? ", %.17g" : "%.17g", s[(size_t)j * n + i]); }
   fclose(f);
   f = fopen((d + "/rhs.txt").c_str(), "w");
   if (!f) return fail(BAGPU_ERR_INVALID, "cannot open rhs.txt");
-  for (int i = 0; i < n; ++i) fprintf(f, "%.17g\n", r[i]);
+  for (int i = 0; i < n; ++i) fprintf(f, i ? "\n%.17g" : "%.17g", r[i]);
   fclose(f);
   return BAGPU_OK;
 }

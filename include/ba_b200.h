@@ -203,7 +203,11 @@ int bagpu_get_pattern(bagpu_handle h, int which, uint32_t* ncols, uint32_t* nnzb
  * rhs_p_sc, rhs_p_, rhs_l_, vi_ (L*L per active landmark) of the last build */
 int bagpu_get_system(bagpu_handle h, double* s_dense, double* rhs_sc, double* rhs_p,
                      double* rhs_l, double* v_inv);
-/* s.txt / rhs.txt in the reference's CSV format (src/BundleAdjuster.cpp:600-606) */
+/* s.txt / rhs.txt of the last build in the reference's CSV format (src/BundleAdjuster.cpp:600-606, Eigen kLongCsvFmt of
+ * include/ba/Utils.h:66: ", " between coefficients, "\n" between rows; %.17g digits).  With
+ * options.write_reduced_camera_matrix set, bagpu_solve writes both files into the working directory at every outer
+ * iteration, as the reference does.  j_pr.txt / r_pr.txt / j_l.txt are not written: the build is matrix-free and never
+ * forms J.  ba_b200/dumpio.py reads the files and converts them to the compact binary twin. */
 int bagpu_dump(bagpu_handle h, const char* dir);
 
 /* ---- multi-GPU (landmark sharding) --------------------------------- */

@@ -57,6 +57,7 @@ struct OracleBase {
   virtual int get_proj(double* r, double* w, double* m) = 0;
   virtual int get_pattern(int which, uint32_t* ncols, uint32_t* nnzb, uint32_t* colptr, uint32_t* rowidx) = 0;
   virtual int get_system(double* s, double* rsc, double* rp, double* rl, double* vi) = 0;
+  virtual int dump(const char* dir) = 0;
 };
 
 template <int LM, int D>
@@ -1007,6 +1008,7 @@ struct BundleAdjuster : OracleBase {
     for (uint32_t kk = 0; kk < uMaxIter; ++kk) {
       BuildProblem();
       SetupProblem();
+      if (opt.write_reduced_camera_matrix) dump(".");   // cpp:600-620
       bagpu_iter_trace tr; RecordBuild(tr);
       Delta applied;
       const bool ok = SolveInternal(rhs_p_sc_, gn_damping, error_increase_allowed, opt.use_dogleg != 0, tr, applied);
@@ -1102,6 +1104,54 @@ struct BundleAdjuster : OracleBase {
     if (vi && LM > 0) for (uint32_t l = 0; l < num_active_landmarks_; ++l) { const Mat<LMS, LMS> v = vi_.coeff(l, l); memcpy(vi + (size_t)l * LMS * LMS, v.a, sizeof(double) * LMS * LMS); }
     return 0;
   }
+
+  // write_reduced_camera_matrix block of Solve (reference src/BundleAdjuster.cpp:600-620): s.txt, rhs.txt,
+  // j_pr.txt, r_pr.txt, j_l.txt in Eigen's kLongCsvFmt (Utils.h:66: ", " between coefficients, "\n" between
+  // rows, no trailing newline).  Digits: %.17g (round-trip) where Eigen's FullPrecision prints 15-16
+  // significant digits.  The Jacobians are densified like Eigen::LoadDenseFromSparse does, so this is for
+  // parity-sized problems only; j_kpr.txt is not written (CalibSize = 0).
+  template <int R, int C>
+  static int write_dense_blocks(const std::string& path, const BlockMat<R, C>& m) {
+    const size_t rows = (size_t)m.rows() * R, cols = (size_t)m.cols() * C;
+    if (rows * cols > ((size_t)1 << 27)) return BAGPU_ERR_INVALID;
+    std::vector<double> d(rows * cols, 0.0);
+    for (int j = 0; j < m.cols(); ++j)
+      for (const auto& e : m.col[j])
+        for (int r = 0; r < R; ++r) for (int c = 0; c < C; ++c) d[((size_t)e.index * R + r) * cols + (size_t)j * C + c] = e.value(r, c);
+    FILE* f = fopen(path.c_str(), "w");
+    if (!f) return BAGPU_ERR_INVALID;
+    for (size_t i = 0; i < rows; ++i) {
+      if (i) fputc('\n', f);
+      for (size_t j = 0; j < cols; ++j) fprintf(f, j ? ", %.17g" : "%.17g", d[i * cols + j]);
+    }
+    fclose(f);
+    return 0;
+  }
+  static int write_vector(const std::string& path, const VecX& v) {
+    FILE* f = fopen(path.c_str(), "w");
+    if (!f) return BAGPU_ERR_INVALID;
+    for (size_t i = 0; i < v.size(); ++i) fprintf(f, i ? "\n%.17g" : "%.17g", v[i]);
+    fclose(f);
+    return 0;
+  }
+  int dump(const char* dir) override {
+    const std::string d = dir ? dir : ".";
+    const int n = s_.n;
+    FILE* f = fopen((d + "/s.txt").c_str(), "w");
+    if (!f) return BAGPU_ERR_INVALID;
+    for (int i = 0; i < n; ++i) {
+      if (i) fputc('\n', f);
+      for (int j = 0; j < n; ++j) fprintf(f, j ? ", %.17g" : "%.17g", (i <= j) ? s_.get(i, j) : 0.0);
+    }
+    fclose(f);
+    int rc = write_vector(d + "/rhs.txt", rhs_p_sc_);
+    if (rc) return rc;
+    if (proj_residuals_.size() == 0) return 0;
+    if ((rc = write_dense_blocks(d + "/j_pr.txt", j_pr_))) return rc;
+    if ((rc = write_vector(d + "/r_pr.txt", r_pr_))) return rc;
+    if (LM > 0 && (rc = write_dense_blocks(d + "/j_l.txt", j_l_))) return rc;
+    return 0;
+  }
 };
 
 static thread_local std::string g_err;
@@ -1180,6 +1230,7 @@ int baoracle_get_deltas(baoracle_handle h, uint32_t iter, double* dp, double* dl
 }
 int baoracle_get_pattern(baoracle_handle h, int which, uint32_t* nc, uint32_t* nnzb, uint32_t* cp, uint32_t* ri) { return h->impl->get_pattern(which, nc, nnzb, cp, ri); }
 int baoracle_get_system(baoracle_handle h, double* s, double* rsc, double* rp, double* rl, double* vi) { return h->impl->get_system(s, rsc, rp, rl, vi); }
+int baoracle_dump(baoracle_handle h, const char* dir) { return h->impl->dump(dir); }
 int baoracle_sync_state(baoracle_handle) { return 0; }
 int baoracle_get_phase_ms(baoracle_handle h, float* ms, uint64_t* launches) {
   for (int i = 0; i < BAGPU_PH_COUNT; ++i) ms[i] = (float)(h->impl->phase_s[i] * 1e3);

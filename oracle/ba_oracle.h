@@ -36,6 +36,8 @@ int baoracle_get_trace(baoracle_handle h, uint32_t max_records, bagpu_iter_trace
 int baoracle_get_deltas(baoracle_handle h, uint32_t iter, double* delta_p, double* delta_l);
 int baoracle_get_pattern(baoracle_handle h, int which, uint32_t* ncols, uint32_t* nnzb, uint32_t* colptr, uint32_t* rowidx);
 int baoracle_get_system(baoracle_handle h, double* s_dense, double* rhs_sc, double* rhs_p, double* rhs_l, double* v_inv);
+/* s.txt rhs.txt j_pr.txt r_pr.txt j_l.txt of the last build, reference src/BundleAdjuster.cpp:600-620 */
+int baoracle_dump(baoracle_handle h, const char* dir);
 int baoracle_sync_state(baoracle_handle h);
 int baoracle_get_phase_ms(baoracle_handle h, float* ms, uint64_t* kernel_launches);
 #ifdef __cplusplus

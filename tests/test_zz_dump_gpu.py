@@ -1,0 +1,78 @@
+"""s.txt / rhs.txt written by the CUDA path (bagpu_dump, options.write_reduced_camera_matrix; reference
+src/BundleAdjuster.cpp:600-606) against the same files from the CPU oracle, read through ba_b200.dumpio."""
+import os
+import numpy as np
+import pytest
+
+from ba_b200 import dumpio, synth
+from ba_b200.abi import PATTERN_S
+
+pytestmark = pytest.mark.gpu
+
+
+def _mk(cls, p, **opts):
+    s = cls(p.lm_dim, p.pose_dim)
+    o = s.default_options()
+    o.error_change_threshold = 0
+    o.param_change_threshold = 0
+    for k, v in opts.items():
+        setattr(o, k, v)
+    s.set_options(o)
+    s.load(p)
+    return s
+
+
+def _pair(p, **opts):
+    from ba_b200.capi import BundleAdjusterGPU
+    from oracle.oracle_py import Oracle
+    return _mk(BundleAdjusterGPU, p, **opts), _mk(Oracle, p, **opts)
+
+
+def rel(a, b):
+    return np.linalg.norm(np.asarray(a) - np.asarray(b)) / max(np.linalg.norm(b), 1e-300)
+
+
+@pytest.mark.parametrize("make", [lambda: synth.make_c1(n_poses=8, n_landmarks=120, obs_per_lm=5, seed=21),
+                                  lambda: synth.make_c2(n_cams=14, n_points=150, seed=21, window=8),
+                                  lambda: synth.make_c5(n_poses=40, seed=21)], ids=["lm1", "lm3", "pose_graph"])
+def test_dump_files_match_the_oracles(tmp_path, make):
+    p = make()
+    g, o = _pair(p)
+    g.build(); o.build()
+    dg, do = str(tmp_path / "gpu"), str(tmp_path / "oracle")
+    os.mkdir(dg); os.mkdir(do)
+    g.dump(dg); o.dump(do)
+    a, b = dumpio.read_dump(dg), dumpio.read_dump(do)
+    assert sorted(a) == ["rhs", "s"]                                   # the GPU build never forms J
+    text = open(os.path.join(dg, "s.txt")).read()
+    assert not text.endswith("\n") and ", " in text                    # Eigen kLongCsvFmt (Utils.h:66)
+    n = g.n_active_poses * p.pose_dim
+    assert a["s"].shape == b["s"].shape == (n, n) and not np.tril(a["s"], -1).any()
+    assert rel(a["s"], b["s"]) < 1e-12 and rel(a["rhs"], b["rhs"]) < 1e-11
+    assert np.array_equal(a["s"], np.triu(g.get_system()["S"]))       # the text round-trips bit-exactly
+    # binary twin on the symbolic pattern: same matrix, same block structure as the oracle's
+    out = dumpio.csv_dump_to_bin(dg, pose_dim=p.pose_dim, lm_dim=p.lm_dim, s_pattern=g.get_pattern(PATTERN_S))
+    cp, ri, val, shape = dumpio.read_bin(out["s"], dense=False)
+    cpo, rio = o.get_pattern(PATTERN_S)
+    assert np.array_equal(cp, cpo) and np.array_equal(ri, rio)
+    assert np.array_equal(dumpio.read_bin(out["s"]), a["s"])
+
+
+def test_write_reduced_camera_matrix_option_dumps_every_iteration(tmp_path, monkeypatch):
+    p = synth.make_c1(n_poses=8, n_landmarks=120, obs_per_lm=5, seed=22)
+    dg, do = str(tmp_path / "gpu"), str(tmp_path / "oracle")
+    os.mkdir(dg); os.mkdir(do)
+    g, o = _pair(p, write_reduced_camera_matrix=1)
+    monkeypatch.chdir(dg)
+    sg = g.solve(3)
+    monkeypatch.chdir(do)
+    so = o.solve(3)
+    assert sg.iterations == so.iterations == 3
+    a, b = dumpio.read_dump(dg), dumpio.read_dump(do)
+    # the files left behind are those of the last iteration's system
+    assert rel(a["s"], b["s"]) < 1e-6 and rel(a["rhs"], b["rhs"]) < 1e-6
+    g1, _ = _pair(p)
+    g1.build()
+    first = g1.get_system()
+    assert rel(a["rhs"], first["rhs_sc"]) > 1e-3                       # not the first iteration's
+    assert abs(sg.post_solve_norm - so.post_solve_norm) <= 1e-9 * so.post_solve_norm
