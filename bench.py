@@ -145,6 +145,19 @@ def cpu_reference_run(name, steps, warmup, budget_s=150.0):
                 cores=1)
 
 
+def l2_note(name, scale):
+    """Timing rule: inputs larger than L2, or say that they are not.  Per iteration the build streams the landmark-sorted
+    observations (40 B each) and writes + reads one record per observation (28 doubles for LmSize 3, 40 for LmSize 1)."""
+    n = make_counts(name) * scale
+    if name == "c5":
+        n = 0
+    mb = n * (40 + 8 * (28 if name == "c2" else 40)) / 1e6
+    if mb > 126:
+        return "inputs larger than L2: every iteration streams %.0f MB of sorted observations and records (L2 = 126 MB)" % mb
+    return ("working set of the build (%.0f MB) fits in L2, no flush between iterations: this configuration is "
+            "launch/latency-bound (SURVEY 8d), its number is not an HBM figure" % mb)
+
+
 def make_counts(name):
     return {"c1": 100000, "c2": 5000000, "c3": 2000499, "c4": 10000000, "c5": 21200}[name]
 
@@ -166,7 +179,7 @@ def main():
             "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
             "config": {"workload": WORKLOADS[name]["desc"] + (" (scale %.3g)" % args.scale if args.scale != 1.0 else ""),
                        "solver": "dogleg, nested-dissection tile LDL^T (dataflow kernel)", "sharding": "landmarks over %d GPU(s)" % args.gpus,
-                       "l2": "inputs larger than L2 (sorted observation stream >= 180 MB)"}}
+                       "l2": l2_note(name, args.scale)}}
 
     if args.impl == "reference":
         if rank != 0:
