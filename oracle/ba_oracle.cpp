@@ -1250,6 +1250,55 @@ void baoracle_math_dlog_dq(const double* q4, double* out12) { Mat<3, 4> m = dlog
 void baoracle_math_dlog_decoupled_dx(const double* a7, const double* b7, double* out36) { Mat<6, 6> m = dlog_decoupled_dx(SE3::from7(a7), SE3::from7(b7)); memcpy(out36, m.a, 288); }
 void baoracle_math_sqrtm6(const double* a36, double* out36) { Mat<6, 6> m; memcpy(m.a, a36, 288); Mat<6, 6> r = sqrtm_spd(m); memcpy(out36, r.a, 288); }
 void baoracle_math_inverse6(const double* a36, double* out36) { Mat<6, 6> m; memcpy(m.a, a36, 288); Mat<6, 6> r = inverse(m); memcpy(out36, r.a, 288); }
+// Block-sparse operations on caller-supplied dense matrices, the checks of the reference's math demo
+// (applications/math_test/main.cpp:157-314: 70x50 blocks of 6x3 against 50x70 blocks of 3x6, dense and ~5 % sparse).
+// a: (nr*6) x (nc*3) row-major, b: (nc*3) x (nr*6) row-major, x: nc*3, y: nr*6.  A block is stored iff it has a non-zero
+// coefficient (LoadSparseFromDense, SparseBlockMatrixOps.h:400-414).  Outputs, all dense row-major:
+// ab (nr*6)^2 = A*B; ab_upper = A*B with upper_triangular (blocks above the break of Ops.h:236-238 only);
+// at (nc*3) x (nr*6) = forceTranspose(A); ax = A*x; aty = A^T*y through the transposed copy; sum = A*B + 2*(A*B);
+// a_scaled (nr*6) x (nc*3) = A * blockdiag(d) with d = the nc diagonal 3x3 blocks given in dblocks (nc*9).
+}  // extern "C"
+template <int R, int C>
+static void load_sparse_from_dense(const double* d, int nrb, int ncb, BlockMat<R, C>& m) {
+  m.resize(nrb, ncb);
+  const size_t ld = (size_t)ncb * C;
+  for (int j = 0; j < ncb; ++j) for (int i = 0; i < nrb; ++i) {
+    Mat<R, C> blk; bool nz = false;
+    for (int r = 0; r < R; ++r) for (int c = 0; c < C; ++c) { blk(r, c) = d[((size_t)i * R + r) * ld + (size_t)j * C + c]; nz |= blk(r, c) != 0.0; }
+    if (nz) m.insertBack(i, j, blk);
+  }
+}
+template <int R, int C>
+static void load_dense_from_sparse(const BlockMat<R, C>& m, double* d) {
+  const size_t ld = (size_t)m.cols() * C;
+  std::fill(d, d + (size_t)m.rows() * R * ld, 0.0);
+  for (int j = 0; j < m.cols(); ++j) for (const auto& e : m.col[j])
+    for (int r = 0; r < R; ++r) for (int c = 0; c < C; ++c) d[((size_t)e.index * R + r) * ld + (size_t)j * C + c] = e.value(r, c);
+}
+extern "C" {
+void baoracle_math_block_sparse_ops(int nr, int nc, const double* a, const double* b, const double* x, const double* y, const double* dblocks,
+                                    double* ab, double* ab_upper, double* at, double* ax, double* aty, double* sum, double* a_scaled,
+                                    uint32_t* nnzb_out /* A, B, A*B, upper A*B */) {
+  BlockMat<6, 3> A; BlockMat<3, 6> B, At; BlockMat<6, 6> AB, ABu, S;
+  load_sparse_from_dense(a, nr, nc, A);
+  load_sparse_from_dense(b, nc, nr, B);
+  SparseBlockProduct(A, B, AB);
+  SparseBlockProduct(A, B, ABu, true);
+  BlockMat<3, 6>::forceTranspose(A, At);
+  load_dense_from_sparse(AB, ab); load_dense_from_sparse(ABu, ab_upper); load_dense_from_sparse(At, at);
+  VecX vx(x, x + (size_t)nc * 3), vy(y, y + (size_t)nr * 6), rax((size_t)nr * 6), raty((size_t)nc * 3);
+  SparseBlockVectorProductDenseResult(A, vx, rax);
+  SparseBlockVectorProductDenseResult(At, vy, raty);
+  memcpy(ax, rax.data(), rax.size() * 8); memcpy(aty, raty.data(), raty.size() * 8);
+  SparseBlockAdd(AB, AB, S, 2);
+  load_dense_from_sparse(S, sum);
+  BlockMat<3, 3> D(nc, nc);
+  for (int j = 0; j < nc; ++j) { Mat<3, 3> blk; memcpy(blk.a, dblocks + (size_t)j * 9, 72); D.insertBack(j, j, blk); }
+  BlockMat<6, 3> AD;
+  SparseBlockDiagonalRhsProduct(A, D, AD);
+  load_dense_from_sparse(AD, a_scaled);
+  if (nnzb_out) { nnzb_out[0] = (uint32_t)A.nonZeros(); nnzb_out[1] = (uint32_t)B.nonZeros(); nnzb_out[2] = (uint32_t)AB.nonZeros(); nnzb_out[3] = (uint32_t)ABu.nonZeros(); }
+}
 // binary residual + Jacobians exactly as BuildProblem computes them (cpp:1396-1411)
 void baoracle_math_binary(const double* tw1_7, const double* tw2_7, const double* t12_7, double* r6, double* j1_36, double* j2_36) {
   const SE3 t_w1 = SE3::from7(tw1_7), t_w2 = SE3::from7(tw2_7), t12m = SE3::from7(t12_7);

@@ -317,3 +317,48 @@ def test_pose_graph_and_visual_inertial_run():
     m = s.get_poses()
     # poses without... every pose has an IMU residual; the root pose gets translation + one rotation axis fixed
     assert m["mask_used"][0] == 1 and list(m["mask"][0][:3]) == [0, 0, 0] and m["mask"][0][3:6].sum() == 2
+
+
+@pytest.mark.parametrize("density", [1.0, 0.05])
+def test_block_sparse_ops_against_dense_numpy(density):
+    """The reference's math demo with assertions (applications/math_test/main.cpp:157-314: 70 x 50 blocks of 6x3 times
+    50 x 70 blocks of 3x6, dense and ~5 % sparse): load / product / upper-triangular product / forceTranspose /
+    vector products / add / block-diagonal product of the oracle's block-CSC container against dense NumPy."""
+    import ctypes as C
+    from oracle.oracle_py import lib
+    rng = np.random.default_rng(17)
+    nr, nc = 70, 50
+
+    def blocks(nrb, ncb, r, c):
+        keep = rng.uniform(size=(nrb, ncb)) < density
+        return (rng.normal(size=(nrb, r, ncb, c)) * keep[:, None, :, None]).reshape(nrb * r, ncb * c), keep
+    a, ka = blocks(nr, nc, 6, 3)
+    b, kb = blocks(nc, nr, 3, 6)
+    x, y = rng.normal(size=nc * 3), rng.normal(size=nr * 6)
+    d = rng.normal(size=(nc, 3, 3))
+    n = nr * 6
+    out = dict(ab=np.zeros((n, n)), abu=np.zeros((n, n)), at=np.zeros((nc * 3, n)), ax=np.zeros(n), aty=np.zeros(nc * 3),
+               sum=np.zeros((n, n)), ad=np.zeros((n, nc * 3)))
+    nnzb = np.zeros(4, np.uint32)
+    f = lib().baoracle_math_block_sparse_ops
+    f.restype = None
+    ptr = lambda v: np.ascontiguousarray(v).ctypes.data_as(C.c_void_p)
+    f(C.c_int(nr), C.c_int(nc), ptr(a), ptr(b), ptr(x), ptr(y), ptr(d), *[ptr(out[k]) for k in ("ab", "abu", "at", "ax", "aty", "sum", "ad")],
+      ptr(nnzb))
+    ab = a @ b
+    tol = 1e-12 * np.abs(ab).max()
+    assert nnzb[0] == ka.sum() and nnzb[1] == kb.sum()                      # LoadSparseFromDense keeps the non-zero blocks
+    assert np.abs(out["ab"] - ab).max() < tol
+    # result pattern = structural product of the block patterns (explicit zeros kept, BlockAmbiVector.h:174-241)
+    assert nnzb[2] == ((ka.astype(int) @ kb.astype(int)) > 0).sum()
+    # upper_triangular (SparseBlockMatrixOps.h:236-238): block rows <= block column only
+    bi = np.arange(n) // 6
+    upper = bi[:, None] <= bi[None, :]
+    assert np.abs(out["abu"] - ab * upper).max() < tol and not out["abu"][~upper].any()
+    assert nnzb[3] == np.triu((ka.astype(int) @ kb.astype(int)) > 0).sum()
+    assert np.array_equal(out["at"], a.T)                                   # forceTranspose is exact
+    assert np.abs(out["ax"] - a @ x).max() < 1e-12 * np.abs(a @ x).max()
+    assert np.abs(out["aty"] - a.T @ y).max() < 1e-12 * np.abs(a.T @ y).max()
+    assert np.abs(out["sum"] - 3 * ab).max() < 3 * tol                      # SparseBlockAdd(lhs, rhs, res, 2)
+    ad = np.einsum("ijk,jkl->ijl", a.reshape(n, nc, 3), d).reshape(n, nc * 3)   # A * blockdiag(d)
+    assert np.abs(out["ad"] - ad).max() < 1e-12 * np.abs(ad).max()
