@@ -127,3 +127,52 @@ def test_pose_graph_dump_has_no_projection_files(tmp_path):
     assert sorted(d) == ["rhs", "s"]
     sysm = s.get_system()
     assert np.array_equal(d["s"], np.triu(sysm["S"])) and np.array_equal(d["rhs"], sysm["rhs_sc"])
+
+
+def _dogleg_from_dump(directory, trust_region):
+    """The step the reference's dogleg prototype takes (reference matlab/dogleg.m:12-41) from the dumped J and r,
+    with the beta of src/BundleAdjuster.cpp:1007-1008 (same expression in dogleg.m:36: -b^2, not -b)."""
+    d = dumpio.read_dump(directory)
+    J = np.hstack([d["j_pr"], d["j_l"]]); r = d["r_pr"]
+    n_p = d["j_pr"].shape[1]
+    g = J.T @ r
+    top, bottom = g @ g, np.linalg.norm(J @ g) ** 2
+    sd = top / bottom * g
+    gn = np.linalg.solve(J.T @ J, g)
+    out = dict(top=top, bottom=bottom, sd=sd, gn=gn, n_p=n_p)
+    if np.linalg.norm(sd) >= trust_region:
+        out["step"], out["branch"] = trust_region / np.linalg.norm(sd) * sd, "sd"
+    elif np.linalg.norm(gn) <= trust_region:
+        out["step"], out["branch"] = gn, "gn"
+    else:
+        diff = gn - sd
+        a, b, c = diff @ diff, 2 * (diff @ sd), sd @ sd - trust_region ** 2
+        beta = (-b * b + np.sqrt(b * b - 4 * a * c)) / (2 * a)
+        out["step"], out["branch"], out["beta"] = sd + beta * diff, "blend", beta
+        out["textbook"] = sd + (-b + np.sqrt(b * b - 4 * a * c)) / (2 * a) * diff
+    return out
+
+
+@pytest.mark.parametrize("trust_region,branch", [(1e-3, "sd"), (0.1, "blend"), (10.0, "gn")])
+def test_dogleg_step_follows_the_prototype(tmp_path, monkeypatch, trust_region, branch):
+    p = synth.make_c1(n_poses=6, n_landmarks=40, obs_per_lm=4, seed=11)
+    s = make_solver(p, record_deltas=1, write_reduced_camera_matrix=1, trust_region_size=trust_region)
+    monkeypatch.chdir(tmp_path)
+    s.solve(1)
+    tr = s.get_trace()[0]
+    ref = _dogleg_from_dump(str(tmp_path), trust_region)
+    assert ref["branch"] == branch and tr["inner_iterations"] == 1
+    assert abs(tr["sd_numerator"] - ref["top"]) <= 1e-12 * ref["top"]
+    assert abs(tr["sd_denominator"] - ref["bottom"]) <= 1e-12 * ref["bottom"]
+    assert abs(tr["sd_norm"] - np.linalg.norm(ref["sd"])) <= 1e-12 * tr["sd_norm"]
+    if branch != "sd":                                                 # the GN step is only computed when needed
+        assert abs(tr["gn_norm"] - np.linalg.norm(ref["gn"])) <= 1e-9 * tr["gn_norm"]
+    dp, dl = s.get_deltas(0)
+    step = np.concatenate([dp, dl])
+    assert np.linalg.norm(step - ref["step"]) <= 1e-9 * np.linalg.norm(step)
+    # summary_.delta_norm adds the two norms (cpp:26)
+    assert abs(tr["delta_norm"] - (np.linalg.norm(dp) + np.linalg.norm(dl))) <= 1e-12 * tr["delta_norm"]
+    if branch == "blend":
+        # quirk Q4: the step is not on the trust-region boundary, the textbook root would be
+        assert abs(np.linalg.norm(ref["textbook"]) - trust_region) < 1e-12
+        assert abs(np.linalg.norm(step) - trust_region) > 1e-5

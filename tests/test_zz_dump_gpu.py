@@ -76,3 +76,27 @@ def test_write_reduced_camera_matrix_option_dumps_every_iteration(tmp_path, monk
     first = g1.get_system()
     assert rel(a["rhs"], first["rhs_sc"]) > 1e-3                       # not the first iteration's
     assert abs(sg.post_solve_norm - so.post_solve_norm) <= 1e-9 * so.post_solve_norm
+
+
+@pytest.mark.parametrize("trust_region,branch", [(1e-3, "sd"), (0.1, "blend"), (10.0, "gn")])
+def test_dogleg_step_follows_the_prototype_on_the_gpu(tmp_path, monkeypatch, trust_region, branch):
+    """The three branches of the dogleg rule (reference matlab/dogleg.m:12-41, beta of cpp:1007-1008) rebuilt in NumPy
+    from the oracle's dumped J and r, against the step the CUDA path takes."""
+    from tests.test_dump_cpu import _dogleg_from_dump
+    p = synth.make_c1(n_poses=6, n_landmarks=40, obs_per_lm=4, seed=11)
+    g, o = _pair(p, record_deltas=1, trust_region_size=trust_region)
+    o.options.write_reduced_camera_matrix = 1
+    o.set_options(o.options)
+    monkeypatch.chdir(tmp_path)
+    o.solve(1); g.solve(1)
+    ref = _dogleg_from_dump(str(tmp_path), trust_region)
+    assert ref["branch"] == branch
+    tg = g.get_trace()[0]
+    assert tg["inner_iterations"] == 1
+    assert abs(tg["sd_numerator"] - ref["top"]) <= 1e-11 * ref["top"]
+    assert abs(tg["sd_denominator"] - ref["bottom"]) <= 1e-11 * ref["bottom"]
+    dp, dl = g.get_deltas(0)
+    step = np.concatenate([dp, dl])
+    assert np.linalg.norm(step - ref["step"]) <= 1e-9 * np.linalg.norm(step)
+    if branch == "blend":
+        assert abs(np.linalg.norm(step) - trust_region) > 1e-5           # quirk Q4 reproduced
