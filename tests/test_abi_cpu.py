@@ -87,6 +87,10 @@ def test_no_cpu_fallback():
     with pytest.raises(RuntimeError) as e:
         g.solve(1)
     assert "no CUDA device" in str(e.value)
+    for call in (g.build, lambda: g.dump("."), g.get_system):           # every computing entry point, not just solve
+        with pytest.raises(RuntimeError) as e:
+            call()
+        assert "no CUDA device" in str(e.value)
 
 
 def test_patterns_from_ids_need_no_device():
