@@ -28,6 +28,7 @@
 #include <cstdio>
 #include <fstream>
 #include <string>
+#include <thread>
 
 namespace orc {
 
@@ -407,9 +408,31 @@ struct BundleAdjuster : OracleBase {
   }
 
   // ---- inertial functor, parallel_algos.h:178-358 ----------------------------------
+  // The reference runs this functor under tbb::parallel_reduce (src/BundleAdjuster.cpp:1494); the residuals are
+  // independent, so a static split over std::threads gives the same numbers, and the error list is filled in
+  // residual order afterwards (what the reduce's join produces).  imu_threads_used reports the split for the
+  // cpu_baseline's core count; BAORACLE_THREADS=1 forces the serial loop.
+  int imu_threads_used = 1;
   void InertialResiduals(std::vector<double>& errors) {
+    const size_t n = inertial_residuals_.size();
+    size_t nt = std::thread::hardware_concurrency();
+    if (const char* e = getenv("BAORACLE_THREADS")) nt = (size_t)std::max(1, atoi(e));
+    nt = std::max<size_t>(1, std::min(nt, n / 8));
+    imu_threads_used = (int)nt;
+    if (nt <= 1) {
+      for (size_t ii = 0; ii < n; ii++) InertialResidual(ii);
+    } else {
+      std::vector<std::thread> pool;
+      for (size_t t = 0; t < nt; ++t)
+        pool.emplace_back([this, t, nt, n]() { for (size_t ii = n * t / nt; ii < n * (t + 1) / nt; ++ii) InertialResidual(ii); });
+      for (std::thread& th : pool) th.join();
+    }
     if constexpr (D >= 9)
-    for (size_t ii = 0; ii < inertial_residuals_.size(); ii++) {
+      for (size_t ii = 0; ii < n; ii++) errors.push_back(inertial_residuals_[ii].mahalanobis_distance);
+  }
+  void InertialResidual(const size_t ii) {
+    if constexpr (D >= 9)
+    {
       ImuRes& res = inertial_residuals_[ii];
       const Vec3 gravity = imu_.g_vec;
       const Pose& pose1 = poses_[res.pose1_id];
@@ -470,7 +493,6 @@ struct BundleAdjuster : OracleBase {
         for (int k = 0; k < 6; ++k) res.residual[BO + k] = pose1.b[k] - pose2.b[k];
       }
       res.mahalanobis_distance = (res.residual.transpose() * res.cov_inv * res.residual)(0, 0);
-      errors.push_back(res.mahalanobis_distance);
     }
   }
 

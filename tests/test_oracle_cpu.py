@@ -362,3 +362,21 @@ def test_block_sparse_ops_against_dense_numpy(density):
     assert np.abs(out["sum"] - 3 * ab).max() < 3 * tol                      # SparseBlockAdd(lhs, rhs, res, 2)
     ad = np.einsum("ijk,jkl->ijl", a.reshape(n, nc, 3), d).reshape(n, nc * 3)   # A * blockdiag(d)
     assert np.abs(out["ad"] - ad).max() < 1e-12 * np.abs(ad).max()
+
+
+def test_threaded_imu_functor_is_bit_identical_to_the_serial_loop(monkeypatch):
+    """The reference runs the IMU functor under tbb::parallel_reduce (cpp:1494); the oracle's thread split must not
+    change a bit of the result (the residuals are independent)."""
+    p = synth.make_c3(n_keyframes=80, n_landmarks=150, obs_per_lm=5)
+
+    def run(threads):
+        if threads is None:
+            monkeypatch.delenv("BAORACLE_THREADS", raising=False)
+        else:
+            monkeypatch.setenv("BAORACLE_THREADS", str(threads))
+        s = make_solver(p)
+        summ = s.solve(3)
+        return summ.post_solve_norm, s.get_poses()["t_wp"].copy(), [t["inertial_error_build"] for t in s.get_trace()]
+    a, b, c = run(1), run(4), run(None)
+    for other in (b, c):
+        assert a[0] == other[0] and np.array_equal(a[1], other[1]) and a[2] == other[2]
