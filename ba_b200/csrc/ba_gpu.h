@@ -1,22 +1,26 @@
 // ba_gpu.h — internal device-side data layout of the B200 BundleAdjuster path.
 //
-// HBM layout (all structure-of-arrays, doubles unless noted):
+// HBM layout (all structure-of-arrays unless noted, doubles unless noted):
 //   poses        q[4P] t[3P] v[3P] b[6P], opt id (int32, -1 inactive), free-parameter bit mask
 //   pose frames  per (pose, camera): T_sw = [R_sw(9) t_sw(3)], T_ws = [R_ws(9) t_ws(3)], plus R_wp(9)
 //                (replaces the PoseT::t_sw cache, reference include/ba/Types.h:59-70)
 //   landmarks    x[4N] (x_s for LmSize 1, x_w for LmSize 3), ref pose/cam, opt id, reliable flag
 //   observations sorted by landmark id, ties by residual id: z[2] (double2), meas pose (u32),
-//                cam (u32), orig weight; CSR lm_obs_start[N+1]; perm[] back to residual ids
+//                cam (u32), orig weight; CSR lm_obs_start[N+1]; perm[] back to residual ids;
+//                the same stream once more as 32-byte records {z, orig weight, pose, landmark} (ObsRec)
+//                for the pose-pair-major pass, which gathers single observations
 //   per-obs      maha0 (median input), weight (Huber)
-//   records      one per observation whose measurement pose is optimised, stored POSE-MAJOR
-//                (slot = obs_slot[obs]; pose p owns slots pose_rec_start[p] .. [p+1]):
-//                  LmSize 3 (28 doubles): C = Bt V^-1 (2x3) | At (2x6) | Bt (2x3) | rt (2) | rho (2)
-//                  LmSize 1 (40 doubles): E = W V^-1 (6) | W = At^T Bt (6) | At (2x6) | Q (2x6) | rt (2) | rho (2)
-//                with At = sqrt(w) J_meas, Bt = sqrt(w) J_lm, rt = sqrt(w) r, rho = rt - Bt V^-1 b_l,
-//                Q = At_ref - Bt V^-1 W_ref^T (the reference-pose Jacobian with the landmark projected out)
-//   per-landmark V^-1 (L x L), b_l (L), dhat = V^-1 b_l, W_ref (6, LmSize 1 only), and for LmSize 1 a
-//                reference-pose record (36 doubles, stored by reference pose): H_rr - W_r V^-1 W_r^T
-//                (upper, 21) | g_r (6) | g_r - W_r dhat (6)
+//   per-landmark record of the current linearisation (LmRec, 128 bytes, rewritten by k_linearize every build):
+//                  LmSize 3: X (3) | rho | V^-1 upper (6) | dhat = V^-1 b_l (3)
+//                  LmSize 1: X world (3) | rho | t_ws of the reference frame (3) | V^-1 | dhat | ray x_s (3) |
+//                            SBl = sum w Bp^T J_l (3)
+//                and, LmSize 1 only, 96 bytes more (LmRecC): SBB = sum w Bp^T Bp upper (6) | SBr = sum w Bp^T r (3),
+//                the sums over the landmark's observations from which the reference pose's blocks follow
+//                (Bp = d project / d X_world, see proj_kernels.cuh)
+//   pose-major   pose_obs: the observation indices (landmark-major positions) of every optimised pose, and for
+//                LmSize 1 pose_lms: the landmarks referenced to every optimised pose.  NO Jacobians, products or
+//                per-observation records are stored: the pose-pair pass recomputes both Jacobians of a pair from
+//                two ObsRec + one LmRec (5 sectors) against pose frames that are uniform over the warp.
 //   reduced S    upper block-tile storage: tiles of T x T doubles (T = 8 poses x PoseSize),
 //                column-major inside a tile, tile_map[tI * nT + tJ] -> tile slot or -1
 #pragma once
@@ -28,7 +32,8 @@ namespace bagpu {
 
 constexpr int kTilePoses = 8;   // poses per S tile
 constexpr uint32_t kNoSlot = 0xffffffffu;
-constexpr int kRec3 = 28, kRec1 = 40, kLmRec = 36;
+constexpr int kLmRec = 16, kLmRecC = 12;   // doubles per landmark record (128 B) / LmSize-1 extension (96 B)
+struct __align__(32) ObsRec { double zx, zy, w0; uint32_t pose, lm; };
 
 struct Scalars {       // device-resident scalar block (one per handle)
   double median;       // nth_element value of maha0
@@ -48,6 +53,7 @@ struct DeviceProblem {
   int L, D;                 // LmSize, PoseSize
   int n_cams, n_poses, n_active_poses, n_lms, n_active_lms, n_obs;
   int n_unary, n_binary, n_imu;
+  int cam_identity;          // every camera has T_vs = identity (the usual case: one branch skips the extrinsics products)
   // cameras
   const double* cam_params;  // 4 per cam
   const double* cam_Rvs;     // 9 per cam
@@ -76,16 +82,17 @@ struct DeviceProblem {
   const uint32_t* obs_lm;    // sorted index -> landmark id (non-decreasing)
   double* obs_maha0;
   double* obs_w;
-  const uint32_t* obs_slot;  // pose-major record slot of the observation, kNoSlot if its pose takes no part
-  double* rec;               // records, rec_stride doubles each
-  int rec_stride;            // 28 (LmSize 3) or 40 (LmSize 1)
+  const ObsRec* obs_rec;     // the same stream as 32-byte records (pose-pair pass)
+  const uint32_t* pose_obs;  // observation indices grouped by optimised measurement pose (pose-major), n_pose_obs entries
+  const uint32_t* pose_obs_lm;  // landmark of pose_obs[k]
+  const uint32_t* pose_lms;  // L == 1: landmark ids grouped by optimised reference pose
+  const int* opt_to_pose;    // opt id -> pose id
   // per landmark outputs
-  double* lm_Vinv;           // L*L
   double* lm_bl;             // L  (rhs_l_, indexed by landmark id; compacted on read-back)
-  double* lm_dhat;           // L  V^-1 b_l
-  double* lm_Wref;           // 6 (L == 1)
-  const uint32_t* lm_rslot;  // L == 1: slot of the landmark's reference-pose record, kNoSlot if none
-  double* lm_rec;            // L == 1: 36 doubles per slot
+  double* lm_rec;            // kLmRec doubles per landmark (layout above)
+  double* lm_recC;           // L == 1: kLmRecC doubles per landmark
+  double* red_partial;       // per-CTA partial sums of the scalar reductions (summed in index order by the last CTA)
+  unsigned int* red_counter; // arrival counter of the running reduction (self-resetting)
   // reduced system
   double* S_tiles;
   const int* tile_map;       // [nT * nT] in PERMUTED tile coordinates -> slot or -1

@@ -262,7 +262,7 @@ struct bagpu_handle_s {
   uint32_t n_rec = 0, n_lmrec = 0;
   int n_items = 0, n_items_sym = 0;
   size_t n_pairs = 0;
-  uint2* d_pairs = nullptr;            // cudaMalloc'ed by build_pair_lists
+  uint32_t* d_pairs = nullptr;         // from build_pair_lists: [a | b | landmark], n_pairs entries each
   int G = 8;
   int nT = 0, T = 48, n_tiles = 0, max_row = 0;
   std::vector<int> row_ptr, row_col, tile_perm;
@@ -279,9 +279,10 @@ struct bagpu_handle_s {
   DevBuf<double2> d_raw_z; DevBuf<uint32_t> d_raw_pose, d_raw_lm, d_raw_cam; DevBuf<double> d_raw_w0;   // residual-id order, as set
   DevBuf<uint32_t> d_sorted_lm, d_perm_global, d_gstarts;   // landmark-major: landmark id, residual id, CSR starts (all ranks' observations)
   DevBuf<double2> d_obs_z; DevBuf<uint32_t> d_obs_pose, d_obs_cam; DevBuf<double> d_obs_w0, d_obs_maha0, d_obs_w;
-  DevBuf<uint32_t> d_obs_slot, d_lm_rslot; DevBuf<double> d_rec, d_lm_rec, d_partial; DevBuf<unsigned int> d_counters;
+  DevBuf<uint32_t> d_pose_obs, d_pose_obs_lm, d_pose_lms; DevBuf<ObsRec> d_obs_rec; DevBuf<int> d_opt_to_pose;
+  DevBuf<double> d_lm_rec, d_lm_recC, d_partial, d_red_partial; DevBuf<unsigned int> d_counters, d_red_counter;
   DevBuf<ReduceItem> d_items, d_items_sym;
-  DevBuf<double> d_lm_Vinv, d_lm_bl, d_lm_dhat, d_lm_Wref;
+  DevBuf<double> d_lm_bl;
   DevBuf<double> d_S, d_S_copy, d_uinv, d_scratch, d_bp, d_rhs_sc, d_rhs_work;
   DevBuf<int> d_tile_map, d_row_ptr, d_row_col, d_chol_sync, d_tile_perm;
   DevBuf<CholTask> d_chol_tasks; DevBuf<CholTerm> d_chol_terms; int n_chol_tasks = 0;
@@ -387,7 +388,7 @@ struct bagpu_handle_s {
     lm_owner_lo = 0; lm_owner_hi = n_lms;
     G = 4; n_tasks = 0; n_long = 0;
     d_lm_obs_start.alloc((size_t)n_lms + 1); d_lm_obs_start.zero(st);
-    if (n == 0 || n_lms == 0) { n_obs = 0; d_obs_slot.alloc(1); return; }
+    if (n == 0 || n_lms == 0) { n_obs = 0; return; }
     if (!raw_on_device) {   // the setters ran before a device was usable: take the host copies
       d_raw_pose.upload(proj_pose, st); d_raw_lm.upload(proj_lm, st);
       if (raw_has_cam) d_raw_cam.upload(proj_cam, st);
@@ -442,7 +443,7 @@ struct bagpu_handle_s {
     }
     // 4. the local stream: gathered values, pose-major record slots
     const uint32_t nl = (uint32_t)n_obs;
-    d_obs_z.alloc(nl); d_obs_pose.alloc(nl); d_obs_w0.alloc(nl); d_obs_slot.alloc(nl);
+    d_obs_z.alloc(nl); d_obs_pose.alloc(nl); d_obs_w0.alloc(nl); d_obs_rec.alloc(nl);
     if (n_cams > 1) d_obs_cam.alloc(nl);
     launch_gather_obs(d_perm_global.p + s_lo, nl, d_raw_z.p, d_raw_pose.p, raw_has_cam ? d_raw_cam.p : nullptr, raw_has_w0 ? d_raw_w0.p : nullptr,
                       d_obs_z.p, d_obs_pose.p, n_cams > 1 ? d_obs_cam.p : nullptr, d_obs_w0.p, nullptr, st);
@@ -453,20 +454,24 @@ struct bagpu_handle_s {
       d_any.alloc((size_t)n_lms); d_any.zero(st);
       launch_slot_keys(d_obs_pose.p, d_sorted_lm.p + s_lo, nl, d_lm_ref_pose.p, d_pose_opt.p, (uint32_t)n_ap, d_keys.p, d_any.p, st);
       if (sort_positions_by_key(d_keys.p, d_keys_s.p, d_vals_s.p, nl, (uint32_t)n_ap, st, err)) throw err;
-      launch_assign_slots(d_keys_s.p, d_vals_s.p, nl, (uint32_t)n_ap, d_obs_slot.p, st);
+      launch_obs_records(d_obs_z.p, d_obs_w0.p, d_obs_pose.p, d_sorted_lm.p + s_lo, nl, d_obs_rec.p, st);
       launch_key_starts(d_keys_s.p, nl, (uint32_t)n_ap, d_starts.p, st);
       d_starts.download(pose_rec_start.data(), (size_t)n_ap + 1, st);
       sync();
       n_rec = pose_rec_start[n_ap];
+      // the pose-major lists: the first n_rec positions of the pose-sorted order belong to optimised poses
+      d_pose_obs.alloc(n_rec); d_pose_obs_lm.alloc(n_rec);
+      launch_pose_lists(d_vals_s.p, n_rec, d_sorted_lm.p + s_lo, d_pose_obs.p, d_pose_obs_lm.p, st);
       if (L == 1) {   // reference-pose record slots of the landmarks
-        d_lm_rslot.alloc((size_t)n_lms);
         launch_rslot_keys(d_any.p, d_lm_ref_pose.p, d_pose_opt.p, (uint32_t)n_lms, (uint32_t)n_ap, d_keys.p, st);
         if (sort_positions_by_key(d_keys.p, d_keys_s.p, d_vals_s.p, (uint32_t)n_lms, (uint32_t)n_ap, st, err)) throw err;
-        launch_assign_slots(d_keys_s.p, d_vals_s.p, (uint32_t)n_lms, (uint32_t)n_ap, d_lm_rslot.p, st);
         launch_key_starts(d_keys_s.p, (uint32_t)n_lms, (uint32_t)n_ap, d_starts.p, st);
         d_starts.download(pose_lmrec_start.data(), (size_t)n_ap + 1, st);
         sync();
         n_lmrec = pose_lmrec_start[n_ap];
+        d_pose_lms.alloc(n_lmrec);
+        if (n_lmrec) CU(cudaMemcpyAsync(d_pose_lms.p, d_vals_s.p, sizeof(uint32_t) * n_lmrec, cudaMemcpyDeviceToDevice, st));
+        sync();   // d_vals_s goes out of scope
       }
     }
     pc.lap("  symbolic: shard + gather + slots");
@@ -633,14 +638,18 @@ struct bagpu_handle_s {
     const bool multi_cam = n_cams > 1;
     d_obs_maha0.alloc(n_obs); d_obs_w.alloc(n_obs);
     const int Ls = std::max(1, L);
-    const int rec_stride = (L == 1) ? kRec1 : kRec3;
-    d_rec.alloc((size_t)n_rec * rec_stride);
-    if (L == 1) {
-      d_lm_rslot.alloc((size_t)n_lms); d_lm_rec.alloc((size_t)n_lmrec * kLmRec);
-      if (n_obs == 0) CU(cudaMemsetAsync(d_lm_rslot.p, 0xff, sizeof(uint32_t) * (size_t)std::max(1, n_lms), st));
-    }
-    d_lm_Vinv.alloc((size_t)n_lms * Ls * Ls); d_lm_bl.alloc((size_t)n_lms * Ls); d_lm_dhat.alloc((size_t)n_lms * Ls); d_lm_Wref.alloc((size_t)n_lms * 6);
+    d_lm_rec.alloc((size_t)n_lms * kLmRec); d_lm_rec.zero(st);
+    if (L == 1) d_lm_recC.alloc((size_t)n_lms * kLmRecC);
+    d_lm_bl.alloc((size_t)n_lms * Ls);
     d_lm_bl.zero(st);
+    d_red_partial.alloc((size_t)kRedMaxGrid * 8);
+    if (!d_red_counter.p) { d_red_counter.alloc(4); d_red_counter.zero(st); }
+    {
+      std::vector<int> o2p((size_t)std::max(1, n_ap), 0);
+      for (int i = 0; i < n_poses; ++i) if (pose_opt[i] >= 0) o2p[pose_opt[i]] = i;
+      d_opt_to_pose.upload(o2p, st);
+      sync();
+    }
     pc.lap("  upload: allocs");
     // reduced system
     const size_t tsz = (size_t)T * T;
@@ -680,9 +689,14 @@ struct bagpu_handle_s {
     P.obs_z = d_obs_z.p; P.obs_pose = d_obs_pose.p; P.obs_cam = multi_cam ? d_obs_cam.p : nullptr; P.obs_w0 = d_obs_w0.p; P.obs_perm = d_perm_global.p ? d_perm_global.p + s_lo : nullptr;
     P.obs_lm = d_sorted_lm.p ? d_sorted_lm.p + s_lo : nullptr;
     P.obs_maha0 = d_obs_maha0.p; P.obs_w = d_obs_w.p;
-    P.obs_slot = d_obs_slot.p; P.rec = d_rec.p; P.rec_stride = rec_stride;
-    P.lm_rslot = (L == 1) ? d_lm_rslot.p : nullptr; P.lm_rec = (L == 1) ? d_lm_rec.p : nullptr;
-    P.lm_Vinv = d_lm_Vinv.p; P.lm_bl = d_lm_bl.p; P.lm_dhat = d_lm_dhat.p; P.lm_Wref = d_lm_Wref.p;
+    P.obs_rec = d_obs_rec.p; P.pose_obs = d_pose_obs.p; P.pose_obs_lm = d_pose_obs_lm.p; P.pose_lms = d_pose_lms.p; P.opt_to_pose = d_opt_to_pose.p;
+    P.lm_rec = d_lm_rec.p; P.lm_recC = (L == 1) ? d_lm_recC.p : nullptr; P.lm_bl = d_lm_bl.p;
+    P.red_partial = d_red_partial.p; P.red_counter = d_red_counter.p;
+    P.cam_identity = 1;
+    for (int c = 0; c < n_cams; ++c) {
+      const double* t7 = &cam_tvs[7 * c];
+      if (!(t7[0] == 0.0 && t7[1] == 0.0 && t7[2] == 0.0 && t7[3] == 1.0 && t7[4] == 0.0 && t7[5] == 0.0 && t7[6] == 0.0)) P.cam_identity = 0;
+    }
     P.S_tiles = d_S.p; P.tile_map = d_tile_map.p; P.tile_perm = d_tile_perm.p; P.nT = nT; P.T = T; P.b_p = d_bp.p; P.rhs_sc = d_rhs_sc.p; P.sc = d_sc.p;
     P.c_huber_factor = 1.2107;
 
@@ -842,8 +856,8 @@ struct bagpu_handle_s {
     }
     CU(cudaEventRecord(ev[4], st));
     CU(cudaMemcpyAsync(d_rhs_sc.p, d_bp.p, sizeof(double) * (size_t)nT * T, cudaMemcpyDeviceToDevice, st));
-    if (n_items) { launch_reduce_blocks(P, d_items.p, n_items, d_pairs, d_partial.p, d_counters.p + 1, d_counters.p, st); ++launches; }
-    if (n_items_sym) { launch_reduce_blocks(P, d_items_sym.p, n_items_sym, d_pairs, d_partial.p, d_counters.p + 1, d_counters.p, st); ++launches; }
+    if (n_items) { launch_reduce_blocks(P, d_items.p, n_items, d_pairs, d_pairs + n_pairs, d_pairs + 2 * n_pairs, d_partial.p, d_counters.p + 1, d_counters.p, st); ++launches; }
+    if (n_items_sym) { launch_reduce_blocks(P, d_items_sym.p, n_items_sym, d_pairs, d_pairs + n_pairs, d_pairs + 2 * n_pairs, d_partial.p, d_counters.p + 1, d_counters.p, st); ++launches; }
     CU(cudaEventRecord(ev[5], st));
     if (world > 1) {
       // one NCCL group: the four reductions share a single launch
@@ -883,7 +897,7 @@ struct bagpu_handle_s {
   double dot(const double* a, const double* b, size_t n, int slot) {
     (void)slot;
     CU(cudaMemsetAsync(&d_sc.p->dot[0], 0, sizeof(double), st));
-    launch_dot(a, b, n, &d_sc.p->dot[0], st); if (n) ++launches;
+    launch_dot(P, a, b, n, &d_sc.p->dot[0], st); if (n) ++launches;
     double v;
     CU(cudaMemcpyAsync(&v, &d_sc.p->dot[0], sizeof(double), cudaMemcpyDeviceToHost, st));
     sync();
@@ -893,8 +907,8 @@ struct bagpu_handle_s {
   void dot_pair(const double* a1, const double* b1, size_t n1, const double* a2, const double* b2, size_t n2, double* r1, double* r2,
                 bool wait = true) {
     CU(cudaMemsetAsync(&d_sc.p->dot[0], 0, 2 * sizeof(double), st));
-    if (n1) { launch_dot(a1, b1, n1, &d_sc.p->dot[0], st); ++launches; }
-    if (n2) { launch_dot(a2, b2, n2, &d_sc.p->dot[1], st); ++launches; }
+    if (n1) { launch_dot(P, a1, b1, n1, &d_sc.p->dot[0], st); ++launches; }
+    if (n2) { launch_dot(P, a2, b2, n2, &d_sc.p->dot[1], st); ++launches; }
     if (world > 1) allreduce_f64(&d_sc.p->dot[1], 1);
     if (!wait) return;
     double v[2];
@@ -1650,14 +1664,19 @@ int bagpu_get_system(bagpu_handle h, double* s_dense, double* rhs_sc, double* rh
     if (rhs_p) h->d_bp.download(rhs_p, n, h->st);
     const int Ls = std::max(1, h->L);
     if ((rhs_l || v_inv) && h->L > 0 && h->n_lms) {
-      std::vector<double> bl((size_t)h->n_lms * Ls), vi((size_t)h->n_lms * Ls * Ls);
-      h->d_lm_bl.download(bl.data(), bl.size(), h->st); h->d_lm_Vinv.download(vi.data(), vi.size(), h->st);
+      std::vector<double> bl((size_t)h->n_lms * Ls), rec((size_t)h->n_lms * kLmRec);
+      h->d_lm_bl.download(bl.data(), bl.size(), h->st); h->d_lm_rec.download(rec.data(), rec.size(), h->st);
       h->sync();
       for (int l = 0; l < h->n_lms; ++l) {
         const int o = h->lm_opt[l];
         if (o < 0) continue;
         if (rhs_l) for (int k = 0; k < Ls; ++k) rhs_l[(size_t)o * Ls + k] = bl[(size_t)l * Ls + k];
-        if (v_inv) for (int k = 0; k < Ls * Ls; ++k) v_inv[(size_t)o * Ls * Ls + k] = vi[(size_t)l * Ls * Ls + k];
+        if (v_inv) {   // the landmark record holds V^-1 (LmSize 3: its upper triangle)
+          const double* r = &rec[(size_t)l * kLmRec];
+          double* v = v_inv + (size_t)o * Ls * Ls;
+          if (Ls == 1) v[0] = r[7];
+          else { v[0] = r[4]; v[1] = r[5]; v[2] = r[6]; v[3] = r[5]; v[4] = r[7]; v[5] = r[8]; v[6] = r[6]; v[7] = r[8]; v[8] = r[9]; }
+        }
       }
     }
     h->sync();

@@ -157,4 +157,51 @@ BA_D unsigned group_mask(int lane) { return G == 32 ? 0xffffffffu : (((1u << G) 
 
 BA_D void red_add(double* p, double v) { atomicAdd(p, v); }  // REDG.E.ADD.F64 (no return value used)
 
+// Bit-reproducible grid-wide sums of NV per-thread values (the reference is a serial, deterministic program: every scalar
+// the step control consumes must not depend on the arrival order of atomics).  Warp shuffles, then the warps of the CTA
+// in index order, then the CTAs in index order by the last CTA to arrive.  `partial` holds gridDim.x * NV doubles,
+// `counter` is zero before the launch and is left zero.  `out[k]` is overwritten, or added to when `accumulate`.
+// The result depends only on the launch geometry, which every launcher derives from the problem size.
+constexpr int kRedMaxGrid = 148 * 16;
+template <int NV>
+BA_D void grid_sum_fixed(const double (&v)[NV], double* __restrict__ partial, unsigned int* __restrict__ counter, double* __restrict__ out,
+                         bool accumulate) {
+  __shared__ double sh_w[32 * NV];
+  __shared__ bool sh_last;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = (blockDim.x + 31) >> 5;
+#pragma unroll
+  for (int k = 0; k < NV; ++k) {
+    const double s = warp_sum(v[k]);
+    if (lane == 0) sh_w[warp * NV + k] = s;
+  }
+  __syncthreads();
+  if (threadIdx.x < NV) {
+    double s = 0.0;
+    for (int w = 0; w < nw; ++w) s += sh_w[w * NV + threadIdx.x];
+    partial[(size_t)blockIdx.x * NV + threadIdx.x] = s;
+    __threadfence();
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) sh_last = (atomicAdd(counter, 1u) + 1u == gridDim.x);
+  __syncthreads();
+  if (!sh_last) return;
+  __threadfence();
+  // the last CTA: thread t takes CTAs t, t + blockDim.x, ... in order, then the threads are combined in index order
+#pragma unroll
+  for (int k = 0; k < NV; ++k) {
+    double s = 0.0;
+    for (unsigned b = threadIdx.x; b < gridDim.x; b += blockDim.x) s += __ldcg(&partial[(size_t)b * NV + k]);
+    s = warp_sum(s);
+    __syncthreads();
+    if (lane == 0) sh_w[warp] = s;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      double t = 0.0;
+      for (int w = 0; w < nw; ++w) t += sh_w[w];
+      out[k] = accumulate ? out[k] + t : t;
+    }
+  }
+  if (threadIdx.x == 0) *counter = 0;
+}
+
 }  // namespace bagpu

@@ -35,13 +35,13 @@ struct OtherResiduals {
 };
 
 // ---- pose-pair-major reduction (schur_kernels.cu / symbolic.cu) -------------------------------
-// pair list entry: (a, b) record slots, a belongs to the block's row pose.  LmSize 1 also lists
-// one entry per observation for the (measurement pose, reference pose) block, tagged in b.
+// pair list entry: (a, b) observation indices (positions in the landmark-major stream), a belongs to the block's row
+// pose.  LmSize 1 also lists one entry per observation for the (measurement pose, reference pose) block, tagged in b.
 constexpr uint32_t kPairTagMeasRow = 0xffffffffu;   // row pose = measurement pose: += At^T Q
 constexpr uint32_t kPairTagRefRow = 0xfffffffeu;    // row pose = reference pose:   += Q^T At
 enum { kItemDiagObs = 0, kItemDiagLm = 1, kItemOff = 2, kItemSym = 3, kItemOffRef = 4 };
 struct ReduceItem {        // one warp's share of one S block
-  uint32_t begin, end;     // record-slot range (diagonal kinds) or pair range
+  uint32_t begin, end;     // range of the pose's observation / landmark list (diagonal kinds) or pair range
   uint32_t row, col;       // pose opt ids, row <= col
   uint32_t kind;
   uint32_t mfirst, mcount; // chunks of the same block: partial-sum slots mfirst .. mfirst + mcount
@@ -49,10 +49,11 @@ struct ReduceItem {        // one warp's share of one S block
   uint32_t pad;
 };
 
-// Builds the pair list on the device (symbolic.cu): *pairs_out is cudaMalloc'ed (caller frees), sorted by
+// Builds the pair list on the device (symbolic.cu): *pairs_out is allocated with dev_alloc (caller frees) and holds three
+// arrays of n_pairs entries [observation of the row pose | observation of the column pose or tag | landmark], sorted by
 // key = (row * n_active_poses + col) * 2 + (1 for the LmSize-1 measurement/reference entries), stable in landmark
 // order; block_key / block_count = the run table of that key.
-int build_pair_lists(const DeviceProblem& P, cudaStream_t st, uint2** pairs_out, size_t* n_pairs_out,
+int build_pair_lists(const DeviceProblem& P, cudaStream_t st, uint32_t** pairs_out, size_t* n_pairs_out,
                      std::vector<unsigned long long>& block_key, std::vector<uint32_t>& block_count, std::string& err);
 
 // ---- device-side symbolic set-up (setup_device.cu) ------------------------------------------------
@@ -68,7 +69,8 @@ void launch_gather_obs(const uint32_t* perm, uint32_t n, const double2* z, const
 void launch_local_starts(const uint32_t* gstarts, uint32_t n_lms, uint32_t s_lo, uint32_t s_hi, uint32_t* out, cudaStream_t st);
 void launch_slot_keys(const uint32_t* obs_pose, const uint32_t* obs_lm, uint32_t n, const uint32_t* lm_ref_pose, const int* pose_opt,
                       uint32_t n_ap, uint32_t* keys, uint8_t* lm_any, cudaStream_t st);
-void launch_assign_slots(const uint32_t* keys_sorted, const uint32_t* vals_sorted, uint32_t n, uint32_t n_ap, uint32_t* slot, cudaStream_t st);
+void launch_pose_lists(const uint32_t* vals_sorted, uint32_t n, const uint32_t* obs_lm, uint32_t* pose_obs, uint32_t* pose_obs_lm, cudaStream_t st);
+void launch_obs_records(const double2* z, const double* w0, const uint32_t* pose, const uint32_t* lm, uint32_t n, ObsRec* out, cudaStream_t st);
 void launch_rslot_keys(const uint8_t* lm_any, const uint32_t* lm_ref_pose, const int* pose_opt, uint32_t n_lms, uint32_t n_ap, uint32_t* keys,
                        cudaStream_t st);
 // dense nT x nT tile table (-1 = structurally empty) from the CSR rows: tiles numbered row by row, diagonal tile first
@@ -86,8 +88,8 @@ void launch_finish_xw(const DeviceProblem& P, double* lm_xw, cudaStream_t st);
 void launch_residual(const DeviceProblem& P, int G, cudaStream_t st);
 // packed tasks: (first observation, number of observations <= 32) of runs of whole landmarks; long_lms: landmarks with > 32 observations
 void launch_linearize(const DeviceProblem& P, const uint2* tasks, int n_tasks, const uint32_t* long_lms, int n_long, cudaStream_t st);
-void launch_reduce_blocks(const DeviceProblem& P, const ReduceItem* items, int n_items, const uint2* pairs, double* partial,
-                          unsigned int* counters, unsigned int* next_item, cudaStream_t st);
+void launch_reduce_blocks(const DeviceProblem& P, const ReduceItem* items, int n_items, const uint32_t* pair_a, const uint32_t* pair_b,
+                          const uint32_t* pair_lm, double* partial, unsigned int* counters, unsigned int* next_item, cudaStream_t st);
 void launch_sd_denominator(const DeviceProblem& P, int G, cudaStream_t st);
 void launch_back_substitute(const DeviceProblem& P, const uint2* tasks, int n_tasks, const uint32_t* long_lms, int n_long, const double* delta_p,
                             double* delta_l, cudaStream_t st);
@@ -95,7 +97,7 @@ void launch_evaluate(const DeviceProblem& P, int G, double* out_sum, double* res
 void launch_update_poses(const DeviceProblem& P, const double* delta_p, double coef, cudaStream_t st);
 void launch_update_landmarks(const DeviceProblem& P, const double* delta_l, double coef, cudaStream_t st);
 void launch_mask_diagonal(const DeviceProblem& P, const uint8_t* mask_used, int global_flag, cudaStream_t st);
-void launch_dot(const double* a, const double* b, size_t n, double* out, cudaStream_t st);
+void launch_dot(const DeviceProblem& P, const double* a, const double* b, size_t n, double* out, cudaStream_t st);   // overwrites *out
 void launch_axpby(double* out, double alpha, const double* x, double beta, const double* y, size_t n, cudaStream_t st);
 void launch_compact_bl(const DeviceProblem& P, double* out, cudaStream_t st);
 void launch_permute_tiles(double* dst, const double* src, const int* perm, int T, int nT, int forward, cudaStream_t st);

@@ -85,7 +85,7 @@ __global__ void __launch_bounds__(256) k_residual(DeviceProblem P) {
 // steepest-descent denominator |J_p b_p + J_l b_l|^2 over projection residuals (cpp:879-906)
 template <int L>
 __global__ void __launch_bounds__(128) k_sd_denominator(DeviceProblem P) {
-  double acc = 0.0;
+  double acc[1] = {0.0};
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < P.n_obs; i += gridDim.x * blockDim.x) {
     const int lm = (int)P.obs_lm[i];
     LmCtx<L> c;
@@ -109,56 +109,57 @@ __global__ void __launch_bounds__(128) k_sd_denominator(DeviceProblem P) {
 #pragma unroll
       for (int k = 0; k < 6; ++k) { v0 += Jr[k] * bp[k]; v1 += Jr[6 + k] * bp[k]; }
     }
-    acc += P.obs_w[i] * (v0 * v0 + v1 * v1);
+    acc[0] += P.obs_w[i] * (v0 * v0 + v1 * v1);
   }
-  acc = warp_sum(acc);
-  if ((threadIdx.x & 31) == 0) red_add(&P.sc->sd_den_proj, acc);
+  grid_sum_fixed<1>(acc, P.red_partial, P.red_counter, &P.sc->sd_den_proj, false);
 }
 
 // ---------------------------------------------------------------------------------------
-// back-substitution: delta_l = V^-1 (b_l - W^T delta_p)   (cpp:709-744), from the pose-major
-// records: V^-1 W_a^T delta = C_a^T (At_a delta) for LmSize 3, E_a . delta for LmSize 1
-// share of one observation: V^-1 W_a^T delta_p(a)
+// back-substitution: delta_l = V^-1 (b_l - W^T delta_p) = dhat - V^-1 sum_a W_a^T delta_p(a)   (cpp:709-744).
+// W_a^T delta = w J_l^T (J_m delta) is re-evaluated from the observation (nothing per observation is stored);
+// V^-1 and dhat come from the landmark's record.
+// share of one observation: w J_l^T J_m delta_p(a)
 template <int L>
-BA_D void back_term(const DeviceProblem& P, int i, const double* delta_p, double* acc) {
-  const uint32_t slot = P.obs_slot[i];
-  if (slot == kNoSlot) return;
-  const double* r = P.rec + (size_t)slot * P.rec_stride;
-  const double* dp = delta_p + (size_t)P.pose_opt[P.obs_pose[i]] * P.D;
-  // the record is read in 16-byte pieces (half as many memory requests as scalar loads)
-  if (L == 3) {
-    double v[18];
+BA_D void back_term(const DeviceProblem& P, const LmCtx<L>& c, int i, int m_known, const double* delta_p, double* acc) {
+  ObsJac<L> o;
+  obs_jacobians<L>(P, c, i, o, m_known);
+  if (o.pm < 0) return;
+  const double* dp = delta_p + (size_t)o.pm * P.D;
+  double t0 = 0.0, t1 = 0.0;
 #pragma unroll
-    for (int a = 0; a < 9; ++a) { const double2 x = reinterpret_cast<const double2*>(r)[a]; v[2 * a] = x.x; v[2 * a + 1] = x.y; }
-    double t0 = 0.0, t1 = 0.0;
+  for (int a = 0; a < 6; ++a) { t0 += o.Jm[a] * dp[a]; t1 += o.Jm[6 + a] * dp[a]; }
+  const double w = P.obs_w[i];
 #pragma unroll
-    for (int a = 0; a < 6; ++a) { t0 += v[6 + a] * dp[a]; t1 += v[12 + a] * dp[a]; }
-#pragma unroll
-    for (int k = 0; k < L; ++k) acc[k] += v[k] * t0 + v[3 + k] * t1;
-  } else {
-    double v[6];
-#pragma unroll
-    for (int a = 0; a < 3; ++a) { const double2 x = reinterpret_cast<const double2*>(r)[a]; v[2 * a] = x.x; v[2 * a + 1] = x.y; }
-#pragma unroll
-    for (int a = 0; a < 6; ++a) acc[0] += v[a] * dp[a];
-  }
+  for (int k = 0; k < L; ++k) acc[k] += w * (o.Jl[k] * t0 + o.Jl[L + k] * t1);
 }
 // landmark part and write-out, by one lane holding the landmark's sum
 template <int L>
 BA_D void back_finish(const DeviceProblem& P, int lm, int lo, const double* delta_p, double* acc, double* delta_l) {
+  const double* r = P.lm_rec + (size_t)lm * kLmRec;
   if (L == 1) {
-    const int ro = P.pose_opt[P.lm_ref_pose[lm]];
-    if (ro >= 0) {
-      const double* W = P.lm_Wref + (size_t)lm * 6;
+    const int rp = (int)P.lm_ref_pose[lm];
+    const int ro = P.pose_opt[rp];
+    if (ro >= 0) {   // W_ref^T delta = SBl^T (M delta)
+      double M[18];
+      ref_M(P, rp, P.n_cams > 1 ? (int)P.lm_ref_cam[lm] : 0, r[3], r + 9, M);
       const double* dp = delta_p + (size_t)ro * P.D;
       double t = 0.0;
 #pragma unroll
-      for (int a = 0; a < 6; ++a) t += W[a] * dp[a];
-      acc[0] += P.lm_Vinv[lm] * t;
-    }
-  }
+      for (int j = 0; j < 3; ++j) {
+        double mj = 0.0;
 #pragma unroll
-  for (int k = 0; k < L; ++k) delta_l[(size_t)lo * L + k] = P.lm_dhat[(size_t)lm * L + k] - acc[k];
+        for (int a = 0; a < 6; ++a) mj += M[6 * j + a] * dp[a];
+        t += r[12 + j] * mj;
+      }
+      acc[0] += t;
+    }
+    delta_l[lo] = r[8] - r[7] * acc[0];
+  } else {
+    const double v00 = r[4], v01 = r[5], v02 = r[6], v11 = r[7], v12 = r[8], v22 = r[9];
+    delta_l[(size_t)lo * L + 0] = r[10] - (v00 * acc[0] + v01 * acc[1] + v02 * acc[2]);
+    delta_l[(size_t)lo * L + 1] = r[11] - (v01 * acc[0] + v11 * acc[1] + v12 * acc[2]);
+    delta_l[(size_t)lo * L + 2] = r[12] - (v02 * acc[0] + v12 * acc[1] + v22 * acc[2]);
+  }
 }
 
 // packed tasks (see k_linearize_packed): one observation per lane, segmented sum over the lanes of a landmark
@@ -182,7 +183,11 @@ __global__ void __launch_bounds__(256) k_back_substitute_packed(DeviceProblem P,
     double acc[L];
 #pragma unroll
     for (int k = 0; k < L; ++k) acc[k] = 0.0;
-    if (on && lo >= 0) back_term<L>(P, i, delta_p, acc);
+    if (on && lo >= 0) {
+      LmCtx<L> c;
+      load_lm<L>(P, lm, c);
+      back_term<L>(P, c, i, -1, delta_p, acc);
+    }
 #pragma unroll
     for (int d = 1; d < 32; d <<= 1) {
       const bool take = on && (lane + d < seg_end);
@@ -210,7 +215,9 @@ __global__ void __launch_bounds__(256) k_back_substitute_long(DeviceProblem P, c
     double acc[L];
 #pragma unroll
     for (int k = 0; k < L; ++k) acc[k] = 0.0;
-    for (int i = s + lane; i < e; i += 32) back_term<L>(P, i, delta_p, acc);
+    LmCtx<L> c;
+    load_lm<L>(P, lm, c);
+    for (int i = s + lane; i < e; i += 32) back_term<L>(P, c, i, -1, delta_p, acc);
 #pragma unroll
     for (int k = 0; k < L; ++k) acc[k] = warp_sum(acc[k]);
     if (lane == 0) back_finish<L>(P, lm, lo, delta_p, acc, delta_l);
@@ -221,7 +228,7 @@ __global__ void __launch_bounds__(256) k_back_substitute_long(DeviceProblem P, c
 // residual-only evaluation with the current Huber weights (cpp:148-188)
 template <int L>
 __global__ void __launch_bounds__(256) k_evaluate(DeviceProblem P, double* out_sum, double* res_out, double* maha_out, int write_maha0) {
-  double acc = 0.0;
+  double acc[1] = {0.0};
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < P.n_obs; i += gridDim.x * blockDim.x) {
     const int lm = (int)P.obs_lm[i];
     LmCtx<L> c;
@@ -230,7 +237,7 @@ __global__ void __launch_bounds__(256) k_evaluate(DeviceProblem P, double* out_s
     obs_residual<L>(P, c, i, r);
     const double n2 = r[0] * r[0] + r[1] * r[1];
     const double m = n2 * P.obs_w[i];
-    acc += m;
+    acc[0] += m;
     // the next BuildProblem starts from this state if the step is accepted: its median input, for free
     if (write_maha0) P.obs_maha0[i] = n2 * P.obs_w0[i];
     if (sqrt(n2) > P.outlier_threshold) atomicAdd(&P.lm_outliers[lm], 1u);   // cpp:184-186
@@ -240,8 +247,7 @@ __global__ void __launch_bounds__(256) k_evaluate(DeviceProblem P, double* out_s
       maha_out[id] = m;
     }
   }
-  acc = warp_sum(acc);
-  if ((threadIdx.x & 31) == 0) red_add(out_sum, acc);
+  grid_sum_fixed<1>(acc, P.red_partial, P.red_counter, out_sum, true);
 }
 
 // ---------------------------------------------------------------------------------------
@@ -306,11 +312,10 @@ __global__ void k_mask_diagonal_poses(DeviceProblem P, const uint8_t* mask_used)
 
 // ---------------------------------------------------------------------------------------
 // small vector kernels for the dogleg step control
-__global__ void k_dot(const double* a, const double* b, size_t n, double* out) {
-  double acc = 0.0;
-  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) acc += a[i] * b[i];
-  acc = warp_sum(acc);
-  if ((threadIdx.x & 31) == 0) red_add(out, acc);
+__global__ void k_dot(const double* a, const double* b, size_t n, double* out, double* partial, unsigned int* counter) {
+  double acc[1] = {0.0};
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) acc[0] += a[i] * b[i];
+  grid_sum_fixed<1>(acc, partial, counter, out, false);
 }
 // out = alpha * x + beta * y  (y may be null)
 __global__ void k_axpby(double* out, double alpha, const double* x, double beta, const double* y, size_t n) {
@@ -420,9 +425,9 @@ void launch_mask_diagonal(const DeviceProblem& P, const uint8_t* mask_used, int 
   k_mask_diagonal<<<(n_pad + 255) / 256, 256, 0, st>>>(P, mask_used, global_flag);
   if (global_flag) k_mask_diagonal_poses<<<(P.n_poses + 127) / 128, 128, 0, st>>>(P, mask_used);
 }
-void launch_dot(const double* a, const double* b, size_t n, double* out, cudaStream_t st) {
+void launch_dot(const DeviceProblem& P, const double* a, const double* b, size_t n, double* out, cudaStream_t st) {
   if (n == 0) return;
-  k_dot<<<grid_for(n, 256, 4), 256, 0, st>>>(a, b, n, out);
+  k_dot<<<grid_for(n, 256, 4), 256, 0, st>>>(a, b, n, out, P.red_partial, P.red_counter);
 }
 void launch_axpby(double* out, double alpha, const double* x, double beta, const double* y, size_t n, cudaStream_t st) {
   if (n == 0) return;

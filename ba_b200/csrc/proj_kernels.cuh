@@ -11,12 +11,13 @@
 //   * back-substitution                            reference src/BundleAdjuster.cpp:709-744
 //   * residual-only evaluation                     reference src/BundleAdjuster.cpp:148-188
 // The Jacobians are the algebraically collapsed closed forms of the reference's
-// 2x4 * 4x7 * 7x7 * 7x6 chain (derivation in DESIGN.md §3); J is never stored.
+// 2x4 * 4x7 * 7x7 * 7x6 chain; J is never stored, every kernel that needs a Jacobian
+// re-evaluates it from the 40-byte observation, the landmark and the pose frame.
 //
-// Work decomposition: observations are sorted by landmark; a group of G lanes (G = 4..32,
-// chosen from the mean track length) owns one landmark, lanes stride over its observations,
-// V / b_l (and the reference-pose blocks for LmSize 1) are reduced with warp shuffles, and the
-// pose-block contributions go to S / b_p with FP64 reductions (RED.E.ADD.F64) into L2.
+// Work decomposition: observations are sorted by landmark.  The landmark-major kernels take one
+// observation per lane (warp tasks = runs of whole landmarks with at most 32 observations, packed at
+// set-up); per-landmark sums are segmented warp reductions.  The pose-pair-major kernel
+// (schur_kernels.cu) owns each S block exclusively: no atomics anywhere in the build.
 #pragma once
 #include "ba_gpu.h"
 #include "device_math.cuh"
@@ -186,9 +187,105 @@ BA_D void ref_jacobian(const LmCtx<L>& c, const double* Bp, double* Jr) {
   }
 }
 
-BA_D double huber_weight(double maha0, double w0, double c_huber, int use_robust) {
-  const double e = sqrt(maha0);
-  return ((use_robust & 1) && e > c_huber) ? w0 * (c_huber / e) : w0;
+// cpp:1372-1382: e = sqrt(maha0); e > c_huber -> weight *= c_huber / e.  The square root is taken only for residuals
+// beyond c_huber^2 (c2): inliers cost one comparison.
+BA_D double huber_weight(double maha0, double w0, double c_huber, double c2, int use_robust) {
+  if ((use_robust & 1) && maha0 > c2) {
+    const double e = sqrt(maha0);
+    if (e > c_huber) return w0 * (c_huber / e);
+  }
+  return w0;
+}
+
+// One side of a pose pair, re-evaluated from the staged landmark record `lm` (X | rho | LmSize 1: t_ws of the
+// reference frame), the observation (z, orig weight) and the frame of pose m, which is the same for every lane of
+// the warp (uniform, L1-resident loads).  Same closed forms as obs_jacobians.
+template <int L>
+struct Side {
+  double Jm[12];            // d z / d x_meas, 2 x 6, masked parameter columns zeroed
+  double B[6];              // d project / d X_world = Jp R_sw, 2 x 3  (LmSize 3: J_l = -B)
+  double jl[2];             // LmSize 1: d z / d rho
+  double r[2];
+  double w;                 // Huber weight
+};
+template <int L>
+BA_D void side_eval(const DeviceProblem& P, const double* __restrict__ lm, double zx, double zy, double w0, int m, int cam, double c_huber,
+                    double c2, Side<L>& s) {
+  double T[12];
+  load_frame(P.Tsw + ((size_t)m * P.n_cams + cam) * 12, T);
+  const double X0 = lm[0], X1 = lm[1], X2 = lm[2], rho = lm[3];
+  const double Xs0 = T[0] * X0 + T[1] * X1 + T[2] * X2 + rho * T[9];
+  const double Xs1 = T[3] * X0 + T[4] * X1 + T[5] * X2 + rho * T[10];
+  const double Xs2 = T[6] * X0 + T[7] * X1 + T[8] * X2 + rho * T[11];
+  const double2 k01 = reinterpret_cast<const double2*>(P.cam_params + 4 * cam)[0], k23 = reinterpret_cast<const double2*>(P.cam_params + 4 * cam)[1];
+  const double iz = 1.0 / Xs2;
+  s.r[0] = zx - (k01.x * Xs0 * iz + k23.x);
+  s.r[1] = zy - (k01.y * Xs1 * iz + k23.y);
+  const double a = k01.x * iz, b = k01.y * iz;
+  const double j02 = -a * Xs0 * iz, j12 = -b * Xs1 * iz;
+#pragma unroll
+  for (int cc = 0; cc < 3; ++cc) {
+    s.B[cc] = a * T[cc] + j02 * T[6 + cc];
+    s.B[3 + cc] = b * T[3 + cc] + j12 * T[6 + cc];
+  }
+  if (L == 1) {
+    s.jl[0] = -(s.B[0] * lm[4] + s.B[1] * lm[5] + s.B[2] * lm[6] + a * T[9] + j02 * T[11]);
+    s.jl[1] = -(s.B[3] * lm[4] + s.B[4] * lm[5] + s.B[5] * lm[6] + b * T[10] + j12 * T[11]);
+  }
+  double Xv0 = Xs0, Xv1 = Xs1, Xv2 = Xs2;
+  double C[6] = {a, 0.0, j02, 0.0, b, j12};      // Jp R_vs^T
+  if (!P.cam_identity) {
+    const double* Rvs = P.cam_Rvs + 9 * cam;
+    const double* tvs = P.cam_tvs + 3 * cam;
+    Xv0 = Rvs[0] * Xs0 + Rvs[1] * Xs1 + Rvs[2] * Xs2 + rho * tvs[0];
+    Xv1 = Rvs[3] * Xs0 + Rvs[4] * Xs1 + Rvs[5] * Xs2 + rho * tvs[1];
+    Xv2 = Rvs[6] * Xs0 + Rvs[7] * Xs1 + Rvs[8] * Xs2 + rho * tvs[2];
+#pragma unroll
+    for (int cc = 0; cc < 3; ++cc) {
+      C[cc] = a * Rvs[3 * cc] + j02 * Rvs[3 * cc + 2];
+      C[3 + cc] = b * Rvs[3 * cc + 1] + j12 * Rvs[3 * cc + 2];
+    }
+  }
+#pragma unroll
+  for (int rr = 0; rr < 2; ++rr) {
+    const double* Cr = C + 3 * rr;
+    s.Jm[6 * rr + 0] = rho * s.B[3 * rr + 0];
+    s.Jm[6 * rr + 1] = rho * s.B[3 * rr + 1];
+    s.Jm[6 * rr + 2] = rho * s.B[3 * rr + 2];
+    s.Jm[6 * rr + 3] = -(Cr[1] * Xv2 - Cr[2] * Xv1);
+    s.Jm[6 * rr + 4] = -(-Cr[0] * Xv2 + Cr[2] * Xv0);
+    s.Jm[6 * rr + 5] = -(Cr[0] * Xv1 - Cr[1] * Xv0);
+  }
+  const uint32_t fr = P.pose_free[m];
+  if ((fr & 63u) != 63u) {
+#pragma unroll
+    for (int k = 0; k < 6; ++k)
+      if (!((fr >> k) & 1u)) { s.Jm[k] = 0.0; s.Jm[6 + k] = 0.0; }
+  }
+  const double n2 = s.r[0] * s.r[0] + s.r[1] * s.r[1];
+  s.w = huber_weight(n2 * w0, w0, c_huber, c2, P.use_robust);
+}
+
+// M = [-rho I | R_wp_r [Y]x] (3 x 6, masked parameter columns zeroed), Y = R_vs ray + rho t_vs: the reference-pose
+// Jacobian of an observation of the landmark is Bp M (proj_kernels.cuh, ref_jacobian)
+BA_D void ref_M(const DeviceProblem& P, int ref_pose, int ref_cam, double rho, const double* ray, double* M) {
+  double Y[3] = {ray[0], ray[1], ray[2]};
+  if (!P.cam_identity) {
+    mat3_vec(P.cam_Rvs + 9 * ref_cam, ray, Y);
+    Y[0] += rho * P.cam_tvs[3 * ref_cam]; Y[1] += rho * P.cam_tvs[3 * ref_cam + 1]; Y[2] += rho * P.cam_tvs[3 * ref_cam + 2];
+  }
+  double Ar[9];
+  mat3_skew(P.Rwp + 9 * (size_t)ref_pose, Y, Ar);
+#pragma unroll
+  for (int j = 0; j < 3; ++j)
+#pragma unroll
+    for (int k = 0; k < 3; ++k) { M[6 * j + k] = (j == k) ? -rho : 0.0; M[6 * j + 3 + k] = Ar[3 * j + k]; }
+  const uint32_t fr = P.pose_free[ref_pose];
+  if ((fr & 63u) != 63u) {
+#pragma unroll
+    for (int k = 0; k < 6; ++k)
+      if (!((fr >> k) & 1u)) { M[k] = 0.0; M[6 + k] = 0.0; M[12 + k] = 0.0; }
+  }
 }
 
 // Pose block (i, j), i <= j (opt ids), inside the tiled S: element (r, c) lives at p[r * rs + c * cs].

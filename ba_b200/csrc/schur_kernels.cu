@@ -1,4 +1,4 @@
-// schur_kernels.cu — atomic-free assembly of the reduced camera system.
+// schur_kernels.cu — atomic-free, record-free assembly of the reduced camera system.
 //
 // Replaces, per outer iteration (reference src/BundleAdjuster.cpp):
 //   U += Jpr^T Jpr, rhs_p += Jpr^T r                                    cpp:337-354
@@ -6,22 +6,23 @@
 //   W = Jpr^T Jl, W V^-1, S = U - W V^-1 W^T, rhs_sc = rhs_p - W V^-1 b_l   cpp:448-485
 // (the four sparse block products of include/ba/SparseBlockMatrixOps.h:159-380).
 //
-// The reference scatters: per landmark it adds k(k+1)/2 outer products into S.  On the GPU
-// that is ~36 FP64 reductions per product into L2 and is bound by the L2 atomic units
-// (profiles/r1a_*: 7 ms for 5M observations).  Here the product is turned around:
+// The reference scatters: per landmark it adds k(k+1)/2 outer products into S.  On the GPU that is ~36 FP64
+// reductions per product into L2, bound by the L2 atomic units (profiles/r1a_*: 7 ms for 5M observations).  Round 1
+// turned the product around with a 224/320-byte record per observation (write once, gather once per pose pair): no
+// atomics, but 1.8x - 3.7x the algorithmic DRAM bytes and an L2-bound gather (profiles/r1f, r1i).  Here nothing per
+// observation is stored at all:
 //
-//   pass A  k_linearize   (landmark-major, one group of G lanes per landmark)
-//       Jacobians, Huber weight, V, b_l, V^-1 by warp shuffles, then ONE record per
-//       observation written to its POSE-MAJOR slot:  sqrt(w) J_pose, sqrt(w) J_lm V^-1, ...
-//       with the landmark already projected out (rho = r~ - B~ V^-1 b_l), see ba_gpu.h.
-//   pass B  k_reduce_blocks (pose-pair-major, one warp per S block chunk)
-//       S_ii   = sum over the pose's records        A~^T (I - C B~^T) A~      (streaming)
-//       S_ij   = sum over the block's pair list    -A~_a^T C_a B~_b^T A~_b    (gather, L2 resident)
-//       b_p, rhs_sc from the same records.  Each block is owned by one warp (or a fixed chain
-//       of chunks combined in index order), so there are NO atomics and the result is
-//       bit-reproducible run to run.
-// The pair lists depend only on the ids; they are built once per Solve() on the device
-// (symbolic.cu).
+//   pass A  k_linearize   (landmark-major, one observation per lane)
+//       Jacobians, Huber weight, V, b_l, V^-1 by segmented warp shuffles; writes the weight (8 B per observation)
+//       and ONE 128-byte record per landmark: the point, V^-1 and dhat = V^-1 b_l (LmSize 1: also the three sums
+//       from which the reference pose's blocks follow).
+//   pass B  k_reduce_blocks (pose-pair-major, one warp per S block chunk, one list entry per lane)
+//       S_ij -= w_a w_b Jm_a^T (Jl_a V^-1 Jl_b^T) Jm_b over the block's pair list; both Jacobians of a pair are
+//       re-evaluated from two 32-byte observations and the landmark record (5 sectors through L2 instead of 9-10)
+//       against the two pose frames of the block, which are uniform over the warp.  Diagonal blocks, b_p and rhs_sc
+//       come from the pose's own observation list the same way.  Each block is owned by one warp (or a fixed
+//       chain of chunks combined in index order): NO atomics, bit-reproducible run to run.
+// The pair lists depend only on the ids; they are built once per Solve() on the device (symbolic.cu).
 #include <algorithm>
 #include <cstdlib>
 #include "proj_kernels.cuh"
@@ -69,16 +70,11 @@ BA_D void sums_add(LmSums<L>& S, const ObsJac<L>& o, double w, bool lm_on) {
   }
 }
 
-// From the complete sums of a landmark: V^-1 (cpp:431-442), dhat = V^-1 b_l, LmSize 1 W_r and the reference-pose
-// record.  Every lane that holds the sums computes Vi / dhat / Wr (it needs them for its own record); the landmark's
-// outputs are written by the lanes with `writer` set, element k of the reference-pose record by the lane with
-// k % MOD == rem.
-template <int L, int MOD>
-BA_D void lm_finalize(const DeviceProblem& P, int lm, const LmCtx<L>& c, bool lm_on, const LmSums<L>& S, double* Vi, double* dhat, double* Wr,
-                      bool writer, int rem) {
+// V^-1 of a landmark from its sums (cpp:431-442); Vi = upper triangle (LmSize 3: 00 01 02 11 12 22), dhat = V^-1 b_l
+template <int L>
+BA_D void lm_invert(const LmSums<L>& S, bool lm_on, double* Vi, double* bl, double* dhat) {
   constexpr int NV = LmSums<L>::NV;
   const double* V = S.v;
-  double bl[L];
 #pragma unroll
   for (int i = 0; i < L; ++i) bl[i] = lm_on ? S.v[NV + i] : 0.0;
   if (lm_on) {
@@ -94,138 +90,53 @@ BA_D void lm_finalize(const DeviceProblem& P, int lm, const LmCtx<L>& c, bool lm
       if (sqrt(n2) < 1e-6) { M[0] += 1e-6; M[4] += 1e-6; M[8] += 1e-6; }
       double Mi[9];
       inv3(M, Mi);
-#pragma unroll
-      for (int i = 0; i < L * L; ++i) Vi[i] = Mi[i];
+      Vi[0] = Mi[0]; Vi[1] = Mi[1]; Vi[2] = Mi[2]; Vi[3] = Mi[4]; Vi[4] = Mi[5]; Vi[5] = Mi[8];
     }
   } else {
 #pragma unroll
-    for (int i = 0; i < L * L; ++i) Vi[i] = 0.0;
-  }
-#pragma unroll
-  for (int r = 0; r < L; ++r) {
-    double v = 0.0;
-#pragma unroll
-    for (int k = 0; k < L; ++k) v += Vi[r * L + k] * bl[k];
-    dhat[r] = v;
+    for (int i = 0; i < NV; ++i) Vi[i] = 0.0;
   }
   if (L == 1) {
-    const uint32_t rslot = P.lm_rslot[lm];
-#pragma unroll
-    for (int i = 0; i < 6; ++i) Wr[i] = 0.0;
-    if (rslot != kNoSlot) {
-      const double* SBB = S.v + NV + L; const double* SBr = SBB + 6; const double* SBl = SBr + 3;
-      double M[18];   // 3 x 6 row-major, masked parameter columns zeroed
-#pragma unroll
-      for (int j = 0; j < 3; ++j)
-#pragma unroll
-        for (int k = 0; k < 3; ++k) { M[6 * j + k] = (j == k) ? -c.rho : 0.0; M[6 * j + 3 + k] = c.Ar[3 * j + k]; }
-      if ((c.ref_free & 63u) != 63u) {
-#pragma unroll
-        for (int k = 0; k < 6; ++k)
-          if (!((c.ref_free >> k) & 1u)) { M[k] = 0.0; M[6 + k] = 0.0; M[12 + k] = 0.0; }
-      }
-      const double S3[9] = {SBB[0], SBB[1], SBB[2], SBB[1], SBB[3], SBB[4], SBB[2], SBB[4], SBB[5]};
-      double TM[18];  // S3 M
-#pragma unroll
-      for (int j = 0; j < 3; ++j)
-#pragma unroll
-        for (int k = 0; k < 6; ++k) TM[6 * j + k] = S3[3 * j] * M[k] + S3[3 * j + 1] * M[6 + k] + S3[3 * j + 2] * M[12 + k];
-      double gr[6];
-#pragma unroll
-      for (int k = 0; k < 6; ++k) {
-        gr[k] = M[k] * SBr[0] + M[6 + k] * SBr[1] + M[12 + k] * SBr[2];
-        Wr[k] = M[k] * SBl[0] + M[6 + k] * SBl[1] + M[12 + k] * SBl[2];
-      }
-      // reference-pose record: H_rr - W_r V^-1 W_r^T (upper) | g_r | g_r - W_r dhat
-      double* o = P.lm_rec + (size_t)rslot * kLmRec;
-      int k = 0;
-#pragma unroll
-      for (int b = 0; b < 6; ++b)
-#pragma unroll
-        for (int a = 0; a <= b; ++a) {
-          if (writer && (k % MOD) == rem) o[k] = (M[a] * TM[b] + M[6 + a] * TM[6 + b] + M[12 + a] * TM[12 + b]) - Vi[0] * Wr[a] * Wr[b];
-          ++k;
-        }
-#pragma unroll
-      for (int a = 0; a < 6; ++a)
-        if (writer && ((21 + a) % MOD) == rem) { o[21 + a] = gr[a]; o[27 + a] = gr[a] - Wr[a] * dhat[0]; }
-    }
-    if (writer && rem == 0) {
-#pragma unroll
-      for (int a = 0; a < 6; ++a) P.lm_Wref[(size_t)lm * 6 + a] = Wr[a];
-    }
-  }
-  if (writer && rem == 0) {
-#pragma unroll
-    for (int i = 0; i < L * L; ++i) P.lm_Vinv[(size_t)lm * L * L + i] = Vi[i];
-#pragma unroll
-    for (int i = 0; i < L; ++i) { P.lm_bl[(size_t)lm * L + i] = bl[i]; P.lm_dhat[(size_t)lm * L + i] = dhat[i]; }
-  }
-}
-
-// the pose-major record of one observation (ba_gpu.h), written once its landmark's V^-1, dhat (and W_r) are known
-template <int L>
-BA_D void emit_record(double* out, const LmCtx<L>& c, const ObsJac<L>& o, double w, bool lm_on, const double* Vi, const double* dhat,
-                      const double* Wr) {
-  const double sw = sqrt(w);
-  double A[12], B[2 * L];
-#pragma unroll
-  for (int k = 0; k < 12; ++k) A[k] = sw * o.Jm[k];
-#pragma unroll
-  for (int k = 0; k < 2 * L; ++k) B[k] = sw * o.Jl[k];
-  const double r0 = sw * o.r[0], r1 = sw * o.r[1];
-  if (L == 3) {
-    double C[6];
-#pragma unroll
-    for (int rr = 0; rr < 2; ++rr)
-#pragma unroll
-      for (int cc = 0; cc < 3; ++cc) C[rr * 3 + cc] = B[rr * 3] * Vi[cc] + B[rr * 3 + 1] * Vi[3 + cc] + B[rr * 3 + 2] * Vi[6 + cc];
-    const double p0 = r0 - (B[0] * dhat[0] + B[1] * dhat[1] + B[2] * dhat[2]);
-    const double p1 = r1 - (B[3] * dhat[0] + B[4] * dhat[1] + B[5] * dhat[2]);
-#pragma unroll
-    for (int k = 0; k < 3; ++k) st2(out + 2 * k, C[2 * k], C[2 * k + 1]);
-#pragma unroll
-    for (int k = 0; k < 6; ++k) st2(out + 6 + 2 * k, A[2 * k], A[2 * k + 1]);
-#pragma unroll
-    for (int k = 0; k < 3; ++k) st2(out + 18 + 2 * k, lm_on ? B[2 * k] : 0.0, lm_on ? B[2 * k + 1] : 0.0);
-    st2(out + 24, r0, r1);
-    st2(out + 26, p0, p1);
+    dhat[0] = Vi[0] * bl[0];
   } else {
-    const double bv0 = lm_on ? B[0] : 0.0, bv1 = lm_on ? B[1] : 0.0;
-    double W[6], Q[12];
-#pragma unroll
-    for (int k = 0; k < 6; ++k) W[k] = A[k] * bv0 + A[6 + k] * bv1;
-    const double c0 = bv0 * Vi[0], c1 = bv1 * Vi[0];
-    if (o.ref_on) {
-      ref_jacobian<L>(c, o.Bp, Q);
-#pragma unroll
-      for (int k = 0; k < 6; ++k) { Q[k] = sw * Q[k] - c0 * Wr[k]; Q[6 + k] = sw * Q[6 + k] - c1 * Wr[k]; }
-    } else {
-#pragma unroll
-      for (int k = 0; k < 12; ++k) Q[k] = 0.0;
-    }
-    const double p0 = r0 - bv0 * dhat[0], p1 = r1 - bv1 * dhat[0];
-#pragma unroll
-    for (int k = 0; k < 3; ++k) st2(out + 2 * k, W[2 * k] * Vi[0], W[2 * k + 1] * Vi[0]);
-#pragma unroll
-    for (int k = 0; k < 3; ++k) st2(out + 6 + 2 * k, W[2 * k], W[2 * k + 1]);
-#pragma unroll
-    for (int k = 0; k < 6; ++k) st2(out + 12 + 2 * k, A[2 * k], A[2 * k + 1]);
-#pragma unroll
-    for (int k = 0; k < 6; ++k) st2(out + 24 + 2 * k, Q[2 * k], Q[2 * k + 1]);
-    st2(out + 36, r0, r1);
-    st2(out + 38, p0, p1);
+    dhat[0] = Vi[0] * bl[0] + Vi[1] * bl[1] + Vi[2] * bl[2];
+    dhat[1] = Vi[1] * bl[0] + Vi[3] * bl[1] + Vi[4] * bl[2];
+    dhat[2] = Vi[2] * bl[0] + Vi[4] * bl[1] + Vi[5] * bl[2];
   }
 }
 
-// Landmarks with more than 32 observations (lm_list): one warp per landmark, lanes stride over the track.  Two sweeps:
-// weights and sums, then the records (the lane's last observation keeps its Jacobians in registers).
+// the landmark's record (ba_gpu.h), written by one lane: eight 16-byte stores into one 128-byte line
 template <int L>
-__global__ void __launch_bounds__(128, (L == 1) ? 3 : 4) k_linearize_long(DeviceProblem P, const uint32_t* __restrict__ lm_list, int n_list) {
+BA_D void lm_write(const DeviceProblem& P, int lm, const LmCtx<L>& c, bool lm_on, const LmSums<L>& S) {
+  constexpr int NV = LmSums<L>::NV;
+  double Vi[NV], bl[L], dhat[L];
+  lm_invert<L>(S, lm_on, Vi, bl, dhat);
+  double* o = P.lm_rec + (size_t)lm * kLmRec;
+  st2(o, c.X[0], c.X[1]); st2(o + 2, c.X[2], c.rho);
+  if (L == 3) {
+    st2(o + 4, Vi[0], Vi[1]); st2(o + 6, Vi[2], Vi[3]); st2(o + 8, Vi[4], Vi[5]);
+    st2(o + 10, dhat[0], dhat[1]); st2(o + 12, dhat[2], 0.0); st2(o + 14, 0.0, 0.0);
+  } else {
+    const double* SBB = S.v + NV + L; const double* SBr = SBB + 6; const double* SBl = SBr + 3;
+    const double* xs = P.lm_x + 4 * (size_t)lm;
+    st2(o + 4, c.tws_r[0], c.tws_r[1]); st2(o + 6, c.tws_r[2], Vi[0]);
+    st2(o + 8, dhat[0], xs[0]); st2(o + 10, xs[1], xs[2]);
+    st2(o + 12, SBl[0], SBl[1]); st2(o + 14, SBl[2], 0.0);
+    double* oc = P.lm_recC + (size_t)lm * kLmRecC;
+    st2(oc, SBB[0], SBB[1]); st2(oc + 2, SBB[2], SBB[3]); st2(oc + 4, SBB[4], SBB[5]);
+    st2(oc + 6, SBr[0], SBr[1]); st2(oc + 8, SBr[2], 0.0);
+  }
+#pragma unroll
+  for (int i = 0; i < L; ++i) P.lm_bl[(size_t)lm * L + i] = bl[i];
+}
+
+// Landmarks with more than 32 observations (lm_list): one warp per landmark, lanes stride over the track.
+template <int L>
+__global__ void __launch_bounds__(128) k_linearize_long(DeviceProblem P, const uint32_t* __restrict__ lm_list, int n_list) {
   const int lane = threadIdx.x & 31;
   const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, n_warps = (gridDim.x * blockDim.x) >> 5;
-  const double c_huber = P.c_huber_factor * sqrt(P.sc->median);
-  double err = 0.0;
+  const double c_huber = P.c_huber_factor * sqrt(P.sc->median), c2 = c_huber * c_huber;
+  double err[1] = {0.0};
   for (int q = warp; q < n_list; q += n_warps) {
     const int lm = (int)lm_list[q];
     const int s = P.lm_obs_start[lm], e = P.lm_obs_start[lm + 1];
@@ -235,52 +146,33 @@ __global__ void __launch_bounds__(128, (L == 1) ? 3 : 4) k_linearize_long(Device
     LmSums<L> S;
 #pragma unroll
     for (int i = 0; i < LmSums<L>::N; ++i) S.v[i] = 0.0;
-    ObsJac<L> o;
-    double w_keep = 0.0;
-    int i_keep = -1;
     for (int i = s + lane; i < e; i += 32) {
+      ObsJac<L> o;
       obs_jacobians<L>(P, c, i, o);
       const double w0 = P.obs_w0[i];
       const double n2 = o.r[0] * o.r[0] + o.r[1] * o.r[1];
-      const double w = huber_weight(n2 * w0, w0, c_huber, P.use_robust);
+      const double w = huber_weight(n2 * w0, w0, c_huber, c2, P.use_robust);
       P.obs_w[i] = w;
-      w_keep = w; i_keep = i;
-      err += n2 * w;
+      err[0] += n2 * w;
       sums_add<L>(S, o, w, lm_on);
     }
 #pragma unroll
     for (int i = 0; i < LmSums<L>::N; ++i) S.v[i] = warp_sum(S.v[i]);
-    double Vi[L * L], dhat[L], Wr[6];
-    lm_finalize<L, 32>(P, lm, c, lm_on, S, Vi, dhat, Wr, true, lane);
-    for (int i = i_keep; i >= s; i -= 32) {
-      const uint32_t slot = P.obs_slot[i];
-      if (slot == kNoSlot) continue;
-      if (i != i_keep) { obs_jacobians<L>(P, c, i, o); w_keep = P.obs_w[i]; }
-      emit_record<L>(P.rec + (size_t)slot * P.rec_stride, c, o, w_keep, lm_on, Vi, dhat, Wr);
-    }
+    if (lane == 0) lm_write<L>(P, lm, c, lm_on, S);
   }
-  err = warp_sum(err);
-  if (lane == 0) red_add(&P.sc->proj_error, err);
+  grid_sum_fixed<1>(err, P.red_partial, P.red_counter, &P.sc->proj_error, true);
 }
 
 // Packed tasks: a task is a run of consecutive landmarks with at most 32 observations in total (packed on the host from
-// the CSR bounds, symbolic set-up).  One warp per task, ONE OBSERVATION PER LANE: the Jacobians are evaluated once and
-// stay in registers, the per-landmark sums are segmented warp reductions over the lanes of the landmark.  (One lane group
-// per landmark left 13 of 32 lanes busy on a BAL-like track-length distribution and evaluated long tracks twice.)
-// STAGE: the 32 records of a task are assembled in shared memory and written out with consecutive lanes on consecutive
-// 16-byte pieces of one record (full 32-byte sectors, a few records per store instruction) instead of every lane
-// storing 14-20 separate half sectors of its own record.
-template <int L, bool STAGE>
-__global__ void __launch_bounds__(128, (L == 1) ? 3 : 4) k_linearize_packed(DeviceProblem P, const uint2* __restrict__ tasks, int n_tasks) {
-  constexpr int RS = (L == 3) ? kRec3 : kRec1;
-  // stage stride RS + 2 doubles: a lane's 16-byte stores land 240 / 336 bytes apart, which spreads the eight lanes of a
-  // store phase over all 32 banks (224 / 320 bytes put them on the same 8 / 16 banks: 2- / 4-way conflicts)
-  constexpr int SS = RS + 2;
-  __shared__ double2 srec[STAGE ? 4 * 32 * SS / 2 : 1];
+// the CSR bounds, symbolic set-up).  One warp per task, ONE OBSERVATION PER LANE: the Jacobians are evaluated once,
+// the per-landmark sums are segmented warp reductions over the lanes of the landmark, the head lane of a landmark
+// writes its record.
+template <int L>
+__global__ void __launch_bounds__(128) k_linearize_packed(DeviceProblem P, const uint2* __restrict__ tasks, int n_tasks) {
   const int lane = threadIdx.x & 31;
   const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, n_warps = (gridDim.x * blockDim.x) >> 5;
-  const double c_huber = P.c_huber_factor * sqrt(P.sc->median);
-  double err = 0.0;
+  const double c_huber = P.c_huber_factor * sqrt(P.sc->median), c2 = c_huber * c_huber;
+  double err[1] = {0.0};
   // two levels of the dependent chain (task -> landmark / pose ids -> landmark point / pose frame) are requested one
   // task ahead: the next task's bounds, and its lanes' landmark and pose ids
   uint2 tk_n = warp < n_tasks ? tasks[warp] : make_uint2(0, 0);
@@ -300,7 +192,6 @@ __global__ void __launch_bounds__(128, (L == 1) ? 3 : 4) k_linearize_packed(Devi
     const int lm_prev = __shfl_up_sync(0xffffffffu, lm, 1);
     const bool head = on && (lane == 0 || lm != lm_prev);
     const unsigned heads = __ballot_sync(0xffffffffu, head);
-    const int hl = 31 - __clz(heads & (0xffffffffu >> (31 - lane)));          // lane 0 is always a head (n >= 1)
     const unsigned above = (lane == 31) ? 0u : (heads & (0xffffffffu << (lane + 1)));
     const int seg_end = above ? (__ffs(above) - 1) : n;
     LmCtx<L> c;
@@ -309,21 +200,17 @@ __global__ void __launch_bounds__(128, (L == 1) ? 3 : 4) k_linearize_packed(Devi
     LmSums<L> S;
 #pragma unroll
     for (int k = 0; k < LmSums<L>::N; ++k) S.v[k] = 0.0;
-    ObsJac<L> o;
-    uint32_t slot = kNoSlot;
-    double w = 0.0;
     if (on) {
-      slot = P.obs_slot[i];
+      ObsJac<L> o;
       obs_jacobians<L>(P, c, i, o, m_pre);
       const double w0 = P.obs_w0[i];
       const double n2 = o.r[0] * o.r[0] + o.r[1] * o.r[1];
-      w = huber_weight(n2 * w0, w0, c_huber, P.use_robust);
+      const double w = huber_weight(n2 * w0, w0, c_huber, c2, P.use_robust);
       P.obs_w[i] = w;
-      err += n2 * w;
+      err[0] += n2 * w;
       sums_add<L>(S, o, w, lm_on);
     }
-    // segmented reduction to the head lane (a lane adds its neighbour at distance d only inside its own landmark),
-    // then every lane of the landmark reads the totals from its head
+    // segmented reduction to the head lane (a lane adds its neighbour at distance d only inside its own landmark)
 #pragma unroll
     for (int d = 1; d < 32; d <<= 1) {
       const bool take = on && (lane + d < seg_end);
@@ -333,32 +220,9 @@ __global__ void __launch_bounds__(128, (L == 1) ? 3 : 4) k_linearize_packed(Devi
         if (take) S.v[k] += other;
       }
     }
-#pragma unroll
-    for (int k = 0; k < LmSums<L>::N; ++k) S.v[k] = __shfl_sync(0xffffffffu, S.v[k], on ? hl : lane);
-    if (on) {
-      double Vi[L * L], dhat[L], Wr[6];
-      lm_finalize<L, 1>(P, lm, c, lm_on, S, Vi, dhat, Wr, head, 0);
-      if (slot != kNoSlot) {
-        double* out = STAGE ? reinterpret_cast<double*>(srec) + ((threadIdx.x >> 5) * 32 + lane) * SS : P.rec + (size_t)slot * P.rec_stride;
-        emit_record<L>(out, c, o, w, lm_on, Vi, dhat, Wr);
-      }
-    }
-    if (STAGE) {
-      __syncwarp();
-      const double2* sw2 = srec + (threadIdx.x >> 5) * 32 * (SS / 2);
-#pragma unroll 2
-      for (int base = 0; base < n * (RS / 2); base += 32) {     // uniform trip count: the shuffle needs every lane
-        const int idx = base + lane;
-        const bool valid = idx < n * (RS / 2);
-        const int rec = valid ? idx / (RS / 2) : 0, ch = idx - rec * (RS / 2);
-        const uint32_t sl = __shfl_sync(0xffffffffu, slot, rec);
-        if (valid && sl != kNoSlot) reinterpret_cast<double2*>(P.rec + (size_t)sl * RS)[ch] = sw2[rec * (SS / 2) + ch];
-      }
-      __syncwarp();
-    }
+    if (head) lm_write<L>(P, lm, c, lm_on, S);
   }
-  err = warp_sum(err);
-  if (lane == 0) red_add(&P.sc->proj_error, err);
+  grid_sum_fixed<1>(err, P.red_partial, P.red_counter, &P.sc->proj_error, true);
 }
 
 // landmarks without a (local) observation: the outputs the kernels above would have written for an empty track
@@ -367,279 +231,305 @@ __global__ void k_lm_defaults(DeviceProblem P) {
   const int lm = blockIdx.x * blockDim.x + threadIdx.x;
   if (lm >= P.n_lms) return;
   if (P.lm_obs_start[lm] != P.lm_obs_start[lm + 1]) return;
-  double Vi[L * L];
+  LmSums<L> S;
 #pragma unroll
-  for (int i = 0; i < L * L; ++i) Vi[i] = 0.0;
-  if (P.lm_opt[lm] >= 0) {
-    if (L == 1) {
-      Vi[0] = 1.0 / 1e-6;
-    } else {
-      double M[9] = {1e-6, 0, 0, 0, 1e-6, 0, 0, 0, 1e-6}, Mi[9];
-      inv3(M, Mi);
-#pragma unroll
-      for (int i = 0; i < L * L; ++i) Vi[i] = Mi[i];
-    }
-  }
-#pragma unroll
-  for (int i = 0; i < L * L; ++i) P.lm_Vinv[(size_t)lm * L * L + i] = Vi[i];
-#pragma unroll
-  for (int i = 0; i < L; ++i) { P.lm_bl[(size_t)lm * L + i] = 0.0; P.lm_dhat[(size_t)lm * L + i] = 0.0; }
-  if (L == 1) {
-#pragma unroll
-    for (int a = 0; a < 6; ++a) P.lm_Wref[(size_t)lm * 6 + a] = 0.0;
-  }
+  for (int k = 0; k < LmSums<L>::N; ++k) S.v[k] = 0.0;
+  LmCtx<L> c;
+  load_lm<L>(P, lm, c);
+  lm_write<L>(P, lm, c, c.lm_opt >= 0, S);
 }
 
 // ---------------------------------------------------------------------------------------
-// pass B: one warp per work item (a chunk of one S block), items claimed in order from one counter
-// so that the warps in flight always work on neighbouring blocks (their records stay in L2).
-// The records of 16 pairs (or 16 consecutive records of a diagonal item) are brought into shared
-// memory by cp.async with CHUNK-wise lane mapping — consecutive lanes copy consecutive 16-byte
-// pieces of one record, a few cache lines per instruction instead of 32 — in a 3-stage pipeline.
-// Two lanes share a pair: each multiplies out three of the six block columns (24 accumulators per
-// lane instead of 36+12: registers set the occupancy of this latency-bound gather).  The partial
-// sets are transposed through shared memory so that lane k owns element k of the block.
-constexpr int kAccL = 24;          // per lane: 6 rows x 3 columns, then 6 entries of b_p (even lane) or rhs_sc (odd lane)
-constexpr int kPartial = 64;       // doubles per partial-sum slot (two halves of kAccL, padded)
+// pass B: one warp per work item (a chunk of one S block), items claimed in order from one counter so that the warps
+// in flight work on neighbouring blocks (their observations and landmark records stay in L2).  One list entry per
+// lane.  The 5 sectors of an entry are brought into shared memory by cp.async with CHUNK-wise lane mapping —
+// consecutive lanes copy consecutive 16-byte pieces of one record, so an instruction touches 4-16 cache lines instead
+// of 32 (L1 serves one line per cycle) — in a multi-stage pipeline; the lane then reads its own entry back (stride of
+// an odd number of 16-byte words: conflict-free).  Accumulators: the 36 elements of the block (or 21 + 6 + 6 for a
+// diagonal block with b_p and rhs_sc) per lane, transposed through shared memory at the end of the item so that lane e
+// owns element e.
+constexpr int kPartial = 64;       // doubles per partial-sum slot
 constexpr int kRedWarps = 4;
-constexpr int kPPB = 16;           // pairs (or records) per batch
-constexpr int kStages = 3;
+constexpr int kNAcc = 36;
 template <int L> struct RedCfg {
-  static constexpr int PS = (L == 3) ? 18 : 24;                 // doubles per staged pair part
-  static constexpr int RS = (L == 3) ? kRec3 : kRec1;           // doubles per record
-  static constexpr int DATA = (2 * kPPB * PS > kPPB * RS) ? 2 * kPPB * PS : kPPB * RS;   // >= kPPB * kLmRec
-  static constexpr int BUF = DATA + 8;                          // + 16 uint32 tags
-  static constexpr size_t smem = sizeof(double) * kStages * BUF * kRedWarps;
+  static constexpr int STRIDE = (L == 3) ? 22 : 30;   // doubles per staged entry: 176 / 240 bytes
+  static constexpr int STAGES = (L == 3) ? 3 : 2;
+  static constexpr int DATA = 32 * STRIDE;
+  static constexpr int BUF = DATA + 32;               // + 32 (a, b) index pairs
+  static constexpr size_t smem = sizeof(double) * STAGES * BUF * kRedWarps;
 };
+static_assert(RedCfg<3>::STAGES * RedCfg<3>::BUF >= kNAcc * 33 && RedCfg<1>::STAGES * RedCfg<1>::BUF >= kNAcc * 33, "transpose buffer");
 
-BA_D void cp_async16(double* smem_dst, const double* gsrc) {
+BA_D void cp_async16(double* smem_dst, const void* gsrc) {
   const unsigned d = (unsigned)__cvta_generic_to_shared(smem_dst);
   asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(d), "l"(gsrc) : "memory");
 }
 BA_D void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
 template <int N> BA_D void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
 
-// diagonal record, lane half h: columns 3h..3h+2 of A^T N A (all six rows) and b_p (h = 0) or rhs_sc (h = 1)
-template <int L>
-BA_D void diag_record(const double* r, int h, double* acc) {
-  double A[12];
+// stage NC 16-byte chunks of the record `base + id * rec_bytes` of every lane's entry (id = kNoSlot: none) at doubles
+// offset `off` of the entry's stage slot
+template <int NC, int STRIDE>
+BA_D void stage_chunks(double* buf, int off, const char* __restrict__ base, int rec_bytes, uint32_t id, int lane) {
 #pragma unroll
-  for (int k = 0; k < 6; ++k) ld2(r + (L == 3 ? 6 : 12) + 2 * k, A[2 * k], A[2 * k + 1]);
-  double q0, q1;
-  ld2(r + (L == 3 ? 24 : 36) + 2 * h, q0, q1);     // (r0, r1) or (rho0, rho1)
-  if (L == 3) {
-    double C[6], B[6];
-#pragma unroll
-    for (int k = 0; k < 3; ++k) { ld2(r + 2 * k, C[2 * k], C[2 * k + 1]); ld2(r + 18 + 2 * k, B[2 * k], B[2 * k + 1]); }
-    const double n00 = 1.0 - (C[0] * B[0] + C[1] * B[1] + C[2] * B[2]);
-    const double n01 = -(C[0] * B[3] + C[1] * B[4] + C[2] * B[5]);
-    const double n10 = -(C[3] * B[0] + C[4] * B[1] + C[5] * B[2]);
-    const double n11 = 1.0 - (C[3] * B[3] + C[4] * B[4] + C[5] * B[5]);
-#pragma unroll
-    for (int c = 0; c < 3; ++c) {
-      const double a0 = h ? A[3 + c] : A[c], a1 = h ? A[9 + c] : A[6 + c];
-      const double t0 = n00 * a0 + n01 * a1, t1 = n10 * a0 + n11 * a1;
-#pragma unroll
-      for (int rr = 0; rr < 6; ++rr) acc[c * 6 + rr] += A[rr] * t0 + A[6 + rr] * t1;
-    }
-  } else {
-    double E[6];
-#pragma unroll
-    for (int k = 0; k < 3; ++k) ld2(r + 2 * k, E[2 * k], E[2 * k + 1]);
-    const double* Wh = r + 6 + 3 * h;
-#pragma unroll
-    for (int c = 0; c < 3; ++c) {
-      const double a0 = h ? A[3 + c] : A[c], a1 = h ? A[9 + c] : A[6 + c], wc = Wh[c];
-#pragma unroll
-      for (int rr = 0; rr < 6; ++rr) acc[c * 6 + rr] += A[rr] * a0 + A[6 + rr] * a1 - E[rr] * wc;
-    }
-  }
-#pragma unroll
-  for (int k = 0; k < 6; ++k) acc[18 + k] += A[k] * q0 + A[6 + k] * q1;
-}
-
-// acc += columns 3h..3h+2 of the contribution of one staged pair to its block.  pa: part of the entry in the
-// row pose, pb: part of the entry in the column pose.
-//   LmSize 3: pa = [C (2x3) | At (2x6)], pb = [At (2x6) | Bt (2x3)]          -At_a^T C_a Bt_b^T At_b
-//   LmSize 1: tag < kPairTagRefRow: pa = E (6), pb = W (6)                    -E_a W_b^T
-//             else pa = [At (2x6) | Q (2x6)]:  At^T Q (measurement pose is the row) or Q^T At
-template <int L>
-BA_D void pair_product(const double* pa, const double* pb, uint32_t tag, int h, double* acc) {
-  if (L == 3) {
-    double C[6], B[6], Aa[12];
-#pragma unroll
-    for (int k = 0; k < 3; ++k) { ld2(pa + 2 * k, C[2 * k], C[2 * k + 1]); ld2(pb + 12 + 2 * k, B[2 * k], B[2 * k + 1]); }
-    const double m00 = -(C[0] * B[0] + C[1] * B[1] + C[2] * B[2]);
-    const double m01 = -(C[0] * B[3] + C[1] * B[4] + C[2] * B[5]);
-    const double m10 = -(C[3] * B[0] + C[4] * B[1] + C[5] * B[2]);
-    const double m11 = -(C[3] * B[3] + C[4] * B[4] + C[5] * B[5]);
-#pragma unroll
-    for (int k = 0; k < 6; ++k) ld2(pa + 6 + 2 * k, Aa[2 * k], Aa[2 * k + 1]);
-    const double* b0 = pb + 3 * h;
-#pragma unroll
-    for (int c = 0; c < 3; ++c) {
-      const double x0 = b0[c], x1 = b0[6 + c];
-      const double t0 = m00 * x0 + m01 * x1, t1 = m10 * x0 + m11 * x1;
-#pragma unroll
-      for (int r = 0; r < 6; ++r) acc[c * 6 + r] += Aa[r] * t0 + Aa[6 + r] * t1;
-    }
-  } else {
-    if (tag < kPairTagRefRow) {
-      double E[6];
-#pragma unroll
-      for (int k = 0; k < 3; ++k) ld2(pa + 2 * k, E[2 * k], E[2 * k + 1]);
-      const double* w = pb + 3 * h;
-#pragma unroll
-      for (int c = 0; c < 3; ++c) {
-        const double wc = w[c];
-#pragma unroll
-        for (int r = 0; r < 6; ++r) acc[c * 6 + r] -= E[r] * wc;
-      }
-    } else {
-      double X[12];
-      const bool meas_row = (tag == kPairTagMeasRow);
-      const double* x = pa + (meas_row ? 0 : 12);
-      const double* z = pa + (meas_row ? 12 : 0) + 3 * h;
-#pragma unroll
-      for (int k = 0; k < 6; ++k) ld2(x + 2 * k, X[2 * k], X[2 * k + 1]);
-#pragma unroll
-      for (int c = 0; c < 3; ++c) {
-        const double z0 = z[c], z1 = z[6 + c];
-#pragma unroll
-        for (int r = 0; r < 6; ++r) acc[c * 6 + r] += X[r] * z0 + X[6 + r] * z1;
-      }
-    }
-  }
-}
-
-// stage the parts of up to kPPB list entries (batch `bt` of the item) into buf, their tags behind the data.
-//   entries between two measurement poses: two parts per entry (row-pose part, column-pose part) of
-//     18 doubles (LmSize 3: [C | At] and [At | Bt]) or 6 doubles (LmSize 1: E and W);
-//   LmSize 1 measurement/reference entries (kItemOffRef): one part of 24 doubles [At | Q].
-template <int L, int KIND> struct PartCfg {
-  static constexpr int PC = (KIND == kItemOffRef) ? 12 : (L == 3 ? 9 : 3);     // 16-byte chunks per part
-  static constexpr int NPART = (KIND == kItemOffRef) ? kPPB : 2 * kPPB;
-  static constexpr int PS = 2 * PC;                                            // doubles per part
-};
-template <int L, int KIND>
-BA_D void stage_pairs(const DeviceProblem& P, const uint2 ab, double* buf, int lane) {
-  typedef PartCfg<L, KIND> C;
-  if (lane < kPPB) reinterpret_cast<uint32_t*>(buf + RedCfg<L>::DATA)[lane] = (ab.x == kNoSlot) ? kNoSlot - 2 : ab.y;
-#pragma unroll
-  for (int k = 0; k < (C::NPART * C::PC + 31) / 32; ++k) {
+  for (int k = 0; k < NC; ++k) {
     const int idx = k * 32 + lane;
-    const int part = idx / C::PC, chunk = idx - part * C::PC;
-    const int pl = ((KIND == kItemOffRef) ? part : (part >> 1)) & (kPPB - 1), side = (KIND == kItemOffRef) ? 0 : (part & 1);
-    const uint32_t sa = __shfl_sync(0xffffffffu, ab.x, pl), sb = __shfl_sync(0xffffffffu, ab.y, pl);
-    if (sa == kNoSlot || idx >= C::NPART * C::PC) continue;
-    const double* src;
-    if (KIND == kItemOffRef) src = P.rec + (size_t)sa * kRec1 + 12;
-    else src = P.rec + (size_t)(side ? sb : sa) * (L == 3 ? kRec3 : kRec1) + (side ? 6 : 0);
-    cp_async16(buf + part * C::PS + chunk * 2, src + chunk * 2);
+    const int p = idx / NC, ch = idx - p * NC;
+    const uint32_t src = __shfl_sync(0xffffffffu, id, p);
+    if (src != kNoSlot) cp_async16(buf + p * STRIDE + off + 2 * ch, base + (size_t)src * rec_bytes + 16 * ch);
   }
 }
 
-// stage up to kPPB consecutive records (stride RS doubles) starting at slot s0 (s0 may be past the end)
-template <int RS>
-BA_D void stage_records(const double* __restrict__ base, uint32_t s0, uint32_t end, double* buf, int lane) {
-  if (s0 >= end) return;
-  const int cnt = (int)min((uint32_t)kPPB, end - s0);
-  const double* src = base + (size_t)s0 * RS;
+struct PairLists { const uint32_t *a, *b, *lm; };   // off-diagonal entries: observation of the row pose, of the column pose (or tag), landmark
+
+// upper-triangle packing of the diagonal accumulators: k = c (c + 1) / 2 + r, r <= c
+BA_D void add_upper(double* acc, const double* x0, const double* x1, const double* y0, const double* y1) {
+  int k = 0;
 #pragma unroll
-  for (int k = 0; k < (kPPB * RS / 2 + 31) / 32; ++k) {
-    const int idx = k * 32 + lane;
-    if (idx < cnt * (RS / 2)) cp_async16(buf + idx * 2, src + idx * 2);
-  }
+  for (int c = 0; c < 6; ++c)
+#pragma unroll
+    for (int r = 0; r <= c; ++r) { acc[k] += x0[r] * y0[c] + x1[r] * y1[c]; ++k; }
 }
 
 template <int L>
-__global__ void __launch_bounds__(kRedWarps * 32, 4) k_reduce_blocks(DeviceProblem P, const ReduceItem* __restrict__ items, int n_items,
-                                                                     const uint2* __restrict__ pairs, double* __restrict__ partial,
-                                                                     unsigned int* __restrict__ counters, unsigned int* __restrict__ next_item) {
+__global__ void __launch_bounds__(kRedWarps * 32, (L == 3) ? 3 : 3) k_reduce_blocks(DeviceProblem P, const ReduceItem* __restrict__ items, int n_items, PairLists pl,
+                                                                     double* __restrict__ partial, unsigned int* __restrict__ counters,
+                                                                     unsigned int* __restrict__ next_item) {
   typedef RedCfg<L> Cfg;
+  constexpr int ST = Cfg::STRIDE, NS = Cfg::STAGES;
   extern __shared__ double sdyn[];
   const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
-  const int pl = lane >> 1, h = lane & 1;
-  double* stage = sdyn + (size_t)wib * kStages * Cfg::BUF;   // the transpose-reduce reuses the stage buffers
+  double* stage = sdyn + (size_t)wib * NS * Cfg::BUF;   // the transpose-reduce reuses the stage buffers
+  const double c_huber = P.c_huber_factor * sqrt(P.sc->median), c2 = c_huber * c_huber;
+  const char* obs_base = reinterpret_cast<const char*>(P.obs_rec);
+  const char* lm_base = reinterpret_cast<const char*>(P.lm_rec);
+  const char* lmc_base = reinterpret_cast<const char*>(P.lm_recC);
   for (;;) {
     int it = 0;
     if (lane == 0) it = (int)atomicAdd(next_item, 1u);
     it = __shfl_sync(0xffffffffu, it, 0);
     if (it >= n_items) break;
     const ReduceItem w = items[it];
-    double acc[kAccL];
+    const int kind = (int)w.kind;
+    const bool diag = (kind == kItemDiagObs || kind == kItemDiagLm);
+    const int row_pose = P.opt_to_pose[w.row], col_pose = P.opt_to_pose[w.col];
+    double acc[kNAcc];
 #pragma unroll
-    for (int k = 0; k < kAccL; ++k) acc[k] = 0.0;
-    const int nb = (int)((w.end - w.begin + kPPB - 1) / kPPB);
-    const bool diag = (w.kind == kItemDiagObs || w.kind == kItemDiagLm);
-    const bool obs = (w.kind == kItemDiagObs);
-    // ---- software pipeline: batch bt + kStages - 1 is in flight while batch bt is multiplied out ----
-    // the list entries of a batch are requested one batch ahead of the record gather that needs them
-    auto entry = [&](int b) {
-      const uint32_t p = w.begin + (uint32_t)b * kPPB + (lane & (kPPB - 1));
-      return (!diag && b < nb && p < w.end) ? pairs[p] : make_uint2(kNoSlot, kNoSlot);
+    for (int k = 0; k < kNAcc; ++k) acc[k] = 0.0;
+    const int nb = (int)((w.end - w.begin + 31) / 32);
+    // list entries of batch b (one per lane): e0 = observation of the row pose (or of the pose, diagonal),
+    // e1 = observation of the column pose / tag, e2 = landmark
+    auto entry = [&](int b, uint32_t& e0, uint32_t& e1, uint32_t& e2) {
+      const uint32_t p = w.begin + (uint32_t)b * 32 + lane;
+      e0 = kNoSlot; e1 = kNoSlot; e2 = kNoSlot;
+      if (b >= nb || p >= w.end) return;
+      if (kind == kItemDiagObs) { e0 = P.pose_obs[p]; e2 = P.pose_obs_lm[p]; }
+      else if (kind == kItemDiagLm) { e2 = P.pose_lms[p]; }
+      else { e0 = pl.a[p]; e1 = pl.b[p]; e2 = pl.lm[p]; }
     };
-    uint2 ab_next = entry(0);
-    for (int bt = -(kStages - 1); bt < nb; ++bt) {
-      const int ld = bt + kStages - 1;
+    uint32_t n0, n1, n2;
+    entry(0, n0, n1, n2);
+    for (int bt = -(NS - 1); bt < nb; ++bt) {
+      const int ld = bt + NS - 1;
       if (ld < nb) {
-        double* dst = stage + (ld % kStages) * Cfg::BUF;
-        const uint2 ab = ab_next;
-        ab_next = entry(ld + 1);
-        if (w.kind == kItemOffRef) { if (L == 1) stage_pairs<1, kItemOffRef>(P, ab, dst, lane); }
-        else if (!diag) stage_pairs<L, kItemOff>(P, ab, dst, lane);
-        else if (obs) stage_records<Cfg::RS>(P.rec, w.begin + (uint32_t)ld * kPPB, w.end, dst, lane);
-        else stage_records<kLmRec>(P.lm_rec, w.begin + (uint32_t)ld * kPPB, w.end, dst, lane);
+        double* dst = stage + (ld % NS) * Cfg::BUF;
+        uint32_t e0 = n0, e1 = n1, e2 = n2;
+        entry(ld + 1, n0, n1, n2);
+        reinterpret_cast<uint2*>(dst + Cfg::DATA)[lane] = make_uint2(e0, (kind == kItemDiagLm) ? e2 : e1);
+        if (kind == kItemOff || kind == kItemSym) {
+          stage_chunks<2, ST>(dst, 0, obs_base, 32, e0, lane);
+          stage_chunks<2, ST>(dst, 4, obs_base, 32, e1, lane);
+          if (L == 3) stage_chunks<5, ST>(dst, 8, lm_base, kLmRec * 8, e2, lane);
+          else stage_chunks<4, ST>(dst, 8, lm_base, kLmRec * 8, e2, lane);
+        } else if (kind == kItemDiagObs) {
+          stage_chunks<2, ST>(dst, 0, obs_base, 32, e0, lane);
+          stage_chunks<8, ST>(dst, 4, lm_base, kLmRec * 8, e2, lane);
+        } else if (L == 1 && kind == kItemOffRef) {
+          stage_chunks<2, ST>(dst, 0, obs_base, 32, e0, lane);
+          stage_chunks<8, ST>(dst, 4, lm_base, kLmRec * 8, e2, lane);
+        } else if (L == 1) {   // kItemDiagLm
+          stage_chunks<5, ST>(dst, 0, lmc_base, kLmRecC * 8, e2, lane);
+          stage_chunks<8, ST>(dst, 12, lm_base, kLmRec * 8, e2, lane);
+        }
       }
       cp_async_commit();
       if (bt < 0) continue;
-      cp_async_wait<kStages - 1>();
+      cp_async_wait<NS - 1>();
       __syncwarp();
-      const double* cur = stage + (bt % kStages) * Cfg::BUF;
-      if (!diag) {
-        const uint32_t tag = reinterpret_cast<const uint32_t*>(cur + Cfg::DATA)[pl];
-        if (tag != kNoSlot - 2) {
-          if (w.kind == kItemOffRef) pair_product<L>(cur + pl * 24, cur, tag, h, acc);
-          else pair_product<L>(cur + (2 * pl) * PartCfg<L, kItemOff>::PS, cur + (2 * pl + 1) * PartCfg<L, kItemOff>::PS, tag, h, acc);
-        }
-      } else if (w.begin + (uint32_t)bt * kPPB + pl < w.end) {
-        if (obs) {
-          diag_record<L>(cur + pl * Cfg::RS, h, acc);
-        } else {   // reference-pose records (LmSize 1): upper triangle (21) | g_r (6) | g_r~ (6), plain sums
-          const double* r = cur + pl * kLmRec;
+      const double* cur = stage + (bt % NS) * Cfg::BUF;
+      const double* d = cur + lane * ST;
+      const uint2 ids = reinterpret_cast<const uint2*>(cur + Cfg::DATA)[lane];
+      const bool valid = (kind == kItemDiagLm) ? (ids.y != kNoSlot) : (ids.x != kNoSlot);
+      if (valid) {
+        if (kind == kItemOff || kind == kItemSym) {
+          const double* lm = d + 8;
+          const int cam_a = P.obs_cam ? (int)P.obs_cam[ids.x] : 0, cam_b = P.obs_cam ? (int)P.obs_cam[ids.y] : 0;
+          Side<L> sa, sb;
+          side_eval<L>(P, lm, d[0], d[1], d[2], row_pose, cam_a, c_huber, c2, sa);
+          side_eval<L>(P, lm, d[4], d[5], d[6], col_pose, cam_b, c_huber, c2, sb);
+          if (L == 3) {
+            // M = w_a w_b B_a V^-1 B_b^T  (J_l = -B on both sides)
+            const double v00 = lm[4], v01 = lm[5], v02 = lm[6], v11 = lm[7], v12 = lm[8], v22 = lm[9];
+            double BV[6];
 #pragma unroll
-          for (int c = 0; c < 3; ++c)
+            for (int x = 0; x < 2; ++x) {
+              const double* b = sa.B + 3 * x;
+              BV[3 * x] = b[0] * v00 + b[1] * v01 + b[2] * v02;
+              BV[3 * x + 1] = b[0] * v01 + b[1] * v11 + b[2] * v12;
+              BV[3 * x + 2] = b[0] * v02 + b[1] * v12 + b[2] * v22;
+            }
+            const double ww = sa.w * sb.w;
+            const double m00 = ww * (BV[0] * sb.B[0] + BV[1] * sb.B[1] + BV[2] * sb.B[2]);
+            const double m01 = ww * (BV[0] * sb.B[3] + BV[1] * sb.B[4] + BV[2] * sb.B[5]);
+            const double m10 = ww * (BV[3] * sb.B[0] + BV[4] * sb.B[1] + BV[5] * sb.B[2]);
+            const double m11 = ww * (BV[3] * sb.B[3] + BV[4] * sb.B[4] + BV[5] * sb.B[5]);
 #pragma unroll
-            for (int rr = 0; rr < 6; ++rr) { const int cg = 3 * h + c; if (rr <= cg) acc[c * 6 + rr] += r[cg * (cg + 1) / 2 + rr]; }
+            for (int c = 0; c < 6; ++c) {
+              const double t0 = m00 * sb.Jm[c] + m01 * sb.Jm[6 + c], t1 = m10 * sb.Jm[c] + m11 * sb.Jm[6 + c];
 #pragma unroll
-          for (int k = 0; k < 6; ++k) acc[18 + k] += r[21 + 6 * h + k];
+              for (int r = 0; r < 6; ++r) acc[r * 6 + c] -= sa.Jm[r] * t0 + sa.Jm[6 + r] * t1;
+            }
+          } else {
+            // - V^-1 W_a W_b^T,  W = w Jm^T J_l
+            const double vi = lm[7];
+            double Wa[6], Wb[6];
+#pragma unroll
+            for (int k = 0; k < 6; ++k) {
+              Wa[k] = vi * sa.w * (sa.Jm[k] * sa.jl[0] + sa.Jm[6 + k] * sa.jl[1]);
+              Wb[k] = sb.w * (sb.Jm[k] * sb.jl[0] + sb.Jm[6 + k] * sb.jl[1]);
+            }
+#pragma unroll
+            for (int r = 0; r < 6; ++r)
+#pragma unroll
+              for (int c = 0; c < 6; ++c) acc[r * 6 + c] -= Wa[r] * Wb[c];
+          }
+        } else if (kind == kItemDiagObs) {
+          const double* lm = d + 4;
+          const int cam_a = P.obs_cam ? (int)P.obs_cam[ids.x] : 0;
+          Side<L> s;
+          side_eval<L>(P, lm, d[0], d[1], d[2], row_pose, cam_a, c_huber, c2, s);
+          double T0[6], T1[6];
+          double q0, q1;   // r - J_l dhat
+          if (L == 3) {
+            const double v00 = lm[4], v01 = lm[5], v02 = lm[6], v11 = lm[7], v12 = lm[8], v22 = lm[9];
+            double BV[6];
+#pragma unroll
+            for (int x = 0; x < 2; ++x) {
+              const double* b = s.B + 3 * x;
+              BV[3 * x] = b[0] * v00 + b[1] * v01 + b[2] * v02;
+              BV[3 * x + 1] = b[0] * v01 + b[1] * v11 + b[2] * v12;
+              BV[3 * x + 2] = b[0] * v02 + b[1] * v12 + b[2] * v22;
+            }
+            // N = I - w B V^-1 B^T
+            const double n00 = 1.0 - s.w * (BV[0] * s.B[0] + BV[1] * s.B[1] + BV[2] * s.B[2]);
+            const double n01 = -s.w * (BV[0] * s.B[3] + BV[1] * s.B[4] + BV[2] * s.B[5]);
+            const double n10 = -s.w * (BV[3] * s.B[0] + BV[4] * s.B[1] + BV[5] * s.B[2]);
+            const double n11 = 1.0 - s.w * (BV[3] * s.B[3] + BV[4] * s.B[4] + BV[5] * s.B[5]);
+#pragma unroll
+            for (int c = 0; c < 6; ++c) {
+              T0[c] = s.w * (n00 * s.Jm[c] + n01 * s.Jm[6 + c]);
+              T1[c] = s.w * (n10 * s.Jm[c] + n11 * s.Jm[6 + c]);
+            }
+            q0 = s.r[0] + (s.B[0] * lm[10] + s.B[1] * lm[11] + s.B[2] * lm[12]);
+            q1 = s.r[1] + (s.B[3] * lm[10] + s.B[4] * lm[11] + s.B[5] * lm[12]);
+          } else {
+            // w Jm^T Jm - V^-1 W W^T = Jm^T (w I - w^2 V^-1 jl jl^T) Jm
+            const double vi = lm[7], ww = s.w * s.w * vi;
+            const double n00 = s.w - ww * s.jl[0] * s.jl[0], n01 = -ww * s.jl[0] * s.jl[1], n11 = s.w - ww * s.jl[1] * s.jl[1];
+#pragma unroll
+            for (int c = 0; c < 6; ++c) {
+              T0[c] = n00 * s.Jm[c] + n01 * s.Jm[6 + c];
+              T1[c] = n01 * s.Jm[c] + n11 * s.Jm[6 + c];
+            }
+            q0 = s.r[0] - s.jl[0] * lm[8];
+            q1 = s.r[1] - s.jl[1] * lm[8];
+          }
+          add_upper(acc, s.Jm, s.Jm + 6, T0, T1);
+          const double wr0 = s.w * s.r[0], wr1 = s.w * s.r[1], wq0 = s.w * q0, wq1 = s.w * q1;
+#pragma unroll
+          for (int k = 0; k < 6; ++k) {
+            acc[21 + k] += s.Jm[k] * wr0 + s.Jm[6 + k] * wr1;
+            acc[27 + k] += s.Jm[k] * wq0 + s.Jm[6 + k] * wq1;
+          }
+        } else if (L == 1 && kind == kItemOffRef) {
+          // block between the measurement pose and the reference pose of one observation:
+          //   X = w Jm^T Jr - V^-1 W_a W_ref^T   (rows: measurement pose, columns: reference pose)
+          const double* lm = d + 4;
+          const bool meas_row = (ids.y == kPairTagMeasRow);
+          const int mp = meas_row ? row_pose : col_pose, rp = meas_row ? col_pose : row_pose;
+          const int cam_a = P.obs_cam ? (int)P.obs_cam[ids.x] : 0;
+          Side<L> s;
+          side_eval<L>(P, lm, d[0], d[1], d[2], mp, cam_a, c_huber, c2, s);
+          double M[18];
+          ref_M(P, rp, P.n_cams > 1 ? (int)P.lm_ref_cam[(uint32_t)((unsigned long long)__double_as_longlong(d[3]) >> 32)] : 0, lm[3], lm + 9, M);
+          double J0[6], J1[6], Wr[6], Wa[6];
+#pragma unroll
+          for (int k = 0; k < 6; ++k) {
+            J0[k] = s.w * (s.B[0] * M[k] + s.B[1] * M[6 + k] + s.B[2] * M[12 + k]);
+            J1[k] = s.w * (s.B[3] * M[k] + s.B[4] * M[6 + k] + s.B[5] * M[12 + k]);
+            Wr[k] = M[k] * lm[12] + M[6 + k] * lm[13] + M[12 + k] * lm[14];
+            Wa[k] = lm[7] * s.w * (s.Jm[k] * s.jl[0] + s.Jm[6 + k] * s.jl[1]);
+          }
+          if (meas_row) {
+#pragma unroll
+            for (int r = 0; r < 6; ++r)
+#pragma unroll
+              for (int c = 0; c < 6; ++c) acc[r * 6 + c] += s.Jm[r] * J0[c] + s.Jm[6 + r] * J1[c] - Wa[r] * Wr[c];
+          } else {
+#pragma unroll
+            for (int r = 0; r < 6; ++r)
+#pragma unroll
+              for (int c = 0; c < 6; ++c) acc[r * 6 + c] += J0[r] * s.Jm[c] + J1[r] * s.Jm[6 + c] - Wr[r] * Wa[c];
+          }
+        } else if (L == 1) {   // kItemDiagLm: the reference pose's own blocks of one landmark
+          const double* lc = d;         // SBB (6) | SBr (3)
+          const double* lm = d + 12;
+          double M[18];
+          ref_M(P, row_pose, P.n_cams > 1 ? (int)P.lm_ref_cam[ids.y] : 0, lm[3], lm + 9, M);
+          const double S3[9] = {lc[0], lc[1], lc[2], lc[1], lc[3], lc[4], lc[2], lc[4], lc[5]};
+          double TM[18];
+#pragma unroll
+          for (int j = 0; j < 3; ++j)
+#pragma unroll
+            for (int k = 0; k < 6; ++k) TM[6 * j + k] = S3[3 * j] * M[k] + S3[3 * j + 1] * M[6 + k] + S3[3 * j + 2] * M[12 + k];
+          double gr[6], Wr[6];
+#pragma unroll
+          for (int k = 0; k < 6; ++k) {
+            gr[k] = M[k] * lc[6] + M[6 + k] * lc[7] + M[12 + k] * lc[8];
+            Wr[k] = M[k] * lm[12] + M[6 + k] * lm[13] + M[12 + k] * lm[14];
+          }
+          const double vi = lm[7], dh = lm[8];
+          int k = 0;
+#pragma unroll
+          for (int c = 0; c < 6; ++c)
+#pragma unroll
+            for (int r = 0; r <= c; ++r) { acc[k] += (M[r] * TM[c] + M[6 + r] * TM[6 + c] + M[12 + r] * TM[12 + c]) - vi * Wr[r] * Wr[c]; ++k; }
+#pragma unroll
+          for (int a = 0; a < 6; ++a) { acc[21 + a] += gr[a]; acc[27 + a] += gr[a] - Wr[a] * dh; }
         }
       }
       __syncwarp();
     }
     cp_async_wait<0>();
-    // ---- transpose-reduce over the 16 lanes of each half: element e = h * 24 + k, e < 48 ----
+    __syncwarp();
+    // ---- transpose-reduce: lane e takes element e (and 32 + e) over the 32 lanes, in lane order ----
     double (*buf)[33] = reinterpret_cast<double (*)[33]>(stage);
 #pragma unroll
-    for (int k = 0; k < kAccL; ++k) buf[k][lane] = acc[k];
+    for (int k = 0; k < kNAcc; ++k) buf[k][lane] = acc[k];
     __syncwarp();
     double v0 = 0.0, v1 = 0.0;
-    {
-      const int e = lane, eh = e / kAccL, ek = e - eh * kAccL;
 #pragma unroll 8
-      for (int j = 0; j < 16; ++j) v0 += buf[ek][2 * j + eh];
-    }
-    if (lane < 2 * kAccL - 32) {
-      const int e = 32 + lane, eh = e / kAccL, ek = e - eh * kAccL;
+    for (int j = 0; j < 32; ++j) v0 += buf[lane][j];
+    if (lane < kNAcc - 32) {
 #pragma unroll 8
-      for (int j = 0; j < 16; ++j) v1 += buf[ek][2 * j + eh];
+      for (int j = 0; j < 32; ++j) v1 += buf[32 + lane][j];
     }
     __syncwarp();
     // ---- chunks of one block are combined in index order by the last one to arrive --------
     if (w.mcount > 1) {
       double* mine = partial + (size_t)w.mself * kPartial;
       mine[lane] = v0;
-      if (lane < 2 * kAccL - 32) mine[32 + lane] = v1;
+      if (lane < kNAcc - 32) mine[32 + lane] = v1;
       __threadfence();
       __syncwarp();
       unsigned int prev = 0;
@@ -652,30 +542,34 @@ __global__ void __launch_bounds__(kRedWarps * 32, 4) k_reduce_blocks(DeviceProbl
       for (uint32_t ch = 0; ch < w.mcount; ++ch) {
         const volatile double* q = partial + (size_t)(w.mfirst + ch) * kPartial;
         v0 += q[lane];
-        if (lane < 2 * kAccL - 32) v1 += q[32 + lane];
+        if (lane < kNAcc - 32) v1 += q[32 + lane];
       }
     }
     // ---- write-out (exclusive owner: plain read-modify-write) ------------------------------
     const SBlock blk = s_block(P, (int)w.row, (int)w.col);
-    if (w.kind == kItemSym) {   // same pose observed twice: X + X^T lands in the (upper) diagonal block
-      double* sy = stage;
-      sy[lane] = v0;
-      if (lane < 2 * kAccL - 32) sy[32 + lane] = v1;
+    if (kind == kItemSym) {   // same pose observed twice: X + X^T lands in the (upper) diagonal block
+      stage[lane] = v0;
+      if (lane < kNAcc - 32) stage[32 + lane] = v1;
       __syncwarp();
     }
 #pragma unroll
     for (int half = 0; half < 2; ++half) {
       const int e = half * 32 + lane;
-      if (half == 1 && lane >= 2 * kAccL - 32) break;
+      if (half == 1 && lane >= kNAcc - 32) break;
       double v = half ? v1 : v0;
-      const int eh = e / kAccL, ek = e - eh * kAccL;
-      if (ek < 18) {
-        const int c = 3 * eh + ek / 6, r = ek % 6;
-        if (w.kind == kItemSym) v += stage[(r / 3) * kAccL + (r % 3) * 6 + c];   // element (c, r)
-        if (w.kind == kItemOff || w.kind == kItemOffRef || r <= c) blk.p[(size_t)r * blk.rs + (size_t)c * blk.cs] += v;
-      } else if (diag) {
-        double* dst = eh ? P.rhs_sc : P.b_p;
-        dst[(size_t)w.row * P.D + (ek - 18)] += v;
+      if (diag) {
+        if (e < 21) {
+          const int c = (e >= 15) ? 5 : (e >= 10) ? 4 : (e >= 6) ? 3 : (e >= 3) ? 2 : (e >= 1) ? 1 : 0;
+          const int r = e - c * (c + 1) / 2;
+          blk.p[(size_t)r * blk.rs + (size_t)c * blk.cs] += v;
+        } else if (e < 33) {
+          double* dst = (e < 27) ? P.b_p : P.rhs_sc;
+          dst[(size_t)w.row * P.D + (e < 27 ? e - 21 : e - 27)] += v;
+        }
+      } else {
+        const int r = e / 6, c = e - r * 6;
+        if (kind == kItemSym) { v += stage[c * 6 + r]; if (r <= c) blk.p[(size_t)r * blk.rs + (size_t)c * blk.cs] += v; }
+        else blk.p[(size_t)r * blk.rs + (size_t)c * blk.cs] += v;
       }
     }
     __syncwarp();
@@ -696,13 +590,11 @@ static int sm_count_cached() {
 
 void launch_linearize(const DeviceProblem& P, const uint2* tasks, int n_tasks, const uint32_t* long_lms, int n_long, cudaStream_t st) {
   if (P.n_lms == 0 || P.L == 0) return;
-  const int cap = sm_count_cached() * 12;
+  const int cap = std::min(kRedMaxGrid, sm_count_cached() * 12);
   if (P.L == 1) k_lm_defaults<1><<<(P.n_lms + 255) / 256, 256, 0, st>>>(P); else k_lm_defaults<3><<<(P.n_lms + 255) / 256, 256, 0, st>>>(P);
   if (n_tasks > 0) {
     const int grid = std::max(1, std::min(cap, (n_tasks + 3) / 4));
-    static const bool stage = getenv("BAGPU_LIN_STAGE") ? atoi(getenv("BAGPU_LIN_STAGE")) != 0 : true;
-    if (P.L == 1) { if (stage) k_linearize_packed<1, true><<<grid, 128, 0, st>>>(P, tasks, n_tasks); else k_linearize_packed<1, false><<<grid, 128, 0, st>>>(P, tasks, n_tasks); }
-    else { if (stage) k_linearize_packed<3, true><<<grid, 128, 0, st>>>(P, tasks, n_tasks); else k_linearize_packed<3, false><<<grid, 128, 0, st>>>(P, tasks, n_tasks); }
+    if (P.L == 1) k_linearize_packed<1><<<grid, 128, 0, st>>>(P, tasks, n_tasks); else k_linearize_packed<3><<<grid, 128, 0, st>>>(P, tasks, n_tasks);
   }
   if (n_long > 0) {
     const int grid = std::max(1, std::min(cap, (n_long + 3) / 4));
@@ -710,8 +602,8 @@ void launch_linearize(const DeviceProblem& P, const uint2* tasks, int n_tasks, c
   }
 }
 
-void launch_reduce_blocks(const DeviceProblem& P, const ReduceItem* items, int n_items, const uint2* pairs, double* partial,
-                          unsigned int* counters, unsigned int* next_item, cudaStream_t st) {
+void launch_reduce_blocks(const DeviceProblem& P, const ReduceItem* items, int n_items, const uint32_t* pair_a, const uint32_t* pair_b,
+                          const uint32_t* pair_lm, double* partial, unsigned int* counters, unsigned int* next_item, cudaStream_t st) {
   if (n_items <= 0) return;
   static bool attr_done = false;
   if (!attr_done) {
@@ -720,11 +612,12 @@ void launch_reduce_blocks(const DeviceProblem& P, const ReduceItem* items, int n
     attr_done = true;
   }
   int grid = (n_items + kRedWarps - 1) / kRedWarps;
-  const int cap = sm_count_cached() * 4;
+  const int cap = sm_count_cached() * 3;
   if (grid > cap) grid = cap;
   cudaMemsetAsync(next_item, 0, sizeof(unsigned int), st);
-  if (P.L == 1) k_reduce_blocks<1><<<grid, kRedWarps * 32, RedCfg<1>::smem, st>>>(P, items, n_items, pairs, partial, counters, next_item);
-  else k_reduce_blocks<3><<<grid, kRedWarps * 32, RedCfg<3>::smem, st>>>(P, items, n_items, pairs, partial, counters, next_item);
+  const PairLists pl = {pair_a, pair_b, pair_lm};
+  if (P.L == 1) k_reduce_blocks<1><<<grid, kRedWarps * 32, RedCfg<1>::smem, st>>>(P, items, n_items, pl, partial, counters, next_item);
+  else k_reduce_blocks<3><<<grid, kRedWarps * 32, RedCfg<3>::smem, st>>>(P, items, n_items, pl, partial, counters, next_item);
 }
 
 }  // namespace bagpu

@@ -6,8 +6,8 @@
 // needs from the ids is derived there with a few sorts and scans instead of host loops over 10^7 residuals:
 //   * landmark-major order (stable radix sort by landmark id  ->  ties keep ascending residual ids, the order
 //     of `landmarks_[ii].proj_residuals`), CSR starts, gathered z / pose / cam / weight arrays
-//   * pose-major record slots (stable sort of the landmark-major stream by the measurement pose's opt id)
-//   * LmSize 1: reference-pose record slots of the landmarks
+//   * pose-major observation lists (stable sort of the landmark-major stream by the measurement pose's opt id)
+//   * LmSize 1: the landmarks referenced to every optimised pose
 //   * which poses own a residual (BundleAdjuster.h:490-497), the conditioning-residual count (cpp:698)
 //   * the tile pattern of S (which T x T tiles the pose pairs of any landmark touch)
 // The radix sort is CUB's (set-up code, outside the per-iteration hot path).
@@ -102,11 +102,23 @@ __global__ void k_slot_keys(const uint32_t* __restrict__ obs_pose, const uint32_
   keys[i] = k;
 }
 
-__global__ void k_assign_slots(const uint32_t* __restrict__ keys_sorted, const uint32_t* __restrict__ vals_sorted, uint32_t n, uint32_t n_ap,
-                               uint32_t* __restrict__ slot) {
+// the pose-major observation list: position j of the pose-sorted order -> observation index and its landmark
+__global__ void k_pose_lists(const uint32_t* __restrict__ vals_sorted, uint32_t n, const uint32_t* __restrict__ obs_lm,
+                             uint32_t* __restrict__ pose_obs, uint32_t* __restrict__ pose_obs_lm) {
   const uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
   if (j >= n) return;
-  slot[vals_sorted[j]] = keys_sorted[j] < n_ap ? j : kNoSlot;
+  const uint32_t i = vals_sorted[j];
+  pose_obs[j] = i; pose_obs_lm[j] = obs_lm[i];
+}
+
+// the landmark-major stream once more as 32-byte records {z, orig weight, pose, landmark} (ba_gpu.h: ObsRec)
+__global__ void k_obs_records(const double2* __restrict__ z, const double* __restrict__ w0, const uint32_t* __restrict__ pose,
+                              const uint32_t* __restrict__ lm, uint32_t n, ObsRec* __restrict__ out) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const double2 zz = z[i];
+  ObsRec r; r.zx = zz.x; r.zy = zz.y; r.w0 = w0[i]; r.pose = pose[i]; r.lm = lm[i];
+  out[i] = r;
 }
 
 __global__ void k_rslot_keys(const uint8_t* __restrict__ lm_any, const uint32_t* __restrict__ lm_ref_pose, const int* __restrict__ pose_opt,
@@ -212,8 +224,11 @@ void launch_slot_keys(const uint32_t* obs_pose, const uint32_t* obs_lm, uint32_t
                       uint32_t n_ap, uint32_t* keys, uint8_t* lm_any, cudaStream_t st) {
   if (n) k_slot_keys<<<blocks_for(n), 256, 0, st>>>(obs_pose, obs_lm, n, lm_ref_pose, pose_opt, n_ap, keys, lm_any);
 }
-void launch_assign_slots(const uint32_t* keys_sorted, const uint32_t* vals_sorted, uint32_t n, uint32_t n_ap, uint32_t* slot, cudaStream_t st) {
-  if (n) k_assign_slots<<<blocks_for(n), 256, 0, st>>>(keys_sorted, vals_sorted, n, n_ap, slot);
+void launch_pose_lists(const uint32_t* vals_sorted, uint32_t n, const uint32_t* obs_lm, uint32_t* pose_obs, uint32_t* pose_obs_lm, cudaStream_t st) {
+  if (n) k_pose_lists<<<blocks_for(n), 256, 0, st>>>(vals_sorted, n, obs_lm, pose_obs, pose_obs_lm);
+}
+void launch_obs_records(const double2* z, const double* w0, const uint32_t* pose, const uint32_t* lm, uint32_t n, ObsRec* out, cudaStream_t st) {
+  if (n) k_obs_records<<<blocks_for(n), 256, 0, st>>>(z, w0, pose, lm, n, out);
 }
 void launch_rslot_keys(const uint8_t* lm_any, const uint32_t* lm_ref_pose, const int* pose_opt, uint32_t n_lms, uint32_t n_ap, uint32_t* keys,
                        cudaStream_t st) {

@@ -19,12 +19,20 @@ namespace bagpu {
 
 namespace {
 
+// an observation takes part in the reduced system when its measurement pose is optimised and is not the landmark's
+// reference pose (parallel_algos.h:86-99: dz/dx_meas is zero there)
+__device__ __forceinline__ int part_opt(const DeviceProblem& P, int i, uint32_t ref_pose) {
+  const uint32_t m = P.obs_pose[i];
+  return (m == ref_pose) ? -1 : P.pose_opt[m];
+}
+
 __global__ void k_pair_count(DeviceProblem P, unsigned long long* count) {
   const int lm = blockIdx.x * blockDim.x + threadIdx.x;
   if (lm >= P.n_lms) return;
   const int s = P.lm_obs_start[lm], e = P.lm_obs_start[lm + 1];
+  const uint32_t rp = P.lm_ref_pose[lm];
   unsigned long long np = 0;
-  for (int i = s; i < e; ++i) np += (P.obs_slot[i] != kNoSlot);
+  for (int i = s; i < e; ++i) np += (part_opt(P, i, rp) >= 0);
   unsigned long long n = 0;
   if (P.lm_opt[lm] >= 0) n += np * (np - (np ? 1 : 0)) / 2;
   if (P.L == 1 && P.pose_opt[P.lm_ref_pose[lm]] >= 0) n += np;
@@ -39,11 +47,13 @@ __global__ void k_pair_emit(DeviceProblem P, const unsigned long long* __restric
   unsigned long long o = offs[lm];
   const unsigned long long np = (unsigned long long)P.n_active_poses;
   const bool lm_on = P.lm_opt[lm] >= 0;
-  const int ref_opt = (P.L == 1) ? P.pose_opt[P.lm_ref_pose[lm]] : -1;
+  const uint32_t rp = P.lm_ref_pose[lm];
+  const int ref_opt = (P.L == 1) ? P.pose_opt[rp] : -1;
   for (int i = s; i < e; ++i) {
-    const uint32_t sa = P.obs_slot[i];
-    if (sa == kNoSlot) continue;
-    const unsigned long long pa = (unsigned long long)P.pose_opt[P.obs_pose[i]];
+    const int oa = part_opt(P, i, rp);
+    if (oa < 0) continue;
+    const uint32_t sa = (uint32_t)i;
+    const unsigned long long pa = (unsigned long long)oa;
     if (ref_opt >= 0) {   // (measurement pose, reference pose) block of this observation
       const unsigned long long pr = (unsigned long long)ref_opt;
       const bool meas_row = pa < pr;
@@ -53,14 +63,26 @@ __global__ void k_pair_emit(DeviceProblem P, const unsigned long long* __restric
     }
     if (!lm_on) continue;
     for (int j = i + 1; j < e; ++j) {
-      const uint32_t sb = P.obs_slot[j];
-      if (sb == kNoSlot) continue;
-      const unsigned long long pb = (unsigned long long)P.pose_opt[P.obs_pose[j]];
+      const int ob = part_opt(P, j, rp);
+      if (ob < 0) continue;
+      const uint32_t sb = (uint32_t)j;
+      const unsigned long long pb = (unsigned long long)ob;
       if (pa <= pb) { keys[o] = (pa * np + pb) << 1; vals[o] = ((unsigned long long)sb << 32) | sa; }
       else { keys[o] = (pb * np + pa) << 1; vals[o] = ((unsigned long long)sa << 32) | sb; }
       ++o;
     }
   }
+}
+
+// sorted (first, second) entries -> three arrays: observation of the row pose, observation of the column pose (or the
+// tag of a measurement/reference entry), landmark
+__global__ void k_pair_split(const unsigned long long* __restrict__ v, size_t n, const uint32_t* __restrict__ obs_lm, uint32_t* __restrict__ a,
+                             uint32_t* __restrict__ b, uint32_t* __restrict__ lm) {
+  const size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const unsigned long long x = v[i];
+  const uint32_t lo = (uint32_t)x;
+  a[i] = lo; b[i] = (uint32_t)(x >> 32); lm[i] = obs_lm[lo];
 }
 
 #define SYM_CU(x)                                                                    \
@@ -71,9 +93,10 @@ __global__ void k_pair_emit(DeviceProblem P, const unsigned long long* __restric
 
 }  // namespace
 
-int build_pair_lists(const DeviceProblem& P, cudaStream_t st, uint2** pairs_out, size_t* n_pairs_out,
+int build_pair_lists(const DeviceProblem& P, cudaStream_t st, uint32_t** pairs_out, size_t* n_pairs_out,
                      std::vector<unsigned long long>& block_key, std::vector<uint32_t>& block_count, std::string& err) {
   *pairs_out = nullptr; *n_pairs_out = 0;
+  uint32_t* d_split = nullptr;
   block_key.clear(); block_count.clear();
   if (P.n_lms == 0 || P.n_obs == 0 || P.n_active_poses == 0) return 0;
   typedef unsigned long long u64;
@@ -116,12 +139,15 @@ int build_pair_lists(const DeviceProblem& P, cudaStream_t st, uint2** pairs_out,
   SYM_CU(cudaMemcpyAsync(block_key.data(), d_unique, sizeof(u64) * n_runs, cudaMemcpyDeviceToHost, st));
   SYM_CU(cudaMemcpyAsync(block_count.data(), d_runs, sizeof(uint32_t) * n_runs, cudaMemcpyDeviceToHost, st));
   SYM_CU(cudaStreamSynchronize(st));
-  *pairs_out = reinterpret_cast<uint2*>(d_vals2); d_vals2 = nullptr;   // ownership moves to the caller
+  SYM_CU(dev_alloc((void**)&d_split, sizeof(uint32_t) * 3 * total));
+  k_pair_split<<<(unsigned)((total + 255) / 256), 256, 0, st>>>(d_vals2, (size_t)total, P.obs_lm, d_split, d_split + total, d_split + 2 * total);
+  SYM_CU(cudaStreamSynchronize(st));
+  *pairs_out = d_split; d_split = nullptr;   // ownership moves to the caller: [a (total) | b (total) | lm (total)]
   *n_pairs_out = (size_t)total;
   rc = 0;
 done:
   dev_free(d_count); dev_free(d_offs); dev_free(d_keys); dev_free(d_vals); dev_free(d_keys2); dev_free(d_vals2);
-  dev_free(d_nruns); dev_free(d_tmp);
+  dev_free(d_nruns); dev_free(d_tmp); dev_free(d_split);
   return rc;
 }
 
