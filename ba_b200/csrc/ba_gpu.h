@@ -6,21 +6,22 @@
 //                (replaces the PoseT::t_sw cache, reference include/ba/Types.h:59-70)
 //   landmarks    x[4N] (x_s for LmSize 1, x_w for LmSize 3), ref pose/cam, opt id, reliable flag
 //   observations sorted by landmark id, ties by residual id: z[2] (double2), meas pose (u32),
-//                cam (u32), orig weight; CSR lm_obs_start[N+1]; perm[] back to residual ids;
-//                the same stream once more as 32-byte records {z, orig weight, pose, landmark} (ObsRec)
-//                for the pose-pair-major pass, which gathers single observations
+//                cam (u32), orig weight; CSR lm_obs_start[N+1]; perm[] back to residual ids
 //   per-obs      maha0 (median input), weight (Huber)
-//   per-landmark record of the current linearisation (LmRec, 128 bytes, rewritten by k_linearize every build):
-//                  LmSize 3: X (3) | rho | V^-1 upper (6) | dhat = V^-1 b_l (3)
-//                  LmSize 1: X world (3) | rho | t_ws of the reference frame (3) | V^-1 | dhat | ray x_s (3) |
-//                            SBl = sum w Bp^T J_l (3)
-//                and, LmSize 1 only, 96 bytes more (LmRecC): SBB = sum w Bp^T Bp upper (6) | SBr = sum w Bp^T r (3),
-//                the sums over the landmark's observations from which the reference pose's blocks follow
-//                (Bp = d project / d X_world, see proj_kernels.cuh)
+//   linearisation (rewritten by k_linearize every build).  With B = d project / d X_world (2 x 3) every projection
+//   Jacobian factors as  d z / d x_pose = B K_pose,  d z / d landmark = -B (LmSize 3) or -B u (LmSize 1, u = baseline
+//   between the reference and the measuring sensor),  d z / d x_ref = -B K_ref,  K_p(X, rho) = [rho I | -[X - rho t_wp]x] D_p,
+//   D_p = blkdiag(I, R_wp) with the masked parameter columns zeroed.  So an observation enters EVERY block of the
+//   reduced system only through
+//     per observation  G = w B^T B (3 x 3 symmetric, 6 doubles in a 64-byte record, obs_G) and h = w B^T r (32-byte record, obs_h)
+//     per landmark     LmRec (128 bytes): LmSize 3: X (3) | rho | V^-1 upper (6) | dhat = V^-1 b_l (3)
+//                                         LmSize 1: X (3) | rho | t_ws of the reference sensor (3) | V^-1 | dhat | gbar = sum G u (3)
+//                      LmSize 1 only, LmRecC (96 bytes): Gbar = sum G (6) | hbar = sum h (3), over the observations the
+//                      reference pose takes part in
+//   and each S block is a sum of  K~_i^T M_e K~_j  over its list entries, M_e a 3 x 3 built from those records
+//   (schur_kernels.cu); D_i^T . D_j is applied once per block.  No Jacobian is stored and none is re-evaluated.
 //   pose-major   pose_obs: the observation indices (landmark-major positions) of every optimised pose, and for
-//                LmSize 1 pose_lms: the landmarks referenced to every optimised pose.  NO Jacobians, products or
-//                per-observation records are stored: the pose-pair pass recomputes both Jacobians of a pair from
-//                two ObsRec + one LmRec (5 sectors) against pose frames that are uniform over the warp.
+//                LmSize 1 pose_lms: the landmarks referenced to every optimised pose.
 //   reduced S    upper block-tile storage: tiles of T x T doubles (T = 8 poses x PoseSize),
 //                column-major inside a tile, tile_map[tI * nT + tJ] -> tile slot or -1
 #pragma once
@@ -33,7 +34,7 @@ namespace bagpu {
 constexpr int kTilePoses = 8;   // poses per S tile
 constexpr uint32_t kNoSlot = 0xffffffffu;
 constexpr int kLmRec = 16, kLmRecC = 12;   // doubles per landmark record (128 B) / LmSize-1 extension (96 B)
-struct __align__(32) ObsRec { double zx, zy, w0; uint32_t pose, lm; };
+constexpr int kObsG = 8, kObsH = 4;         // doubles per observation record: G (6 + 2 pad, 64 B), h (3 + 1 pad, 32 B)
 
 struct Scalars {       // device-resident scalar block (one per handle)
   double median;       // nth_element value of maha0
@@ -82,7 +83,8 @@ struct DeviceProblem {
   const uint32_t* obs_lm;    // sorted index -> landmark id (non-decreasing)
   double* obs_maha0;
   double* obs_w;
-  const ObsRec* obs_rec;     // the same stream as 32-byte records (pose-pair pass)
+  double* obs_G;             // kObsG doubles per observation: w B^T B upper (00 01 02 11 12 22)
+  double* obs_h;             // kObsH doubles per observation: w B^T r
   const uint32_t* pose_obs;  // observation indices grouped by optimised measurement pose (pose-major), n_pose_obs entries
   const uint32_t* pose_obs_lm;  // landmark of pose_obs[k]
   const uint32_t* pose_lms;  // L == 1: landmark ids grouped by optimised reference pose

@@ -272,14 +272,14 @@ struct bagpu_handle_s {
   // ---- device buffers ----
   DevBuf<double> d_cam_params, d_cam_Rvs, d_cam_tvs;
   DevBuf<double> d_pose_q, d_pose_t, d_pose_v, d_pose_b, d_Tsw, d_Tws, d_Rwp;
-  DevBuf<double> d_bk_q, d_bk_t, d_bk_v, d_bk_b, d_bk_lm_x; DevBuf<uint8_t> d_bk_rel;
+  DevBuf<double> d_bk_q, d_bk_t, d_bk_v, d_bk_b, d_bk_lm_x; DevBuf<uint8_t> d_bk_rel; DevBuf<uint32_t> d_bk_outliers;
   DevBuf<int> d_pose_opt, d_lm_opt; DevBuf<uint32_t> d_pose_free; DevBuf<uint8_t> d_pose_mask_used;
   DevBuf<double> d_lm_x, d_lm_xw; DevBuf<uint32_t> d_lm_ref_pose, d_lm_ref_cam, d_lm_outliers, d_lm_obs_start;
   DevBuf<uint8_t> d_lm_reliable;
   DevBuf<double2> d_raw_z; DevBuf<uint32_t> d_raw_pose, d_raw_lm, d_raw_cam; DevBuf<double> d_raw_w0;   // residual-id order, as set
   DevBuf<uint32_t> d_sorted_lm, d_perm_global, d_gstarts;   // landmark-major: landmark id, residual id, CSR starts (all ranks' observations)
   DevBuf<double2> d_obs_z; DevBuf<uint32_t> d_obs_pose, d_obs_cam; DevBuf<double> d_obs_w0, d_obs_maha0, d_obs_w;
-  DevBuf<uint32_t> d_pose_obs, d_pose_obs_lm, d_pose_lms; DevBuf<ObsRec> d_obs_rec; DevBuf<int> d_opt_to_pose;
+  DevBuf<uint32_t> d_pose_obs, d_pose_obs_lm, d_pose_lms; DevBuf<double> d_obs_G, d_obs_h; DevBuf<int> d_opt_to_pose;
   DevBuf<double> d_lm_rec, d_lm_recC, d_partial, d_red_partial; DevBuf<unsigned int> d_counters, d_red_counter;
   DevBuf<ReduceItem> d_items, d_items_sym;
   DevBuf<double> d_lm_bl;
@@ -315,7 +315,9 @@ struct bagpu_handle_s {
   int rank = 0, world = 1;
 
   // =======================================================================================
-  void sync() { CU(cudaStreamSynchronize(st)); }
+  // every phase ends here: execution faults come back from the synchronise, launch-configuration errors (too much
+  // shared memory, an empty grid, ...) of any launch since the last call from cudaGetLastError
+  void sync() { CU(cudaStreamSynchronize(st)); CU(cudaGetLastError()); }
 
   void ensure_device() {
     if (has_device) return;
@@ -443,7 +445,7 @@ struct bagpu_handle_s {
     }
     // 4. the local stream: gathered values, pose-major record slots
     const uint32_t nl = (uint32_t)n_obs;
-    d_obs_z.alloc(nl); d_obs_pose.alloc(nl); d_obs_w0.alloc(nl); d_obs_rec.alloc(nl);
+    d_obs_z.alloc(nl); d_obs_pose.alloc(nl); d_obs_w0.alloc(nl); d_obs_G.alloc((size_t)nl * kObsG); d_obs_h.alloc((size_t)nl * kObsH);
     if (n_cams > 1) d_obs_cam.alloc(nl);
     launch_gather_obs(d_perm_global.p + s_lo, nl, d_raw_z.p, d_raw_pose.p, raw_has_cam ? d_raw_cam.p : nullptr, raw_has_w0 ? d_raw_w0.p : nullptr,
                       d_obs_z.p, d_obs_pose.p, n_cams > 1 ? d_obs_cam.p : nullptr, d_obs_w0.p, nullptr, st);
@@ -454,7 +456,6 @@ struct bagpu_handle_s {
       d_any.alloc((size_t)n_lms); d_any.zero(st);
       launch_slot_keys(d_obs_pose.p, d_sorted_lm.p + s_lo, nl, d_lm_ref_pose.p, d_pose_opt.p, (uint32_t)n_ap, d_keys.p, d_any.p, st);
       if (sort_positions_by_key(d_keys.p, d_keys_s.p, d_vals_s.p, nl, (uint32_t)n_ap, st, err)) throw err;
-      launch_obs_records(d_obs_z.p, d_obs_w0.p, d_obs_pose.p, d_sorted_lm.p + s_lo, nl, d_obs_rec.p, st);
       launch_key_starts(d_keys_s.p, nl, (uint32_t)n_ap, d_starts.p, st);
       d_starts.download(pose_rec_start.data(), (size_t)n_ap + 1, st);
       sync();
@@ -625,7 +626,7 @@ struct bagpu_handle_s {
       if (n_lm_set) CU(cudaMemsetAsync(d_lm_reliable.p, 1, n_lm_set, st));
       lm_rel_on_device = true;
     }
-    d_bk_rel.alloc(n_lm_set); d_lm_outliers.alloc(n_lms);
+    d_bk_rel.alloc(n_lm_set); d_lm_outliers.alloc(n_lms); d_bk_outliers.alloc(n_lms);
     d_lm_outliers.zero(st);
     pc.lap("  upload: cameras, poses, landmarks");
     // observations: landmark-major stream, record slots and the tile pattern, derived on the device
@@ -689,7 +690,7 @@ struct bagpu_handle_s {
     P.obs_z = d_obs_z.p; P.obs_pose = d_obs_pose.p; P.obs_cam = multi_cam ? d_obs_cam.p : nullptr; P.obs_w0 = d_obs_w0.p; P.obs_perm = d_perm_global.p ? d_perm_global.p + s_lo : nullptr;
     P.obs_lm = d_sorted_lm.p ? d_sorted_lm.p + s_lo : nullptr;
     P.obs_maha0 = d_obs_maha0.p; P.obs_w = d_obs_w.p;
-    P.obs_rec = d_obs_rec.p; P.pose_obs = d_pose_obs.p; P.pose_obs_lm = d_pose_obs_lm.p; P.pose_lms = d_pose_lms.p; P.opt_to_pose = d_opt_to_pose.p;
+    P.obs_G = d_obs_G.p; P.obs_h = d_obs_h.p; P.pose_obs = d_pose_obs.p; P.pose_obs_lm = d_pose_obs_lm.p; P.pose_lms = d_pose_lms.p; P.opt_to_pose = d_opt_to_pose.p;
     P.lm_rec = d_lm_rec.p; P.lm_recC = (L == 1) ? d_lm_recC.p : nullptr; P.lm_bl = d_lm_bl.p;
     P.red_partial = d_red_partial.p; P.red_counter = d_red_counter.p;
     P.cam_identity = 1;
@@ -807,12 +808,14 @@ struct bagpu_handle_s {
   }
 
   // ---- median of maha0 (exact) -------------------------------------------------------------
-  void run_select(const double* x, size_t n_local, unsigned long long n_total, double* out) {
+  // `distributed`: x is one rank's shard of n_total values (histograms summed over ranks); false: x is the whole,
+  // replicated list and no collective is issued (unary residuals, evaluated on rank 0 only)
+  void run_select(const double* x, size_t n_local, unsigned long long n_total, double* out, bool distributed = true) {
     if (n_total == 0) return;
     launch_select_init(d_sel.p, n_total / 2, st); ++launches;
     for (int pass = 0; pass < select_num_passes(); ++pass) {
       launch_select_hist(x, n_local, d_sel.p, pass, sms, st); ++launches;
-      if (world > 1) allreduce_u32(d_sel.p->hist, 4096);
+      if (world > 1 && distributed) allreduce_u32(d_sel.p->hist, 4096);
       launch_select_scan(d_sel.p, pass, out, st); ++launches;
     }
   }
@@ -850,7 +853,7 @@ struct bagpu_handle_s {
     if (rank == 0) {   // replicated residuals are added once
       if (R.n_unary) {
         launch_unary_maha(P, R, st); ++launches;
-        run_select(d_un_maha.p, R.n_unary, R.n_unary, &d_sc.p->unary_median);
+        run_select(d_un_maha.p, R.n_unary, R.n_unary, &d_sc.p->unary_median, false);
       }
       launch_other_build(P, R, st, &launches);
     }
@@ -934,6 +937,7 @@ struct bagpu_handle_s {
     if (n_lms) {
       CU(cudaMemcpyAsync(d_bk_lm_x.p, d_lm_x.p, sizeof(double) * 4 * n_lms, cudaMemcpyDeviceToDevice, st));
       CU(cudaMemcpyAsync(d_bk_rel.p, d_lm_reliable.p, n_lms, cudaMemcpyDeviceToDevice, st));
+      CU(cudaMemcpyAsync(d_bk_outliers.p, d_lm_outliers.p, sizeof(uint32_t) * n_lms, cudaMemcpyDeviceToDevice, st));   // landmarks_copy carries num_outlier_residuals (cpp:1022,1062)
     }
   }
   void restore_state() {
@@ -944,6 +948,7 @@ struct bagpu_handle_s {
     if (n_lms) {
       CU(cudaMemcpyAsync(d_lm_x.p, d_bk_lm_x.p, sizeof(double) * 4 * n_lms, cudaMemcpyDeviceToDevice, st));
       CU(cudaMemcpyAsync(d_lm_reliable.p, d_bk_rel.p, n_lms, cudaMemcpyDeviceToDevice, st));
+      CU(cudaMemcpyAsync(d_lm_outliers.p, d_bk_outliers.p, sizeof(uint32_t) * n_lms, cudaMemcpyDeviceToDevice, st));
     }
     launch_pose_frames(P, st); ++launches;
   }
@@ -1079,7 +1084,7 @@ struct bagpu_handle_s {
         // "pre" evaluation: same state and weights as the build, so the build sums are reused;
         // only the binary error uses a different formula in EvaluateResiduals (quirk Q7).
         double pre_bin = 0;
-        if (R.n_binary && rank == 0) {
+        if (R.n_binary) {   // on every rank (binary residuals are replicated): all ranks must take the same accept / reject branch
           CU(cudaMemsetAsync(&d_sc.p->eval_binary, 0, sizeof(double), st));
           OtherResiduals Rb = R; Rb.n_unary = 0; Rb.n_imu = 0;
           launch_other_evaluate(P, Rb, st, &launches);
@@ -1163,6 +1168,14 @@ struct bagpu_handle_s {
         if (lm_owner_lo > 0) CU(cudaMemsetAsync(d_lm_x.p, 0, sizeof(double) * 4 * (size_t)lm_owner_lo, st));
         if (lm_owner_hi < n_lms) CU(cudaMemsetAsync(d_lm_x.p + 4 * (size_t)lm_owner_hi, 0, sizeof(double) * 4 * (size_t)(n_lms - lm_owner_hi), st));
         allreduce_f64(d_lm_x.p, 4 * (size_t)n_lms);
+        // reliable flags (set by the owner's ApplyUpdate, cpp:127-134) and outlier counts (counted over the owner's
+        // observations, cpp:184-186): AND / sum over ranks, so every rank reports what a single GPU would
+        DevBuf<unsigned int> d_unrel; d_unrel.alloc((size_t)n_lms);
+        launch_reliable_merge(d_lm_reliable.p, d_unrel.p, (uint32_t)n_lms, 0, st); ++launches;
+        allreduce_u32(d_unrel.p, (size_t)n_lms);
+        launch_reliable_merge(d_lm_reliable.p, d_unrel.p, (uint32_t)n_lms, 1, st); ++launches;
+        allreduce_u32(d_lm_outliers.p, (size_t)n_lms);
+        sync();   // d_unrel goes out of scope
       }
       if (L == 1) { launch_finish_xw(P, d_lm_xw.p, st); ++launches; }
       else CU(cudaMemcpyAsync(d_lm_xw.p, d_lm_x.p, sizeof(double) * 4 * n_lms, cudaMemcpyDeviceToDevice, st));
@@ -1296,6 +1309,8 @@ extern "C" {
   try { __VA_ARGS__ } catch (const std::string& e) {                              \
     const bool nodev = e.find("no CUDA device") != std::string::npos;             \
     return fail(nodev ? BAGPU_ERR_NO_DEVICE : BAGPU_ERR_CUDA, e);                 \
+  } catch (const std::exception& e) {   /* bad_alloc, system_error: never across the C boundary */ \
+    return fail(BAGPU_ERR_CUDA, std::string("host exception: ") + e.what());      \
   }
 
 const char* bagpu_last_error(void) { return g_err.c_str(); }
@@ -1686,8 +1701,12 @@ int bagpu_get_system(bagpu_handle h, double* s_dense, double* rhs_sc, double* rh
 
 int bagpu_dump(bagpu_handle h, const char* dir) {
   // s.txt / rhs.txt with Eigen's FullPrecision ", " separated rows (reference Utils.h:66, cpp:604-605)
+  if (!h) return fail(BAGPU_ERR_INVALID, "null handle");
   const int n = h->n_ap * h->D;
-  std::vector<double> s((size_t)n * n), r(n);
+  // the reference writes the dense (P d)^2 matrix as text (cpp:604): refuse sizes nobody can hold or read (C4 = 28.8 GB)
+  if ((size_t)n * n > ((size_t)1 << 28)) return fail(BAGPU_ERR_UNSUPPORTED, "dense s.txt dump refused above 2 GB (use bagpu_get_pattern / the tile storage)");
+  std::vector<double> s, r;
+  try { s.resize((size_t)n * n); r.resize(n); } catch (const std::exception&) { return fail(BAGPU_ERR_INVALID, "out of host memory for the dense dump"); }
   int rc = bagpu_get_system(h, s.data(), r.data(), nullptr, nullptr, nullptr);
   if (rc) return rc;
   const std::string d = dir ? dir : ".";

@@ -7,8 +7,9 @@
 namespace bagpu {
 namespace {
 std::mutex g_mu;
-std::unordered_map<void*, size_t> g_live;          // blocks handed out -> rounded size
-std::multimap<size_t, void*> g_free;               // cached blocks by size
+struct Live { size_t size; int dev; };
+std::unordered_map<void*, Live> g_live;            // blocks handed out -> rounded size, owning device
+std::multimap<std::pair<int, size_t>, void*> g_free;   // cached blocks by (device, size): a block never changes GPUs
 size_t g_cached = 0;
 constexpr size_t kBudget = (size_t)24 << 30;       // cached (unused) bytes kept at most
 
@@ -27,11 +28,13 @@ void trim_locked() {
 cudaError_t dev_alloc(void** p, size_t bytes) {
   const size_t sz = round_up(bytes);
   std::lock_guard<std::mutex> g(g_mu);
-  auto it = g_free.lower_bound(sz);
-  if (it != g_free.end() && it->first <= sz + sz / 4) {
+  int dev = 0;
+  cudaGetDevice(&dev);
+  auto it = g_free.lower_bound(std::make_pair(dev, sz));
+  if (it != g_free.end() && it->first.first == dev && it->first.second <= sz + sz / 4) {
     *p = it->second;
-    g_live[*p] = it->first;
-    g_cached -= it->first;
+    g_live[*p] = Live{it->first.second, dev};
+    g_cached -= it->first.second;
     g_free.erase(it);
     return cudaSuccess;
   }
@@ -43,7 +46,7 @@ cudaError_t dev_alloc(void** p, size_t bytes) {
     e = cudaMalloc(p, sz);
     if (e != cudaSuccess) return e;
   }
-  g_live[*p] = sz;
+  g_live[*p] = Live{sz, dev};
   return cudaSuccess;
 }
 
@@ -53,9 +56,10 @@ void dev_free(void* p) {
   std::lock_guard<std::mutex> g(g_mu);
   auto it = g_live.find(p);
   if (it == g_live.end()) { cudaFree(p); return; }
-  const size_t sz = it->second;
+  const size_t sz = it->second.size;
+  const int dev = it->second.dev;
   g_live.erase(it);
-  g_free.emplace(sz, p);
+  g_free.emplace(std::make_pair(dev, sz), p);
   g_cached += sz;
   if (g_cached > kBudget) trim_locked();
 }

@@ -70,7 +70,6 @@ void launch_local_starts(const uint32_t* gstarts, uint32_t n_lms, uint32_t s_lo,
 void launch_slot_keys(const uint32_t* obs_pose, const uint32_t* obs_lm, uint32_t n, const uint32_t* lm_ref_pose, const int* pose_opt,
                       uint32_t n_ap, uint32_t* keys, uint8_t* lm_any, cudaStream_t st);
 void launch_pose_lists(const uint32_t* vals_sorted, uint32_t n, const uint32_t* obs_lm, uint32_t* pose_obs, uint32_t* pose_obs_lm, cudaStream_t st);
-void launch_obs_records(const double2* z, const double* w0, const uint32_t* pose, const uint32_t* lm, uint32_t n, ObsRec* out, cudaStream_t st);
 void launch_rslot_keys(const uint8_t* lm_any, const uint32_t* lm_ref_pose, const int* pose_opt, uint32_t n_lms, uint32_t n_ap, uint32_t* keys,
                        cudaStream_t st);
 // dense nT x nT tile table (-1 = structurally empty) from the CSR rows: tiles numbered row by row, diagonal tile first
@@ -80,6 +79,7 @@ void launch_tile_pattern(const uint32_t* starts, const uint32_t* perm, const uin
 void launch_cond_error(const uint32_t* obs_pose, const uint32_t* obs_lm, const uint32_t* obs_perm, uint32_t n, const uint32_t* lm_ref_pose,
                        const int* pose_opt, const double* maha_by_id, const double* w, double* out, cudaStream_t st);
 void launch_scatter_by_perm(const uint32_t* perm, const double* in, uint32_t n, double* out, cudaStream_t st);
+void launch_reliable_merge(uint8_t* rel, unsigned int* unrel, uint32_t n, int phase, cudaStream_t st);
 
 void set_sm_count(int n);
 void launch_pose_frames(const DeviceProblem& P, cudaStream_t st);

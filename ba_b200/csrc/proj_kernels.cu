@@ -139,19 +139,21 @@ BA_D void back_finish(const DeviceProblem& P, int lm, int lo, const double* delt
   if (L == 1) {
     const int rp = (int)P.lm_ref_pose[lm];
     const int ro = P.pose_opt[rp];
-    if (ro >= 0) {   // W_ref^T delta = SBl^T (M delta)
-      double M[18];
-      ref_M(P, rp, P.n_cams > 1 ? (int)P.lm_ref_cam[lm] : 0, r[3], r + 9, M);
+    if (ro >= 0) {   // W_ref^T delta = gbar^T K_ref delta,  K_ref delta = rho x_t - Y x x_w,  x = D delta (ba_gpu.h)
       const double* dp = delta_p + (size_t)ro * P.D;
-      double t = 0.0;
+      const uint32_t fr = P.pose_free[rp];
+      double x[6];
 #pragma unroll
-      for (int j = 0; j < 3; ++j) {
-        double mj = 0.0;
-#pragma unroll
-        for (int a = 0; a < 6; ++a) mj += M[6 * j + a] * dp[a];
-        t += r[12 + j] * mj;
-      }
-      acc[0] += t;
+      for (int a = 0; a < 6; ++a) x[a] = ((fr >> a) & 1u) ? dp[a] : 0.0;
+      double xw[3];
+      mat3_vec(P.Rwp + 9 * (size_t)rp, x + 3, xw);
+      const double* tp = P.pose_t + 3 * (size_t)rp;
+      const double rho = r[3];
+      const double Y[3] = {r[0] - rho * tp[0], r[1] - rho * tp[1], r[2] - rho * tp[2]};
+      const double k0 = rho * x[0] - (Y[1] * xw[2] - Y[2] * xw[1]);
+      const double k1 = rho * x[1] - (Y[2] * xw[0] - Y[0] * xw[2]);
+      const double k2 = rho * x[2] - (Y[0] * xw[1] - Y[1] * xw[0]);
+      acc[0] += r[9] * k0 + r[10] * k1 + r[11] * k2;
     }
     delta_l[lo] = r[8] - r[7] * acc[0];
   } else {

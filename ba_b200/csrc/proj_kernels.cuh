@@ -197,95 +197,111 @@ BA_D double huber_weight(double maha0, double w0, double c_huber, double c2, int
   return w0;
 }
 
-// One side of a pose pair, re-evaluated from the staged landmark record `lm` (X | rho | LmSize 1: t_ws of the
-// reference frame), the observation (z, orig weight) and the frame of pose m, which is the same for every lane of
-// the warp (uniform, L1-resident loads).  Same closed forms as obs_jacobians.
+// Linearisation of one observation for the Schur build (ba_gpu.h): B = d project / d X_world = Jp R_sw, the Huber
+// weight, G = w B^T B, h = w B^T r and, LmSize 1, j = B u = -d z / d rho (u = baseline reference sensor -> measuring
+// sensor; B u = B t_ws_ref + Jp t_sw without forming u).
 template <int L>
-struct Side {
-  double Jm[12];            // d z / d x_meas, 2 x 6, masked parameter columns zeroed
-  double B[6];              // d project / d X_world = Jp R_sw, 2 x 3  (LmSize 3: J_l = -B)
-  double jl[2];             // LmSize 1: d z / d rho
-  double r[2];
-  double w;                 // Huber weight
+struct ObsLin {
+  double G[6];      // upper: 00 01 02 11 12 22
+  double h[3];
+  double j[2];      // LmSize 1: B u
+  double gj[3];     // LmSize 1: G u = w B^T j
+  double wjr;       // LmSize 1: u^T h = w j.r
+  double w, n2;     // Huber weight, |r|^2
+  bool pm_on;       // measurement pose takes part (optimised, not the landmark's reference pose)
+  bool ref_on;      // reference pose takes part (LmSize 1, optimised, diff_poses)
 };
 template <int L>
-BA_D void side_eval(const DeviceProblem& P, const double* __restrict__ lm, double zx, double zy, double w0, int m, int cam, double c_huber,
-                    double c2, Side<L>& s) {
+BA_D void obs_linearize(const DeviceProblem& P, const LmCtx<L>& c, int obs, int m, double c_huber, double c2, ObsLin<L>& o) {
+  const int cam = P.obs_cam ? (int)P.obs_cam[obs] : 0;
   double T[12];
   load_frame(P.Tsw + ((size_t)m * P.n_cams + cam) * 12, T);
-  const double X0 = lm[0], X1 = lm[1], X2 = lm[2], rho = lm[3];
-  const double Xs0 = T[0] * X0 + T[1] * X1 + T[2] * X2 + rho * T[9];
-  const double Xs1 = T[3] * X0 + T[4] * X1 + T[5] * X2 + rho * T[10];
-  const double Xs2 = T[6] * X0 + T[7] * X1 + T[8] * X2 + rho * T[11];
+  const double Xs0 = T[0] * c.X[0] + T[1] * c.X[1] + T[2] * c.X[2] + c.rho * T[9];
+  const double Xs1 = T[3] * c.X[0] + T[4] * c.X[1] + T[5] * c.X[2] + c.rho * T[10];
+  const double Xs2 = T[6] * c.X[0] + T[7] * c.X[1] + T[8] * c.X[2] + c.rho * T[11];
   const double2 k01 = reinterpret_cast<const double2*>(P.cam_params + 4 * cam)[0], k23 = reinterpret_cast<const double2*>(P.cam_params + 4 * cam)[1];
   const double iz = 1.0 / Xs2;
-  s.r[0] = zx - (k01.x * Xs0 * iz + k23.x);
-  s.r[1] = zy - (k01.y * Xs1 * iz + k23.y);
+  const double2 z = P.obs_z[obs];
+  const double r0 = z.x - (k01.x * Xs0 * iz + k23.x), r1 = z.y - (k01.y * Xs1 * iz + k23.y);
   const double a = k01.x * iz, b = k01.y * iz;
   const double j02 = -a * Xs0 * iz, j12 = -b * Xs1 * iz;
+  double B[6];
 #pragma unroll
-  for (int cc = 0; cc < 3; ++cc) {
-    s.B[cc] = a * T[cc] + j02 * T[6 + cc];
-    s.B[3 + cc] = b * T[3 + cc] + j12 * T[6 + cc];
-  }
+  for (int cc = 0; cc < 3; ++cc) { B[cc] = a * T[cc] + j02 * T[6 + cc]; B[3 + cc] = b * T[3 + cc] + j12 * T[6 + cc]; }
   if (L == 1) {
-    s.jl[0] = -(s.B[0] * lm[4] + s.B[1] * lm[5] + s.B[2] * lm[6] + a * T[9] + j02 * T[11]);
-    s.jl[1] = -(s.B[3] * lm[4] + s.B[4] * lm[5] + s.B[5] * lm[6] + b * T[10] + j12 * T[11]);
+    o.j[0] = B[0] * c.tws_r[0] + B[1] * c.tws_r[1] + B[2] * c.tws_r[2] + a * T[9] + j02 * T[11];
+    o.j[1] = B[3] * c.tws_r[0] + B[4] * c.tws_r[1] + B[5] * c.tws_r[2] + b * T[10] + j12 * T[11];
   }
-  double Xv0 = Xs0, Xv1 = Xs1, Xv2 = Xs2;
-  double C[6] = {a, 0.0, j02, 0.0, b, j12};      // Jp R_vs^T
-  if (!P.cam_identity) {
-    const double* Rvs = P.cam_Rvs + 9 * cam;
-    const double* tvs = P.cam_tvs + 3 * cam;
-    Xv0 = Rvs[0] * Xs0 + Rvs[1] * Xs1 + Rvs[2] * Xs2 + rho * tvs[0];
-    Xv1 = Rvs[3] * Xs0 + Rvs[4] * Xs1 + Rvs[5] * Xs2 + rho * tvs[1];
-    Xv2 = Rvs[6] * Xs0 + Rvs[7] * Xs1 + Rvs[8] * Xs2 + rho * tvs[2];
-#pragma unroll
-    for (int cc = 0; cc < 3; ++cc) {
-      C[cc] = a * Rvs[3 * cc] + j02 * Rvs[3 * cc + 2];
-      C[3 + cc] = b * Rvs[3 * cc + 1] + j12 * Rvs[3 * cc + 2];
-    }
+  const double w0 = P.obs_w0[obs];
+  o.n2 = r0 * r0 + r1 * r1;
+  o.w = huber_weight(o.n2 * w0, w0, c_huber, c2, P.use_robust);
+  const double wb0 = o.w * B[0], wb1 = o.w * B[1], wb2 = o.w * B[2], wb3 = o.w * B[3], wb4 = o.w * B[4], wb5 = o.w * B[5];
+  o.G[0] = wb0 * B[0] + wb3 * B[3]; o.G[1] = wb0 * B[1] + wb3 * B[4]; o.G[2] = wb0 * B[2] + wb3 * B[5];
+  o.G[3] = wb1 * B[1] + wb4 * B[4]; o.G[4] = wb1 * B[2] + wb4 * B[5]; o.G[5] = wb2 * B[2] + wb5 * B[5];
+  o.h[0] = wb0 * r0 + wb3 * r1; o.h[1] = wb1 * r0 + wb4 * r1; o.h[2] = wb2 * r0 + wb5 * r1;
+  if (L == 1) {
+    o.gj[0] = wb0 * o.j[0] + wb3 * o.j[1]; o.gj[1] = wb1 * o.j[0] + wb4 * o.j[1]; o.gj[2] = wb2 * o.j[0] + wb5 * o.j[1];
+    o.wjr = o.w * (o.j[0] * r0 + o.j[1] * r1);
   }
-#pragma unroll
-  for (int rr = 0; rr < 2; ++rr) {
-    const double* Cr = C + 3 * rr;
-    s.Jm[6 * rr + 0] = rho * s.B[3 * rr + 0];
-    s.Jm[6 * rr + 1] = rho * s.B[3 * rr + 1];
-    s.Jm[6 * rr + 2] = rho * s.B[3 * rr + 2];
-    s.Jm[6 * rr + 3] = -(Cr[1] * Xv2 - Cr[2] * Xv1);
-    s.Jm[6 * rr + 4] = -(-Cr[0] * Xv2 + Cr[2] * Xv0);
-    s.Jm[6 * rr + 5] = -(Cr[0] * Xv1 - Cr[1] * Xv0);
-  }
-  const uint32_t fr = P.pose_free[m];
-  if ((fr & 63u) != 63u) {
-#pragma unroll
-    for (int k = 0; k < 6; ++k)
-      if (!((fr >> k) & 1u)) { s.Jm[k] = 0.0; s.Jm[6 + k] = 0.0; }
-  }
-  const double n2 = s.r[0] * s.r[0] + s.r[1] * s.r[1];
-  s.w = huber_weight(n2 * w0, w0, c_huber, c2, P.use_robust);
+  const bool diff = (m != c.ref_pose);
+  o.pm_on = diff && P.pose_opt[m] >= 0;
+  o.ref_on = (L == 1) && diff && c.ref_opt >= 0;
 }
 
-// M = [-rho I | R_wp_r [Y]x] (3 x 6, masked parameter columns zeroed), Y = R_vs ray + rho t_vs: the reference-pose
-// Jacobian of an observation of the landmark is Bp M (proj_kernels.cuh, ref_jacobian)
-BA_D void ref_M(const DeviceProblem& P, int ref_pose, int ref_cam, double rho, const double* ray, double* M) {
-  double Y[3] = {ray[0], ray[1], ray[2]};
-  if (!P.cam_identity) {
-    mat3_vec(P.cam_Rvs + 9 * ref_cam, ray, Y);
-    Y[0] += rho * P.cam_tvs[3 * ref_cam]; Y[1] += rho * P.cam_tvs[3 * ref_cam + 1]; Y[2] += rho * P.cam_tvs[3 * ref_cam + 2];
+// ---- K~^T M K~ products: K~(Y) = [rho I | -[Y]x] (3 x 6), Y = X - rho t_wp ----------------------------------------
+// symmetric 3 x 3 (upper 00 01 02 11 12 22) times vector
+BA_D void sym3_vec(const double* G, const double* v, double* o) {
+  o[0] = G[0] * v[0] + G[1] * v[1] + G[2] * v[2];
+  o[1] = G[1] * v[0] + G[3] * v[1] + G[4] * v[2];
+  o[2] = G[2] * v[0] + G[4] * v[1] + G[5] * v[2];
+}
+// p = K~^T g = [rho g ; Y x g]
+BA_D void kt_vec(double rho, const double* Y, const double* g, double* p) {
+  p[0] = rho * g[0]; p[1] = rho * g[1]; p[2] = rho * g[2];
+  p[3] = Y[1] * g[2] - Y[2] * g[1]; p[4] = Y[2] * g[0] - Y[0] * g[2]; p[5] = Y[0] * g[1] - Y[1] * g[0];
+}
+// N = M K~(Yb)  (3 x 6, row-major): [rho M | -M [Yb]x]
+BA_D void m_times_k(const double* M, double rho, const double* Yb, double* N) {
+#pragma unroll
+  for (int r = 0; r < 3; ++r) {
+    const double m0 = M[3 * r], m1 = M[3 * r + 1], m2 = M[3 * r + 2];
+    N[6 * r] = rho * m0; N[6 * r + 1] = rho * m1; N[6 * r + 2] = rho * m2;
+    N[6 * r + 3] = m2 * Yb[1] - m1 * Yb[2];
+    N[6 * r + 4] = m0 * Yb[2] - m2 * Yb[0];
+    N[6 * r + 5] = m1 * Yb[0] - m0 * Yb[1];
   }
-  double Ar[9];
-  mat3_skew(P.Rwp + 9 * (size_t)ref_pose, Y, Ar);
+}
+// acc (6 x 6 row-major) += K~(Ya)^T M K~(Yb), M full 3 x 3 row-major
+BA_D void acc_kmk(double* acc, double rho, const double* Ya, const double* Yb, const double* M) {
+  double N[18];
+  m_times_k(M, rho, Yb, N);
 #pragma unroll
-  for (int j = 0; j < 3; ++j)
-#pragma unroll
-    for (int k = 0; k < 3; ++k) { M[6 * j + k] = (j == k) ? -rho : 0.0; M[6 * j + 3 + k] = Ar[3 * j + k]; }
-  const uint32_t fr = P.pose_free[ref_pose];
-  if ((fr & 63u) != 63u) {
-#pragma unroll
-    for (int k = 0; k < 6; ++k)
-      if (!((fr >> k) & 1u)) { M[k] = 0.0; M[6 + k] = 0.0; M[12 + k] = 0.0; }
+  for (int c = 0; c < 6; ++c) {
+    const double n0 = N[c], n1 = N[6 + c], n2 = N[12 + c];
+    acc[c] += rho * n0; acc[6 + c] += rho * n1; acc[12 + c] += rho * n2;
+    acc[18 + c] += Ya[1] * n2 - Ya[2] * n1;
+    acc[24 + c] += Ya[2] * n0 - Ya[0] * n2;
+    acc[30 + c] += Ya[0] * n1 - Ya[1] * n0;
   }
+}
+// acc (upper triangle packed k = c (c + 1) / 2 + r, r <= c) += K~(Y)^T M K~(Y), M symmetric given as full row-major
+BA_D void acc_kmk_sym(double* acc, double rho, const double* Y, const double* M) {
+  double N[18];
+  m_times_k(M, rho, Y, N);
+  int k = 0;
+#pragma unroll
+  for (int c = 0; c < 6; ++c) {
+    const double n0 = N[c], n1 = N[6 + c], n2 = N[12 + c];
+    const double col[6] = {rho * n0, rho * n1, rho * n2, Y[1] * n2 - Y[2] * n1, Y[2] * n0 - Y[0] * n2, Y[0] * n1 - Y[1] * n0};
+#pragma unroll
+    for (int r = 0; r <= c; ++r) { acc[k] += col[r]; ++k; }
+  }
+}
+// D_p = blkdiag(I, R_wp) with masked parameter columns zeroed: element (q, c), R row-major
+BA_D double d_elem(const double* R, uint32_t free_bits, int q, int c) {
+  if (!((free_bits >> c) & 1u)) return 0.0;
+  if (c < 3) return q == c ? 1.0 : 0.0;
+  return q >= 3 ? R[3 * (q - 3) + (c - 3)] : 0.0;
 }
 
 // Pose block (i, j), i <= j (opt ids), inside the tiled S: element (r, c) lives at p[r * rs + c * cs].

@@ -1,4 +1,4 @@
-// schur_kernels.cu — atomic-free, record-free assembly of the reduced camera system.
+// schur_kernels.cu — atomic-free, Jacobian-free assembly of the reduced camera system.
 //
 // Replaces, per outer iteration (reference src/BundleAdjuster.cpp):
 //   U += Jpr^T Jpr, rhs_p += Jpr^T r                                    cpp:337-354
@@ -8,20 +8,19 @@
 //
 // The reference scatters: per landmark it adds k(k+1)/2 outer products into S.  On the GPU that is ~36 FP64
 // reductions per product into L2, bound by the L2 atomic units (profiles/r1a_*: 7 ms for 5M observations).  Round 1
-// turned the product around with a 224/320-byte record per observation (write once, gather once per pose pair): no
-// atomics, but 1.8x - 3.7x the algorithmic DRAM bytes and an L2-bound gather (profiles/r1f, r1i).  Here nothing per
-// observation is stored at all:
+// turned the product around with a 224/320-byte record per observation (1.8x - 3.7x the algorithmic DRAM bytes); the
+// first round-2 version stored nothing and re-evaluated both Jacobians of every pair (profiles/r2a_*: instruction- and
+// latency-bound, 26 warp instructions per list entry).  This version uses the factorisation of ba_gpu.h: with
+// B = d project / d X_world every projection Jacobian is B K_pose (or -B, -B u for the landmark), so
 //
 //   pass A  k_linearize   (landmark-major, one observation per lane)
-//       Jacobians, Huber weight, V, b_l, V^-1 by segmented warp shuffles; writes the weight (8 B per observation)
-//       and ONE 128-byte record per landmark: the point, V^-1 and dhat = V^-1 b_l (LmSize 1: also the three sums
-//       from which the reference pose's blocks follow).
+//       residual, Huber weight, G = w B^T B (64-byte record) and h = w B^T r (32-byte record) per observation;
+//       V = sum G (LmSize 1: sum u^T G u), b_l, V^-1 by segmented warp shuffles; ONE 128-byte record per landmark.
 //   pass B  k_reduce_blocks (pose-pair-major, one warp per S block chunk, one list entry per lane)
-//       S_ij -= w_a w_b Jm_a^T (Jl_a V^-1 Jl_b^T) Jm_b over the block's pair list; both Jacobians of a pair are
-//       re-evaluated from two 32-byte observations and the landmark record (5 sectors through L2 instead of 9-10)
-//       against the two pose frames of the block, which are uniform over the warp.  Diagonal blocks, b_p and rhs_sc
-//       come from the pose's own observation list the same way.  Each block is owned by one warp (or a fixed
-//       chain of chunks combined in index order): NO atomics, bit-reproducible run to run.
+//       S_ij += sum_e K~_i^T M_e K~_j,  K~_p = [rho I | -[X - rho t_p]x],  M_e = -G_a V^-1 G_b (off-diagonal, LmSize 3),
+//       G_a - G_a V^-1 G_a (diagonal), -V^-1 g_a g_b^T (LmSize 1), ...: no camera model, no division, no weights.
+//       The pose's rotation and parameter mask (D_i^T . D_j) are applied once per block at write-out.  Each block is
+//       owned by one warp (or a fixed chain of chunks combined in index order): NO atomics, bit-reproducible.
 // The pair lists depend only on the ids; they are built once per Solve() on the device (symbolic.cu).
 #include <algorithm>
 #include <cstdlib>
@@ -31,41 +30,40 @@
 namespace bagpu {
 
 BA_D void st2(double* p, double a, double b) { *reinterpret_cast<double2*>(p) = make_double2(a, b); }
-BA_D void ld2(const double* p, double& a, double& b) { const double2 v = *reinterpret_cast<const double2*>(p); a = v.x; b = v.y; }
 
 // ---------------------------------------------------------------------------------------
 // pass A
-// Running sums of one landmark over its observations.  LmSize 1: the reference-pose Jacobian of every observation of
-// the landmark is Bp M with the same 3 x 6 M = [-rho I | Ar], so H_rr = M^T (sum w Bp^T Bp) M, g_r = M^T sum w Bp^T r,
-// W_r = M^T sum w Bp^T J_l: 12 running sums instead of 33.
+// Running sums of one landmark over its observations.
+//   LmSize 3: V = sum G (6) | b_l = -sum h (3)
+//   LmSize 1: V = sum w j.j | b_l = -sum w j.r | Gbar = sum G (6) | hbar = sum h (3) | gbar = sum w B^T j (3)
+//             (the last three over the observations whose reference pose takes part: from them follow the reference
+//             pose's own blocks, W_ref = K_ref^T gbar, U_ref = K_ref^T Gbar K_ref, b_ref = -K_ref^T hbar)
 template <int L> struct LmSums {
   static constexpr int NV = L * (L + 1) / 2;
   static constexpr int N = NV + L + (L == 1 ? 12 : 0);
-  double v[N];   // V (upper, NV) | b_l (L) | LmSize 1: SBB (6) | SBr (3) | SBl (3)
+  double v[N];
 };
 
 template <int L>
-BA_D void sums_add(LmSums<L>& S, const ObsJac<L>& o, double w, bool lm_on) {
-  constexpr int NV = LmSums<L>::NV;
-  const double wr0 = w * o.r[0], wr1 = w * o.r[1];
-  if (lm_on) {
-    int k = 0;
+BA_D void sums_add(LmSums<L>& S, const ObsLin<L>& o, bool lm_on) {
+  if constexpr (L == 3) {
+    if (lm_on) {
 #pragma unroll
-    for (int a = 0; a < L; ++a) {
+      for (int k = 0; k < 6; ++k) S.v[k] += o.G[k];
 #pragma unroll
-      for (int b = a; b < L; ++b) { S.v[k] += w * (o.Jl[a] * o.Jl[b] + o.Jl[L + a] * o.Jl[L + b]); ++k; }
-      S.v[NV + a] += o.Jl[a] * wr0 + o.Jl[L + a] * wr1;
+      for (int k = 0; k < 3; ++k) S.v[6 + k] -= o.h[k];
     }
-  }
-  if (L == 1 && o.ref_on) {
-    double* SBB = S.v + NV + L; double* SBr = SBB + 6; double* SBl = SBr + 3;
-    int k = 0;
+  } else {
+    if (lm_on) { S.v[0] += o.w * (o.j[0] * o.j[0] + o.j[1] * o.j[1]); S.v[1] -= o.wjr; }
+    if (o.ref_on) {
 #pragma unroll
-    for (int a = 0; a < 3; ++a) {
+      for (int k = 0; k < 6; ++k) S.v[2 + k] += o.G[k];
 #pragma unroll
-      for (int b = a; b < 3; ++b) { SBB[k] += w * (o.Bp[a] * o.Bp[b] + o.Bp[3 + a] * o.Bp[3 + b]); ++k; }
-      SBr[a] += o.Bp[a] * wr0 + o.Bp[3 + a] * wr1;
-      if (lm_on) SBl[a] += w * (o.Bp[a] * o.Jl[0] + o.Bp[3 + a] * o.Jl[1]);
+      for (int k = 0; k < 3; ++k) S.v[8 + k] += o.h[k];
+      if (lm_on) {
+#pragma unroll
+        for (int k = 0; k < 3; ++k) S.v[11 + k] += o.gj[k];
+      }
     }
   }
 }
@@ -105,7 +103,7 @@ BA_D void lm_invert(const LmSums<L>& S, bool lm_on, double* Vi, double* bl, doub
   }
 }
 
-// the landmark's record (ba_gpu.h), written by one lane: eight 16-byte stores into one 128-byte line
+// the landmark's record (ba_gpu.h), written by one lane: 16-byte stores into one 128-byte line
 template <int L>
 BA_D void lm_write(const DeviceProblem& P, int lm, const LmCtx<L>& c, bool lm_on, const LmSums<L>& S) {
   constexpr int NV = LmSums<L>::NV;
@@ -113,21 +111,37 @@ BA_D void lm_write(const DeviceProblem& P, int lm, const LmCtx<L>& c, bool lm_on
   lm_invert<L>(S, lm_on, Vi, bl, dhat);
   double* o = P.lm_rec + (size_t)lm * kLmRec;
   st2(o, c.X[0], c.X[1]); st2(o + 2, c.X[2], c.rho);
-  if (L == 3) {
+  if constexpr (L == 3) {
     st2(o + 4, Vi[0], Vi[1]); st2(o + 6, Vi[2], Vi[3]); st2(o + 8, Vi[4], Vi[5]);
     st2(o + 10, dhat[0], dhat[1]); st2(o + 12, dhat[2], 0.0); st2(o + 14, 0.0, 0.0);
   } else {
-    const double* SBB = S.v + NV + L; const double* SBr = SBB + 6; const double* SBl = SBr + 3;
-    const double* xs = P.lm_x + 4 * (size_t)lm;
+    const double* Gb = S.v + 2; const double* hb = S.v + 8; const double* gb = S.v + 11;
     st2(o + 4, c.tws_r[0], c.tws_r[1]); st2(o + 6, c.tws_r[2], Vi[0]);
-    st2(o + 8, dhat[0], xs[0]); st2(o + 10, xs[1], xs[2]);
-    st2(o + 12, SBl[0], SBl[1]); st2(o + 14, SBl[2], 0.0);
+    st2(o + 8, dhat[0], gb[0]); st2(o + 10, gb[1], gb[2]);
+    st2(o + 12, 0.0, 0.0); st2(o + 14, 0.0, 0.0);
     double* oc = P.lm_recC + (size_t)lm * kLmRecC;
-    st2(oc, SBB[0], SBB[1]); st2(oc + 2, SBB[2], SBB[3]); st2(oc + 4, SBB[4], SBB[5]);
-    st2(oc + 6, SBr[0], SBr[1]); st2(oc + 8, SBr[2], 0.0);
+    st2(oc, Gb[0], Gb[1]); st2(oc + 2, Gb[2], Gb[3]); st2(oc + 4, Gb[4], Gb[5]);
+    st2(oc + 6, hb[0], hb[1]); st2(oc + 8, hb[2], 0.0); st2(oc + 10, 0.0, 0.0);
   }
 #pragma unroll
   for (int i = 0; i < L; ++i) P.lm_bl[(size_t)lm * L + i] = bl[i];
+}
+
+// one observation of pass A: linearise, write weight and records, add into the landmark's sums
+template <int L>
+BA_D void linearize_one(const DeviceProblem& P, const LmCtx<L>& c, int i, int m, bool lm_on, double c_huber, double c2, LmSums<L>& S,
+                        double& err) {
+  ObsLin<L> o;
+  obs_linearize<L>(P, c, i, m, c_huber, c2, o);
+  P.obs_w[i] = o.w;
+  err += o.n2 * o.w;
+  if (o.pm_on) {   // the records are read only through the pose-major lists, which hold exactly these observations
+    double* g = P.obs_G + (size_t)i * kObsG;
+    st2(g, o.G[0], o.G[1]); st2(g + 2, o.G[2], o.G[3]); st2(g + 4, o.G[4], o.G[5]); st2(g + 6, 0.0, 0.0);   // whole sectors
+    double* hh = P.obs_h + (size_t)i * kObsH;
+    st2(hh, o.h[0], o.h[1]); st2(hh + 2, o.h[2], 0.0);
+  }
+  sums_add<L>(S, o, lm_on);
 }
 
 // Landmarks with more than 32 observations (lm_list): one warp per landmark, lanes stride over the track.
@@ -146,16 +160,7 @@ __global__ void __launch_bounds__(128) k_linearize_long(DeviceProblem P, const u
     LmSums<L> S;
 #pragma unroll
     for (int i = 0; i < LmSums<L>::N; ++i) S.v[i] = 0.0;
-    for (int i = s + lane; i < e; i += 32) {
-      ObsJac<L> o;
-      obs_jacobians<L>(P, c, i, o);
-      const double w0 = P.obs_w0[i];
-      const double n2 = o.r[0] * o.r[0] + o.r[1] * o.r[1];
-      const double w = huber_weight(n2 * w0, w0, c_huber, c2, P.use_robust);
-      P.obs_w[i] = w;
-      err[0] += n2 * w;
-      sums_add<L>(S, o, w, lm_on);
-    }
+    for (int i = s + lane; i < e; i += 32) linearize_one<L>(P, c, i, (int)P.obs_pose[i], lm_on, c_huber, c2, S, err[0]);
 #pragma unroll
     for (int i = 0; i < LmSums<L>::N; ++i) S.v[i] = warp_sum(S.v[i]);
     if (lane == 0) lm_write<L>(P, lm, c, lm_on, S);
@@ -164,7 +169,7 @@ __global__ void __launch_bounds__(128) k_linearize_long(DeviceProblem P, const u
 }
 
 // Packed tasks: a task is a run of consecutive landmarks with at most 32 observations in total (packed on the host from
-// the CSR bounds, symbolic set-up).  One warp per task, ONE OBSERVATION PER LANE: the Jacobians are evaluated once,
+// the CSR bounds, symbolic set-up).  One warp per task, ONE OBSERVATION PER LANE: the observation is linearised once,
 // the per-landmark sums are segmented warp reductions over the lanes of the landmark, the head lane of a landmark
 // writes its record.
 template <int L>
@@ -200,16 +205,7 @@ __global__ void __launch_bounds__(128) k_linearize_packed(DeviceProblem P, const
     LmSums<L> S;
 #pragma unroll
     for (int k = 0; k < LmSums<L>::N; ++k) S.v[k] = 0.0;
-    if (on) {
-      ObsJac<L> o;
-      obs_jacobians<L>(P, c, i, o, m_pre);
-      const double w0 = P.obs_w0[i];
-      const double n2 = o.r[0] * o.r[0] + o.r[1] * o.r[1];
-      const double w = huber_weight(n2 * w0, w0, c_huber, c2, P.use_robust);
-      P.obs_w[i] = w;
-      err[0] += n2 * w;
-      sums_add<L>(S, o, w, lm_on);
-    }
+    if (on) linearize_one<L>(P, c, i, m_pre, lm_on, c_huber, c2, S, err[0]);
     // segmented reduction to the head lane (a lane adds its neighbour at distance d only inside its own landmark)
 #pragma unroll
     for (int d = 1; d < 32; d <<= 1) {
@@ -241,19 +237,19 @@ __global__ void k_lm_defaults(DeviceProblem P) {
 
 // ---------------------------------------------------------------------------------------
 // pass B: one warp per work item (a chunk of one S block), items claimed in order from one counter so that the warps
-// in flight work on neighbouring blocks (their observations and landmark records stay in L2).  One list entry per
-// lane.  The 5 sectors of an entry are brought into shared memory by cp.async with CHUNK-wise lane mapping —
-// consecutive lanes copy consecutive 16-byte pieces of one record, so an instruction touches 4-16 cache lines instead
-// of 32 (L1 serves one line per cycle) — in a multi-stage pipeline; the lane then reads its own entry back (stride of
-// an odd number of 16-byte words: conflict-free).  Accumulators: the 36 elements of the block (or 21 + 6 + 6 for a
-// diagonal block with b_p and rhs_sc) per lane, transposed through shared memory at the end of the item so that lane e
-// owns element e.
+// in flight work on neighbouring blocks (their records stay in L2).  One list entry per lane.  The records of an entry
+// (two 64-byte G records and 64-80 bytes of the landmark record off the diagonal; G, h and the landmark record on
+// it) are brought into shared memory by cp.async with CHUNK-wise lane mapping — consecutive lanes copy consecutive
+// 16-byte pieces of one record, so an instruction touches 6-11 cache lines instead of 32 (L1 serves one line per
+// cycle) — double buffered; the lane then reads its own entry back (stride of an odd number of 16-byte words:
+// conflict-free).  Accumulators: the 36 elements of the block (or 21 + 6 + 6 for a diagonal block with b_p and rhs_sc)
+// per lane, transposed through shared memory at the end of the item so that lane e owns element e.
 constexpr int kPartial = 64;       // doubles per partial-sum slot
 constexpr int kRedWarps = 4;
 constexpr int kNAcc = 36;
 template <int L> struct RedCfg {
-  static constexpr int STRIDE = (L == 3) ? 22 : 30;   // doubles per staged entry: 176 / 240 bytes
-  static constexpr int STAGES = (L == 3) ? 3 : 2;
+  static constexpr int STRIDE = (L == 3) ? 26 : 22;   // doubles per staged entry
+  static constexpr int STAGES = 2;
   static constexpr int DATA = 32 * STRIDE;
   static constexpr int BUF = DATA + 32;               // + 32 (a, b) index pairs
   static constexpr size_t smem = sizeof(double) * STAGES * BUF * kRedWarps;
@@ -267,8 +263,8 @@ BA_D void cp_async16(double* smem_dst, const void* gsrc) {
 BA_D void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
 template <int N> BA_D void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
 
-// stage NC 16-byte chunks of the record `base + id * rec_bytes` of every lane's entry (id = kNoSlot: none) at doubles
-// offset `off` of the entry's stage slot
+// stage the first NC 16-byte chunks of the record `base + id * rec_bytes` of every lane's entry (id = kNoSlot: none)
+// at doubles offset `off` of the entry's stage slot
 template <int NC, int STRIDE>
 BA_D void stage_chunks(double* buf, int off, const char* __restrict__ base, int rec_bytes, uint32_t id, int lane) {
 #pragma unroll
@@ -282,28 +278,37 @@ BA_D void stage_chunks(double* buf, int off, const char* __restrict__ base, int 
 
 struct PairLists { const uint32_t *a, *b, *lm; };   // off-diagonal entries: observation of the row pose, of the column pose (or tag), landmark
 
-// upper-triangle packing of the diagonal accumulators: k = c (c + 1) / 2 + r, r <= c
-BA_D void add_upper(double* acc, const double* x0, const double* x1, const double* y0, const double* y1) {
-  int k = 0;
+BA_D void sym3_full(const double* G, double* F) {
+  F[0] = G[0]; F[1] = G[1]; F[2] = G[2]; F[3] = G[1]; F[4] = G[3]; F[5] = G[4]; F[6] = G[2]; F[7] = G[4]; F[8] = G[5];
+}
+// Y = X - rho t
+BA_D void y_of(const double* X, double rho, const double* t, double* Y) { Y[0] = X[0] - rho * t[0]; Y[1] = X[1] - rho * t[1]; Y[2] = X[2] - rho * t[2]; }
+// diagonal accumulators: 21 (block, packed upper) | 6 (b_p) | 6 (rhs_sc)
+BA_D void acc_diag(double* acc, double rho, const double* Y, const double* M, const double* v1, const double* v2) {
+  acc_kmk_sym(acc, rho, Y, M);
+  double p[6];
+  kt_vec(rho, Y, v1, p);
 #pragma unroll
-  for (int c = 0; c < 6; ++c)
+  for (int k = 0; k < 6; ++k) acc[21 + k] += p[k];
+  kt_vec(rho, Y, v2, p);
 #pragma unroll
-    for (int r = 0; r <= c; ++r) { acc[k] += x0[r] * y0[c] + x1[r] * y1[c]; ++k; }
+  for (int k = 0; k < 6; ++k) acc[27 + k] += p[k];
 }
 
 template <int L>
-__global__ void __launch_bounds__(kRedWarps * 32, (L == 3) ? 3 : 3) k_reduce_blocks(DeviceProblem P, const ReduceItem* __restrict__ items, int n_items, PairLists pl,
+__global__ void __launch_bounds__(kRedWarps * 32, 4) k_reduce_blocks(DeviceProblem P, const ReduceItem* __restrict__ items, int n_items, PairLists pl,
                                                                      double* __restrict__ partial, unsigned int* __restrict__ counters,
                                                                      unsigned int* __restrict__ next_item) {
   typedef RedCfg<L> Cfg;
   constexpr int ST = Cfg::STRIDE, NS = Cfg::STAGES;
   extern __shared__ double sdyn[];
   const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
-  double* stage = sdyn + (size_t)wib * NS * Cfg::BUF;   // the transpose-reduce reuses the stage buffers
-  const double c_huber = P.c_huber_factor * sqrt(P.sc->median), c2 = c_huber * c_huber;
-  const char* obs_base = reinterpret_cast<const char*>(P.obs_rec);
+  double* stage = sdyn + (size_t)wib * NS * Cfg::BUF;   // the transpose-reduce and the write-out reuse the stage buffers
+  const char* g_base = reinterpret_cast<const char*>(P.obs_G);
+  const char* h_base = reinterpret_cast<const char*>(P.obs_h);
   const char* lm_base = reinterpret_cast<const char*>(P.lm_rec);
   const char* lmc_base = reinterpret_cast<const char*>(P.lm_recC);
+  constexpr int kGB = kObsG * 8, kHB = kObsH * 8, kLB = kLmRec * 8, kCB = kLmRecC * 8;
   for (;;) {
     int it = 0;
     if (lane == 0) it = (int)atomicAdd(next_item, 1u);
@@ -313,6 +318,8 @@ __global__ void __launch_bounds__(kRedWarps * 32, (L == 3) ? 3 : 3) k_reduce_blo
     const int kind = (int)w.kind;
     const bool diag = (kind == kItemDiagObs || kind == kItemDiagLm);
     const int row_pose = P.opt_to_pose[w.row], col_pose = P.opt_to_pose[w.col];
+    const double* ti = P.pose_t + 3 * (size_t)row_pose;
+    const double* tj = P.pose_t + 3 * (size_t)col_pose;
     double acc[kNAcc];
 #pragma unroll
     for (int k = 0; k < kNAcc; ++k) acc[k] = 0.0;
@@ -337,19 +344,21 @@ __global__ void __launch_bounds__(kRedWarps * 32, (L == 3) ? 3 : 3) k_reduce_blo
         entry(ld + 1, n0, n1, n2);
         reinterpret_cast<uint2*>(dst + Cfg::DATA)[lane] = make_uint2(e0, (kind == kItemDiagLm) ? e2 : e1);
         if (kind == kItemOff || kind == kItemSym) {
-          stage_chunks<2, ST>(dst, 0, obs_base, 32, e0, lane);
-          stage_chunks<2, ST>(dst, 4, obs_base, 32, e1, lane);
-          if (L == 3) stage_chunks<5, ST>(dst, 8, lm_base, kLmRec * 8, e2, lane);
-          else stage_chunks<4, ST>(dst, 8, lm_base, kLmRec * 8, e2, lane);
+          stage_chunks<3, ST>(dst, 0, g_base, kGB, e0, lane);
+          stage_chunks<3, ST>(dst, 6, g_base, kGB, e1, lane);
+          if (L == 3) stage_chunks<5, ST>(dst, 12, lm_base, kLB, e2, lane);
+          else stage_chunks<4, ST>(dst, 12, lm_base, kLB, e2, lane);
         } else if (kind == kItemDiagObs) {
-          stage_chunks<2, ST>(dst, 0, obs_base, 32, e0, lane);
-          stage_chunks<8, ST>(dst, 4, lm_base, kLmRec * 8, e2, lane);
+          stage_chunks<3, ST>(dst, 0, g_base, kGB, e0, lane);
+          stage_chunks<2, ST>(dst, 6, h_base, kHB, e0, lane);
+          if (L == 3) stage_chunks<7, ST>(dst, 10, lm_base, kLB, e2, lane);
+          else stage_chunks<5, ST>(dst, 10, lm_base, kLB, e2, lane);
         } else if (L == 1 && kind == kItemOffRef) {
-          stage_chunks<2, ST>(dst, 0, obs_base, 32, e0, lane);
-          stage_chunks<8, ST>(dst, 4, lm_base, kLmRec * 8, e2, lane);
+          stage_chunks<3, ST>(dst, 0, g_base, kGB, e0, lane);
+          stage_chunks<6, ST>(dst, 6, lm_base, kLB, e2, lane);
         } else if (L == 1) {   // kItemDiagLm
-          stage_chunks<5, ST>(dst, 0, lmc_base, kLmRecC * 8, e2, lane);
-          stage_chunks<8, ST>(dst, 12, lm_base, kLmRec * 8, e2, lane);
+          stage_chunks<5, ST>(dst, 0, lmc_base, kCB, e2, lane);
+          stage_chunks<6, ST>(dst, 10, lm_base, kLB, e2, lane);
         }
       }
       cp_async_commit();
@@ -362,150 +371,118 @@ __global__ void __launch_bounds__(kRedWarps * 32, (L == 3) ? 3 : 3) k_reduce_blo
       const bool valid = (kind == kItemDiagLm) ? (ids.y != kNoSlot) : (ids.x != kNoSlot);
       if (valid) {
         if (kind == kItemOff || kind == kItemSym) {
-          const double* lm = d + 8;
-          const int cam_a = P.obs_cam ? (int)P.obs_cam[ids.x] : 0, cam_b = P.obs_cam ? (int)P.obs_cam[ids.y] : 0;
-          Side<L> sa, sb;
-          side_eval<L>(P, lm, d[0], d[1], d[2], row_pose, cam_a, c_huber, c2, sa);
-          side_eval<L>(P, lm, d[4], d[5], d[6], col_pose, cam_b, c_huber, c2, sb);
+          const double* lm = d + 12;
+          const double rho = lm[3];
+          double Ya[3], Yb[3];
+          y_of(lm, rho, ti, Ya); y_of(lm, rho, tj, Yb);
           if (L == 3) {
-            // M = w_a w_b B_a V^-1 B_b^T  (J_l = -B on both sides)
-            const double v00 = lm[4], v01 = lm[5], v02 = lm[6], v11 = lm[7], v12 = lm[8], v22 = lm[9];
-            double BV[6];
+            // M = -G_a V^-1 G_b
+            double Ga[9], Vi[9], Gb[9], T[9], M[9];
+            sym3_full(d, Ga); sym3_full(lm + 4, Vi); sym3_full(d + 6, Gb);
+            mat3_mul(Ga, Vi, T);
+            mat3_mul(T, Gb, M);
 #pragma unroll
-            for (int x = 0; x < 2; ++x) {
-              const double* b = sa.B + 3 * x;
-              BV[3 * x] = b[0] * v00 + b[1] * v01 + b[2] * v02;
-              BV[3 * x + 1] = b[0] * v01 + b[1] * v11 + b[2] * v12;
-              BV[3 * x + 2] = b[0] * v02 + b[1] * v12 + b[2] * v22;
-            }
-            const double ww = sa.w * sb.w;
-            const double m00 = ww * (BV[0] * sb.B[0] + BV[1] * sb.B[1] + BV[2] * sb.B[2]);
-            const double m01 = ww * (BV[0] * sb.B[3] + BV[1] * sb.B[4] + BV[2] * sb.B[5]);
-            const double m10 = ww * (BV[3] * sb.B[0] + BV[4] * sb.B[1] + BV[5] * sb.B[2]);
-            const double m11 = ww * (BV[3] * sb.B[3] + BV[4] * sb.B[4] + BV[5] * sb.B[5]);
-#pragma unroll
-            for (int c = 0; c < 6; ++c) {
-              const double t0 = m00 * sb.Jm[c] + m01 * sb.Jm[6 + c], t1 = m10 * sb.Jm[c] + m11 * sb.Jm[6 + c];
-#pragma unroll
-              for (int r = 0; r < 6; ++r) acc[r * 6 + c] -= sa.Jm[r] * t0 + sa.Jm[6 + r] * t1;
-            }
+            for (int k = 0; k < 9; ++k) M[k] = -M[k];
+            acc_kmk(acc, rho, Ya, Yb, M);
           } else {
-            // - V^-1 W_a W_b^T,  W = w Jm^T J_l
+            // -V^-1 (K~_a^T g_a)(K~_b^T g_b)^T,  g = G u,  u = baseline reference sensor -> measuring sensor
+            const int cam_a = P.obs_cam ? (int)P.obs_cam[ids.x] : 0, cam_b = P.obs_cam ? (int)P.obs_cam[ids.y] : 0;
+            const double* twa = P.Tws + ((size_t)row_pose * P.n_cams + cam_a) * 12 + 9;
+            const double* twb = P.Tws + ((size_t)col_pose * P.n_cams + cam_b) * 12 + 9;
+            const double ua[3] = {lm[4] - twa[0], lm[5] - twa[1], lm[6] - twa[2]};
+            const double ub[3] = {lm[4] - twb[0], lm[5] - twb[1], lm[6] - twb[2]};
+            double ga[3], gb[3], pa[6], pb[6];
+            sym3_vec(d, ua, ga); sym3_vec(d + 6, ub, gb);
+            kt_vec(rho, Ya, ga, pa); kt_vec(rho, Yb, gb, pb);
             const double vi = lm[7];
-            double Wa[6], Wb[6];
 #pragma unroll
-            for (int k = 0; k < 6; ++k) {
-              Wa[k] = vi * sa.w * (sa.Jm[k] * sa.jl[0] + sa.Jm[6 + k] * sa.jl[1]);
-              Wb[k] = sb.w * (sb.Jm[k] * sb.jl[0] + sb.Jm[6 + k] * sb.jl[1]);
+            for (int r = 0; r < 6; ++r) {
+              const double s = -vi * pa[r];
+#pragma unroll
+              for (int c = 0; c < 6; ++c) acc[r * 6 + c] += s * pb[c];
             }
-#pragma unroll
-            for (int r = 0; r < 6; ++r)
-#pragma unroll
-              for (int c = 0; c < 6; ++c) acc[r * 6 + c] -= Wa[r] * Wb[c];
           }
         } else if (kind == kItemDiagObs) {
-          const double* lm = d + 4;
-          const int cam_a = P.obs_cam ? (int)P.obs_cam[ids.x] : 0;
-          Side<L> s;
-          side_eval<L>(P, lm, d[0], d[1], d[2], row_pose, cam_a, c_huber, c2, s);
-          double T0[6], T1[6];
-          double q0, q1;   // r - J_l dhat
+          const double* h = d + 6;
+          const double* lm = d + 10;
+          const double rho = lm[3];
+          double Y[3], M[9], v2[3];
+          y_of(lm, rho, ti, Y);
           if (L == 3) {
-            const double v00 = lm[4], v01 = lm[5], v02 = lm[6], v11 = lm[7], v12 = lm[8], v22 = lm[9];
-            double BV[6];
+            // M = G - G V^-1 G (exactly symmetric: upper computed, mirrored); v2 = h + G dhat
+            double Ga[9], Vi[9], T[9];
+            sym3_full(d, Ga); sym3_full(lm + 4, Vi);
+            mat3_mul(Ga, Vi, T);
 #pragma unroll
-            for (int x = 0; x < 2; ++x) {
-              const double* b = s.B + 3 * x;
-              BV[3 * x] = b[0] * v00 + b[1] * v01 + b[2] * v02;
-              BV[3 * x + 1] = b[0] * v01 + b[1] * v11 + b[2] * v12;
-              BV[3 * x + 2] = b[0] * v02 + b[1] * v12 + b[2] * v22;
-            }
-            // N = I - w B V^-1 B^T
-            const double n00 = 1.0 - s.w * (BV[0] * s.B[0] + BV[1] * s.B[1] + BV[2] * s.B[2]);
-            const double n01 = -s.w * (BV[0] * s.B[3] + BV[1] * s.B[4] + BV[2] * s.B[5]);
-            const double n10 = -s.w * (BV[3] * s.B[0] + BV[4] * s.B[1] + BV[5] * s.B[2]);
-            const double n11 = 1.0 - s.w * (BV[3] * s.B[3] + BV[4] * s.B[4] + BV[5] * s.B[5]);
+            for (int r = 0; r < 3; ++r)
 #pragma unroll
-            for (int c = 0; c < 6; ++c) {
-              T0[c] = s.w * (n00 * s.Jm[c] + n01 * s.Jm[6 + c]);
-              T1[c] = s.w * (n10 * s.Jm[c] + n11 * s.Jm[6 + c]);
-            }
-            q0 = s.r[0] + (s.B[0] * lm[10] + s.B[1] * lm[11] + s.B[2] * lm[12]);
-            q1 = s.r[1] + (s.B[3] * lm[10] + s.B[4] * lm[11] + s.B[5] * lm[12]);
+              for (int c = r; c < 3; ++c) {
+                const double m = Ga[3 * r + c] - (T[3 * r] * Ga[c] + T[3 * r + 1] * Ga[3 + c] + T[3 * r + 2] * Ga[6 + c]);
+                M[3 * r + c] = m; M[3 * c + r] = m;
+              }
+            double gd[3];
+            sym3_vec(d, lm + 10, gd);
+            v2[0] = h[0] + gd[0]; v2[1] = h[1] + gd[1]; v2[2] = h[2] + gd[2];
           } else {
-            // w Jm^T Jm - V^-1 W W^T = Jm^T (w I - w^2 V^-1 jl jl^T) Jm
-            const double vi = lm[7], ww = s.w * s.w * vi;
-            const double n00 = s.w - ww * s.jl[0] * s.jl[0], n01 = -ww * s.jl[0] * s.jl[1], n11 = s.w - ww * s.jl[1] * s.jl[1];
+            // M = G - V^-1 g g^T; v2 = h + g dhat
+            const int cam_a = P.obs_cam ? (int)P.obs_cam[ids.x] : 0;
+            const double* twa = P.Tws + ((size_t)row_pose * P.n_cams + cam_a) * 12 + 9;
+            const double u[3] = {lm[4] - twa[0], lm[5] - twa[1], lm[6] - twa[2]};
+            double g[3];
+            sym3_vec(d, u, g);
+            const double vi = lm[7], dh = lm[8];
+            sym3_full(d, M);
 #pragma unroll
-            for (int c = 0; c < 6; ++c) {
-              T0[c] = n00 * s.Jm[c] + n01 * s.Jm[6 + c];
-              T1[c] = n01 * s.Jm[c] + n11 * s.Jm[6 + c];
-            }
-            q0 = s.r[0] - s.jl[0] * lm[8];
-            q1 = s.r[1] - s.jl[1] * lm[8];
-          }
-          add_upper(acc, s.Jm, s.Jm + 6, T0, T1);
-          const double wr0 = s.w * s.r[0], wr1 = s.w * s.r[1], wq0 = s.w * q0, wq1 = s.w * q1;
+            for (int r = 0; r < 3; ++r)
 #pragma unroll
-          for (int k = 0; k < 6; ++k) {
-            acc[21 + k] += s.Jm[k] * wr0 + s.Jm[6 + k] * wr1;
-            acc[27 + k] += s.Jm[k] * wq0 + s.Jm[6 + k] * wq1;
+              for (int c = r; c < 3; ++c) { const double m = M[3 * r + c] - vi * g[r] * g[c]; M[3 * r + c] = m; M[3 * c + r] = m; }
+            v2[0] = h[0] + g[0] * dh; v2[1] = h[1] + g[1] * dh; v2[2] = h[2] + g[2] * dh;
           }
+          acc_diag(acc, rho, Y, M, h, v2);
         } else if (L == 1 && kind == kItemOffRef) {
           // block between the measurement pose and the reference pose of one observation:
-          //   X = w Jm^T Jr - V^-1 W_a W_ref^T   (rows: measurement pose, columns: reference pose)
-          const double* lm = d + 4;
+          //   K_m^T (-G_a + V^-1 g_a gbar^T) K_r   (rows: measurement pose, columns: reference pose), or its transpose
+          const double* lm = d + 6;
+          const double rho = lm[3];
           const bool meas_row = (ids.y == kPairTagMeasRow);
-          const int mp = meas_row ? row_pose : col_pose, rp = meas_row ? col_pose : row_pose;
+          const int mp = meas_row ? row_pose : col_pose;
           const int cam_a = P.obs_cam ? (int)P.obs_cam[ids.x] : 0;
-          Side<L> s;
-          side_eval<L>(P, lm, d[0], d[1], d[2], mp, cam_a, c_huber, c2, s);
-          double M[18];
-          ref_M(P, rp, P.n_cams > 1 ? (int)P.lm_ref_cam[(uint32_t)((unsigned long long)__double_as_longlong(d[3]) >> 32)] : 0, lm[3], lm + 9, M);
-          double J0[6], J1[6], Wr[6], Wa[6];
-#pragma unroll
-          for (int k = 0; k < 6; ++k) {
-            J0[k] = s.w * (s.B[0] * M[k] + s.B[1] * M[6 + k] + s.B[2] * M[12 + k]);
-            J1[k] = s.w * (s.B[3] * M[k] + s.B[4] * M[6 + k] + s.B[5] * M[12 + k]);
-            Wr[k] = M[k] * lm[12] + M[6 + k] * lm[13] + M[12 + k] * lm[14];
-            Wa[k] = lm[7] * s.w * (s.Jm[k] * s.jl[0] + s.Jm[6 + k] * s.jl[1]);
-          }
+          const double* twa = P.Tws + ((size_t)mp * P.n_cams + cam_a) * 12 + 9;
+          const double u[3] = {lm[4] - twa[0], lm[5] - twa[1], lm[6] - twa[2]};
+          double g[3], Gf[9], M[9], Ya[3], Yb[3];
+          sym3_vec(d, u, g);
+          sym3_full(d, Gf);
+          const double vi = lm[7];
+          const double* gbar = lm + 9;
+          y_of(lm, rho, ti, Ya); y_of(lm, rho, tj, Yb);
           if (meas_row) {
 #pragma unroll
-            for (int r = 0; r < 6; ++r)
+            for (int r = 0; r < 3; ++r)
 #pragma unroll
-              for (int c = 0; c < 6; ++c) acc[r * 6 + c] += s.Jm[r] * J0[c] + s.Jm[6 + r] * J1[c] - Wa[r] * Wr[c];
+              for (int c = 0; c < 3; ++c) M[3 * r + c] = vi * g[r] * gbar[c] - Gf[3 * r + c];
           } else {
 #pragma unroll
-            for (int r = 0; r < 6; ++r)
+            for (int r = 0; r < 3; ++r)
 #pragma unroll
-              for (int c = 0; c < 6; ++c) acc[r * 6 + c] += J0[r] * s.Jm[c] + J1[r] * s.Jm[6 + c] - Wr[r] * Wa[c];
+              for (int c = 0; c < 3; ++c) M[3 * r + c] = vi * gbar[r] * g[c] - Gf[3 * r + c];
           }
+          acc_kmk(acc, rho, Ya, Yb, M);
         } else if (L == 1) {   // kItemDiagLm: the reference pose's own blocks of one landmark
-          const double* lc = d;         // SBB (6) | SBr (3)
-          const double* lm = d + 12;
-          double M[18];
-          ref_M(P, row_pose, P.n_cams > 1 ? (int)P.lm_ref_cam[ids.y] : 0, lm[3], lm + 9, M);
-          const double S3[9] = {lc[0], lc[1], lc[2], lc[1], lc[3], lc[4], lc[2], lc[4], lc[5]};
-          double TM[18];
-#pragma unroll
-          for (int j = 0; j < 3; ++j)
-#pragma unroll
-            for (int k = 0; k < 6; ++k) TM[6 * j + k] = S3[3 * j] * M[k] + S3[3 * j + 1] * M[6 + k] + S3[3 * j + 2] * M[12 + k];
-          double gr[6], Wr[6];
-#pragma unroll
-          for (int k = 0; k < 6; ++k) {
-            gr[k] = M[k] * lc[6] + M[6 + k] * lc[7] + M[12 + k] * lc[8];
-            Wr[k] = M[k] * lm[12] + M[6 + k] * lm[13] + M[12 + k] * lm[14];
-          }
+          const double* lc = d;         // Gbar (6) | hbar (3)
+          const double* lm = d + 10;
+          const double rho = lm[3];
           const double vi = lm[7], dh = lm[8];
-          int k = 0;
+          const double* gbar = lm + 9;
+          double Y[3], M[9], v1[3], v2[3];
+          y_of(lm, rho, ti, Y);
+          sym3_full(lc, M);
 #pragma unroll
-          for (int c = 0; c < 6; ++c)
+          for (int r = 0; r < 3; ++r)
 #pragma unroll
-            for (int r = 0; r <= c; ++r) { acc[k] += (M[r] * TM[c] + M[6 + r] * TM[6 + c] + M[12 + r] * TM[12 + c]) - vi * Wr[r] * Wr[c]; ++k; }
+            for (int c = r; c < 3; ++c) { const double m = M[3 * r + c] - vi * gbar[r] * gbar[c]; M[3 * r + c] = m; M[3 * c + r] = m; }
 #pragma unroll
-          for (int a = 0; a < 6; ++a) { acc[21 + a] += gr[a]; acc[27 + a] += gr[a] - Wr[a] * dh; }
+          for (int k = 0; k < 3; ++k) { v1[k] = -lc[6 + k]; v2[k] = -(lc[6 + k] + gbar[k] * dh); }
+          acc_diag(acc, rho, Y, M, v1, v2);
         }
       }
       __syncwarp();
@@ -545,32 +522,73 @@ __global__ void __launch_bounds__(kRedWarps * 32, (L == 3) ? 3 : 3) k_reduce_blo
         if (lane < kNAcc - 32) v1 += q[32 + lane];
       }
     }
-    // ---- write-out (exclusive owner: plain read-modify-write) ------------------------------
-    const SBlock blk = s_block(P, (int)w.row, (int)w.col);
-    if (kind == kItemSym) {   // same pose observed twice: X + X^T lands in the (upper) diagonal block
-      stage[lane] = v0;
-      if (lane < kNAcc - 32) stage[32 + lane] = v1;
-      __syncwarp();
-    }
+    // ---- the poses' rotation and parameter masks: out = D_i^T A D_j (vectors: D_i^T v), once per block ----
+    double* tA = stage;            // 36 (or 21 + 12 packed)
+    double* tT = stage + 64;       // A D_j, 6 x 6 row-major
+    double* tO = stage + 128;      // out, 6 x 6 row-major (kItemSym needs the transpose)
+    tA[lane] = v0;
+    if (lane < kNAcc - 32) tA[32 + lane] = v1;
+    __syncwarp();
+    const double* Ri = P.Rwp + 9 * (size_t)row_pose;
+    const double* Rj = P.Rwp + 9 * (size_t)col_pose;
+    const uint32_t fi = P.pose_free[row_pose], fj = P.pose_free[col_pose];
 #pragma unroll
     for (int half = 0; half < 2; ++half) {
       const int e = half * 32 + lane;
-      if (half == 1 && lane >= kNAcc - 32) break;
-      double v = half ? v1 : v0;
-      if (diag) {
-        if (e < 21) {
-          const int c = (e >= 15) ? 5 : (e >= 10) ? 4 : (e >= 6) ? 3 : (e >= 3) ? 2 : (e >= 1) ? 1 : 0;
-          const int r = e - c * (c + 1) / 2;
-          blk.p[(size_t)r * blk.rs + (size_t)c * blk.cs] += v;
-        } else if (e < 33) {
-          double* dst = (e < 27) ? P.b_p : P.rhs_sc;
-          dst[(size_t)w.row * P.D + (e < 27 ? e - 21 : e - 27)] += v;
-        }
-      } else {
+      if (e < 36) {
         const int r = e / 6, c = e - r * 6;
-        if (kind == kItemSym) { v += stage[c * 6 + r]; if (r <= c) blk.p[(size_t)r * blk.rs + (size_t)c * blk.cs] += v; }
-        else blk.p[(size_t)r * blk.rs + (size_t)c * blk.cs] += v;
+        auto A = [&](int p, int q) { return diag ? tA[p <= q ? q * (q + 1) / 2 + p : p * (p + 1) / 2 + q] : tA[p * 6 + q]; };
+        double t = 0.0;
+        if ((fj >> c) & 1u) {
+          if (c < 3) t = A(r, c);
+          else t = A(r, 3) * Rj[c - 3] + A(r, 4) * Rj[3 + c - 3] + A(r, 5) * Rj[6 + c - 3];
+        }
+        tT[e] = t;
       }
+    }
+    __syncwarp();
+    double o0 = 0.0, o1 = 0.0;
+#pragma unroll
+    for (int half = 0; half < 2; ++half) {
+      const int e = half * 32 + lane;
+      if (e < 36) {
+        const int r = e / 6, c = e - r * 6;
+        double t = 0.0;
+        if ((fi >> r) & 1u) {
+          if (r < 3) t = tT[r * 6 + c];
+          else t = Ri[r - 3] * tT[18 + c] + Ri[3 + r - 3] * tT[24 + c] + Ri[6 + r - 3] * tT[30 + c];
+        }
+        if (half) o1 = t; else o0 = t;
+        tO[e] = t;
+      }
+    }
+    double bv = 0.0;   // diagonal kinds: lanes 0..11 transform the two vectors (b_p: 0..5, rhs_sc: 6..11)
+    if (diag && lane < 12) {
+      const int r = lane % 6;
+      const double* v = tA + 21 + (lane / 6) * 6;
+      if ((fi >> r) & 1u) bv = (r < 3) ? v[r] : Ri[r - 3] * v[3] + Ri[3 + r - 3] * v[4] + Ri[6 + r - 3] * v[5];
+    }
+    __syncwarp();
+    // ---- write-out (exclusive owner: plain read-modify-write) ------------------------------
+    const SBlock blk = s_block(P, (int)w.row, (int)w.col);
+#pragma unroll
+    for (int half = 0; half < 2; ++half) {
+      const int e = half * 32 + lane;
+      if (e >= 36) break;
+      const int r = e / 6, c = e - r * 6;
+      double v = half ? o1 : o0;
+      if (diag) {
+        if (r <= c) blk.p[(size_t)r * blk.rs + (size_t)c * blk.cs] += v;
+      } else if (kind == kItemSym) {   // same pose observed twice: X + X^T lands in the (upper) diagonal block
+        v += tO[c * 6 + r];
+        if (r <= c) blk.p[(size_t)r * blk.rs + (size_t)c * blk.cs] += v;
+      } else {
+        blk.p[(size_t)r * blk.rs + (size_t)c * blk.cs] += v;
+      }
+    }
+    if (diag && lane < 12) {
+      double* dst = (lane < 6) ? P.b_p : P.rhs_sc;
+      dst[(size_t)w.row * P.D + (lane % 6)] += bv;
     }
     __syncwarp();
   }
@@ -612,7 +630,7 @@ void launch_reduce_blocks(const DeviceProblem& P, const ReduceItem* items, int n
     attr_done = true;
   }
   int grid = (n_items + kRedWarps - 1) / kRedWarps;
-  const int cap = sm_count_cached() * 3;
+  const int cap = sm_count_cached() * 4;
   if (grid > cap) grid = cap;
   cudaMemsetAsync(next_item, 0, sizeof(unsigned int), st);
   const PairLists pl = {pair_a, pair_b, pair_lm};

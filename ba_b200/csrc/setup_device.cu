@@ -111,15 +111,6 @@ __global__ void k_pose_lists(const uint32_t* __restrict__ vals_sorted, uint32_t 
   pose_obs[j] = i; pose_obs_lm[j] = obs_lm[i];
 }
 
-// the landmark-major stream once more as 32-byte records {z, orig weight, pose, landmark} (ba_gpu.h: ObsRec)
-__global__ void k_obs_records(const double2* __restrict__ z, const double* __restrict__ w0, const uint32_t* __restrict__ pose,
-                              const uint32_t* __restrict__ lm, uint32_t n, ObsRec* __restrict__ out) {
-  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= n) return;
-  const double2 zz = z[i];
-  ObsRec r; r.zx = zz.x; r.zy = zz.y; r.w0 = w0[i]; r.pose = pose[i]; r.lm = lm[i];
-  out[i] = r;
-}
 
 __global__ void k_rslot_keys(const uint8_t* __restrict__ lm_any, const uint32_t* __restrict__ lm_ref_pose, const int* __restrict__ pose_opt,
                              uint32_t n_lms, uint32_t n_ap, uint32_t* __restrict__ keys) {
@@ -227,9 +218,6 @@ void launch_slot_keys(const uint32_t* obs_pose, const uint32_t* obs_lm, uint32_t
 void launch_pose_lists(const uint32_t* vals_sorted, uint32_t n, const uint32_t* obs_lm, uint32_t* pose_obs, uint32_t* pose_obs_lm, cudaStream_t st) {
   if (n) k_pose_lists<<<blocks_for(n), 256, 0, st>>>(vals_sorted, n, obs_lm, pose_obs, pose_obs_lm);
 }
-void launch_obs_records(const double2* z, const double* w0, const uint32_t* pose, const uint32_t* lm, uint32_t n, ObsRec* out, cudaStream_t st) {
-  if (n) k_obs_records<<<blocks_for(n), 256, 0, st>>>(z, w0, pose, lm, n, out);
-}
 void launch_rslot_keys(const uint8_t* lm_any, const uint32_t* lm_ref_pose, const int* pose_opt, uint32_t n_lms, uint32_t n_ap, uint32_t* keys,
                        cudaStream_t st) {
   if (n_lms) k_rslot_keys<<<blocks_for(n_lms), 256, 0, st>>>(lm_any, lm_ref_pose, pose_opt, n_lms, n_ap, keys);
@@ -258,6 +246,17 @@ void launch_cond_error(const uint32_t* obs_pose, const uint32_t* obs_lm, const u
 }
 void launch_scatter_by_perm(const uint32_t* perm, const double* in, uint32_t n, double* out, cudaStream_t st) {
   if (n) k_scatter_by_perm<<<blocks_for(n), 256, 0, st>>>(perm, in, n, out);
+}
+// is_reliable over ranks: phase 0 writes 1 for every landmark this rank marked unreliable, phase 1 (after the sum over
+// ranks) clears the flag of every landmark any rank marked
+__global__ void k_reliable_merge(uint8_t* rel, unsigned int* unrel, uint32_t n, int phase) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  if (phase == 0) unrel[i] = rel[i] ? 0u : 1u;
+  else if (unrel[i]) rel[i] = 0;
+}
+void launch_reliable_merge(uint8_t* rel, unsigned int* unrel, uint32_t n, int phase, cudaStream_t st) {
+  if (n) k_reliable_merge<<<blocks_for(n), 256, 0, st>>>(rel, unrel, n, phase);
 }
 
 }  // namespace bagpu

@@ -173,6 +173,7 @@ def main():
     ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS))
     ap.add_argument("--scale", type=float, default=1.0, help="shrink the workload (development only; invalidates the number)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true", help="development / profiler runs only: skip the end-to-end leg (the line then has no e2e)")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0")); world = int(os.environ.get("WORLD_SIZE", "1")); local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     K, W = max(1, args.steps), max(0, args.warmup)
@@ -268,42 +269,44 @@ def main():
                               "frac": tot_b / world / (t_build * 1e-3) / 1e9 / peak, "kernel_ms": kt, "kernel_bytes": per_kernel, "nnzb_S": nnzb}}
     s.close()
 
-    # ---- e2e: host buffers in, refined state out, every call ------------------------------------------
-    # The caller's arrays live in page-locked host memory (bagpu_host_alloc, what include/ba/BundleAdjuster.h keeps
-    # its observation buffers in); everything from handing them to the ABI to reading the refined state is timed.
-    from ba_b200.capi import pinned_like, release_pinned
-    from ba_b200.problem import Problem
-    pp = Problem(L, d)
-    pp.set_bulk(**{k: pinned_like(v) for k, v in a.items()})
-    if hasattr(p, "gravity"):
-        pp.gravity = p.gravity
-    s2 = fresh(False)
-    s2.load(pp); s2.solve(1); s2.close()                     # warm the allocator / module load
-    h2d = sum(v.nbytes for k, v in a.items())
-    d2h = a["pose_t_wp"].nbytes + a["pose_v_w"].nbytes + a["pose_b"].nbytes + 2 * a["lm_x_w"].nbytes + len(a["lm_x_w"]) * 5
-    n_l = len(a["lm_x_w"])
-    lm_out = dict(x_w=pinned_like(np.zeros((n_l, 4))), x_s=pinned_like(np.zeros((n_l, 4))),
-                  is_reliable=pinned_like(np.zeros(n_l, np.uint8)), num_outlier_residuals=pinned_like(np.zeros(n_l, np.uint32)))
-    e2e_times = []
-    for _rep in range(3):                                    # median of three complete end-to-end calls
-        s3 = fresh(False)                                    # handle + NCCL communicator: set-up, like the process group
-        barrier()
-        t0 = time.time()
-        s3.load(pp)
-        sm3 = s3.solve(K)
-        if sm3.iterations != K:
-            raise SystemExit("bench.py: the e2e Solve() stopped after %d of %d iterations" % (sm3.iterations, K))
-        res = s3.get_poses(); lm = s3.get_landmarks(out=lm_out) if L else None
-        barrier()
-        t_e2e = torch.tensor([time.time() - t0], dtype=torch.float64, device="cuda")
-        if world > 1:
-            dist.all_reduce(t_e2e, op=dist.ReduceOp.MAX)
-        e2e_times.append(float(t_e2e.item()))
-        s3.close()
-    t_e2e = torch.tensor([sorted(e2e_times)[1]], dtype=torch.float64)
-    e2e_its = K / float(t_e2e.item())
-    del pp
-    release_pinned()
+    e2e_its, e2e_times, h2d, d2h = None, [], 0, 0
+    if not args.no_e2e:
+        # ---- e2e: host buffers in, refined state out, every call ------------------------------------------
+        # The caller's arrays live in page-locked host memory (bagpu_host_alloc, what include/ba/BundleAdjuster.h keeps
+        # its observation buffers in); everything from handing them to the ABI to reading the refined state is timed.
+        from ba_b200.capi import pinned_like, release_pinned
+        from ba_b200.problem import Problem
+        pp = Problem(L, d)
+        pp.set_bulk(**{k: pinned_like(v) for k, v in a.items()})
+        if hasattr(p, "gravity"):
+            pp.gravity = p.gravity
+        s2 = fresh(False)
+        s2.load(pp); s2.solve(1); s2.close()                     # warm the allocator / module load
+        h2d = sum(v.nbytes for k, v in a.items())
+        d2h = a["pose_t_wp"].nbytes + a["pose_v_w"].nbytes + a["pose_b"].nbytes + 2 * a["lm_x_w"].nbytes + len(a["lm_x_w"]) * 5
+        n_l = len(a["lm_x_w"])
+        lm_out = dict(x_w=pinned_like(np.zeros((n_l, 4))), x_s=pinned_like(np.zeros((n_l, 4))),
+                      is_reliable=pinned_like(np.zeros(n_l, np.uint8)), num_outlier_residuals=pinned_like(np.zeros(n_l, np.uint32)))
+        e2e_times = []
+        for _rep in range(3):                                    # median of three complete end-to-end calls
+            s3 = fresh(False)                                    # handle + NCCL communicator: set-up, like the process group
+            barrier()
+            t0 = time.time()
+            s3.load(pp)
+            sm3 = s3.solve(K)
+            if sm3.iterations != K:
+                raise SystemExit("bench.py: the e2e Solve() stopped after %d of %d iterations" % (sm3.iterations, K))
+            res = s3.get_poses(); lm = s3.get_landmarks(out=lm_out) if L else None
+            barrier()
+            t_e2e = torch.tensor([time.time() - t0], dtype=torch.float64, device="cuda")
+            if world > 1:
+                dist.all_reduce(t_e2e, op=dist.ReduceOp.MAX)
+            e2e_times.append(float(t_e2e.item()))
+            s3.close()
+        t_e2e = torch.tensor([sorted(e2e_times)[1]], dtype=torch.float64)
+        e2e_its = K / float(t_e2e.item())
+        del pp
+        release_pinned()
 
     if rank == 0:
         out = dict(base)
