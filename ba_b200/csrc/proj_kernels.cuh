@@ -271,13 +271,17 @@ BA_D void m_times_k(const double* M, double rho, const double* Yb, double* N) {
     N[6 * r + 5] = m1 * Yb[0] - m0 * Yb[1];
   }
 }
-// acc (6 x 6 row-major) += K~(Ya)^T M K~(Yb), M full 3 x 3 row-major
+// acc (6 x 6 row-major) += K~(Ya)^T M K~(Yb), M full 3 x 3 row-major.  Column by column: column c of M K~(Yb) is
+// rho M[:, c] (c < 3) or M (e_{c-3} x Yb), three values live at a time.
 BA_D void acc_kmk(double* acc, double rho, const double* Ya, const double* Yb, const double* M) {
-  double N[18];
-  m_times_k(M, rho, Yb, N);
 #pragma unroll
   for (int c = 0; c < 6; ++c) {
-    const double n0 = N[c], n1 = N[6 + c], n2 = N[12 + c];
+    double n0, n1, n2;
+    if (c < 3) { n0 = rho * M[c]; n1 = rho * M[3 + c]; n2 = rho * M[6 + c]; }
+    else {
+      const int p = (c - 3 + 2) % 3, q = (c - 3 + 1) % 3;   // column = M[:, p] Yb[q] - M[:, q] Yb[p]
+      n0 = M[p] * Yb[q] - M[q] * Yb[p]; n1 = M[3 + p] * Yb[q] - M[3 + q] * Yb[p]; n2 = M[6 + p] * Yb[q] - M[6 + q] * Yb[p];
+    }
     acc[c] += rho * n0; acc[6 + c] += rho * n1; acc[12 + c] += rho * n2;
     acc[18 + c] += Ya[1] * n2 - Ya[2] * n1;
     acc[24 + c] += Ya[2] * n0 - Ya[0] * n2;

@@ -29,7 +29,10 @@
 
 namespace bagpu {
 
-BA_D void st2(double* p, double a, double b) { *reinterpret_cast<double2*>(p) = make_double2(a, b); }
+// 256-bit store (sm_100: STG.E.ENL2.256): one whole 32-byte sector per lane and instruction
+BA_D void st4(double* p, double a, double b, double c, double d) {
+  asm volatile("st.global.v4.f64 [%0], {%1, %2, %3, %4};" ::"l"(p), "d"(a), "d"(b), "d"(c), "d"(d) : "memory");
+}
 
 // ---------------------------------------------------------------------------------------
 // pass A
@@ -103,25 +106,23 @@ BA_D void lm_invert(const LmSums<L>& S, bool lm_on, double* Vi, double* bl, doub
   }
 }
 
-// the landmark's record (ba_gpu.h), written by one lane: 16-byte stores into one 128-byte line
+// the landmark's record (ba_gpu.h), written by one lane: four 32-byte stores into one 128-byte line
 template <int L>
 BA_D void lm_write(const DeviceProblem& P, int lm, const LmCtx<L>& c, bool lm_on, const LmSums<L>& S) {
   constexpr int NV = LmSums<L>::NV;
   double Vi[NV], bl[L], dhat[L];
   lm_invert<L>(S, lm_on, Vi, bl, dhat);
   double* o = P.lm_rec + (size_t)lm * kLmRec;
-  st2(o, c.X[0], c.X[1]); st2(o + 2, c.X[2], c.rho);
+  st4(o, c.X[0], c.X[1], c.X[2], c.rho);
   if constexpr (L == 3) {
-    st2(o + 4, Vi[0], Vi[1]); st2(o + 6, Vi[2], Vi[3]); st2(o + 8, Vi[4], Vi[5]);
-    st2(o + 10, dhat[0], dhat[1]); st2(o + 12, dhat[2], 0.0); st2(o + 14, 0.0, 0.0);
+    st4(o + 4, Vi[0], Vi[1], Vi[2], Vi[3]); st4(o + 8, Vi[4], Vi[5], dhat[0], dhat[1]); st4(o + 12, dhat[2], 0.0, 0.0, 0.0);
   } else {
     const double* Gb = S.v + 2; const double* hb = S.v + 8; const double* gb = S.v + 11;
-    st2(o + 4, c.tws_r[0], c.tws_r[1]); st2(o + 6, c.tws_r[2], Vi[0]);
-    st2(o + 8, dhat[0], gb[0]); st2(o + 10, gb[1], gb[2]);
-    st2(o + 12, 0.0, 0.0); st2(o + 14, 0.0, 0.0);
+    st4(o + 4, c.tws_r[0], c.tws_r[1], c.tws_r[2], Vi[0]);
+    st4(o + 8, dhat[0], gb[0], gb[1], gb[2]);
+    st4(o + 12, 0.0, 0.0, 0.0, 0.0);
     double* oc = P.lm_recC + (size_t)lm * kLmRecC;
-    st2(oc, Gb[0], Gb[1]); st2(oc + 2, Gb[2], Gb[3]); st2(oc + 4, Gb[4], Gb[5]);
-    st2(oc + 6, hb[0], hb[1]); st2(oc + 8, hb[2], 0.0); st2(oc + 10, 0.0, 0.0);
+    st4(oc, Gb[0], Gb[1], Gb[2], Gb[3]); st4(oc + 4, Gb[4], Gb[5], hb[0], hb[1]); st4(oc + 8, hb[2], 0.0, 0.0, 0.0);
   }
 #pragma unroll
   for (int i = 0; i < L; ++i) P.lm_bl[(size_t)lm * L + i] = bl[i];
@@ -137,9 +138,8 @@ BA_D void linearize_one(const DeviceProblem& P, const LmCtx<L>& c, int i, int m,
   err += o.n2 * o.w;
   if (o.pm_on) {   // the records are read only through the pose-major lists, which hold exactly these observations
     double* g = P.obs_G + (size_t)i * kObsG;
-    st2(g, o.G[0], o.G[1]); st2(g + 2, o.G[2], o.G[3]); st2(g + 4, o.G[4], o.G[5]); st2(g + 6, 0.0, 0.0);   // whole sectors
-    double* hh = P.obs_h + (size_t)i * kObsH;
-    st2(hh, o.h[0], o.h[1]); st2(hh + 2, o.h[2], 0.0);
+    st4(g, o.G[0], o.G[1], o.G[2], o.G[3]); st4(g + 4, o.G[4], o.G[5], 0.0, 0.0);   // whole sectors
+    st4(P.obs_h + (size_t)i * kObsH, o.h[0], o.h[1], o.h[2], 0.0);
   }
   sums_add<L>(S, o, lm_on);
 }

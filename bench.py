@@ -4,10 +4,12 @@ ms/iter at 1/2/4/8 B200 vs host CPU").
 
 A step is one outer iteration of ba::BundleAdjuster::Solve (reference src/BundleAdjuster.cpp:298-663):
 BuildProblem + Schur complement + reduced camera solve + dogleg step with its residual evaluations.
-Workload (N = 1 and every N of the scaling run): BASELINE configs[1], the synthetic BAL-shaped
-<double,3,6,0> problem (1,778 cameras, 993k points, 5.0M observations); `--workload c4` selects the
-10M-observation problem of configs[3].  With N > 1 (torchrun, one process per GPU) the landmarks are
-sharded across ranks and the partial reduced systems are NCCL-all-reduced: strong scaling.
+Headline workload (N = 1 and every N of the scaling run): BASELINE configs[3], the 10M-observation problem
+north_star quotes its roofline and scaling targets on (10k cameras, 2M landmarks, <double,1,6,0>); BASELINE
+configs[1] (BAL-shaped <double,3,6,0>, 1,778 cameras, 993k points, 5.0M observations) is measured in the same
+run and reported as the keyed block `also.c2` of the same JSON line (`--workload` / `--also` choose).  With
+N > 1 (torchrun, one process per GPU) the landmarks are sharded across ranks and the partial reduced systems
+are all-reduced: strong scaling.
 
   value        whole-job LM iterations/s, inputs resident in HBM, device timeline (CUDA events on the
                solver's stream), max over ranks
@@ -15,8 +17,10 @@ sharded across ranks and the partial reduced systems are NCCL-all-reduced: stron
                K iterations, download of the refined poses/landmarks, all inside the timed region
   roofline     dominant kernel of the Schur build vs the measured HBM copy bandwidth
   cpu_baseline the CPU oracle (port of the reference loop, single-threaded like the reference's
-               projection path) on a bounded sample, N = 1 only
-`--impl reference` times that CPU implementation alone (the reference itself cannot be built here).
+               projection path): 2 iterations of the FULL workload, N = 1 only
+  parity       first two iterations of the end-to-end GPU trace against that oracle run (same problem, same start)
+`--impl reference` times that CPU implementation alone on the full workload (the reference itself cannot be
+built here).
 """
 import argparse
 import json
@@ -119,43 +123,63 @@ def measured_peak():
         return 6650.0, "fallback (B200_PROFILING.md)"
 
 
-def cpu_reference_run(name, steps, warmup, budget_s=150.0):
-    """The CPU implementation of the path (oracle port, 1 thread like the reference's projection loop)."""
+def cpu_reference_run(name, steps, warmup, budget_s=420.0, scale=1.0):
+    """The CPU implementation of the path (oracle port; projection, sparse algebra and solve on 1 thread like the
+    reference, cpp:1345-1347) on the FULL workload (`scale` 1.0).  Only the number of iterations is bounded: when
+    `steps` + `warmup` iterations would not fit `budget_s`, fewer are run and the sample says so."""
     from oracle.oracle_py import Oracle
-    per_iter_full = {"c1": 0.09, "c2": 9.0, "c3": 5.0, "c4": 18.0, "c5": 0.3}[name]   # rough, only to size the sample
-    scale = min(1.0, budget_s / max(1e-9, (steps + warmup) * per_iter_full))
-    scale = max(scale, 0.002)
+    per_iter_full = {"c1": 0.09, "c2": 7.0, "c3": 5.0, "c4": 19.0, "c5": 0.3}[name] * scale   # rough, only to bound the iterations
+    warm = min(warmup, 1)
+    steps_run = max(1, min(steps, int(budget_s / per_iter_full) - warm))
     p = make_workload(name, scale)
-    full = make_counts(name)
     s = Oracle(p.lm_dim, p.pose_dim)
     s.set_options(options_for(s, p, False))
     s.load(p)
-    if warmup:
-        s.solve(warmup)
+    trace = []
+    if warm:
+        s.solve(warm); trace += s.get_trace()
     t0 = time.time()
-    s.solve(steps)
+    s.solve(steps_run)
     dt = time.time() - t0
+    trace += s.get_trace()
     ph, _ = s.get_phase_ms()
     n_res = max(1, p.counts["proj"] + p.counts["binary"] + p.counts["unary"] + p.counts["imu"])
-    frac = n_res / max(1, full)
-    its = steps / dt * frac                       # full-size-equivalent iterations/s (cost ~ linear in residuals)
-    build_ms = (ph["residual"] + ph["median"] + ph["accumulate"] + ph["other_residuals"] + ph["schur"]) / steps / frac
-    return dict(value=its, build_ms=build_ms, ms_per_step=dt / steps * 1e3 / frac, scale=scale, frac=frac,
-                sample="%d iterations on %.4g of the workload (%d residuals), scaled linearly in the residual count" % (steps, frac, n_res),
+    build_ms = (ph["residual"] + ph["median"] + ph["accumulate"] + ph["other_residuals"] + ph["schur"]) / steps_run
+    return dict(value=steps_run / dt, build_ms=build_ms, ms_per_step=dt / steps_run * 1e3, scale=scale, trace=trace,
+                sample="%d timed iteration(s) (%d asked) after %d warm-up on %.4g of the workload (%d residuals): full size, nothing extrapolated"
+                       % (steps_run, steps, warm, scale, n_res),
                 # projection / sparse algebra / solve are serial as in the reference (cpp:1345-1347); only the IMU functor is
                 # spread over threads, like its tbb::parallel_reduce (cpp:1494) — oracle InertialResiduals, same split rule
                 cores=max(1, min(os.cpu_count() or 1, p.counts["imu"] // 8)))
 
 
+def trace_parity(gpu_trace, cpu_trace, n=2):
+    """Largest relative difference between the first `n` outer iterations of the GPU trace (end-to-end Solve() from the
+    initial state) and the CPU oracle's on the same full-size problem."""
+    keys = ("pre_solve_norm", "post_solve_norm", "median_maha", "proj_error_build", "delta_norm", "gn_norm", "sd_norm")
+    per_key = {}
+    m = min(n, len(gpu_trace), len(cpu_trace))
+    for i in range(m):
+        for k in keys:
+            a, b = gpu_trace[i][k], cpu_trace[i][k]
+            per_key[k] = max(per_key.get(k, 0.0), abs(a - b) / max(abs(b), 1e-300))
+    cost_keys = ("pre_solve_norm", "post_solve_norm", "median_maha", "proj_error_build")
+    return {"iterations_compared": m, "max_rel_diff_costs": max([per_key[k] for k in cost_keys] or [0.0]),
+            "max_rel_diff_steps": max([per_key[k] for k in keys if k not in cost_keys] or [0.0]), "per_key": per_key,
+            "note": "costs, median and build errors are conditioning-free; the step norms inherit cond(S) * 2^-53 from the reduced solve (a long camera chain with two fixed cameras is gauge-weak)",
+            "against": "CPU oracle (port of the reference loop, parity unpinned) on the same full-size problem, same initial state"}
+
+
 def l2_note(name, scale):
     """Timing rule: inputs larger than L2, or say that they are not.  Per iteration the build streams the landmark-sorted
-    observations (40 B each) and writes + reads one record per observation (28 doubles for LmSize 3, 40 for LmSize 1)."""
+    observations (40 B each), writes and re-reads a 96-byte linearisation per observation (G and h records) and one
+    128-byte record per landmark."""
     n = make_counts(name) * scale
     if name == "c5":
         n = 0
-    mb = n * (40 + 8 * (28 if name == "c2" else 40)) / 1e6
+    mb = n * (40 + 8 + 96) / 1e6
     if mb > 126:
-        return "inputs larger than L2: every iteration streams %.0f MB of sorted observations and records (L2 = 126 MB)" % mb
+        return "inputs larger than L2: every iteration streams %.0f MB of sorted observations and linearisation records (L2 = 126 MB)" % mb
     return ("working set of the build (%.0f MB) fits in L2, no flush between iterations: this configuration is "
             "launch/latency-bound (SURVEY 8d), its number is not an HBM figure" % mb)
 
@@ -164,51 +188,19 @@ def make_counts(name):
     return {"c1": 100000, "c2": 5000000, "c3": 2000499, "c4": 10000000, "c5": 21200}[name]
 
 
-def main():
-    ap = argparse.ArgumentParser()
-    ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=10)
-    ap.add_argument("--warmup", type=int, default=3)
-    ap.add_argument("--impl", default="ba_b200")
-    ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS))
-    ap.add_argument("--scale", type=float, default=1.0, help="shrink the workload (development only; invalidates the number)")
-    ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--no-e2e", action="store_true", help="development / profiler runs only: skip the end-to-end leg (the line then has no e2e)")
-    args = ap.parse_args()
-    rank = int(os.environ.get("RANK", "0")); world = int(os.environ.get("WORLD_SIZE", "1")); local_rank = int(os.environ.get("LOCAL_RANK", "0"))
-    K, W = max(1, args.steps), max(0, args.warmup)
-    name = args.workload
-    base = {"metric": "lm_iterations_per_sec", "unit": "iter/s", "n_gpus": args.gpus, "steps": K, "warmup": W,
-            "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": {"workload": WORKLOADS[name]["desc"] + (" (scale %.3g)" % args.scale if args.scale != 1.0 else ""),
-                       "solver": "dogleg, nested-dissection tile LDL^T (dataflow kernel)", "sharding": "landmarks over %d GPU(s)" % args.gpus,
-                       "l2": l2_note(name, args.scale)}}
+def config_for(name, scale, gpus):
+    return {"workload": WORKLOADS[name]["desc"] + (" (scale %.3g)" % scale if scale != 1.0 else ""),
+            "solver": "dogleg, nested-dissection tile LDL^T (dataflow kernel)", "sharding": "landmarks over %d GPU(s)" % gpus,
+            "l2": l2_note(name, scale)}
 
-    if args.impl == "reference":
-        if rank != 0:
-            return
-        r = cpu_reference_run(name, K, W)
-        out = dict(base)
-        out.update({"impl": "reference", "value": r["value"], "ms_per_step": r["ms_per_step"], "n_gpus": args.gpus,
-                    "schur_build_ms_per_iter": r["build_ms"], "gpu_launches": 0, "scaling": "strong",
-                    "cpu_baseline": {"value": r["value"], "unit": "iter/s", "cores": r["cores"], "kind": "port", "sample": r["sample"],
-                                     "note": "the reference is unbuildable here (Eigen3/Sophus/Calibu/TBB absent); its projection path is single-threaded (src/BundleAdjuster.cpp:1345-1347); only the IMU functor is threaded, as under its tbb::parallel_reduce (cpp:1494): `cores` = those threads, 1 when there are no IMU residuals"},
-                    "e2e": {"value": r["value"], "unit": "iter/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}})
-        print(json.dumps(out))
-        return
 
-    # stdout carries exactly one line (the JSON): NCCL writes its version banner there unless told otherwise
-    if os.environ.get("NCCL_DEBUG", "VERSION").upper() == "VERSION":
-        os.environ["NCCL_DEBUG"] = "WARN"
+def run_gpu_workload(name, args, K, W, rank, world, local_rank, with_e2e, with_cpu):
+    """One workload through the CUDA path: device-resident iterations (value), end-to-end Solve() (e2e), roofline of the
+    build, and (N = 1) the CPU oracle on the same full-size problem with a trace comparison."""
     import torch
     import torch.distributed as dist
     from ba_b200.capi import BundleAdjusterGPU
     from ba_b200.dist import init_nccl_for
-    if not torch.cuda.is_available():
-        raise SystemExit("bench.py needs a CUDA device: the product path has no CPU fallback")
-    torch.cuda.set_device(local_rank)
-    if world > 1:
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     p = make_workload(name, args.scale)
     a = p.arrays()
     L, d = p.lm_dim, p.pose_dim
@@ -235,7 +227,7 @@ def main():
         sm = s.solve(K)
         barrier()
     if sm.iterations != K or sm.result in (4, 5):
-        raise SystemExit("bench.py: the timed Solve() stopped after %d of %d iterations (result %d): no number" % (sm.iterations, K, sm.result))
+        raise SystemExit("bench.py: the timed Solve() of %s stopped after %d of %d iterations (result %d): no number" % (name, sm.iterations, K, sm.result))
     ph, launches = s.get_phase_ms()
     t_ms = torch.tensor([ph["total"]], dtype=torch.float64, device="cuda")
     if world > 1:
@@ -264,13 +256,13 @@ def main():
             pass
         roofline = {"bound": "hbm", "kernel": dom, "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak, "traffic": traffic,
                     "algorithmic_bytes_per_launch": per_kernel[dom] / world, "launch_ms": kt[dom], "peak_source": peak_src,
-                    "note": "achieved = SURVEY 8d algorithmic bytes of this kernel / its CUDA-event time; the kernel gathers each record once per pose pair from L2 (DESIGN.md 4)",
+                    "note": "achieved = SURVEY 8d algorithmic bytes of this kernel / its CUDA-event time; the kernel gathers a 64-byte record per observation of a pose pair and 80 bytes of the landmark record from L2 (DESIGN.md 4)",
                     "build": {"algorithmic_bytes": tot_b / world, "ms": t_build, "achieved": tot_b / world / (t_build * 1e-3) / 1e9,
                               "frac": tot_b / world / (t_build * 1e-3) / 1e9 / peak, "kernel_ms": kt, "kernel_bytes": per_kernel, "nnzb_S": nnzb}}
     s.close()
 
-    e2e_its, e2e_times, h2d, d2h = None, [], 0, 0
-    if not args.no_e2e:
+    e2e_its, e2e_times, h2d, d2h, e2e_trace = None, [], 0, 0, None
+    if with_e2e:
         # ---- e2e: host buffers in, refined state out, every call ------------------------------------------
         # The caller's arrays live in page-locked host memory (bagpu_host_alloc, what include/ba/BundleAdjuster.h keeps
         # its observation buffers in); everything from handing them to the ABI to reading the refined state is timed.
@@ -297,6 +289,7 @@ def main():
             if sm3.iterations != K:
                 raise SystemExit("bench.py: the e2e Solve() stopped after %d of %d iterations" % (sm3.iterations, K))
             res = s3.get_poses(); lm = s3.get_landmarks(out=lm_out) if L else None
+            e2e_trace = s3.get_trace()
             barrier()
             t_e2e = torch.tensor([time.time() - t0], dtype=torch.float64, device="cuda")
             if world > 1:
@@ -308,21 +301,83 @@ def main():
         del pp
         release_pinned()
 
+    out = None
     if rank == 0:
-        out = dict(base)
-        out.update({"value": K / (total_ms * 1e-3), "ms_per_step": total_ms / K, "schur_build_ms_per_iter": build_ms,
-                    "phases_ms_per_iter": {k: v / K for k, v in ph.items() if k != "total"},
-                    "gpu_launches": int(launches), "clocks": clk.summary(),
-                    "e2e": {"value": e2e_its, "unit": "iter/s", "h2d_bytes_per_step": h2d / K, "d2h_bytes_per_step": d2h / K,
-                            "seconds": e2e_times, "note": "median of 3; one Solve(K) call from page-locked host arrays: upload of the whole problem + symbolic set-up on the device + K iterations + download of the refined poses and landmarks"},
-                    "final_cost": trace[-1]["post_solve_norm"] if trace else None,
-                    "first_cost": trace[0]["pre_solve_norm"] if trace else None})
+        out = {"value": K / (total_ms * 1e-3), "ms_per_step": total_ms / K, "schur_build_ms_per_iter": build_ms,
+               "phases_ms_per_iter": {k: v / K for k, v in ph.items() if k != "total"},
+               "gpu_launches": int(launches), "clocks": clk.summary(),
+               "final_cost": trace[-1]["post_solve_norm"] if trace else None,
+               "first_cost": trace[0]["pre_solve_norm"] if trace else None}
+        if with_e2e:
+            out["e2e"] = {"value": e2e_its, "unit": "iter/s", "h2d_bytes_per_step": h2d / K, "d2h_bytes_per_step": d2h / K,
+                          "seconds": e2e_times, "note": "median of 3; one Solve(K) call from page-locked host arrays: upload of the whole problem + symbolic set-up on the device + K iterations + download of the refined poses and landmarks"}
         if roofline:
             out["roofline"] = roofline
-        if world == 1 and not args.no_cpu_baseline:
-            r = cpu_reference_run(name, 2, 0, budget_s=25.0)
+        if with_cpu:
+            # the CPU oracle on the SAME full-size problem: 2 iterations from the same initial state, timed, and its
+            # trace compared with the end-to-end GPU run's (full-size parity, not only the minis of tests/)
+            r = cpu_reference_run(name, 2, 0, scale=args.scale)
             out["cpu_baseline"] = {"value": r["value"], "unit": "iter/s", "cores": r["cores"], "kind": "port", "sample": r["sample"],
                                    "schur_build_ms_per_iter": r["build_ms"]}
+            if e2e_trace:
+                out["parity"] = trace_parity(e2e_trace, r["trace"], 2)
+    return out
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ba_b200")
+    ap.add_argument("--workload", default="c4", choices=sorted(WORKLOADS),
+                    help="headline workload; default c4 = the 10M-observation problem north_star quotes its targets on")
+    ap.add_argument("--also", default="c2", help="second workload reported as a keyed block of the same line ('' = none)")
+    ap.add_argument("--scale", type=float, default=1.0, help="shrink the workload (development only; invalidates the number)")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true", help="development / profiler runs only: skip the end-to-end leg (the line then has no e2e)")
+    args = ap.parse_args()
+    rank = int(os.environ.get("RANK", "0")); world = int(os.environ.get("WORLD_SIZE", "1")); local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    K, W = max(1, args.steps), max(0, args.warmup)
+    name = args.workload
+    base = {"metric": "lm_iterations_per_sec", "unit": "iter/s", "n_gpus": args.gpus, "steps": K, "warmup": W,
+            "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": config_for(name, args.scale, args.gpus)}
+
+    if args.impl == "reference":
+        if rank != 0:
+            return
+        r = cpu_reference_run(name, K, W, scale=args.scale)
+        out = dict(base)
+        out.update({"impl": "reference", "value": r["value"], "ms_per_step": r["ms_per_step"], "n_gpus": args.gpus,
+                    "schur_build_ms_per_iter": r["build_ms"], "gpu_launches": 0, "scaling": "strong",
+                    "cpu_baseline": {"value": r["value"], "unit": "iter/s", "cores": r["cores"], "kind": "port", "sample": r["sample"],
+                                     "note": "the reference is unbuildable here (Eigen3/Sophus/Calibu/TBB absent); its projection path is single-threaded (src/BundleAdjuster.cpp:1345-1347); only the IMU functor is threaded, as under its tbb::parallel_reduce (cpp:1494): `cores` = those threads, 1 when there are no IMU residuals"},
+                    "e2e": {"value": r["value"], "unit": "iter/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}})
+        print(json.dumps(out))
+        return
+
+    # stdout carries exactly one line (the JSON): NCCL writes its version banner there unless told otherwise
+    if os.environ.get("NCCL_DEBUG", "VERSION").upper() == "VERSION":
+        os.environ["NCCL_DEBUG"] = "WARN"
+    import torch
+    import torch.distributed as dist
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: the product path has no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    with_cpu = world == 1 and not args.no_cpu_baseline
+    head = run_gpu_workload(name, args, K, W, rank, world, local_rank, not args.no_e2e, with_cpu)
+    second = None
+    if args.also and args.also != name:
+        second = run_gpu_workload(args.also, args, K, W, rank, world, local_rank, not args.no_e2e, with_cpu)
+    if rank == 0:
+        out = dict(base)
+        out.update(head)
+        if second is not None:
+            second["config"] = config_for(args.also, args.scale, args.gpus)
+            out["also"] = {args.also: second}
         print(json.dumps(out))
     if world > 1:
         dist.destroy_process_group()
