@@ -58,9 +58,12 @@ template <typename T>
 struct DevBuf {
   T* p = nullptr;
   size_t n = 0;
+  bool view = false;   // p points into memory owned by somebody else (the peer-mapped system window)
   ~DevBuf() { release(); }
-  void release() { if (p) dev_free(p); p = nullptr; n = 0; }
+  void release() { if (p && !view) dev_free(p); p = nullptr; n = 0; view = false; }
+  void adopt(T* ptr, size_t count) { release(); p = ptr; n = count; view = true; }
   void alloc(size_t count) {
+    if (view) release();
     if (count <= n && p) return;
     release();
     if (count == 0) count = 1;
@@ -311,7 +314,9 @@ struct bagpu_handle_s {
 
   // ---- multi-GPU ----
   void* comm = nullptr;
-  PeerReduce peer;   // small reductions over NVLink peer memory (peer_reduce.h); bulk ones go through NCCL
+  PeerReduce peer;   // small reductions over NVLink peer memory (peer_reduce.h)
+  PeerBulk bulk;     // the reduced system (S tiles | b_p | rhs_sc) in one peer-mapped allocation; NCCL when it cannot be mapped
+  std::vector<int> red_slots; DevBuf<int> d_red_slots;   // tile slots of the symbolic pattern (fill tiles are zero on every rank)
   int rank = 0, world = 1;
 
   // =======================================================================================
@@ -525,6 +530,7 @@ struct bagpu_handle_s {
       for (auto& r : pp) std::sort(r.begin(), r.end());
       rows.swap(pp);
     }
+    const std::vector<std::vector<int>> pattern_rows = rows;   // before fill: the tiles the build can write
     // fill: eliminating tile row k couples every pair of its columns.  It is enough to merge the columns behind the
     // first one into the row of the first one (its parent in the elimination tree): the parent passes them on.
     {
@@ -547,6 +553,11 @@ struct bagpu_handle_s {
       row_col.insert(row_col.end(), rows[k].begin(), rows[k].end());
       row_ptr[k + 1] = (int)row_col.size();
       max_row = std::max(max_row, row_ptr[k + 1] - row_ptr[k]);
+    }
+    red_slots.clear();
+    for (int k = 0; k < nT; ++k) {
+      red_slots.push_back(tile_slot(k, k));
+      for (int b : pattern_rows[k]) red_slots.push_back(tile_slot(k, b));
     }
   }
 
@@ -654,8 +665,20 @@ struct bagpu_handle_s {
     pc.lap("  upload: allocs");
     // reduced system
     const size_t tsz = (size_t)T * T;
-    d_S.alloc((size_t)n_tiles * tsz); d_uinv.alloc((size_t)nT * tsz); d_scratch.alloc(3 * (size_t)nT * T + 2 * (size_t)n_tiles * T);
-    d_bp.alloc((size_t)nT * T); d_rhs_sc.alloc((size_t)nT * T); d_rhs_work.alloc((size_t)nT * T);
+    d_uinv.alloc((size_t)nT * tsz); d_scratch.alloc(3 * (size_t)nT * T + 2 * (size_t)n_tiles * T);
+    d_rhs_work.alloc((size_t)nT * T);
+    {
+      // the system the ranks sum: S tiles | b_p | rhs_sc, in one peer-mapped allocation when the windows work
+      const size_t nS = (size_t)n_tiles * tsz, nV = (size_t)nT * T;
+      ensure_bulk_window((nS + 2 * nV) * sizeof(double));
+      if (bulk.ok) {
+        double* b = bulk.base[rank];
+        d_S.adopt(b, nS); d_bp.adopt(b + nS, nV); d_rhs_sc.adopt(b + nS + nV, nV);
+        d_red_slots.upload(red_slots, st);
+      } else {
+        d_S.alloc(nS); d_bp.alloc(nV); d_rhs_sc.alloc(nV);
+      }
+    }
     d_row_ptr.upload(row_ptr, st); d_row_col.upload(row_col, st); d_tile_perm.upload(tile_perm, st);
     d_tile_map.alloc((size_t)nT * nT); launch_fill_tile_map(d_row_ptr.p, d_row_col.p, nT, d_tile_map.p, st);
     {
@@ -714,6 +737,40 @@ struct bagpu_handle_s {
     finish_task_packing();
     pc.lap("  task packing (join)");
     dirty = false;
+  }
+
+  // (Re)allocate the peer-mapped system window; every rank calls this with the same size at the same point of Solve().
+  void ensure_bulk_window(size_t bytes) {
+    if (world <= 1 || !peer.ok || getenv("BAGPU_NO_BULK")) return;
+    if (bulk.ok && bulk.cap_bytes >= bytes) return;
+    DevBuf<unsigned int> d_tab; d_tab.alloc((size_t)world * 16 + 1);
+    if (bulk.base[rank] || bulk.ok) {   // unmap, meet, free (a window may be freed only after every importer has unmapped it)
+      d_S.release(); d_bp.release(); d_rhs_sc.release();
+      bulk.close_peers();
+      d_tab.zero(st); allreduce_u32(d_tab.p, 1); sync();
+      bulk.destroy();
+    }
+    const size_t cap = ((bytes + bytes / 4) + ((size_t)2 << 20) - 1) / ((size_t)2 << 20) * ((size_t)2 << 20);
+    std::vector<unsigned int> tab((size_t)world * 16 + 1, 0u);
+    bool mine = bulk.create_local(rank, world, cap, &tab[(size_t)rank * 16]) == cudaSuccess;
+    if (!mine) { cudaGetLastError(); memset(&tab[(size_t)rank * 16], 0, 64); }
+    CU(cudaMemcpyAsync(d_tab.p, tab.data(), tab.size() * 4, cudaMemcpyHostToDevice, st));
+    nccl_allreduce_u32(d_tab.p, tab.size());
+    CU(cudaMemcpyAsync(tab.data(), d_tab.p, tab.size() * 4, cudaMemcpyDeviceToHost, st));
+    sync();
+    const bool opened = mine && bulk.open_peers(tab.data());
+    unsigned int vote = opened ? 1u : 0u;
+    CU(cudaMemcpyAsync(d_tab.p, &vote, 4, cudaMemcpyHostToDevice, st));
+    nccl_allreduce_u32(d_tab.p, 1);
+    CU(cudaMemcpyAsync(&vote, d_tab.p, 4, cudaMemcpyDeviceToHost, st));
+    sync();
+    if (vote == (unsigned int)world) bulk.ok = true;
+    else { bulk.close_peers(); nccl_allreduce_u32(d_tab.p, 1); sync(); bulk.destroy(); }
+    if (getenv("BAGPU_TIMING")) fprintf(stderr, "[bagpu] rank %d: peer-mapped system window %s (%.1f MB)\n", rank, bulk.ok ? "on" : "off (NCCL)", cap / 1e6);
+  }
+  void nccl_allreduce_u32(unsigned int* buf, size_t n) {
+    int rc = g_nccl.allReduce(buf, buf, n, kNcclUint32, kNcclSum, comm, st);
+    if (rc != 0) throw std::string("ncclAllReduce(u32) failed");
   }
 
   // ---- work items of the pose-pair-major reduction (schur_kernels.cu): the device builds the pair
@@ -862,7 +919,13 @@ struct bagpu_handle_s {
     if (n_items) { launch_reduce_blocks(P, d_items.p, n_items, d_pairs, d_pairs + n_pairs, d_pairs + 2 * n_pairs, d_partial.p, d_counters.p + 1, d_counters.p, st); ++launches; }
     if (n_items_sym) { launch_reduce_blocks(P, d_items_sym.p, n_items_sym, d_pairs, d_pairs + n_pairs, d_pairs + 2 * n_pairs, d_partial.p, d_counters.p + 1, d_counters.p, st); ++launches; }
     CU(cudaEventRecord(ev[5], st));
-    if (world > 1) {
+    if (world > 1 && bulk.ok) {
+      // the error sums over the small windows double as the barrier "every rank has built its partial system"; then
+      // the fused reduce-scatter + all-gather over peer memory, then the barrier "every owner has delivered"
+      allreduce_f64(&d_sc.p->proj_error, 8);
+      bulk.allreduce(d_red_slots.p, (int)red_slots.size(), T * T, (size_t)n_tiles * T * T, 2 * (size_t)nT * T, sms, st); ++launches;
+      allreduce_u32(&d_sel.p->hist[0], 1);
+    } else if (world > 1) {
       // one NCCL group: the four reductions share a single launch
       const bool grp = g_nccl.groupStart && g_nccl.groupEnd;
       if (grp) g_nccl.groupStart();
@@ -956,7 +1019,7 @@ struct bagpu_handle_s {
   // EvaluateResiduals at the current state (cpp:144-274); returns the four sums
   void evaluate(double* e_proj, double* e_bin, double* e_un, double* e_in) {
     CU(cudaMemsetAsync(&d_sc.p->eval_proj, 0, 4 * sizeof(double), st));
-    launch_evaluate(P, G, &d_sc.p->eval_proj, nullptr, nullptr, 1, st); if (n_obs) ++launches;
+    launch_evaluate(P, G, &d_sc.p->eval_proj, nullptr, nullptr, 1, 1, st); if (n_obs) ++launches;
     maha0_valid = false;   // overwritten with this state's values; valid for the next build only if the step is kept
     if (rank == 0) launch_other_evaluate(P, R, st, &launches);
     if (world > 1) allreduce_f64(&d_sc.p->eval_proj, 4);
@@ -1282,7 +1345,7 @@ struct bagpu_handle_s {
     d_res_out.alloc(2 * nt); d_maha_out.alloc(nt);
     if (world > 1) { d_res_out.zero(st); d_maha_out.zero(st); }
     CU(cudaMemsetAsync(&d_sc.p->dot[5], 0, sizeof(double), st));
-    launch_evaluate(P, G, &d_sc.p->dot[5], d_res_out.p, d_maha_out.p, 0, st); ++launches;
+    launch_evaluate(P, G, &d_sc.p->dot[5], d_res_out.p, d_maha_out.p, 0, 0, st); ++launches;
   }
 
   void export_residuals(double* res2, double* weight, double* maha) {
@@ -1378,6 +1441,8 @@ void bagpu_destroy(bagpu_handle h) {
     // the other ranks in one tiny NCCL all-reduce before freeing.  The wait is bounded: if the others never come (a
     // rank died) the window and the communicator are abandoned instead of hanging the caller.
     h->peer.close_peers();
+    h->d_S.release(); h->d_bp.release(); h->d_rhs_sc.release();   // views into the bulk window
+    h->bulk.close_peers();
     try {
       DevBuf<unsigned int> one; one.alloc(1); one.zero(h->st);
       h->allreduce_u32(one.p, 1);
@@ -1392,6 +1457,7 @@ void bagpu_destroy(bagpu_handle h) {
   h->join_packer();
   if (comm_stuck) return;   // abandon the handle (freeing its buffers would wait for the pending collective): the job is failing anyway
   h->peer.destroy();
+  h->bulk.destroy();
   if (h->comm && g_nccl.commDestroy) g_nccl.commDestroy(h->comm);
   if (h->ev_ok) for (auto& e : h->ev) cudaEventDestroy(e);
   if (h->d_pairs) dev_free(h->d_pairs);

@@ -257,7 +257,7 @@ BA_D void invert(double* M, double* I) {
 }
 
 template <int D>
-BA_D void imu_build_one(const DeviceProblem& P, const OtherResiduals& R, int i) {
+BA_D double imu_build_one(const DeviceProblem& P, const OtherResiduals& R, int i) {   // returns this residual's share of inertial_error
   const int p1 = (int)R.imu_p1[i], p2 = (int)R.imu_p2[i];
   ImuState s1, s2, y;
   double b1[6], b2[6];
@@ -373,8 +373,7 @@ BA_D void imu_build_one(const DeviceProblem& P, const OtherResiduals& R, int i) 
   if (o2 >= 0) { const uint32_t fr = P.pose_free[p2]; for (int k = 0; k < D; ++k) if (!((fr >> k) & 1u)) for (int rr = 0; rr < D; ++rr) J2[rr * D + k] = 0.0; }
   for (int k = 0; k < D * D; ++k) { J1o[k] = (o1 >= 0) ? J1[k] : 0.0; J2o[k] = (o2 >= 0) ? J2[k] : 0.0; }
   for (int k = 0; k < D; ++k) ro[k] = r[k];
-  if (!have_proj) return;   // Q3: nothing is written to r_i_ / J_i without projection residuals
-  red_add(&P.sc->inertial_error, maha * weight);
+  if (!have_proj) return 0.0;   // Q3: nothing is written to r_i_ / J_i without projection residuals
   // U and b_p: J^T C J, J^T C r
   double Cr[D];
   for (int rr = 0; rr < D; ++rr) { double s = 0.0; for (int c = 0; c < D; ++c) s += Ci[rr * D + c] * r[c]; Cr[rr] = s; }
@@ -396,11 +395,12 @@ BA_D void imu_build_one(const DeviceProblem& P, const OtherResiduals& R, int i) 
       for (int c = 0; c < D; ++c) for (int rr = 0; rr < D; ++rr) { double s = 0.0; for (int k = 0; k < D; ++k) s += Ja[k * D + rr] * CJ[k * D + c]; red_add(xb.p + (size_t)rr * xb.rs + (size_t)c * xb.cs, s); }
     }
   }
+  return maha * weight;
 }
 
 template <int D>
-BA_D void imu_sd_one(const DeviceProblem& P, const OtherResiduals& R, int i) {
-  if (!(P.sc->dot[7] > 0.5)) return;
+BA_D double imu_sd_one(const DeviceProblem& P, const OtherResiduals& R, int i) {
+  if (!(P.sc->dot[7] > 0.5)) return 0.0;
   const int o1 = P.pose_opt[R.imu_p1[i]], o2 = P.pose_opt[R.imu_p2[i]];
   const double* J1 = R.imu_J1 + (size_t)i * D * D;
   const double* J2 = R.imu_J2 + (size_t)i * D * D;
@@ -414,11 +414,11 @@ BA_D void imu_sd_one(const DeviceProblem& P, const OtherResiduals& R, int i) {
   }
   double s = 0.0;
   for (int r = 0; r < D; ++r) for (int c = 0; c < D; ++c) s += v[r] * C[r * D + c] * v[c];
-  red_add(&P.sc->sd_den_other, s);
+  return s;
 }
 
 template <int D>
-BA_D void imu_eval_one(const DeviceProblem& P, const OtherResiduals& R, int i) {
+BA_D double imu_eval_one(const DeviceProblem& P, const OtherResiduals& R, int i) {
   const int p1 = (int)R.imu_p1[i], p2 = (int)R.imu_p2[i];
   ImuState s1, s2, y, yn;
   double b1[6], b2[6];
@@ -437,7 +437,7 @@ BA_D void imu_eval_one(const DeviceProblem& P, const OtherResiduals& R, int i) {
   const double* C = R.imu_cov_inv + (size_t)i * D * D;
   double s = 0.0;
   for (int rr = 0; rr < D; ++rr) for (int c = 0; c < D; ++c) s += r[rr] * C[rr * D + c] * r[c];
-  red_add(&P.sc->eval_inertial, s);
+  return s;
 }
 
 }  // namespace bagpu

@@ -93,7 +93,8 @@ void launch_reduce_blocks(const DeviceProblem& P, const ReduceItem* items, int n
 void launch_sd_denominator(const DeviceProblem& P, int G, cudaStream_t st);
 void launch_back_substitute(const DeviceProblem& P, const uint2* tasks, int n_tasks, const uint32_t* long_lms, int n_long, const double* delta_p,
                             double* delta_l, cudaStream_t st);
-void launch_evaluate(const DeviceProblem& P, int G, double* out_sum, double* res_out, double* maha_out, int write_maha0, cudaStream_t st);
+void launch_evaluate(const DeviceProblem& P, int G, double* out_sum, double* res_out, double* maha_out, int write_maha0, int count_outliers,
+                     cudaStream_t st);
 void launch_update_poses(const DeviceProblem& P, const double* delta_p, double coef, cudaStream_t st);
 void launch_update_landmarks(const DeviceProblem& P, const double* delta_l, double coef, cudaStream_t st);
 void launch_mask_diagonal(const DeviceProblem& P, const uint8_t* mask_used, int global_flag, cudaStream_t st);

@@ -97,9 +97,11 @@ BA_D void binary_eval(const DeviceProblem& P, const OtherResiduals& R, int i, Bi
   if (e.o2 >= 0) mask_cols6(e.J2, P.pose_free[p2]);
 }
 
-__global__ void k_binary_build(DeviceProblem P, OtherResiduals R) {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= R.n_binary) return;
+// Scalar sums of these kernels (errors, evaluation sums, the steepest-descent denominator) go through grid_sum_fixed:
+// fixed summation order, so every rank and every run gets the same bits (the step control branches on them).
+__global__ void __launch_bounds__(64) k_binary_build(DeviceProblem P, OtherResiduals R) {
+  double acc[1] = {0.0};
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < R.n_binary; i += gridDim.x * blockDim.x) {
   BinEval e;
   binary_eval(P, R, i, e, true);
   const double* C = R.bin_cov_inv + 36 * (size_t)i;
@@ -109,7 +111,7 @@ __global__ void k_binary_build(DeviceProblem P, OtherResiduals R) {
   // binary_error_ += (r_w^T cov_inv r_w) * weight with r_w = sqrtm(cov_inv) r  (quirk Q7) = |cov_inv r|^2
   double m = 0.0;
   for (int r = 0; r < 6; ++r) m += Cr[r] * Cr[r];
-  red_add(&P.sc->binary_error, m * wgt);
+  acc[0] += m * wgt;
   if (e.o1 >= 0) {
     add_jtcj(P, e.o1, e.o1, e.J1, C, e.J1, wgt);
     for (int c = 0; c < 6; ++c) { double s = 0.0; for (int k = 0; k < 6; ++k) s += e.J1[6 * k + c] * Cr[k]; red_add(P.b_p + (size_t)e.o1 * P.D + c, wgt * s); }
@@ -122,30 +124,36 @@ __global__ void k_binary_build(DeviceProblem P, OtherResiduals R) {
     if (e.o1 < e.o2) add_jtcj(P, e.o1, e.o2, e.J1, C, e.J2, wgt);
     else add_jtcj(P, e.o2, e.o1, e.J2, C, e.J1, wgt);
   }
+  }
+  grid_sum_fixed<1>(acc, P.red_partial, P.red_counter, &P.sc->binary_error, true);
 }
 
-__global__ void k_binary_sd(DeviceProblem P, OtherResiduals R) {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= R.n_binary) return;
-  BinEval e;
-  binary_eval(P, R, i, e, true);
-  double v[6] = {0, 0, 0, 0, 0, 0};
-  if (e.o1 >= 0) for (int r = 0; r < 6; ++r) for (int k = 0; k < 6; ++k) v[r] += e.J1[6 * r + k] * P.b_p[(size_t)e.o1 * P.D + k];
-  if (e.o2 >= 0) for (int r = 0; r < 6; ++r) for (int k = 0; k < 6; ++k) v[r] += e.J2[6 * r + k] * P.b_p[(size_t)e.o2 * P.D + k];
-  const double* C = R.bin_cov_inv + 36 * (size_t)i;
-  double s = 0.0;
-  for (int r = 0; r < 6; ++r) for (int k = 0; k < 6; ++k) s += v[r] * C[6 * r + k] * v[k];
-  red_add(&P.sc->sd_den_other, s);
+__global__ void __launch_bounds__(64) k_binary_sd(DeviceProblem P, OtherResiduals R) {
+  double acc[1] = {0.0};
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < R.n_binary; i += gridDim.x * blockDim.x) {
+    BinEval e;
+    binary_eval(P, R, i, e, true);
+    double v[6] = {0, 0, 0, 0, 0, 0};
+    if (e.o1 >= 0) for (int r = 0; r < 6; ++r) for (int k = 0; k < 6; ++k) v[r] += e.J1[6 * r + k] * P.b_p[(size_t)e.o1 * P.D + k];
+    if (e.o2 >= 0) for (int r = 0; r < 6; ++r) for (int k = 0; k < 6; ++k) v[r] += e.J2[6 * r + k] * P.b_p[(size_t)e.o2 * P.D + k];
+    const double* C = R.bin_cov_inv + 36 * (size_t)i;
+    double s = 0.0;
+    for (int r = 0; r < 6; ++r) for (int k = 0; k < 6; ++k) s += v[r] * C[6 * r + k] * v[k];
+    acc[0] += s;
+  }
+  grid_sum_fixed<1>(acc, P.red_partial, P.red_counter, &P.sc->sd_den_other, true);
 }
 
-__global__ void k_binary_eval(DeviceProblem P, OtherResiduals R) {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= R.n_binary) return;
-  BinEval e;
-  binary_eval(P, R, i, e, false);
-  double s = 0.0;
-  for (int r = 0; r < 6; ++r) s += e.r[r] * e.r[r];
-  red_add(&P.sc->eval_binary, s * R.bin_weight[i]);
+__global__ void __launch_bounds__(64) k_binary_eval(DeviceProblem P, OtherResiduals R) {
+  double acc[1] = {0.0};
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < R.n_binary; i += gridDim.x * blockDim.x) {
+    BinEval e;
+    binary_eval(P, R, i, e, false);
+    double s = 0.0;
+    for (int r = 0; r < 6; ++r) s += e.r[r] * e.r[r];
+    acc[0] += s * R.bin_weight[i];
+  }
+  grid_sum_fixed<1>(acc, P.red_partial, P.red_counter, &P.sc->eval_binary, true);
 }
 
 // ---- unary --------------------------------------------------------------------------------------
@@ -190,100 +198,107 @@ __global__ void k_unary_maha(DeviceProblem P, OtherResiduals R) {
   R.un_maha[i] = s;
 }
 
-__global__ void k_unary_build(DeviceProblem P, OtherResiduals R) {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= R.n_unary) return;
-  UnEval e;
-  unary_eval(P, R, i, e, true);
-  const double c_huber = 1.2107 * sqrt(P.sc->unary_median);
-  const double em = sqrt(R.un_maha[i]);
-  const double weight = (em > c_huber) ? c_huber / em : 1.0;
-  double* C = R.un_cov_inv + 36 * (size_t)i;
-  for (int k = 0; k < 36; ++k) C[k] *= weight;   // persists across iterations (quirk Q6)
-  double Cr[6];
-  for (int r = 0; r < 6; ++r) { double s = 0.0; for (int k = 0; k < 6; ++k) s += C[6 * r + k] * e.r[k]; Cr[r] = s; }
-  double m = 0.0;
-  for (int r = 0; r < 6; ++r) m += e.r[r] * Cr[r];
-  red_add(&P.sc->unary_error, m);
-  if (e.o >= 0) {
-    add_jtcj(P, e.o, e.o, e.J, C, e.J, 1.0);
-    for (int c = 0; c < 6; ++c) { double s = 0.0; for (int k = 0; k < 6; ++k) s += e.J[6 * k + c] * Cr[k]; red_add(P.b_p + (size_t)e.o * P.D + c, s); }
+__global__ void __launch_bounds__(64) k_unary_build(DeviceProblem P, OtherResiduals R) {
+  double acc[1] = {0.0};
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < R.n_unary; i += gridDim.x * blockDim.x) {
+    UnEval e;
+    unary_eval(P, R, i, e, true);
+    const double c_huber = 1.2107 * sqrt(P.sc->unary_median);
+    const double em = sqrt(R.un_maha[i]);
+    const double weight = (em > c_huber) ? c_huber / em : 1.0;
+    double* C = R.un_cov_inv + 36 * (size_t)i;
+    for (int k = 0; k < 36; ++k) C[k] *= weight;   // persists across iterations (quirk Q6)
+    double Cr[6];
+    for (int r = 0; r < 6; ++r) { double s = 0.0; for (int k = 0; k < 6; ++k) s += C[6 * r + k] * e.r[k]; Cr[r] = s; }
+    double m = 0.0;
+    for (int r = 0; r < 6; ++r) m += e.r[r] * Cr[r];
+    acc[0] += m;
+    if (e.o >= 0) {
+      add_jtcj(P, e.o, e.o, e.J, C, e.J, 1.0);
+      for (int c = 0; c < 6; ++c) { double s = 0.0; for (int k = 0; k < 6; ++k) s += e.J[6 * k + c] * Cr[k]; red_add(P.b_p + (size_t)e.o * P.D + c, s); }
+    }
   }
+  grid_sum_fixed<1>(acc, P.red_partial, P.red_counter, &P.sc->unary_error, true);
 }
 
-__global__ void k_unary_sd(DeviceProblem P, OtherResiduals R) {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= R.n_unary) return;
-  UnEval e;
-  unary_eval(P, R, i, e, true);
-  if (e.o < 0) return;
-  double v[6] = {0, 0, 0, 0, 0, 0};
-  for (int r = 0; r < 6; ++r) for (int k = 0; k < 6; ++k) v[r] += e.J[6 * r + k] * P.b_p[(size_t)e.o * P.D + k];
-  const double* C = R.un_cov_inv + 36 * (size_t)i;
-  double s = 0.0;
-  for (int r = 0; r < 6; ++r) for (int k = 0; k < 6; ++k) s += v[r] * C[6 * r + k] * v[k];
-  red_add(&P.sc->sd_den_other, s);
+__global__ void __launch_bounds__(64) k_unary_sd(DeviceProblem P, OtherResiduals R) {
+  double acc[1] = {0.0};
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < R.n_unary; i += gridDim.x * blockDim.x) {
+    UnEval e;
+    unary_eval(P, R, i, e, true);
+    if (e.o < 0) continue;
+    double v[6] = {0, 0, 0, 0, 0, 0};
+    for (int r = 0; r < 6; ++r) for (int k = 0; k < 6; ++k) v[r] += e.J[6 * r + k] * P.b_p[(size_t)e.o * P.D + k];
+    const double* C = R.un_cov_inv + 36 * (size_t)i;
+    double s = 0.0;
+    for (int r = 0; r < 6; ++r) for (int k = 0; k < 6; ++k) s += v[r] * C[6 * r + k] * v[k];
+    acc[0] += s;
+  }
+  grid_sum_fixed<1>(acc, P.red_partial, P.red_counter, &P.sc->sd_den_other, true);
 }
 
-__global__ void k_unary_evalk(DeviceProblem P, OtherResiduals R) {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= R.n_unary) return;
-  UnEval e;
-  unary_eval(P, R, i, e, false);
-  const double* C = R.un_cov_inv + 36 * (size_t)i;
-  double s = 0.0;
-  for (int r = 0; r < 6; ++r) for (int k = 0; k < 6; ++k) s += e.r[r] * C[6 * r + k] * e.r[k];
-  red_add(&P.sc->eval_unary, s);
+__global__ void __launch_bounds__(64) k_unary_evalk(DeviceProblem P, OtherResiduals R) {
+  double acc[1] = {0.0};
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < R.n_unary; i += gridDim.x * blockDim.x) {
+    UnEval e;
+    unary_eval(P, R, i, e, false);
+    const double* C = R.un_cov_inv + 36 * (size_t)i;
+    double s = 0.0;
+    for (int r = 0; r < 6; ++r) for (int k = 0; k < 6; ++k) s += e.r[r] * C[6 * r + k] * e.r[k];
+    acc[0] += s;
+  }
+  grid_sum_fixed<1>(acc, P.red_partial, P.red_counter, &P.sc->eval_unary, true);
 }
 
 // ---- inertial -----------------------------------------------------------------------------------
 template <int D>
 __global__ void __launch_bounds__(64) k_imu_build(DeviceProblem P, OtherResiduals R) {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= R.n_imu) return;
-  imu_build_one<D>(P, R, i);
+  double acc[1] = {0.0};
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < R.n_imu; i += gridDim.x * blockDim.x) acc[0] += imu_build_one<D>(P, R, i);
+  grid_sum_fixed<1>(acc, P.red_partial, P.red_counter, &P.sc->inertial_error, true);
 }
 template <int D>
 __global__ void __launch_bounds__(64) k_imu_sd(DeviceProblem P, OtherResiduals R) {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= R.n_imu) return;
-  imu_sd_one<D>(P, R, i);
+  double acc[1] = {0.0};
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < R.n_imu; i += gridDim.x * blockDim.x) acc[0] += imu_sd_one<D>(P, R, i);
+  grid_sum_fixed<1>(acc, P.red_partial, P.red_counter, &P.sc->sd_den_other, true);
 }
 template <int D>
 __global__ void __launch_bounds__(64) k_imu_eval(DeviceProblem P, OtherResiduals R) {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= R.n_imu) return;
-  imu_eval_one<D>(P, R, i);
+  double acc[1] = {0.0};
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < R.n_imu; i += gridDim.x * blockDim.x) acc[0] += imu_eval_one<D>(P, R, i);
+  grid_sum_fixed<1>(acc, P.red_partial, P.red_counter, &P.sc->eval_inertial, true);
 }
 
 // ---- launchers ----------------------------------------------------------------------------------
+static inline int og(int n) { const int b = (n + 63) / 64; return b > kRedMaxGrid ? kRedMaxGrid : (b < 1 ? 1 : b); }   // grid_sum_fixed: at most kRedMaxGrid CTAs
 void launch_unary_maha(const DeviceProblem& P, const OtherResiduals& R, cudaStream_t st) {
   if (R.n_unary) k_unary_maha<<<(R.n_unary + 63) / 64, 64, 0, st>>>(P, R);
 }
 void launch_other_build(const DeviceProblem& P, const OtherResiduals& R, cudaStream_t st, uint64_t* launches) {
-  if (R.n_binary) { k_binary_build<<<(R.n_binary + 63) / 64, 64, 0, st>>>(P, R); ++*launches; }
-  if (R.n_unary) { k_unary_build<<<(R.n_unary + 63) / 64, 64, 0, st>>>(P, R); ++*launches; }
+  if (R.n_binary) { k_binary_build<<<og(R.n_binary), 64, 0, st>>>(P, R); ++*launches; }
+  if (R.n_unary) { k_unary_build<<<og(R.n_unary), 64, 0, st>>>(P, R); ++*launches; }
   if (R.n_imu) {
-    if (P.D == 9) k_imu_build<9><<<(R.n_imu + 63) / 64, 64, 0, st>>>(P, R);
-    else if (P.D == 15) k_imu_build<15><<<(R.n_imu + 63) / 64, 64, 0, st>>>(P, R);
+    if (P.D == 9) k_imu_build<9><<<og(R.n_imu), 64, 0, st>>>(P, R);
+    else if (P.D == 15) k_imu_build<15><<<og(R.n_imu), 64, 0, st>>>(P, R);
     ++*launches;
   }
 }
 void launch_other_sd(const DeviceProblem& P, const OtherResiduals& R, cudaStream_t st, uint64_t* launches) {
-  if (R.n_binary) { k_binary_sd<<<(R.n_binary + 63) / 64, 64, 0, st>>>(P, R); ++*launches; }
-  if (R.n_unary) { k_unary_sd<<<(R.n_unary + 63) / 64, 64, 0, st>>>(P, R); ++*launches; }
+  if (R.n_binary) { k_binary_sd<<<og(R.n_binary), 64, 0, st>>>(P, R); ++*launches; }
+  if (R.n_unary) { k_unary_sd<<<og(R.n_unary), 64, 0, st>>>(P, R); ++*launches; }
   if (R.n_imu) {
-    if (P.D == 9) k_imu_sd<9><<<(R.n_imu + 63) / 64, 64, 0, st>>>(P, R);
-    else if (P.D == 15) k_imu_sd<15><<<(R.n_imu + 63) / 64, 64, 0, st>>>(P, R);
+    if (P.D == 9) k_imu_sd<9><<<og(R.n_imu), 64, 0, st>>>(P, R);
+    else if (P.D == 15) k_imu_sd<15><<<og(R.n_imu), 64, 0, st>>>(P, R);
     ++*launches;
   }
 }
 void launch_other_evaluate(const DeviceProblem& P, const OtherResiduals& R, cudaStream_t st, uint64_t* launches) {
-  if (R.n_binary) { k_binary_eval<<<(R.n_binary + 63) / 64, 64, 0, st>>>(P, R); ++*launches; }
-  if (R.n_unary) { k_unary_evalk<<<(R.n_unary + 63) / 64, 64, 0, st>>>(P, R); ++*launches; }
+  if (R.n_binary) { k_binary_eval<<<og(R.n_binary), 64, 0, st>>>(P, R); ++*launches; }
+  if (R.n_unary) { k_unary_evalk<<<og(R.n_unary), 64, 0, st>>>(P, R); ++*launches; }
   if (R.n_imu) {
-    if (P.D == 9) k_imu_eval<9><<<(R.n_imu + 63) / 64, 64, 0, st>>>(P, R);
-    else if (P.D == 15) k_imu_eval<15><<<(R.n_imu + 63) / 64, 64, 0, st>>>(P, R);
+    if (P.D == 9) k_imu_eval<9><<<og(R.n_imu), 64, 0, st>>>(P, R);
+    else if (P.D == 15) k_imu_eval<15><<<og(R.n_imu), 64, 0, st>>>(P, R);
     ++*launches;
   }
 }

@@ -43,7 +43,92 @@ __global__ void __launch_bounds__(1024) k_peer_allreduce(PeerWindow w, T* buf, i
   }
 }
 
+struct BulkView { double* base[kPeerMaxWorld]; int rank, world; };
+
+// sum of one 16-byte piece over the ranks, in rank order, delivered to every rank
+__device__ __forceinline__ void bulk_piece(const BulkView& v, size_t off2) {
+  double2 s = make_double2(0.0, 0.0);
+  for (int q = 0; q < v.world; ++q) {
+    double2 x;
+    const double2* src = reinterpret_cast<const double2*>(v.base[q]) + off2;
+    asm volatile("ld.relaxed.sys.global.v2.f64 {%0, %1}, [%2];" : "=d"(x.x), "=d"(x.y) : "l"(src) : "memory");
+    s.x += x.x; s.y += x.y;
+  }
+  for (int q = 0; q < v.world; ++q) {
+    double2* dst = reinterpret_cast<double2*>(v.base[q]) + off2;
+    asm volatile("st.relaxed.sys.global.v2.f64 [%0], {%1, %2};" ::"l"(dst), "d"(s.x), "d"(s.y) : "memory");
+  }
+}
+
+constexpr int kBulkTailChunk = 2048;   // doubles
+__global__ void __launch_bounds__(256) k_peer_bulk_allreduce(BulkView v, const int* __restrict__ slots, int n_slots, int tile_elems,
+                                                             size_t tail_off, size_t tail_n) {
+  const int n_tail_chunks = (int)((tail_n + kBulkTailChunk - 1) / kBulkTailChunk);
+  const int n_units = n_slots + n_tail_chunks;
+  // unit u belongs to rank u % world; this rank's units are dealt to its CTAs
+  for (int u = v.rank + blockIdx.x * v.world; u < n_units; u += gridDim.x * v.world) {
+    size_t off, n;
+    if (u < n_slots) { off = (size_t)slots[u] * tile_elems; n = (size_t)tile_elems; }
+    else { const size_t c = (size_t)(u - n_slots) * kBulkTailChunk; off = tail_off + c; n = tail_n - c < (size_t)kBulkTailChunk ? tail_n - c : (size_t)kBulkTailChunk; }
+    // offsets and lengths are even (tiles of T x T doubles with even T, an even tail offset): 16-byte pieces
+    for (size_t i = threadIdx.x; i < n / 2; i += blockDim.x) bulk_piece(v, off / 2 + i);
+  }
+  __threadfence_system();
+}
+
 }  // namespace
+
+cudaError_t PeerBulk::create_local(int rank_, int world_, size_t bytes, void* handle64) {
+  rank = rank_; world = world_;
+  for (auto& p : base) p = nullptr;
+  void* p = nullptr;
+  cudaError_t e = cudaMalloc(&p, bytes);
+  if (e != cudaSuccess) return e;
+  e = cudaMemset(p, 0, bytes);
+  if (e != cudaSuccess) return e;
+  base[rank] = static_cast<double*>(p);
+  cap_bytes = bytes;
+  cudaIpcMemHandle_t h;
+  e = cudaIpcGetMemHandle(&h, p);
+  if (e != cudaSuccess) return e;
+  memcpy(handle64, &h, 64);
+  return cudaDeviceSynchronize();
+}
+bool PeerBulk::open_peers(const void* handles) {
+  bool all = true;
+  for (int p = 0; p < world; ++p) {
+    if (p == rank) continue;
+    cudaIpcMemHandle_t h;
+    memcpy(&h, static_cast<const char*>(handles) + (size_t)p * 64, 64);
+    void* q = nullptr;
+    if (cudaIpcOpenMemHandle(&q, h, cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) { cudaGetLastError(); all = false; q = nullptr; }
+    base[p] = static_cast<double*>(q);
+  }
+  return all;
+}
+void PeerBulk::close_peers() {
+  for (int p = 0; p < world; ++p) {
+    if (!base[p] || p == rank) continue;
+    cudaIpcCloseMemHandle(base[p]);
+    base[p] = nullptr;
+  }
+  ok = false;
+}
+void PeerBulk::destroy() {
+  close_peers();
+  if (world > 0 && base[rank]) { cudaFree(base[rank]); base[rank] = nullptr; }
+  cap_bytes = 0;
+}
+void PeerBulk::allreduce(const int* slots, int n_slots, int tile_elems, size_t tail_off, size_t tail_n, int sms, cudaStream_t st) {
+  BulkView v;
+  for (int p = 0; p < kPeerMaxWorld; ++p) v.base[p] = base[p];
+  v.rank = rank; v.world = world;
+  const int n_units = n_slots + (int)((tail_n + kBulkTailChunk - 1) / kBulkTailChunk);
+  int grid = (n_units + world - 1) / world;
+  if (grid > sms * 2) grid = sms * 2;
+  if (grid < 1) grid = 1;
+  k_peer_bulk_allreduce<<<grid, 256, 0, st>>>(v, slots, n_slots, tile_elems, tail_off, tail_n);
+}
 
 cudaError_t PeerReduce::create_local(int rank, int world, void* handle64) {
   w.rank = rank; w.world = world;

@@ -6,7 +6,8 @@
 // its peers map through CUDA IPC; one single-CTA kernel stores the rank's vector into its slot of every peer's window
 // (plain NVLink stores), publishes a sequence number with a system-scope release, waits for the peers' sequence
 // numbers with acquire loads and sums the slots in rank order — so every rank gets bit-identical sums.
-// Bulk reductions (the S tiles) stay on NCCL.
+// The bulk reduction of the partial reduced systems (S tiles, b_p, rhs_sc) goes over peer memory too (PeerBulk below);
+// NCCL is the fall-back when the windows cannot be mapped.
 #pragma once
 #include <cuda_runtime.h>
 #include <cstddef>
@@ -37,4 +38,25 @@ struct PeerReduce {
   void allreduce_f64(double* buf, int n, cudaStream_t st);
   void allreduce_u32(unsigned int* buf, int n, cudaStream_t st);
   int error(cudaStream_t st) const;  // synchronises the stream
+};
+
+// Bulk all-reduce of the reduced system over NVLink peer memory.  Every rank keeps its S tiles / b_p / rhs_sc in one
+// allocation that its peers map through CUDA IPC.  One multi-CTA kernel: the tiles (and 16 KB chunks of the vector
+// tail) are dealt round-robin to the ranks; the owner of a chunk loads the N partial copies straight from the peers'
+// memory, adds them in rank order and stores the sum into every rank's copy (a fused reduce-scatter + all-gather:
+// (N-1)/N of the data in and out per rank, every rank ends with bit-identical sums).  Only tiles of the symbolic
+// pattern are visited: fill tiles of the factorisation are zero on every rank.  The caller brackets the kernel with two
+// barriers of the small-reduction windows (PeerReduce): no rank reads a peer's partial system before that peer has
+// finished building it, and no rank uses the summed system before every owner has delivered.
+struct PeerBulk {
+  double* base[kPeerMaxWorld] = {nullptr};   // base[rank] is the local allocation
+  size_t cap_bytes = 0;
+  int rank = 0, world = 1;
+  bool ok = false;
+  cudaError_t create_local(int rank_, int world_, size_t bytes, void* handle64);
+  bool open_peers(const void* handles /* world x 64 bytes */);
+  void close_peers();
+  void destroy();
+  // slots: tile slots of the symbolic pattern (device array), tile_elems doubles each; tail: [tail_off, tail_off + tail_n) doubles
+  void allreduce(const int* slots, int n_slots, int tile_elems, size_t tail_off, size_t tail_n, int sms, cudaStream_t st);
 };

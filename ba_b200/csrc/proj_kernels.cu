@@ -229,7 +229,7 @@ __global__ void __launch_bounds__(256) k_back_substitute_long(DeviceProblem P, c
 // ---------------------------------------------------------------------------------------
 // residual-only evaluation with the current Huber weights (cpp:148-188)
 template <int L>
-__global__ void __launch_bounds__(256) k_evaluate(DeviceProblem P, double* out_sum, double* res_out, double* maha_out, int write_maha0) {
+__global__ void __launch_bounds__(256) k_evaluate(DeviceProblem P, double* out_sum, double* res_out, double* maha_out, int write_maha0, int count_outliers) {
   double acc[1] = {0.0};
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < P.n_obs; i += gridDim.x * blockDim.x) {
     const int lm = (int)P.obs_lm[i];
@@ -242,7 +242,7 @@ __global__ void __launch_bounds__(256) k_evaluate(DeviceProblem P, double* out_s
     acc[0] += m;
     // the next BuildProblem starts from this state if the step is accepted: its median input, for free
     if (write_maha0) P.obs_maha0[i] = n2 * P.obs_w0[i];
-    if (sqrt(n2) > P.outlier_threshold) atomicAdd(&P.lm_outliers[lm], 1u);   // cpp:184-186
+    if (count_outliers && sqrt(n2) > P.outlier_threshold) atomicAdd(&P.lm_outliers[lm], 1u);   // cpp:184-186
     if (res_out) {
       const uint32_t id = P.obs_perm[i];
       res_out[2 * (size_t)id] = r[0]; res_out[2 * (size_t)id + 1] = r[1];
@@ -404,13 +404,17 @@ void launch_back_substitute(const DeviceProblem& P, const uint2* tasks, int n_ta
     else k_back_substitute_long<3><<<grid, 256, 0, st>>>(P, long_lms, n_long, delta_p, delta_l);
   }
 }
-void launch_evaluate(const DeviceProblem& P, int G, double* out_sum, double* res_out, double* maha_out, int write_maha0, cudaStream_t st) {
+// count_outliers: EvaluateResiduals resets and recounts num_outlier_residuals (cpp:148-186); the read-out passes after
+// Solve() (per-residual export, conditioning summary) must leave the counts alone (on several GPUs they have been
+// merged over the ranks by then)
+void launch_evaluate(const DeviceProblem& P, int G, double* out_sum, double* res_out, double* maha_out, int write_maha0, int count_outliers,
+                     cudaStream_t st) {
   if (P.n_obs == 0) return;
-  cudaMemsetAsync(P.lm_outliers, 0, sizeof(uint32_t) * P.n_lms, st);
+  if (count_outliers) cudaMemsetAsync(P.lm_outliers, 0, sizeof(uint32_t) * P.n_lms, st);
   (void)G;
   const int grid = grid_for((size_t)P.n_obs, 256, 8);
-  if (P.L == 1) k_evaluate<1><<<grid, 256, 0, st>>>(P, out_sum, res_out, maha_out, write_maha0);
-  else k_evaluate<3><<<grid, 256, 0, st>>>(P, out_sum, res_out, maha_out, write_maha0);
+  if (P.L == 1) k_evaluate<1><<<grid, 256, 0, st>>>(P, out_sum, res_out, maha_out, write_maha0, count_outliers);
+  else k_evaluate<3><<<grid, 256, 0, st>>>(P, out_sum, res_out, maha_out, write_maha0, count_outliers);
 }
 void launch_update_poses(const DeviceProblem& P, const double* delta_p, double coef, cudaStream_t st) {
   if (P.n_poses == 0) return;

@@ -11,7 +11,9 @@ import sys
 import numpy as np
 import pytest
 
-from ba_b200 import synth
+import sys as _sys
+_sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
+from _mg_problems import make, options
 
 pytestmark = pytest.mark.gpu
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
@@ -28,15 +30,17 @@ def _run_sharded(tmp_path, tag, name, scale, iters, p2p, port):
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr", "127.0.0.1",
            "--master-port", str(port), os.path.join(ROOT, "tests", "_multi_gpu_worker.py"), out, name, str(scale), str(iters)]
     r = subprocess.run(cmd, env=env, cwd=ROOT, capture_output=True, text=True, timeout=240)
-    assert r.returncode == 0, r.stderr[-2000:]
+    assert r.returncode == 0, "\n".join(l for l in r.stderr.splitlines() if "rror" in l or "ssert" in l or "bagpu" in l)[-3000:]
     return np.load(out)
 
 
 def _single(name, scale, iters):
     from ba_b200.capi import BundleAdjusterGPU
-    p = synth.make(name, scale)
+    p = make(name, scale)
     s = BundleAdjusterGPU(p.lm_dim, p.pose_dim)
     o = s.default_options(); o.error_change_threshold = 0; o.param_change_threshold = 0; o.record_deltas = 1
+    for k_, v_ in options(name).items():
+        setattr(o, k_, v_)
     if hasattr(p, "gravity"):
         o.gravity[0], o.gravity[1], o.gravity[2] = [float(x) for x in p.gravity]
     s.set_options(o); s.load(p)
@@ -44,13 +48,20 @@ def _single(name, scale, iters):
     tr = s.get_trace()
     res = dict(iterations=sm.iterations, result=sm.result, post=np.array([t["post_solve_norm"] for t in tr]),
                median=np.array([t["median_maha"] for t in tr]), poses=s.get_poses()["t_wp"],
-               lms=s.get_landmarks()["x_w"] if p.lm_dim else np.zeros(0))
+               lms=s.get_landmarks()["x_w"] if p.lm_dim else np.zeros(0),
+               reliable=s.get_landmarks()["is_reliable"] if p.lm_dim else np.zeros(0),
+               outliers=s.get_landmarks()["num_outlier_residuals"] if p.lm_dim else np.zeros(0))
     s.close()
     return res
 
 
-@pytest.mark.parametrize("name,scale,iters", [("c1", 1.0, 6), ("c4", 0.02, 5)])
-def test_two_gpu_solve_matches_single_gpu(tmp_path, name, scale, iters):
+# c5: unary + binary residuals (replicated, added on rank 0: the advisor's two collective-mismatch bugs lived here);
+# c3: inertial residuals
+# (c3: the reduced system of the visual-inertial problem is ill-conditioned at the reference's IMU sigmas, the sharded
+# sums round differently: 1e-6 on the cost, as in test_parity_gpu.py)
+@pytest.mark.parametrize("name,scale,iters,tol", [("c1", 1.0, 6, 1e-9), ("c4", 0.02, 5, 1e-9), ("c2", 0.02, 4, 1e-9), ("c5mini", 1.0, 4, 1e-9),
+                                                    ("c3mini", 1.0, 3, 1e-6)])
+def test_two_gpu_solve_matches_single_gpu(tmp_path, name, scale, iters, tol):
     if _n_gpus() < 2:
         pytest.skip("needs two GPUs")
     one = _single(name, scale, iters)
@@ -58,10 +69,13 @@ def test_two_gpu_solve_matches_single_gpu(tmp_path, name, scale, iters):
     nccl = _run_sharded(tmp_path, "nccl", name, scale, iters, False, 29612)
     for got in (two, nccl):
         assert int(got["iterations"]) == one["iterations"] and int(got["result"]) == one["result"]
-        np.testing.assert_allclose(got["post"], one["post"], rtol=1e-9)
+        np.testing.assert_allclose(got["post"], one["post"], rtol=tol)
         # the exact median is an order statistic of the same multiset: identical up to the rounding of its inputs
-        np.testing.assert_allclose(got["median"], one["median"], rtol=1e-9)
-        np.testing.assert_allclose(got["poses"], one["poses"], rtol=0, atol=1e-7)
-        np.testing.assert_allclose(got["lms"], one["lms"], rtol=0, atol=1e-6)
+        np.testing.assert_allclose(got["median"], one["median"], rtol=tol)
+        np.testing.assert_allclose(got["poses"], one["poses"], rtol=0, atol=1e-7 * (tol / 1e-9))
+        np.testing.assert_allclose(got["lms"], one["lms"], rtol=0, atol=1e-6 * (tol / 1e-9))
+        # flags and counts set by the owning rank only, merged at the end of Solve()
+        np.testing.assert_array_equal(got["reliable"], one["reliable"])
+        np.testing.assert_array_equal(got["outliers"], one["outliers"])
     # both reduction paths sum the ranks' contributions; the peer path does it in rank order on every rank
-    np.testing.assert_allclose(two["post"], nccl["post"], rtol=1e-10)
+    np.testing.assert_allclose(two["post"], nccl["post"], rtol=tol / 10)
