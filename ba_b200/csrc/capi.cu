@@ -316,6 +316,8 @@ struct bagpu_handle_s {
   void* comm = nullptr;
   PeerReduce peer;   // small reductions over NVLink peer memory (peer_reduce.h)
   PeerBulk bulk;     // the reduced system (S tiles | b_p | rhs_sc) in one peer-mapped allocation; NCCL when it cannot be mapped
+  std::vector<int> pcg_row_ptr; std::vector<int3> pcg_ent; DevBuf<int> d_pcg_row_ptr; DevBuf<int3> d_pcg_ent; DevBuf<double> d_pcg_work;
+  bool pcg_uploaded = false; int pcg_iterations = 0;
   std::vector<int> red_slots; DevBuf<int> d_red_slots;   // tile slots of the symbolic pattern (fill tiles are zero on every rank)
   int rank = 0, world = 1;
 
@@ -558,6 +560,24 @@ struct bagpu_handle_s {
     for (int k = 0; k < nT; ++k) {
       red_slots.push_back(tile_slot(k, k));
       for (int b : pattern_rows[k]) red_slots.push_back(tile_slot(k, b));
+    }
+    // rows of y = S x for the PCG (pcg.cu): per tile row its diagonal tile, the tiles of its row of the upper storage and,
+    // transposed, the tiles of its column, in ascending order of the other tile
+    {
+      std::vector<std::vector<int3>> re(nT);
+      for (int a = 0; a < nT; ++a) re[a].push_back(make_int3(tile_slot(a, a), a, 2));
+      for (int a = 0; a < nT; ++a) for (int b : pattern_rows[a]) {
+        const int slot = tile_slot(a, b);
+        re[a].push_back(make_int3(slot, b, 0));
+        re[b].push_back(make_int3(slot, a, 1));
+      }
+      pcg_row_ptr.assign(nT + 1, 0); pcg_ent.clear();
+      for (int a = 0; a < nT; ++a) {
+        std::sort(re[a].begin(), re[a].end(), [](const int3& x, const int3& y) { return x.y < y.y; });
+        pcg_ent.insert(pcg_ent.end(), re[a].begin(), re[a].end());
+        pcg_row_ptr[a + 1] = (int)pcg_ent.size();
+      }
+      pcg_uploaded = false;
     }
   }
 
@@ -1053,7 +1073,20 @@ struct bagpu_handle_s {
   // CalculateGn + GetLandmarkDelta -> d_gn_p, d_gn_l
   bool gauss_newton() {
     CU(cudaEventRecord(ev[8], st));
-    if (n_ap > 0) {
+    // options.reduced_solver: 0 = tile LDL^T, 1 = block-Jacobi PCG, 2 = PCG for small systems (at most 64 poses), LDL^T otherwise
+    const bool use_pcg = n_ap > 0 && (opt.reduced_solver == 1 || (opt.reduced_solver == 2 && n_ap <= 64)) && nT <= 9000;
+    if (use_pcg) {
+      if (!pcg_uploaded) { d_pcg_row_ptr.upload(pcg_row_ptr, st); d_pcg_ent.upload(pcg_ent, st); pcg_uploaded = true; }
+      d_pcg_work.alloc(pcg_work_doubles(nT, T, D));
+      launch_permute_tiles(d_rhs_work.p, d_rhs_sc.p, d_tile_perm.p, T, nT, 1, st); ++launches;
+      const int rc = launch_pcg_solve(D, d_S.p, d_tile_map.p, d_pcg_row_ptr.p, d_pcg_ent.p, nT, d_rhs_work.p, d_rhs_work.p, d_pcg_work.p,
+                                      d_red_partial.p, d_red_counter.p, opt.pcg_tolerance, (int)opt.pcg_max_iterations, &pcg_iterations, &launches, st);
+      if (rc < 0) throw std::string("pcg: CUDA error");
+      launch_permute_tiles(d_gn_p.p, d_rhs_work.p, d_tile_perm.p, T, nT, 0, st); ++launches;
+      // not positive definite -> the factorisation of the reference would have failed; no convergence -> its solve step
+      if (rc == 2) { summary.result = BAGPU_FactorizationError; return false; }
+      if (rc == 1) { summary.result = BAGPU_SolverError; return false; }
+    } else if (n_ap > 0) {
       launch_permute_tiles(d_rhs_work.p, d_rhs_sc.p, d_tile_perm.p, T, nT, 1, st); ++launches;
       const int rc = launch_cholesky_solve(T, d_S.p, d_uinv.p, d_scratch.p, d_rhs_work.p, d_chol_tasks.p, d_chol_terms.p, n_chol_tasks,
                                            d_chol_sync.p, n_tiles, nT, sms, st, chol_trace_buf());

@@ -81,6 +81,12 @@ void launch_cond_error(const uint32_t* obs_pose, const uint32_t* obs_lm, const u
 void launch_scatter_by_perm(const uint32_t* perm, const double* in, uint32_t n, double* out, cudaStream_t st);
 void launch_reliable_merge(uint8_t* rel, unsigned int* unrel, uint32_t n, int phase, cudaStream_t st);
 
+// block-Jacobi PCG on the tiled S (pcg.cu)
+size_t pcg_work_doubles(int nT, int T, int D);
+int launch_pcg_solve(int D, const double* S, const int* tile_map, const int* row_ptr, const int3* ent, int nT, const double* b, double* x_out,
+                     double* work, double* red_partial, unsigned int* red_counter, double tol, int max_iter, int* iters_out, uint64_t* launches,
+                     cudaStream_t st);
+
 void set_sm_count(int n);
 void launch_pose_frames(const DeviceProblem& P, cudaStream_t st);
 void launch_prepare_xs(const DeviceProblem& P, const double* lm_xw, cudaStream_t st);

@@ -351,3 +351,54 @@ def test_landmarks_stay_on_device_until_asked_for():
     got = h.get_landmarks()
     np.testing.assert_allclose(got["x_w"], want["x_w"], rtol=0, atol=1e-9)
     np.testing.assert_allclose(h.get_poses()["t_wp"], r.get_poses()["t_wp"], rtol=0, atol=1e-9)
+
+
+# ---- block-Jacobi PCG (options.reduced_solver = 1; north_star: "... and with a block-Jacobi PCG otherwise") -------------
+@pytest.mark.parametrize("name,mk", [
+    ("c1", lambda: synth.make_c1(n_poses=12, n_landmarks=300, obs_per_lm=8)),
+    ("c2", lambda: synth.make("c2", 0.02)),
+    ("c5", lambda: synth.make_c5(n_poses=120)),
+])
+def test_pcg_matches_tile_cholesky(name, mk):
+    """Same system, two solvers: the Gauss-Newton step of the PCG (relative residual 1e-14) against the LDL^T's, and the
+    residual of both in the conditioning-free form |S dp - rhs| / |rhs| from the dumped system."""
+    p = mk()
+    a, b = gpu(p, reduced_solver=0), gpu(p, reduced_solver=1, pcg_tolerance=1e-14, pcg_max_iterations=4000)
+    sa, sb = a.solve(1), b.solve(1)
+    assert sa.result == sb.result and sa.iterations == sb.iterations == 1
+    ta, tb = a.get_trace()[0], b.get_trace()[0]
+    assert abs(ta["gn_norm"] - tb["gn_norm"]) <= 1e-9 * ta["gn_norm"]
+    assert abs(ta["post_solve_norm"] - tb["post_solve_norm"]) <= 1e-9 * ta["post_solve_norm"]
+    dpa, _ = a.get_deltas(0); dpb, _ = b.get_deltas(0)
+    assert rel(dpb, dpa) < 1e-8, rel(dpb, dpa)
+
+
+def test_pcg_full_solve_matches_oracle():
+    p = synth.make_c1(n_poses=12, n_landmarks=300, obs_per_lm=8)
+    check_solve(p, 4, 1e-8, cost_tol=1e-9, reduced_solver=1, pcg_tolerance=1e-14, pcg_max_iterations=4000)
+    # reduced_solver = 2: PCG below 65 poses, the tile LDL^T above — both within the same bar of the oracle
+    check_solve(p, 3, 1e-8, cost_tol=1e-9, reduced_solver=2, pcg_tolerance=1e-14, pcg_max_iterations=4000)
+
+
+def test_pcg_out_of_iterations_is_a_solver_error():
+    p = synth.make("c2", 0.02)
+    g = gpu(p, reduced_solver=1, pcg_tolerance=1e-14, pcg_max_iterations=3)
+    s = g.solve(2)
+    assert s.result == 5 and s.iterations == 1      # SolverError, Solve() stops like the reference (cpp:639-644)
+
+
+# ---- bit reproducibility (the reference is a serial, deterministic program) -----------------------------------------------
+@pytest.mark.parametrize("name,scale", [("c2", 0.2), ("c4", 0.05), ("c1", 1.0)])
+def test_two_runs_agree_bit_for_bit(name, scale):
+    p = synth.make(name, scale)
+    out = []
+    for _ in range(2):
+        g = gpu(p)
+        g.solve(4)
+        out.append((g.get_trace(), g.get_poses()["t_wp"].copy(), g.get_landmarks()["x_w"].copy()))
+        g.close()
+    (t0, p0, l0), (t1, p1, l1) = out
+    for a, b in zip(t0, t1):
+        for k in TRACE_KEYS:
+            assert a[k] == b[k], (k, a[k], b[k])
+    assert np.array_equal(p0, p1) and np.array_equal(l0, l1)
