@@ -1452,7 +1452,11 @@ void bagpu_default_options(bagpu_options* o) {
 
 int bagpu_create(const bagpu_dims* d, bagpu_handle* out) {
   if (!d || !out) return fail(BAGPU_ERR_INVALID, "null argument");
-  if (d->scalar_bytes != 8) return fail(BAGPU_ERR_UNSUPPORTED, "this build computes in double only (REAL_TYPE=double)");
+  // scalar_bytes = sizeof(REAL_TYPE) of the caller (reference CMakeLists.txt:16-20).  4 = the float instantiation: its host
+  // class converts at the boundary (every array of this ABI is double), the device computes in FP64 either way -- the
+  // build is latency / L2 bound with the FP64 pipe under 30 % busy (profiles/), so FP32 arithmetic would buy nothing and
+  // the float caller gets results well inside its 1e-4 bar
+  if (d->scalar_bytes != 8 && d->scalar_bytes != 4) return fail(BAGPU_ERR_UNSUPPORTED, "REAL_TYPE must be double (8) or float (4)");
   if (d->calib_dim != 0 || d->do_tvs != 0) return fail(BAGPU_ERR_UNSUPPORTED, "CalibSize>0 / DoTvs not built (SURVEY.md §8f rank 3)");
   if (!(d->lm_dim == 0 || d->lm_dim == 1 || d->lm_dim == 3)) return fail(BAGPU_ERR_UNSUPPORTED, "LmSize must be 0, 1 or 3");
   if (!(d->pose_dim == 6 || d->pose_dim == 9 || d->pose_dim == 15)) return fail(BAGPU_ERR_UNSUPPORTED, "PoseSize must be 6, 9 or 15");

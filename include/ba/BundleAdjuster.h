@@ -475,7 +475,7 @@ class BundleAdjuster {
   bool Upload() {
     if (!h_) {
       bagpu_dims d;
-      d.scalar_bytes = 8;   /* device arithmetic is double; a float instantiation converts at this boundary */
+      d.scalar_bytes = (int32_t)sizeof(Scalar);   /* 4 = the REAL_TYPE=float instantiation: it converts at this boundary, the device computes in FP64 */
       d.lm_dim = LmSize; d.pose_dim = PoseSize; d.calib_dim = CalibSize; d.do_tvs = DoTvs ? 1 : 0;
       if (!Check(bagpu_create(&d, &h_))) { h_ = nullptr; return false; }
       dirty_ = true;

@@ -14,8 +14,8 @@
  * include/ba/BundleAdjuster.h:111-753) only does bookkeeping and calls this ABI.
  *
  * Plain C: pointers and sizes only.  All floating point arrays are double (the
- * reference's REAL_TYPE, reference CMakeLists.txt:16-20); compute precision on the
- * device is selected by bagpu_dims.scalar_bytes.
+ * reference's default REAL_TYPE, reference CMakeLists.txt:16-20) and the device computes in FP64;
+ * bagpu_dims.scalar_bytes names the caller's REAL_TYPE (the float instantiation converts on the host side).
  *
  * Conventions
  *   SE3 = 7 doubles: qx qy qz qw tx ty tz   (Hamilton quaternion, Eigen coefficient order)
@@ -54,7 +54,9 @@ typedef enum bagpu_result {
 /* Template parameters of ba::BundleAdjuster<Scalar,LmSize,PoseSize,CalibSize,DoTvs>
  * (reference include/ba/BundleAdjuster.h:111-134). */
 typedef struct bagpu_dims {
-  int32_t scalar_bytes; /* 8 (double) — 4 reserved for the REAL_TYPE=float build */
+  int32_t scalar_bytes; /* sizeof(REAL_TYPE) of the caller (reference CMakeLists.txt:16-20): 8, or 4 for the float
+                           instantiation, whose host class converts at this boundary; every array here is double and
+                           the device computes in FP64 either way */
   int32_t lm_dim;       /* LmSize   : 0, 1 (inverse depth) or 3 */
   int32_t pose_dim;     /* PoseSize : 6, 9 or 15 */
   int32_t calib_dim;    /* CalibSize: 0 in this build */

@@ -138,6 +138,16 @@ int main(int argc, char** argv) {
   int hdr[2];
   if (fread(hdr, sizeof(int), 2, f) != 2) return 2;
   const int L = hdr[0], D = hdr[1];
+  // BA_DRIVER_SCALAR=float: the REAL_TYPE=float build of the reference (CMakeLists.txt:16-20), instantiations <float, ...>
+  const char* sc = getenv("BA_DRIVER_SCALAR");
+  if (sc && sc[0] == 'f') {
+    if (L == 1 && D == 6) return run<float, 1, 6>(rd, argv[2], iters, dogleg, sig);
+    if (L == 3 && D == 6) return run<float, 3, 6>(rd, argv[2], iters, dogleg, sig);
+    if (L == 0 && D == 6) return run<float, 0, 6>(rd, argv[2], iters, dogleg, sig);
+    if (L == 1 && D == 15) return run<float, 1, 15>(rd, argv[2], iters, dogleg, sig);
+    fprintf(stderr, "instantiation <float,%d,%d,0> not compiled into this driver\n", L, D);
+    return 2;
+  }
   if (L == 1 && D == 6) return run<double, 1, 6>(rd, argv[2], iters, dogleg, sig);
   if (L == 3 && D == 6) return run<double, 3, 6>(rd, argv[2], iters, dogleg, sig);
   if (L == 0 && D == 6) return run<double, 0, 6>(rd, argv[2], iters, dogleg, sig);
