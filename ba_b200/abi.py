@@ -103,6 +103,7 @@ class Binding:
         self.h = C.c_void_p()
         self._check(self._f("create")(C.byref(self.dims), C.byref(self.h)))
         self.n_poses = self.n_landmarks = self.n_proj = 0
+        self.n_unary = self.n_binary = self.n_imu = 0
         self.n_active_poses = self.n_active_landmarks = 0
         self.options = options if options is not None else self.default_options()
         self.set_options(self.options)
@@ -166,13 +167,16 @@ class Binding:
         self._check(self._f("set_proj_residuals")(self.h, C.c_uint32(n), _p(a["proj_z"], np.float64), _p(a["proj_meas_pose"], np.uint32),
                                                   _p(a["proj_lm"], np.uint32), _p(a["proj_cam"], np.uint32), _p(a["proj_weight"], np.float64)))
         n = len(a["un_pose"])
+        self.n_unary = n
         self._check(self._f("set_unary_residuals")(self.h, C.c_uint32(n), _p(a["un_pose"], np.uint32), _p(a["un_t_wp"], np.float64),
                                                    _p(a["un_cov_inv"], np.float64), _p(a["un_use_rot"], np.uint8)))
         n = len(a["bin_p1"])
+        self.n_binary = n
         self._check(self._f("set_binary_residuals")(self.h, C.c_uint32(n), _p(a["bin_p1"], np.uint32), _p(a["bin_p2"], np.uint32),
                                                     _p(a["bin_t_12"], np.float64), _p(a["bin_cov_inv"], np.float64),
                                                     _p(a["bin_weight"], np.float64), _p(a["bin_use_rot"], np.uint8)))
         n = len(a["imu_p1"])
+        self.n_imu = n
         self._check(self._f("set_imu_residuals")(self.h, C.c_uint32(n), _p(a["imu_p1"], np.uint32), _p(a["imu_p2"], np.uint32),
                                                  _p(a["imu_meas_start"], np.uint32), _p(a["imu_meas"], np.float64),
                                                  _p(a["imu_weight"], np.float64)))
@@ -217,6 +221,14 @@ class Binding:
         r = np.zeros((n, 2)); w = np.zeros(n); m = np.zeros(n)
         self._check(self._f("get_proj_residuals")(self.h, _p(r, np.float64), _p(w, np.float64), _p(m, np.float64)))
         return dict(residual=r, weight=w, maha=m)
+
+    def get_other_residuals(self):
+        """residual / mahalanobis_distance / cov_inv of the unary, binary and inertial residuals as Solve() left them."""
+        nu, nb, ni, D = self.n_unary, self.n_binary, self.n_imu, self.pose_dim
+        ur = np.zeros((nu, 6)); um = np.zeros(nu); uc = np.zeros((nu, 6, 6)); br = np.zeros((nb, 6)); bm = np.zeros(nb)
+        ir = np.zeros((ni, D)); im = np.zeros(ni); ic = np.zeros((ni, D, D))
+        self._check(self._f("get_other_residuals")(self.h, *[_p(x, np.float64) for x in (ur, um, uc, br, bm, ir, im, ic)]))
+        return dict(un_residual=ur, un_maha=um, un_cov_inv=uc, bin_residual=br, bin_maha=bm, imu_residual=ir, imu_maha=im, imu_cov_inv=ic)
 
     def get_trace(self):
         n = C.c_uint32(0)

@@ -16,7 +16,7 @@ _LIB = None
 EXPORTS = [
     "create", "destroy", "last_error", "set_options", "default_options", "set_cameras", "set_poses",
     "set_landmarks", "set_proj_residuals", "set_unary_residuals", "set_binary_residuals",
-    "set_imu_residuals", "solve", "build", "get_poses", "get_landmarks", "get_proj_residuals",
+    "set_imu_residuals", "solve", "build", "get_poses", "get_landmarks", "get_proj_residuals", "get_other_residuals",
     "get_trace", "get_deltas", "get_pattern", "get_system", "dump", "nccl_unique_id", "comm_init",
     "get_phase_ms", "sync_state", "host_alloc", "host_free", "symbolic_tile_fill", "pack_warp_tasks", "build_work_items",
 ]

@@ -295,7 +295,7 @@ struct bagpu_handle_s {
   // other residuals
   DevBuf<uint32_t> d_un_pose, d_bin_p1, d_bin_p2, d_imu_p1, d_imu_p2, d_imu_ms;
   DevBuf<double> d_un_t, d_un_cov_inv, d_un_maha, d_bin_t, d_bin_cov_inv, d_bin_w, d_imu_meas, d_imu_w;
-  DevBuf<double> d_imu_cov_inv, d_imu_J1, d_imu_J2, d_imu_res;
+  DevBuf<double> d_imu_cov_inv, d_imu_J1, d_imu_J2, d_imu_res, d_un_out, d_bin_out, d_imu_out, d_imu_once; DevBuf<uint8_t> d_imu_once_done;
   DevBuf<uint8_t> d_un_rot, d_bin_rot;
 
   DeviceProblem P;
@@ -721,6 +721,9 @@ struct bagpu_handle_s {
     d_imu_p1.upload(imu_p1, st); d_imu_p2.upload(imu_p2, st); d_imu_ms.upload(imu_ms, st); d_imu_meas.upload(imu_meas, st); d_imu_w.upload(imu_w, st);
     const size_t ni = imu_p1.size();
     d_imu_cov_inv.alloc(ni * D * D); d_imu_J1.alloc(ni * D * D); d_imu_J2.alloc(ni * D * D); d_imu_res.alloc(ni * D);
+    d_un_out.alloc(7 * un_pose.size()); d_bin_out.alloc(7 * bin_p1.size()); d_imu_out.alloc(ni * (D + 1));
+    d_un_out.zero(st); d_bin_out.zero(st); d_imu_out.zero(st);
+    d_imu_once.alloc(ni * 160); d_imu_once_done.alloc(ni); d_imu_once_done.zero(st);
 
     memset(&P, 0, sizeof(P));
     P.L = L; P.D = D; P.n_cams = n_cams; P.n_poses = n_poses; P.n_active_poses = n_ap; P.n_lms = n_lms; P.n_active_lms = n_al; P.n_obs = n_obs;
@@ -750,6 +753,7 @@ struct bagpu_handle_s {
     R.bin_p1 = d_bin_p1.p; R.bin_p2 = d_bin_p2.p; R.bin_t12 = d_bin_t.p; R.bin_cov_inv = d_bin_cov_inv.p; R.bin_weight = d_bin_w.p; R.bin_use_rot = d_bin_rot.p;
     R.imu_p1 = d_imu_p1.p; R.imu_p2 = d_imu_p2.p; R.imu_meas_start = d_imu_ms.p; R.imu_meas = d_imu_meas.p; R.imu_weight = d_imu_w.p;
     R.imu_cov_inv = d_imu_cov_inv.p; R.imu_J1 = d_imu_J1.p; R.imu_J2 = d_imu_J2.p; R.imu_res = d_imu_res.p;
+    R.un_out = d_un_out.p; R.bin_out = d_bin_out.p; R.imu_out = d_imu_out.p; R.imu_once = d_imu_once.p; R.imu_once_done = d_imu_once_done.p;
     apply_options();
     sync(); pc.lap("  upload: rest");
     build_reduce_items();
@@ -817,6 +821,7 @@ struct bagpu_handle_s {
   void apply_options() {
     P.use_robust = (opt.use_robust_norm_for_proj_residuals ? 1 : 0) | (opt.use_robust_norm_for_inertial_residuals ? 2 : 0);
     P.outlier_threshold = opt.projection_outlier_threshold;
+    R.cov_once = opt.calculate_inertial_covariance_once ? 1 : 0;
     for (int k = 0; k < 3; ++k) R.gravity[k] = opt.gravity[k];
     for (int k = 0; k < 3; ++k) {
       R.imu_r[k] = opt.gyro_sigma * opt.gyro_sigma; R.imu_r[3 + k] = opt.accel_sigma * opt.accel_sigma;
@@ -1359,6 +1364,11 @@ struct bagpu_handle_s {
     for (size_t i = 0; i < imu_p1.size(); ++i) if (!pose_active[imu_p1[i]] && pose_active[imu_p2[i]]) ++nci;
     summary.num_cond_inertial_residuals = nci;
     summary.cond_proj_error = 0; summary.cond_inertial_error = 0;
+    if (nci) {   // cpp:688-691: sum of res.mahalanobis_distance (as left by the last EvaluateResiduals) over the conditioning residuals
+      std::vector<double> io = other_outputs(d_imu_out, imu_p1.size() * (D + 1));
+      for (size_t i = 0; i < imu_p1.size(); ++i)
+        if (!pose_active[imu_p1[i]] && pose_active[imu_p2[i]]) summary.cond_inertial_error += io[i * (D + 1) + D];
+    }
     if (n_cond_proj) {
       evaluate_by_id();
       CU(cudaMemsetAsync(&d_sc.p->dot[4], 0, sizeof(double), st));
@@ -1370,6 +1380,20 @@ struct bagpu_handle_s {
       summary.cond_proj_error = shard_sum(v);
     }
     pcs.lap("summary");
+  }
+
+  // Per-residual outputs of the replicated residual types live on rank 0 (the rank that evaluates them); the other ranks
+  // get them through one sum with their own copy zeroed.
+  std::vector<double> other_outputs(DevBuf<double>& buf, size_t n) {
+    std::vector<double> out(n, 0.0);
+    if (n == 0) return out;
+    if (world > 1) {
+      if (rank != 0) buf.zero(st, n);
+      allreduce_f64(buf.p, n);
+    }
+    buf.download(out.data(), n, st);
+    sync();
+    return out;
   }
 
   // residual and maha of every local observation, written at its residual id (d_res_out, d_maha_out)
@@ -1504,6 +1528,11 @@ void bagpu_destroy(bagpu_handle h) {
 
 int bagpu_set_options(bagpu_handle h, const bagpu_options* o) {
   if (!h || !o) return fail(BAGPU_ERR_INVALID, "null argument");
+  // options this path cannot honour are refused, not ignored: per-pose camera parameters (parallel_algos.h:54-57,138-140:
+  // the ABI carries one parameter set per camera), calibration marginals (cpp:771-784: CalibSize > 0 only)
+  if (o->use_per_pose_cam_params) return fail(BAGPU_ERR_UNSUPPORTED, "use_per_pose_cam_params is not supported (one parameter set per camera)");
+  if (o->calculate_calibration_marginals) return fail(BAGPU_ERR_UNSUPPORTED, "calculate_calibration_marginals needs CalibSize > 0, which this build does not have");
+  if (o->reduced_solver < 0 || o->reduced_solver > 2) return fail(BAGPU_ERR_INVALID, "reduced_solver must be 0 (tile LDL^T), 1 (PCG) or 2 (PCG below 65 poses)");
   h->opt = *o;
   // Init() sets trust_region_size_ = options_.trust_region_size (BundleAdjuster.h:193); later changes through
   // options() (BundleAdjuster.h:605) leave the running trust region alone
@@ -1679,6 +1708,32 @@ int bagpu_get_proj_residuals(bagpu_handle h, double* r, double* w, double* m) {
   GUARD(h->ensure_device(); if (h->dirty) return fail(BAGPU_ERR_INVALID, "no solve yet"); h->export_residuals(r, w, m);)
   return BAGPU_OK;
 }
+int bagpu_get_other_residuals(bagpu_handle h, double* un_residual, double* un_maha, double* un_cov_inv, double* bin_residual, double* bin_maha,
+                              double* imu_residual, double* imu_maha, double* imu_cov_inv) {
+  if (!h) return fail(BAGPU_ERR_INVALID, "null handle");
+  GUARD(
+    h->ensure_device();
+    if (h->dirty) return fail(BAGPU_ERR_INVALID, "no solve yet");
+    const int D = h->D;
+    const size_t nu = h->un_pose.size(), nb = h->bin_p1.size(), ni = h->imu_p1.size();
+    if (nu && (un_residual || un_maha)) {
+      const std::vector<double> o = h->other_outputs(h->d_un_out, 7 * nu);
+      for (size_t i = 0; i < nu; ++i) { if (un_residual) memcpy(un_residual + 6 * i, &o[7 * i], 48); if (un_maha) un_maha[i] = o[7 * i + 6]; }
+    }
+    if (nu && un_cov_inv) { const std::vector<double> o = h->other_outputs(h->d_un_cov_inv, 36 * nu); memcpy(un_cov_inv, o.data(), o.size() * 8); }
+    if (nb && (bin_residual || bin_maha)) {
+      const std::vector<double> o = h->other_outputs(h->d_bin_out, 7 * nb);
+      for (size_t i = 0; i < nb; ++i) { if (bin_residual) memcpy(bin_residual + 6 * i, &o[7 * i], 48); if (bin_maha) bin_maha[i] = o[7 * i + 6]; }
+    }
+    if (ni && (imu_residual || imu_maha)) {
+      const std::vector<double> o = h->other_outputs(h->d_imu_out, (size_t)(D + 1) * ni);
+      for (size_t i = 0; i < ni; ++i) { if (imu_residual) memcpy(imu_residual + (size_t)D * i, &o[(size_t)(D + 1) * i], sizeof(double) * D); if (imu_maha) imu_maha[i] = o[(size_t)(D + 1) * i + D]; }
+    }
+    if (ni && imu_cov_inv) { const std::vector<double> o = h->other_outputs(h->d_imu_cov_inv, (size_t)D * D * ni); memcpy(imu_cov_inv, o.data(), o.size() * 8); }
+  )
+  return BAGPU_OK;
+}
+
 int bagpu_get_trace(bagpu_handle h, uint32_t maxr, bagpu_iter_trace* out, uint32_t* n) {
   const uint32_t c = std::min<uint32_t>(maxr, (uint32_t)h->trace.size());
   if (out && c) memcpy(out, h->trace.data(), c * sizeof(bagpu_iter_trace));

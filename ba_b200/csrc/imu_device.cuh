@@ -284,6 +284,11 @@ BA_D double imu_build_one(const DeviceProblem& P, const OtherResiduals& R, int i
     mm<10, 10, 6>(dy_dy0, db, t3);
     for (int k = 0; k < 60; ++k) db[k] = dy_db[k] + t3[k];
   }
+  if (R.cov_once) {   // res.covariance_computed: later builds keep the first build's dintegration_db / c_integration
+    double* keep = R.imu_once + (size_t)i * 160;
+    if (R.imu_once_done[i]) { for (int k = 0; k < 60; ++k) db[k] = keep[k]; for (int k = 0; k < 100; ++k) C[k] = keep[60 + k]; }
+    else { for (int k = 0; k < 60; ++k) keep[k] = db[k]; for (int k = 0; k < 100; ++k) keep[60 + k] = C[k]; R.imu_once_done[i] = 1; }
+  }
   ImuSample zf, zl;
   load_sample(R.imu_meas + 7 * (size_t)m0, zf); load_sample(R.imu_meas + 7 * (size_t)(m1 - 1), zl);
   const double total_dt = zl.time - zf.time;
@@ -437,6 +442,9 @@ BA_D double imu_eval_one(const DeviceProblem& P, const OtherResiduals& R, int i)
   const double* C = R.imu_cov_inv + (size_t)i * D * D;
   double s = 0.0;
   for (int rr = 0; rr < D; ++rr) for (int c = 0; c < D; ++c) s += r[rr] * C[rr * D + c] * r[c];
+  double* out = R.imu_out + (size_t)i * (D + 1);
+  for (int rr = 0; rr < D; ++rr) out[rr] = r[rr];
+  out[D] = s;
   return s;
 }
 

@@ -21,6 +21,10 @@ struct OtherResiduals {
   double* un_cov_inv;                            // 36, multiplied by the Huber weight every build (Q6)
   const uint8_t* un_use_rot;
   double* un_maha;                               // scratch: r^T cov_inv r
+  // per-residual outputs of the last EvaluateResiduals (cpp:190-256: res.residual, res.mahalanobis_distance)
+  double* un_out;                                // 7 per unary residual: residual (6) | mahalanobis_distance
+  double* bin_out;                               // 7 per binary residual
+  double* imu_out;                               // D + 1 per inertial residual
   // binary (Types.h:268-280)
   const uint32_t *bin_p1, *bin_p2; const double* bin_t12; const double* bin_cov_inv; const double* bin_weight;
   const uint8_t* bin_use_rot;
@@ -29,6 +33,9 @@ struct OtherResiduals {
   double* imu_cov_inv;      // D*D per residual, of the last build (weighted)
   double* imu_J1; double* imu_J2;   // D*D per residual (row-major), kept for the SD denominator
   double* imu_res;          // D per residual
+  // options.calculate_inertial_covariance_once (parallel_algos.h:190-205): dintegration_db (60) and c_integration (100) of
+  // the first build are kept per residual and reused by every later one
+  int cov_once; double* imu_once; uint8_t* imu_once_done;
   double gravity[3];
   double imu_r[6];          // sensor noise diagonal (imu_.r)
   double imu_rb[6];         // bias random walk (imu_.r_b)

@@ -152,6 +152,8 @@ __global__ void __launch_bounds__(64) k_binary_eval(DeviceProblem P, OtherResidu
     double s = 0.0;
     for (int r = 0; r < 6; ++r) s += e.r[r] * e.r[r];
     acc[0] += s * R.bin_weight[i];
+    for (int r = 0; r < 6; ++r) R.bin_out[7 * (size_t)i + r] = e.r[r];
+    R.bin_out[7 * (size_t)i + 6] = s * R.bin_weight[i];
   }
   grid_sum_fixed<1>(acc, P.red_partial, P.red_counter, &P.sc->eval_binary, true);
 }
@@ -246,6 +248,8 @@ __global__ void __launch_bounds__(64) k_unary_evalk(DeviceProblem P, OtherResidu
     double s = 0.0;
     for (int r = 0; r < 6; ++r) for (int k = 0; k < 6; ++k) s += e.r[r] * C[6 * r + k] * e.r[k];
     acc[0] += s;
+    for (int r = 0; r < 6; ++r) R.un_out[7 * (size_t)i + r] = e.r[r];
+    R.un_out[7 * (size_t)i + 6] = s;
   }
   grid_sum_fixed<1>(acc, P.red_partial, P.red_counter, &P.sc->eval_unary, true);
 }

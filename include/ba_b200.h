@@ -191,6 +191,12 @@ int bagpu_get_poses(bagpu_handle h, double* t_wp7, double* v_w3, double* b6,
 int bagpu_get_landmarks(bagpu_handle h, double* x_w4, double* x_s4, uint8_t* is_reliable,
                         uint32_t* num_outlier_residuals);
 int bagpu_get_proj_residuals(bagpu_handle h, double* residual2, double* weight, double* maha);
+/* What Solve() leaves in the unary / binary / inertial residual structs (reference src/BundleAdjuster.cpp:190-256:
+ * res.residual and res.mahalanobis_distance of the last EvaluateResiduals; cpp:1469,1526: res.cov_inv, multiplied by the
+ * Huber weight in place).  residual: 6 doubles per unary / binary residual, PoseSize per inertial residual; cov_inv:
+ * 36 / PoseSize^2 row-major.  Any pointer may be NULL.  On several GPUs every rank must call it (one small reduction). */
+int bagpu_get_other_residuals(bagpu_handle h, double* un_residual6, double* un_maha, double* un_cov_inv36, double* bin_residual6,
+                              double* bin_maha, double* imu_residualD, double* imu_maha, double* imu_cov_invDD);
 int bagpu_get_trace(bagpu_handle h, uint32_t max_records, bagpu_iter_trace* out, uint32_t* n_out);
 /* delta of outer iteration `iter` (needs options.record_deltas) */
 int bagpu_get_deltas(bagpu_handle h, uint32_t iter, double* delta_p, double* delta_l);

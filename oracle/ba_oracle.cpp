@@ -56,6 +56,7 @@ struct OracleBase {
   virtual int get_poses(double* t, double* v, double* b, uint8_t* mu, uint8_t* m) = 0;
   virtual int get_landmarks(double* xw, double* xs, uint8_t* rel, uint32_t* nout) = 0;
   virtual int get_proj(double* r, double* w, double* m) = 0;
+  virtual int get_other(double* ur, double* um, double* uc, double* br, double* bm, double* ir, double* im, double* ic) = 0;
   virtual int get_pattern(int which, uint32_t* ncols, uint32_t* nnzb, uint32_t* colptr, uint32_t* rowidx) = 0;
   virtual int get_system(double* s, double* rsc, double* rp, double* rl, double* vi) = 0;
   virtual int dump(const char* dir) = 0;
@@ -1095,6 +1096,28 @@ struct BundleAdjuster : OracleBase {
     }
     return 0;
   }
+  // res.residual / res.mahalanobis_distance / res.cov_inv of the unary, binary and inertial residuals as Solve() leaves them
+  // (reference cpp:190-256 EvaluateResiduals, cpp:1469,1526 cov_inv *= weight)
+  int get_other(double* ur, double* um, double* uc, double* br, double* bm, double* ir, double* im, double* ic) override {
+    for (size_t i = 0; i < unary_residuals_.size(); ++i) {
+      const UnaryResidual& r = unary_residuals_[i];
+      if (ur) for (int k = 0; k < 6; ++k) ur[6 * i + k] = r.residual[k];
+      if (um) um[i] = r.mahalanobis_distance;
+      if (uc) for (int a = 0; a < 6; ++a) for (int b = 0; b < 6; ++b) uc[36 * i + 6 * a + b] = r.cov_inv(a, b);
+    }
+    for (size_t i = 0; i < binary_residuals_.size(); ++i) {
+      const BinaryResidual& r = binary_residuals_[i];
+      if (br) for (int k = 0; k < 6; ++k) br[6 * i + k] = r.residual[k];
+      if (bm) bm[i] = r.mahalanobis_distance;
+    }
+    for (size_t i = 0; i < inertial_residuals_.size(); ++i) {
+      const auto& r = inertial_residuals_[i];
+      if (ir) for (int k = 0; k < D; ++k) ir[(size_t)D * i + k] = r.residual[k];
+      if (im) im[i] = r.mahalanobis_distance;
+      if (ic) for (int a = 0; a < D; ++a) for (int b = 0; b < D; ++b) ic[(size_t)D * D * i + D * a + b] = r.cov_inv(a, b);
+    }
+    return 0;
+  }
   int get_pattern(int which, uint32_t* ncols, uint32_t* nnzb, uint32_t* colptr, uint32_t* rowidx) override {
     std::vector<uint32_t> cp, ri;
     if (which == BAGPU_PATTERN_U) u_.pattern(cp, ri);
@@ -1238,6 +1261,9 @@ int baoracle_build(baoracle_handle h, float* ms) {
 int baoracle_get_poses(baoracle_handle h, double* t, double* v, double* b, uint8_t* mu, uint8_t* m) { return h->impl->get_poses(t, v, b, mu, m); }
 int baoracle_get_landmarks(baoracle_handle h, double* xw, double* xs, uint8_t* rel, uint32_t* n) { return h->impl->get_landmarks(xw, xs, rel, n); }
 int baoracle_get_proj_residuals(baoracle_handle h, double* r, double* w, double* m) { return h->impl->get_proj(r, w, m); }
+int baoracle_get_other_residuals(baoracle_handle h, double* ur, double* um, double* uc, double* br, double* bm, double* ir, double* im, double* ic) {
+  return h->impl->get_other(ur, um, uc, br, bm, ir, im, ic);
+}
 int baoracle_get_trace(baoracle_handle h, uint32_t maxr, bagpu_iter_trace* out, uint32_t* n) {
   uint32_t c = std::min<uint32_t>(maxr, h->impl->trace.size());
   if (out) memcpy(out, h->impl->trace.data(), c * sizeof(bagpu_iter_trace));

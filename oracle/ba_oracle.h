@@ -32,6 +32,8 @@ int baoracle_build(baoracle_handle h, float* ms_out);
 int baoracle_get_poses(baoracle_handle h, double* t_wp7, double* v_w3, double* b6, uint8_t* mask_used, uint8_t* mask);
 int baoracle_get_landmarks(baoracle_handle h, double* x_w4, double* x_s4, uint8_t* is_reliable, uint32_t* num_outlier_residuals);
 int baoracle_get_proj_residuals(baoracle_handle h, double* residual2, double* weight, double* maha);
+int baoracle_get_other_residuals(baoracle_handle h, double* un_residual6, double* un_maha, double* un_cov_inv36, double* bin_residual6,
+                                 double* bin_maha, double* imu_residualD, double* imu_maha, double* imu_cov_invDD);
 int baoracle_get_trace(baoracle_handle h, uint32_t max_records, bagpu_iter_trace* out, uint32_t* n_out);
 int baoracle_get_deltas(baoracle_handle h, uint32_t iter, double* delta_p, double* delta_l);
 int baoracle_get_pattern(baoracle_handle h, int which, uint32_t* ncols, uint32_t* nnzb, uint32_t* colptr, uint32_t* rowidx);

@@ -49,8 +49,11 @@ def test_struct_sizes_match_header():
 def test_create_rejects_unbuilt_instantiations():
     lib = capi.lib()
     h = C.c_void_p()
-    for dims in (abi.Dims(4, 1, 6, 0, 0), abi.Dims(8, 1, 6, 5, 0), abi.Dims(8, 2, 6, 0, 0), abi.Dims(8, 1, 7, 0, 0)):
+    for dims in (abi.Dims(2, 1, 6, 0, 0), abi.Dims(8, 1, 6, 5, 0), abi.Dims(8, 2, 6, 0, 0), abi.Dims(8, 1, 7, 0, 0)):
         assert lib.bagpu_create(C.byref(dims), C.byref(h)) == 5  # BAGPU_ERR_UNSUPPORTED
+    # REAL_TYPE=float callers (scalar_bytes 4) are accepted: their host class converts at the boundary
+    assert lib.bagpu_create(C.byref(abi.Dims(4, 1, 6, 0, 0)), C.byref(h)) == 0
+    lib.bagpu_destroy(h)
 
 
 def test_add_projection_residual_rules():
