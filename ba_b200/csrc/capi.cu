@@ -1877,6 +1877,47 @@ int bagpu_dump(bagpu_handle h, const char* dir) {
   if (!f) return fail(BAGPU_ERR_INVALID, "cannot open rhs.txt");
   for (int i = 0; i < n; ++i) fprintf(f, i ? "\n%.17g" : "%.17g", r[i]);
   fclose(f);
+  // j_pr.txt / r_pr.txt / j_l.txt (cpp:607-620): the dense images of the block-sparse Jacobians, rows in residual-id
+  // order.  The build is matrix-free, so the rows are evaluated for the dump only (k_jacobian_rows), with the Huber
+  // weights of the last build.  Single GPU only (a rank holds the observations of its landmarks).
+  const int L = h->L;
+  const size_t no = (size_t)h->n_obs_total;
+  if (L == 0 || no == 0 || h->world > 1) return BAGPU_OK;
+  const size_t cols_p = (size_t)h->n_ap * 6, cols_l = (size_t)h->n_al * L;
+  if (2 * no * std::max(cols_p, cols_l) > ((size_t)1 << 27)) return BAGPU_OK;   // like the oracle: no dense J beyond 1 GB
+  const int W = 28 + 2 * L;
+  std::vector<double> rows;
+  GUARD(
+    DevBuf<double> d_rows; d_rows.alloc(no * W);
+    launch_jacobian_rows(h->P, d_rows.p, h->st);
+    rows.resize(no * W);
+    d_rows.download(rows.data(), rows.size(), h->st);
+    h->sync();
+  )
+  GUARD(h->host_ids();)
+  FILE* fj = fopen((d + "/j_pr.txt").c_str(), "w");
+  FILE* fr = fopen((d + "/r_pr.txt").c_str(), "w");
+  FILE* fl = fopen((d + "/j_l.txt").c_str(), "w");
+  if (!fj || !fr || !fl) { if (fj) fclose(fj); if (fr) fclose(fr); if (fl) fclose(fl); return fail(BAGPU_ERR_INVALID, "cannot open j_pr.txt / r_pr.txt / j_l.txt"); }
+  std::vector<double> line(std::max(cols_p, cols_l));
+  for (size_t i = 0; i < no; ++i) {
+    const double* q = &rows[i * W];
+    const int om = (int)q[26 + 2 * L], orf = (int)q[27 + 2 * L];
+    const int ol = h->lm_opt[h->proj_lm[i]];
+    for (int rr = 0; rr < 2; ++rr) {
+      std::fill(line.begin(), line.begin() + cols_p, 0.0);
+      if (om >= 0) for (int k = 0; k < 6; ++k) line[(size_t)om * 6 + k] = q[2 + 6 * rr + k];
+      if (orf >= 0) for (int k = 0; k < 6; ++k) line[(size_t)orf * 6 + k] = q[14 + 6 * rr + k];
+      if (i || rr) fputc('\n', fj);
+      for (size_t j = 0; j < cols_p; ++j) fprintf(fj, j ? ", %.17g" : "%.17g", line[j]);
+      fprintf(fr, (i || rr) ? "\n%.17g" : "%.17g", q[rr]);
+      std::fill(line.begin(), line.begin() + cols_l, 0.0);
+      if (ol >= 0) for (int k = 0; k < L; ++k) line[(size_t)ol * L + k] = q[26 + L * rr + k];
+      if (i || rr) fputc('\n', fl);
+      for (size_t j = 0; j < cols_l; ++j) fprintf(fl, j ? ", %.17g" : "%.17g", line[j]);
+    }
+  }
+  fclose(fj); fclose(fr); fclose(fl);
   return BAGPU_OK;
 }
 

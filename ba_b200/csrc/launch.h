@@ -104,6 +104,8 @@ void launch_linearize(const DeviceProblem& P, const uint2* tasks, int n_tasks, c
 void launch_reduce_blocks(const DeviceProblem& P, const ReduceItem* items, int n_items, const uint32_t* pair_a, const uint32_t* pair_b,
                           const uint32_t* pair_lm, double* partial, unsigned int* counters, unsigned int* next_item, cudaStream_t st);
 void launch_sd_denominator(const DeviceProblem& P, int G, cudaStream_t st);
+// per residual id: r sqrt(w) | dz_dx_meas sqrt(w) | dz_dx_ref sqrt(w) | dz_dlm sqrt(w) | meas / ref opt ids (28 + 2 L doubles)
+void launch_jacobian_rows(const DeviceProblem& P, double* out, cudaStream_t st);
 void launch_back_substitute(const DeviceProblem& P, const uint2* tasks, int n_tasks, const uint32_t* long_lms, int n_long, const double* delta_p,
                             double* delta_l, cudaStream_t st);
 void launch_evaluate(const DeviceProblem& P, int G, double* out_sum, double* res_out, double* maha_out, int write_maha0, int count_outliers,

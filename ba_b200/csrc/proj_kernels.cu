@@ -115,6 +115,38 @@ __global__ void __launch_bounds__(128) k_sd_denominator(DeviceProblem P) {
 }
 
 // ---------------------------------------------------------------------------------------
+// The rows of j_pr_ / r_pr_ / j_l_ the reference inserts per residual (cpp:1636-1642, 1795-1796), written at the
+// residual's id for the dump (cpp:607-620).  The build never forms them: this kernel exists for the interchange files
+// only.  out (28 + 2 L doubles per residual): r sqrt(w) (2) | dz_dx_meas sqrt(w) (12) | dz_dx_ref sqrt(w) (12) |
+// dz_dlm sqrt(w) (2 L) | meas opt id, ref opt id as doubles (-1: no block)
+template <int L>
+__global__ void __launch_bounds__(128) k_jacobian_rows(DeviceProblem P, double* __restrict__ out) {
+  constexpr int W = 28 + 2 * L;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < P.n_obs; i += gridDim.x * blockDim.x) {
+    const int lm = (int)P.obs_lm[i];
+    LmCtx<L> c;
+    load_lm<L>(P, lm, c);
+    ObsJac<L> o;
+    obs_jacobians<L>(P, c, i, o);
+    const double sw = sqrt(P.obs_w[i]);
+    double* q = out + (size_t)P.obs_perm[i] * W;
+    q[0] = o.r[0] * sw; q[1] = o.r[1] * sw;
+#pragma unroll
+    for (int k = 0; k < 12; ++k) q[2 + k] = (o.pm >= 0) ? o.Jm[k] * sw : 0.0;
+    double Jr[12];
+#pragma unroll
+    for (int k = 0; k < 12; ++k) Jr[k] = 0.0;
+    if (L == 1 && o.ref_on) ref_jacobian<L>(c, o.Bp, Jr);
+#pragma unroll
+    for (int k = 0; k < 12; ++k) q[14 + k] = Jr[k] * sw;
+#pragma unroll
+    for (int k = 0; k < 2 * L; ++k) q[26 + k] = (c.lm_opt >= 0) ? o.Jl[k] * sw : 0.0;
+    q[26 + 2 * L] = (double)o.pm;
+    q[27 + 2 * L] = (L == 1 && o.ref_on) ? (double)c.ref_opt : -1.0;
+  }
+}
+
+// ---------------------------------------------------------------------------------------
 // back-substitution: delta_l = V^-1 (b_l - W^T delta_p) = dhat - V^-1 sum_a W_a^T delta_p(a)   (cpp:709-744).
 // W_a^T delta = w J_l^T (J_m delta) is re-evaluated from the observation (nothing per observation is stored);
 // V^-1 and dhat come from the landmark's record.
@@ -383,6 +415,11 @@ void launch_residual(const DeviceProblem& P, int G, cudaStream_t st) {
   (void)G;
   const int grid = grid_for((size_t)P.n_obs, 256, 8);
   if (P.L == 1) k_residual<1><<<grid, 256, 0, st>>>(P); else k_residual<3><<<grid, 256, 0, st>>>(P);
+}
+void launch_jacobian_rows(const DeviceProblem& P, double* out, cudaStream_t st) {
+  if (P.n_obs == 0 || P.L == 0) return;
+  const int grid = grid_for((size_t)P.n_obs, 128, 8);
+  if (P.L == 1) k_jacobian_rows<1><<<grid, 128, 0, st>>>(P, out); else k_jacobian_rows<3><<<grid, 128, 0, st>>>(P, out);
 }
 void launch_sd_denominator(const DeviceProblem& P, int G, cudaStream_t st) {
   if (P.n_obs == 0) return;

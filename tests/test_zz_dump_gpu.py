@@ -43,7 +43,13 @@ def test_dump_files_match_the_oracles(tmp_path, make):
     os.mkdir(dg); os.mkdir(do)
     g.dump(dg); o.dump(do)
     a, b = dumpio.read_dump(dg), dumpio.read_dump(do)
-    assert sorted(a) == ["rhs", "s"]                                   # the GPU build never forms J
+    # j_pr / r_pr / j_l: the build never forms J; the dump evaluates the rows for the files (k_jacobian_rows)
+    assert sorted(a) == sorted(b)
+    for k in ("j_pr", "r_pr", "j_l"):
+        if k in b:
+            assert a[k].shape == b[k].shape, k
+            assert rel(a[k], b[k]) < 1e-11, (k, rel(a[k], b[k]))
+            assert np.array_equal(a[k] != 0, b[k] != 0), k                # same block pattern, element for element
     text = open(os.path.join(dg, "s.txt")).read()
     assert not text.endswith("\n") and ", " in text                    # Eigen kLongCsvFmt (Utils.h:66)
     n = g.n_active_poses * p.pose_dim
