@@ -31,6 +31,22 @@ def build(force=False):
     return SO_PATH
 
 
+def build_cpp_driver():
+    """tests/cpp/host_api_driver: a C++ program that drives the drop-in class include/ba/BundleAdjuster.h the way the
+    reference's applications drive ba::BundleAdjuster (used by the tests and by bench.py's e2e_cpp leg)."""
+    root = os.path.dirname(_HERE)
+    src = os.path.join(root, "tests", "cpp", "host_api_driver.cpp")
+    exe = os.path.join(root, "tests", "cpp", "build", "host_api_driver")
+    os.makedirs(os.path.dirname(exe), exist_ok=True)
+    deps = [src, os.path.join(root, "include", "ba", "BundleAdjuster.h"), os.path.join(root, "include", "ba", "MiniTypes.h"),
+            os.path.join(root, "include", "ba_b200.h"), SO_PATH]
+    if os.path.exists(exe) and all(os.path.getmtime(d) <= os.path.getmtime(exe) for d in deps if os.path.exists(d)):
+        return exe
+    subprocess.check_call(["g++", "-std=c++17", "-O2", "-Wall", "-I" + os.path.join(root, "include"), src, "-o", exe,
+                           "-L" + _HERE, "-lba_b200", "-Wl,-rpath," + _HERE])
+    return exe
+
+
 def lib():
     global _LIB
     if _LIB is None:

@@ -159,3 +159,29 @@ class Problem:
         a = self.arrays()
         return dict(poses=len(a["pose_t_wp"]), landmarks=len(a["lm_x_w"]), proj=len(a["proj_z"]),
                     unary=len(a["un_pose"]), binary=len(a["bin_p1"]), imu=len(a["imu_p1"]))
+
+
+def write_driver_problem(path, p):
+    """Problem file of tests/cpp/host_api_driver.cpp (the C++ drop-in class driven like the reference's applications):
+    int32 L, D, then per category a uint32 count followed by the raw arrays."""
+    import struct
+    a = p.arrays()
+    g = getattr(p, "gravity", np.zeros(3))
+    with open(path, "wb") as f:
+        f.write(struct.pack("<ii", p.lm_dim, p.pose_dim))
+
+        def blk(n, *arrs):
+            f.write(struct.pack("<I", n))
+            for x in arrs:
+                f.write(np.ascontiguousarray(x).tobytes())
+        blk(len(a["cam_params"]), a["cam_params"], a["cam_t_vs"])
+        blk(len(a["pose_t_wp"]), a["pose_t_wp"], a["pose_v_w"], a["pose_b"], a["pose_active"])
+        blk(len(a["lm_x_w"]), a["lm_x_w"], a["lm_ref_pose"], a["lm_ref_cam"], a["lm_active"])
+        blk(len(a["proj_z"]), a["proj_z"], a["proj_meas_pose"], a["proj_lm"], a["proj_cam"], a["proj_weight"])
+        # the C++ API takes covariances (it inverts them, reference BundleAdjuster.h:398,444)
+        ucov = np.array([np.linalg.inv(c.reshape(6, 6)).reshape(36) for c in a["un_cov_inv"]]).reshape(-1, 36)
+        blk(len(a["un_pose"]), a["un_pose"], a["un_t_wp"], ucov, a["un_use_rot"])
+        bcov = np.array([np.linalg.inv(c.reshape(6, 6)).reshape(36) for c in a["bin_cov_inv"]]).reshape(-1, 36)
+        blk(len(a["bin_p1"]), a["bin_p1"], a["bin_p2"], a["bin_t_12"], bcov, a["bin_weight"], a["bin_use_rot"])
+        blk(len(a["imu_p1"]), a["imu_p1"], a["imu_p2"], a["imu_meas_start"], a["imu_meas"], a["imu_weight"])
+        f.write(np.asarray(g, np.float64).tobytes())

@@ -188,6 +188,41 @@ def make_counts(name):
     return {"c1": 100000, "c2": 5000000, "c3": 2000499, "c4": 10000000, "c5": 21200}[name]
 
 
+def e2e_cpp_run(p, K, tmp_dir):
+    """The API north_star names: the C++ drop-in class (include/ba/BundleAdjuster.h) driven through AddPose / AddLandmark /
+    AddProjectionResidual / ... / Solve(K) / getters by tests/cpp/host_api_driver.cpp.  The problem is handed to the driver as
+    a file (read before the clock starts); timed: the Add* calls (host-side SoA marshalling into page-locked buffers),
+    Solve() (upload + set-up + K iterations + read-back of poses and landmarks), the getters of the refined state."""
+    from ba_b200.capi import build_cpp_driver
+    from ba_b200.problem import write_driver_problem
+    exe = build_cpp_driver()
+    prob, outp = os.path.join(tmp_dir, "bench_problem.bin"), os.path.join(tmp_dir, "bench_out.bin")
+    write_driver_problem(prob, p)
+    best = None
+    for _rep in range(2):          # the first run pays the CUDA context and module load
+        env = dict(os.environ, BA_DRIVER_NO_RESIDUALS="1")
+        r = subprocess.run([exe, prob, outp, str(K)], capture_output=True, text=True, env=env)
+        if r.returncode != 0:
+            return {"error": "driver exit %d: %s" % (r.returncode, r.stderr[-300:])}
+        t = None
+        for line in r.stderr.splitlines():
+            if line.startswith('{"driver_timing"'):
+                t = json.loads(line)["driver_timing"]
+        if t is None:
+            return {"error": "no timing line"}
+        if best is None or t["solve_s"] < best["solve_s"]:
+            best = t
+    for f in (prob, outp):
+        try:
+            os.remove(f)
+        except OSError:
+            pass
+    its = best["iterations"]
+    return {"value": its / (best["add_s"] + best["solve_s"] + best["get_state_s"]), "unit": "iter/s", "iterations": its,
+            "add_calls_s": best["add_s"], "solve_s": best["solve_s"], "getters_s": best["get_state_s"],
+            "note": "one process, best of 2 (the first pays the CUDA context): Add* calls + Solve(K) + GetPose / GetLandmark over the whole state, wall clock inside the C++ driver"}
+
+
 def config_for(name, scale, gpus):
     return {"workload": WORKLOADS[name]["desc"] + (" (scale %.3g)" % scale if scale != 1.0 else ""),
             "solver": "dogleg, nested-dissection tile LDL^T (dataflow kernel)", "sharding": "landmarks over %d GPU(s)" % gpus,
@@ -313,6 +348,10 @@ def run_gpu_workload(name, args, K, W, rank, world, local_rank, with_e2e, with_c
                           "seconds": e2e_times, "note": "median of 3; one Solve(K) call from page-locked host arrays: upload of the whole problem + symbolic set-up on the device + K iterations + download of the refined poses and landmarks"}
         if roofline:
             out["roofline"] = roofline
+        if with_e2e and world == 1 and not args.no_e2e_cpp:
+            import tempfile
+            with tempfile.TemporaryDirectory() as td:
+                out["e2e_cpp"] = e2e_cpp_run(p, K, td)
         if with_cpu:
             # the CPU oracle on the SAME full-size problem: 2 iterations from the same initial state, timed, and its
             # trace compared with the end-to-end GPU run's (full-size parity, not only the minis of tests/)
@@ -335,6 +374,7 @@ def main():
     ap.add_argument("--also", default="c2", help="second workload reported as a keyed block of the same line ('' = none)")
     ap.add_argument("--scale", type=float, default=1.0, help="shrink the workload (development only; invalidates the number)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e-cpp", action="store_true", help="skip the leg that drives the C++ drop-in class")
     ap.add_argument("--no-e2e", action="store_true", help="development / profiler runs only: skip the end-to-end leg (the line then has no e2e)")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0")); world = int(os.environ.get("WORLD_SIZE", "1")); local_rank = int(os.environ.get("LOCAL_RANK", "0"))

@@ -383,6 +383,7 @@ class BundleAdjuster {
     r.residual_id = id; r.residual_offset = 2 * id; r.orig_weight = (Scalar)pr_w0_[id];
     r.z[0] = (Scalar)pr_z_[2 * id]; r.z[1] = (Scalar)pr_z_[2 * id + 1];
     r.x_meas_id = pr_pose_[id]; r.landmark_id = pr_lm_[id]; r.x_ref_id = lm_ref_pose_[pr_lm_[id]]; r.cam_id = pr_cam_[id];
+    FetchProjResiduals();
     if (pr_w_.size() == pr_pose_.size()) {
       r.residual[0] = (Scalar)pr_res_[2 * id]; r.residual[1] = (Scalar)pr_res_[2 * id + 1];
       r.weight = (Scalar)pr_w_[id]; r.mahalanobis_distance = (Scalar)pr_maha_[id];
@@ -512,6 +513,14 @@ class BundleAdjuster {
     return true;
   }
 
+  void FetchProjResiduals() const {
+    const size_t nr = pr_pose_.size();
+    if (pr_fetched_ || !h_ || !nr) return;
+    pr_res_.resize(2 * nr); pr_w_.resize(nr); pr_maha_.resize(nr);
+    if (bagpu_get_proj_residuals(h_, pr_res_.data(), pr_w_.data(), pr_maha_.data()) != BAGPU_OK) { pr_res_.clear(); pr_w_.clear(); pr_maha_.clear(); }
+    pr_fetched_ = true;
+  }
+
   void Download() {
     const uint32_t np = (uint32_t)poses_.size();
     std::vector<double> t(7 * (size_t)np), v(3 * (size_t)np), b(6 * (size_t)np);
@@ -526,11 +535,9 @@ class BundleAdjuster {
       if (p.is_param_mask_used) { p.param_mask.assign(PoseSize, true); for (int k = 0; k < PoseSize; ++k) p.param_mask[k] = mk[(size_t)i * PoseSize + k] != 0; }
     }
     if (!lm_ref_pose_.empty()) bagpu_get_landmarks(h_, lm_x_w_.data(), lm_x_s_.data(), lm_reliable_.data(), lm_outliers_.data());
-    const size_t nr = pr_pose_.size();
-    if (nr) {
-      pr_res_.resize(2 * nr); pr_w_.resize(nr); pr_maha_.resize(nr);
-      bagpu_get_proj_residuals(h_, pr_res_.data(), pr_w_.data(), pr_maha_.data());
-    }
+    /* residual / weight / mahalanobis_distance of the projection residuals stay on the device until somebody asks for
+       one (GetProjectionResidual): three arrays of N_o doubles and one more evaluation pass that most callers never need */
+    pr_fetched_ = false;
     if (kBiasInState && np) {   /* cpp:666-669: the last pose's biases become the IMU calibration's */
       for (int k = 0; k < 3; ++k) { imu_.b_g[k] = poses_.back().b[k]; imu_.b_a[k] = poses_.back().b[3 + k]; }
     }
@@ -548,7 +555,7 @@ class BundleAdjuster {
   std::vector<uint8_t> lm_active_; detail::HostVector<uint8_t> lm_reliable_;
   std::vector<int> lm_external_;
   /* projection residuals, SoA (proj_residuals_) */
-  detail::HostVector<double> pr_z_, pr_w0_; std::vector<double> pr_res_, pr_w_, pr_maha_;
+  detail::HostVector<double> pr_z_, pr_w0_; mutable std::vector<double> pr_res_, pr_w_, pr_maha_; mutable bool pr_fetched_ = true;
   detail::HostVector<uint32_t> pr_pose_, pr_lm_, pr_cam_;
   std::vector<uint32_t> conditioning_proj_residuals_, conditioning_inertial_residuals_;
   /* unary / binary / inertial residuals, SoA */

@@ -9,6 +9,7 @@
 // category a uint32 count followed by the raw arrays in the order read below.  out.bin: the
 // refined poses / landmarks / summary as doubles.  Exit code 3 = Solve() reported SolverError
 // (e.g. no CUDA device: there is no CPU path behind this class).
+#include <chrono>
 #include <cstdio>
 #include <cstdlib>
 #include <vector>
@@ -47,6 +48,8 @@ int run(Reader& rd, const char* out_path, int iters, bool dogleg, const double* 
   auto im = rd.arr<double>(7 * (size_t)(ni ? ims[ni] : 0)); auto iw = rd.arr<double>(ni);
   auto g = rd.arr<double>(3);
 
+  const auto t_start = std::chrono::steady_clock::now();
+  auto since = [](std::chrono::steady_clock::time_point t0) { return std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count(); };
   ba.Init(opt, np, nr, nl);
   typename BA::Vector3t gv; gv[0] = (Scalar)g[0]; gv[1] = (Scalar)g[1]; gv[2] = (Scalar)g[2];
   ba.SetGravity(gv);
@@ -91,13 +94,20 @@ int run(Reader& rd, const char* out_path, int iters, bool dogleg, const double* 
   }
   try { ba.GetPose(np + 5); return 2; } catch (int) {}   // reference BundleAdjuster.h:573-580
 
+  const double t_add = since(t_start);
+  const auto t_solve0 = std::chrono::steady_clock::now();
   ba.Solve((uint32_t)iters);
+  const double t_solve = since(t_solve0);
   const ba::SolutionSummary<Scalar>& s = ba.GetSolutionSummary();
   if (s.result == ba::SolverError || s.result == ba::FactorizationError) { fprintf(stderr, "Solve: result %d\n", (int)s.result); return 3; }
 
+  const auto t_get0 = std::chrono::steady_clock::now();
+  // BA_DRIVER_NO_RESIDUALS: a caller that reads poses and landmarks only (the per-residual records stay on the device)
+  const bool want_residuals = getenv("BA_DRIVER_NO_RESIDUALS") == nullptr;
   FILE* o = fopen(out_path, "wb");
   if (!o) return 2;
   std::vector<double> out;
+  out.reserve(10 + 16 * (size_t)np + 6 * (size_t)nl + 3 * (size_t)nr);
   Scalar e0, e1, e2, e3;
   ba.GetErrors(e0, e1, e2, e3);
   const double head[] = {(double)s.result, (double)ba.GetNumIterations(), (double)s.pre_solve_norm, (double)s.post_solve_norm, (double)s.delta_norm,
@@ -115,12 +125,18 @@ int run(Reader& rd, const char* out_path, int iters, bool dogleg, const double* 
     out.push_back(ba.IsLandmarkReliable(i) ? 1.0 : 0.0);
     out.push_back(ba.LandmarkOutlierRatio(i));
   }
-  for (uint32_t i = 0; i < nr; ++i) {
+  const double t_get_state = since(t_get0);
+  for (uint32_t i = 0; want_residuals && i < nr; ++i) {
     const typename BA::ProjectionResidual r = ba.GetProjectionResidual(i);
     out.push_back((double)r.residual[0]); out.push_back((double)r.residual[1]); out.push_back((double)r.weight);
   }
+  const double t_get = since(t_get0);
   fwrite(out.data(), sizeof(double), out.size(), o);
   fclose(o);
+  // one JSON line for bench.py's e2e_cpp leg: the Add* calls (host-side SoA marshalling), Solve() (upload + set-up + iterations +
+  // read-back of poses / landmarks), the getters
+  fprintf(stderr, "{\"driver_timing\": {\"add_s\": %.6f, \"solve_s\": %.6f, \"get_state_s\": %.6f, \"get_all_s\": %.6f, \"iterations\": %u}}\n",
+          t_add, t_solve, t_get_state, t_get, ba.GetNumIterations());
   printf("host_api_driver: result %d, %u iterations, cost %.12g -> %.12g\n", (int)s.result, ba.GetNumIterations(), (double)s.pre_solve_norm, (double)s.post_solve_norm);
   return 0;
 }

@@ -19,37 +19,13 @@ EXE = os.path.join(ROOT, "tests", "cpp", "build", "host_api_driver")
 
 
 def build_driver():
-    os.makedirs(os.path.dirname(EXE), exist_ok=True)
-    deps = [SRC, os.path.join(ROOT, "include", "ba", "BundleAdjuster.h"), os.path.join(ROOT, "include", "ba", "MiniTypes.h"),
-            os.path.join(ROOT, "include", "ba_b200.h")]
-    if os.path.exists(EXE) and all(os.path.getmtime(d) <= os.path.getmtime(EXE) for d in deps):
-        return EXE
-    subprocess.check_call(["g++", "-std=c++17", "-O2", "-Wall", "-I" + os.path.join(ROOT, "include"), SRC, "-o", EXE,
-                           "-L" + os.path.join(ROOT, "ba_b200"), "-lba_b200", "-Wl,-rpath," + os.path.join(ROOT, "ba_b200")])
-    return EXE
+    from ba_b200.capi import build_cpp_driver
+    return build_cpp_driver()
 
 
 def write_problem(path, p):
-    a = p.arrays()
-    g = getattr(p, "gravity", np.zeros(3))
-    with open(path, "wb") as f:
-        f.write(struct.pack("<ii", p.lm_dim, p.pose_dim))
-
-        def blk(n, *arrs):
-            f.write(struct.pack("<I", n))
-            for x in arrs:
-                f.write(np.ascontiguousarray(x).tobytes())
-        blk(len(a["cam_params"]), a["cam_params"], a["cam_t_vs"])
-        blk(len(a["pose_t_wp"]), a["pose_t_wp"], a["pose_v_w"], a["pose_b"], a["pose_active"])
-        blk(len(a["lm_x_w"]), a["lm_x_w"], a["lm_ref_pose"], a["lm_ref_cam"], a["lm_active"])
-        blk(len(a["proj_z"]), a["proj_z"], a["proj_meas_pose"], a["proj_lm"], a["proj_cam"], a["proj_weight"])
-        # the C++ API takes covariances (it inverts them, reference BundleAdjuster.h:398,444)
-        ucov = np.array([np.linalg.inv(c.reshape(6, 6)).reshape(36) for c in a["un_cov_inv"]]).reshape(-1, 36)
-        blk(len(a["un_pose"]), a["un_pose"], a["un_t_wp"], ucov, a["un_use_rot"])
-        bcov = np.array([np.linalg.inv(c.reshape(6, 6)).reshape(36) for c in a["bin_cov_inv"]]).reshape(-1, 36)
-        blk(len(a["bin_p1"]), a["bin_p1"], a["bin_p2"], a["bin_t_12"], bcov, a["bin_weight"], a["bin_use_rot"])
-        blk(len(a["imu_p1"]), a["imu_p1"], a["imu_p2"], a["imu_meas_start"], a["imu_meas"], a["imu_weight"])
-        f.write(np.asarray(g, np.float64).tobytes())
+    from ba_b200.problem import write_driver_problem
+    write_driver_problem(path, p)
 
 
 def read_out(path, p):
