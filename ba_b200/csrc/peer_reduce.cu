@@ -45,18 +45,27 @@ __global__ void __launch_bounds__(1024) k_peer_allreduce(PeerWindow w, T* buf, i
 
 struct BulkView { double* base[kPeerMaxWorld]; int rank, world; };
 
-// sum of one 16-byte piece over the ranks, in rank order, delivered to every rank
+// sum of one 16-byte piece over the ranks, in rank order, delivered to every rank.  All N loads are issued before the
+// first add (a remote load is ~2 us: eight dependent ones would serialise), then N stores.
 __device__ __forceinline__ void bulk_piece(const BulkView& v, size_t off2) {
-  double2 s = make_double2(0.0, 0.0);
-  for (int q = 0; q < v.world; ++q) {
-    double2 x;
-    const double2* src = reinterpret_cast<const double2*>(v.base[q]) + off2;
-    asm volatile("ld.relaxed.sys.global.v2.f64 {%0, %1}, [%2];" : "=d"(x.x), "=d"(x.y) : "l"(src) : "memory");
-    s.x += x.x; s.y += x.y;
+  double2 x[kPeerMaxWorld];
+#pragma unroll
+  for (int q = 0; q < kPeerMaxWorld; ++q) {
+    x[q] = make_double2(0.0, 0.0);
+    if (q < v.world) {
+      const double2* src = reinterpret_cast<const double2*>(v.base[q]) + off2;
+      asm volatile("ld.relaxed.sys.global.v2.f64 {%0, %1}, [%2];" : "=d"(x[q].x), "=d"(x[q].y) : "l"(src));
+    }
   }
-  for (int q = 0; q < v.world; ++q) {
-    double2* dst = reinterpret_cast<double2*>(v.base[q]) + off2;
-    asm volatile("st.relaxed.sys.global.v2.f64 [%0], {%1, %2};" ::"l"(dst), "d"(s.x), "d"(s.y) : "memory");
+  double2 s = make_double2(0.0, 0.0);
+#pragma unroll
+  for (int q = 0; q < kPeerMaxWorld; ++q) if (q < v.world) { s.x += x[q].x; s.y += x[q].y; }
+#pragma unroll
+  for (int q = 0; q < kPeerMaxWorld; ++q) {
+    if (q < v.world) {
+      double2* dst = reinterpret_cast<double2*>(v.base[q]) + off2;
+      asm volatile("st.relaxed.sys.global.v2.f64 [%0], {%1, %2};" ::"l"(dst), "d"(s.x), "d"(s.y) : "memory");
+    }
   }
 }
 
@@ -71,7 +80,7 @@ __global__ void __launch_bounds__(256) k_peer_bulk_allreduce(BulkView v, const i
     if (u < n_slots) { off = (size_t)slots[u] * tile_elems; n = (size_t)tile_elems; }
     else { const size_t c = (size_t)(u - n_slots) * kBulkTailChunk; off = tail_off + c; n = tail_n - c < (size_t)kBulkTailChunk ? tail_n - c : (size_t)kBulkTailChunk; }
     // offsets and lengths are even (tiles of T x T doubles with even T, an even tail offset): 16-byte pieces
-    for (size_t i = threadIdx.x; i < n / 2; i += blockDim.x) bulk_piece(v, off / 2 + i);
+    for (size_t i = threadIdx.x; i < n / 2; i += blockDim.x) bulk_piece(v, off / 2 + i);   // independent pieces: the loads of consecutive iterations overlap
   }
   __threadfence_system();
 }
@@ -125,7 +134,7 @@ void PeerBulk::allreduce(const int* slots, int n_slots, int tile_elems, size_t t
   v.rank = rank; v.world = world;
   const int n_units = n_slots + (int)((tail_n + kBulkTailChunk - 1) / kBulkTailChunk);
   int grid = (n_units + world - 1) / world;
-  if (grid > sms * 2) grid = sms * 2;
+  if (grid > sms * 8) grid = sms * 8;
   if (grid < 1) grid = 1;
   k_peer_bulk_allreduce<<<grid, 256, 0, st>>>(v, slots, n_slots, tile_elems, tail_off, tail_n);
 }
