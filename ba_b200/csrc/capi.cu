@@ -661,12 +661,19 @@ struct bagpu_handle_s {
     d_lm_outliers.zero(st);
     pc.lap("  upload: cameras, poses, landmarks");
     // observations: landmark-major stream, record slots and the tile pattern, derived on the device
-    {
-      std::vector<uint8_t> present;
-      device_symbolic(present);
-      tile_structure(present);
-      pc.lap("  tile structure (host)");
-    }
+    std::vector<uint8_t> present;
+    device_symbolic(present);
+    pc.lap("  device symbolic");
+    // The tile structure of S (elimination order, symbolic fill) and the task plan of the factorisation are host-only
+    // work (3 - 4 ms for 10k poses): they run on a helper thread beside the pair-list set-up below, which needs
+    // nothing of S.
+    std::vector<CholTask> plan_tasks; std::vector<CholTerm> plan_terms;
+    std::string tiler_err;
+    std::thread tiler([&]() {
+      try { tile_structure(present); chol_build_plan(nT, row_ptr, row_col, plan_tasks, plan_terms); }
+      catch (const std::exception& e) { tiler_err = e.what(); }
+    });
+    struct Joiner { std::thread& t; ~Joiner() { if (t.joinable()) t.join(); } } tiler_guard{tiler};
     const bool multi_cam = n_cams > 1;
     d_obs_maha0.alloc(n_obs); d_obs_w.alloc(n_obs);
     const int Ls = std::max(1, L);
@@ -683,37 +690,10 @@ struct bagpu_handle_s {
       sync();
     }
     pc.lap("  upload: allocs");
-    // reduced system
-    const size_t tsz = (size_t)T * T;
-    d_uinv.alloc((size_t)nT * tsz); d_scratch.alloc(3 * (size_t)nT * T + 2 * (size_t)n_tiles * T);
-    d_rhs_work.alloc((size_t)nT * T);
-    {
-      // the system the ranks sum: S tiles | b_p | rhs_sc, in one peer-mapped allocation when the windows work
-      const size_t nS = (size_t)n_tiles * tsz, nV = (size_t)nT * T;
-      ensure_bulk_window((nS + 2 * nV) * sizeof(double));
-      if (bulk.ok) {
-        double* b = bulk.base[rank];
-        d_S.adopt(b, nS); d_bp.adopt(b + nS, nV); d_rhs_sc.adopt(b + nS + nV, nV);
-        d_red_slots.upload(red_slots, st);
-      } else {
-        d_S.alloc(nS); d_bp.alloc(nV); d_rhs_sc.alloc(nV);
-      }
-    }
-    d_row_ptr.upload(row_ptr, st); d_row_col.upload(row_col, st); d_tile_perm.upload(tile_perm, st);
-    d_tile_map.alloc((size_t)nT * nT); launch_fill_tile_map(d_row_ptr.p, d_row_col.p, nT, d_tile_map.p, st);
-    {
-      std::vector<CholTask> tasks; std::vector<CholTerm> terms;
-      chol_build_plan(nT, row_ptr, row_col, tasks, terms);
-      n_chol_tasks = (int)tasks.size();
-      if (getenv("BAGPU_CHOL_TRACE")) h_chol_tasks = tasks;
-      d_chol_tasks.upload(tasks, st); d_chol_terms.upload(terms, st); d_chol_sync.alloc(chol_sync_ints(n_tiles, nT));
-      sync();
-    }
-    pc.lap("  upload: S + chol plan");
     d_sc.alloc(1); d_sc.zero(st); d_sel.alloc(1);
-    d_bl_compact.alloc((size_t)n_al * Ls); d_gn_p.alloc((size_t)nT * T); d_gn_l.alloc((size_t)n_al * Ls);
-    d_dl_p.alloc((size_t)nT * T); d_dl_l.alloc((size_t)n_al * Ls); d_tmp_p.alloc((size_t)nT * T); d_tmp_l.alloc((size_t)n_al * Ls);
-    d_gn_p.zero(st); d_gn_l.zero(st); d_dl_p.zero(st); d_dl_l.zero(st); d_bl_compact.zero(st);
+    d_bl_compact.alloc((size_t)n_al * Ls); d_gn_l.alloc((size_t)n_al * Ls);
+    d_dl_l.alloc((size_t)n_al * Ls); d_tmp_l.alloc((size_t)n_al * Ls);
+    d_gn_l.zero(st); d_dl_l.zero(st); d_bl_compact.zero(st);
     // other residuals
     d_un_pose.upload(un_pose, st); d_un_t.upload(un_t, st); d_un_cov_inv.upload(un_cov_inv, st); d_un_rot.upload(un_rot, st); d_un_maha.alloc(un_pose.size());
     d_bin_p1.upload(bin_p1, st); d_bin_p2.upload(bin_p2, st); d_bin_t.upload(bin_t, st); d_bin_cov_inv.upload(bin_cov_inv, st);
@@ -744,7 +724,7 @@ struct bagpu_handle_s {
       const double* t7 = &cam_tvs[7 * c];
       if (!(t7[0] == 0.0 && t7[1] == 0.0 && t7[2] == 0.0 && t7[3] == 1.0 && t7[4] == 0.0 && t7[5] == 0.0 && t7[6] == 0.0)) P.cam_identity = 0;
     }
-    P.S_tiles = d_S.p; P.tile_map = d_tile_map.p; P.tile_perm = d_tile_perm.p; P.nT = nT; P.T = T; P.b_p = d_bp.p; P.rhs_sc = d_rhs_sc.p; P.sc = d_sc.p;
+    P.sc = d_sc.p; P.T = T;
     P.c_huber_factor = 1.2107;
 
     memset(&R, 0, sizeof(R));
@@ -758,6 +738,38 @@ struct bagpu_handle_s {
     sync(); pc.lap("  upload: rest");
     build_reduce_items();
     pc.lap("  build_reduce_items");
+    tiler.join();
+    if (!tiler_err.empty()) throw std::string("tile structure: ") + tiler_err;
+    pc.lap("  tile structure + factorisation plan (join)");
+    // reduced system
+    const size_t tsz = (size_t)T * T;
+    d_uinv.alloc((size_t)nT * tsz); d_scratch.alloc(3 * (size_t)nT * T + 2 * (size_t)n_tiles * T);
+    d_rhs_work.alloc((size_t)nT * T);
+    {
+      // the system the ranks sum: S tiles | b_p | rhs_sc, in one peer-mapped allocation when the windows work
+      const size_t nS = (size_t)n_tiles * tsz, nV = (size_t)nT * T;
+      ensure_bulk_window((nS + 2 * nV) * sizeof(double));
+      if (bulk.ok) {
+        double* b = bulk.base[rank];
+        d_S.adopt(b, nS); d_bp.adopt(b + nS, nV); d_rhs_sc.adopt(b + nS + nV, nV);
+        d_red_slots.upload(red_slots, st);
+      } else {
+        d_S.alloc(nS); d_bp.alloc(nV); d_rhs_sc.alloc(nV);
+      }
+    }
+    d_row_ptr.upload(row_ptr, st); d_row_col.upload(row_col, st); d_tile_perm.upload(tile_perm, st);
+    d_tile_map.alloc((size_t)nT * nT); launch_fill_tile_map(d_row_ptr.p, d_row_col.p, nT, d_tile_map.p, st);
+    {
+      n_chol_tasks = (int)plan_tasks.size();
+      if (getenv("BAGPU_CHOL_TRACE")) h_chol_tasks = plan_tasks;
+      d_chol_tasks.upload(plan_tasks, st); d_chol_terms.upload(plan_terms, st); d_chol_sync.alloc(chol_sync_ints(n_tiles, nT));
+      sync();
+    }
+    pc.lap("  upload: S + chol plan");
+    d_gn_p.alloc((size_t)nT * T); d_dl_p.alloc((size_t)nT * T); d_tmp_p.alloc((size_t)nT * T);
+    d_gn_p.zero(st); d_dl_p.zero(st);
+    P.S_tiles = d_S.p; P.tile_map = d_tile_map.p; P.tile_perm = d_tile_perm.p; P.nT = nT; P.b_p = d_bp.p; P.rhs_sc = d_rhs_sc.p;
+    sync();
     finish_task_packing();
     pc.lap("  task packing (join)");
     dirty = false;
@@ -1566,7 +1578,7 @@ int bagpu_set_landmarks(bagpu_handle h, uint32_t n, const double* x, const uint3
   h->n_lm_set = n; h->lm_xs.clear();   // x_s is filled by the first Solve()
   h->lm_rel_on_device = false;
   if (dev && n > 0) {
-    GUARD(h->d_lm_xw.upload(x, 4 * (size_t)n, h->st); h->sync();)   // the caller's buffer is free again on return
+    GUARD(h->d_lm_xw.upload(x, 4 * (size_t)n, h->st);)   // DMA in flight while the id arrays are copied below
     h->lm_xw.clear(); h->lm_host_fresh = false;
   } else {
     h->lm_xw.assign(x, x + 4 * (size_t)n); h->lm_host_fresh = true;
@@ -1574,6 +1586,7 @@ int bagpu_set_landmarks(bagpu_handle h, uint32_t n, const double* x, const uint3
   h->lm_ref_pose.assign(rp, rp + n);
   if (rc) h->lm_ref_cam.assign(rc, rc + n); else h->lm_ref_cam.assign(n, 0);
   if (a) h->lm_active.assign(a, a + n); else h->lm_active.assign(n, 1);
+  if (dev && n > 0) { GUARD(h->sync();) }   // the caller's buffer is free again on return
   h->lm_reliable.clear(); h->lm_outliers.clear();   // all reliable, no outliers until a Solve() says otherwise
   h->dirty = true;
   return BAGPU_OK;

@@ -83,6 +83,9 @@ __global__ void __launch_bounds__(256) k_residual(DeviceProblem P) {
 
 // ---------------------------------------------------------------------------------------
 // steepest-descent denominator |J_p b_p + J_l b_l|^2 over projection residuals (cpp:879-906)
+// Every projection Jacobian is B times something (ba_gpu.h), so J_p b_p + J_l b_l = B v with
+//   v = K_meas b_meas - K_ref b_ref - (b_l  or  u b_l)     and     w |B v|^2 = v^T G v
+// from the G record of the last build: no camera model here.
 template <int L>
 __global__ void __launch_bounds__(128) k_sd_denominator(DeviceProblem P) {
   double acc[1] = {0.0};
@@ -90,26 +93,32 @@ __global__ void __launch_bounds__(128) k_sd_denominator(DeviceProblem P) {
     const int lm = (int)P.obs_lm[i];
     LmCtx<L> c;
     load_lm<L>(P, lm, c);
-    ObsJac<L> o;
-    obs_jacobians<L>(P, c, i, o);
-    double v0 = 0.0, v1 = 0.0;
+    const int m = (int)P.obs_pose[i];
+    const bool diff = (m != c.ref_pose);
+    const int mo = P.pose_opt[m];
+    double v[3] = {0.0, 0.0, 0.0};
+    if (diff && mo >= 0) k_times_delta(P, m, c.X, c.rho, P.b_p + (size_t)mo * P.D, v);
+    if (L == 1 && diff && c.ref_opt >= 0) {
+      double y[3];
+      k_times_delta(P, c.ref_pose, c.X, c.rho, P.b_p + (size_t)c.ref_opt * P.D, y);
+      v[0] -= y[0]; v[1] -= y[1]; v[2] -= y[2];
+    }
     if (c.lm_opt >= 0) {
+      if (L == 3) {
 #pragma unroll
-      for (int k = 0; k < L; ++k) { const double b = P.lm_bl[(size_t)lm * L + k]; v0 += o.Jl[k] * b; v1 += o.Jl[L + k] * b; }
-    }
-    if (o.pm >= 0) {
-      const double* bp = P.b_p + (size_t)o.pm * P.D;
+        for (int k = 0; k < 3; ++k) v[k] -= P.lm_bl[(size_t)lm * 3 + k];
+      } else {
+        const int cam = P.obs_cam ? (int)P.obs_cam[i] : 0;
+        const double* tw = P.Tws + ((size_t)m * P.n_cams + cam) * 12 + 9;
+        const double bl = P.lm_bl[lm];
 #pragma unroll
-      for (int k = 0; k < 6; ++k) { v0 += o.Jm[k] * bp[k]; v1 += o.Jm[6 + k] * bp[k]; }
+        for (int k = 0; k < 3; ++k) v[k] -= (c.tws_r[k] - tw[k]) * bl;
+      }
     }
-    if (L == 1 && o.ref_on) {
-      const double* bp = P.b_p + (size_t)c.ref_opt * P.D;
-      double Jr[12];
-      ref_jacobian<L>(c, o.Bp, Jr);
-#pragma unroll
-      for (int k = 0; k < 6; ++k) { v0 += Jr[k] * bp[k]; v1 += Jr[6 + k] * bp[k]; }
-    }
-    acc[0] += P.obs_w[i] * (v0 * v0 + v1 * v1);
+    double G[6], gv[3];
+    load_G(P, i, G);
+    sym3_vec(G, v, gv);
+    acc[0] += v[0] * gv[0] + v[1] * gv[1] + v[2] * gv[2];
   }
   grid_sum_fixed<1>(acc, P.red_partial, P.red_counter, &P.sc->sd_den_proj, false);
 }
@@ -153,16 +162,23 @@ __global__ void __launch_bounds__(128) k_jacobian_rows(DeviceProblem P, double* 
 // share of one observation: w J_l^T J_m delta_p(a)
 template <int L>
 BA_D void back_term(const DeviceProblem& P, const LmCtx<L>& c, int i, int m_known, const double* delta_p, double* acc) {
-  ObsJac<L> o;
-  obs_jacobians<L>(P, c, i, o, m_known);
-  if (o.pm < 0) return;
-  const double* dp = delta_p + (size_t)o.pm * P.D;
-  double t0 = 0.0, t1 = 0.0;
+  // W_a^T delta = w J_l^T J_m delta = -G (K_m delta)   (LmSize 1: -u^T G K_m delta), from the G record of the last build
+  const int m = m_known >= 0 ? m_known : (int)P.obs_pose[i];
+  if (m == c.ref_pose) return;
+  const int mo = P.pose_opt[m];
+  if (mo < 0) return;
+  double y[3], G[6], gy[3];
+  k_times_delta(P, m, c.X, c.rho, delta_p + (size_t)mo * P.D, y);
+  load_G(P, i, G);
+  sym3_vec(G, y, gy);
+  if (L == 3) {
 #pragma unroll
-  for (int a = 0; a < 6; ++a) { t0 += o.Jm[a] * dp[a]; t1 += o.Jm[6 + a] * dp[a]; }
-  const double w = P.obs_w[i];
-#pragma unroll
-  for (int k = 0; k < L; ++k) acc[k] += w * (o.Jl[k] * t0 + o.Jl[L + k] * t1);
+    for (int k = 0; k < 3; ++k) acc[k] -= gy[k];
+  } else {
+    const int cam = P.obs_cam ? (int)P.obs_cam[i] : 0;
+    const double* tw = P.Tws + ((size_t)m * P.n_cams + cam) * 12 + 9;
+    acc[0] -= (c.tws_r[0] - tw[0]) * gy[0] + (c.tws_r[1] - tw[1]) * gy[1] + (c.tws_r[2] - tw[2]) * gy[2];
+  }
 }
 // landmark part and write-out, by one lane holding the landmark's sum
 template <int L>
@@ -171,21 +187,10 @@ BA_D void back_finish(const DeviceProblem& P, int lm, int lo, const double* delt
   if (L == 1) {
     const int rp = (int)P.lm_ref_pose[lm];
     const int ro = P.pose_opt[rp];
-    if (ro >= 0) {   // W_ref^T delta = gbar^T K_ref delta,  K_ref delta = rho x_t - Y x x_w,  x = D delta (ba_gpu.h)
-      const double* dp = delta_p + (size_t)ro * P.D;
-      const uint32_t fr = P.pose_free[rp];
-      double x[6];
-#pragma unroll
-      for (int a = 0; a < 6; ++a) x[a] = ((fr >> a) & 1u) ? dp[a] : 0.0;
-      double xw[3];
-      mat3_vec(P.Rwp + 9 * (size_t)rp, x + 3, xw);
-      const double* tp = P.pose_t + 3 * (size_t)rp;
-      const double rho = r[3];
-      const double Y[3] = {r[0] - rho * tp[0], r[1] - rho * tp[1], r[2] - rho * tp[2]};
-      const double k0 = rho * x[0] - (Y[1] * xw[2] - Y[2] * xw[1]);
-      const double k1 = rho * x[1] - (Y[2] * xw[0] - Y[0] * xw[2]);
-      const double k2 = rho * x[2] - (Y[0] * xw[1] - Y[1] * xw[0]);
-      acc[0] += r[9] * k0 + r[10] * k1 + r[11] * k2;
+    if (ro >= 0) {   // W_ref^T delta = gbar^T K_ref delta
+      double k[3];
+      k_times_delta(P, rp, r, r[3], delta_p + (size_t)ro * P.D, k);
+      acc[0] += r[9] * k[0] + r[10] * k[1] + r[11] * k[2];
     }
     delta_l[lo] = r[8] - r[7] * acc[0];
   } else {

@@ -301,6 +301,27 @@ BA_D void acc_kmk_sym(double* acc, double rho, const double* Y, const double* M)
     for (int r = 0; r <= c; ++r) { acc[k] += col[r]; ++k; }
   }
 }
+// y = K_pose delta = K~ (D delta): x_t = mask . delta[0:3], x_w = R_wp (mask . delta[3:6]), y = rho x_t - (X - rho t_wp) x x_w
+BA_D void k_times_delta(const DeviceProblem& P, int pose, const double* X, double rho, const double* __restrict__ delta, double* y) {
+  const uint32_t fr = P.pose_free[pose];
+  double x[6];
+#pragma unroll
+  for (int a = 0; a < 6; ++a) x[a] = ((fr >> a) & 1u) ? delta[a] : 0.0;
+  double xw[3];
+  mat3_vec(P.Rwp + 9 * (size_t)pose, x + 3, xw);
+  const double* tp = P.pose_t + 3 * (size_t)pose;
+  const double Y[3] = {X[0] - rho * tp[0], X[1] - rho * tp[1], X[2] - rho * tp[2]};
+  y[0] = rho * x[0] - (Y[1] * xw[2] - Y[2] * xw[1]);
+  y[1] = rho * x[1] - (Y[2] * xw[0] - Y[0] * xw[2]);
+  y[2] = rho * x[2] - (Y[0] * xw[1] - Y[1] * xw[0]);
+}
+// the G record of an observation (upper 00 01 02 11 12 22): three 16-byte loads
+BA_D void load_G(const DeviceProblem& P, int obs, double* G) {
+  const double2* g = reinterpret_cast<const double2*>(P.obs_G + (size_t)obs * kObsG);
+  const double2 a = g[0], b = g[1], c = g[2];
+  G[0] = a.x; G[1] = a.y; G[2] = b.x; G[3] = b.y; G[4] = c.x; G[5] = c.y;
+}
+
 // D_p = blkdiag(I, R_wp) with masked parameter columns zeroed: element (q, c), R row-major
 BA_D double d_elem(const double* R, uint32_t free_bits, int q, int c) {
   if (!((free_bits >> c) & 1u)) return 0.0;

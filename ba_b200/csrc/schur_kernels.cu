@@ -136,11 +136,11 @@ BA_D void linearize_one(const DeviceProblem& P, const LmCtx<L>& c, int i, int m,
   obs_linearize<L>(P, c, i, m, c_huber, c2, o);
   P.obs_w[i] = o.w;
   err += o.n2 * o.w;
-  if (o.pm_on) {   // the records are read only through the pose-major lists, which hold exactly these observations
-    double* g = P.obs_G + (size_t)i * kObsG;
-    st4(g, o.G[0], o.G[1], o.G[2], o.G[3]); st4(g + 4, o.G[4], o.G[5], 0.0, 0.0);   // whole sectors
-    st4(P.obs_h + (size_t)i * kObsH, o.h[0], o.h[1], o.h[2], 0.0);
-  }
+  // G for every observation (the steepest-descent denominator and the back-substitution read it as well); h only where the
+  // pose-major lists will ask for it
+  double* g = P.obs_G + (size_t)i * kObsG;
+  st4(g, o.G[0], o.G[1], o.G[2], o.G[3]); st4(g + 4, o.G[4], o.G[5], 0.0, 0.0);   // whole sectors
+  if (o.pm_on) st4(P.obs_h + (size_t)i * kObsH, o.h[0], o.h[1], o.h[2], 0.0);
   sums_add<L>(S, o, lm_on);
 }
 
