@@ -222,6 +222,7 @@ struct bagpu_handle_s {
   bool lm_host_fresh = true;   // false: the current landmarks live on the device only (sent there by the setter, or
                                // refined by a Solve()); the host vectors are filled on demand
   bool lm_rel_on_device = false;
+  bool lm_ids_on_device = false;   // d_lm_ref_pose / d_lm_ref_cam hold the current arrays (sent by bagpu_set_proj_residuals)
   size_t n_lm_set = 0;         // landmarks handed to bagpu_set_landmarks
   std::vector<uint32_t> lm_ref_pose, lm_ref_cam;
   std::vector<uint8_t> lm_active, lm_reliable;
@@ -289,7 +290,7 @@ struct bagpu_handle_s {
   DevBuf<double> d_S, d_S_copy, d_uinv, d_scratch, d_bp, d_rhs_sc, d_rhs_work;
   DevBuf<int> d_tile_map, d_row_ptr, d_row_col, d_chol_sync, d_tile_perm;
   DevBuf<CholTask> d_chol_tasks; DevBuf<CholTerm> d_chol_terms; int n_chol_tasks = 0;
-  DevBuf<Scalars> d_sc; DevBuf<SelectState> d_sel;
+  DevBuf<Scalars> d_sc; DevBuf<SelectState> d_sel; DevBuf<unsigned long long> d_sel_cand, d_sel_all;
   DevBuf<double> d_bl_compact, d_gn_p, d_gn_l, d_dl_p, d_dl_l, d_tmp_p, d_tmp_l;
   DevBuf<double> d_res_out, d_maha_out;
   // other residuals
@@ -307,6 +308,7 @@ struct bagpu_handle_s {
   std::vector<std::vector<double>> rec_dp, rec_dl;
   double proj_error = 0, binary_error = 0, unary_error = 0, inertial_error = 0;
   float phase_ms[BAGPU_PH_COUNT] = {0};
+  float dev_sd_ms = 0;   // development aid (BAGPU_TIMING): device time of the steepest-descent section, not part of any reported phase
   uint64_t launches = 0;
   cudaEvent_t ev[16];
   bool ev_ok = false;
@@ -651,7 +653,8 @@ struct bagpu_handle_s {
     // landmarks
     if (lm_host_fresh) d_lm_xw.upload(lm_xw, st);
     d_lm_x.alloc(4 * n_lm_set); d_bk_lm_x.alloc(4 * n_lm_set);
-    d_lm_ref_pose.upload(lm_ref_pose, st); d_lm_ref_cam.upload(lm_ref_cam, st); d_lm_opt.upload(lm_opt, st);
+    if (!lm_ids_on_device) { d_lm_ref_pose.upload(lm_ref_pose, st); d_lm_ref_cam.upload(lm_ref_cam, st); lm_ids_on_device = true; }
+    d_lm_opt.upload(lm_opt, st);
     if (!lm_rel_on_device) {   // every landmark starts reliable (host copies of these flags exist only after a fetch)
       d_lm_reliable.alloc(n_lm_set);
       if (n_lm_set) CU(cudaMemsetAsync(d_lm_reliable.p, 1, n_lm_set, st));
@@ -906,10 +909,35 @@ struct bagpu_handle_s {
   // replicated list and no collective is issued (unary residuals, evaluated on rank 0 only)
   void run_select(const double* x, size_t n_local, unsigned long long n_total, double* out, bool distributed = true) {
     if (n_total == 0) return;
+    const bool multi = world > 1 && distributed;
     launch_select_init(d_sel.p, n_total / 2, st); ++launches;
-    for (int pass = 0; pass < select_num_passes(); ++pass) {
+    int pass = 0;
+    // Two 12-bit passes (sign + exponent + 13 mantissa bits), then — when the bucket of the k-th value is small enough for one
+    // CTA, which it is unless thousands of values tie — its members are collected, gathered over the ranks and the selection is
+    // finished by one CTA: 2 histogram exchanges + 1 gather instead of 6 exchanges, 3 passes over the data instead of 6.
+    // The branch is taken on the GLOBAL bucket count, which every rank reads: all ranks issue the same collectives.
+    const bool cand_path = (!multi || peer.ok) && !getenv("BAGPU_SELECT_RADIX");
+    if (cand_path) {
+      for (; pass < 2; ++pass) {
+        launch_select_hist(x, n_local, d_sel.p, pass, sms, st); ++launches;
+        if (multi) allreduce_u32(d_sel.p->hist, 4096);
+        launch_select_scan(d_sel.p, pass, out, st); ++launches;
+      }
+      unsigned long long cnt = 0;
+      CU(cudaMemcpyAsync(&cnt, &d_sel.p->bucket_count, sizeof(cnt), cudaMemcpyDeviceToHost, st));
+      sync();
+      if (cnt <= (unsigned long long)kSelCandCap) {
+        d_sel_cand.alloc((size_t)kSelCandCap + 1); d_sel_all.alloc((size_t)kSelCandCap * (multi ? world : 1) + 1);
+        launch_select_compact(x, n_local, d_sel.p, 2, d_sel_cand.p, sms, st); ++launches;
+        const unsigned long long* all = d_sel_cand.p; const unsigned int* all_n = &d_sel.p->cand_n;
+        if (multi) { peer.gather_u64(d_sel_cand.p, &d_sel.p->cand_n, d_sel_all.p, &d_sel.p->all_n, st); ++launches; all = d_sel_all.p; all_n = &d_sel.p->all_n; }
+        launch_select_final(all, all_n, d_sel.p, out, st); ++launches;
+        return;
+      }
+    }
+    for (; pass < select_num_passes(); ++pass) {
       launch_select_hist(x, n_local, d_sel.p, pass, sms, st); ++launches;
-      if (world > 1 && distributed) allreduce_u32(d_sel.p->hist, 4096);
+      if (multi) allreduce_u32(d_sel.p->hist, 4096);
       launch_select_scan(d_sel.p, pass, out, st); ++launches;
     }
   }
@@ -1132,6 +1160,7 @@ struct bagpu_handle_s {
     double e_proj, e_bin, e_un, e_in;
     if (opt.use_dogleg) {
       // steepest descent step (cpp:857-929)
+      CU(cudaEventRecord(ev[12], st));
       if (L > 0 && n_al > 0) { launch_compact_bl(P, d_bl_compact.p, st); ++launches; }
       double n2_bp = 0.0, n2_bl = 0.0;
       dot_pair(d_bp.p, d_bp.p, np, d_bl_compact.p, d_bl_compact.p, (L > 0) ? nl : 0, &n2_bp, &n2_bl, false);
@@ -1142,7 +1171,9 @@ struct bagpu_handle_s {
       double den[2], nn[2];
       CU(cudaMemcpyAsync(den, &d_sc.p->sd_den_proj, 2 * sizeof(double), cudaMemcpyDeviceToHost, st));
       CU(cudaMemcpyAsync(nn, &d_sc.p->dot[0], 2 * sizeof(double), cudaMemcpyDeviceToHost, st));
+      CU(cudaEventRecord(ev[13], st));
       sync();
+      { float ms; cudaEventElapsedTime(&ms, ev[12], ev[13]); dev_sd_ms += ms; }
       n2_bp = nn[0]; n2_bl = nn[1];
       const double numerator = n2_bp + n2_bl;
       const double denominator = den[0] + den[1];
@@ -1324,6 +1355,7 @@ struct bagpu_handle_s {
   void solve(uint32_t max_iter, double gn_damping, bool error_increase_allowed) {
     trace.clear(); rec_dp.clear(); rec_dl.clear();
     for (float& m : phase_ms) m = 0;
+    dev_sd_ms = 0;
     launches = 0;
     summary.iterations = 0;
     if (n_raw == 0 && bin_p1.empty() && un_pose.empty() && imu_p1.empty()) return;
@@ -1363,6 +1395,11 @@ struct bagpu_handle_s {
     sync();
     { float ms; cudaEventElapsedTime(&ms, ev[14], ev[15]); phase_ms[BAGPU_PH_TOTAL] = ms; }
     pcs.lap("solve: prepare + iterations");
+    if (pcs.on) {
+      float sum = 0; for (int i = 0; i < BAGPU_PH_TOTAL; ++i) sum += phase_ms[i];
+      fprintf(stderr, "[bagpu timing]   device: total %.3f ms, phases %.3f, steepest-descent section %.3f, rest (host round trips, vector kernels) %.3f over %u iterations\n",
+              phase_ms[BAGPU_PH_TOTAL], sum, dev_sd_ms, phase_ms[BAGPU_PH_TOTAL] - sum - dev_sd_ms, summary.iterations);
+    }
     if (!opt.keep_on_device) download_state();
     pcs.lap("download_state");
     solved_once = true;
@@ -1576,7 +1613,7 @@ int bagpu_set_landmarks(bagpu_handle h, uint32_t n, const double* x, const uint3
   bool dev = true;
   try { h->ensure_device(); } catch (const std::string&) { dev = false; }
   h->n_lm_set = n; h->lm_xs.clear();   // x_s is filled by the first Solve()
-  h->lm_rel_on_device = false;
+  h->lm_rel_on_device = false; h->lm_ids_on_device = false;
   if (dev && n > 0) {
     GUARD(h->d_lm_xw.upload(x, 4 * (size_t)n, h->st);)   // DMA in flight while the id arrays are copied below
     h->lm_xw.clear(); h->lm_host_fresh = false;
@@ -1606,7 +1643,7 @@ int bagpu_set_proj_residuals(bagpu_handle h, uint32_t n, const double* z, const 
       if (cam) h->d_raw_cam.upload(cam, n, h->st);
       if (w) h->d_raw_w0.upload(w, n, h->st);
       if (api_clock.pc.on) { h->sync(); api_clock.pc.lap("  raw observation upload"); }
-      h->d_lm_ref_pose.upload(h->lm_ref_pose, h->st); h->d_lm_ref_cam.upload(h->lm_ref_cam, h->st);
+      h->d_lm_ref_pose.upload(h->lm_ref_pose, h->st); h->d_lm_ref_cam.upload(h->lm_ref_cam, h->st); h->lm_ids_on_device = true;
       DevBuf<int> flag; flag.alloc(2); flag.zero(h->st);
       launch_validate_obs(h->d_raw_pose.p, h->d_raw_lm.p, cam ? h->d_raw_cam.p : nullptr, n, (uint32_t)np, (uint32_t)nl, h->L, h->d_lm_ref_pose.p,
                           h->d_lm_ref_cam.p, flag.p, h->st);

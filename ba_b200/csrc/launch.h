@@ -8,9 +8,12 @@
 
 namespace bagpu {
 
+constexpr int kSelCandCap = 8191;   // candidates the final single-CTA selection takes (= one rank's share of a peer gather)
 struct SelectState {
   unsigned int hist[4096];
   unsigned long long prefix, k_rem, prefix_next, k_rem_next;
+  unsigned long long bucket_count;   // values (all ranks) in the bucket the last scan chose
+  unsigned int cand_n, all_n;        // local candidates written by k_select_compact; candidates of all ranks after the gather
 };
 
 // unary / binary / inertial residual records in HBM (SoA)
@@ -122,6 +125,10 @@ int select_num_passes();
 void launch_select_init(SelectState* st, unsigned long long k, cudaStream_t s);
 void launch_select_hist(const double* x, size_t n, SelectState* st, int pass, int sms, cudaStream_t s);
 void launch_select_scan(SelectState* st, int pass, double* out, cudaStream_t s);
+// keys whose top 12 * passes_done bits equal the prefix -> cand[0 .. st->cand_n)
+void launch_select_compact(const double* x, size_t n, SelectState* st, int passes_done, unsigned long long* cand, int sms, cudaStream_t s);
+// the st->k_rem-th smallest of all[0 .. *all_n) (at most kSelCandCap keys) -> *out
+void launch_select_final(const unsigned long long* all, const unsigned int* all_n, SelectState* st, double* out, cudaStream_t s);
 
 // reduced solve (chol.cu): tile tasks of the persistent dataflow kernel, built on the host from the tile pattern
 struct CholTask { int kind, i, j, slot, lb, le, pad0, pad1; };

@@ -43,6 +43,44 @@ __global__ void __launch_bounds__(1024) k_peer_allreduce(PeerWindow w, T* buf, i
   }
 }
 
+// all-gather of a few u64 items per rank (the candidates of the exact median): same flag protocol as k_peer_allreduce; a slot
+// holds [count | items]
+__global__ void __launch_bounds__(1024) k_peer_gather(PeerWindow w, const unsigned long long* items, const unsigned int* count,
+                                                      unsigned long long* all, unsigned int* all_n, unsigned long long seq, int* err) {
+  const int tid = threadIdx.x, parity = (int)(seq & 1ull);
+  if (*reinterpret_cast<volatile int*>(err)) return;
+  unsigned int n = *count;
+  if (n > (unsigned int)kPeerGatherCap) n = (unsigned int)kPeerGatherCap;
+  for (int p = 0; p < w.world; ++p) {
+    unsigned long long* dst = reinterpret_cast<unsigned long long*>(slot_ptr(w.win[p], parity, w.rank));
+    if (tid == 0) dst[0] = n;
+    for (unsigned int i = tid; i < n; i += blockDim.x) dst[1 + i] = items[i];
+  }
+  __syncthreads();
+  if (tid < w.world) {
+    __threadfence_system();
+    unsigned long long* f = flag_ptr(w.win[tid], parity, w.rank);
+    asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(f), "l"(seq) : "memory");
+    const unsigned long long* mine = flag_ptr(w.win[w.rank], parity, tid);
+    const long long t0 = clock64();
+    unsigned long long v;
+    do {
+      asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(mine) : "memory");
+      if (v < seq && clock64() - t0 > 120000000000ll) { *err = 1; break; }
+    } while (v < seq);
+  }
+  __syncthreads();
+  unsigned char* local = w.win[w.rank];
+  unsigned int off = 0;
+  for (int q = 0; q < w.world; ++q) {
+    const volatile unsigned long long* src = reinterpret_cast<const volatile unsigned long long*>(slot_ptr(local, parity, q));
+    const unsigned int nq = (unsigned int)src[0];
+    for (unsigned int i = tid; i < nq; i += blockDim.x) all[off + i] = src[1 + i];
+    off += nq;
+  }
+  if (tid == 0) *all_n = off;
+}
+
 struct BulkView { double* base[kPeerMaxWorld]; int rank, world; };
 
 // sum of one 16-byte piece over the ranks, in rank order, delivered to every rank.  All N loads are issued before the
@@ -190,6 +228,9 @@ void PeerReduce::allreduce_f64(double* buf, int n, cudaStream_t st) {
 }
 void PeerReduce::allreduce_u32(unsigned int* buf, int n, cudaStream_t st) {
   k_peer_allreduce<unsigned int><<<1, n >= 1024 ? 1024 : (n > 32 ? ((n + 31) / 32) * 32 : 32), 0, st>>>(w, buf, n, ++seq, d_err);
+}
+void PeerReduce::gather_u64(const unsigned long long* items, const unsigned int* count, unsigned long long* all, unsigned int* all_n, cudaStream_t st) {
+  k_peer_gather<<<1, 1024, 0, st>>>(w, items, count, all, all_n, ++seq, d_err);
 }
 int PeerReduce::error(cudaStream_t st) const {
   if (!d_err) return 0;

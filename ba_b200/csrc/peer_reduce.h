@@ -14,7 +14,9 @@
 #include <cstdint>
 
 constexpr int kPeerMaxWorld = 8;
-constexpr size_t kPeerSlotBytes = 16384;  // one 4096-bin u32 histogram
+constexpr size_t kPeerSlotBytes = 65536;  // all-reduce payloads up to kPeerReduceMax; the candidate gather of the exact median uses the whole slot
+constexpr size_t kPeerReduceMax = 16384;  // one 4096-bin u32 histogram: larger vectors are not worth a single-CTA kernel
+constexpr int kPeerGatherCap = (int)(kPeerSlotBytes / 8) - 1;   // u64 items one rank can contribute to a gather
 constexpr size_t kPeerFlagBytes = 256;    // 2 parities x 8 ranks x u64, padded
 constexpr size_t kPeerWindowBytes = kPeerFlagBytes + 2 * kPeerMaxWorld * kPeerSlotBytes;
 
@@ -34,9 +36,12 @@ struct PeerReduce {
   bool open_peers(const void* handles /* world x 64 bytes */);
   void close_peers();   // unmap the peers' windows (every rank must have done this before any rank frees its own)
   void destroy();       // close_peers + free the local window
-  bool fits(size_t bytes) const { return ok && bytes <= kPeerSlotBytes; }
+  bool fits(size_t bytes) const { return ok && bytes <= kPeerReduceMax; }
   void allreduce_f64(double* buf, int n, cudaStream_t st);
   void allreduce_u32(unsigned int* buf, int n, cudaStream_t st);
+  // all-gather of at most kPeerGatherCap u64 items per rank: every rank ends with the concatenation in rank order in `all`
+  // and the total count in *all_n (device pointers; *count is read on the device)
+  void gather_u64(const unsigned long long* items, const unsigned int* count, unsigned long long* all, unsigned int* all_n, cudaStream_t st);
   int error(cudaStream_t st) const;  // synchronises the stream
 };
 

@@ -9,7 +9,7 @@ BAGPU_TIMING=1 timeout 600 python -m torch.distributed.run --nnodes=1 --nproc-pe
 grep -a "peer" gpurun_out/${TAG}_bench_n2.err | head -6
 python - <<P
 import json
-d=json.load(open("gpurun_out/${TAG}_bench_n2.json"))
+d=json.loads([l for l in open("gpurun_out/${TAG}_bench_n2.json").read().splitlines() if l.startswith("{")][-1])
 def show(n,d):
     print(n, "it/s %.1f ms %.3f build %.3f e2e %.1f"%(d["value"], d["ms_per_step"], d["schur_build_ms_per_iter"], d.get("e2e",{}).get("value",0)), "cost", d["final_cost"])
     print("   phases", {k: round(v,3) for k,v in d["phases_ms_per_iter"].items()})
