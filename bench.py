@@ -397,9 +397,13 @@ def main():
         print(json.dumps(out))
         return
 
-    # stdout carries exactly one line (the JSON): NCCL writes its version banner there unless told otherwise
+    # stdout carries exactly one line (the JSON): NCCL / the process group write a version banner there, so file
+    # descriptor 1 points at stderr until the line is printed
     if os.environ.get("NCCL_DEBUG", "VERSION").upper() == "VERSION":
         os.environ["NCCL_DEBUG"] = "WARN"
+    sys.stdout.flush()
+    saved_stdout = os.dup(1)
+    os.dup2(2, 1)
     import torch
     import torch.distributed as dist
     if not torch.cuda.is_available():
@@ -418,7 +422,10 @@ def main():
         if second is not None:
             second["config"] = config_for(args.also, args.scale, args.gpus)
             out["also"] = {args.also: second}
-        print(json.dumps(out))
+        sys.stdout.flush()
+        os.dup2(saved_stdout, 1)
+        print(json.dumps(out), flush=True)
+        os.dup2(2, 1)
     if world > 1:
         dist.destroy_process_group()
 
