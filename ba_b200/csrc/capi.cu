@@ -1082,12 +1082,13 @@ struct bagpu_handle_s {
   }
 
   // EvaluateResiduals at the current state (cpp:144-274); returns the four sums
-  void evaluate(double* e_proj, double* e_bin, double* e_un, double* e_in) {
+  void evaluate(double* e_proj, double* e_bin, double* e_un, double* e_in, cudaEvent_t mark = nullptr) {
     CU(cudaMemsetAsync(&d_sc.p->eval_proj, 0, 4 * sizeof(double), st));
     launch_evaluate(P, G, &d_sc.p->eval_proj, nullptr, nullptr, 1, 1, st); if (n_obs) ++launches;
     maha0_valid = false;   // overwritten with this state's values; valid for the next build only if the step is kept
     if (rank == 0) launch_other_evaluate(P, R, st, &launches);
     if (world > 1) allreduce_f64(&d_sc.p->eval_proj, 4);
+    if (mark) CU(cudaEventRecord(mark, st));   // end of the step phase on the device: read with the same round trip
     double v[4];
     CU(cudaMemcpyAsync(v, &d_sc.p->eval_proj, 4 * sizeof(double), cudaMemcpyDeviceToHost, st));
     sync();
@@ -1138,18 +1139,41 @@ struct bagpu_handle_s {
       if (rc != 0) throw std::string("cholesky launch: ") + cudaGetErrorString((cudaError_t)rc);
       ++launches;
       launch_permute_tiles(d_gn_p.p, d_rhs_work.p, d_tile_perm.p, T, nT, 0, st); ++launches;
-      int f = 0;
-      CU(cudaMemcpyAsync(&f, d_chol_sync.p + 1, sizeof(int), cudaMemcpyDeviceToHost, st));
-      sync();
-      chol_trace_dump();
-      if (f != 0) { summary.result = BAGPU_FactorizationError; return false; }
+      chol_flag_pending = true;
     }
     summary.result = BAGPU_Success;
     if (n_al > 0) { launch_back_substitute(P, d_tasks.p, n_tasks, d_long_lms.p, n_long, d_gn_p.p, d_gn_l.p, st); launches += (n_tasks > 0) + (n_long > 0); }
     CU(cudaEventRecord(ev[9], st));
+    // ONE host round trip for the whole Gauss-Newton step: the factorisation's failure flag and the two norms of the step come
+    // back together (on a failed factorisation the back-substitution and the norms ran on garbage and are thrown away)
+    const size_t np = (size_t)n_ap * D, nl = (size_t)n_al * std::max(1, L);
+    dot_pair(d_gn_p.p, d_gn_p.p, np, d_gn_l.p, d_gn_l.p, nl, nullptr, nullptr, false);
+    int f = 0;
+    double v[2] = {0.0, 0.0};
+    if (chol_flag_pending) CU(cudaMemcpyAsync(&f, d_chol_sync.p + 1, sizeof(int), cudaMemcpyDeviceToHost, st));
+    CU(cudaMemcpyAsync(v, &d_sc.p->dot[0], 2 * sizeof(double), cudaMemcpyDeviceToHost, st));
     sync();
+    chol_flag_pending = false;
+    chol_trace_dump();
+    gn_norm2_p = v[0]; gn_norm2_l = v[1];
     float ms; cudaEventElapsedTime(&ms, ev[8], ev[9]); phase_ms[BAGPU_PH_SOLVE] += ms;
+    if (f != 0) { summary.result = BAGPU_FactorizationError; return false; }
     return true;
+  }
+  bool chol_flag_pending = false;
+  double gn_norm2_p = 0, gn_norm2_l = 0;   // |delta_p|^2, |delta_l|^2 of the last Gauss-Newton step
+
+  // the steepest-descent sums |b_p|^2, |b_l|^2 and |J_p b_p + J_l b_l|^2 (cpp:858-925), enqueued behind the build
+  void enqueue_sd() {
+    const size_t np = (size_t)n_ap * D, nl = (size_t)n_al * std::max(1, L);
+    CU(cudaEventRecord(ev[12], st));
+    if (L > 0 && n_al > 0) { launch_compact_bl(P, d_bl_compact.p, st); ++launches; }
+    dot_pair(d_bp.p, d_bp.p, np, d_bl_compact.p, d_bl_compact.p, (L > 0) ? nl : 0, nullptr, nullptr, false);
+    CU(cudaMemsetAsync(&d_sc.p->sd_den_proj, 0, 2 * sizeof(double), st));
+    if (n_ap > 0 || n_al > 0) { launch_sd_denominator(P, G, st); if (n_obs) ++launches; }
+    if (n_ap > 0 && rank == 0) launch_other_sd(P, R, st, &launches);
+    if (world > 1) allreduce_f64(&d_sc.p->sd_den_proj, 2);
+    CU(cudaEventRecord(ev[13], st));
   }
 
   // SolveInternal (cpp:838-1161)
@@ -1159,28 +1183,15 @@ struct bagpu_handle_s {
     bool gn_computed = false;
     double e_proj, e_bin, e_un, e_in;
     if (opt.use_dogleg) {
-      // steepest descent step (cpp:857-929)
-      CU(cudaEventRecord(ev[12], st));
-      if (L > 0 && n_al > 0) { launch_compact_bl(P, d_bl_compact.p, st); ++launches; }
-      double n2_bp = 0.0, n2_bl = 0.0;
-      dot_pair(d_bp.p, d_bp.p, np, d_bl_compact.p, d_bl_compact.p, (L > 0) ? nl : 0, &n2_bp, &n2_bl, false);
-      CU(cudaMemsetAsync(&d_sc.p->sd_den_proj, 0, 2 * sizeof(double), st));
-      if (n_ap > 0 || n_al > 0) { launch_sd_denominator(P, G, st); if (n_obs) ++launches; }
-      if (n_ap > 0 && rank == 0) launch_other_sd(P, R, st, &launches);
-      if (world > 1) allreduce_f64(&d_sc.p->sd_den_proj, 2);
-      double den[2], nn[2];
-      CU(cudaMemcpyAsync(den, &d_sc.p->sd_den_proj, 2 * sizeof(double), cudaMemcpyDeviceToHost, st));
-      CU(cudaMemcpyAsync(nn, &d_sc.p->dot[0], 2 * sizeof(double), cudaMemcpyDeviceToHost, st));
-      CU(cudaEventRecord(ev[13], st));
-      sync();
-      { float ms; cudaEventElapsedTime(&ms, ev[12], ev[13]); dev_sd_ms += ms; }
-      n2_bp = nn[0]; n2_bl = nn[1];
+      // steepest descent step (cpp:857-929): its kernels were enqueued right behind the build (enqueue_sd) and their sums came
+      // back with the build scalars in one round trip
+      const double n2_bp = sb.dot[0], n2_bl = sb.dot[1];
+      const double den[2] = {sb.sd_den_proj, sb.sd_den_other};
       const double numerator = n2_bp + n2_bl;
       const double denominator = den[0] + den[1];
       const double factor = numerator / denominator;
       const double delta_sd_norm = std::sqrt(factor * factor * n2_bp + factor * factor * n2_bl);
       tr.sd_numerator = numerator; tr.sd_denominator = denominator; tr.sd_norm = delta_sd_norm;
-      double gn_norm2_p = 0, gn_norm2_l = 0;
       uint32_t iteration_count = 0;
       while (true) {
         iteration_count++;
@@ -1196,7 +1207,6 @@ struct bagpu_handle_s {
           if (!gn_computed) {
             if (!gauss_newton()) return false;
             gn_computed = true;
-            dot_pair(d_gn_p.p, d_gn_p.p, np, d_gn_l.p, d_gn_l.p, nl, &gn_norm2_p, &gn_norm2_l);
           }
           const double delta_gn_norm = std::sqrt(gn_norm2_p + gn_norm2_l);
           tr.gn_norm = delta_gn_norm;
@@ -1242,11 +1252,9 @@ struct bagpu_handle_s {
           launch_update_landmarks(P, d_dl_l.p, 1.0, st); if (n_lms && L) ++launches;
           launch_pose_frames(P, st); ++launches;
         }
-        evaluate(&e_proj, &e_bin, &e_un, &e_in);
+        evaluate(&e_proj, &e_bin, &e_un, &e_in, ev[11]);
         summary.post_solve_norm = e_proj + e_in + e_bin + e_un;
         tr.delta_p_norm = std::sqrt(n2_dl_p); tr.delta_l_norm = std::sqrt(n2_dl_l);
-        CU(cudaEventRecord(ev[11], st));
-        sync();
         { float ms; cudaEventElapsedTime(&ms, ev[10], ev[11]); phase_ms[BAGPU_PH_STEP] += ms; }
         if (summary.post_solve_norm > summary.pre_solve_norm) {
           if (opt.apply_results) restore_state();
@@ -1364,8 +1372,10 @@ struct bagpu_handle_s {
     CU(cudaEventRecord(ev[14], st));
     for (uint32_t kk = 0; kk < max_iter; ++kk) {
       build();
-      const Scalars sb = read_scalars();
+      if (opt.use_dogleg) enqueue_sd();
+      const Scalars sb = read_scalars();   // one round trip: build scalars + steepest-descent sums
       collect_build_times();
+      if (opt.use_dogleg) { float ms; cudaEventElapsedTime(&ms, ev[12], ev[13]); dev_sd_ms += ms; }
       // options.write_reduced_camera_matrix (cpp:600-606): s.txt / rhs.txt of this iteration's system into the working
       // directory, overwritten every iteration like the reference's std::ios_base::trunc streams
       if (opt.write_reduced_camera_matrix && bagpu_dump(this, ".") != BAGPU_OK) throw std::string("write_reduced_camera_matrix: cannot write s.txt / rhs.txt");
