@@ -239,6 +239,14 @@ struct bagpu_handle_s {
   int n_cams = 0, n_poses = 0, n_lms = 0, n_obs = 0, n_obs_total = 0, n_ap = 0, n_al = 0;
   int lm_owner_lo = 0, lm_owner_hi = 0;
   std::vector<int> pose_opt, lm_opt;
+  bool lm_opt_valid = false;
+  void host_lm_opt() {
+    if (lm_opt_valid) return;
+    lm_opt.assign(n_lms, -1);
+    int k = 0;
+    for (int i = 0; i < n_lms; ++i) if (lm_active[i]) lm_opt[i] = k++;
+    lm_opt_valid = true;
+  }
   std::vector<uint8_t> pose_has_res;     // any residual in the pose's lists
   std::vector<uint8_t> pose_has_imu;
   std::vector<uint32_t> lm_obs_start, obs_perm;   // host landmark-major order (pattern queries only, host_order())
@@ -351,8 +359,10 @@ struct bagpu_handle_s {
     if (n_cams == 0) { n_cams = 1; cam_params = {1, 1, 0, 0}; cam_tvs = {0, 0, 0, 1, 0, 0, 0}; }
     pose_opt.assign(n_poses, -1); n_ap = 0;
     for (int i = 0; i < n_poses; ++i) if (pose_active[i]) pose_opt[i] = n_ap++;
-    lm_opt.assign(n_lms, -1); n_al = 0;
-    for (int i = 0; i < n_lms; ++i) if (lm_active[i]) lm_opt[i] = n_al++;
+    // opt ids of the landmarks: with every landmark active (the usual case) opt id = id, written on the device; the host
+    // vector is built only when somebody walks it (pattern queries, bagpu_get_system, the J dump)
+    n_al = (int)std::count_if(lm_active.begin(), lm_active.begin() + n_lms, [](uint8_t a) { return a != 0; });
+    lm_opt.clear(); lm_opt_valid = false;
     // residual membership per pose (reference BundleAdjuster.h:490-497, :405, :452-453, :537-538); the projection
     // residuals add theirs on the device (device_symbolic) or in host_order()
     pose_has_res.assign(n_poses, 0); pose_has_imu.assign(n_poses, 0);
@@ -654,7 +664,8 @@ struct bagpu_handle_s {
     if (lm_host_fresh) d_lm_xw.upload(lm_xw, st);
     d_lm_x.alloc(4 * n_lm_set); d_bk_lm_x.alloc(4 * n_lm_set);
     if (!lm_ids_on_device) { d_lm_ref_pose.upload(lm_ref_pose, st); d_lm_ref_cam.upload(lm_ref_cam, st); lm_ids_on_device = true; }
-    d_lm_opt.upload(lm_opt, st);
+    if (n_al == n_lms) { d_lm_opt.alloc((size_t)n_lms); launch_iota_i32(d_lm_opt.p, (uint32_t)n_lms, st); }
+    else { host_lm_opt(); d_lm_opt.upload(lm_opt, st); }
     if (!lm_rel_on_device) {   // every landmark starts reliable (host copies of these flags exist only after a fetch)
       d_lm_reliable.alloc(n_lm_set);
       if (n_lm_set) CU(cudaMemsetAsync(d_lm_reliable.p, 1, n_lm_set, st));
@@ -1813,6 +1824,7 @@ int bagpu_get_deltas(bagpu_handle h, uint32_t iter, double* dp, double* dl) {
 int bagpu_get_pattern(bagpu_handle h, int which, uint32_t* ncols, uint32_t* nnzb, uint32_t* colptr, uint32_t* rowidx) {
   if (h->dirty) { h->setup(); }
   GUARD(h->host_order();)
+  h->host_lm_opt();
   const int P = h->n_ap, NL = h->n_al, L = h->L;
   std::vector<std::vector<uint32_t>> cols;
   auto lm_poses = [&](int l, std::vector<uint32_t>& out) {   // pose rows of W column l (sorted unique)
@@ -1897,6 +1909,7 @@ int bagpu_get_system(bagpu_handle h, double* s_dense, double* rhs_sc, double* rh
     if (rhs_p) h->d_bp.download(rhs_p, n, h->st);
     const int Ls = std::max(1, h->L);
     if ((rhs_l || v_inv) && h->L > 0 && h->n_lms) {
+      h->host_lm_opt();
       std::vector<double> bl((size_t)h->n_lms * Ls), rec((size_t)h->n_lms * kLmRec);
       h->d_lm_bl.download(bl.data(), bl.size(), h->st); h->d_lm_rec.download(rec.data(), rec.size(), h->st);
       h->sync();
@@ -1955,6 +1968,7 @@ int bagpu_dump(bagpu_handle h, const char* dir) {
     h->sync();
   )
   GUARD(h->host_ids();)
+  h->host_lm_opt();
   FILE* fj = fopen((d + "/j_pr.txt").c_str(), "w");
   FILE* fr = fopen((d + "/r_pr.txt").c_str(), "w");
   FILE* fl = fopen((d + "/j_l.txt").c_str(), "w");

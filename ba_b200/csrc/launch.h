@@ -89,6 +89,7 @@ void launch_tile_pattern(const uint32_t* starts, const uint32_t* perm, const uin
 void launch_cond_error(const uint32_t* obs_pose, const uint32_t* obs_lm, const uint32_t* obs_perm, uint32_t n, const uint32_t* lm_ref_pose,
                        const int* pose_opt, const double* maha_by_id, const double* w, double* out, cudaStream_t st);
 void launch_scatter_by_perm(const uint32_t* perm, const double* in, uint32_t n, double* out, cudaStream_t st);
+void launch_iota_i32(int* v, uint32_t n, cudaStream_t st);   // v[i] = i
 void launch_reliable_merge(uint8_t* rel, unsigned int* unrel, uint32_t n, int phase, cudaStream_t st);
 
 // block-Jacobi PCG on the tiled S (pcg.cu)

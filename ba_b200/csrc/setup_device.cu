@@ -255,6 +255,9 @@ __global__ void k_reliable_merge(uint8_t* rel, unsigned int* unrel, uint32_t n, 
   if (phase == 0) unrel[i] = rel[i] ? 0u : 1u;
   else if (unrel[i]) rel[i] = 0;
 }
+void launch_iota_i32(int* v, uint32_t n, cudaStream_t st) {
+  if (n) k_iota<<<blocks_for(n), 256, 0, st>>>(reinterpret_cast<uint32_t*>(v), n);
+}
 void launch_reliable_merge(uint8_t* rel, unsigned int* unrel, uint32_t n, int phase, cudaStream_t st) {
   if (n) k_reliable_merge<<<blocks_for(n), 256, 0, st>>>(rel, unrel, n, phase);
 }
