@@ -26,6 +26,9 @@ s.set_options(o)
 ids = [BundleAdjusterGPU.nccl_unique_id() if rank == 0 else None]
 dist.broadcast_object_list(ids, src=0)
 s.comm_init(rank, world, ids[0])
+if os.environ.get("MG_RELOAD") == "1":
+    # a smaller problem first in the SAME handle: the peer-mapped system window must be re-allocated for the larger one
+    s.load(make("c1", 0.2)); s.solve(2)
 s.load(p)
 sm = s.solve(iters)
 tr = s.get_trace()
@@ -38,8 +41,9 @@ if rank == 0 and not all(t == all_tr[0] for t in all_tr):
     for r_, t_ in enumerate(all_tr):
         print("bagpu-test rank %d trace %s" % (r_, t_), file=sys.stderr)
 assert all(t == all_tr[0] for t in all_tr), "ranks disagree on the trace"
+other = s.get_other_residuals()     # collective: every rank calls it
 if rank == 0:
-    np.savez(out, iterations=sm.iterations, result=sm.result,
+    np.savez(out, un_maha=other["un_maha"], bin_maha=other["bin_maha"], imu_maha=other["imu_maha"], un_cov_inv=other["un_cov_inv"], iterations=sm.iterations, result=sm.result,
              post=[t["post_solve_norm"] for t in tr], pre=[t["pre_solve_norm"] for t in tr],
              median=[t["median_maha"] for t in tr], delta=[t["delta_norm"] for t in tr],
              poses=np.asarray(poses["t_wp"] if isinstance(poses, dict) else poses, float),

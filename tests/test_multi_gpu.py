@@ -24,9 +24,9 @@ def _n_gpus():
     return torch.cuda.device_count()
 
 
-def _run_sharded(tmp_path, tag, name, scale, iters, p2p, port):
+def _run_sharded(tmp_path, tag, name, scale, iters, p2p, port, reload=False):
     out = str(tmp_path / ("%s.npz" % tag))
-    env = dict(os.environ, BAGPU_P2P="1" if p2p else "0")
+    env = dict(os.environ, BAGPU_P2P="1" if p2p else "0", MG_RELOAD="1" if reload else "0")
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr", "127.0.0.1",
            "--master-port", str(port), os.path.join(ROOT, "tests", "_multi_gpu_worker.py"), out, name, str(scale), str(iters)]
     r = subprocess.run(cmd, env=env, cwd=ROOT, capture_output=True, text=True, timeout=240)
@@ -34,7 +34,7 @@ def _run_sharded(tmp_path, tag, name, scale, iters, p2p, port):
     return np.load(out)
 
 
-def _single(name, scale, iters):
+def _single(name, scale, iters, reload=False):
     from ba_b200.capi import BundleAdjusterGPU
     p = make(name, scale)
     s = BundleAdjusterGPU(p.lm_dim, p.pose_dim)
@@ -43,10 +43,14 @@ def _single(name, scale, iters):
         setattr(o, k_, v_)
     if hasattr(p, "gravity"):
         o.gravity[0], o.gravity[1], o.gravity[2] = [float(x) for x in p.gravity]
-    s.set_options(o); s.load(p)
+    s.set_options(o)
+    if reload:
+        s.load(make("c1", 0.2)); s.solve(2)
+    s.load(p)
     sm = s.solve(iters)
     tr = s.get_trace()
-    res = dict(iterations=sm.iterations, result=sm.result, post=np.array([t["post_solve_norm"] for t in tr]),
+    other = s.get_other_residuals()
+    res = dict(un_maha=other["un_maha"], bin_maha=other["bin_maha"], imu_maha=other["imu_maha"], un_cov_inv=other["un_cov_inv"],iterations=sm.iterations, result=sm.result, post=np.array([t["post_solve_norm"] for t in tr]),
                median=np.array([t["median_maha"] for t in tr]), poses=s.get_poses()["t_wp"],
                lms=s.get_landmarks()["x_w"] if p.lm_dim else np.zeros(0),
                reliable=s.get_landmarks()["is_reliable"] if p.lm_dim else np.zeros(0),
@@ -74,8 +78,24 @@ def test_two_gpu_solve_matches_single_gpu(tmp_path, name, scale, iters, tol):
         np.testing.assert_allclose(got["median"], one["median"], rtol=tol)
         np.testing.assert_allclose(got["poses"], one["poses"], rtol=0, atol=1e-7 * (tol / 1e-9))
         np.testing.assert_allclose(got["lms"], one["lms"], rtol=0, atol=1e-6 * (tol / 1e-9))
+        # per-residual outputs of the replicated residual types live on rank 0 and are handed to every rank
+        for k in ("un_maha", "bin_maha", "imu_maha", "un_cov_inv"):
+            d = np.linalg.norm(np.asarray(got[k]) - np.asarray(one[k]))
+            assert d <= max(tol, 1e-8) * 100 * max(np.linalg.norm(one[k]), 1e-300), (k, d)
         # flags and counts set by the owning rank only, merged at the end of Solve()
         np.testing.assert_array_equal(got["reliable"], one["reliable"])
         np.testing.assert_array_equal(got["outliers"], one["outliers"])
     # both reduction paths sum the ranks' contributions; the peer path does it in rank order on every rank
     np.testing.assert_allclose(two["post"], nccl["post"], rtol=tol / 10)
+
+
+def test_second_larger_problem_in_the_same_handle(tmp_path):
+    """A handle that has solved a small problem is given a larger one: the peer-mapped allocation that holds the reduced system
+    is unmapped by every rank, freed, re-created and re-exchanged (capi.cu, ensure_bulk_window)."""
+    if _n_gpus() < 2:
+        pytest.skip("needs two GPUs")
+    one = _single("c4", 0.02, 4, reload=True)
+    two = _run_sharded(tmp_path, "reload", "c4", 0.02, 4, True, 29613, reload=True)
+    assert int(two["iterations"]) == one["iterations"]
+    np.testing.assert_allclose(two["post"], one["post"], rtol=1e-9)
+    np.testing.assert_allclose(two["poses"], one["poses"], rtol=0, atol=1e-7)
