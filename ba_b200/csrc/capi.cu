@@ -684,7 +684,7 @@ struct bagpu_handle_s {
     std::vector<CholTask> plan_tasks; std::vector<CholTerm> plan_terms;
     std::string tiler_err;
     std::thread tiler([&]() {
-      try { tile_structure(present); chol_build_plan(nT, row_ptr, row_col, plan_tasks, plan_terms); }
+      try { tile_structure(present); chol_build_plan(T, nT, row_ptr, row_col, plan_tasks, plan_terms); }
       catch (const std::exception& e) { tiler_err = e.what(); }
     });
     struct Joiner { std::thread& t; ~Joiner() { if (t.joinable()) t.join(); } } tiler_guard{tiler};
@@ -1145,7 +1145,7 @@ struct bagpu_handle_s {
       if (rc == 1) { summary.result = BAGPU_SolverError; return false; }
     } else if (n_ap > 0) {
       launch_permute_tiles(d_rhs_work.p, d_rhs_sc.p, d_tile_perm.p, T, nT, 1, st); ++launches;
-      const int rc = launch_cholesky_solve(T, d_S.p, d_uinv.p, d_scratch.p, d_rhs_work.p, d_chol_tasks.p, d_chol_terms.p, n_chol_tasks,
+      const int rc = launch_cholesky_solve(T, d_S.p, d_uinv.p, d_scratch.p, d_rhs_work.p, d_chol_tasks.p, d_chol_terms.p, d_row_ptr.p, d_row_col.p, n_chol_tasks,
                                            d_chol_sync.p, n_tiles, nT, sms, st, chol_trace_buf());
       if (rc != 0) throw std::string("cholesky launch: ") + cudaGetErrorString((cudaError_t)rc);
       ++launches;

@@ -21,8 +21,11 @@
 //              (one barrier per column) -> U_kk^-1, Sigma, y_k, z_k
 //     i <  j : U_ij = Sigma U_ii^-T R (GEMM), c_ij = U_ij^T y_i (its share of the forward
 //              substitution, summed in fixed order by the diagonal task of column j)
-//   backward substitution, rows bottom-up: tile tasks p_kj = U_kj x_j (tile prefetched into
-//       registers before x_j exists), row task x_k = U_kk^-1 (z_k - sum_j p_kj).
+//   backward substitution: consecutive rows that depend on each other (tile (i, i+1) exists: a dense separator of the
+//       nested dissection, a band) form a CHAIN that ONE CTA solves bottom-up without leaving the SM — x of the chain stays
+//       in shared memory, the chain's own tiles are streamed from L2 — because a dependent row costs two flag hops (~8 us)
+//       when every row is a task of its own and ~2 us inside a chain.  Tiles whose column lies outside the chain are
+//       tile tasks p_kj = U_kj x_j as before (prefetched into registers before x_j exists), run by other CTAs.
 // Every tile is written by exactly one task and all sums run in a fixed order: the solve is
 // bit-reproducible.  All T x T x T products run on the FP64 tensor pipe (mma.sync.m8n8k4.f64 —
 // tcgen05 has no FP64 kind, so DMMA is the FP64 tensor path on sm_100a), fragments loaded
@@ -46,6 +49,12 @@ BA_D int ld_acquire(const int* p) {
 }
 BA_D void st_release(int* p, int v) { asm volatile("st.release.gpu.global.s32 [%0], %1;" ::"l"(p), "r"(v) : "memory"); }
 BA_D double ldcg(const double* p) { return __ldcg(p); }
+BA_D void cp_async16(void* dst_shared, const void* src) {
+  const unsigned d = (unsigned)__cvta_generic_to_shared(dst_shared);
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(d), "l"(src) : "memory");
+}
+BA_D void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N> BA_D void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
 // reciprocal off the critical path of the pivot chain: MUFU seed + two Newton steps (~1 ulp)
 BA_D double fast_rcp(double d) {
   double x;
@@ -59,7 +68,10 @@ BA_D double fast_rcp(double d) {
 BA_D unsigned long long gtime() { unsigned long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); return t; }
 #define CHOL_STAMP(slot) do { if (c.trace && tid == 0) c.trace[(size_t)t * 4 + (slot)] = gtime(); } while (0)
 
-enum { kTaskDiag = 0, kTaskOff = 1, kTaskBackTile = 2, kTaskBackRow = 3 };
+enum { kTaskDiag = 0, kTaskOff = 1, kTaskBackTile = 2, kTaskBackRow = 3, kTaskBackChain = 4 };
+constexpr int kMaxChain = 16;   // rows per backward chain (their x live in shared memory)
+// the 960 threads of T = 120 have 64 registers each: one prefetched tile, not three
+constexpr int chol_chain_near(int T) { return T <= 72 ? 3 : 1; }
 
 struct CholDev {
   double* tiles;        // S tiles (off-diagonal tiles are overwritten by U_kj)
@@ -72,6 +84,8 @@ struct CholDev {
   double* pvec;         // n_tiles*T: backward-substitution share of each off-diagonal tile
   const CholTask* tasks;
   const CholTerm* terms;
+  const int* row_ptr;   // CSR of the off-diagonal tile columns per row (ascending), slot(k, k) = k + row_ptr[k]
+  const int* row_col;
   int* sync;            // [0] task counter, [1] first failing pivot + 1, then tile_flag[n_tiles], diag_flag[nT], x_flag[nT], row_count[nT]
   int n_tasks, n_tiles, nT;
   unsigned long long* trace;   // development aid: 4 globaltimer stamps per task (claim, inputs ready, computed, published)
@@ -84,17 +98,30 @@ template <int T> struct CholCfg {
   static constexpr int LD = T + 1;
   static constexpr int NG2 = NT / T;               // thread groups of the matrix-vector tasks
   static constexpr int XC = (T + NG2 - 1) / NG2;
-  static constexpr size_t smem = sizeof(double) * (size_t)(T * LD + 5 * T + NG2 * T);
+  // Operand tiles of the T x T x T products are staged in shared memory with cp.async (two stages of two tiles, column
+  // stride SS: SS mod 16 = +-4 keeps the DMMA fragment loads of a half-warp on 16 different banks).  The elimination
+  // workspace M is only live after the products, so it shares the space.  T = 120 does not fit and loads fragments from L2.
+  static constexpr bool STAGED = T <= 72;
+  static constexpr int NEAR = chol_chain_near(T);  // columns next to the diagonal that a backward chain multiplies itself
+  static constexpr int SS = T + 4;
+  static constexpr int TILE_S = T * SS;            // doubles per staged tile
+  static constexpr int STAGE = STAGED ? 4 * TILE_S + 2 * T : 0;
+  static constexpr int REGION0 = STAGE > T * LD ? STAGE : T * LD;
+  static constexpr size_t smem = sizeof(double) * (size_t)(REGION0 + 5 * T + NG2 * T);
 };
 
 template <int T>
 __global__ void __launch_bounds__(CholCfg<T>::NT, 1) k_chol_dataflow(CholDev c) {
   typedef CholCfg<T> Cfg;
   constexpr int LD = Cfg::LD, NS = Cfg::NS, MH = Cfg::MH, NT = Cfg::NT, KQ = T / 4, NG2 = Cfg::NG2, XC = Cfg::XC;
-  extern __shared__ double sm[];
+  constexpr int SS = Cfg::SS, TILE_S = Cfg::TILE_S;
+  extern __shared__ __align__(16) double sm[];
   __shared__ int s_task, s_ready;
+  __shared__ int s_tsa[32], s_tsb[32], s_tk[32];   // the polled terms (tile slots, producing row)
   double* M = sm;                  // [T][LD]
-  double* av = M + T * LD;         // |d|^-1/2
+  double* stg = sm;                // staged operand tiles [2 stages][A, B][T][SS], then Sigma [2][T]  (STAGED only; aliases M)
+  double* sgs = sm + 4 * TILE_S;
+  double* av = sm + Cfg::REGION0;  // |d|^-1/2
   double* sv = av + T;             // sign(d)
   double* part = sv + T;           // [2][T]
   double* dinv = part + 2 * T;     // 1 / d
@@ -131,6 +158,38 @@ __global__ void __launch_bounds__(CholCfg<T>::NT, 1) k_chol_dataflow(CholDev c) 
       // diagonal task: the forward-substitution shares c_ik of the same terms are folded in as the terms arrive
       const bool bsum_on = (tk.kind == kTaskDiag) && tid < T;
       double bsum = bsum_on ? c.rhs[(size_t)tk.i * T + tid] : 0.0;
+      // A_ij in C-fragment layout, fetched now so that the latency is off the path behind the last term
+      const double* Aij = c.tiles + (size_t)tk.slot * T * T;
+      double a0[MH], a1[MH];
+#pragma unroll
+      for (int mi = 0; mi < MH; ++mi) {
+        const int mb = mlo + mi;
+        a0[mi] = 0.0; a1[mi] = 0.0;
+        if (mb < mhi) {
+          const int r = mb * 8 + gid, cc = n0 + 2 * tig;
+          a0[mi] = Aij[(size_t)cc * T + r]; a1[mi] = Aij[(size_t)(cc + 1) * T + r];
+        }
+      }
+      // one term's operand tiles (and Sigma of the producing row) into stage buffer `buf`; q indexes the polled batch
+      auto stage_term = [&](int q, int buf) {
+        const int sa = s_tsa[q], sb = s_tsb[q];
+        double* dA = stg + (size_t)buf * 2 * TILE_S;
+        const double* gA = c.tiles + (size_t)sa * T * T;
+        for (int ch = tid; ch < T * T / 2; ch += NT) {
+          const int col = ch / (T / 2), w = ch - col * (T / 2);
+          cp_async16(dA + col * SS + 2 * w, gA + (size_t)col * T + 2 * w);
+        }
+        if (sb != sa) {
+          double* dB = dA + TILE_S;
+          const double* gB = c.tiles + (size_t)sb * T * T;
+          for (int ch = tid; ch < T * T / 2; ch += NT) {
+            const int col = ch / (T / 2), w = ch - col * (T / 2);
+            cp_async16(dB + col * SS + 2 * w, gB + (size_t)col * T + 2 * w);
+          }
+        }
+        if (tid < T / 2) cp_async16(sgs + buf * T + 2 * tid, c.sgn + (size_t)s_tk[q] * T + 2 * tid);
+        cp_async_commit();
+      };
       for (int e = tk.lb; e < tk.le;) {
         if (warp == 0) {
           const int idx = e + lane;
@@ -138,39 +197,65 @@ __global__ void __launch_bounds__(CholCfg<T>::NT, 1) k_chol_dataflow(CholDev c) 
           if (idx < tk.le) {
             const CholTerm tm = c.terms[idx];
             ready = ld_acquire(tile_flag + tm.sa) != 0 && ld_acquire(tile_flag + tm.sb) != 0;
+            s_tsa[lane] = tm.sa; s_tsb[lane] = tm.sb; s_tk[lane] = tm.k;
           }
           const unsigned m = __ballot_sync(0xffffffffu, ready);
           if (lane == 0) s_ready = (m == 0xffffffffu) ? 32 : (__ffs(~m) - 1);
         }
         __syncthreads();
         const int nr = s_ready;
-        __syncthreads();
-        if (nr == 0) { __nanosleep(40); continue; }
-        for (int q = 0; q < nr; ++q) {
-          const CholTerm tm = c.terms[e + q];
-          const double* Ua = c.tiles + (size_t)tm.sa * T * T;
-          const double* Ub = c.tiles + (size_t)tm.sb * T * T;
-          const double* sg = c.sgn + (size_t)tm.k * T;
-          if (bsum_on) bsum -= ldcg(c.cvec + (size_t)tm.sa * T + tid);
-          double bfr[KQ];
+        if (nr == 0) { __syncthreads(); __nanosleep(40); continue; }
+        if constexpr (Cfg::STAGED) {
+          stage_term(0, 0);
+          for (int q = 0; q < nr; ++q) {
+            const double cv = bsum_on ? ldcg(c.cvec + (size_t)s_tsa[q] * T + tid) : 0.0;
+            if (q + 1 < nr) { stage_term(q + 1, (q + 1) & 1); cp_async_wait<1>(); } else { cp_async_wait<0>(); }
+            __syncthreads();
+            const double* As = stg + (size_t)(q & 1) * 2 * TILE_S;
+            const double* Bs = (s_tsb[q] != s_tsa[q]) ? As + TILE_S : As;
+            const double* sg = sgs + (q & 1) * T;
+            double bfr[KQ];
 #pragma unroll
-          for (int kq = 0; kq < KQ; ++kq) bfr[kq] = ldcg(Ub + (size_t)(n0 + gid) * T + kq * 4 + tig) * ldcg(sg + kq * 4 + tig);
+            for (int kq = 0; kq < KQ; ++kq) bfr[kq] = Bs[(n0 + gid) * SS + kq * 4 + tig] * sg[kq * 4 + tig];
 #pragma unroll
-          for (int mi = 0; mi < MH; ++mi) {
-            const int mb = mlo + mi;
-            if (mb < mhi) {
-              double afr[KQ];
+            for (int mi = 0; mi < MH; ++mi) {
+              const int mb = mlo + mi;
+              if (mb < mhi) {
 #pragma unroll
-              for (int kq = 0; kq < KQ; ++kq) afr[kq] = ldcg(Ua + (size_t)(mb * 8 + gid) * T + kq * 4 + tig);
+                for (int kq = 0; kq < KQ; ++kq) dmma_m8n8k4(acc0[mi], acc1[mi], As[(mb * 8 + gid) * SS + kq * 4 + tig], bfr[kq]);
+              }
+            }
+            bsum -= cv;
+            __syncthreads();     // the buffer is refilled two terms on; s_t* by the next poll
+          }
+        } else {
+          for (int q = 0; q < nr; ++q) {
+            const int sa = s_tsa[q], sb = s_tsb[q];
+            const double* Ua = c.tiles + (size_t)sa * T * T;
+            const double* Ub = c.tiles + (size_t)sb * T * T;
+            const double* sg = c.sgn + (size_t)s_tk[q] * T;
+            if (bsum_on) bsum -= ldcg(c.cvec + (size_t)sa * T + tid);
+            double bfr[KQ];
 #pragma unroll
-              for (int kq = 0; kq < KQ; ++kq) dmma_m8n8k4(acc0[mi], acc1[mi], afr[kq], bfr[kq]);
+            for (int kq = 0; kq < KQ; ++kq) bfr[kq] = ldcg(Ub + (size_t)(n0 + gid) * T + kq * 4 + tig) * ldcg(sg + kq * 4 + tig);
+#pragma unroll
+            for (int mi = 0; mi < MH; ++mi) {
+              const int mb = mlo + mi;
+              if (mb < mhi) {
+                double afr[KQ];
+#pragma unroll
+                for (int kq = 0; kq < KQ; ++kq) afr[kq] = ldcg(Ua + (size_t)(mb * 8 + gid) * T + kq * 4 + tig);
+#pragma unroll
+                for (int kq = 0; kq < KQ; ++kq) dmma_m8n8k4(acc0[mi], acc1[mi], afr[kq], bfr[kq]);
+              }
             }
           }
+          __syncthreads();
         }
         e += nr;
       }
       CHOL_STAMP(1);
-      double* Aij = c.tiles + (size_t)tk.slot * T * T;
+      double* Aout = c.tiles + (size_t)tk.slot * T * T;
       if (tk.kind == kTaskDiag) {
         const int k = tk.i;
         // R (upper) into M, row-major, zero below the diagonal; column T = b_k - sum c_ik
@@ -179,8 +264,8 @@ __global__ void __launch_bounds__(CholCfg<T>::NT, 1) k_chol_dataflow(CholDev c) 
           const int mb = mlo + mi;
           if (mb < mhi) {
             const int r = mb * 8 + gid, cc = n0 + 2 * tig;
-            M[r * LD + cc] = (r <= cc) ? Aij[(size_t)cc * T + r] - acc0[mi] : 0.0;
-            M[r * LD + cc + 1] = (r <= cc + 1) ? Aij[(size_t)(cc + 1) * T + r] - acc1[mi] : 0.0;
+            M[r * LD + cc] = (r <= cc) ? a0[mi] - acc0[mi] : 0.0;
+            M[r * LD + cc + 1] = (r <= cc + 1) ? a1[mi] - acc1[mi] : 0.0;
           }
         }
         if (bsum_on) M[tid * LD + T] = bsum;
@@ -283,8 +368,8 @@ __global__ void __launch_bounds__(CholCfg<T>::NT, 1) k_chol_dataflow(CholDev c) 
           const int mb = mlo + mi;
           if (mb < mhi) {
             const int r = mb * 8 + gid, cc = n0 + 2 * tig;
-            M[cc * LD + r] = Aij[(size_t)cc * T + r] - acc0[mi];
-            M[(cc + 1) * LD + r] = Aij[(size_t)(cc + 1) * T + r] - acc1[mi];
+            M[cc * LD + r] = a0[mi] - acc0[mi];
+            M[(cc + 1) * LD + r] = a1[mi] - acc1[mi];
           }
         }
         if (tid == 0) { while (ld_acquire(diag_flag + k) == 0) __nanosleep(40); }
@@ -293,6 +378,22 @@ __global__ void __launch_bounds__(CholCfg<T>::NT, 1) k_chol_dataflow(CholDev c) 
         const double* X = c.uinv + (size_t)k * T * T;
         const double* sg = c.sgn + (size_t)k * T;
         const double* yk = c.y + (size_t)k * T;
+        double* Xs = stg + TILE_S;       // behind M
+        if constexpr (Cfg::STAGED) {
+          for (int ch = tid; ch < T * T / 2; ch += NT) {
+            const int col = ch / (T / 2), w = ch - col * (T / 2);
+            cp_async16(Xs + col * SS + 2 * w, X + (size_t)col * T + 2 * w);
+          }
+          cp_async_commit();
+        }
+        double wv[MH], yv[MH];
+#pragma unroll
+        for (int mi = 0; mi < MH; ++mi) {
+          const int mb = mlo + mi;
+          wv[mi] = 0.0; yv[mi] = 0.0;
+          if (mb < mhi) { wv[mi] = ldcg(sg + mb * 8 + gid); yv[mi] = ldcg(yk + mb * 8 + gid); }
+        }
+        if constexpr (Cfg::STAGED) { cp_async_wait<0>(); __syncthreads(); }
         double s0 = 0.0, s1 = 0.0;
 #pragma unroll
         for (int mi = 0; mi < MH; ++mi) {
@@ -304,16 +405,16 @@ __global__ void __launch_bounds__(CholCfg<T>::NT, 1) k_chol_dataflow(CholDev c) 
             for (int kq = 0; kq < KQ; ++kq) {
               if (kq * 4 <= mb * 8 + 7) {       // U_kk^-T is lower triangular
                 const int kk = kq * 4 + tig;
-                const double a = (kk <= r) ? ldcg(X + (size_t)r * T + kk) : 0.0;
+                double a;
+                if constexpr (Cfg::STAGED) a = (kk <= r) ? Xs[r * SS + kk] : 0.0;
+                else a = (kk <= r) ? ldcg(X + (size_t)r * T + kk) : 0.0;
                 dmma_m8n8k4(c0, c1, a, M[(n0 + gid) * LD + kk]);
               }
             }
-            const double w = ldcg(sg + r);
-            const double u0 = w * c0, u1 = w * c1;
-            double* o = Aij + (size_t)(n0 + 2 * tig) * T + r;
+            const double u0 = wv[mi] * c0, u1 = wv[mi] * c1;
+            double* o = Aout + (size_t)(n0 + 2 * tig) * T + r;
             o[0] = u0; o[T] = u1;
-            const double yv = ldcg(yk + r);
-            s0 += u0 * yv; s1 += u1 * yv;
+            s0 += u0 * yv[mi]; s1 += u1 * yv[mi];
           }
         }
         // c_kj[col] = sum_r U_kj[r][col] y_k[r]: reduce over the 8 rows of the lane group, then the two halves
@@ -326,6 +427,99 @@ __global__ void __launch_bounds__(CholCfg<T>::NT, 1) k_chol_dataflow(CholDev c) 
         if (tid == 0) { __threadfence(); st_release(tile_flag + tk.slot, 1); }
         CHOL_STAMP(3);
       }
+    } else if (tk.kind == kTaskBackChain) {
+      // ---- backward substitution of a chain of dependent rows k_hi .. k_lo, bottom-up, on this SM ---------------------------
+      // Row i's tiles in the columns i+1 .. i+NEAR of the chain are multiplied here (x from shared memory, the tiles, U_ii^-1 and
+      // z_i prefetched into registers one row ahead); every other tile of the row is a kTaskBackTile of another CTA, whose
+      // x_j was published at least NEAR rows earlier.
+      constexpr int NEAR = Cfg::NEAR;
+      const int g = tid / T, r = tid - g * T;
+      const bool on = g < NG2;
+      const int k_hi = tk.i, k_lo = tk.j, n_rows = k_hi - k_lo + 1;
+      double* xs = M;                              // x of the chain's rows: xs[(i - k_lo) * T + c]
+      double* part3 = M + kMaxChain * T;           // [NG2][T]
+      __shared__ int s_rp[kMaxChain + 1], s_rc[kMaxChain * 3];
+      // once diag k_hi is published so is everything the factorisation wrote for the chain's rows (diag i+1 depends on tile (i, i+1))
+      if (tid == 0) { while (ld_acquire(diag_flag + k_hi) == 0) __nanosleep(40); }
+      if (tid <= n_rows) s_rp[tid] = c.row_ptr[k_lo + tid];
+      __syncthreads();
+      if (tid < n_rows * NEAR) {
+        const int ri = tid / NEAR, q = tid - ri * NEAR;
+        const int e = s_rp[ri] + q;
+        const int col = e < s_rp[ri + 1] ? c.row_col[e] : 0x7fffffff;
+        s_rc[ri * 3 + q] = (col <= k_hi && col <= k_lo + ri + NEAR) ? col : 0x7fffffff;
+      }
+      __syncthreads();
+      double ureg[NEAR][XC], xreg[XC], zreg = 0.0;
+      auto load_row = [&](int i, double (&u)[NEAR][XC], double (&x)[XC], double& z) {
+        const int ri = i - k_lo, base = i + s_rp[ri];
+#pragma unroll
+        for (int q = 0; q < NEAR; ++q) {
+          const bool have = s_rc[ri * 3 + q] != 0x7fffffff;
+          const double* U = c.tiles + (size_t)(base + 1 + q) * T * T;
+#pragma unroll
+          for (int qq = 0; qq < XC; ++qq) { const int col = g + qq * NG2; u[q][qq] = (on && have && col < T) ? ldcg(U + (size_t)col * T + r) : 0.0; }
+        }
+        const double* X = c.uinv + (size_t)i * T * T;
+#pragma unroll
+        for (int qq = 0; qq < XC; ++qq) { const int col = g + qq * NG2; x[qq] = (on && col < T && col >= r) ? ldcg(X + (size_t)col * T + r) : 0.0; }
+        z = tid < T ? ldcg(c.z + (size_t)i * T + tid) : 0.0;
+      };
+      load_row(k_hi, ureg, xreg, zreg);
+      for (int i = k_hi; i >= k_lo; --i) {
+        const int ri = i - k_lo, base = i + s_rp[ri];
+        int n_in = 0;
+#pragma unroll
+        for (int q = 0; q < NEAR; ++q) n_in += s_rc[ri * 3 + q] != 0x7fffffff;
+        const int n_all = s_rp[ri + 1] - s_rp[ri];
+        if (on) {
+          double a = 0.0;
+#pragma unroll
+          for (int q = 0; q < NEAR; ++q) {
+            const int cj = s_rc[ri * 3 + q];
+            if (cj != 0x7fffffff) {
+              const double* xj = xs + (size_t)(cj - k_lo) * T;
+#pragma unroll
+              for (int qq = 0; qq < XC; ++qq) { const int col = g + qq * NG2; if (col < T) a += ureg[q][qq] * xj[col]; }
+            }
+          }
+          part2[g * T + r] = a;
+        }
+        const double zi = zreg;
+        double xnext[XC];
+        if (i > k_lo) load_row(i - 1, ureg, xnext, zreg);
+        if (tid == 0 && n_all > n_in) { while (ld_acquire(row_count + i) < n_all - n_in) __nanosleep(40); __threadfence(); }
+        __syncthreads();
+        if (tid < T) {
+          double s = zi;
+          for (int e = n_in; e < n_all; ++e) s -= ldcg(c.pvec + (size_t)(base + 1 + e) * T + tid);
+#pragma unroll
+          for (int gg = 0; gg < NG2; ++gg) s -= part2[gg * T + tid];
+          part[tid] = s;
+        }
+        __syncthreads();
+        if (on) {
+          double b = 0.0;
+#pragma unroll
+          for (int qq = 0; qq < XC; ++qq) { const int col = g + qq * NG2; if (col < T) b += xreg[qq] * part[col]; }
+          part3[g * T + r] = b;
+        }
+        if (i > k_lo) {
+#pragma unroll
+          for (int qq = 0; qq < XC; ++qq) xreg[qq] = xnext[qq];
+        }
+        __syncthreads();
+        if (tid < T) {
+          double s = 0.0;
+#pragma unroll
+          for (int gg = 0; gg < NG2; ++gg) s += part3[gg * T + tid];
+          c.rhs[(size_t)i * T + tid] = s;
+          xs[(size_t)ri * T + tid] = s;
+        }
+        __syncthreads();
+        if (tid == 0) { __threadfence(); st_release(x_flag + i, 1); }
+      }
+      CHOL_STAMP(3);
     } else {
       // ---- backward substitution -----------------------------------------------------------
       const int g = tid / T, r = tid - g * T;
@@ -401,8 +595,9 @@ __global__ void __launch_bounds__(CholCfg<T>::NT, 1) k_chol_dataflow(CholDev c) 
 }
 
 // ---- host: task list in a topological order (claimed in this order by the CTAs) ---------------
-void chol_build_plan(int nT, const std::vector<int>& row_ptr, const std::vector<int>& row_col,
+void chol_build_plan(int T, int nT, const std::vector<int>& row_ptr, const std::vector<int>& row_col,
                      std::vector<CholTask>& tasks, std::vector<CholTerm>& terms) {
+  const int near = chol_chain_near(T);
   tasks.clear(); terms.clear();
   std::vector<std::vector<int>> col_rows(nT);      // rows k < c that hold tile (k, c), ascending
   for (int k = 0; k < nT; ++k)
@@ -424,41 +619,73 @@ void chol_build_plan(int nT, const std::vector<int>& row_ptr, const std::vector<
   std::vector<int> level(nT, 0), rows(nT);
   for (int i = 0; i < nT; ++i) { for (int k : col_rows[i]) level[i] = std::max(level[i], level[k] + 1); rows[i] = i; }
   std::stable_sort(rows.begin(), rows.end(), [&](int a, int b) { return level[a] < level[b]; });
-  for (int ri = 0; ri < nT; ++ri) {
-    const int i = rows[ri];
-    int lb = (int)terms.size();
-    // terms in the order their tiles become ready (wavefront level of the producing row, then row): the kernel
-    // accumulates the ready prefix while it waits for the rest
-    auto by_level = [&](const CholTerm& a, const CholTerm& b) { return level[a.k] != level[b.k] ? level[a.k] < level[b.k] : a.k < b.k; };
-    for (int k : col_rows[i]) { CholTerm tm; tm.sa = slot(k, i); tm.sb = tm.sa; tm.k = k; terms.push_back(tm); }
-    std::sort(terms.begin() + lb, terms.end(), by_level);
-    add(kTaskDiag, i, i, slot(i, i), lb, (int)terms.size());
-    for (int e = row_ptr[i]; e < row_ptr[i + 1]; ++e) {
-      const int j = row_col[e];
-      lb = (int)terms.size();
-      const std::vector<int>&ci = col_rows[i], &cj = col_rows[j];
-      size_t a = 0, b = 0;
-      while (a < ci.size() && b < cj.size()) {
-        if (ci[a] == cj[b]) {
-          if (ci[a] < i) { CholTerm tm; tm.sa = slot(ci[a], i); tm.sb = slot(ci[a], j); tm.k = ci[a]; terms.push_back(tm); }
-          ++a; ++b;
-        } else if (ci[a] < cj[b]) ++a; else ++b;
-      }
+  // Inside a wavefront the diagonal tasks come first: an off-diagonal task claimed together with its diagonal task holds a
+  // CTA idle for the whole elimination (~11 us), which halves the throughput of wide wavefronts (hundreds of leaves).
+  auto by_level = [&](const CholTerm& a, const CholTerm& b) { return level[a.k] != level[b.k] ? level[a.k] < level[b.k] : a.k < b.k; };
+  for (int r0 = 0; r0 < nT;) {
+    int r1 = r0;
+    while (r1 < nT && level[rows[r1]] == level[rows[r0]]) ++r1;
+    for (int ri = r0; ri < r1; ++ri) {
+      const int i = rows[ri];
+      const int lb = (int)terms.size();
+      // terms in the order their tiles become ready (wavefront level of the producing row, then row): the kernel
+      // accumulates the ready prefix while it waits for the rest
+      for (int k : col_rows[i]) { CholTerm tm; tm.sa = slot(k, i); tm.sb = tm.sa; tm.k = k; terms.push_back(tm); }
       std::sort(terms.begin() + lb, terms.end(), by_level);
-      add(kTaskOff, i, j, slot(i, j), lb, (int)terms.size());
+      add(kTaskDiag, i, i, slot(i, i), lb, (int)terms.size());
     }
+    for (int ri = r0; ri < r1; ++ri) {
+      const int i = rows[ri];
+      for (int e = row_ptr[i]; e < row_ptr[i + 1]; ++e) {
+        const int j = row_col[e];
+        const int lb = (int)terms.size();
+        const std::vector<int>&ci = col_rows[i], &cj = col_rows[j];
+        size_t a = 0, b = 0;
+        while (a < ci.size() && b < cj.size()) {
+          if (ci[a] == cj[b]) {
+            if (ci[a] < i) { CholTerm tm; tm.sa = slot(ci[a], i); tm.sb = slot(ci[a], j); tm.k = ci[a]; terms.push_back(tm); }
+            ++a; ++b;
+          } else if (ci[a] < cj[b]) ++a; else ++b;
+        }
+        std::sort(terms.begin() + lb, terms.end(), by_level);
+        add(kTaskOff, i, j, slot(i, j), lb, (int)terms.size());
+      }
+    }
+    r0 = r1;
   }
-  std::vector<int> level2(nT, 0);
-  for (int k = nT - 1; k >= 0; --k) {
-    for (int e = row_ptr[k]; e < row_ptr[k + 1]; ++e) level2[k] = std::max(level2[k], level2[row_col[e]] + 1);
-    rows[nT - 1 - k] = k;
+  // ---- backward substitution: chains of dependent rows (see the header) ----------------------------------------------------
+  // chain = maximal run k_lo .. k_hi (at most kMaxChain rows) in which every row holds the tile (i, i + 1)
+  std::vector<int> chain_of(nT, -1), chain_lo, chain_hi;
+  for (int k = nT - 1; k >= 0;) {
+    int lo = k;
+    while (lo - 1 >= 0 && k - (lo - 1) < kMaxChain && row_ptr[lo - 1] < row_ptr[lo] && row_col[row_ptr[lo - 1]] == lo) --lo;
+    const int id = (int)chain_lo.size();
+    chain_lo.push_back(lo); chain_hi.push_back(k);
+    for (int i = lo; i <= k; ++i) chain_of[i] = id;
+    k = lo - 1;
   }
-  std::stable_sort(rows.begin(), rows.end(), [&](int a, int b) { return level2[a] < level2[b]; });
-  for (int ri = 0; ri < nT; ++ri) {
-    const int k = rows[ri];
-    const int m = row_ptr[k + 1] - row_ptr[k];
-    for (int e = row_ptr[k]; e < row_ptr[k + 1]; ++e) add(kTaskBackTile, k, row_col[e], slot(k, row_col[e]), 0, 0);
-    add(kTaskBackRow, k, k, slot(k, k), m, 0);
+  // wavefront level of a chain = longest dependency chain of chains above it (columns outside the chain)
+  const int n_chains = (int)chain_lo.size();
+  std::vector<int> clevel(n_chains, 0), order(n_chains);
+  for (int cid = 0; cid < n_chains; ++cid) {       // chains were created from the last row down: their outside columns belong to earlier ids
+    for (int i = chain_lo[cid]; i <= chain_hi[cid]; ++i)
+      for (int e = row_ptr[i]; e < row_ptr[i + 1]; ++e)
+        if (row_col[e] > chain_hi[cid]) clevel[cid] = std::max(clevel[cid], clevel[chain_of[row_col[e]]] + 1);
+    order[cid] = cid;
+  }
+  std::stable_sort(order.begin(), order.end(), [&](int a, int b) { return clevel[a] < clevel[b]; });
+  for (int oi = 0; oi < n_chains; ++oi) {
+    const int cid = order[oi], lo = chain_lo[cid], hi = chain_hi[cid];
+    // tiles outside the chain first (their x belong to chains listed earlier), then the chain, then the chain's own tiles
+    // beyond the near columns: those wait for x the chain publishes as it descends, so they are listed top row first and
+    // behind the chain task — every task before them is then either done or held by a CTA that does not wait for them
+    for (int i = hi; i >= lo; --i)
+      for (int e = row_ptr[i]; e < row_ptr[i + 1]; ++e)
+        if (row_col[e] > hi) add(kTaskBackTile, i, row_col[e], slot(i, row_col[e]), 0, 0);
+    add(kTaskBackChain, hi, lo, slot(hi, hi), 0, 0);
+    for (int i = hi; i >= lo; --i)
+      for (int e = row_ptr[i]; e < row_ptr[i + 1]; ++e)
+        if (row_col[e] <= hi && row_col[e] > i + near) add(kTaskBackTile, i, row_col[e], slot(i, row_col[e]), 0, 0);
   }
 }
 
@@ -480,14 +707,14 @@ static int chol_run(CholDev& c, int sms, cudaStream_t st) {
 }
 
 int launch_cholesky_solve(int T, double* tiles, double* uinv, double* work /* 3*nT*T + 2*n_tiles*T */, double* rhs,
-                          const CholTask* tasks, const CholTerm* terms, int n_tasks, int* sync_ints, int n_tiles, int nT, int sms,
-                          cudaStream_t st, unsigned long long* trace) {
+                          const CholTask* tasks, const CholTerm* terms, const int* row_ptr, const int* row_col, int n_tasks, int* sync_ints,
+                          int n_tiles, int nT, int sms, cudaStream_t st, unsigned long long* trace) {
   CholDev c;
   c.trace = trace;
   const size_t v = (size_t)nT * T;
   c.tiles = tiles; c.uinv = uinv; c.z = work; c.sgn = work + v; c.y = work + 2 * v;
   c.cvec = work + 3 * v; c.pvec = c.cvec + (size_t)n_tiles * T; c.rhs = rhs;
-  c.tasks = tasks; c.terms = terms; c.sync = sync_ints; c.n_tasks = n_tasks; c.n_tiles = n_tiles; c.nT = nT;
+  c.tasks = tasks; c.terms = terms; c.row_ptr = row_ptr; c.row_col = row_col; c.sync = sync_ints; c.n_tasks = n_tasks; c.n_tiles = n_tiles; c.nT = nT;
   cudaMemsetAsync(sync_ints, 0, sizeof(int) * chol_sync_ints(n_tiles, nT), st);
   if (T == 48) return chol_run<48>(c, sms, st);
   if (T == 72) return chol_run<72>(c, sms, st);

@@ -134,12 +134,13 @@ void launch_select_final(const unsigned long long* all, const unsigned int* all_
 // reduced solve (chol.cu): tile tasks of the persistent dataflow kernel, built on the host from the tile pattern
 struct CholTask { int kind, i, j, slot, lb, le, pad0, pad1; };
 struct CholTerm { int sa, sb, k; };   // slots of U_ki, U_kj and the row k of one left-looking update term
-void chol_build_plan(int nT, const std::vector<int>& row_ptr, const std::vector<int>& row_col,
+void chol_build_plan(int T, int nT, const std::vector<int>& row_ptr, const std::vector<int>& row_col,
                      std::vector<CholTask>& tasks, std::vector<CholTerm>& terms);
 size_t chol_sync_ints(int n_tiles, int nT);
 // sync_ints[1] holds the first failing pivot + 1 (0 = ok) after the solve; returns a cudaError_t
 int launch_cholesky_solve(int T, double* tiles, double* uinv, double* work /* 3*nT*T + 2*n_tiles*T */, double* rhs,
-                          const CholTask* tasks, const CholTerm* terms, int n_tasks, int* sync_ints, int n_tiles, int nT, int sms,
+                          const CholTask* tasks, const CholTerm* terms, const int* row_ptr, const int* row_col, int n_tasks, int* sync_ints,
+                          int n_tiles, int nT, int sms,
                           cudaStream_t st, unsigned long long* trace = nullptr);
 
 // unary / binary / inertial residuals (other_kernels.cu)

@@ -7,9 +7,9 @@ tasks = np.frombuffer(raw[4:4 + 32 * n], np.int32).reshape(n, 8)
 st = np.frombuffer(raw[4 + 32 * n:], np.uint64).reshape(n, 4).astype(np.float64)
 t0 = st[:, 0].min()
 st = (st - t0) / 1e3   # us
-names = ["diag", "off", "backtile", "backrow"]
+names = ["diag", "off", "backtile", "backrow", "backchain"]
 print("tasks", n, "span %.1f us" % (st[:, 3].max()))
-for k in range(4):
+for k in range(5):
     m = tasks[:, 0] == k
     if not m.any():
         continue
@@ -19,8 +19,10 @@ for k in range(4):
 dg = st[tasks[:, 0] == 0]
 print("phase 1 end %.1f us; diag-to-diag publish interval mean %.2f us" % (dg[:, 3].max(), np.diff(dg[:, 3]).mean()))
 print("diag: ready->computed (factor) median %.2f ; claim->ready median %.2f" % (np.median(dg[:, 2] - dg[:, 1]), np.median(dg[:, 1] - dg[:, 0])))
-br = st[tasks[:, 0] == 3]
-print("phase 2: %.1f us; row-to-row interval mean %.2f us" % (br[:, 3].max() - br[:, 0].min(), np.abs(np.diff(br[:, 3])).mean()))
+br = st[tasks[:, 0] >= 2]
+ch = tasks[tasks[:, 0] == 4]
+print("phase 2: %.1f us from the first claim, %.1f us after phase 1; %d chains, longest %d rows" % (
+    br[:, 3].max() - br[:, 0].min(), br[:, 3].max() - dg[:, 3].max(), len(ch), (ch[:, 1] - ch[:, 2] + 1).max() if len(ch) else 0))
 # a few consecutive rows in detail
 off = tasks[:, 0] == 1
 for k in range(100, 103):
