@@ -66,6 +66,7 @@ struct DeviceProblem {
   double* Tsw;   // [P * n_cams * 12]
   double* Tws;   // [P * n_cams * 12]
   double* Rwp;   // [P * 9]
+  double* kd_pack;   // [P * 12] per-pose operands of K_pose delta for the current delta (k_pose_delta_pack)
   // landmarks
   double* lm_x;             // 4 per lm: x_s (L=1) or x_w (L=3)
   const uint32_t* lm_ref_pose;

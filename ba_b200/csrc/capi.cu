@@ -283,7 +283,7 @@ struct bagpu_handle_s {
 
   // ---- device buffers ----
   DevBuf<double> d_cam_params, d_cam_Rvs, d_cam_tvs;
-  DevBuf<double> d_pose_q, d_pose_t, d_pose_v, d_pose_b, d_Tsw, d_Tws, d_Rwp;
+  DevBuf<double> d_pose_q, d_pose_t, d_pose_v, d_pose_b, d_Tsw, d_Tws, d_Rwp, d_kd_pack;
   DevBuf<double> d_bk_q, d_bk_t, d_bk_v, d_bk_b, d_bk_lm_x; DevBuf<uint8_t> d_bk_rel; DevBuf<uint32_t> d_bk_outliers;
   DevBuf<int> d_pose_opt, d_lm_opt; DevBuf<uint32_t> d_pose_free; DevBuf<uint8_t> d_pose_mask_used;
   DevBuf<double> d_lm_x, d_lm_xw; DevBuf<uint32_t> d_lm_ref_pose, d_lm_ref_cam, d_lm_outliers, d_lm_obs_start;
@@ -659,7 +659,7 @@ struct bagpu_handle_s {
     d_pose_q.upload(q, st); d_pose_t.upload(t, st); d_pose_v.upload(pose_v, st); d_pose_b.upload(pose_b, st);
     d_bk_q.alloc(q.size()); d_bk_t.alloc(t.size()); d_bk_v.alloc(pose_v.size()); d_bk_b.alloc(pose_b.size());
     d_pose_opt.upload(pose_opt, st); d_pose_free.alloc(n_poses); d_pose_mask_used.alloc(n_poses);
-    d_Tsw.alloc((size_t)n_poses * n_cams * 12); d_Tws.alloc((size_t)n_poses * n_cams * 12); d_Rwp.alloc((size_t)n_poses * 9);
+    d_Tsw.alloc((size_t)n_poses * n_cams * 12); d_Tws.alloc((size_t)n_poses * n_cams * 12); d_Rwp.alloc((size_t)n_poses * 9); d_kd_pack.alloc((size_t)n_poses * 12);
     // landmarks
     if (lm_host_fresh) d_lm_xw.upload(lm_xw, st);
     d_lm_x.alloc(4 * n_lm_set); d_bk_lm_x.alloc(4 * n_lm_set);
@@ -724,7 +724,7 @@ struct bagpu_handle_s {
     P.n_unary = (int)un_pose.size(); P.n_binary = (int)bin_p1.size(); P.n_imu = (int)imu_p1.size();
     P.cam_params = d_cam_params.p; P.cam_Rvs = d_cam_Rvs.p; P.cam_tvs = d_cam_tvs.p;
     P.pose_q = d_pose_q.p; P.pose_t = d_pose_t.p; P.pose_v = d_pose_v.p; P.pose_b = d_pose_b.p; P.pose_opt = d_pose_opt.p; P.pose_free = d_pose_free.p;
-    P.Tsw = d_Tsw.p; P.Tws = d_Tws.p; P.Rwp = d_Rwp.p;
+    P.Tsw = d_Tsw.p; P.Tws = d_Tws.p; P.Rwp = d_Rwp.p; P.kd_pack = d_kd_pack.p;
     P.lm_x = d_lm_x.p; P.lm_ref_pose = d_lm_ref_pose.p; P.lm_ref_cam = d_lm_ref_cam.p; P.lm_opt = d_lm_opt.p; P.lm_reliable = d_lm_reliable.p;
     P.lm_outliers = d_lm_outliers.p; P.lm_obs_start = d_lm_obs_start.p;
     P.obs_z = d_obs_z.p; P.obs_pose = d_obs_pose.p; P.obs_cam = multi_cam ? d_obs_cam.p : nullptr; P.obs_w0 = d_obs_w0.p; P.obs_perm = d_perm_global.p ? d_perm_global.p + s_lo : nullptr;
@@ -1153,7 +1153,7 @@ struct bagpu_handle_s {
       chol_flag_pending = true;
     }
     summary.result = BAGPU_Success;
-    if (n_al > 0) { launch_back_substitute(P, d_tasks.p, n_tasks, d_long_lms.p, n_long, d_gn_p.p, d_gn_l.p, st); launches += (n_tasks > 0) + (n_long > 0); }
+    if (n_al > 0) { launch_back_substitute(P, d_tasks.p, n_tasks, d_long_lms.p, n_long, d_gn_p.p, d_gn_l.p, st); launches += 1 + (n_tasks > 0) + (n_long > 0); }
     CU(cudaEventRecord(ev[9], st));
     // ONE host round trip for the whole Gauss-Newton step: the factorisation's failure flag and the two norms of the step come
     // back together (on a failed factorisation the back-substitution and the norms ran on garbage and are thrown away)
@@ -1181,7 +1181,7 @@ struct bagpu_handle_s {
     if (L > 0 && n_al > 0) { launch_compact_bl(P, d_bl_compact.p, st); ++launches; }
     dot_pair(d_bp.p, d_bp.p, np, d_bl_compact.p, d_bl_compact.p, (L > 0) ? nl : 0, nullptr, nullptr, false);
     CU(cudaMemsetAsync(&d_sc.p->sd_den_proj, 0, 2 * sizeof(double), st));
-    if (n_ap > 0 || n_al > 0) { launch_sd_denominator(P, G, st); if (n_obs) ++launches; }
+    if (n_ap > 0 || n_al > 0) { launch_sd_denominator(P, G, st); if (n_obs) launches += 2; }
     if (n_ap > 0 && rank == 0) launch_other_sd(P, R, st, &launches);
     if (world > 1) allreduce_f64(&d_sc.p->sd_den_proj, 2);
     CU(cudaEventRecord(ev[13], st));

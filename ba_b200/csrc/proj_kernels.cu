@@ -86,30 +86,52 @@ __global__ void __launch_bounds__(256) k_residual(DeviceProblem P) {
 // Every projection Jacobian is B times something (ba_gpu.h), so J_p b_p + J_l b_l = B v with
 //   v = K_meas b_meas - K_ref b_ref - (b_l  or  u b_l)     and     w |B v|^2 = v^T G v
 // from the G record of the last build: no camera model here.
+// per-pose operands of K_pose delta (proj_kernels.cuh, k_times_pack) for the vector `delta` over the optimised poses
+__global__ void k_pose_delta_pack(DeviceProblem P, const double* __restrict__ delta, double* __restrict__ out) {
+  const int p = blockIdx.x * blockDim.x + threadIdx.x;
+  if (p >= P.n_poses) return;
+  const int o = P.pose_opt[p];
+  double x[6] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0}, xw[3] = {0.0, 0.0, 0.0};
+  if (o >= 0) {
+    const uint32_t fr = P.pose_free[p];
+#pragma unroll
+    for (int a = 0; a < 6; ++a) x[a] = ((fr >> a) & 1u) ? delta[(size_t)o * P.D + a] : 0.0;
+    mat3_vec(P.Rwp + 9 * (size_t)p, x + 3, xw);
+  } else {
+    x[0] = __longlong_as_double(0x7ff8000000000000LL);
+  }
+  const double* tp = P.pose_t + 3 * (size_t)p;
+  const double* tw = P.Tws + (size_t)p * P.n_cams * 12 + 9;
+  double* q = out + (size_t)p * kPosePack;
+  q[0] = x[0]; q[1] = x[1]; q[2] = x[2]; q[3] = xw[0]; q[4] = xw[1]; q[5] = xw[2];
+  q[6] = tp[0]; q[7] = tp[1]; q[8] = tp[2]; q[9] = tw[0]; q[10] = tw[1]; q[11] = tw[2];
+}
+
 template <int L>
 __global__ void __launch_bounds__(128) k_sd_denominator(DeviceProblem P) {
   double acc[1] = {0.0};
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < P.n_obs; i += gridDim.x * blockDim.x) {
     const int lm = (int)P.obs_lm[i];
-    LmCtx<L> c;
-    load_lm<L>(P, lm, c);
+    LmRecCtx c;
+    load_lm_rec<L>(P, lm, c);
     const int m = (int)P.obs_pose[i];
     const bool diff = (m != c.ref_pose);
-    const int mo = P.pose_opt[m];
-    double v[3] = {0.0, 0.0, 0.0};
-    if (diff && mo >= 0) k_times_delta(P, m, c.X, c.rho, P.b_p + (size_t)mo * P.D, v);
-    if (L == 1 && diff && c.ref_opt >= 0) {
-      double y[3];
-      k_times_delta(P, c.ref_pose, c.X, c.rho, P.b_p + (size_t)c.ref_opt * P.D, y);
-      v[0] -= y[0]; v[1] -= y[1]; v[2] -= y[2];
+    double v[3], tw[3];
+    k_times_pack(P.kd_pack + (size_t)m * kPosePack, c.X, c.rho, v, tw);
+    if (!diff) { v[0] = 0.0; v[1] = 0.0; v[2] = 0.0; }
+    if (L == 1 && diff) {
+      double y[3], tr[3];
+      if (k_times_pack(P.kd_pack + (size_t)c.ref_pose * kPosePack, c.X, c.rho, y, tr)) { v[0] -= y[0]; v[1] -= y[1]; v[2] -= y[2]; }
     }
-    if (c.lm_opt >= 0) {
+    if (P.lm_opt[lm] >= 0) {
       if (L == 3) {
 #pragma unroll
         for (int k = 0; k < 3; ++k) v[k] -= P.lm_bl[(size_t)lm * 3 + k];
       } else {
-        const int cam = P.obs_cam ? (int)P.obs_cam[i] : 0;
-        const double* tw = P.Tws + ((size_t)m * P.n_cams + cam) * 12 + 9;
+        if (P.n_cams > 1 && P.obs_cam) {
+          const double* t2 = P.Tws + ((size_t)m * P.n_cams + (int)P.obs_cam[i]) * 12 + 9;
+          tw[0] = t2[0]; tw[1] = t2[1]; tw[2] = t2[2];
+        }
         const double bl = P.lm_bl[lm];
 #pragma unroll
         for (int k = 0; k < 3; ++k) v[k] -= (c.tws_r[k] - tw[k]) * bl;
@@ -161,37 +183,34 @@ __global__ void __launch_bounds__(128) k_jacobian_rows(DeviceProblem P, double* 
 // V^-1 and dhat come from the landmark's record.
 // share of one observation: w J_l^T J_m delta_p(a)
 template <int L>
-BA_D void back_term(const DeviceProblem& P, const LmCtx<L>& c, int i, int m_known, const double* delta_p, double* acc) {
-  // W_a^T delta = w J_l^T J_m delta = -G (K_m delta)   (LmSize 1: -u^T G K_m delta), from the G record of the last build
-  const int m = m_known >= 0 ? m_known : (int)P.obs_pose[i];
+BA_D void back_term(const DeviceProblem& P, const LmRecCtx& c, int i, double* acc) {
+  // W_a^T delta = w J_l^T J_m delta = -G (K_m delta)   (LmSize 1: -u^T G K_m delta), from the G record of the last build and
+  // the pose's pack for delta_p (launch_back_substitute)
+  const int m = (int)P.obs_pose[i];
   if (m == c.ref_pose) return;
-  const int mo = P.pose_opt[m];
-  if (mo < 0) return;
-  double y[3], G[6], gy[3];
-  k_times_delta(P, m, c.X, c.rho, delta_p + (size_t)mo * P.D, y);
+  double y[3], tw[3], G[6], gy[3];
+  if (!k_times_pack(P.kd_pack + (size_t)m * kPosePack, c.X, c.rho, y, tw)) return;
   load_G(P, i, G);
   sym3_vec(G, y, gy);
   if (L == 3) {
 #pragma unroll
     for (int k = 0; k < 3; ++k) acc[k] -= gy[k];
   } else {
-    const int cam = P.obs_cam ? (int)P.obs_cam[i] : 0;
-    const double* tw = P.Tws + ((size_t)m * P.n_cams + cam) * 12 + 9;
+    if (P.n_cams > 1 && P.obs_cam) {
+      const double* t2 = P.Tws + ((size_t)m * P.n_cams + (int)P.obs_cam[i]) * 12 + 9;
+      tw[0] = t2[0]; tw[1] = t2[1]; tw[2] = t2[2];
+    }
     acc[0] -= (c.tws_r[0] - tw[0]) * gy[0] + (c.tws_r[1] - tw[1]) * gy[1] + (c.tws_r[2] - tw[2]) * gy[2];
   }
 }
 // landmark part and write-out, by one lane holding the landmark's sum
 template <int L>
-BA_D void back_finish(const DeviceProblem& P, int lm, int lo, const double* delta_p, double* acc, double* delta_l) {
+BA_D void back_finish(const DeviceProblem& P, int lm, int lo, double* acc, double* delta_l) {
   const double* r = P.lm_rec + (size_t)lm * kLmRec;
   if (L == 1) {
     const int rp = (int)P.lm_ref_pose[lm];
-    const int ro = P.pose_opt[rp];
-    if (ro >= 0) {   // W_ref^T delta = gbar^T K_ref delta
-      double k[3];
-      k_times_delta(P, rp, r, r[3], delta_p + (size_t)ro * P.D, k);
-      acc[0] += r[9] * k[0] + r[10] * k[1] + r[11] * k[2];
-    }
+    double k[3], tw[3];     // W_ref^T delta = gbar^T K_ref delta
+    if (k_times_pack(P.kd_pack + (size_t)rp * kPosePack, r, r[3], k, tw)) acc[0] += r[9] * k[0] + r[10] * k[1] + r[11] * k[2];
     delta_l[lo] = r[8] - r[7] * acc[0];
   } else {
     const double v00 = r[4], v01 = r[5], v02 = r[6], v11 = r[7], v12 = r[8], v22 = r[9];
@@ -203,8 +222,7 @@ BA_D void back_finish(const DeviceProblem& P, int lm, int lo, const double* delt
 
 // packed tasks (see k_linearize_packed): one observation per lane, segmented sum over the lanes of a landmark
 template <int L>
-__global__ void __launch_bounds__(256) k_back_substitute_packed(DeviceProblem P, const uint2* __restrict__ tasks, int n_tasks,
-                                                                const double* delta_p, double* delta_l) {
+__global__ void __launch_bounds__(256) k_back_substitute_packed(DeviceProblem P, const uint2* __restrict__ tasks, int n_tasks, double* delta_l) {
   const int lane = threadIdx.x & 31;
   const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, n_warps = (gridDim.x * blockDim.x) >> 5;
   for (int t = warp; t < n_tasks; t += n_warps) {
@@ -223,9 +241,9 @@ __global__ void __launch_bounds__(256) k_back_substitute_packed(DeviceProblem P,
 #pragma unroll
     for (int k = 0; k < L; ++k) acc[k] = 0.0;
     if (on && lo >= 0) {
-      LmCtx<L> c;
-      load_lm<L>(P, lm, c);
-      back_term<L>(P, c, i, -1, delta_p, acc);
+      LmRecCtx c;
+      load_lm_rec<L>(P, lm, c);
+      back_term<L>(P, c, i, acc);
     }
 #pragma unroll
     for (int d = 1; d < 32; d <<= 1) {
@@ -236,14 +254,13 @@ __global__ void __launch_bounds__(256) k_back_substitute_packed(DeviceProblem P,
         if (take) acc[k] += other;
       }
     }
-    if (head && lo >= 0) back_finish<L>(P, lm, lo, delta_p, acc, delta_l);
+    if (head && lo >= 0) back_finish<L>(P, lm, lo, acc, delta_l);
   }
 }
 
 // landmarks with more than 32 observations: one warp per landmark
 template <int L>
-__global__ void __launch_bounds__(256) k_back_substitute_long(DeviceProblem P, const uint32_t* __restrict__ lm_list, int n_list,
-                                                              const double* delta_p, double* delta_l) {
+__global__ void __launch_bounds__(256) k_back_substitute_long(DeviceProblem P, const uint32_t* __restrict__ lm_list, int n_list, double* delta_l) {
   const int lane = threadIdx.x & 31;
   const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, n_warps = (gridDim.x * blockDim.x) >> 5;
   for (int q = warp; q < n_list; q += n_warps) {
@@ -254,12 +271,12 @@ __global__ void __launch_bounds__(256) k_back_substitute_long(DeviceProblem P, c
     double acc[L];
 #pragma unroll
     for (int k = 0; k < L; ++k) acc[k] = 0.0;
-    LmCtx<L> c;
-    load_lm<L>(P, lm, c);
-    for (int i = s + lane; i < e; i += 32) back_term<L>(P, c, i, -1, delta_p, acc);
+    LmRecCtx c;
+    load_lm_rec<L>(P, lm, c);
+    for (int i = s + lane; i < e; i += 32) back_term<L>(P, c, i, acc);
 #pragma unroll
     for (int k = 0; k < L; ++k) acc[k] = warp_sum(acc[k]);
-    if (lane == 0) back_finish<L>(P, lm, lo, delta_p, acc, delta_l);
+    if (lane == 0) back_finish<L>(P, lm, lo, acc, delta_l);
   }
 }
 
@@ -429,21 +446,23 @@ void launch_jacobian_rows(const DeviceProblem& P, double* out, cudaStream_t st) 
 void launch_sd_denominator(const DeviceProblem& P, int G, cudaStream_t st) {
   if (P.n_obs == 0) return;
   (void)G;
+  k_pose_delta_pack<<<(P.n_poses + 127) / 128, 128, 0, st>>>(P, P.b_p, P.kd_pack);
   const int grid = grid_for((size_t)P.n_obs, 128, 12);
   if (P.L == 1) k_sd_denominator<1><<<grid, 128, 0, st>>>(P); else k_sd_denominator<3><<<grid, 128, 0, st>>>(P);
 }
 void launch_back_substitute(const DeviceProblem& P, const uint2* tasks, int n_tasks, const uint32_t* long_lms, int n_long, const double* delta_p,
                             double* delta_l, cudaStream_t st) {
   if (P.n_active_lms == 0) return;
+  k_pose_delta_pack<<<(P.n_poses + 127) / 128, 128, 0, st>>>(P, delta_p, P.kd_pack);
   if (n_tasks > 0) {
     const int grid = grid_for((size_t)n_tasks * 32, 256, 8);
-    if (P.L == 1) k_back_substitute_packed<1><<<grid, 256, 0, st>>>(P, tasks, n_tasks, delta_p, delta_l);
-    else k_back_substitute_packed<3><<<grid, 256, 0, st>>>(P, tasks, n_tasks, delta_p, delta_l);
+    if (P.L == 1) k_back_substitute_packed<1><<<grid, 256, 0, st>>>(P, tasks, n_tasks, delta_l);
+    else k_back_substitute_packed<3><<<grid, 256, 0, st>>>(P, tasks, n_tasks, delta_l);
   }
   if (n_long > 0) {
     const int grid = grid_for((size_t)n_long * 32, 256, 8);
-    if (P.L == 1) k_back_substitute_long<1><<<grid, 256, 0, st>>>(P, long_lms, n_long, delta_p, delta_l);
-    else k_back_substitute_long<3><<<grid, 256, 0, st>>>(P, long_lms, n_long, delta_p, delta_l);
+    if (P.L == 1) k_back_substitute_long<1><<<grid, 256, 0, st>>>(P, long_lms, n_long, delta_l);
+    else k_back_substitute_long<3><<<grid, 256, 0, st>>>(P, long_lms, n_long, delta_l);
   }
 }
 // count_outliers: EvaluateResiduals resets and recounts num_outlier_residuals (cpp:148-186); the read-out passes after

@@ -24,6 +24,16 @@
 
 namespace bagpu {
 
+// 256-bit read-only load (32-byte aligned).  The gathers of per-pose data are scattered over the lanes of a warp, and L1
+// looks up one cache line per cycle whatever the access width: the fewer, wider instructions a gather takes, the better.
+BA_D void ld4(const double* p, double& a, double& b, double& c, double& d) {
+  asm volatile("ld.global.nc.v4.f64 {%0,%1,%2,%3}, [%4];" : "=d"(a), "=d"(b), "=d"(c), "=d"(d) : "l"(p));
+}
+// a pose frame [R (9, row-major) | t (3)] in three 32-byte loads (frames are 96 bytes apart)
+BA_D void load_frame(const double* __restrict__ T, double* f) {
+  ld4(T, f[0], f[1], f[2], f[3]); ld4(T + 4, f[4], f[5], f[6], f[7]); ld4(T + 8, f[8], f[9], f[10], f[11]);
+}
+
 template <int L>
 struct LmCtx {
   double X[3];      // world point (LmSize 3: x_w; LmSize 1: R_ws_r ray + rho t_ws_r)
@@ -42,7 +52,8 @@ BA_D void load_lm(const DeviceProblem& P, int lm, LmCtx<L>& c) {
   c.rho = x.w;
   if (L == 1) {
     const int rc = (int)P.lm_ref_cam[lm];
-    const double* Tws = P.Tws + ((size_t)c.ref_pose * P.n_cams + rc) * 12;
+    double Tws[12];
+    load_frame(P.Tws + ((size_t)c.ref_pose * P.n_cams + rc) * 12, Tws);
     const double ray[3] = {x.x, x.y, x.z};
     double Xw[3];
     mat3_vec(Tws, ray, Xw);
@@ -58,12 +69,6 @@ BA_D void load_lm(const DeviceProblem& P, int lm, LmCtx<L>& c) {
     c.X[0] = x.x; c.X[1] = x.y; c.X[2] = x.z;
     c.ref_opt = -1; c.ref_free = 0;
   }
-}
-
-// a pose frame [R (9, row-major) | t (3)] in six 16-byte loads (frames are 96 bytes apart)
-BA_D void load_frame(const double* __restrict__ T, double* f) {
-#pragma unroll
-  for (int k = 0; k < 6; ++k) { const double2 v = reinterpret_cast<const double2*>(T)[k]; f[2 * k] = v.x; f[2 * k + 1] = v.y; }
 }
 
 template <int L>
@@ -314,6 +319,31 @@ BA_D void k_times_delta(const DeviceProblem& P, int pose, const double* X, doubl
   y[0] = rho * x[0] - (Y[1] * xw[2] - Y[2] * xw[1]);
   y[1] = rho * x[1] - (Y[2] * xw[0] - Y[0] * xw[2]);
   y[2] = rho * x[2] - (Y[0] * xw[1] - Y[1] * xw[0]);
+}
+// The same product from the pose's PACK (k_pose_delta_pack: 12 doubles = three 32-byte loads per pose instead of ~20 scalar
+// gathers): [x_t (3) | x_w (3) | t_wp (3) | t_ws of camera 0 (3)], x_t[0] = NaN for a pose that is not optimised.
+// Same arithmetic in the same order as k_times_delta.  Returns false (y = 0) for a pose that is not optimised.
+constexpr int kPosePack = 12;
+BA_D bool k_times_pack(const double* __restrict__ pk, const double* X, double rho, double* y, double* tw) {
+  double x[12];
+  load_frame(pk, x);
+  tw[0] = x[9]; tw[1] = x[10]; tw[2] = x[11];
+  if (x[0] != x[0]) { y[0] = 0.0; y[1] = 0.0; y[2] = 0.0; return false; }
+  const double Y[3] = {X[0] - rho * x[6], X[1] - rho * x[7], X[2] - rho * x[8]};
+  y[0] = rho * x[0] - (Y[1] * x[5] - Y[2] * x[4]);
+  y[1] = rho * x[1] - (Y[2] * x[3] - Y[0] * x[5]);
+  y[2] = rho * x[2] - (Y[0] * x[4] - Y[1] * x[3]);
+  return true;
+}
+// what the kernels behind the build need of a landmark, from the record the linearisation wrote (state unchanged since)
+struct LmRecCtx { double X[3], rho, tws_r[3]; int ref_pose; };
+template <int L>
+BA_D void load_lm_rec(const DeviceProblem& P, int lm, LmRecCtx& c) {
+  const double* r = P.lm_rec + (size_t)lm * kLmRec;
+  ld4(r, c.X[0], c.X[1], c.X[2], c.rho);
+  if (L == 1) { double vi; ld4(r + 4, c.tws_r[0], c.tws_r[1], c.tws_r[2], vi); (void)vi; }
+  else { c.tws_r[0] = c.tws_r[1] = c.tws_r[2] = 0.0; }
+  c.ref_pose = (int)P.lm_ref_pose[lm];
 }
 // the G record of an observation (upper 00 01 02 11 12 22): three 16-byte loads
 BA_D void load_G(const DeviceProblem& P, int obs, double* G) {
