@@ -1493,6 +1493,9 @@ struct bagpu_handle_s {
 };
 
 // ============================================================================================
+// for the entry points that live in other translation units (select_static.cu)
+namespace bagpu { void set_last_error(const std::string& msg) { g_err = msg; } }
+
 extern "C" {
 
 #define GUARD(...)                                                                \

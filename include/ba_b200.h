@@ -259,6 +259,19 @@ int bagpu_pack_warp_tasks(uint32_t n_lms, const uint32_t* starts, uint32_t lm_lo
 int bagpu_symbolic_tile_fill(uint32_t nT, uint32_t n_edges, const uint32_t* edge_a, const uint32_t* edge_b,
                              uint32_t* perm, uint32_t* row_ptr, uint32_t* row_col, uint32_t cap);
 
+/* Allocation-free exact k-th order statistic (0-based; k = n / 2 is the value std::nth_element leaves at
+ * errors_.begin() + n / 2, i.e. what the build calls the median).  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that may not call cudaMalloc (CUDA graph capture, tight serving loops, harnesses
+ * that forbid it).  d_x: n non-negative finite doubles (sign bit clear) in DEVICE memory of the current device; d_out: one
+ * double in device memory; stream: a cudaStream_t (NULL = the default stream).  The call only queues kernels on `stream`
+ * (13 launches, no synchronisation, no host round trip): *d_out holds the value once that work has run.  The radix-select
+ * state lives in a 16640-byte static __device__ array inside the library (held by every GPU that loads it until exit),
+ * shared by all calls: it is cleared on `stream` at the start of every call, and calls that overlap on the GPU race.
+ * The first call on a device loads the module — make it before a graph capture begins.
+ * n > BAGPU_SELECT_STATIC_MAX_N (32-bit histogram bins), n == 0, k >= n or a null pointer: BAGPU_ERR_INVALID. */
+#define BAGPU_SELECT_STATIC_MAX_N (1ull << 31)
+int bagpu_select_kth_static(const double* d_x, uint64_t n, uint64_t k, double* d_out, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
