@@ -14,6 +14,8 @@
 //   D_p = blkdiag(I, R_wp) with the masked parameter columns zeroed.  So an observation enters EVERY block of the
 //   reduced system only through
 //     per observation  G = w B^T B (3 x 3 symmetric, 6 doubles in a 64-byte record, obs_G) and h = w B^T r (32-byte record, obs_h)
+//                      LmSize 1 also gv = [G u (3) | V^-1 of the landmark] (32-byte record, obs_gv): all an off-diagonal
+//                      block needs of an observation, since there  M_e = -V^-1 (G_a u_a)(G_b u_b)^T
 //     per landmark     LmRec (128 bytes): LmSize 3: X (3) | rho | V^-1 upper (6) | dhat = V^-1 b_l (3)
 //                                         LmSize 1: X (3) | rho | t_ws of the reference sensor (3) | V^-1 | dhat | gbar = sum G u (3)
 //                      LmSize 1 only, LmRecC (96 bytes): Gbar = sum G (6) | hbar = sum h (3), over the observations the
@@ -35,6 +37,7 @@ constexpr int kTilePoses = 8;   // poses per S tile
 constexpr uint32_t kNoSlot = 0xffffffffu;
 constexpr int kLmRec = 16, kLmRecC = 12;   // doubles per landmark record (128 B) / LmSize-1 extension (96 B)
 constexpr int kObsG = 8, kObsH = 4;         // doubles per observation record: G (6 + 2 pad, 64 B), h (3 + 1 pad, 32 B)
+constexpr int kObsGv = 4;                   // LmSize 1: G u (3) | V^-1 (32 B)
 
 struct Scalars {       // device-resident scalar block (one per handle)
   double median;       // nth_element value of maha0
@@ -86,6 +89,7 @@ struct DeviceProblem {
   double* obs_w;
   double* obs_G;             // kObsG doubles per observation: w B^T B upper (00 01 02 11 12 22)
   double* obs_h;             // kObsH doubles per observation: w B^T r
+  double* obs_gv;            // LmSize 1, kObsGv doubles per observation: G u | V^-1 of its landmark
   const uint32_t* pose_obs;  // observation indices grouped by optimised measurement pose (pose-major), n_pose_obs entries
   const uint32_t* pose_obs_lm;  // landmark of pose_obs[k]
   const uint32_t* pose_lms;  // L == 1: landmark ids grouped by optimised reference pose

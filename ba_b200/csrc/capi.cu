@@ -291,7 +291,7 @@ struct bagpu_handle_s {
   DevBuf<double2> d_raw_z; DevBuf<uint32_t> d_raw_pose, d_raw_lm, d_raw_cam; DevBuf<double> d_raw_w0;   // residual-id order, as set
   DevBuf<uint32_t> d_sorted_lm, d_perm_global, d_gstarts;   // landmark-major: landmark id, residual id, CSR starts (all ranks' observations)
   DevBuf<double2> d_obs_z; DevBuf<uint32_t> d_obs_pose, d_obs_cam; DevBuf<double> d_obs_w0, d_obs_maha0, d_obs_w;
-  DevBuf<uint32_t> d_pose_obs, d_pose_obs_lm, d_pose_lms; DevBuf<double> d_obs_G, d_obs_h; DevBuf<int> d_opt_to_pose;
+  DevBuf<uint32_t> d_pose_obs, d_pose_obs_lm, d_pose_lms; DevBuf<double> d_obs_G, d_obs_h, d_obs_gv; DevBuf<int> d_opt_to_pose;
   DevBuf<double> d_lm_rec, d_lm_recC, d_partial, d_red_partial; DevBuf<unsigned int> d_counters, d_red_counter;
   DevBuf<ReduceItem> d_items, d_items_sym;
   DevBuf<double> d_lm_bl;
@@ -464,7 +464,7 @@ struct bagpu_handle_s {
     }
     // 4. the local stream: gathered values, pose-major record slots
     const uint32_t nl = (uint32_t)n_obs;
-    d_obs_z.alloc(nl); d_obs_pose.alloc(nl); d_obs_w0.alloc(nl); d_obs_G.alloc((size_t)nl * kObsG); d_obs_h.alloc((size_t)nl * kObsH);
+    d_obs_z.alloc(nl); d_obs_pose.alloc(nl); d_obs_w0.alloc(nl); d_obs_G.alloc((size_t)nl * kObsG); d_obs_h.alloc((size_t)nl * kObsH); if (L == 1) d_obs_gv.alloc((size_t)nl * kObsGv);
     if (n_cams > 1) d_obs_cam.alloc(nl);
     launch_gather_obs(d_perm_global.p + s_lo, nl, d_raw_z.p, d_raw_pose.p, raw_has_cam ? d_raw_cam.p : nullptr, raw_has_w0 ? d_raw_w0.p : nullptr,
                       d_obs_z.p, d_obs_pose.p, n_cams > 1 ? d_obs_cam.p : nullptr, d_obs_w0.p, nullptr, st);
@@ -730,7 +730,7 @@ struct bagpu_handle_s {
     P.obs_z = d_obs_z.p; P.obs_pose = d_obs_pose.p; P.obs_cam = multi_cam ? d_obs_cam.p : nullptr; P.obs_w0 = d_obs_w0.p; P.obs_perm = d_perm_global.p ? d_perm_global.p + s_lo : nullptr;
     P.obs_lm = d_sorted_lm.p ? d_sorted_lm.p + s_lo : nullptr;
     P.obs_maha0 = d_obs_maha0.p; P.obs_w = d_obs_w.p;
-    P.obs_G = d_obs_G.p; P.obs_h = d_obs_h.p; P.pose_obs = d_pose_obs.p; P.pose_obs_lm = d_pose_obs_lm.p; P.pose_lms = d_pose_lms.p; P.opt_to_pose = d_opt_to_pose.p;
+    P.obs_G = d_obs_G.p; P.obs_h = d_obs_h.p; P.obs_gv = d_obs_gv.p; P.pose_obs = d_pose_obs.p; P.pose_obs_lm = d_pose_obs_lm.p; P.pose_lms = d_pose_lms.p; P.opt_to_pose = d_opt_to_pose.p;
     P.lm_rec = d_lm_rec.p; P.lm_recC = (L == 1) ? d_lm_recC.p : nullptr; P.lm_bl = d_lm_bl.p;
     P.red_partial = d_red_partial.p; P.red_counter = d_red_counter.p;
     P.cam_identity = 1;

@@ -108,7 +108,7 @@ BA_D void lm_invert(const LmSums<L>& S, bool lm_on, double* Vi, double* bl, doub
 
 // the landmark's record (ba_gpu.h), written by one lane: four 32-byte stores into one 128-byte line
 template <int L>
-BA_D void lm_write(const DeviceProblem& P, int lm, const LmCtx<L>& c, bool lm_on, const LmSums<L>& S) {
+BA_D double lm_write(const DeviceProblem& P, int lm, const LmCtx<L>& c, bool lm_on, const LmSums<L>& S) {
   constexpr int NV = LmSums<L>::NV;
   double Vi[NV], bl[L], dhat[L];
   lm_invert<L>(S, lm_on, Vi, bl, dhat);
@@ -126,12 +126,13 @@ BA_D void lm_write(const DeviceProblem& P, int lm, const LmCtx<L>& c, bool lm_on
   }
 #pragma unroll
   for (int i = 0; i < L; ++i) P.lm_bl[(size_t)lm * L + i] = bl[i];
+  return Vi[0];   // LmSize 1: V^-1, which the gv records of the landmark's observations carry as well
 }
 
 // one observation of pass A: linearise, write weight and records, add into the landmark's sums
 template <int L>
 BA_D void linearize_one(const DeviceProblem& P, const LmCtx<L>& c, int i, int m, bool lm_on, double c_huber, double c2, LmSums<L>& S,
-                        double& err) {
+                        double& err, double* gu) {
   ObsLin<L> o;
   obs_linearize<L>(P, c, i, m, c_huber, c2, o);
   P.obs_w[i] = o.w;
@@ -142,6 +143,7 @@ BA_D void linearize_one(const DeviceProblem& P, const LmCtx<L>& c, int i, int m,
   st4(g, o.G[0], o.G[1], o.G[2], o.G[3]); st4(g + 4, o.G[4], o.G[5], 0.0, 0.0);   // whole sectors
   if (o.pm_on) st4(P.obs_h + (size_t)i * kObsH, o.h[0], o.h[1], o.h[2], 0.0);
   sums_add<L>(S, o, lm_on);
+  if constexpr (L == 1) { gu[0] = o.gj[0]; gu[1] = o.gj[1]; gu[2] = o.gj[2]; }
 }
 
 // Landmarks with more than 32 observations (lm_list): one warp per landmark, lanes stride over the track.
@@ -160,10 +162,19 @@ __global__ void __launch_bounds__(128) k_linearize_long(DeviceProblem P, const u
     LmSums<L> S;
 #pragma unroll
     for (int i = 0; i < LmSums<L>::N; ++i) S.v[i] = 0.0;
-    for (int i = s + lane; i < e; i += 32) linearize_one<L>(P, c, i, (int)P.obs_pose[i], lm_on, c_huber, c2, S, err[0]);
+    for (int i = s + lane; i < e; i += 32) {
+      double gu[3];
+      linearize_one<L>(P, c, i, (int)P.obs_pose[i], lm_on, c_huber, c2, S, err[0], gu);
+      if constexpr (L == 1) st4(P.obs_gv + (size_t)i * kObsGv, gu[0], gu[1], gu[2], 0.0);   // V^-1 follows below
+    }
 #pragma unroll
     for (int i = 0; i < LmSums<L>::N; ++i) S.v[i] = warp_sum(S.v[i]);
-    if (lane == 0) lm_write<L>(P, lm, c, lm_on, S);
+    double vi = 0.0;
+    if (lane == 0) vi = lm_write<L>(P, lm, c, lm_on, S);
+    if constexpr (L == 1) {
+      vi = __shfl_sync(0xffffffffu, vi, 0);
+      for (int i = s + lane; i < e; i += 32) P.obs_gv[(size_t)i * kObsGv + 3] = vi;   // the lane that wrote the record
+    }
   }
   grid_sum_fixed<1>(err, P.red_partial, P.red_counter, &P.sc->proj_error, true);
 }
@@ -205,7 +216,8 @@ __global__ void __launch_bounds__(128) k_linearize_packed(DeviceProblem P, const
     LmSums<L> S;
 #pragma unroll
     for (int k = 0; k < LmSums<L>::N; ++k) S.v[k] = 0.0;
-    if (on) linearize_one<L>(P, c, i, m_pre, lm_on, c_huber, c2, S, err[0]);
+    double gu[3] = {0.0, 0.0, 0.0};
+    if (on) linearize_one<L>(P, c, i, m_pre, lm_on, c_huber, c2, S, err[0], gu);
     // segmented reduction to the head lane (a lane adds its neighbour at distance d only inside its own landmark)
 #pragma unroll
     for (int d = 1; d < 32; d <<= 1) {
@@ -216,7 +228,14 @@ __global__ void __launch_bounds__(128) k_linearize_packed(DeviceProblem P, const
         if (take) S.v[k] += other;
       }
     }
-    if (head) lm_write<L>(P, lm, c, lm_on, S);
+    double vi = 0.0;
+    if (head) vi = lm_write<L>(P, lm, c, lm_on, S);
+    if constexpr (L == 1) {
+      // V^-1 from the head lane of my landmark, then the observation's gv record
+      const int hl = 31 - __clz(heads & (0xffffffffu >> (31 - lane)));
+      vi = __shfl_sync(0xffffffffu, vi, on ? hl : 0);
+      if (on) st4(P.obs_gv + (size_t)i * kObsGv, gu[0], gu[1], gu[2], vi);
+    }
   }
   grid_sum_fixed<1>(err, P.red_partial, P.red_counter, &P.sc->proj_error, true);
 }
@@ -308,7 +327,8 @@ __global__ void __launch_bounds__(kRedWarps * 32, 4) k_reduce_blocks(DeviceProbl
   const char* h_base = reinterpret_cast<const char*>(P.obs_h);
   const char* lm_base = reinterpret_cast<const char*>(P.lm_rec);
   const char* lmc_base = reinterpret_cast<const char*>(P.lm_recC);
-  constexpr int kGB = kObsG * 8, kHB = kObsH * 8, kLB = kLmRec * 8, kCB = kLmRecC * 8;
+  const char* gv_base = reinterpret_cast<const char*>(P.obs_gv);
+  constexpr int kGB = kObsG * 8, kHB = kObsH * 8, kLB = kLmRec * 8, kCB = kLmRecC * 8, kVB = kObsGv * 8;
   for (;;) {
     int it = 0;
     if (lane == 0) it = (int)atomicAdd(next_item, 1u);
@@ -343,11 +363,15 @@ __global__ void __launch_bounds__(kRedWarps * 32, 4) k_reduce_blocks(DeviceProbl
         uint32_t e0 = n0, e1 = n1, e2 = n2;
         entry(ld + 1, n0, n1, n2);
         reinterpret_cast<uint2*>(dst + Cfg::DATA)[lane] = make_uint2(e0, (kind == kItemDiagLm) ? e2 : e1);
-        if (kind == kItemOff || kind == kItemSym) {
+        if (L == 1 && (kind == kItemOff || kind == kItemSym)) {
+          // three sectors per entry: gv of both observations, X | rho of the landmark
+          stage_chunks<2, ST>(dst, 0, gv_base, kVB, e0, lane);
+          stage_chunks<2, ST>(dst, 4, gv_base, kVB, e1, lane);
+          stage_chunks<2, ST>(dst, 8, lm_base, kLB, e2, lane);
+        } else if (kind == kItemOff || kind == kItemSym) {
           stage_chunks<3, ST>(dst, 0, g_base, kGB, e0, lane);
           stage_chunks<3, ST>(dst, 6, g_base, kGB, e1, lane);
-          if (L == 3) stage_chunks<5, ST>(dst, 12, lm_base, kLB, e2, lane);
-          else stage_chunks<4, ST>(dst, 12, lm_base, kLB, e2, lane);
+          stage_chunks<5, ST>(dst, 12, lm_base, kLB, e2, lane);
         } else if (kind == kItemDiagObs) {
           stage_chunks<3, ST>(dst, 0, g_base, kGB, e0, lane);
           stage_chunks<2, ST>(dst, 6, h_base, kHB, e0, lane);
@@ -371,7 +395,7 @@ __global__ void __launch_bounds__(kRedWarps * 32, 4) k_reduce_blocks(DeviceProbl
       const bool valid = (kind == kItemDiagLm) ? (ids.y != kNoSlot) : (ids.x != kNoSlot);
       if (valid) {
         if (kind == kItemOff || kind == kItemSym) {
-          const double* lm = d + 12;
+          const double* lm = d + (L == 3 ? 12 : 8);
           const double rho = lm[3];
           double Ya[3], Yb[3];
           y_of(lm, rho, ti, Ya); y_of(lm, rho, tj, Yb);
@@ -385,16 +409,11 @@ __global__ void __launch_bounds__(kRedWarps * 32, 4) k_reduce_blocks(DeviceProbl
             for (int k = 0; k < 9; ++k) M[k] = -M[k];
             acc_kmk(acc, rho, Ya, Yb, M);
           } else {
-            // -V^-1 (K~_a^T g_a)(K~_b^T g_b)^T,  g = G u,  u = baseline reference sensor -> measuring sensor
-            const int cam_a = P.obs_cam ? (int)P.obs_cam[ids.x] : 0, cam_b = P.obs_cam ? (int)P.obs_cam[ids.y] : 0;
-            const double* twa = P.Tws + ((size_t)row_pose * P.n_cams + cam_a) * 12 + 9;
-            const double* twb = P.Tws + ((size_t)col_pose * P.n_cams + cam_b) * 12 + 9;
-            const double ua[3] = {lm[4] - twa[0], lm[5] - twa[1], lm[6] - twa[2]};
-            const double ub[3] = {lm[4] - twb[0], lm[5] - twb[1], lm[6] - twb[2]};
-            double ga[3], gb[3], pa[6], pb[6];
-            sym3_vec(d, ua, ga); sym3_vec(d + 6, ub, gb);
-            kt_vec(rho, Ya, ga, pa); kt_vec(rho, Yb, gb, pb);
-            const double vi = lm[7];
+            // -V^-1 (K~_a^T g_a)(K~_b^T g_b)^T,  g = G u (u = baseline reference sensor -> measuring sensor) and V^-1
+            // straight from the gv records
+            double pa[6], pb[6];
+            kt_vec(rho, Ya, d, pa); kt_vec(rho, Yb, d + 4, pb);
+            const double vi = d[3];
 #pragma unroll
             for (int r = 0; r < 6; ++r) {
               const double s = -vi * pa[r];
