@@ -1068,12 +1068,15 @@ struct bagpu_handle_s {
     return v;
   }
 
-  void backup_state() {
-    CU(cudaMemcpyAsync(d_bk_q.p, d_pose_q.p, sizeof(double) * 4 * n_poses, cudaMemcpyDeviceToDevice, st));
-    CU(cudaMemcpyAsync(d_bk_t.p, d_pose_t.p, sizeof(double) * 3 * n_poses, cudaMemcpyDeviceToDevice, st));
-    CU(cudaMemcpyAsync(d_bk_v.p, d_pose_v.p, sizeof(double) * 3 * n_poses, cudaMemcpyDeviceToDevice, st));
-    CU(cudaMemcpyAsync(d_bk_b.p, d_pose_b.p, sizeof(double) * 6 * n_poses, cudaMemcpyDeviceToDevice, st));
-    if (n_lms) {
+  bool outliers_cleared = false;   // k_update_landmarks zeroed lm_outliers for the evaluation that follows
+  void backup_state(bool poses = true, bool landmarks = true) {
+    if (poses) {
+      CU(cudaMemcpyAsync(d_bk_q.p, d_pose_q.p, sizeof(double) * 4 * n_poses, cudaMemcpyDeviceToDevice, st));
+      CU(cudaMemcpyAsync(d_bk_t.p, d_pose_t.p, sizeof(double) * 3 * n_poses, cudaMemcpyDeviceToDevice, st));
+      CU(cudaMemcpyAsync(d_bk_v.p, d_pose_v.p, sizeof(double) * 3 * n_poses, cudaMemcpyDeviceToDevice, st));
+      CU(cudaMemcpyAsync(d_bk_b.p, d_pose_b.p, sizeof(double) * 6 * n_poses, cudaMemcpyDeviceToDevice, st));
+    }
+    if (n_lms && landmarks) {
       CU(cudaMemcpyAsync(d_bk_lm_x.p, d_lm_x.p, sizeof(double) * 4 * n_lms, cudaMemcpyDeviceToDevice, st));
       CU(cudaMemcpyAsync(d_bk_rel.p, d_lm_reliable.p, n_lms, cudaMemcpyDeviceToDevice, st));
       CU(cudaMemcpyAsync(d_bk_outliers.p, d_lm_outliers.p, sizeof(uint32_t) * n_lms, cudaMemcpyDeviceToDevice, st));   // landmarks_copy carries num_outlier_residuals (cpp:1022,1062)
@@ -1095,7 +1098,8 @@ struct bagpu_handle_s {
   // EvaluateResiduals at the current state (cpp:144-274); returns the four sums
   void evaluate(double* e_proj, double* e_bin, double* e_un, double* e_in, cudaEvent_t mark = nullptr) {
     CU(cudaMemsetAsync(&d_sc.p->eval_proj, 0, 4 * sizeof(double), st));
-    launch_evaluate(P, G, &d_sc.p->eval_proj, nullptr, nullptr, 1, 1, st); if (n_obs) ++launches;
+    launch_evaluate(P, G, &d_sc.p->eval_proj, nullptr, nullptr, 1, outliers_cleared ? 2 : 1, st); if (n_obs) ++launches;
+    outliers_cleared = false;
     maha0_valid = false;   // overwritten with this state's values; valid for the next build only if the step is kept
     if (rank == 0) launch_other_evaluate(P, R, st, &launches);
     if (world > 1) allreduce_f64(&d_sc.p->eval_proj, 4);
@@ -1245,7 +1249,9 @@ struct bagpu_handle_s {
           }
         }
         CU(cudaEventRecord(ev[10], st));
-        backup_state();
+        // with apply_results the copy of the state is taken by the update kernels themselves
+        const bool lm_fused = n_lms > 0 && L > 0;
+        if (!opt.apply_results) backup_state();
         // "pre" evaluation: same state and weights as the build, so the build sums are reused;
         // only the binary error uses a different formula in EvaluateResiduals (quirk Q7).
         double pre_bin = 0;
@@ -1259,8 +1265,10 @@ struct bagpu_handle_s {
         summary.pre_solve_norm = pre_proj + pre_in + pre_bin + pre_un;
         if (opt.apply_results) {
           summary.delta_norm = std::sqrt(n2_dl_l) + std::sqrt(n2_dl_p);
-          launch_update_poses(P, d_dl_p.p, 1.0, st); ++launches;
-          launch_update_landmarks(P, d_dl_l.p, 1.0, st); if (n_lms && L) ++launches;
+          const StateBackup bk = {d_bk_q.p, d_bk_t.p, d_bk_v.p, d_bk_b.p, d_bk_lm_x.p, d_bk_rel.p, d_bk_outliers.p};
+          launch_update_poses(P, d_dl_p.p, 1.0, st, &bk); ++launches;
+          if (lm_fused) { launch_update_landmarks(P, d_dl_l.p, 1.0, st, &bk); ++launches; outliers_cleared = true; }
+          else backup_state(false, true);
           launch_pose_frames(P, st); ++launches;
         }
         evaluate(&e_proj, &e_bin, &e_un, &e_in, ev[11]);

@@ -114,8 +114,10 @@ void launch_back_substitute(const DeviceProblem& P, const uint2* tasks, int n_ta
                             double* delta_l, cudaStream_t st);
 void launch_evaluate(const DeviceProblem& P, int G, double* out_sum, double* res_out, double* maha_out, int write_maha0, int count_outliers,
                      cudaStream_t st);
-void launch_update_poses(const DeviceProblem& P, const double* delta_p, double coef, cudaStream_t st);
-void launch_update_landmarks(const DeviceProblem& P, const double* delta_l, double coef, cudaStream_t st);
+// the arrays the dogleg loop restores a rejected step from
+struct StateBackup { double *q, *t, *v, *b, *lm_x; uint8_t* rel; uint32_t* outliers; };
+void launch_update_poses(const DeviceProblem& P, const double* delta_p, double coef, cudaStream_t st, const StateBackup* bk = nullptr);
+void launch_update_landmarks(const DeviceProblem& P, const double* delta_l, double coef, cudaStream_t st, const StateBackup* bk = nullptr);
 void launch_mask_diagonal(const DeviceProblem& P, const uint8_t* mask_used, int global_flag, cudaStream_t st);
 void launch_dot(const DeviceProblem& P, const double* a, const double* b, size_t n, double* out, cudaStream_t st);   // overwrites *out
 void launch_axpby(double* out, double alpha, const double* x, double beta, const double* y, size_t n, cudaStream_t st);

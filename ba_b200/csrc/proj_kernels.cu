@@ -188,19 +188,20 @@ BA_D void back_term(const DeviceProblem& P, const LmRecCtx& c, int i, double* ac
   // the pose's pack for delta_p (launch_back_substitute)
   const int m = (int)P.obs_pose[i];
   if (m == c.ref_pose) return;
-  double y[3], tw[3], G[6], gy[3];
+  double y[3], tw[3];
   if (!k_times_pack(P.kd_pack + (size_t)m * kPosePack, c.X, c.rho, y, tw)) return;
-  load_G(P, i, G);
-  sym3_vec(G, y, gy);
   if (L == 3) {
+    double G[6], gy[3];
+    load_G(P, i, G);
+    sym3_vec(G, y, gy);
 #pragma unroll
     for (int k = 0; k < 3; ++k) acc[k] -= gy[k];
   } else {
-    if (P.n_cams > 1 && P.obs_cam) {
-      const double* t2 = P.Tws + ((size_t)m * P.n_cams + (int)P.obs_cam[i]) * 12 + 9;
-      tw[0] = t2[0]; tw[1] = t2[1]; tw[2] = t2[2];
-    }
-    acc[0] -= (c.tws_r[0] - tw[0]) * gy[0] + (c.tws_r[1] - tw[1]) * gy[1] + (c.tws_r[2] - tw[2]) * gy[2];
+    // u^T G y = (G u) . y: the 32-byte gv record of the observation instead of G and the two sensor positions
+    double g0, g1, g2, vi;
+    ld4(P.obs_gv + (size_t)i * kObsGv, g0, g1, g2, vi);
+    (void)vi;
+    acc[0] -= g0 * y[0] + g1 * y[1] + g2 * y[2];
   }
 }
 // landmark part and write-out, by one lane holding the landmark's sum
@@ -242,7 +243,7 @@ __global__ void __launch_bounds__(256) k_back_substitute_packed(DeviceProblem P,
     for (int k = 0; k < L; ++k) acc[k] = 0.0;
     if (on && lo >= 0) {
       LmRecCtx c;
-      load_lm_rec<L>(P, lm, c);
+      load_lm_rec<L, false>(P, lm, c);
       back_term<L>(P, c, i, acc);
     }
 #pragma unroll
@@ -272,7 +273,7 @@ __global__ void __launch_bounds__(256) k_back_substitute_long(DeviceProblem P, c
 #pragma unroll
     for (int k = 0; k < L; ++k) acc[k] = 0.0;
     LmRecCtx c;
-    load_lm_rec<L>(P, lm, c);
+    load_lm_rec<L, false>(P, lm, c);
     for (int i = s + lane; i < e; i += 32) back_term<L>(P, c, i, acc);
 #pragma unroll
     for (int k = 0; k < L; ++k) acc[k] = warp_sum(acc[k]);
@@ -308,9 +309,16 @@ __global__ void __launch_bounds__(256) k_evaluate(DeviceProblem P, double* out_s
 
 // ---------------------------------------------------------------------------------------
 // ApplyUpdate (cpp:84-139): poses and landmarks, coefficient `coef`
-__global__ void k_update_poses(DeviceProblem P, const double* delta_p, double coef) {
+// bk.q != nullptr: the state before the update goes to the backup arrays on the way (poses_copy / landmarks_copy,
+// cpp:1020-1023: one kernel instead of seven device-to-device copies)
+__global__ void k_update_poses(DeviceProblem P, const double* delta_p, double coef, StateBackup bk) {
   const int p = blockIdx.x * blockDim.x + threadIdx.x;
   if (p >= P.n_poses) return;
+  if (bk.q) {
+    for (int k = 0; k < 4; ++k) bk.q[4 * (size_t)p + k] = P.pose_q[4 * (size_t)p + k];
+    for (int k = 0; k < 3; ++k) { bk.t[3 * (size_t)p + k] = P.pose_t[3 * (size_t)p + k]; bk.v[3 * (size_t)p + k] = P.pose_v[3 * (size_t)p + k]; }
+    for (int k = 0; k < 6; ++k) bk.b[6 * (size_t)p + k] = P.pose_b[6 * (size_t)p + k];
+  }
   const int o = P.pose_opt[p];
   if (o < 0) return;
   const double* d = delta_p + (size_t)o * P.D;
@@ -328,12 +336,18 @@ __global__ void k_update_poses(DeviceProblem P, const double* delta_p, double co
 }
 
 template <int L>
-__global__ void k_update_landmarks(DeviceProblem P, const double* delta_l, double coef) {
+__global__ void k_update_landmarks(DeviceProblem P, const double* delta_l, double coef, StateBackup bk) {
   const int lm = blockIdx.x * blockDim.x + threadIdx.x;
   if (lm >= P.n_lms) return;
+  double* x = P.lm_x + 4 * (size_t)lm;
+  if (bk.lm_x) {
+    reinterpret_cast<double4*>(bk.lm_x)[lm] = *reinterpret_cast<const double4*>(x);
+    bk.rel[lm] = P.lm_reliable[lm];
+    bk.outliers[lm] = P.lm_outliers[lm];
+    P.lm_outliers[lm] = 0;      // the evaluation that follows recounts them (launch_evaluate, count_outliers = 2)
+  }
   const int o = P.lm_opt[lm];
   if (o < 0) return;
-  double* x = P.lm_x + 4 * (size_t)lm;
   if (L == 1) {
     const double d = delta_l[o] * coef;
     x[3] -= d;
@@ -471,20 +485,24 @@ void launch_back_substitute(const DeviceProblem& P, const uint2* tasks, int n_ta
 void launch_evaluate(const DeviceProblem& P, int G, double* out_sum, double* res_out, double* maha_out, int write_maha0, int count_outliers,
                      cudaStream_t st) {
   if (P.n_obs == 0) return;
-  if (count_outliers) cudaMemsetAsync(P.lm_outliers, 0, sizeof(uint32_t) * P.n_lms, st);
+  if (count_outliers == 1) cudaMemsetAsync(P.lm_outliers, 0, sizeof(uint32_t) * P.n_lms, st);   // 2: cleared by k_update_landmarks
   (void)G;
   const int grid = grid_for((size_t)P.n_obs, 256, 8);
   if (P.L == 1) k_evaluate<1><<<grid, 256, 0, st>>>(P, out_sum, res_out, maha_out, write_maha0, count_outliers);
   else k_evaluate<3><<<grid, 256, 0, st>>>(P, out_sum, res_out, maha_out, write_maha0, count_outliers);
 }
-void launch_update_poses(const DeviceProblem& P, const double* delta_p, double coef, cudaStream_t st) {
+void launch_update_poses(const DeviceProblem& P, const double* delta_p, double coef, cudaStream_t st, const StateBackup* bk) {
   if (P.n_poses == 0) return;
-  k_update_poses<<<(P.n_poses + 127) / 128, 128, 0, st>>>(P, delta_p, coef);
+  StateBackup b = {};
+  if (bk) b = *bk;
+  k_update_poses<<<(P.n_poses + 127) / 128, 128, 0, st>>>(P, delta_p, coef, b);
 }
-void launch_update_landmarks(const DeviceProblem& P, const double* delta_l, double coef, cudaStream_t st) {
+void launch_update_landmarks(const DeviceProblem& P, const double* delta_l, double coef, cudaStream_t st, const StateBackup* bk) {
   if (P.n_lms == 0 || P.L == 0) return;
-  if (P.L == 1) k_update_landmarks<1><<<(P.n_lms + 255) / 256, 256, 0, st>>>(P, delta_l, coef);
-  else k_update_landmarks<3><<<(P.n_lms + 255) / 256, 256, 0, st>>>(P, delta_l, coef);
+  StateBackup b = {};
+  if (bk) b = *bk;
+  if (P.L == 1) k_update_landmarks<1><<<(P.n_lms + 255) / 256, 256, 0, st>>>(P, delta_l, coef, b);
+  else k_update_landmarks<3><<<(P.n_lms + 255) / 256, 256, 0, st>>>(P, delta_l, coef, b);
 }
 void launch_mask_diagonal(const DeviceProblem& P, const uint8_t* mask_used, int global_flag, cudaStream_t st) {
   const int n_pad = P.nT * P.T;

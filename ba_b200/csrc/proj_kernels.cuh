@@ -337,11 +337,11 @@ BA_D bool k_times_pack(const double* __restrict__ pk, const double* X, double rh
 }
 // what the kernels behind the build need of a landmark, from the record the linearisation wrote (state unchanged since)
 struct LmRecCtx { double X[3], rho, tws_r[3]; int ref_pose; };
-template <int L>
+template <int L, bool WITH_TWS = true>
 BA_D void load_lm_rec(const DeviceProblem& P, int lm, LmRecCtx& c) {
   const double* r = P.lm_rec + (size_t)lm * kLmRec;
   ld4(r, c.X[0], c.X[1], c.X[2], c.rho);
-  if (L == 1) { double vi; ld4(r + 4, c.tws_r[0], c.tws_r[1], c.tws_r[2], vi); (void)vi; }
+  if (L == 1 && WITH_TWS) { double vi; ld4(r + 4, c.tws_r[0], c.tws_r[1], c.tws_r[2], vi); (void)vi; }
   else { c.tws_r[0] = c.tws_r[1] = c.tws_r[2] = 0.0; }
   c.ref_pose = (int)P.lm_ref_pose[lm];
 }
