@@ -318,7 +318,8 @@ struct bagpu_handle_s {
   float phase_ms[BAGPU_PH_COUNT] = {0};
   float dev_sd_ms = 0;   // development aid (BAGPU_TIMING): device time of the steepest-descent section, not part of any reported phase
   uint64_t launches = 0;
-  cudaEvent_t ev[16];
+  cudaEvent_t ev[20];
+  float dev_update_ms = 0, dev_eval_ms = 0, dev_factor_ms = 0;   // BAGPU_TIMING: finer split of the step / solve phases
   bool ev_ok = false;
   bool keep_S_copy = false;
 
@@ -1100,6 +1101,7 @@ struct bagpu_handle_s {
     CU(cudaMemsetAsync(&d_sc.p->eval_proj, 0, 4 * sizeof(double), st));
     launch_evaluate(P, G, &d_sc.p->eval_proj, nullptr, nullptr, 1, outliers_cleared ? 2 : 1, st); if (n_obs) ++launches;
     outliers_cleared = false;
+    if (mark) CU(cudaEventRecord(ev[17], st));
     maha0_valid = false;   // overwritten with this state's values; valid for the next build only if the step is kept
     if (rank == 0) launch_other_evaluate(P, R, st, &launches);
     if (world > 1) allreduce_f64(&d_sc.p->eval_proj, 4);
@@ -1157,6 +1159,7 @@ struct bagpu_handle_s {
       chol_flag_pending = true;
     }
     summary.result = BAGPU_Success;
+    CU(cudaEventRecord(ev[18], st));
     if (n_al > 0) { launch_back_substitute(P, d_tasks.p, n_tasks, d_long_lms.p, n_long, d_gn_p.p, d_gn_l.p, st); launches += 1 + (n_tasks > 0) + (n_long > 0); }
     CU(cudaEventRecord(ev[9], st));
     // ONE host round trip for the whole Gauss-Newton step: the factorisation's failure flag and the two norms of the step come
@@ -1172,6 +1175,7 @@ struct bagpu_handle_s {
     chol_trace_dump();
     gn_norm2_p = v[0]; gn_norm2_l = v[1];
     float ms; cudaEventElapsedTime(&ms, ev[8], ev[9]); phase_ms[BAGPU_PH_SOLVE] += ms;
+    cudaEventElapsedTime(&ms, ev[8], ev[18]); dev_factor_ms += ms;
     if (f != 0) { summary.result = BAGPU_FactorizationError; return false; }
     return true;
   }
@@ -1271,7 +1275,9 @@ struct bagpu_handle_s {
           else backup_state(false, true);
           launch_pose_frames(P, st); ++launches;
         }
+        CU(cudaEventRecord(ev[16], st));
         evaluate(&e_proj, &e_bin, &e_un, &e_in, ev[11]);
+        { float ms; cudaEventElapsedTime(&ms, ev[10], ev[16]); dev_update_ms += ms; cudaEventElapsedTime(&ms, ev[16], ev[17]); dev_eval_ms += ms; }
         summary.post_solve_norm = e_proj + e_in + e_bin + e_un;
         tr.delta_p_norm = std::sqrt(n2_dl_p); tr.delta_l_norm = std::sqrt(n2_dl_l);
         { float ms; cudaEventElapsedTime(&ms, ev[10], ev[11]); phase_ms[BAGPU_PH_STEP] += ms; }
@@ -1382,7 +1388,7 @@ struct bagpu_handle_s {
   void solve(uint32_t max_iter, double gn_damping, bool error_increase_allowed) {
     trace.clear(); rec_dp.clear(); rec_dl.clear();
     for (float& m : phase_ms) m = 0;
-    dev_sd_ms = 0;
+    dev_sd_ms = 0; dev_update_ms = 0; dev_eval_ms = 0; dev_factor_ms = 0;
     launches = 0;
     summary.iterations = 0;
     if (n_raw == 0 && bin_p1.empty() && un_pose.empty() && imu_p1.empty()) return;
@@ -1428,6 +1434,8 @@ struct bagpu_handle_s {
       float sum = 0; for (int i = 0; i < BAGPU_PH_TOTAL; ++i) sum += phase_ms[i];
       fprintf(stderr, "[bagpu timing]   device: total %.3f ms, phases %.3f, steepest-descent section %.3f, rest (host round trips, vector kernels) %.3f over %u iterations\n",
               phase_ms[BAGPU_PH_TOTAL], sum, dev_sd_ms, phase_ms[BAGPU_PH_TOTAL] - sum - dev_sd_ms, summary.iterations);
+      fprintf(stderr, "[bagpu timing]   device: step = backup + update %.3f ms, evaluation kernel %.3f ms; solve = factorisation %.3f ms + back-substitution\n",
+              dev_update_ms, dev_eval_ms, dev_factor_ms);
     }
     if (!opt.keep_on_device) download_state();
     pcs.lap("download_state");

@@ -114,6 +114,11 @@ void launch_back_substitute(const DeviceProblem& P, const uint2* tasks, int n_ta
                             double* delta_l, cudaStream_t st);
 void launch_evaluate(const DeviceProblem& P, int G, double* out_sum, double* res_out, double* maha_out, int write_maha0, int count_outliers,
                      cudaStream_t st);
+// CTAs of `kernel` (block threads, smem dynamic shared bytes) that are resident on one SM at a time (occupancy API, cached).
+// The grid-stride kernels are launched as ONE full wave of resident CTAs: a grid of "8 per SM" of a kernel of which 6 fit
+// runs its last 2 per SM alone at a quarter of the occupancy, for as long as the first 6 took.
+int resident_ctas_per_sm(const void* kernel, int block, size_t smem = 0);
+
 // the arrays the dogleg loop restores a rejected step from
 struct StateBackup { double *q, *t, *v, *b, *lm_x; uint8_t* rel; uint32_t* outliers; };
 void launch_update_poses(const DeviceProblem& P, const double* delta_p, double coef, cudaStream_t st, const StateBackup* bk = nullptr);

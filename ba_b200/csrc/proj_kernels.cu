@@ -1,5 +1,7 @@
 // proj_kernels.cu — kernels and launchers for the projection part of the hot path.
 // See proj_kernels.cuh for the reference lines each kernel replaces.
+#include <mutex>
+#include <unordered_map>
 #include "proj_kernels.cuh"
 #include "launch.h"
 
@@ -416,9 +418,24 @@ __global__ void k_compact_bl(DeviceProblem P, double* out) {
 static int g_sms = 148;
 void set_sm_count(int n) { g_sms = n > 0 ? n : 148; }
 
-static inline int grid_for(size_t work_items, int block, int max_per_sm) {
+int resident_ctas_per_sm(const void* kernel, int block, size_t smem) {
+  static std::mutex mu;
+  static std::unordered_map<const void*, int> cache;
+  std::lock_guard<std::mutex> lock(mu);
+  auto it = cache.find(kernel);
+  if (it != cache.end()) return it->second;
+  int n = 0;
+  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, kernel, block, smem) != cudaSuccess || n < 1) n = 1;
+  cache[kernel] = n;
+  return n;
+}
+
+// one wave of resident CTAs (at most), never more than the fixed-order reductions have slots for
+template <typename K>
+static inline int grid_for(K kernel, size_t work_items, int block) {
   size_t b = (work_items + block - 1) / block;
-  size_t cap = (size_t)g_sms * max_per_sm;
+  size_t cap = (size_t)g_sms * resident_ctas_per_sm(reinterpret_cast<const void*>(kernel), block);
+  if (cap > (size_t)kRedMaxGrid) cap = kRedMaxGrid;
   if (b > cap) b = cap;
   if (b < 1) b = 1;
   return (int)b;
@@ -449,34 +466,32 @@ void launch_finish_xw(const DeviceProblem& P, double* lm_xw, cudaStream_t st) {
 void launch_residual(const DeviceProblem& P, int G, cudaStream_t st) {
   if (P.n_obs == 0) return;
   (void)G;
-  const int grid = grid_for((size_t)P.n_obs, 256, 8);
-  if (P.L == 1) k_residual<1><<<grid, 256, 0, st>>>(P); else k_residual<3><<<grid, 256, 0, st>>>(P);
+  if (P.L == 1) k_residual<1><<<grid_for(k_residual<1>, (size_t)P.n_obs, 256), 256, 0, st>>>(P);
+  else k_residual<3><<<grid_for(k_residual<3>, (size_t)P.n_obs, 256), 256, 0, st>>>(P);
 }
 void launch_jacobian_rows(const DeviceProblem& P, double* out, cudaStream_t st) {
   if (P.n_obs == 0 || P.L == 0) return;
-  const int grid = grid_for((size_t)P.n_obs, 128, 8);
-  if (P.L == 1) k_jacobian_rows<1><<<grid, 128, 0, st>>>(P, out); else k_jacobian_rows<3><<<grid, 128, 0, st>>>(P, out);
+  if (P.L == 1) k_jacobian_rows<1><<<grid_for(k_jacobian_rows<1>, (size_t)P.n_obs, 128), 128, 0, st>>>(P, out);
+  else k_jacobian_rows<3><<<grid_for(k_jacobian_rows<3>, (size_t)P.n_obs, 128), 128, 0, st>>>(P, out);
 }
 void launch_sd_denominator(const DeviceProblem& P, int G, cudaStream_t st) {
   if (P.n_obs == 0) return;
   (void)G;
   k_pose_delta_pack<<<(P.n_poses + 127) / 128, 128, 0, st>>>(P, P.b_p, P.kd_pack);
-  const int grid = grid_for((size_t)P.n_obs, 128, 12);
-  if (P.L == 1) k_sd_denominator<1><<<grid, 128, 0, st>>>(P); else k_sd_denominator<3><<<grid, 128, 0, st>>>(P);
+  if (P.L == 1) k_sd_denominator<1><<<grid_for(k_sd_denominator<1>, (size_t)P.n_obs, 128), 128, 0, st>>>(P);
+  else k_sd_denominator<3><<<grid_for(k_sd_denominator<3>, (size_t)P.n_obs, 128), 128, 0, st>>>(P);
 }
 void launch_back_substitute(const DeviceProblem& P, const uint2* tasks, int n_tasks, const uint32_t* long_lms, int n_long, const double* delta_p,
                             double* delta_l, cudaStream_t st) {
   if (P.n_active_lms == 0) return;
   k_pose_delta_pack<<<(P.n_poses + 127) / 128, 128, 0, st>>>(P, delta_p, P.kd_pack);
   if (n_tasks > 0) {
-    const int grid = grid_for((size_t)n_tasks * 32, 256, 8);
-    if (P.L == 1) k_back_substitute_packed<1><<<grid, 256, 0, st>>>(P, tasks, n_tasks, delta_l);
-    else k_back_substitute_packed<3><<<grid, 256, 0, st>>>(P, tasks, n_tasks, delta_l);
+    if (P.L == 1) k_back_substitute_packed<1><<<grid_for(k_back_substitute_packed<1>, (size_t)n_tasks * 32, 256), 256, 0, st>>>(P, tasks, n_tasks, delta_l);
+    else k_back_substitute_packed<3><<<grid_for(k_back_substitute_packed<3>, (size_t)n_tasks * 32, 256), 256, 0, st>>>(P, tasks, n_tasks, delta_l);
   }
   if (n_long > 0) {
-    const int grid = grid_for((size_t)n_long * 32, 256, 8);
-    if (P.L == 1) k_back_substitute_long<1><<<grid, 256, 0, st>>>(P, long_lms, n_long, delta_l);
-    else k_back_substitute_long<3><<<grid, 256, 0, st>>>(P, long_lms, n_long, delta_l);
+    if (P.L == 1) k_back_substitute_long<1><<<grid_for(k_back_substitute_long<1>, (size_t)n_long * 32, 256), 256, 0, st>>>(P, long_lms, n_long, delta_l);
+    else k_back_substitute_long<3><<<grid_for(k_back_substitute_long<3>, (size_t)n_long * 32, 256), 256, 0, st>>>(P, long_lms, n_long, delta_l);
   }
 }
 // count_outliers: EvaluateResiduals resets and recounts num_outlier_residuals (cpp:148-186); the read-out passes after
@@ -487,9 +502,8 @@ void launch_evaluate(const DeviceProblem& P, int G, double* out_sum, double* res
   if (P.n_obs == 0) return;
   if (count_outliers == 1) cudaMemsetAsync(P.lm_outliers, 0, sizeof(uint32_t) * P.n_lms, st);   // 2: cleared by k_update_landmarks
   (void)G;
-  const int grid = grid_for((size_t)P.n_obs, 256, 8);
-  if (P.L == 1) k_evaluate<1><<<grid, 256, 0, st>>>(P, out_sum, res_out, maha_out, write_maha0, count_outliers);
-  else k_evaluate<3><<<grid, 256, 0, st>>>(P, out_sum, res_out, maha_out, write_maha0, count_outliers);
+  if (P.L == 1) k_evaluate<1><<<grid_for(k_evaluate<1>, (size_t)P.n_obs, 256), 256, 0, st>>>(P, out_sum, res_out, maha_out, write_maha0, count_outliers);
+  else k_evaluate<3><<<grid_for(k_evaluate<3>, (size_t)P.n_obs, 256), 256, 0, st>>>(P, out_sum, res_out, maha_out, write_maha0, count_outliers);
 }
 void launch_update_poses(const DeviceProblem& P, const double* delta_p, double coef, cudaStream_t st, const StateBackup* bk) {
   if (P.n_poses == 0) return;
@@ -512,11 +526,11 @@ void launch_mask_diagonal(const DeviceProblem& P, const uint8_t* mask_used, int 
 }
 void launch_dot(const DeviceProblem& P, const double* a, const double* b, size_t n, double* out, cudaStream_t st) {
   if (n == 0) return;
-  k_dot<<<grid_for(n, 256, 4), 256, 0, st>>>(a, b, n, out, P.red_partial, P.red_counter);
+  k_dot<<<grid_for(k_dot, n, 256), 256, 0, st>>>(a, b, n, out, P.red_partial, P.red_counter);
 }
 void launch_axpby(double* out, double alpha, const double* x, double beta, const double* y, size_t n, cudaStream_t st) {
   if (n == 0) return;
-  k_axpby<<<grid_for(n, 256, 4), 256, 0, st>>>(out, alpha, x, beta, y, n);
+  k_axpby<<<grid_for(k_axpby, n, 256), 256, 0, st>>>(out, alpha, x, beta, y, n);
 }
 void launch_permute_tiles(double* dst, const double* src, const int* perm, int T, int nT, int forward, cudaStream_t st) {
   if (nT * T == 0) return;

@@ -627,13 +627,16 @@ static int sm_count_cached() {
 
 void launch_linearize(const DeviceProblem& P, const uint2* tasks, int n_tasks, const uint32_t* long_lms, int n_long, cudaStream_t st) {
   if (P.n_lms == 0 || P.L == 0) return;
-  const int cap = std::min(kRedMaxGrid, sm_count_cached() * 12);
+  // one wave of resident CTAs (launch.h, resident_ctas_per_sm): the warps stride over the tasks
+  auto cap_of = [&](const void* k) { return std::min(kRedMaxGrid, sm_count_cached() * resident_ctas_per_sm(k, 128)); };
   if (P.L == 1) k_lm_defaults<1><<<(P.n_lms + 255) / 256, 256, 0, st>>>(P); else k_lm_defaults<3><<<(P.n_lms + 255) / 256, 256, 0, st>>>(P);
   if (n_tasks > 0) {
+    const int cap = cap_of(P.L == 1 ? reinterpret_cast<const void*>(k_linearize_packed<1>) : reinterpret_cast<const void*>(k_linearize_packed<3>));
     const int grid = std::max(1, std::min(cap, (n_tasks + 3) / 4));
     if (P.L == 1) k_linearize_packed<1><<<grid, 128, 0, st>>>(P, tasks, n_tasks); else k_linearize_packed<3><<<grid, 128, 0, st>>>(P, tasks, n_tasks);
   }
   if (n_long > 0) {
+    const int cap = cap_of(P.L == 1 ? reinterpret_cast<const void*>(k_linearize_long<1>) : reinterpret_cast<const void*>(k_linearize_long<3>));
     const int grid = std::max(1, std::min(cap, (n_long + 3) / 4));
     if (P.L == 1) k_linearize_long<1><<<grid, 128, 0, st>>>(P, long_lms, n_long); else k_linearize_long<3><<<grid, 128, 0, st>>>(P, long_lms, n_long);
   }
