@@ -1106,11 +1106,10 @@ struct bagpu_handle_s {
     if (rank == 0) launch_other_evaluate(P, R, st, &launches);
     if (world > 1) allreduce_f64(&d_sc.p->eval_proj, 4);
     if (mark) CU(cudaEventRecord(mark, st));   // end of the step phase on the device: read with the same round trip
-    double v[4];
-    CU(cudaMemcpyAsync(v, &d_sc.p->eval_proj, 4 * sizeof(double), cudaMemcpyDeviceToHost, st));
-    sync();
-    *e_proj = v[0]; *e_bin = v[1]; *e_un = v[2]; *e_in = v[3];
+    last_eval = read_scalars();   // the whole block: the dogleg loop parks other sums in it (dot[4..5])
+    *e_proj = last_eval.eval_proj; *e_bin = last_eval.eval_binary; *e_un = last_eval.eval_unary; *e_in = last_eval.eval_inertial;
   }
+  Scalars last_eval;
 
   // development aid: BAGPU_CHOL_TRACE=<file> dumps the task table and 4 globaltimer stamps per task of the last solve
   DevBuf<unsigned long long> d_chol_trace;
@@ -1217,6 +1216,7 @@ struct bagpu_handle_s {
         if (iteration_count > opt.dogleg_max_inner_iterations) break;
         tr.inner_iterations = iteration_count;
         double n2_dl_p = 0, n2_dl_l = 0;
+        bool norms_pending = false;
         if (delta_sd_norm > trust_region && trust_region != -1.0) {
           const double f = trust_region / delta_sd_norm * factor;
           launch_axpby(d_dl_p.p, f, d_bp.p, 0, nullptr, np, st); if (np) ++launches;
@@ -1236,20 +1236,22 @@ struct bagpu_handle_s {
             if (nl) CU(cudaMemcpyAsync(d_dl_l.p, d_gn_l.p, sizeof(double) * nl, cudaMemcpyDeviceToDevice, st));
             n2_dl_p = gn_norm2_p; n2_dl_l = gn_norm2_l;
           } else {
-            // diff = gn - sd, formed explicitly like the reference (cpp:991-1017)
-            launch_axpby(d_tmp_p.p, 1.0, d_gn_p.p, -factor, d_bp.p, np, st); if (np) ++launches;
-            if (nl) { launch_axpby(d_tmp_l.p, 1.0, d_gn_l.p, -factor, d_bl_compact.p, nl, st); ++launches; }
-            double ap = 0, al = 0, bpp = 0, bll = 0;
-            dot_pair(d_tmp_p.p, d_tmp_p.p, np, d_tmp_l.p, d_tmp_l.p, nl, &ap, &al);
-            dot_pair(d_tmp_p.p, d_bp.p, np, d_tmp_l.p, d_bl_compact.p, nl, &bpp, &bll);
+            // diff = gn - sd, formed explicitly like the reference (cpp:991-1017); its two dot products in the same pass
+            launch_blend_diff(P, d_tmp_p.p, d_gn_p.p, d_bp.p, np, d_tmp_l.p, d_gn_l.p, d_bl_compact.p, nl, factor, &d_sc.p->dot[0], st); ++launches;
+            if (world > 1) allreduce_f64(&d_sc.p->dot[2], 2);   // the landmark parts are sums over the shards
+            double v4[4];
+            CU(cudaMemcpyAsync(v4, &d_sc.p->dot[0], 4 * sizeof(double), cudaMemcpyDeviceToHost, st));
+            sync();
+            const double ap = v4[0], bpp = v4[1], al = v4[2], bll = v4[3];
             const double a = ap + al;
             const double b = 2 * (factor * bpp + factor * bll);
             const double c = (factor * factor * n2_bp + factor * factor * n2_bl) - trust_region * trust_region;
             double beta = 0;
             if (b * b > 4 * a * c && a > 1e-10) beta = (-(b * b) + std::sqrt(b * b - 4 * a * c)) / (2 * a);   // quirk Q4
-            launch_axpby(d_dl_p.p, beta, d_tmp_p.p, factor, d_bp.p, np, st); if (np) ++launches;
-            if (nl) { launch_axpby(d_dl_l.p, beta, d_tmp_l.p, factor, d_bl_compact.p, nl, st); ++launches; }
-            dot_pair(d_dl_p.p, d_dl_p.p, np, d_dl_l.p, d_dl_l.p, nl, &n2_dl_p, &n2_dl_l);
+            // the step and its two norms; they come back with the scalars of the evaluation below
+            launch_blend_step(P, d_dl_p.p, d_tmp_p.p, d_bp.p, np, d_dl_l.p, d_tmp_l.p, d_bl_compact.p, nl, beta, factor, &d_sc.p->dot[4], st); ++launches;
+            if (world > 1) allreduce_f64(&d_sc.p->dot[5], 1);
+            norms_pending = true;
           }
         }
         CU(cudaEventRecord(ev[10], st));
@@ -1268,7 +1270,6 @@ struct bagpu_handle_s {
         }
         summary.pre_solve_norm = pre_proj + pre_in + pre_bin + pre_un;
         if (opt.apply_results) {
-          summary.delta_norm = std::sqrt(n2_dl_l) + std::sqrt(n2_dl_p);
           const StateBackup bk = {d_bk_q.p, d_bk_t.p, d_bk_v.p, d_bk_b.p, d_bk_lm_x.p, d_bk_rel.p, d_bk_outliers.p};
           launch_update_poses(P, d_dl_p.p, 1.0, st, &bk); ++launches;
           if (lm_fused) { launch_update_landmarks(P, d_dl_l.p, 1.0, st, &bk); ++launches; outliers_cleared = true; }
@@ -1278,6 +1279,8 @@ struct bagpu_handle_s {
         CU(cudaEventRecord(ev[16], st));
         evaluate(&e_proj, &e_bin, &e_un, &e_in, ev[11]);
         { float ms; cudaEventElapsedTime(&ms, ev[10], ev[16]); dev_update_ms += ms; cudaEventElapsedTime(&ms, ev[16], ev[17]); dev_eval_ms += ms; }
+        if (norms_pending) { n2_dl_p = last_eval.dot[4]; n2_dl_l = last_eval.dot[5]; }
+        if (opt.apply_results) summary.delta_norm = std::sqrt(n2_dl_l) + std::sqrt(n2_dl_p);
         summary.post_solve_norm = e_proj + e_in + e_bin + e_un;
         tr.delta_p_norm = std::sqrt(n2_dl_p); tr.delta_l_norm = std::sqrt(n2_dl_l);
         { float ms; cudaEventElapsedTime(&ms, ev[10], ev[11]); phase_ms[BAGPU_PH_STEP] += ms; }

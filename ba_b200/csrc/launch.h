@@ -121,6 +121,10 @@ int resident_ctas_per_sm(const void* kernel, int block, size_t smem = 0);
 
 // the arrays the dogleg loop restores a rejected step from
 struct StateBackup { double *q, *t, *v, *b, *lm_x; uint8_t* rel; uint32_t* outliers; };
+void launch_blend_diff(const DeviceProblem& P, double* tmp_p, const double* gn_p, const double* sd_p, size_t np, double* tmp_l, const double* gn_l,
+                       const double* sd_l, size_t nl, double f, double* out4, cudaStream_t st);
+void launch_blend_step(const DeviceProblem& P, double* dl_p, const double* tmp_p, const double* sd_p, size_t np, double* dl_l, const double* tmp_l,
+                       const double* sd_l, size_t nl, double beta, double f, double* out2, cudaStream_t st);
 void launch_update_poses(const DeviceProblem& P, const double* delta_p, double coef, cudaStream_t st, const StateBackup* bk = nullptr);
 void launch_update_landmarks(const DeviceProblem& P, const double* delta_l, double coef, cudaStream_t st, const StateBackup* bk = nullptr);
 void launch_mask_diagonal(const DeviceProblem& P, const uint8_t* mask_used, int global_flag, cudaStream_t st);

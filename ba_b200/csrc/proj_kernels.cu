@@ -394,6 +394,30 @@ __global__ void k_axpby(double* out, double alpha, const double* x, double beta,
   for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
     out[i] = alpha * x[i] + (y ? beta * y[i] : 0.0);
 }
+// Dogleg blend (cpp:991-1017), poses and landmarks in one pass each (index space [0, np) + [np, np + nl)):
+//   first half   tmp = gn - f sd, out = { |tmp_p|^2, tmp_p . sd_p, |tmp_l|^2, tmp_l . sd_l }
+//   second half  dl = beta tmp + f sd, out = { |dl_p|^2, |dl_l|^2 }
+// (two launches and one host round trip instead of ten launches and three)
+__global__ void __launch_bounds__(256) k_blend_diff(double* __restrict__ tmp_p, const double* __restrict__ gn_p, const double* __restrict__ sd_p, size_t np,
+                                                    double* __restrict__ tmp_l, const double* __restrict__ gn_l, const double* __restrict__ sd_l, size_t nl,
+                                                    double f, double* out, double* partial, unsigned int* counter) {
+  double acc[4] = {0.0, 0.0, 0.0, 0.0};
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < np + nl; i += (size_t)gridDim.x * blockDim.x) {
+    if (i < np) { const double s = sd_p[i], t = gn_p[i] - f * s; tmp_p[i] = t; acc[0] += t * t; acc[1] += t * s; }
+    else { const size_t j = i - np; const double s = sd_l[j], t = gn_l[j] - f * s; tmp_l[j] = t; acc[2] += t * t; acc[3] += t * s; }
+  }
+  grid_sum_fixed<4>(acc, partial, counter, out, false);
+}
+__global__ void __launch_bounds__(256) k_blend_step(double* __restrict__ dl_p, const double* __restrict__ tmp_p, const double* __restrict__ sd_p, size_t np,
+                                                    double* __restrict__ dl_l, const double* __restrict__ tmp_l, const double* __restrict__ sd_l, size_t nl,
+                                                    double beta, double f, double* out, double* partial, unsigned int* counter) {
+  double acc[2] = {0.0, 0.0};
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < np + nl; i += (size_t)gridDim.x * blockDim.x) {
+    if (i < np) { const double d = beta * tmp_p[i] + f * sd_p[i]; dl_p[i] = d; acc[0] += d * d; }
+    else { const size_t j = i - np; const double d = beta * tmp_l[j] + f * sd_l[j]; dl_l[j] = d; acc[1] += d * d; }
+  }
+  grid_sum_fixed<2>(acc, partial, counter, out, false);
+}
 // tile-wise permutation of a padded pose vector: forward (natural -> elimination order) or back
 __global__ void k_permute_tiles(double* dst, const double* src, const int* perm, int T, int nT, int forward) {
   const int idx = blockIdx.x * blockDim.x + threadIdx.x;
@@ -531,6 +555,14 @@ void launch_dot(const DeviceProblem& P, const double* a, const double* b, size_t
 void launch_axpby(double* out, double alpha, const double* x, double beta, const double* y, size_t n, cudaStream_t st) {
   if (n == 0) return;
   k_axpby<<<grid_for(k_axpby, n, 256), 256, 0, st>>>(out, alpha, x, beta, y, n);
+}
+void launch_blend_diff(const DeviceProblem& P, double* tmp_p, const double* gn_p, const double* sd_p, size_t np, double* tmp_l, const double* gn_l,
+                       const double* sd_l, size_t nl, double f, double* out4, cudaStream_t st) {
+  k_blend_diff<<<grid_for(k_blend_diff, np + nl, 256), 256, 0, st>>>(tmp_p, gn_p, sd_p, np, tmp_l, gn_l, sd_l, nl, f, out4, P.red_partial, P.red_counter);
+}
+void launch_blend_step(const DeviceProblem& P, double* dl_p, const double* tmp_p, const double* sd_p, size_t np, double* dl_l, const double* tmp_l,
+                       const double* sd_l, size_t nl, double beta, double f, double* out2, cudaStream_t st) {
+  k_blend_step<<<grid_for(k_blend_step, np + nl, 256), 256, 0, st>>>(dl_p, tmp_p, sd_p, np, dl_l, tmp_l, sd_l, nl, beta, f, out2, P.red_partial, P.red_counter);
 }
 void launch_permute_tiles(double* dst, const double* src, const int* perm, int T, int nT, int forward, cudaStream_t st) {
   if (nT * T == 0) return;

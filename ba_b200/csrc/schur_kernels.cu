@@ -338,8 +338,9 @@ __global__ void __launch_bounds__(kRedWarps * 32, 4) k_reduce_blocks(DeviceProbl
     const int kind = (int)w.kind;
     const bool diag = (kind == kItemDiagObs || kind == kItemDiagLm);
     const int row_pose = P.opt_to_pose[w.row], col_pose = P.opt_to_pose[w.col];
-    const double* ti = P.pose_t + 3 * (size_t)row_pose;
-    const double* tj = P.pose_t + 3 * (size_t)col_pose;
+    // positions of the two poses, once per item (the cp.async fences would make the compiler reload them every batch)
+    const double ti[3] = {P.pose_t[3 * (size_t)row_pose], P.pose_t[3 * (size_t)row_pose + 1], P.pose_t[3 * (size_t)row_pose + 2]};
+    const double tj[3] = {P.pose_t[3 * (size_t)col_pose], P.pose_t[3 * (size_t)col_pose + 1], P.pose_t[3 * (size_t)col_pose + 2]};
     double acc[kNAcc];
 #pragma unroll
     for (int k = 0; k < kNAcc; ++k) acc[k] = 0.0;
