@@ -291,7 +291,7 @@ def run_gpu_workload(name, args, K, W, rank, world, local_rank, with_e2e, with_c
             pass
         roofline = {"bound": "hbm", "kernel": dom, "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak, "traffic": traffic,
                     "algorithmic_bytes_per_launch": per_kernel[dom] / world, "launch_ms": kt[dom], "peak_source": peak_src,
-                    "note": "achieved = SURVEY 8d algorithmic bytes of this kernel / its CUDA-event time; the kernel gathers a 64-byte record per observation of a pose pair and 80 bytes of the landmark record from L2 (DESIGN.md 4)",
+                    "note": "achieved = SURVEY 8d algorithmic bytes of this kernel / its CUDA-event time; the kernel gathers per list entry the G records (64 B) of a pose pair's two observations and 80 B of the landmark record from L2 (LmSize 1, off-diagonal: two 32-byte gv records and 32 B of the landmark record); traffic is the ncu figure of the capture named in profiles/ncu_traffic.json (DESIGN.md 4)",
                     "build": {"algorithmic_bytes": tot_b / world, "ms": t_build, "achieved": tot_b / world / (t_build * 1e-3) / 1e9,
                               "frac": tot_b / world / (t_build * 1e-3) / 1e9 / peak, "kernel_ms": kt, "kernel_bytes": per_kernel, "nnzb_S": nnzb}}
     s.close()
