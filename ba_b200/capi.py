@@ -18,7 +18,7 @@ EXPORTS = [
     "set_landmarks", "set_proj_residuals", "set_unary_residuals", "set_binary_residuals",
     "set_imu_residuals", "solve", "build", "get_poses", "get_landmarks", "get_proj_residuals", "get_other_residuals",
     "get_trace", "get_deltas", "get_pattern", "get_system", "dump", "nccl_unique_id", "comm_init",
-    "get_phase_ms", "sync_state", "host_alloc", "host_free", "symbolic_tile_fill", "pack_warp_tasks", "build_work_items", "select_kth_static",
+    "get_phase_ms", "sync_state", "host_alloc", "host_free", "symbolic_tile_fill", "pack_warp_tasks", "build_work_items", "select_kth_static", "chol_task_plan",
 ]
 
 

@@ -2128,6 +2128,27 @@ int bagpu_symbolic_tile_fill(uint32_t nT, uint32_t n_edges, const uint32_t* ea, 
   return BAGPU_OK;
 }
 
+int bagpu_chol_task_plan(int tile_dim, uint32_t nT, const uint32_t* row_ptr, const uint32_t* row_col, int32_t* tasks8, uint32_t* n_tasks,
+                         int32_t* terms3, uint32_t* n_terms) {
+  if (!row_ptr || !n_tasks || !n_terms || (nT && row_ptr[nT] && !row_col)) return fail(BAGPU_ERR_INVALID, "null argument");
+  if (tile_dim != 48 && tile_dim != 72 && tile_dim != 120) return fail(BAGPU_ERR_INVALID, "tile_dim must be 48, 72 or 120");
+  GUARD(
+    std::vector<int> rp(row_ptr, row_ptr + nT + 1), rc(row_col, row_col + row_ptr[nT]);
+    for (uint32_t k = 0; k < nT; ++k)
+      for (int e = rp[k]; e < rp[k + 1]; ++e)
+        if (rc[e] <= (int)k || rc[e] >= (int)nT || (e > rp[k] && rc[e] <= rc[e - 1])) return fail(BAGPU_ERR_INVALID, "rows must list ascending columns above the diagonal");
+    std::vector<CholTask> tasks; std::vector<CholTerm> terms;
+    chol_build_plan(tile_dim, (int)nT, rp, rc, tasks, terms);
+    const bool fits = tasks.size() <= *n_tasks && terms.size() <= *n_terms && (tasks8 || tasks.empty()) && (terms3 || terms.empty());
+    *n_tasks = (uint32_t)tasks.size(); *n_terms = (uint32_t)terms.size();
+    if (!fits) return fail(BAGPU_ERR_INVALID, "task plan does not fit");
+    static_assert(sizeof(CholTask) == 8 * sizeof(int32_t) && sizeof(CholTerm) == 3 * sizeof(int32_t), "plan records are plain ints");
+    if (!tasks.empty()) memcpy(tasks8, tasks.data(), tasks.size() * sizeof(CholTask));
+    if (!terms.empty()) memcpy(terms3, terms.data(), terms.size() * sizeof(CholTerm));
+  )
+  return BAGPU_OK;
+}
+
 int bagpu_sync_state(bagpu_handle h) {
   if (!h) return fail(BAGPU_ERR_INVALID, "null handle");
   GUARD(h->ensure_device(); if (h->dirty) return fail(BAGPU_ERR_INVALID, "no solve yet"); h->download_state(); h->fetch_landmarks_host();)

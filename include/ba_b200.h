@@ -258,6 +258,17 @@ int bagpu_pack_warp_tasks(uint32_t n_lms, const uint32_t* starts, uint32_t lm_lo
                           uint32_t* task_count, uint32_t* n_tasks, uint32_t* long_lms, uint32_t* n_long);
 int bagpu_symbolic_tile_fill(uint32_t nT, uint32_t n_edges, const uint32_t* edge_a, const uint32_t* edge_b,
                              uint32_t* perm, uint32_t* row_ptr, uint32_t* row_col, uint32_t cap);
+/* Host-only, for tests: the task list of the dataflow factorisation + substitution kernel for a filled tile pattern
+ * (row_ptr / row_col as bagpu_symbolic_tile_fill returns them; tile_dim = 8 x PoseSize = 48, 72 or 120).  Replaces the
+ * elimination schedule inside Eigen::SimplicialLDLT (reference src/BundleAdjuster.cpp:748-833).  The CTAs of the kernel
+ * claim tasks in list order from one counter and wait on flags of other tasks' outputs, so the ORDER is what keeps the
+ * kernel free of deadlock; tests/test_symbolic_cpu.py replays it with a few workers.  Task = eight int32: kind (0 pivot
+ * tile: factor + invert, 1 off-diagonal tile: update + triangular solve, 2 backward tile product U_ij x_j, 4 backward
+ * chain of the dependent rows j .. i solved by one CTA), i, j, tile slot, first / end index of its update terms, 0, 0.
+ * Term = three int32: slots of U_ki and U_kj, row k.  Slots: row by row, the diagonal tile first (slot(k, k) = k +
+ * row_ptr[k]).  *n_tasks / *n_terms: capacity in, count out (BAGPU_ERR_INVALID if it does not fit). */
+int bagpu_chol_task_plan(int tile_dim, uint32_t nT, const uint32_t* row_ptr, const uint32_t* row_col, int32_t* tasks8,
+                         uint32_t* n_tasks, int32_t* terms3, uint32_t* n_terms);
 
 /* Allocation-free exact k-th order statistic (0-based; k = n / 2 is the value std::nth_element leaves at
  * errors_.begin() + n / 2, i.e. what the build calls the median).  NO COUNTERPART IN THE REFERENCE: added

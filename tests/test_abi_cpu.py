@@ -96,6 +96,26 @@ def test_no_cpu_fallback():
         assert "no CUDA device" in str(e.value)
 
 
+def test_static_select_validates_its_arguments_before_touching_the_device():
+    # bagpu_select_kth_static: sizes and pointers are checked on the host first (no device needed for the refusals)
+    L = capi.lib()
+    f = L.bagpu_select_kth_static
+    f.restype = C.c_int
+    f.argtypes = [C.c_void_p, C.c_uint64, C.c_uint64, C.c_void_p, C.c_void_p]
+    L.bagpu_last_error.restype = C.c_char_p
+    fake = C.c_void_p(256)                                              # never dereferenced by a refused call
+    hdr = open(os.path.join(ROOT, "include", "ba_b200.h")).read()
+    assert re.search(r"#define\s+BAGPU_SELECT_STATIC_MAX_N\s+\(1ull\s*<<\s*31\)", hdr)
+    for n, k, word in (((1 << 31) + 1, 0, b"BAGPU_SELECT_STATIC_MAX_N"), (0, 0, b"n = 0"), (5, 5, b"below n")):
+        assert f(fake, n, k, fake, None) == 1                           # BAGPU_ERR_INVALID
+        assert word in L.bagpu_last_error()
+    assert f(None, 5, 0, fake, None) == 1 and f(fake, 5, 0, None, None) == 1
+    assert b"null device pointer" in L.bagpu_last_error()
+    if not _has_gpu():
+        assert f(fake, 5, 0, fake, None) != 0                           # a valid request without a device fails loudly
+        assert b"bagpu_select_kth_static" in L.bagpu_last_error()
+
+
 def test_patterns_from_ids_need_no_device():
     # block patterns are symbolic (host): compare against a numpy derivation from the id arrays
     p = synth.make_c1(n_poses=8, n_landmarks=40, obs_per_lm=4, n_inactive_poses=2)

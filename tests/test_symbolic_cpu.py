@@ -86,6 +86,121 @@ def test_dissection_shortens_the_dependency_chain_of_a_banded_matrix():
     assert level.max() < nT // 4
 
 
+def _plan(T, row_ptr, row_col):
+    lib = capi.lib()
+    nT = len(row_ptr) - 1
+    rp = np.ascontiguousarray(row_ptr, np.uint32); rc = np.ascontiguousarray(row_col, np.uint32)
+    n_tiles = nT + len(rc)
+    cap_t = 3 * n_tiles + 8; cap_m = n_tiles * max(1, nT) + 8
+    tasks = np.zeros((cap_t, 8), np.int32); terms = np.zeros((cap_m, 3), np.int32)
+    nt = C.c_uint32(cap_t); nm = C.c_uint32(cap_m)
+    p = lambda a: a.ctypes.data_as(C.c_void_p)
+    ret = lib.bagpu_chol_task_plan(C.c_int(T), C.c_uint32(nT), p(rp), p(rc), p(tasks), C.byref(nt), p(terms), C.byref(nm))
+    assert ret == 0
+    return tasks[:nt.value].astype(int), terms[:nm.value].astype(int)
+
+
+def _replay(tasks, terms, row_ptr, row_col, near, workers):
+    """The kernel's scheduling rule on the host: `workers` CTAs claim tasks in list order from one counter; a CTA holds its
+    task until the flags it waits on are set by other tasks.  Returns the number of tasks completed (all of them, unless the
+    order can deadlock with this many CTAs)."""
+    nT = len(row_ptr) - 1
+    tile_done = set(); diag_done = set(); x_done = set(); row_count = np.zeros(nT, int)
+
+    def run(t):
+        kind, i, j, slot, lb, le = t[:6]
+        if kind in (0, 1):
+            for sa, sb, _k in terms[lb:le]:
+                while not (sa in tile_done and sb in tile_done):
+                    yield
+            if kind == 0:
+                diag_done.add(i)
+            else:
+                while i not in diag_done:
+                    yield
+                tile_done.add(slot)
+        elif kind == 2:
+            while slot not in tile_done:
+                yield
+            while j not in x_done:
+                yield
+            row_count[i] += 1
+        else:
+            hi, lo = i, j
+            while hi not in diag_done:
+                yield
+            for r in range(hi, lo - 1, -1):
+                cols = row_col[row_ptr[r]:row_ptr[r + 1]]
+                n_in = sum(1 for q, c in enumerate(cols) if q < near and c <= hi and c <= r + near)
+                for c in cols[:n_in]:
+                    assert c in x_done                                   # x of the near columns is the chain's own, already solved
+                while row_count[r] < len(cols) - n_in:
+                    yield
+                x_done.add(r)
+
+    nxt = 0; held = [None] * workers; finished = 0
+    while True:
+        progress = False
+        for w in range(workers):
+            if held[w] is None and nxt < len(tasks):
+                held[w] = run(tasks[nxt]); nxt += 1; progress = True
+            if held[w] is not None:
+                try:
+                    next(held[w])
+                except StopIteration:
+                    held[w] = None; finished += 1; progress = True
+        if not progress:
+            return finished, len(x_done)
+
+
+@pytest.mark.parametrize("case", range(6))
+@pytest.mark.parametrize("T", [48, 120])
+def test_task_plan_covers_every_tile_once_and_cannot_deadlock(case, T):
+    nT, edges = _graphs()[case]
+    _perm, row_ptr, row_col = _fill(nT, edges)
+    tasks, terms = _plan(T, row_ptr, row_col)
+    near = 3 if T <= 72 else 1
+    slot = {}
+    for k in range(nT):
+        slot[(k, k)] = k + row_ptr[k]
+        for q, c in enumerate(row_col[row_ptr[k]:row_ptr[k + 1]]):
+            slot[(k, int(c))] = k + row_ptr[k] + 1 + q
+    have = set(slot)
+    # factorisation: one task per stored tile, with its slot, and exactly the update terms of the left-looking rule
+    fact = [t for t in tasks if t[0] in (0, 1)]
+    assert sorted((t[1], t[2]) for t in fact) == sorted(have)
+    for kind, i, j, sl, lb, le, _a, _b in fact:
+        assert (kind == 0) == (i == j) and sl == slot[(i, j)]
+        want = sorted(k for k in range(i) if (k, i) in have and (k, j) in have)
+        assert sorted(terms[lb:le, 2].tolist()) == want
+        for sa, sb, k in terms[lb:le]:
+            assert sa == slot[(k, i)] and sb == slot[(k, j)]
+    # backward substitution: chains partition the rows, consecutive rows of a chain are coupled, every off-diagonal tile is
+    # either a tile task or one of the chain's near columns
+    chains = [t for t in tasks if t[0] == 4]
+    rows = []
+    for _k, hi, lo, *_ in chains:
+        assert 0 <= lo <= hi < nT and hi - lo + 1 <= 16
+        for r in range(lo, hi):
+            assert (r, r + 1) in have
+        rows += range(lo, hi + 1)
+    assert sorted(rows) == list(range(nT))
+    chain_hi = {}
+    for _k, hi, lo, *_ in chains:
+        for r in range(lo, hi + 1):
+            chain_hi[r] = hi
+    tile_tasks = sorted((t[1], t[2]) for t in tasks if t[0] == 2)
+    want = sorted((i, j) for (i, j) in have if i != j and not (j <= chain_hi[i] and j <= i + near
+                                                              and list(row_col[row_ptr[i]:row_ptr[i + 1]]).index(j) < near))
+    assert tile_tasks == want
+    assert len(tasks) == len(fact) + len(chains) + len(tile_tasks)
+    # the order: with as few as two CTAs every task completes (a task only ever waits for tasks that were claimed before it,
+    # or — the far tiles of a chain — for x the chain publishes while it descends)
+    for workers in (2, 3, 148):
+        done, solved = _replay(tasks, terms, row_ptr, row_col, near, workers)
+        assert done == len(tasks) and solved == nT, (workers, done, len(tasks))
+
+
 def _pack(starts, lo, hi):
     lib = capi.lib()
     starts = np.ascontiguousarray(starts, np.uint32)
