@@ -47,7 +47,7 @@ WORKLOADS = {
 def algorithmic_bytes(a, L, d, nnzb):
     """compulsory traffic of one fused, matrix-free build (J never stored), split over the
     kernels that carry it.  W blocks (6 x L doubles per pose-landmark pair) are written once by k_linearize and
-    read once by k_reduce_blocks; the records the kernels really move are larger (28 / 40 doubles),
+    read once by k_reduce_blocks; the records the kernels really move are larger (12 / 16 doubles per observation),
     which shows up as roofline.traffic > algorithmic bytes, not in `achieved`."""
     n_o = len(a["proj_z"]); n_l = len(a["lm_x_w"]); P = int(a["pose_active"].sum())
     n_pl = n_o if L == 3 else n_o + n_l
@@ -172,12 +172,12 @@ def trace_parity(gpu_trace, cpu_trace, n=2):
 
 def l2_note(name, scale):
     """Timing rule: inputs larger than L2, or say that they are not.  Per iteration the build streams the landmark-sorted
-    observations (40 B each), writes and re-reads a 96-byte linearisation per observation (G and h records) and one
-    128-byte record per landmark."""
+    observations (40 B each), writes and re-reads a 96-byte linearisation per observation (G and h records; 128 bytes with
+    the gv record of the inverse-depth configurations) and one 128-byte record per landmark."""
     n = make_counts(name) * scale
     if name == "c5":
         n = 0
-    mb = n * (40 + 8 + 96) / 1e6
+    mb = n * (40 + 8 + 96 + (32 if name in ("c1", "c3", "c4") else 0)) / 1e6
     if mb > 126:
         return "inputs larger than L2: every iteration streams %.0f MB of sorted observations and linearisation records (L2 = 126 MB)" % mb
     return ("working set of the build (%.0f MB) fits in L2, no flush between iterations: this configuration is "
